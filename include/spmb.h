@@ -1,0 +1,172 @@
+/*
+ * spmb.h -- C ABI of the B200-native online pattern-matching path (libspmb.so).
+ *
+ * The reference (rrahn/libspm) is a header-only C++20 template library with NO plugin/FFI
+ * boundary of its own; this header is the boundary a maintainer binds:
+ * every entry point names the reference interface it stands in for.  The C++ facade
+ * include/libspm_b200/spm.hpp re-creates the reference's spm:: names on top of it.
+ *
+ * Conventions: plain pointers and sizes only; symbols are 1 byte each holding the dna4
+ * rank 0..3 (libspm/libspm/seqan/alphabet.hpp:34-83,118 -- one spm::dna4 is one byte whose
+ * integral value is the rank); positions are 0-based, "end" is EXCLUSIVE like
+ * seqan2::endPosition(finder).  All functions return SPMB_OK (0) or an error code; the
+ * reference's entry points are noexcept and have no error channel
+ * (seqan_pattern_base.hpp:41,54,61,68), so any non-zero code is new information.
+ * A context is bound to one device and one CUDA stream and is used from one host thread at
+ * a time (a reference matcher is mutable state and not shareable either: concept.hpp:126-130).
+ * There is NO CPU fallback: without a CUDA device every call fails with SPMB_ERR_NO_DEVICE.
+ */
+#ifndef SPMB_H
+#define SPMB_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SPMB_VERSION 100
+
+enum {
+    SPMB_OK = 0,
+    SPMB_ERR_ARG = 1,         /* null pointer, bad size, unsorted journal ... */
+    SPMB_ERR_CUDA = 2,        /* a CUDA runtime call failed: see spmb_last_error() */
+    SPMB_ERR_OOM = 3,
+    SPMB_ERR_UNSUPPORTED = 4, /* pattern too long for the algorithm / store geometry */
+    SPMB_ERR_NO_DEVICE = 5
+};
+
+/* algorithms: the three searchers of the hot path */
+enum {
+    SPMB_ALG_HORSPOOL = 1, /* spm::horspool_matcher  libspm/libspm/matcher/horspool_matcher.hpp:20-44 */
+    SPMB_ALG_SHIFTOR = 2,  /* spm::shiftor_matcher   libspm/libspm/matcher/shiftor_matcher.hpp:20-44  */
+    SPMB_ALG_MYERS = 3     /* spm::myers_matcher     libspm/libspm/matcher/myers_matcher.hpp:19-60     */
+};
+
+typedef struct spmb_context spmb_context;
+typedef struct spmb_store spmb_store;
+typedef struct spmb_pattern spmb_pattern;
+typedef struct spmb_hits spmb_hits;
+typedef struct spmb_stream spmb_stream;
+
+/* One hit = what the reference's callback reads off the finder, plus what it hides:
+ * seqan2::endPosition(finder) -> end; seqan2::beginPosition(finder) -> end - m (exact only);
+ * errors is the edit distance of the best alignment ending there (the reference exposes it
+ * only through capture().errors, myers_matcher_restorable.hpp:57-59).
+ * Sorted by (pattern_id, seq_id, end) when handed back. */
+typedef struct spmb_hit {
+    uint64_t end;        /* exclusive end, in the coordinates of sequence seq_id */
+    uint32_t seq_id;     /* sequence / haplotype id (0 for a plain store) */
+    uint32_t pattern_id; /* index inside a pattern set (0 for a single pattern) */
+    uint32_t errors;     /* 0 for the exact searchers */
+    uint32_t reserved;
+} spmb_hit;
+
+/* journal event (a14; specs/journaled_sequence_class_diagram.drawio:196 record_sequence_edit):
+ * replace ref[ref_pos, ref_pos+del_len) by pool[ins_off, ins_off+ins_len).
+ * Events sorted by ref_pos, non-overlapping.  SNP = (p,1,1,off). */
+typedef struct spmb_journal_event {
+    uint64_t ref_pos;
+    uint32_t del_len;
+    uint32_t ins_len;
+    uint64_t ins_off;
+} spmb_journal_event;
+
+/* ---------------- library / context ---------------- */
+int spmb_version(void);
+const char *spmb_status_string(int status);
+/* stream: a cudaStream_t to enqueue on (NULL = the context creates its own). */
+int spmb_context_create(int device, void *stream, spmb_context **out);
+int spmb_context_destroy(spmb_context *ctx);
+void *spmb_context_stream(const spmb_context *ctx);
+const char *spmb_last_error(const spmb_context *ctx);
+int spmb_context_sync(spmb_context *ctx);
+
+/* ---------------- sequence store (north_star item 1) ----------------
+ * Replaces the haystack argument of seqan_pattern_base::operator()
+ * (seqan_pattern_base.hpp:40-47, wrapped by spm::seqan_container_adapter,
+ * libspm/libspm/seqan/container_adapter.hpp:23-100): instead of viewing host memory per call
+ * the sequence is packed once into 2 bits/symbol in HBM ("strided bit planes").
+ * row_len = 0 lets the library choose the geometry. */
+int spmb_store_create(spmb_context *ctx, const uint8_t *host_ranks, uint64_t n, uint32_t row_len,
+                      spmb_store **out);
+int spmb_store_create_from_device(spmb_context *ctx, const uint8_t *dev_ranks, uint64_t n,
+                                  uint32_t row_len, spmb_store **out);
+/* journaled sequence: base + events, materialised on the device into a new packed store whose
+ * coordinates are those of the derived sequence. */
+int spmb_store_create_journaled(spmb_context *ctx, const spmb_store *base,
+                                const spmb_journal_event *events, uint64_t n_events,
+                                const uint8_t *ins_pool, uint64_t pool_len, uint32_t row_len,
+                                spmb_store **out);
+int spmb_store_destroy(spmb_store *s);
+uint64_t spmb_store_length(const spmb_store *s);
+uint32_t spmb_store_row_len(const spmb_store *s);
+uint64_t spmb_store_device_bytes(const spmb_store *s);
+/* unpack [begin, begin+n) back to 1-byte ranks in host memory (round-trip checks). */
+int spmb_store_read(spmb_context *ctx, const spmb_store *s, uint64_t begin, uint64_t n,
+                    uint8_t *host_out);
+
+/* ---------------- patterns ----------------
+ * spmb_pattern_create == the matcher constructors
+ *   horspool_matcher{needle} / shiftor_matcher{needle} / myers_matcher{needle, k}
+ * (horspool_matcher.hpp:35-40, shiftor_matcher.hpp:35-40, myers_matcher.hpp:37-43).
+ * The needle is copied (the reference only views it). */
+int spmb_pattern_create(spmb_context *ctx, int alg, const uint8_t *ranks, uint32_t m, uint32_t k,
+                        spmb_pattern **out);
+/* a set of n_patterns needles searched in one pass (config C5); lengths[i] symbols each,
+ * concatenated in ranks.  All must share ceil(len/32) for SPMB_ALG_MYERS. */
+int spmb_pattern_set_create(spmb_context *ctx, int alg, const uint8_t *ranks,
+                            const uint32_t *lengths, uint32_t n_patterns, uint32_t k,
+                            spmb_pattern **out);
+int spmb_pattern_destroy(spmb_pattern *p);
+/* spm::window_size(matcher): m for the exact searchers (seqan_pattern_base.hpp:97-99),
+ * m + k for Myers (myers_matcher.hpp:51-53); 0 for an empty needle. */
+uint32_t spmb_pattern_window_size(const spmb_pattern *p);
+uint32_t spmb_pattern_count(const spmb_pattern *p);
+
+/* ---------------- hits ---------------- */
+int spmb_hits_create(spmb_context *ctx, uint64_t capacity_hint, spmb_hits **out);
+int spmb_hits_destroy(spmb_hits *h);
+uint64_t spmb_hits_count(const spmb_hits *h);
+const spmb_hit *spmb_hits_data(const spmb_hits *h); /* host memory, valid until the next search */
+
+/* ---------------- search ----------------
+ * spmb_search == seqan_pattern_base::operator()(haystack, callback)
+ * (seqan_pattern_base.hpp:40-52): all hits of the pattern (set) in the store, ascending.
+ * launch enqueues the kernels on the context's stream and returns; finish waits, grows the
+ * hit buffer and re-runs if it overflowed, copies the hits back and sorts them. */
+int spmb_search_launch(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p, spmb_hits *h);
+int spmb_search_finish(spmb_context *ctx, spmb_hits *h);
+int spmb_search(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p, spmb_hits *h);
+/* the reference's call shape with a HOST haystack: upload + pack + search + hits back. */
+int spmb_search_host(spmb_context *ctx, const uint8_t *host_ranks, uint64_t n,
+                     const spmb_pattern *p, spmb_hits *h);
+/* number of kernel launches the last search enqueued (bench.py's gpu_launches). */
+uint32_t spmb_last_launch_count(const spmb_context *ctx);
+
+/* ---------------- resumable search (capture / restore) ----------------
+ * restorable_myers_matcher / restorable_shiftor_matcher
+ * (myers_matcher_restorable.hpp:57-63,72-82; shiftor_matcher_restorable.hpp:44-63):
+ * feed the haystack in chunks; the concatenated hit list equals the unchunked one.
+ * The state is the carried context (the last window_size-1 symbols + stream offset), which
+ * determines every later hit exactly. */
+int spmb_stream_create(spmb_context *ctx, const spmb_pattern *p, spmb_stream **out);
+int spmb_stream_destroy(spmb_stream *st);
+/* hits of this chunk; end positions are relative to the chunk start like the reference's
+ * fresh Finder on each chunk (myers_matcher_restorable_test.cpp:66-69) */
+int spmb_stream_feed(spmb_context *ctx, spmb_stream *st, const uint8_t *host_ranks, uint64_t n,
+                     spmb_hits *h);
+/* capture(): copies the state into buf (size query when buf==NULL); restore(): sets it. */
+int spmb_stream_capture(const spmb_stream *st, void *buf, size_t *size);
+int spmb_stream_restore(spmb_stream *st, const void *buf, size_t size);
+
+/* ---------------- measurement helpers ---------------- */
+/* INT32 ALU-pipe peak (LOP3 / IADD3 chains on all SMs), in 1e9 lane-instructions per second:
+ * the roofline denominator for the Myers kernels. */
+int spmb_measure_int_peak(spmb_context *ctx, double *lop3_gops, double *iadd3_gops);
+int spmb_device_info(spmb_context *ctx, int *sm_count, int *sm_clock_khz, uint64_t *mem_bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,371 @@
+"""libspm_b200 -- B200-native online pattern matching behind the libspm matcher API.
+
+This Python module is a thin ctypes binding of the C ABI in include/spmb.h (libspmb.so, built
+from libspm_b200/csrc by `make`), used by tests/ and bench.py.  The reference is a C++ library,
+so the user-facing host side is the C++ facade include/libspm_b200/spm.hpp; nothing here
+computes anything on the CPU.  If the CUDA library is missing or no GPU is present the calls
+fail loudly -- there is no fallback path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+__all__ = ["Context", "Store", "Pattern", "Hits", "Stream", "SpmbError", "HIT_DTYPE", "EVENT_DTYPE",
+           "ALG_HORSPOOL", "ALG_SHIFTOR", "ALG_MYERS", "lib", "lib_path"]
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "lib", "libspmb.so")
+
+ALG_HORSPOOL, ALG_SHIFTOR, ALG_MYERS = 1, 2, 3
+
+HIT_DTYPE = np.dtype([("end", "<u8"), ("seq_id", "<u4"), ("pattern_id", "<u4"), ("errors", "<u4"),
+                      ("reserved", "<u4")])
+EVENT_DTYPE = np.dtype([("ref_pos", "<u8"), ("del_len", "<u4"), ("ins_len", "<u4"), ("ins_off", "<u8")])
+
+# every symbol include/spmb.h declares (tests check the library exports all of them)
+EXPORTS = [
+    "spmb_version", "spmb_status_string", "spmb_context_create", "spmb_context_destroy",
+    "spmb_context_stream", "spmb_last_error", "spmb_context_sync", "spmb_store_create",
+    "spmb_store_create_from_device", "spmb_store_create_journaled", "spmb_store_destroy",
+    "spmb_store_length", "spmb_store_row_len", "spmb_store_device_bytes", "spmb_store_read",
+    "spmb_pattern_create", "spmb_pattern_set_create", "spmb_pattern_destroy",
+    "spmb_pattern_window_size", "spmb_pattern_count", "spmb_hits_create", "spmb_hits_destroy",
+    "spmb_hits_count", "spmb_hits_data", "spmb_search_launch", "spmb_search_finish", "spmb_search",
+    "spmb_search_host", "spmb_last_launch_count", "spmb_stream_create", "spmb_stream_destroy",
+    "spmb_stream_feed", "spmb_stream_capture", "spmb_stream_restore", "spmb_measure_int_peak",
+    "spmb_device_info",
+]
+
+
+class SpmbError(RuntimeError):
+    def __init__(self, code, where, detail=""):
+        self.code = code
+        super().__init__(f"{where}: status {code} ({_status(code)}) {detail}".strip())
+
+
+_lib = None
+
+
+def lib_path() -> str:
+    return _SO
+
+
+def lib():
+    """load libspmb.so (raises if it has not been built -- there is no fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_SO):
+            raise ImportError(f"{_SO} not found: build it with `make` (or __graft_entry__.build()); "
+                              "libspm_b200 has no CPU fallback")
+        L = C.CDLL(_SO)
+        vp, u64, u32, i32 = C.c_void_p, C.c_uint64, C.c_uint32, C.c_int
+        pp = C.POINTER(C.c_void_p)
+        sig = {
+            "spmb_version": (i32, []),
+            "spmb_status_string": (C.c_char_p, [i32]),
+            "spmb_context_create": (i32, [i32, vp, pp]),
+            "spmb_context_destroy": (i32, [vp]),
+            "spmb_context_stream": (vp, [vp]),
+            "spmb_last_error": (C.c_char_p, [vp]),
+            "spmb_context_sync": (i32, [vp]),
+            "spmb_store_create": (i32, [vp, vp, u64, u32, pp]),
+            "spmb_store_create_from_device": (i32, [vp, vp, u64, u32, pp]),
+            "spmb_store_create_journaled": (i32, [vp, vp, vp, u64, vp, u64, u32, pp]),
+            "spmb_store_destroy": (i32, [vp]),
+            "spmb_store_length": (u64, [vp]),
+            "spmb_store_row_len": (u32, [vp]),
+            "spmb_store_device_bytes": (u64, [vp]),
+            "spmb_store_read": (i32, [vp, vp, u64, u64, vp]),
+            "spmb_pattern_create": (i32, [vp, i32, vp, u32, u32, pp]),
+            "spmb_pattern_set_create": (i32, [vp, i32, vp, vp, u32, u32, pp]),
+            "spmb_pattern_destroy": (i32, [vp]),
+            "spmb_pattern_window_size": (u32, [vp]),
+            "spmb_pattern_count": (u32, [vp]),
+            "spmb_hits_create": (i32, [vp, u64, pp]),
+            "spmb_hits_destroy": (i32, [vp]),
+            "spmb_hits_count": (u64, [vp]),
+            "spmb_hits_data": (vp, [vp]),
+            "spmb_search_launch": (i32, [vp, vp, vp, vp]),
+            "spmb_search_finish": (i32, [vp, vp]),
+            "spmb_search": (i32, [vp, vp, vp, vp]),
+            "spmb_search_host": (i32, [vp, vp, u64, vp, vp]),
+            "spmb_last_launch_count": (u32, [vp]),
+            "spmb_stream_create": (i32, [vp, vp, pp]),
+            "spmb_stream_destroy": (i32, [vp]),
+            "spmb_stream_feed": (i32, [vp, vp, vp, u64, vp]),
+            "spmb_stream_capture": (i32, [vp, vp, C.POINTER(C.c_size_t)]),
+            "spmb_stream_restore": (i32, [vp, vp, C.c_size_t]),
+            "spmb_measure_int_peak": (i32, [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+            "spmb_device_info": (i32, [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(u64)]),
+        }
+        for name, (res, args) in sig.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def _status(code):
+    try:
+        return lib().spmb_status_string(code).decode()
+    except Exception:
+        return "?"
+
+
+def _ranks(a):
+    a = np.ascontiguousarray(a, dtype=np.uint8)
+    return a
+
+
+class Context:
+    """one device + one stream (spmb_context).  `stream` is a raw cudaStream_t (int) or None."""
+
+    def __init__(self, device: int = 0, stream: int | None = None):
+        self._h = C.c_void_p()
+        rc = lib().spmb_context_create(int(device), C.c_void_p(stream) if stream else None, C.byref(self._h))
+        if rc:
+            raise SpmbError(rc, "spmb_context_create")
+        self.device = device
+
+    def _check(self, rc, where):
+        if rc:
+            raise SpmbError(rc, where, (lib().spmb_last_error(self._h) or b"").decode())
+
+    def sync(self):
+        self._check(lib().spmb_context_sync(self._h), "spmb_context_sync")
+
+    @property
+    def stream(self) -> int:
+        return int(lib().spmb_context_stream(self._h) or 0)
+
+    @property
+    def last_launch_count(self) -> int:
+        return int(lib().spmb_last_launch_count(self._h))
+
+    def device_info(self):
+        sm, khz, mem = C.c_int(), C.c_int(), C.c_uint64()
+        self._check(lib().spmb_device_info(self._h, C.byref(sm), C.byref(khz), C.byref(mem)), "spmb_device_info")
+        return {"sm_count": sm.value, "sm_clock_khz": khz.value, "mem_bytes": mem.value}
+
+    def measure_int_peak(self):
+        a, b = C.c_double(), C.c_double()
+        self._check(lib().spmb_measure_int_peak(self._h, C.byref(a), C.byref(b)), "spmb_measure_int_peak")
+        return {"lop3_gops": a.value, "iadd3_gops": b.value}
+
+    def close(self):
+        if self._h:
+            lib().spmb_context_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Store:
+    """packed sequence in HBM (spmb_store)."""
+
+    def __init__(self, ctx: Context, handle):
+        self.ctx = ctx
+        self._h = handle
+
+    @classmethod
+    def from_host(cls, ctx: Context, ranks, row_len: int = 0):
+        r = _ranks(ranks)
+        h = C.c_void_p()
+        ctx._check(lib().spmb_store_create(ctx._h, r.ctypes.data, r.size, row_len, C.byref(h)), "spmb_store_create")
+        return cls(ctx, h)
+
+    @classmethod
+    def from_device(cls, ctx: Context, dev_ptr: int, n: int, row_len: int = 0):
+        h = C.c_void_p()
+        ctx._check(lib().spmb_store_create_from_device(ctx._h, C.c_void_p(dev_ptr), n, row_len, C.byref(h)),
+                   "spmb_store_create_from_device")
+        return cls(ctx, h)
+
+    def journaled(self, events, pool, row_len: int = 0):
+        ev = np.ascontiguousarray(events, dtype=EVENT_DTYPE)
+        pl = _ranks(pool)
+        h = C.c_void_p()
+        self.ctx._check(lib().spmb_store_create_journaled(self.ctx._h, self._h, ev.ctypes.data if ev.size else None,
+                                                          ev.size, pl.ctypes.data if pl.size else None, pl.size,
+                                                          row_len, C.byref(h)), "spmb_store_create_journaled")
+        return Store(self.ctx, h)
+
+    def __len__(self):
+        return int(lib().spmb_store_length(self._h))
+
+    @property
+    def row_len(self):
+        return int(lib().spmb_store_row_len(self._h))
+
+    @property
+    def device_bytes(self):
+        return int(lib().spmb_store_device_bytes(self._h))
+
+    def read(self, begin=0, n=None):
+        n = len(self) - begin if n is None else n
+        out = np.empty(n, dtype=np.uint8)
+        self.ctx._check(lib().spmb_store_read(self.ctx._h, self._h, begin, n, out.ctypes.data), "spmb_store_read")
+        return out
+
+    def close(self):
+        if self._h:
+            lib().spmb_store_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Pattern:
+    """compiled needle(s) (spmb_pattern) == horspool_matcher / shiftor_matcher / myers_matcher ctor."""
+
+    def __init__(self, ctx: Context, alg: int, needle, k: int = 0):
+        self.ctx = ctx
+        self._h = C.c_void_p()
+        if isinstance(needle, (list, tuple)) and len(needle) and not np.isscalar(needle[0]):
+            parts = [_ranks(p) for p in needle]
+            lens = np.array([p.size for p in parts], dtype=np.uint32)
+            cat = np.concatenate(parts) if parts else np.zeros(0, np.uint8)
+            ctx._check(lib().spmb_pattern_set_create(ctx._h, alg, cat.ctypes.data, lens.ctypes.data, len(parts), k,
+                                                     C.byref(self._h)), "spmb_pattern_set_create")
+        else:
+            r = _ranks(needle)
+            ctx._check(lib().spmb_pattern_create(ctx._h, alg, r.ctypes.data if r.size else None, r.size, k,
+                                                 C.byref(self._h)), "spmb_pattern_create")
+        self.alg, self.k = alg, k
+
+    @property
+    def window_size(self):
+        return int(lib().spmb_pattern_window_size(self._h))
+
+    @property
+    def count(self):
+        return int(lib().spmb_pattern_count(self._h))
+
+    def close(self):
+        if self._h:
+            lib().spmb_pattern_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Hits:
+    def __init__(self, ctx: Context, capacity: int = 0):
+        self.ctx = ctx
+        self._h = C.c_void_p()
+        ctx._check(lib().spmb_hits_create(ctx._h, capacity, C.byref(self._h)), "spmb_hits_create")
+
+    def __len__(self):
+        return int(lib().spmb_hits_count(self._h))
+
+    def array(self) -> np.ndarray:
+        n = len(self)
+        if n == 0:
+            return np.zeros(0, dtype=HIT_DTYPE)
+        ptr = lib().spmb_hits_data(self._h)
+        buf = (C.c_char * (n * HIT_DTYPE.itemsize)).from_address(ptr)
+        return np.frombuffer(buf, dtype=HIT_DTYPE, count=n).copy()
+
+    def close(self):
+        if self._h:
+            lib().spmb_hits_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def search(ctx: Context, store: Store, pattern: Pattern, hits: Hits | None = None) -> np.ndarray:
+    """seqan_pattern_base::operator(): all hits, sorted by (pattern_id, seq_id, end)."""
+    own = hits is None
+    hits = hits or Hits(ctx)
+    ctx._check(lib().spmb_search(ctx._h, store._h, pattern._h, hits._h), "spmb_search")
+    out = hits.array()
+    if own:
+        hits.close()
+    return out
+
+
+def search_launch(ctx: Context, store: Store, pattern: Pattern, hits: Hits):
+    ctx._check(lib().spmb_search_launch(ctx._h, store._h, pattern._h, hits._h), "spmb_search_launch")
+
+
+def search_finish(ctx: Context, hits: Hits) -> np.ndarray:
+    ctx._check(lib().spmb_search_finish(ctx._h, hits._h), "spmb_search_finish")
+    return hits.array()
+
+
+def search_host(ctx: Context, haystack, pattern: Pattern, hits: Hits | None = None, ptr: int | None = None,
+                n: int | None = None) -> np.ndarray:
+    """the reference's call shape: host haystack in, hits out (upload + pack + search)."""
+    own = hits is None
+    hits = hits or Hits(ctx)
+    if ptr is None:
+        r = _ranks(haystack)
+        ptr, n = r.ctypes.data, r.size
+    ctx._check(lib().spmb_search_host(ctx._h, C.c_void_p(ptr), n, pattern._h, hits._h), "spmb_search_host")
+    out = hits.array()
+    if own:
+        hits.close()
+    return out
+
+
+class Stream:
+    """resumable search (restorable_myers_matcher / restorable_shiftor_matcher)."""
+
+    def __init__(self, ctx: Context, pattern: Pattern):
+        self.ctx, self.pattern = ctx, pattern
+        self._h = C.c_void_p()
+        ctx._check(lib().spmb_stream_create(ctx._h, pattern._h, C.byref(self._h)), "spmb_stream_create")
+        self._hits = Hits(ctx)
+
+    def feed(self, chunk) -> np.ndarray:
+        r = _ranks(chunk)
+        self.ctx._check(lib().spmb_stream_feed(self.ctx._h, self._h, r.ctypes.data if r.size else None, r.size,
+                                               self._hits._h), "spmb_stream_feed")
+        return self._hits.array()
+
+    def capture(self) -> bytes:
+        sz = C.c_size_t(0)
+        lib().spmb_stream_capture(self._h, None, C.byref(sz))
+        buf = C.create_string_buffer(sz.value)
+        rc = lib().spmb_stream_capture(self._h, buf, C.byref(sz))
+        if rc:
+            raise SpmbError(rc, "spmb_stream_capture")
+        return bytes(buf.raw[:sz.value])
+
+    def restore(self, state: bytes):
+        rc = lib().spmb_stream_restore(self._h, state, len(state))
+        if rc:
+            raise SpmbError(rc, "spmb_stream_restore")
+
+    def close(self):
+        if self._h:
+            lib().spmb_stream_destroy(self._h)
+            self._h = C.c_void_p()
+        self._hits.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

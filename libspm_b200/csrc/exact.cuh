@@ -1,0 +1,211 @@
+// exact.cuh -- exact search kernel (serves SPMB_ALG_HORSPOOL and SPMB_ALG_SHIFTOR).
+//
+// Replaces the inner loops behind spm::horspool_matcher / spm::shiftor_matcher
+// (libspm/libspm/matcher/horspool_matcher.hpp:20-44, shiftor_matcher.hpp:20-44, both driven by
+// seqan_pattern_base::operator(), seqan_pattern_base.hpp:40-52).  Semantics kept: EVERY
+// occurrence, overlapping ones included, end = begin + m.  Control flow not kept: Horspool's
+// data-dependent skip and Shift-Or's serial D-word recurrence are both hostile to SIMT, and the
+// path is HBM-bound (0.25 B/bp), so the kernel is a bit-sliced shift-AND over ALIGNMENTS:
+//
+//   thread-row = 32 consecutive columns x 32 bit-rows = 1024 alignments.
+//   mismatch[c] |= f_sym_j(H[c+j], L[c+j])   for the first J<=8 pattern symbols j
+// where f_sym is ONE LOP3 whose truth table is picked by a warp-uniform switch on the pattern
+// symbol (text position p+j lives in column c+j, same bit: no shifts at all).  After J=8 steps
+// a random alignment survives with probability 4^-8; survivors (and all true hits) go to a
+// warp-cooperative verification of the remaining m-J symbols and are appended to the hit buffer
+// with one warp-aggregated atomic.
+//
+// Per thread-row: 20 coalesced LDG.128 + ~8.5 LOP3 per column  => ~0.3 instr / searched bp.
+#pragma once
+#include "layout.cuh"
+#include "hits.cuh"
+
+struct ExactArgs {
+    const uint4 *planes;     // packed store viewed as uint4 (two columns)
+    SpmbLayout lay;
+    uint64_t n_tiles;        // n_cols / 32 thread-rows
+    const uint8_t *pat;      // m ranks (device)
+    const uint32_t *row_len; // windows mode: valid symbols per row; else null
+    const uint32_t *row_seq; // windows mode: seq id per row; else null
+    uint32_t m;
+    uint32_t J;              // filter depth = min(m, 8)
+    uint32_t filt_syms;      // pattern symbol j at bits [2j, 2j+1], j < J
+    uint32_t seq_id;
+    uint32_t pattern_id;
+    HitSink sink;
+};
+
+// mismatch-accumulate for one filter step; SYM is a compile-time constant inside each case so
+// every line below is a single LOP3 with an immediate truth table.
+template <int SYM>
+__device__ __forceinline__ uint32_t exact_acc(uint32_t acc, uint32_t h, uint32_t l)
+{
+    if (SYM == 0) return acc | h | l;
+    if (SYM == 1) return acc | h | ~l;
+    if (SYM == 2) return acc | ~h | l;
+    return acc | ~h | ~l;
+}
+
+#define SPMB_EXACT_STEP(j)                                                                       \
+    if (J > (j)) {                                                                               \
+        switch ((fs >> (2 * (j))) & 3u) {                                                        \
+        case 0:  _Pragma("unroll") for (int c = 0; c < 32; ++c) acc[c] = exact_acc<0>(acc[c], H[c + (j)], L[c + (j)]); break; \
+        case 1:  _Pragma("unroll") for (int c = 0; c < 32; ++c) acc[c] = exact_acc<1>(acc[c], H[c + (j)], L[c + (j)]); break; \
+        case 2:  _Pragma("unroll") for (int c = 0; c < 32; ++c) acc[c] = exact_acc<2>(acc[c], H[c + (j)], L[c + (j)]); break; \
+        default: _Pragma("unroll") for (int c = 0; c < 32; ++c) acc[c] = exact_acc<3>(acc[c], H[c + (j)], L[c + (j)]); break; \
+        }                                                                                        \
+    }
+
+// Warp-cooperative verification of the candidates in one column word.
+// gc = global column, cm = candidate bits (bit b = row b).  Lane i checks pattern offsets
+// J+i, J+i+32, ...; returns the surviving candidate mask (same value in every lane).
+template <int MODE>
+__device__ __forceinline__ uint32_t exact_verify(const ExactArgs &a, uint64_t gc, uint32_t cm, uint32_t lane)
+{
+    const uint2 *P2 = reinterpret_cast<const uint2 *>(a.planes);
+    const uint32_t RL = a.lay.row_len;
+    uint64_t st = spmb_div_rl(a.lay, gc);
+    uint32_t col = (uint32_t)(gc - st * RL);
+    for (uint32_t j0 = a.J; j0 < a.m && cm; j0 += 32) {
+        uint32_t j = j0 + lane;
+        uint32_t mm = 0xffffffffu;
+        if (j < a.m) {
+            uint32_t x = col + j, wraps = 0;
+            if (x >= RL) { wraps = x / RL; x -= wraps * RL; }
+            uint32_t h, l;
+            if (wraps == 0) {
+                uint2 v = __ldg(P2 + spmb_perm(st * RL + x));
+                h = v.x; l = v.y;
+                uint32_t s = a.pat[j];
+                mm = ~((h ^ (0u - ((s >> 1) & 1u))) | (l ^ (0u - (s & 1u))));
+            } else if (MODE == SPMB_MODE_PLAIN) {
+                // the pattern runs off the row end: row r continues in row r+1 (next bit),
+                // row 31 continues in row 0 of the next super-tile
+                uint2 v0 = __ldg(P2 + spmb_perm(st * RL + x));
+                uint2 v1 = __ldg(P2 + spmb_perm((st + 1) * RL + x));
+                h = __funnelshift_r(v0.x, v1.x, wraps);
+                l = __funnelshift_r(v0.y, v1.y, wraps);
+                uint32_t s = a.pat[j];
+                mm = ~((h ^ (0u - ((s >> 1) & 1u))) | (l ^ (0u - (s & 1u))));
+            } else {
+                mm = 0; // windows do not continue: nothing can match past the row
+            }
+        }
+        cm &= __reduce_and_sync(0xffffffffu, mm);
+    }
+    return cm;
+}
+
+template <int MODE>
+__device__ __forceinline__ void exact_emit(const ExactArgs &a, uint64_t gc, uint32_t cm, uint32_t lane)
+{
+    const uint32_t RL = a.lay.row_len;
+    uint64_t st = spmb_div_rl(a.lay, gc);
+    uint32_t col = (uint32_t)(gc - st * RL);
+    uint64_t R = st * 32 + lane;
+    bool ok = (cm >> lane) & 1u;
+    uint64_t end;
+    uint32_t seq = a.seq_id;
+    if (MODE == SPMB_MODE_PLAIN) {
+        end = R * RL + col + a.m;
+        ok = ok && (end <= a.lay.n);
+    } else {
+        end = (uint64_t)col + a.m;
+        ok = ok && (R * RL < a.lay.n) && (end <= a.row_len[R]);
+        if (ok && a.row_seq) seq = a.row_seq[R];
+    }
+    uint32_t em = __ballot_sync(0xffffffffu, ok);
+    if (em == 0) return;
+    unsigned long long base = 0;
+    if (lane == 0) base = atomicAdd(a.sink.count, (unsigned long long)__popc(em));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (ok) {
+        unsigned long long idx = base + __popc(em & ((1u << lane) - 1u));
+        if (idx < a.sink.cap) {
+            spmb_hit hrec;
+            hrec.end = end; hrec.seq_id = seq; hrec.pattern_id = a.pattern_id; hrec.errors = 0; hrec.reserved = 0;
+            a.sink.hits[idx] = hrec;
+        }
+    }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(256, 2) exact_kernel(ExactArgs a)
+{
+    __shared__ uint32_t sbuf[8][32][33];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint64_t tile = (uint64_t)blockIdx.x * 256 + threadIdx.x;
+    const uint32_t J = a.J, fs = a.filt_syms;
+    const uint32_t RL = a.lay.row_len;
+    uint32_t acc[32];
+    uint32_t all = 0xffffffffu;
+
+    if (tile < a.n_tiles) {
+        uint32_t H[40], L[40];
+        // own thread-row: chunk k (columns 2k, 2k+1) of lane l sits at uint4 index blk*512 + k*32 + l
+        const uint4 *p = a.planes + (tile >> 5) * 512 + (tile & 31);
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            uint4 q = __ldg(p + k * 32);
+            H[2 * k] = q.x; L[2 * k] = q.y; H[2 * k + 1] = q.z; L[2 * k + 1] = q.w;
+        }
+        // halo: first 8 columns of the next thread-row
+        const uint64_t g0 = tile * 32;
+        const uint64_t st = spmb_div_rl(a.lay, g0);
+        const uint32_t col0 = (uint32_t)(g0 - st * RL);
+        if (col0 + 32 != RL) {
+            const uint4 *pn = a.planes + ((tile + 1) >> 5) * 512 + ((tile + 1) & 31);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                uint4 q = __ldg(pn + k * 32);
+                H[32 + 2 * k] = q.x; L[32 + 2 * k] = q.y; H[33 + 2 * k] = q.z; L[33 + 2 * k] = q.w;
+            }
+        } else if (MODE == SPMB_MODE_PLAIN) {
+            // last thread-row of a super-tile: row r continues in row r+1, i.e. the same
+            // columns 0..7 one bit up; row 31 continues in row 0 of the next super-tile.
+            const uint2 *P2 = reinterpret_cast<const uint2 *>(a.planes);
+#pragma unroll
+            for (int t = 0; t < 8; ++t) {
+                uint2 v0 = __ldg(P2 + spmb_perm(st * RL + t));
+                uint2 v1 = __ldg(P2 + spmb_perm((st + 1) * RL + t));
+                H[32 + t] = (v0.x >> 1) | (v1.x << 31);
+                L[32 + t] = (v0.y >> 1) | (v1.y << 31);
+            }
+        } else {
+#pragma unroll
+            for (int t = 0; t < 8; ++t) { H[32 + t] = 0; L[32 + t] = 0; }
+        }
+#pragma unroll
+        for (int c = 0; c < 32; ++c) acc[c] = 0;
+        SPMB_EXACT_STEP(0) SPMB_EXACT_STEP(1) SPMB_EXACT_STEP(2) SPMB_EXACT_STEP(3)
+        SPMB_EXACT_STEP(4) SPMB_EXACT_STEP(5) SPMB_EXACT_STEP(6) SPMB_EXACT_STEP(7)
+#pragma unroll
+        for (int c = 0; c < 32; ++c) all &= acc[c];
+    }
+
+    const bool cand = (all != 0xffffffffu);
+    uint32_t vote = __ballot_sync(0xffffffffu, cand);
+    if (vote == 0) return;
+
+    // ---- rare path: a lane saw a candidate ----
+    if (cand) {
+#pragma unroll
+        for (int c = 0; c < 32; ++c) sbuf[warp][lane][c] = acc[c];
+    }
+    __syncwarp();
+    while (vote) {
+        const int src = __ffs(vote) - 1;
+        vote &= vote - 1;
+        const uint64_t stile = __shfl_sync(0xffffffffu, tile, src);
+        const uint32_t w = ~sbuf[warp][src][lane]; // lane i: candidate bits of column i
+        uint32_t cvote = __ballot_sync(0xffffffffu, w != 0);
+        while (cvote) {
+            const int c = __ffs(cvote) - 1;
+            cvote &= cvote - 1;
+            uint32_t cm = __shfl_sync(0xffffffffu, w, c);
+            const uint64_t gc = stile * 32 + c;
+            cm = exact_verify<MODE>(a, gc, cm, lane);
+            if (cm) exact_emit<MODE>(a, gc, cm, lane);
+        }
+    }
+}

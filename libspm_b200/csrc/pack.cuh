@@ -1,0 +1,139 @@
+// pack.cuh -- kernels that build / read the packed store.
+//   pack_kernel<ByteSource>     1-byte dna4 ranks (a std::vector<spm::dna4> image)  -> strided bit planes
+//   pack_kernel<JournalSource>  base store + journal events (a14)                   -> planes of the derived sequence
+//   unpack_kernel               planes -> 1-byte ranks (round trips, tests)
+// One CTA (32 warps) produces one 1024-column block (8 KB); warp w owns thread-row w of the
+// block (32 columns).  Lane b reads the 32 symbols of its row for those columns, the warp
+// transposes them with ballots, the block is staged in shared memory in the permuted order and
+// written out as one coalesced 8 KB burst.
+#pragma once
+#include "layout.cuh"
+
+// symbol at absolute position p of a packed plain store
+__device__ __forceinline__ uint32_t spmb_symbol_at(const uint2 *__restrict__ planes, const SpmbLayout &lay,
+                                                   uint64_t p)
+{
+    uint64_t R = spmb_div_rl(lay, p);
+    uint32_t col = (uint32_t)(p - R * lay.row_len);
+    uint64_t g = (R >> 5) * lay.row_len + col;
+    uint2 w = __ldg(planes + spmb_perm(g));
+    uint32_t bit = (uint32_t)R & 31u;
+    return (((w.x >> bit) & 1u) << 1) | ((w.y >> bit) & 1u);
+}
+
+struct ByteSource {
+    const uint8_t *__restrict__ in;
+    uint64_t n;
+    // 32 symbols of one row starting at absolute position p0 (p0 % 32 == 0), packed 4 per word
+    __device__ __forceinline__ void load32(uint64_t p0, uint32_t (&w)[8]) const
+    {
+        if (p0 + 32 <= n && ((reinterpret_cast<uintptr_t>(in) & 15) == 0)) {
+            const uint4 *q = reinterpret_cast<const uint4 *>(in + p0);
+            uint4 a = __ldg(q), b = __ldg(q + 1);
+            w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w;
+            w[4] = b.x; w[5] = b.y; w[6] = b.z; w[7] = b.w;
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                uint32_t v = 0;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    uint64_t p = p0 + 4 * i + j;
+                    uint32_t s = (p < n) ? (uint32_t)in[p] : 0u;
+                    v |= (s & 3u) << (8 * j);
+                }
+                w[i] = v;
+            }
+        }
+    }
+};
+
+// journaled sequence: derived position d -> base symbol or inserted symbol.
+// ev_der[i] = derived position where event i's inserted segment begins (host prefix sum).
+struct JournalSource {
+    const uint2 *__restrict__ base_planes;
+    SpmbLayout base;
+    const uint64_t *__restrict__ ev_der;
+    const uint64_t *__restrict__ ev_ref;
+    const uint32_t *__restrict__ ev_del;
+    const uint32_t *__restrict__ ev_ins;
+    const uint64_t *__restrict__ ev_off;
+    const uint8_t *__restrict__ pool;
+    uint64_t n_ev;
+    uint64_t n; // derived length
+
+    __device__ __forceinline__ void load32(uint64_t d0, uint32_t (&w)[8]) const
+    {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) w[i] = 0;
+        if (d0 >= n) return;
+        // last event with ev_der <= d0  (idx in [-1, n_ev-1])
+        int64_t lo = -1, hi = (int64_t)n_ev - 1;
+        while (lo < hi) {
+            int64_t mid = (lo + hi + 1) >> 1;
+            if (ev_der[mid] <= d0) lo = mid; else hi = mid - 1;
+        }
+        int64_t e = lo;
+        uint64_t next_der = (e + 1 < (int64_t)n_ev) ? ev_der[e + 1] : ~0ull;
+        uint64_t seg_der = 0, seg_ref = 0, seg_off = 0;
+        uint32_t seg_ins = 0;
+        if (e >= 0) { seg_der = ev_der[e]; seg_ins = ev_ins[e]; seg_ref = ev_ref[e] + ev_del[e]; seg_off = ev_off[e]; }
+        for (int t = 0; t < 32; ++t) {
+            uint64_t d = d0 + t;
+            if (d >= n) break;
+            while (d >= next_der) { // enter the next event (several may start at the same d)
+                ++e;
+                seg_der = next_der; seg_ins = ev_ins[e]; seg_ref = ev_ref[e] + ev_del[e]; seg_off = ev_off[e];
+                next_der = (e + 1 < (int64_t)n_ev) ? ev_der[e + 1] : ~0ull;
+            }
+            uint32_t s;
+            uint64_t o = d - seg_der;
+            if (e >= 0 && o < seg_ins) s = pool[seg_off + o] & 3u;
+            else s = spmb_symbol_at(base_planes, base, (e >= 0) ? seg_ref + (o - seg_ins) : d);
+            w[t >> 2] |= s << (8 * (t & 3));
+        }
+    }
+};
+
+template <class Source>
+__global__ void __launch_bounds__(1024) pack_kernel(Source src, SpmbLayout lay, uint2 *__restrict__ planes)
+{
+    __shared__ uint2 tile[1024];
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint64_t g0 = (uint64_t)blockIdx.x * 1024 + warp * 32; // first column of this thread-row
+    uint32_t w[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) w[i] = 0;
+    if (g0 < lay.n_cols) {
+        uint64_t st = spmb_div_rl(lay, g0);
+        uint32_t col0 = (uint32_t)(g0 - st * lay.row_len);
+        uint64_t p0 = (st * 32 + lane) * (uint64_t)lay.row_len + col0;
+        if (p0 < lay.n) src.load32(p0, w);
+    }
+    uint32_t myH = 0, myL = 0;
+#pragma unroll
+    for (int c = 0; c < 32; ++c) {
+        uint32_t s = w[c >> 2] >> (8 * (c & 3));
+        uint32_t h = __ballot_sync(0xffffffffu, (s >> 1) & 1u);
+        uint32_t l = __ballot_sync(0xffffffffu, s & 1u);
+        if (lane == c) { myH = h; myL = l; }
+    }
+    // lane c holds column g0 + c  ->  permuted slot inside the block
+    tile[((lane >> 1) << 6) | (warp << 1) | (lane & 1)] = make_uint2(myH, myL);
+    __syncthreads();
+    planes[(uint64_t)blockIdx.x * 1024 + threadIdx.x] = tile[threadIdx.x];
+}
+
+__global__ void unpack_kernel(const uint2 *__restrict__ planes, SpmbLayout lay, uint64_t begin, uint64_t n,
+                              uint8_t *__restrict__ out)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[i] = (uint8_t)spmb_symbol_at(planes, lay, begin + i);
+}
+
+__global__ void zero_kernel(uint4 *p, uint64_t n16)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n16) p[i] = make_uint4(0, 0, 0, 0);
+}

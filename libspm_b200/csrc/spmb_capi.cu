@@ -1,0 +1,710 @@
+// spmb_capi.cu -- implementation of the C ABI declared in include/spmb.h.
+// Host-side plumbing only: owns device buffers, builds pattern tables, enqueues the kernels of
+// pack.cuh / exact.cuh / myers.cuh on the context's stream, brings the hit list back.
+// There is no CPU search path in this file: if no CUDA device is present every entry point
+// fails with SPMB_ERR_NO_DEVICE.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/spmb.h"
+#include "exact.cuh"
+#include "hits.cuh"
+#include "layout.cuh"
+#include "myers.cuh"
+#include "pack.cuh"
+
+// ------------------------------------------------------------------------------------------
+// objects
+// ------------------------------------------------------------------------------------------
+struct spmb_context {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    std::string err;
+    uint32_t launches = 0;
+    int sm_count = 0;
+    unsigned long long *h_count = nullptr; // pinned
+};
+
+struct spmb_store {
+    spmb_context *ctx = nullptr;
+    SpmbLayout lay{};
+    uint2 *planes = nullptr;
+    size_t bytes = 0;
+    // windows mode
+    uint32_t *row_len = nullptr, *row_seq = nullptr, *row_own = nullptr;
+};
+
+struct spmb_pattern {
+    spmb_context *ctx = nullptr;
+    int alg = 0;
+    uint32_t n_pat = 0, k = 0;
+    std::vector<uint32_t> len, off;   // per pattern
+    std::vector<uint8_t> ranks;       // host copy, concatenated
+    std::vector<uint32_t> filt;       // exact: packed first min(m,8) symbols
+    uint32_t max_m = 0, min_m = 0;
+    int NW = 0;                       // myers: 32-bit words
+    uint32_t warm = 0;                // myers: warm-up columns (multiple of 32)
+    uint8_t *d_ranks = nullptr;
+    uint32_t *d_eq = nullptr;
+    MyersPatMeta *d_meta = nullptr;
+};
+
+struct spmb_hits {
+    spmb_context *ctx = nullptr;
+    spmb_hit *d_hits = nullptr;
+    unsigned long long *d_count = nullptr;
+    unsigned long long cap = 0;
+    std::vector<spmb_hit> host;
+    uint64_t count = 0;
+    const spmb_store *pend_store = nullptr;
+    const spmb_pattern *pend_pat = nullptr;
+};
+
+struct spmb_stream {
+    spmb_context *ctx = nullptr;
+    const spmb_pattern *pat = nullptr;
+    uint64_t offset = 0;            // symbols consumed so far
+    std::vector<uint8_t> tail;      // last window_size-1 symbols
+    std::vector<uint8_t> scratch;
+};
+
+// ------------------------------------------------------------------------------------------
+// helpers
+// ------------------------------------------------------------------------------------------
+static int set_err(spmb_context *ctx, int code, const char *what, cudaError_t e = cudaSuccess)
+{
+    if (ctx) {
+        ctx->err = what ? what : "";
+        if (e != cudaSuccess) { ctx->err += ": "; ctx->err += cudaGetErrorString(e); }
+    }
+    return code;
+}
+
+#define CU(call)                                                                      \
+    do {                                                                              \
+        cudaError_t e__ = (call);                                                     \
+        if (e__ != cudaSuccess) {                                                     \
+            cudaGetLastError();                                                       \
+            return set_err(ctx, e__ == cudaErrorMemoryAllocation ? SPMB_ERR_OOM : SPMB_ERR_CUDA, #call, e__); \
+        }                                                                             \
+    } while (0)
+
+extern "C" int spmb_version(void) { return SPMB_VERSION; }
+
+extern "C" const char *spmb_status_string(int s)
+{
+    switch (s) {
+    case SPMB_OK: return "ok";
+    case SPMB_ERR_ARG: return "bad argument";
+    case SPMB_ERR_CUDA: return "CUDA error";
+    case SPMB_ERR_OOM: return "out of device memory";
+    case SPMB_ERR_UNSUPPORTED: return "unsupported pattern / geometry";
+    case SPMB_ERR_NO_DEVICE: return "no CUDA device (this library has no CPU path)";
+    default: return "unknown";
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// context
+// ------------------------------------------------------------------------------------------
+extern "C" int spmb_context_create(int device, void *stream, spmb_context **out)
+{
+    if (!out) return SPMB_ERR_ARG;
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return SPMB_ERR_NO_DEVICE; }
+    if (device < 0 || device >= ndev) return SPMB_ERR_ARG;
+    spmb_context *ctx = new (std::nothrow) spmb_context();
+    if (!ctx) return SPMB_ERR_OOM;
+    ctx->device = device;
+    if (cudaSetDevice(device) != cudaSuccess) { delete ctx; return SPMB_ERR_CUDA; }
+    if (stream) ctx->stream = (cudaStream_t)stream;
+    else {
+        if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return SPMB_ERR_CUDA; }
+        ctx->own_stream = true;
+    }
+    cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
+    if (cudaMallocHost(&ctx->h_count, sizeof(unsigned long long)) != cudaSuccess) { delete ctx; return SPMB_ERR_CUDA; }
+    *out = ctx;
+    return SPMB_OK;
+}
+
+extern "C" int spmb_context_destroy(spmb_context *ctx)
+{
+    if (!ctx) return SPMB_OK;
+    cudaSetDevice(ctx->device);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+    if (ctx->h_count) cudaFreeHost(ctx->h_count);
+    delete ctx;
+    return SPMB_OK;
+}
+
+extern "C" void *spmb_context_stream(const spmb_context *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
+extern "C" const char *spmb_last_error(const spmb_context *ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+extern "C" uint32_t spmb_last_launch_count(const spmb_context *ctx) { return ctx ? ctx->launches : 0; }
+
+extern "C" int spmb_context_sync(spmb_context *ctx)
+{
+    if (!ctx) return SPMB_ERR_ARG;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return SPMB_OK;
+}
+
+extern "C" int spmb_device_info(spmb_context *ctx, int *sm_count, int *sm_clock_khz, uint64_t *mem_bytes)
+{
+    if (!ctx) return SPMB_ERR_ARG;
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, ctx->device));
+    if (sm_count) *sm_count = prop.multiProcessorCount;
+    if (sm_clock_khz) { int khz = 0; cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, ctx->device); *sm_clock_khz = khz; }
+    if (mem_bytes) *mem_bytes = (uint64_t)prop.totalGlobalMem;
+    return SPMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// store
+// ------------------------------------------------------------------------------------------
+static int store_alloc(spmb_context *ctx, uint64_t n, uint32_t row_len, uint32_t mode, spmb_store **out)
+{
+    if (row_len == 0) row_len = spmb_auto_row_len(n);
+    if (row_len % 32 != 0 || row_len > 65536) return set_err(ctx, SPMB_ERR_ARG, "row_len must be a multiple of 32, <= 65536");
+    if (n >= (1ull << 41)) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "sequence too long");
+    spmb_store *s = new (std::nothrow) spmb_store();
+    if (!s) return SPMB_ERR_OOM;
+    s->ctx = ctx;
+    s->lay = spmb_make_layout(n, row_len, mode);
+    s->bytes = (size_t)s->lay.n_cols_alloc * sizeof(uint2);
+    cudaError_t e = cudaMalloc(&s->planes, s->bytes);
+    if (e != cudaSuccess) { cudaGetLastError(); delete s; return set_err(ctx, SPMB_ERR_OOM, "cudaMalloc(store)", e); }
+    *out = s;
+    return SPMB_OK;
+}
+
+template <class Source>
+static int store_pack(spmb_context *ctx, spmb_store *s, const Source &src)
+{
+    // every 1024-column block of the allocation is written (padding blocks become zeros)
+    unsigned blocks = (unsigned)(s->lay.n_cols_alloc / 1024);
+    pack_kernel<Source><<<blocks, 1024, 0, ctx->stream>>>(src, s->lay, s->planes);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    return SPMB_OK;
+}
+
+extern "C" int spmb_store_create_from_device(spmb_context *ctx, const uint8_t *dev_ranks, uint64_t n,
+                                             uint32_t row_len, spmb_store **out)
+{
+    if (!ctx || !out || (!dev_ranks && n)) return SPMB_ERR_ARG;
+    CU(cudaSetDevice(ctx->device));
+    spmb_store *s = nullptr;
+    int rc = store_alloc(ctx, n, row_len, SPMB_MODE_PLAIN, &s);
+    if (rc) return rc;
+    ByteSource src{dev_ranks, n};
+    rc = store_pack(ctx, s, src);
+    if (rc) { spmb_store_destroy(s); return rc; }
+    *out = s;
+    return SPMB_OK;
+}
+
+extern "C" int spmb_store_create(spmb_context *ctx, const uint8_t *host_ranks, uint64_t n, uint32_t row_len,
+                                 spmb_store **out)
+{
+    if (!ctx || !out || (!host_ranks && n)) return SPMB_ERR_ARG;
+    CU(cudaSetDevice(ctx->device));
+    uint8_t *d = nullptr;
+    CU(cudaMalloc(&d, n ? n : 1));
+    cudaError_t e = cudaMemcpyAsync(d, host_ranks, n, cudaMemcpyHostToDevice, ctx->stream);
+    if (e != cudaSuccess) { cudaFree(d); return set_err(ctx, SPMB_ERR_CUDA, "H2D haystack", e); }
+    int rc = spmb_store_create_from_device(ctx, d, n, row_len, out);
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(d);
+    return rc;
+}
+
+extern "C" int spmb_store_create_journaled(spmb_context *ctx, const spmb_store *base,
+                                           const spmb_journal_event *ev, uint64_t n_ev,
+                                           const uint8_t *pool, uint64_t pool_len, uint32_t row_len,
+                                           spmb_store **out)
+{
+    if (!ctx || !base || !out || (n_ev && !ev)) return SPMB_ERR_ARG;
+    if (base->lay.mode != SPMB_MODE_PLAIN) return set_err(ctx, SPMB_ERR_ARG, "journal base must be a plain store");
+    CU(cudaSetDevice(ctx->device));
+    // host: validate + prefix sums (derived start of every event)
+    std::vector<uint64_t> der(n_ev), ref(n_ev), off(n_ev);
+    std::vector<uint32_t> del(n_ev), ins(n_ev);
+    uint64_t r = 0;
+    int64_t shift = 0;
+    for (uint64_t i = 0; i < n_ev; ++i) {
+        if (ev[i].ref_pos < r || ev[i].ref_pos + ev[i].del_len > base->lay.n)
+            return set_err(ctx, SPMB_ERR_ARG, "journal events must be sorted, non-overlapping and inside the reference");
+        if ((uint64_t)ev[i].ins_off + ev[i].ins_len > pool_len)
+            return set_err(ctx, SPMB_ERR_ARG, "journal insertion outside the pool");
+        der[i] = (uint64_t)((int64_t)ev[i].ref_pos + shift);
+        ref[i] = ev[i].ref_pos; del[i] = ev[i].del_len; ins[i] = ev[i].ins_len; off[i] = ev[i].ins_off;
+        shift += (int64_t)ev[i].ins_len - (int64_t)ev[i].del_len;
+        r = ev[i].ref_pos + ev[i].del_len;
+    }
+    const uint64_t n_der = (uint64_t)((int64_t)base->lay.n + shift);
+    spmb_store *s = nullptr;
+    int rc = store_alloc(ctx, n_der, row_len, SPMB_MODE_PLAIN, &s);
+    if (rc) return rc;
+    uint64_t *d_der = nullptr, *d_ref = nullptr, *d_off = nullptr;
+    uint32_t *d_del = nullptr, *d_ins = nullptr;
+    uint8_t *d_pool = nullptr;
+    const size_t ne = n_ev ? n_ev : 1;
+    cudaError_t e = cudaSuccess;
+    if (e == cudaSuccess) e = cudaMalloc(&d_der, ne * 8);
+    if (e == cudaSuccess) e = cudaMalloc(&d_ref, ne * 8);
+    if (e == cudaSuccess) e = cudaMalloc(&d_off, ne * 8);
+    if (e == cudaSuccess) e = cudaMalloc(&d_del, ne * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&d_ins, ne * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&d_pool, pool_len ? pool_len : 1);
+    if (e == cudaSuccess && n_ev) {
+        e = cudaMemcpyAsync(d_der, der.data(), n_ev * 8, cudaMemcpyHostToDevice, ctx->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(d_ref, ref.data(), n_ev * 8, cudaMemcpyHostToDevice, ctx->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(d_off, off.data(), n_ev * 8, cudaMemcpyHostToDevice, ctx->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(d_del, del.data(), n_ev * 4, cudaMemcpyHostToDevice, ctx->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(d_ins, ins.data(), n_ev * 4, cudaMemcpyHostToDevice, ctx->stream);
+    }
+    if (e == cudaSuccess && pool_len) e = cudaMemcpyAsync(d_pool, pool, pool_len, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) {
+        JournalSource src{base->planes, base->lay, d_der, d_ref, d_del, d_ins, d_off, d_pool, n_ev, n_der};
+        rc = store_pack(ctx, s, src);
+        if (rc == SPMB_OK) e = cudaStreamSynchronize(ctx->stream);
+    }
+    cudaFree(d_der); cudaFree(d_ref); cudaFree(d_off); cudaFree(d_del); cudaFree(d_ins); cudaFree(d_pool);
+    if (e != cudaSuccess || rc) {
+        spmb_store_destroy(s);
+        return rc ? rc : set_err(ctx, SPMB_ERR_CUDA, "journal materialise", e);
+    }
+    *out = s;
+    return SPMB_OK;
+}
+
+extern "C" int spmb_store_destroy(spmb_store *s)
+{
+    if (!s) return SPMB_OK;
+    if (s->ctx) cudaSetDevice(s->ctx->device);
+    cudaFree(s->planes);
+    cudaFree(s->row_len);
+    cudaFree(s->row_seq);
+    cudaFree(s->row_own);
+    delete s;
+    return SPMB_OK;
+}
+
+extern "C" uint64_t spmb_store_length(const spmb_store *s) { return s ? s->lay.n : 0; }
+extern "C" uint32_t spmb_store_row_len(const spmb_store *s) { return s ? s->lay.row_len : 0; }
+extern "C" uint64_t spmb_store_device_bytes(const spmb_store *s) { return s ? s->bytes : 0; }
+
+extern "C" int spmb_store_read(spmb_context *ctx, const spmb_store *s, uint64_t begin, uint64_t n, uint8_t *host_out)
+{
+    if (!ctx || !s || (!host_out && n)) return SPMB_ERR_ARG;
+    if (s->lay.mode != SPMB_MODE_PLAIN) return set_err(ctx, SPMB_ERR_ARG, "read: plain stores only");
+    if (begin + n > s->lay.n) return set_err(ctx, SPMB_ERR_ARG, "read range outside the sequence");
+    if (n == 0) return SPMB_OK;
+    CU(cudaSetDevice(ctx->device));
+    uint8_t *d = nullptr;
+    CU(cudaMalloc(&d, n));
+    unsigned blocks = (unsigned)((n + 255) / 256);
+    unpack_kernel<<<blocks, 256, 0, ctx->stream>>>(s->planes, s->lay, begin, n, d);
+    ctx->launches++;
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(host_out, d, n, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d);
+    if (e != cudaSuccess) return set_err(ctx, SPMB_ERR_CUDA, "store_read", e);
+    return SPMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// patterns
+// ------------------------------------------------------------------------------------------
+extern "C" int spmb_pattern_set_create(spmb_context *ctx, int alg, const uint8_t *ranks, const uint32_t *lengths,
+                                       uint32_t n_pat, uint32_t k, spmb_pattern **out)
+{
+    if (!ctx || !out || !lengths || n_pat == 0) return SPMB_ERR_ARG;
+    if (alg != SPMB_ALG_HORSPOOL && alg != SPMB_ALG_SHIFTOR && alg != SPMB_ALG_MYERS) return SPMB_ERR_ARG;
+    CU(cudaSetDevice(ctx->device));
+    spmb_pattern *p = new (std::nothrow) spmb_pattern();
+    if (!p) return SPMB_ERR_OOM;
+    p->ctx = ctx; p->alg = alg; p->n_pat = n_pat; p->k = (alg == SPMB_ALG_MYERS) ? k : 0;
+    uint64_t total = 0;
+    p->max_m = 0; p->min_m = 0xffffffffu;
+    for (uint32_t i = 0; i < n_pat; ++i) {
+        p->off.push_back((uint32_t)total);
+        p->len.push_back(lengths[i]);
+        total += lengths[i];
+        p->max_m = std::max(p->max_m, lengths[i]);
+        p->min_m = std::min(p->min_m, lengths[i]);
+    }
+    if (total && !ranks) { delete p; return SPMB_ERR_ARG; }
+    if (total >= (1ull << 31)) { delete p; return set_err(ctx, SPMB_ERR_UNSUPPORTED, "pattern set too large"); }
+    p->ranks.assign(ranks, ranks + total);
+    for (auto &c : p->ranks) c &= 3;
+
+    cudaError_t e = cudaMalloc(&p->d_ranks, total ? total : 1);
+    if (e == cudaSuccess && total) e = cudaMemcpyAsync(p->d_ranks, p->ranks.data(), total, cudaMemcpyHostToDevice, ctx->stream);
+
+    if (alg == SPMB_ALG_MYERS) {
+        // an empty needle matches nothing (window_size 0): keep NW = 0 and never launch
+        if (p->max_m > 256) { spmb_pattern_destroy(p); return set_err(ctx, SPMB_ERR_UNSUPPORTED, "Myers needle longer than 256 symbols"); }
+        p->NW = (int)((p->max_m + 31) / 32);
+        for (uint32_t i = 0; i < n_pat; ++i)
+            if (p->len[i] && (int)((p->len[i] + 31) / 32) != p->NW) {
+                spmb_pattern_destroy(p);
+                return set_err(ctx, SPMB_ERR_UNSUPPORTED, "all needles of a Myers set must share ceil(m/32)");
+            }
+        if (p->NW > 0) {
+            const int NWP = p->NW <= 4 ? 4 : 8;
+            std::vector<uint32_t> eq((size_t)n_pat * 4 * NWP, 0);
+            std::vector<MyersPatMeta> meta(n_pat);
+            for (uint32_t i = 0; i < n_pat; ++i) {
+                const uint32_t m = p->len[i];
+                const uint8_t *pr = p->ranks.data() + p->off[i];
+                uint32_t *e4 = eq.data() + (size_t)i * 4 * NWP;
+                for (uint32_t j = 0; j < (uint32_t)p->NW * 32; ++j) {
+                    for (int c = 0; c < 4; ++c) {
+                        bool match = (j < m) ? (pr[j] == c) : true; // wildcard padding rows
+                        if (match) e4[c * NWP + j / 32] |= 1u << (j % 32);
+                    }
+                }
+                meta[i].m = m; meta[i].k = k; meta[i].pad = (uint32_t)p->NW * 32 - m; meta[i].pattern_id = i;
+            }
+            p->warm = (p->max_m + k - 1 + 31) / 32 * 32;
+            if (e == cudaSuccess) e = cudaMalloc(&p->d_eq, eq.size() * 4);
+            if (e == cudaSuccess) e = cudaMalloc(&p->d_meta, meta.size() * sizeof(MyersPatMeta));
+            if (e == cudaSuccess) e = cudaMemcpyAsync(p->d_eq, eq.data(), eq.size() * 4, cudaMemcpyHostToDevice, ctx->stream);
+            if (e == cudaSuccess) e = cudaMemcpyAsync(p->d_meta, meta.data(), meta.size() * sizeof(MyersPatMeta), cudaMemcpyHostToDevice, ctx->stream);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream); // host vectors go out of scope
+        }
+    } else {
+        for (uint32_t i = 0; i < n_pat; ++i) {
+            uint32_t fs = 0;
+            const uint32_t J = std::min<uint32_t>(p->len[i], 8);
+            for (uint32_t j = 0; j < J; ++j) fs |= (uint32_t)p->ranks[p->off[i] + j] << (2 * j);
+            p->filt.push_back(fs);
+        }
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) { spmb_pattern_destroy(p); return set_err(ctx, SPMB_ERR_CUDA, "pattern upload", e); }
+    *out = p;
+    return SPMB_OK;
+}
+
+extern "C" int spmb_pattern_create(spmb_context *ctx, int alg, const uint8_t *ranks, uint32_t m, uint32_t k,
+                                   spmb_pattern **out)
+{
+    return spmb_pattern_set_create(ctx, alg, ranks, &m, 1, k, out);
+}
+
+extern "C" int spmb_pattern_destroy(spmb_pattern *p)
+{
+    if (!p) return SPMB_OK;
+    if (p->ctx) cudaSetDevice(p->ctx->device);
+    cudaFree(p->d_ranks);
+    cudaFree(p->d_eq);
+    cudaFree(p->d_meta);
+    delete p;
+    return SPMB_OK;
+}
+
+extern "C" uint32_t spmb_pattern_window_size(const spmb_pattern *p)
+{
+    if (!p || p->max_m == 0) return 0;
+    return p->max_m + p->k;
+}
+extern "C" uint32_t spmb_pattern_count(const spmb_pattern *p) { return p ? p->n_pat : 0; }
+
+// ------------------------------------------------------------------------------------------
+// hits
+// ------------------------------------------------------------------------------------------
+static int hits_reserve(spmb_context *ctx, spmb_hits *h, unsigned long long cap)
+{
+    if (cap <= h->cap) return SPMB_OK;
+    cudaFree(h->d_hits);
+    h->d_hits = nullptr;
+    h->cap = 0;
+    CU(cudaMalloc(&h->d_hits, cap * sizeof(spmb_hit)));
+    h->cap = cap;
+    return SPMB_OK;
+}
+
+extern "C" int spmb_hits_create(spmb_context *ctx, uint64_t capacity_hint, spmb_hits **out)
+{
+    if (!ctx || !out) return SPMB_ERR_ARG;
+    CU(cudaSetDevice(ctx->device));
+    spmb_hits *h = new (std::nothrow) spmb_hits();
+    if (!h) return SPMB_ERR_OOM;
+    h->ctx = ctx;
+    cudaError_t e = cudaMalloc(&h->d_count, sizeof(unsigned long long));
+    if (e != cudaSuccess) { delete h; return set_err(ctx, SPMB_ERR_OOM, "cudaMalloc(hit counter)", e); }
+    int rc = hits_reserve(ctx, h, capacity_hint ? capacity_hint : (1ull << 16));
+    if (rc) { cudaFree(h->d_count); delete h; return rc; }
+    *out = h;
+    return SPMB_OK;
+}
+
+extern "C" int spmb_hits_destroy(spmb_hits *h)
+{
+    if (!h) return SPMB_OK;
+    if (h->ctx) cudaSetDevice(h->ctx->device);
+    cudaFree(h->d_hits);
+    cudaFree(h->d_count);
+    delete h;
+    return SPMB_OK;
+}
+
+extern "C" uint64_t spmb_hits_count(const spmb_hits *h) { return h ? h->count : 0; }
+extern "C" const spmb_hit *spmb_hits_data(const spmb_hits *h) { return (h && !h->host.empty()) ? h->host.data() : nullptr; }
+
+// ------------------------------------------------------------------------------------------
+// search
+// ------------------------------------------------------------------------------------------
+template <int MODE>
+static cudaError_t launch_myers(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p, const MyersArgs &a)
+{
+    dim3 grid((unsigned)((s->lay.n_st + 3) / 4), p->n_pat);
+    switch (p->NW) {
+    case 1: myers_kernel<1, MODE><<<grid, 128, 0, ctx->stream>>>(a); break;
+    case 2: myers_kernel<2, MODE><<<grid, 128, 0, ctx->stream>>>(a); break;
+    case 3: myers_kernel<3, MODE><<<grid, 128, 0, ctx->stream>>>(a); break;
+    case 4: myers_kernel<4, MODE><<<grid, 128, 0, ctx->stream>>>(a); break;
+    case 5: myers_kernel<5, MODE><<<grid, 128, 0, ctx->stream>>>(a); break;
+    case 6: myers_kernel<6, MODE><<<grid, 128, 0, ctx->stream>>>(a); break;
+    case 7: myers_kernel<7, MODE><<<grid, 128, 0, ctx->stream>>>(a); break;
+    case 8: myers_kernel<8, MODE><<<grid, 128, 0, ctx->stream>>>(a); break;
+    default: return cudaErrorInvalidValue;
+    }
+    ctx->launches++;
+    return cudaGetLastError();
+}
+
+static int enqueue_search(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p, spmb_hits *h)
+{
+    CU(cudaMemsetAsync(h->d_count, 0, sizeof(unsigned long long), ctx->stream));
+    HitSink sink{h->d_hits, h->d_count, h->cap};
+    if (p->max_m == 0 || s->lay.n == 0) return SPMB_OK; // empty needle / haystack: no hits
+    if (p->alg == SPMB_ALG_MYERS) {
+        if (p->n_pat > 65535) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "more than 65535 patterns in one Myers set");
+        MyersArgs a;
+        a.planes = reinterpret_cast<const uint4 *>(s->planes);
+        a.lay = s->lay;
+        a.eq = p->d_eq;
+        a.meta = p->d_meta;
+        a.row_len = s->row_len; a.row_seq = s->row_seq; a.row_own = s->row_own;
+        a.warm = p->warm;
+        a.seq_id = 0;
+        a.sink = sink;
+        cudaError_t e = (s->lay.mode == SPMB_MODE_PLAIN) ? launch_myers<SPMB_MODE_PLAIN>(ctx, s, p, a)
+                                                          : launch_myers<SPMB_MODE_WINDOWS>(ctx, s, p, a);
+        if (e != cudaSuccess) return set_err(ctx, SPMB_ERR_CUDA, "myers_kernel launch", e);
+        return SPMB_OK;
+    }
+    // exact searchers (Horspool and Shift-Or share the bit-sliced kernel)
+    if ((uint64_t)p->max_m > 31ull * s->lay.row_len)
+        return set_err(ctx, SPMB_ERR_UNSUPPORTED, "needle longer than 31 rows of this store");
+    for (uint32_t i = 0; i < p->n_pat; ++i) {
+        if (p->len[i] == 0) continue;
+        ExactArgs a;
+        a.planes = reinterpret_cast<const uint4 *>(s->planes);
+        a.lay = s->lay;
+        a.n_tiles = s->lay.n_cols / 32;
+        a.pat = p->d_ranks + p->off[i];
+        a.row_len = s->row_len; a.row_seq = s->row_seq;
+        a.m = p->len[i];
+        a.J = std::min<uint32_t>(a.m, 8);
+        a.filt_syms = p->filt[i];
+        a.seq_id = 0;
+        a.pattern_id = i;
+        a.sink = sink;
+        unsigned blocks = (unsigned)((a.n_tiles + 255) / 256);
+        if (s->lay.mode == SPMB_MODE_PLAIN) exact_kernel<SPMB_MODE_PLAIN><<<blocks, 256, 0, ctx->stream>>>(a);
+        else exact_kernel<SPMB_MODE_WINDOWS><<<blocks, 256, 0, ctx->stream>>>(a);
+        ctx->launches++;
+        CU(cudaGetLastError());
+    }
+    return SPMB_OK;
+}
+
+extern "C" int spmb_search_launch(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p, spmb_hits *h)
+{
+    if (!ctx || !s || !p || !h) return SPMB_ERR_ARG;
+    CU(cudaSetDevice(ctx->device));
+    ctx->launches = 0;
+    h->pend_store = s;
+    h->pend_pat = p;
+    return enqueue_search(ctx, s, p, h);
+}
+
+static bool hit_less(const spmb_hit &a, const spmb_hit &b)
+{
+    if (a.pattern_id != b.pattern_id) return a.pattern_id < b.pattern_id;
+    if (a.seq_id != b.seq_id) return a.seq_id < b.seq_id;
+    return a.end < b.end;
+}
+
+extern "C" int spmb_search_finish(spmb_context *ctx, spmb_hits *h)
+{
+    if (!ctx || !h || !h->pend_store) return SPMB_ERR_ARG;
+    CU(cudaSetDevice(ctx->device));
+    for (int attempt = 0; attempt < 4; ++attempt) {
+        CU(cudaMemcpyAsync(ctx->h_count, h->d_count, sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+        unsigned long long cnt = *ctx->h_count;
+        if (cnt <= h->cap) {
+            h->count = cnt;
+            h->host.resize(cnt);
+            if (cnt) {
+                CU(cudaMemcpyAsync(h->host.data(), h->d_hits, cnt * sizeof(spmb_hit), cudaMemcpyDeviceToHost, ctx->stream));
+                CU(cudaStreamSynchronize(ctx->stream));
+                std::sort(h->host.begin(), h->host.end(), hit_less);
+            }
+            h->pend_store = nullptr;
+            h->pend_pat = nullptr;
+            return SPMB_OK;
+        }
+        // overflow: the counter kept counting, so it is the exact size needed
+        int rc = hits_reserve(ctx, h, cnt + cnt / 8 + 1024);
+        if (rc) return rc;
+        rc = enqueue_search(ctx, h->pend_store, h->pend_pat, h);
+        if (rc) return rc;
+    }
+    return set_err(ctx, SPMB_ERR_CUDA, "hit buffer kept overflowing");
+}
+
+extern "C" int spmb_search(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p, spmb_hits *h)
+{
+    int rc = spmb_search_launch(ctx, s, p, h);
+    if (rc) return rc;
+    return spmb_search_finish(ctx, h);
+}
+
+extern "C" int spmb_search_host(spmb_context *ctx, const uint8_t *host_ranks, uint64_t n, const spmb_pattern *p,
+                                spmb_hits *h)
+{
+    if (!ctx || !p || !h || (!host_ranks && n)) return SPMB_ERR_ARG;
+    spmb_store *s = nullptr;
+    int rc = spmb_store_create(ctx, host_ranks, n, 0, &s);
+    if (rc) return rc;
+    uint32_t pack_launches = ctx->launches;
+    rc = spmb_search(ctx, s, p, h);
+    ctx->launches += pack_launches;
+    spmb_store_destroy(s);
+    return rc;
+}
+
+// ------------------------------------------------------------------------------------------
+// resumable search: the carried state is the last window_size-1 symbols
+// ------------------------------------------------------------------------------------------
+extern "C" int spmb_stream_create(spmb_context *ctx, const spmb_pattern *p, spmb_stream **out)
+{
+    if (!ctx || !p || !out) return SPMB_ERR_ARG;
+    if (p->n_pat != 1) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "streams take a single pattern");
+    spmb_stream *st = new (std::nothrow) spmb_stream();
+    if (!st) return SPMB_ERR_OOM;
+    st->ctx = ctx; st->pat = p;
+    *out = st;
+    return SPMB_OK;
+}
+
+extern "C" int spmb_stream_destroy(spmb_stream *st) { delete st; return SPMB_OK; }
+
+extern "C" int spmb_stream_feed(spmb_context *ctx, spmb_stream *st, const uint8_t *host_ranks, uint64_t n, spmb_hits *h)
+{
+    if (!ctx || !st || !h || (!host_ranks && n)) return SPMB_ERR_ARG;
+    const uint32_t ws = spmb_pattern_window_size(st->pat);
+    const size_t keep = ws ? ws - 1 : 0;
+    const size_t tl = st->tail.size();
+    st->scratch.resize(tl + n);
+    if (tl) memcpy(st->scratch.data(), st->tail.data(), tl);
+    if (n) memcpy(st->scratch.data() + tl, host_ranks, n);
+    int rc = spmb_search_host(ctx, st->scratch.data(), st->scratch.size(), st->pat, h);
+    if (rc) return rc;
+    // hits ending inside the carried context were reported by an earlier feed
+    size_t w = 0;
+    for (size_t i = 0; i < h->host.size(); ++i) {
+        if (h->host[i].end > tl) {
+            spmb_hit x = h->host[i];
+            x.end -= tl;
+            h->host[w++] = x;
+        }
+    }
+    h->host.resize(w);
+    h->count = w;
+    const size_t total = st->scratch.size();
+    const size_t nk = std::min(keep, total);
+    st->tail.assign(st->scratch.begin() + (total - nk), st->scratch.end());
+    st->offset += n;
+    return SPMB_OK;
+}
+
+extern "C" int spmb_stream_capture(const spmb_stream *st, void *buf, size_t *size)
+{
+    if (!st || !size) return SPMB_ERR_ARG;
+    const size_t need = 16 + st->tail.size();
+    if (!buf) { *size = need; return SPMB_OK; }
+    if (*size < need) { *size = need; return SPMB_ERR_ARG; }
+    uint64_t hdr[2] = {st->offset, (uint64_t)st->tail.size()};
+    memcpy(buf, hdr, 16);
+    if (!st->tail.empty()) memcpy((char *)buf + 16, st->tail.data(), st->tail.size());
+    *size = need;
+    return SPMB_OK;
+}
+
+extern "C" int spmb_stream_restore(spmb_stream *st, const void *buf, size_t size)
+{
+    if (!st || !buf || size < 16) return SPMB_ERR_ARG;
+    uint64_t hdr[2];
+    memcpy(hdr, buf, 16);
+    if (size < 16 + hdr[1]) return SPMB_ERR_ARG;
+    st->offset = hdr[0];
+    st->tail.assign((const uint8_t *)buf + 16, (const uint8_t *)buf + 16 + hdr[1]);
+    return SPMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// measurement helpers
+// ------------------------------------------------------------------------------------------
+extern "C" int spmb_measure_int_peak(spmb_context *ctx, double *lop3_gops, double *iadd3_gops)
+{
+    if (!ctx) return SPMB_ERR_ARG;
+    CU(cudaSetDevice(ctx->device));
+    uint32_t *d = nullptr;
+    CU(cudaMalloc(&d, 4));
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0));
+    CU(cudaEventCreate(&e1));
+    const int iters = 4000, blocks = ctx->sm_count * 8, threads = 256;
+    double res[2] = {0, 0};
+    for (int op = 0; op < 2; ++op) {
+        float best = 1e30f;
+        for (int rep = 0; rep < 4; ++rep) {
+            cudaEventRecord(e0, ctx->stream);
+            if (op == 0) int_peak_kernel<0><<<blocks, threads, 0, ctx->stream>>>(d, iters, 0x5a5a5a5au + rep);
+            else int_peak_kernel<1><<<blocks, threads, 0, ctx->stream>>>(d, iters, 0x5a5a5a5au + rep);
+            cudaEventRecord(e1, ctx->stream);
+            cudaError_t e = cudaEventSynchronize(e1);
+            if (e != cudaSuccess) { cudaFree(d); return set_err(ctx, SPMB_ERR_CUDA, "int peak probe", e); }
+            float ms = 0;
+            cudaEventElapsedTime(&ms, e0, e1);
+            if (rep > 0 && ms < best) best = ms;
+        }
+        double ops = (double)blocks * threads * (double)iters * 64.0;
+        res[op] = ops / (best * 1e-3) / 1e9;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(d);
+    if (lop3_gops) *lop3_gops = res[0];
+    if (iadd3_gops) *iadd3_gops = res[1];
+    return SPMB_OK;
+}
