@@ -1,0 +1,493 @@
+#!/usr/bin/env python
+"""bench.py -- searched Gbp/s of the online pattern-matching hot path on B200.
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU algorithms (oracle port)
+
+A "step" is one search pass (kernel launch -> sorted hit list on the host) over one resident
+sequence store.  Headline workload = BASELINE.json configs[1] at steady-state scale ("C2x"):
+Shift-Or exact search, m=64, over a journaled sequence (reference + 1% SNP/indel journal),
+N = 3.2 Gbp per GPU so that the packed text (0.25 B/bp = 800 MB) exceeds the 126 MB L2.
+The same line also carries the Myers k-error measurement (configs[2], "C3": m=100, k=4,
+250 Mbp) with its INT-pipe roofline, and the as-specified small configs C1/C2.
+Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+ALG_NAMES = {1: "horspool", 2: "shiftor", 3: "myers"}
+BYTES_PER_BP = 0.25                 # 2-bit packed text read once
+
+
+def myers_ops_per_bp(m):            # INT32 instructions per (bp x pattern), SURVEY.md 8(d)
+    return 10 * ((m + 31) // 32) + 4
+
+
+# ------------------------------------------------------------------------------------------
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)", d
+    return 6650.0, "fallback (B200_PROFILING.md)", {}
+
+
+def ncu_traffic(key):
+    """per-launch DRAM bytes of the dominant kernel from the committed ncu --set full capture."""
+    p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p)).get(key)
+        except Exception:
+            return None
+    return None
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons DURING the timed region (B200_PROFILING.md)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.lines = []
+        self.proc = None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "50", "-i", str(self.index)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _pump(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def __exit__(self, *a):
+        if self.proc:
+            time.sleep(0.06)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        sm, mx, reasons, pw = [], [], set(), []
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "samples": len(sm), "power_w_max": max(pw)}
+
+
+# ------------------------------------------------------------------------------------------
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def build_c2x(sp, synth, torch, ctx, dev, n, seed, m=64):
+    """reference (device RNG) + 1% journal (host RNG) -> base store + journaled store + pattern."""
+    ref = synth.text_device(n, seed, dev)
+    rng = np.random.default_rng(seed ^ 0xABCDEF)
+    pat = rng.integers(0, 4, size=m, dtype=np.uint8)
+    # plant copies of the needle at seeded reference offsets (about half survive the journal)
+    n_plant = 100
+    starts = np.sort(rng.integers(0, n - m, size=n_plant)).astype(np.int64)
+    idx = (torch.from_numpy(starts).to(dev)[:, None] + torch.arange(m, device=dev)[None, :]).reshape(-1)
+    ref[idx] = torch.from_numpy(np.tile(pat, n_plant)).to(dev)
+    ev, pool, kinds = synth.journal(n, seed)
+    snp_pos = torch.from_numpy(ev["ref_pos"][kinds == 0].astype(np.int64)).to(dev)
+    pool = synth.finish_snps(ev, pool, kinds, ref[snp_pos].cpu().numpy())
+    return ref, ev, pool, pat
+
+
+def time_search(sp, torch, ctx, stream, store, pattern, hits, steps, warmup, flush=None):
+    """returns (total_ms for `steps` launch+finish passes, mean kernel ms, n_hits, launches/step)."""
+    for _ in range(warmup):
+        if flush is not None:
+            flush.add_(1)
+        sp.search_launch(ctx, store, pattern, hits)
+        sp.search_finish(ctx, hits)
+    ks = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+    ke = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    flush_ms = 0.0
+    e0.record(stream)
+    n_hits = 0
+    for i in range(steps):
+        if flush is not None:
+            flush.add_(1)       # evict L2 between iterations (buffer > L2)
+        ks[i].record(stream)
+        sp.search_launch(ctx, store, pattern, hits)
+        ke[i].record(stream)
+        n_hits = len(sp.search_finish(ctx, hits))
+    e1.record(stream)
+    torch.cuda.synchronize()
+    kern = [ks[i].elapsed_time(ke[i]) for i in range(steps)]
+    total = e0.elapsed_time(e1)
+    if flush is not None:       # take the flush writes out of the step time
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record(stream)
+        for _ in range(steps):
+            flush.add_(1)
+        f1.record(stream)
+        torch.cuda.synchronize()
+        flush_ms = f0.elapsed_time(f1)
+    return max(total - flush_ms, 1e-6), float(np.mean(kern)), n_hits, ctx.last_launch_count
+
+
+def run_ours(args):
+    import torch
+    import libspm_b200 as sp
+    from libspm_b200 import synth
+
+    rank, world, local = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- libspm_b200 has no CPU path to measure")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    stream = torch.cuda.Stream(device=dev)
+    hbm_peak, peak_src, _ = measured_peaks()
+    out = {}
+    with torch.cuda.stream(stream):
+        ctx = sp.Context(local, stream=stream.cuda_stream)
+        hits = sp.Hits(ctx, 1 << 16)
+        n = args.n
+        m = 64
+        # ---------------- headline: C2x exact search over a journaled sequence ----------------
+        t0 = time.perf_counter()
+        ref, ev, pool, pat = build_c2x(sp, synth, torch, ctx, dev, n, synth.SEEDS["C2"] + rank, m)
+        host_ref = torch.empty(n, dtype=torch.uint8, pin_memory=True)
+        host_ref.copy_(ref)
+        torch.cuda.synchronize()
+        base = sp.Store.from_device(ctx, ref.data_ptr(), n)
+        ctx.sync()
+        del ref
+        torch.cuda.empty_cache()
+        j0, j1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        j0.record(stream)
+        js = base.journaled(ev, pool)
+        j1.record(stream)
+        torch.cuda.synchronize()
+        journal_ms = j0.elapsed_time(j1)
+        n_der = len(js)
+        pattern = sp.Pattern(ctx, sp.ALG_SHIFTOR, pat)
+        setup_s = time.perf_counter() - t0
+
+        if world > 1:
+            dist.barrier()
+        with ClockSampler(local) as clk:
+            total_ms, kern_ms, n_hits, launches = time_search(sp, torch, ctx, stream, js, pattern, hits,
+                                                              args.steps, args.warmup)
+        if world > 1:
+            t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            total_ms = float(t.item())
+        value = world * n_der * args.steps / (total_ms * 1e-3) / 1e9
+        achieved = n_der * BYTES_PER_BP / (kern_ms * 1e-3) / 1e9
+        out.update({
+            "metric": "searched_gbp_per_s", "value": value, "unit": "Gbp/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32",
+            "data": "synthetic",
+            "config": {"workload": "C2x: Shift-Or exact search m=64 over a journaled sequence "
+                                   f"({n} bp reference + 1% SNP/indel journal, {len(ev)} events) per GPU; "
+                                   "BASELINE configs[1] generator at steady-state scale",
+                       "searched_bp_per_step_per_gpu": n_der, "pattern_len": m, "hits": n_hits,
+                       "l2": f"inputs larger than L2 ({n_der * BYTES_PER_BP / 1e6:.0f} MB packed text vs 126 MB)",
+                       "row_len": js.row_len, "journal_materialise_ms": journal_ms,
+                       "step": "kernel launch + hit count/list D2H + host sort"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": achieved / hbm_peak, "traffic": ncu_traffic("exact_c2x"), "peak_source": peak_src,
+                         "kernel": "exact_kernel<plain>", "kernel_ms": kern_ms,
+                         "algorithmic_bytes_per_launch": n_der * BYTES_PER_BP},
+            "gpu_launches": launches * args.steps,
+            "clocks": clk.summary(),
+        })
+
+        # ---------------- e2e: host buffers -> hits through the C ABI ----------------
+        e2e_steps = max(1, min(args.steps, args.e2e_steps))
+        hp = host_ref.data_ptr()
+        ev_bytes = ev.nbytes + pool.nbytes
+
+        def e2e_once():
+            b2 = sp.Store(ctx, _store_from_ptr(sp, ctx, hp, n))
+            j2 = b2.journaled(ev, pool)
+            h = sp.search(ctx, j2, pattern, hits)
+            j2.close(); b2.close()
+            return len(h)
+
+        e2e_once()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            nh = e2e_once()
+        torch.cuda.synchronize()
+        e2e_s = time.perf_counter() - t0
+        if world > 1:
+            t = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            e2e_s = float(t.item())
+        out["e2e"] = {"value": world * n_der * e2e_steps / e2e_s / 1e9, "unit": "Gbp/s",
+                      "h2d_bytes_per_step": int(n + ev_bytes + m), "d2h_bytes_per_step": int(8 + nh * 24),
+                      "steps": e2e_steps, "ms_per_step": e2e_s / e2e_steps * 1e3,
+                      "path": "spmb_store_create(host ranks) + spmb_store_create_journaled + spmb_search"}
+        # resident-store e2e: the store is the persistent object; per step only the needle goes up
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            p2 = sp.Pattern(ctx, sp.ALG_SHIFTOR, pat)
+            nh = len(sp.search(ctx, js, p2, hits))
+            p2.close()
+        e2e_res_s = time.perf_counter() - t0
+        out["e2e_resident"] = {"value": world * n_der * args.steps / e2e_res_s / 1e9, "unit": "Gbp/s",
+                               "h2d_bytes_per_step": m, "d2h_bytes_per_step": int(8 + nh * 24),
+                               "path": "spmb_pattern_create(host needle) + spmb_search on the resident store"}
+
+        # ---------------- CPU baseline + cross-check (rank 0, N=1 only) ----------------
+        if rank == 0 and world == 1 and not args.no_cpu:
+            import oracle as orc
+            s_n = int(min(n_der, args.cpu_sample))
+            sample = js.read(0, s_n)
+            threads = orc.max_threads()
+            best = 1e30
+            for _ in range(3):
+                t0 = time.perf_counter()
+                cnt, ce, _ = orc.search_mt(2, sample, pat, 0, threads=threads)
+                best = min(best, time.perf_counter() - t0)
+            g = sp.search(ctx, js, pattern, hits)
+            ge = g["end"][g["end"] <= s_n]
+            out["cpu_baseline"] = {"value": s_n / best / 1e9, "unit": "Gbp/s", "cores": threads, "kind": "port",
+                                   "sample": f"first {s_n} bp of the derived sequence, oracle Shift-Or (32-bit blocks), "
+                                             f"{threads} threads, best of 3; journal already applied",
+                                   "hits_match_gpu": bool(np.array_equal(ge, ce))}
+            del sample
+        js.close(); base.close(); del host_ref
+
+        # ---------------- Myers k-error: C3 (m=100, k=4, 250 Mbp) ----------------
+        if not args.no_myers:
+            out["myers"] = bench_myers(sp, synth, torch, ctx, dev, stream, hits, args, rank, world, hbm_peak)
+        if rank == 0 and world == 1 and not args.no_small:
+            out["small_configs"] = bench_small(sp, synth, torch, ctx, dev, stream, hits, args)
+        out["setup_s"] = setup_s
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(out))
+
+
+def _store_from_ptr(sp, ctx, ptr, n):
+    import ctypes as C
+    h = C.c_void_p()
+    ctx._check(sp.lib().spmb_store_create(ctx._h, C.c_void_p(ptr), n, 0, C.byref(h)), "spmb_store_create")
+    return h
+
+
+def bench_myers(sp, synth, torch, ctx, dev, stream, hits, args, rank, world, hbm_peak):
+    n, m, k = args.n_myers, 100, 4
+    seed = synth.SEEDS["C3"] + rank
+    text = synth.text_device(n, seed, dev)
+    rng = np.random.default_rng(seed)
+    s0 = int(rng.integers(0, n - m))
+    pat = text[s0:s0 + m].cpu().numpy().copy()
+    # 1000 planted copies, each with e in U{0..6} random edits (0..4 hit, 5..6 are decoys)
+    starts = np.sort(rng.integers(0, n - 2 * m, size=1000)).astype(np.int64)
+    for st in starts:
+        mp = synth.mutate(rng, pat, int(rng.integers(0, 7)))
+        text[int(st):int(st) + len(mp)] = torch.from_numpy(mp).to(dev)
+    store = sp.Store.from_device(ctx, text.data_ptr(), n)
+    ctx.sync()
+    pattern = sp.Pattern(ctx, sp.ALG_MYERS, pat, k)
+    flush = torch.zeros(64 << 20, dtype=torch.int32, device=dev)   # 256 MB > L2
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    with ClockSampler(torch.cuda.current_device()) as clk:
+        total_ms, kern_ms, n_hits, launches = time_search(sp, torch, ctx, stream, store, pattern, hits, args.steps,
+                                                          args.warmup, flush=flush)
+    if world > 1:
+        t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms = float(t.item())
+    peak = ctx.measure_int_peak()
+    ops = myers_ops_per_bp(m)
+    achieved = n * ops / (kern_ms * 1e-3) / 1e9
+    res = {"workload": f"C3: Myers m={m} k={k} over {n} bp per GPU, 1000 planted mutated copies",
+           "value": world * n * args.steps / (total_ms * 1e-3) / 1e9, "unit": "Gbp/s", "ms_per_step": total_ms / args.steps,
+           "kernel_ms": kern_ms, "hits": n_hits, "row_len": store.row_len, "l2": "256 MB flush write between iterations",
+           "roofline": {"bound": "int_alu", "achieved": achieved, "peak": peak["lop3_gops"], "unit": "Ginstr/s",
+                        "frac": achieved / peak["lop3_gops"], "traffic": ncu_traffic("myers_c3"),
+                        "peak_source": "measured live: spmb_measure_int_peak (LOP3 chains, all SMs)",
+                        "int_peak_iadd3": peak["iadd3_gops"], "algorithmic_int32_instr_per_bp": ops,
+                        "kernel": "myers_kernel<4,plain>"},
+           "clocks": clk.summary()}
+    if rank == 0 and world == 1 and not args.no_cpu:
+        import oracle as orc
+        host = text.cpu().numpy()
+        threads = orc.max_threads()
+        best = 1e30
+        for _ in range(2):
+            t0 = time.perf_counter()
+            cnt, ce, cr = orc.search_mt(3, host, pat, k, threads=threads)
+            best = min(best, time.perf_counter() - t0)
+        g = sp.search(ctx, store, pattern, hits)
+        res["cpu_baseline"] = {"value": n / best / 1e9, "unit": "Gbp/s", "cores": threads, "kind": "port",
+                               "sample": f"whole {n} bp text, oracle Myers (64-bit blocks, Ukkonen cut-off), {threads} threads",
+                               "hits_match_gpu": bool(np.array_equal(g["end"], ce) and np.array_equal(g["errors"], cr))}
+    store.close()
+    del text, flush
+    torch.cuda.empty_cache()
+    return res
+
+
+def bench_small(sp, synth, torch, ctx, dev, stream, hits, args):
+    """C1 and C2 exactly as BASELINE.json specifies them (they fit in L2: flushed between iterations)."""
+    import oracle as orc
+    res = {}
+    flush = torch.zeros(64 << 20, dtype=torch.int32, device=dev)
+    # C1: Horspool m=32 over 1 Mbp
+    n = 1_000_000
+    text = synth.text_host(n, synth.SEEDS["C1"])
+    pat = text[333_333:333_333 + 32].copy()
+    rng = np.random.default_rng(synth.SEEDS["C1"])
+    for st in rng.integers(0, n - 32, size=99):
+        text[int(st):int(st) + 32] = pat
+    store = sp.Store.from_host(ctx, text)
+    p = sp.Pattern(ctx, sp.ALG_HORSPOOL, pat)
+    tot, kern, nh, _ = time_search(sp, torch, ctx, stream, store, p, hits, args.steps, args.warmup, flush=flush)
+    want = orc.horspool(text, pat)
+    got = sp.search(ctx, store, p, hits)
+    t0 = time.perf_counter(); orc.horspool(text, pat); cpu_s = time.perf_counter() - t0
+    res["C1"] = {"workload": "Horspool m=32, 1 Mbp", "kernel_us": kern * 1e3, "step_us": tot / args.steps * 1e3,
+                 "gbp_per_s_kernel": n / (kern * 1e-3) / 1e9, "hits": nh, "parity": bool(np.array_equal(got["end"], want)),
+                 "cpu_1thread_gbp_per_s": n / cpu_s / 1e9}
+    store.close()
+    # C2: Shift-Or m=64 over 50 Mbp + 1% journal
+    n = 50_000_000
+    ref = synth.text_host(n, synth.SEEDS["C2"])
+    ev, pool, kinds = synth.journal(n, synth.SEEDS["C2"])
+    pool = synth.finish_snps(ev, pool, kinds, ref[ev["ref_pos"][kinds == 0].astype(np.int64)])
+    base = sp.Store.from_host(ctx, ref)
+    js = base.journaled(ev, pool)
+    nd = len(js)
+    pat = js.read(nd // 3, 64)
+    p = sp.Pattern(ctx, sp.ALG_SHIFTOR, pat)
+    tot, kern, nh, _ = time_search(sp, torch, ctx, stream, js, p, hits, args.steps, args.warmup, flush=flush)
+    derived = orc.journal_apply(ref, ev.astype(orc.EVENT_DTYPE), pool)
+    same_text = bool(np.array_equal(js.read(), derived))
+    cnt, ce, _ = orc.search_mt(2, derived, pat, 0)
+    got = sp.search(ctx, js, p, hits)
+    res["C2"] = {"workload": "Shift-Or m=64, 50 Mbp + 1% journal", "kernel_us": kern * 1e3,
+                 "step_us": tot / args.steps * 1e3, "gbp_per_s_kernel": nd / (kern * 1e-3) / 1e9, "hits": nh,
+                 "journal_events": int(len(ev)), "derived_text_matches_oracle": same_text,
+                 "parity": bool(np.array_equal(got["end"], ce))}
+    js.close(); base.close()
+    return res
+
+
+# ------------------------------------------------------------------------------------------
+def run_reference(args):
+    """The reference's CPU algorithms for the path (the oracle port: SeqAn2 is not on this machine,
+    SURVEY.md 8(c)), all host threads, bounded sample of the same workload per step."""
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return
+    import oracle as orc
+    from libspm_b200 import synth
+    m = 64
+    s_n = int(min(args.n, args.cpu_sample))
+    seed = synth.SEEDS["C2"]
+    ref = synth.text_host(s_n, seed)
+    ev, pool, kinds = synth.journal(s_n, seed)
+    pool = synth.finish_snps(ev, pool, kinds, ref[ev["ref_pos"][kinds == 0].astype(np.int64)])
+    rng = np.random.default_rng(seed ^ 0xABCDEF)
+    pat = rng.integers(0, 4, size=m, dtype=np.uint8)
+    threads = orc.max_threads()
+    times = []
+    hits = 0
+    derived = orc.journal_apply(ref, ev.astype(orc.EVENT_DTYPE), pool)   # the journaled haystack, resident
+    for i in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        hits, _, _ = orc.search_mt(2, derived, pat, 0, threads=threads, store=False)
+        dt = time.perf_counter() - t0
+        if i >= args.warmup:
+            times.append(dt)
+    tot = sum(times)
+    v = len(derived) * args.steps / tot / 1e9
+    sample = (f"{s_n} bp reference + 1% journal (bounded sample of the {args.n} bp workload), journal applied once "
+              f"outside the timed steps (like the resident store of the GPU arm); each step = oracle Shift-Or "
+              f"(32-bit blocks) over the derived text on {threads} threads")
+    print(json.dumps({
+        "impl": "reference", "metric": "searched_gbp_per_s", "value": v, "unit": "Gbp/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": tot / args.steps * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+        "config": {"workload": "C2x: Shift-Or exact search m=64 over a journaled sequence (CPU, bounded sample)",
+                   "searched_bp_per_step": int(len(derived)), "pattern_len": m, "hits": int(hits)},
+        "cpu_baseline": {"value": v, "unit": "Gbp/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "Gbp/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n", type=int, default=3_200_000_000, help="reference symbols per GPU (C2x)")
+    ap.add_argument("--n-myers", type=int, default=250_000_000)
+    ap.add_argument("--cpu-sample", type=int, default=1_000_000_000)
+    ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-myers", action="store_true")
+    ap.add_argument("--no-small", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -207,8 +207,10 @@ __global__ void __launch_bounds__(256) int_peak_kernel(uint32_t *out, int iters,
         for (int u = 0; u < 8; ++u) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-                if (OP == 0) a[j] = (a[j] & k1) ^ a[(j + 1) & 7]; // one LOP3
-                else a[j] = a[j] + a[(j + 1) & 7] + k1;            // one IADD3
+                if (OP == 0) // exactly one LOP3 (asm: the compiler must not merge rounds algebraically)
+                    asm volatile("lop3.b32 %0, %0, %1, %2, 0x6a;" : "+r"(a[j]) : "r"(k1), "r"(a[(j + 1) & 7]));
+                else         // exactly one IADD3
+                    asm volatile("{ .reg .u32 t; add.u32 t, %0, %1; add.u32 %0, t, %2; }" : "+r"(a[j]) : "r"(a[(j + 1) & 7]), "r"(k1));
             }
         }
     }
