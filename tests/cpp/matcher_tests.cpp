@@ -1,0 +1,144 @@
+// matcher_tests.cpp -- the reference's matcher unit tests, replayed against the C++ facade.
+// Same fixture, same calls, same expected vectors as
+//   /root/reference/test/api/libspm/matcher/horspool_matcher_test.cpp:19-52
+//   /root/reference/test/api/libspm/matcher/shiftor_matcher_test.cpp:19-52
+//   /root/reference/test/api/libspm/matcher/myers_matcher_test.cpp:19-53
+//   /root/reference/test/api/libspm/matcher/myers_matcher_restorable_test.cpp:19-74
+// (GoogleTest swapped for tests/cpp/mini_test.hpp).  Runs on the GPU box only.
+#include <algorithm>
+#include <cstddef>
+#include <vector>
+
+#include <libspm_b200/spm.hpp>
+
+#include "mini_test.hpp"
+
+using spm::operator""_dna4;
+using sequence_t = std::vector<spm::dna4>;
+
+static const sequence_t haystack = "ACGTGACTAGCACGTGACTAGCACGTGACTAGCACGTGACTAGC"_dna4;
+static const sequence_t needle = "GCACG"_dna4;
+static const std::vector<std::size_t> exact_begin{9, 20, 31};
+static const std::vector<std::size_t> myers_end{13, 14, 15, 24, 25, 26, 35, 36, 37};
+
+MINI_TEST(horspool_concept_and_window_size) {
+    auto matcher = spm::horspool_matcher{needle};
+    EXPECT_TRUE(spm::window_matcher<decltype(matcher)>);
+    EXPECT_EQ(spm::window_size(matcher), std::ranges::size(needle));
+}
+
+MINI_TEST(horspool_dna4_pattern) {
+    auto matcher = spm::horspool_matcher{needle};
+    std::vector<std::size_t> actual{};
+    matcher(haystack, [&](auto const &finder) { actual.push_back(seqan2::beginPosition(finder)); });
+    EXPECT_TRUE(std::ranges::equal(actual, exact_begin));
+}
+
+MINI_TEST(shiftor_concept_and_window_size) {
+    auto matcher = spm::shiftor_matcher{needle};
+    EXPECT_TRUE(spm::window_matcher<decltype(matcher)>);
+    EXPECT_EQ(spm::window_size(matcher), std::ranges::size(needle));
+}
+
+MINI_TEST(shiftor_dna4_pattern) {
+    auto matcher = spm::shiftor_matcher{needle};
+    std::vector<std::size_t> actual{};
+    matcher(haystack, [&](auto const &finder) { actual.push_back(seqan2::beginPosition(finder)); });
+    EXPECT_TRUE(std::ranges::equal(actual, exact_begin));
+}
+
+MINI_TEST(myers_concept_and_window_size) {
+    std::size_t errors = 1;
+    auto matcher = spm::myers_matcher{needle, errors};
+    EXPECT_TRUE(spm::window_matcher<decltype(matcher)>);
+    EXPECT_EQ(spm::window_size(matcher), std::ranges::size(needle) + errors);
+}
+
+MINI_TEST(myers_dna4_pattern) {
+    auto matcher = spm::myers_matcher{needle, 1};
+    std::vector<std::size_t> actual{};
+    std::vector<unsigned> errs{};
+    matcher(haystack, [&](auto const &finder) {
+        actual.push_back(seqan2::endPosition(finder));
+        errs.push_back(finder.errors());
+    });
+    EXPECT_TRUE(std::ranges::equal(actual, myers_end));
+    EXPECT_TRUE(std::ranges::equal(errs, std::vector<unsigned>{1, 0, 1, 1, 0, 1, 1, 0, 1}));
+}
+
+MINI_TEST(restorable_myers_concept_and_window_size) {
+    std::size_t errors = 1;
+    auto matcher = spm::restorable_myers_matcher{needle, errors};
+    EXPECT_TRUE(spm::window_matcher<decltype(matcher)>);
+    EXPECT_TRUE(spm::restorable_matcher<decltype(matcher)>);
+    EXPECT_EQ(spm::window_size(matcher), std::ranges::size(needle) + errors);
+}
+
+MINI_TEST(restorable_myers_dna4_pattern) {
+    auto matcher = spm::restorable_myers_matcher{needle, 1u};
+    std::vector<std::size_t> actual{};
+    matcher(haystack, [&](auto const &finder) { actual.push_back(seqan2::endPosition(finder)); });
+    EXPECT_TRUE(std::ranges::equal(actual, myers_end));
+}
+
+MINI_TEST(restorable_myers_dna4_pattern_captured) {
+    std::size_t chunk_size{13};
+    std::ptrdiff_t chunk_count = (haystack.size() + chunk_size - 1) / chunk_size;
+    auto matcher = spm::restorable_myers_matcher{needle, 1u};
+    auto state = matcher.capture();
+    std::vector<std::size_t> actual{};
+    for (std::ptrdiff_t chunk_idx = 0; chunk_idx < chunk_count; ++chunk_idx) {
+        std::ptrdiff_t offset = chunk_idx * chunk_size;
+        sequence_t chunk{haystack.begin() + offset,
+                         haystack.begin() + std::min<std::ptrdiff_t>(offset + chunk_size, haystack.size())};
+        matcher.restore(state);
+        matcher(chunk, [&](auto const &finder) { actual.push_back(seqan2::endPosition(finder) + offset); });
+        state = matcher.capture();
+    }
+    EXPECT_TRUE(std::ranges::equal(actual, myers_end));
+}
+
+// untested in the reference, covered here
+MINI_TEST(restorable_shiftor_chunks) {
+    auto matcher = spm::restorable_shiftor_matcher{needle};
+    EXPECT_TRUE(spm::restorable_matcher<decltype(matcher)>);
+    std::vector<std::size_t> actual{};
+    for (std::size_t offset = 0; offset < haystack.size(); offset += 7) {
+        sequence_t chunk{haystack.begin() + offset, haystack.begin() + std::min(offset + 7, haystack.size())};
+        matcher(chunk, [&](auto const &finder) { actual.push_back(seqan2::beginPosition(finder) + offset); });
+    }
+    // beginPosition of a hit that started in an earlier chunk is clamped at 0 of the chunk; use ends
+    std::vector<std::size_t> ends{};
+    auto m2 = spm::restorable_shiftor_matcher{needle};
+    for (std::size_t offset = 0; offset < haystack.size(); offset += 7) {
+        sequence_t chunk{haystack.begin() + offset, haystack.begin() + std::min(offset + 7, haystack.size())};
+        m2(chunk, [&](auto const &finder) { ends.push_back(seqan2::endPosition(finder) + offset); });
+    }
+    EXPECT_TRUE(std::ranges::equal(ends, std::vector<std::size_t>{14, 25, 36}));
+}
+
+MINI_TEST(device_resident_sequence_and_copies) {
+    spm::device_sequence seq{haystack};
+    EXPECT_EQ(seq.size(), haystack.size());
+    auto matcher = spm::myers_matcher{needle, 1};
+    auto copy = matcher; // matchers are copyable (concept.hpp:126-130)
+    std::vector<std::size_t> a{}, b{};
+    matcher(seq, [&](auto const &f) { a.push_back(seqan2::endPosition(f)); });
+    copy(seq, [&](auto const &f) { b.push_back(seqan2::endPosition(f)); });
+    EXPECT_TRUE(std::ranges::equal(a, myers_end));
+    EXPECT_TRUE(std::ranges::equal(b, myers_end));
+}
+
+MINI_TEST(empty_needle_and_haystack) {
+    sequence_t none{};
+    auto matcher = spm::horspool_matcher{none};
+    EXPECT_TRUE(matcher.empty());
+    EXPECT_EQ(spm::window_size(matcher), 0u);
+    int calls = 0;
+    matcher(haystack, [&](auto const &) { ++calls; });
+    auto m2 = spm::shiftor_matcher{needle};
+    m2(none, [&](auto const &) { ++calls; });
+    EXPECT_EQ(calls, 0);
+}
+
+int main() { return mini::run_all(); }
