@@ -8,6 +8,7 @@
 // written out as one coalesced 8 KB burst.
 #pragma once
 #include "layout.cuh"
+#include "../../include/spmb.h"
 
 // symbol at absolute position p of a packed plain store
 __device__ __forceinline__ uint32_t spmb_symbol_at(const uint2 *__restrict__ planes, const SpmbLayout &lay,
@@ -49,15 +50,15 @@ struct ByteSource {
 };
 
 // journaled sequence: derived position d -> base symbol or inserted symbol.
-// ev_der[i] = derived position where event i's inserted segment begins (host prefix sum).
+// ev_der[i] = derived position where event i's inserted segment begins (device prefix sum);
+// blk_idx[b] = index of the last event with ev_der <= b*1024 (or -1): a lane finds its first
+// event with a <= 5-step search instead of a log2(n_ev)-deep chain of dependent loads.
 struct JournalSource {
     const uint2 *__restrict__ base_planes;
     SpmbLayout base;
+    const spmb_journal_event *__restrict__ ev;
     const uint64_t *__restrict__ ev_der;
-    const uint64_t *__restrict__ ev_ref;
-    const uint32_t *__restrict__ ev_del;
-    const uint32_t *__restrict__ ev_ins;
-    const uint64_t *__restrict__ ev_off;
+    const int64_t *__restrict__ blk_idx;
     const uint8_t *__restrict__ pool;
     uint64_t n_ev;
     uint64_t n; // derived length
@@ -68,7 +69,7 @@ struct JournalSource {
         for (int i = 0; i < 8; ++i) w[i] = 0;
         if (d0 >= n) return;
         // last event with ev_der <= d0  (idx in [-1, n_ev-1])
-        int64_t lo = -1, hi = (int64_t)n_ev - 1;
+        int64_t lo = blk_idx[d0 >> 10], hi = blk_idx[(d0 >> 10) + 1];
         while (lo < hi) {
             int64_t mid = (lo + hi + 1) >> 1;
             if (ev_der[mid] <= d0) lo = mid; else hi = mid - 1;
@@ -77,13 +78,17 @@ struct JournalSource {
         uint64_t next_der = (e + 1 < (int64_t)n_ev) ? ev_der[e + 1] : ~0ull;
         uint64_t seg_der = 0, seg_ref = 0, seg_off = 0;
         uint32_t seg_ins = 0;
-        if (e >= 0) { seg_der = ev_der[e]; seg_ins = ev_ins[e]; seg_ref = ev_ref[e] + ev_del[e]; seg_off = ev_off[e]; }
+        if (e >= 0) {
+            const spmb_journal_event x = ev[e];
+            seg_der = ev_der[e]; seg_ins = x.ins_len; seg_ref = x.ref_pos + x.del_len; seg_off = x.ins_off;
+        }
         for (int t = 0; t < 32; ++t) {
             uint64_t d = d0 + t;
             if (d >= n) break;
             while (d >= next_der) { // enter the next event (several may start at the same d)
                 ++e;
-                seg_der = next_der; seg_ins = ev_ins[e]; seg_ref = ev_ref[e] + ev_del[e]; seg_off = ev_off[e];
+                const spmb_journal_event x = ev[e];
+                seg_der = next_der; seg_ins = x.ins_len; seg_ref = x.ref_pos + x.del_len; seg_off = x.ins_off;
                 next_der = (e + 1 < (int64_t)n_ev) ? ev_der[e + 1] : ~0ull;
             }
             uint32_t s;
@@ -94,6 +99,47 @@ struct JournalSource {
         }
     }
 };
+
+// journal preparation on the device: validation + (ins - del) deltas, then an exclusive scan
+// (CUB) gives every event's shift; ev_der = ref_pos + shift.
+__global__ void journal_delta_kernel(const spmb_journal_event *__restrict__ ev, uint64_t n_ev, uint64_t n_ref,
+                                     uint64_t pool_len, long long *__restrict__ delta, int *__restrict__ bad)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_ev) return;
+    const spmb_journal_event x = ev[i];
+    delta[i] = (long long)x.ins_len - (long long)x.del_len;
+    bool ok = (x.ref_pos + x.del_len <= n_ref) && (x.ins_off + x.ins_len <= pool_len);
+    if (i > 0) {
+        const spmb_journal_event y = ev[i - 1];
+        ok = ok && (x.ref_pos >= y.ref_pos + y.del_len);
+    }
+    if (!ok) atomicExch(bad, 1);
+}
+
+__global__ void journal_der_kernel(const spmb_journal_event *__restrict__ ev, uint64_t n_ev,
+                                   const long long *__restrict__ shift, const long long *__restrict__ delta,
+                                   uint64_t *__restrict__ der, long long *__restrict__ total)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_ev) return;
+    der[i] = (uint64_t)((long long)ev[i].ref_pos + shift[i]);
+    if (i == n_ev - 1) *total = shift[i] + delta[i];
+}
+
+__global__ void journal_blkidx_kernel(const uint64_t *__restrict__ der, uint64_t n_ev, uint64_t n_blk,
+                                      int64_t *__restrict__ blk_idx)
+{
+    uint64_t b = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= n_blk) return;
+    const uint64_t d = b << 10;
+    int64_t lo = -1, hi = (int64_t)n_ev - 1;
+    while (lo < hi) {
+        int64_t mid = (lo + hi + 1) >> 1;
+        if (der[mid] <= d) lo = mid; else hi = mid - 1;
+    }
+    blk_idx[b] = lo;
+}
 
 template <class Source>
 __global__ void __launch_bounds__(1024) pack_kernel(Source src, SpmbLayout lay, uint2 *__restrict__ planes)

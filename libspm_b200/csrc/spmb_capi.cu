@@ -4,6 +4,7 @@
 // There is no CPU search path in this file: if no CUDA device is present every entry point
 // fails with SPMB_ERR_NO_DEVICE.
 #include <cuda_runtime.h>
+#include <cub/device/device_scan.cuh>
 
 #include <algorithm>
 #include <cstdio>
@@ -29,7 +30,7 @@ struct spmb_context {
     std::string err;
     uint32_t launches = 0;
     int sm_count = 0;
-    unsigned long long *h_count = nullptr; // pinned
+    unsigned long long *h_count = nullptr; // pinned (8 slots)
 };
 
 struct spmb_store {
@@ -131,7 +132,15 @@ extern "C" int spmb_context_create(int device, void *stream, spmb_context **out)
         ctx->own_stream = true;
     }
     cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
-    if (cudaMallocHost(&ctx->h_count, sizeof(unsigned long long)) != cudaSuccess) { delete ctx; return SPMB_ERR_CUDA; }
+    {
+        cudaMemPool_t pool;
+        if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+            unsigned long long thr = ~0ull;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+        }
+        cudaGetLastError();
+    }
+    if (cudaMallocHost(&ctx->h_count, 8 * sizeof(unsigned long long)) != cudaSuccess) { delete ctx; return SPMB_ERR_CUDA; }
     *out = ctx;
     return SPMB_OK;
 }
@@ -182,8 +191,8 @@ static int store_alloc(spmb_context *ctx, uint64_t n, uint32_t row_len, uint32_t
     s->ctx = ctx;
     s->lay = spmb_make_layout(n, row_len, mode);
     s->bytes = (size_t)s->lay.n_cols_alloc * sizeof(uint2);
-    cudaError_t e = cudaMalloc(&s->planes, s->bytes);
-    if (e != cudaSuccess) { cudaGetLastError(); delete s; return set_err(ctx, SPMB_ERR_OOM, "cudaMalloc(store)", e); }
+    cudaError_t e = cudaMallocAsync(&s->planes, s->bytes, ctx->stream); // stream-ordered pool: cheap re-creation
+    if (e != cudaSuccess) { cudaGetLastError(); delete s; return set_err(ctx, SPMB_ERR_OOM, "cudaMallocAsync(store)", e); }
     *out = s;
     return SPMB_OK;
 }
@@ -220,12 +229,19 @@ extern "C" int spmb_store_create(spmb_context *ctx, const uint8_t *host_ranks, u
     if (!ctx || !out || (!host_ranks && n)) return SPMB_ERR_ARG;
     CU(cudaSetDevice(ctx->device));
     uint8_t *d = nullptr;
-    CU(cudaMalloc(&d, n ? n : 1));
+    CU(cudaMallocAsync(&d, n ? n : 1, ctx->stream));
     cudaError_t e = cudaMemcpyAsync(d, host_ranks, n, cudaMemcpyHostToDevice, ctx->stream);
-    if (e != cudaSuccess) { cudaFree(d); return set_err(ctx, SPMB_ERR_CUDA, "H2D haystack", e); }
-    int rc = spmb_store_create_from_device(ctx, d, n, row_len, out);
-    cudaStreamSynchronize(ctx->stream);
-    cudaFree(d);
+    int rc = SPMB_OK;
+    if (e != cudaSuccess) rc = set_err(ctx, SPMB_ERR_CUDA, "H2D haystack", e);
+    if (rc == SPMB_OK) rc = spmb_store_create_from_device(ctx, d, n, row_len, out);
+    cudaFreeAsync(d, ctx->stream);
+    // the caller's buffer may be pinned (truly asynchronous copy): do not return before it is consumed
+    e = cudaStreamSynchronize(ctx->stream);
+    if (rc == SPMB_OK && e != cudaSuccess) {
+        spmb_store_destroy(*out);
+        *out = nullptr;
+        rc = set_err(ctx, SPMB_ERR_CUDA, "store_create", e);
+    }
     return rc;
 }
 
@@ -234,55 +250,76 @@ extern "C" int spmb_store_create_journaled(spmb_context *ctx, const spmb_store *
                                            const uint8_t *pool, uint64_t pool_len, uint32_t row_len,
                                            spmb_store **out)
 {
-    if (!ctx || !base || !out || (n_ev && !ev)) return SPMB_ERR_ARG;
+    if (!ctx || !base || !out || (n_ev && !ev) || (pool_len && !pool)) return SPMB_ERR_ARG;
     if (base->lay.mode != SPMB_MODE_PLAIN) return set_err(ctx, SPMB_ERR_ARG, "journal base must be a plain store");
     CU(cudaSetDevice(ctx->device));
-    // host: validate + prefix sums (derived start of every event)
-    std::vector<uint64_t> der(n_ev), ref(n_ev), off(n_ev);
-    std::vector<uint32_t> del(n_ev), ins(n_ev);
-    uint64_t r = 0;
-    int64_t shift = 0;
-    for (uint64_t i = 0; i < n_ev; ++i) {
-        if (ev[i].ref_pos < r || ev[i].ref_pos + ev[i].del_len > base->lay.n)
-            return set_err(ctx, SPMB_ERR_ARG, "journal events must be sorted, non-overlapping and inside the reference");
-        if ((uint64_t)ev[i].ins_off + ev[i].ins_len > pool_len)
-            return set_err(ctx, SPMB_ERR_ARG, "journal insertion outside the pool");
-        der[i] = (uint64_t)((int64_t)ev[i].ref_pos + shift);
-        ref[i] = ev[i].ref_pos; del[i] = ev[i].del_len; ins[i] = ev[i].ins_len; off[i] = ev[i].ins_off;
-        shift += (int64_t)ev[i].ins_len - (int64_t)ev[i].del_len;
-        r = ev[i].ref_pos + ev[i].del_len;
-    }
-    const uint64_t n_der = (uint64_t)((int64_t)base->lay.n + shift);
-    spmb_store *s = nullptr;
-    int rc = store_alloc(ctx, n_der, row_len, SPMB_MODE_PLAIN, &s);
-    if (rc) return rc;
-    uint64_t *d_der = nullptr, *d_ref = nullptr, *d_off = nullptr;
-    uint32_t *d_del = nullptr, *d_ins = nullptr;
-    uint8_t *d_pool = nullptr;
+    cudaStream_t sm = ctx->stream;
     const size_t ne = n_ev ? n_ev : 1;
+    spmb_journal_event *d_ev = nullptr;
+    long long *d_delta = nullptr, *d_shift = nullptr, *d_total = nullptr;
+    uint64_t *d_der = nullptr;
+    int64_t *d_blk = nullptr;
+    int *d_bad = nullptr;
+    uint8_t *d_pool = nullptr;
+    void *d_tmp = nullptr;
+    spmb_store *s = nullptr;
+    int rc = SPMB_OK;
     cudaError_t e = cudaSuccess;
-    if (e == cudaSuccess) e = cudaMalloc(&d_der, ne * 8);
-    if (e == cudaSuccess) e = cudaMalloc(&d_ref, ne * 8);
-    if (e == cudaSuccess) e = cudaMalloc(&d_off, ne * 8);
-    if (e == cudaSuccess) e = cudaMalloc(&d_del, ne * 4);
-    if (e == cudaSuccess) e = cudaMalloc(&d_ins, ne * 4);
-    if (e == cudaSuccess) e = cudaMalloc(&d_pool, pool_len ? pool_len : 1);
+    auto cleanup = [&]() {
+        cudaFreeAsync(d_ev, sm); cudaFreeAsync(d_delta, sm); cudaFreeAsync(d_shift, sm); cudaFreeAsync(d_total, sm);
+        cudaFreeAsync(d_der, sm); cudaFreeAsync(d_blk, sm); cudaFreeAsync(d_bad, sm); cudaFreeAsync(d_pool, sm);
+        cudaFreeAsync(d_tmp, sm);
+    };
+#define JCU(call) do { if (e == cudaSuccess) e = (call); } while (0)
+    JCU(cudaMallocAsync(&d_ev, ne * sizeof(spmb_journal_event), sm));
+    JCU(cudaMallocAsync(&d_delta, ne * 8, sm));
+    JCU(cudaMallocAsync(&d_shift, ne * 8, sm));
+    JCU(cudaMallocAsync(&d_der, ne * 8, sm));
+    JCU(cudaMallocAsync(&d_total, 16, sm));
+    JCU(cudaMallocAsync(&d_bad, 16, sm));
+    JCU(cudaMallocAsync(&d_pool, pool_len ? pool_len : 1, sm));
+    JCU(cudaMemsetAsync(d_total, 0, 16, sm));
+    JCU(cudaMemsetAsync(d_bad, 0, 16, sm));
+    if (n_ev) JCU(cudaMemcpyAsync(d_ev, ev, n_ev * sizeof(spmb_journal_event), cudaMemcpyHostToDevice, sm));
+    if (pool_len) JCU(cudaMemcpyAsync(d_pool, pool, pool_len, cudaMemcpyHostToDevice, sm));
     if (e == cudaSuccess && n_ev) {
-        e = cudaMemcpyAsync(d_der, der.data(), n_ev * 8, cudaMemcpyHostToDevice, ctx->stream);
-        if (e == cudaSuccess) e = cudaMemcpyAsync(d_ref, ref.data(), n_ev * 8, cudaMemcpyHostToDevice, ctx->stream);
-        if (e == cudaSuccess) e = cudaMemcpyAsync(d_off, off.data(), n_ev * 8, cudaMemcpyHostToDevice, ctx->stream);
-        if (e == cudaSuccess) e = cudaMemcpyAsync(d_del, del.data(), n_ev * 4, cudaMemcpyHostToDevice, ctx->stream);
-        if (e == cudaSuccess) e = cudaMemcpyAsync(d_ins, ins.data(), n_ev * 4, cudaMemcpyHostToDevice, ctx->stream);
+        unsigned blocks = (unsigned)((n_ev + 255) / 256);
+        journal_delta_kernel<<<blocks, 256, 0, sm>>>(d_ev, n_ev, base->lay.n, pool_len, d_delta, d_bad);
+        size_t tmp_bytes = 0;
+        JCU(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, d_delta, d_shift, (int64_t)n_ev, sm));
+        JCU(cudaMallocAsync(&d_tmp, tmp_bytes ? tmp_bytes : 1, sm));
+        JCU(cub::DeviceScan::ExclusiveSum(d_tmp, tmp_bytes, d_delta, d_shift, (int64_t)n_ev, sm));
+        journal_der_kernel<<<blocks, 256, 0, sm>>>(d_ev, n_ev, d_shift, d_delta, d_der, d_total);
+        ctx->launches += 3;
+        JCU(cudaGetLastError());
     }
-    if (e == cudaSuccess && pool_len) e = cudaMemcpyAsync(d_pool, pool, pool_len, cudaMemcpyHostToDevice, ctx->stream);
+    // derived length (and the validation verdict) must reach the host before the store is sized
+    JCU(cudaMemcpyAsync(&ctx->h_count[1], d_total, 8, cudaMemcpyDeviceToHost, sm));
+    JCU(cudaMemcpyAsync(&ctx->h_count[2], d_bad, 4, cudaMemcpyDeviceToHost, sm));
+    JCU(cudaStreamSynchronize(sm));
+    if (e != cudaSuccess) { cleanup(); cudaGetLastError(); return set_err(ctx, SPMB_ERR_CUDA, "journal upload/prefix", e); }
+    if ((int)(ctx->h_count[2] & 0xffffffffu) != 0) {
+        cleanup();
+        return set_err(ctx, SPMB_ERR_ARG, "journal events must be sorted, non-overlapping, inside the reference and the pool");
+    }
+    const long long total_shift = (long long)ctx->h_count[1];
+    const uint64_t n_der = (uint64_t)((long long)base->lay.n + total_shift);
+    rc = store_alloc(ctx, n_der, row_len, SPMB_MODE_PLAIN, &s);
+    if (rc) { cleanup(); return rc; }
+    const uint64_t n_blk = (n_der >> 10) + 2;
+    JCU(cudaMallocAsync(&d_blk, n_blk * 8, sm));
     if (e == cudaSuccess) {
-        JournalSource src{base->planes, base->lay, d_der, d_ref, d_del, d_ins, d_off, d_pool, n_ev, n_der};
+        journal_blkidx_kernel<<<(unsigned)((n_blk + 255) / 256), 256, 0, sm>>>(d_der, n_ev, n_blk, d_blk);
+        ctx->launches++;
+        JournalSource src{base->planes, base->lay, d_ev, d_der, d_blk, d_pool, n_ev, n_der};
         rc = store_pack(ctx, s, src);
-        if (rc == SPMB_OK) e = cudaStreamSynchronize(ctx->stream);
     }
-    cudaFree(d_der); cudaFree(d_ref); cudaFree(d_off); cudaFree(d_del); cudaFree(d_ins); cudaFree(d_pool);
+    cleanup();
+    JCU(cudaStreamSynchronize(sm));
+#undef JCU
     if (e != cudaSuccess || rc) {
         spmb_store_destroy(s);
+        cudaGetLastError();
         return rc ? rc : set_err(ctx, SPMB_ERR_CUDA, "journal materialise", e);
     }
     *out = s;
@@ -293,7 +330,7 @@ extern "C" int spmb_store_destroy(spmb_store *s)
 {
     if (!s) return SPMB_OK;
     if (s->ctx) cudaSetDevice(s->ctx->device);
-    cudaFree(s->planes);
+    if (s->ctx) cudaFreeAsync(s->planes, s->ctx->stream); else cudaFree(s->planes);
     cudaFree(s->row_len);
     cudaFree(s->row_seq);
     cudaFree(s->row_own);

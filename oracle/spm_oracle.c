@@ -420,21 +420,31 @@ uint64_t orc_search_mt(int alg, const uint8_t *text, uint64_t n, const uint8_t *
 uint64_t orc_journal_apply(const uint8_t *ref, uint64_t n, const orc_event_t *ev, uint64_t n_ev,
                            const uint8_t *pool, uint8_t *out, uint64_t out_cap)
 {
+    /* pass 1 (serial, cheap): validate and find the derived start of every event */
     uint64_t o = 0, r = 0;
+    uint64_t *der = out ? (uint64_t *)malloc((n_ev + 1) * sizeof(uint64_t)) : NULL;
     for (uint64_t i = 0; i < n_ev; ++i) {
         uint64_t p = ev[i].ref_pos;
-        if (p < r || p > n) return (uint64_t)-1; /* unsorted / overlapping */
-        if (out) {
-            uint64_t len = p - r;
-            if (o + len <= out_cap) memcpy(out + o, ref + r, len);
-        }
+        if (p < r || p > n || p + ev[i].del_len > n) { free(der); return (uint64_t)-1; } /* unsorted / overlapping */
         o += p - r;
-        if (out && o + ev[i].ins_len <= out_cap && ev[i].ins_len) memcpy(out + o, pool + ev[i].ins_off, ev[i].ins_len);
+        if (der) der[i] = o;
         o += ev[i].ins_len;
         r = p + ev[i].del_len;
-        if (r > n) return (uint64_t)-1;
     }
-    if (out && o + (n - r) <= out_cap) memcpy(out + o, ref + r, n - r);
-    o += n - r;
-    return o;
+    uint64_t total = o + (n - r);
+    if (!out) return total;
+    if (total > out_cap) { free(der); return total; }
+    /* pass 2 (parallel): copy the reference slice before each event and its insertion */
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static)
+#endif
+    for (int64_t i = 0; i <= (int64_t)n_ev; ++i) {
+        uint64_t prev_end = (i == 0) ? 0 : ev[i - 1].ref_pos + ev[i - 1].del_len;
+        uint64_t prev_out = (i == 0) ? 0 : der[i - 1] + ev[i - 1].ins_len;
+        uint64_t upto = (i == (int64_t)n_ev) ? n : ev[i].ref_pos;
+        memcpy(out + prev_out, ref + prev_end, upto - prev_end);
+        if (i < (int64_t)n_ev && ev[i].ins_len) memcpy(out + der[i], pool + ev[i].ins_off, ev[i].ins_len);
+    }
+    free(der);
+    return total;
 }

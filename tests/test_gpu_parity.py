@@ -302,3 +302,24 @@ def test_search_host_call_shape(ctx):
 def test_int_peak_probe(ctx):
     r = ctx.measure_int_peak()
     assert r["lop3_gops"] > 1000 and r["iadd3_gops"] > 1000
+
+
+def test_journal_validation_errors(ctx):
+    ref = rand_text(np.random.default_rng(3), 10_000)
+    base = sp.Store.from_host(ctx, ref)
+    pool = np.zeros(4, np.uint8)
+    bad_sets = [
+        [(500, 1, 1, 0), (400, 1, 1, 1)],          # unsorted
+        [(500, 10, 0, 0), (505, 1, 1, 0)],         # overlapping
+        [(9_995, 10, 0, 0)],                       # deletion runs off the reference
+        [(100, 0, 3, 2)],                          # insertion outside the pool
+    ]
+    for evs in bad_sets:
+        with pytest.raises(sp.SpmbError) as ei:
+            base.journaled(np.array(evs, dtype=sp.EVENT_DTYPE), pool)
+        assert ei.value.code == 1
+    # adjacent events (deletion directly followed by an insertion) are legal
+    ev = np.array([(100, 5, 0, 0), (105, 0, 4, 0), (9_999, 1, 1, 0)], dtype=sp.EVENT_DTYPE)
+    js = base.journaled(ev, pool)
+    want = orc.journal_apply(ref, ev.astype(orc.EVENT_DTYPE), pool)
+    assert np.array_equal(js.read(), want)
