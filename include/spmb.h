@@ -160,6 +160,28 @@ int spmb_stream_feed(spmb_context *ctx, spmb_stream *st, const uint8_t *host_ran
 int spmb_stream_capture(const spmb_stream *st, void *buf, size_t *size);
 int spmb_stream_restore(spmb_stream *st, const void *buf, size_t size);
 
+/* ---------------- journaled string tree (north_star items 1-2; a14) ----------------
+ * What an external JST traverser does with the reference's matchers (it sizes branch contexts
+ * with spm::window_size, concept.hpp:27-50, and runs matcher(context, callback) on each),
+ * done here in one call: the tree is flattened on the host into an array of branch-context
+ * windows (each carries window_size-1 symbols of context before its first variant), the
+ * reference is scanned once, the windows are scanned by the windows-mode kernels, and every hit
+ * is expanded to (haplotype id = seq_id, end in that haplotype's coordinates, errors).
+ * variants: sorted by ref_pos (insertions first on ties); coverage: n_variants rows of
+ * ceil(n_haplotypes/64) 64-bit words, bit h of row v set = haplotype h carries variant v; the
+ * variants carried by one haplotype must form a valid journal (sorted, non-overlapping).
+ * The reference store must outlive the JST. */
+typedef struct spmb_jst spmb_jst;
+int spmb_jst_create(spmb_context *ctx, const spmb_store *reference, const spmb_journal_event *variants,
+                    uint64_t n_variants, const uint8_t *ins_pool, uint64_t pool_len,
+                    const uint64_t *coverage, uint32_t n_haplotypes, spmb_jst **out);
+int spmb_jst_destroy(spmb_jst *j);
+int spmb_jst_search(spmb_context *ctx, spmb_jst *j, const spmb_pattern *p, spmb_hits *h);
+/* figures of the last search: stats[0] windows, [1] window symbols, [2] length buckets,
+ * [3] raw device hits before expansion; ms[0] host flattening (0 when cached), [1] window
+ * materialisation, [2] search kernels (reference + windows), [3] host expansion + sort */
+int spmb_jst_last_stats(const spmb_jst *j, uint64_t stats[4], double ms[4]);
+
 /* ---------------- measurement helpers ---------------- */
 /* INT32 ALU-pipe peak (LOP3 / IADD3 chains on all SMs), in 1e9 lane-instructions per second:
  * the roofline denominator for the Myers kernels. */

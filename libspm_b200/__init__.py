@@ -13,7 +13,7 @@ import os
 
 import numpy as np
 
-__all__ = ["Context", "Store", "Pattern", "Hits", "Stream", "SpmbError", "HIT_DTYPE", "EVENT_DTYPE",
+__all__ = ["Context", "Store", "Pattern", "Hits", "Stream", "Jst", "SpmbError", "HIT_DTYPE", "EVENT_DTYPE",
            "ALG_HORSPOOL", "ALG_SHIFTOR", "ALG_MYERS", "lib", "lib_path"]
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -36,7 +36,7 @@ EXPORTS = [
     "spmb_hits_count", "spmb_hits_data", "spmb_search_launch", "spmb_search_finish", "spmb_search",
     "spmb_search_host", "spmb_last_launch_count", "spmb_stream_create", "spmb_stream_destroy",
     "spmb_stream_feed", "spmb_stream_capture", "spmb_stream_restore", "spmb_measure_int_peak",
-    "spmb_device_info",
+    "spmb_device_info", "spmb_jst_create", "spmb_jst_destroy", "spmb_jst_search", "spmb_jst_last_stats",
 ]
 
 
@@ -100,6 +100,10 @@ def lib():
             "spmb_stream_restore": (i32, [vp, vp, C.c_size_t]),
             "spmb_measure_int_peak": (i32, [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
             "spmb_device_info": (i32, [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(u64)]),
+            "spmb_jst_create": (i32, [vp, vp, vp, u64, vp, u64, vp, u32, pp]),
+            "spmb_jst_destroy": (i32, [vp]),
+            "spmb_jst_search": (i32, [vp, vp, vp, vp]),
+            "spmb_jst_last_stats": (i32, [vp, C.POINTER(u64 * 4), C.POINTER(C.c_double * 4)]),
         }
         for name, (res, args) in sig.items():
             fn = getattr(L, name)
@@ -363,6 +367,50 @@ class Stream:
             lib().spmb_stream_destroy(self._h)
             self._h = C.c_void_p()
         self._hits.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Jst:
+    """journaled string tree over a resident reference store (spmb_jst)."""
+
+    def __init__(self, ctx: Context, reference: Store, variants, pool, coverage, n_haplotypes: int):
+        self.ctx, self.reference = ctx, reference
+        var = np.ascontiguousarray(variants, dtype=EVENT_DTYPE)
+        pl = _ranks(pool)
+        cov = np.ascontiguousarray(coverage, dtype=np.uint64)
+        wpr = (n_haplotypes + 63) // 64
+        assert cov.shape == (len(var), wpr), (cov.shape, len(var), wpr)
+        self._h = C.c_void_p()
+        ctx._check(lib().spmb_jst_create(ctx._h, reference._h, var.ctypes.data if var.size else None, var.size,
+                                         pl.ctypes.data if pl.size else None, pl.size,
+                                         cov.ctypes.data if cov.size else None, n_haplotypes, C.byref(self._h)),
+                   "spmb_jst_create")
+        self.n_haplotypes = n_haplotypes
+
+    def search(self, pattern: Pattern, hits: Hits | None = None) -> np.ndarray:
+        own = hits is None
+        hits = hits or Hits(self.ctx)
+        self.ctx._check(lib().spmb_jst_search(self.ctx._h, self._h, pattern._h, hits._h), "spmb_jst_search")
+        out = hits.array()
+        if own:
+            hits.close()
+        return out
+
+    def last_stats(self):
+        st, ms = (C.c_uint64 * 4)(), (C.c_double * 4)()
+        lib().spmb_jst_last_stats(self._h, C.byref(st), C.byref(ms))
+        return {"windows": st[0], "window_symbols": st[1], "buckets": st[2], "raw_hits": st[3],
+                "flatten_ms": ms[0], "materialise_ms": ms[1], "kernels_ms": ms[2], "expand_ms": ms[3]}
+
+    def close(self):
+        if self._h:
+            lib().spmb_jst_destroy(self._h)
+            self._h = C.c_void_p()
 
     def __del__(self):
         try:

@@ -27,6 +27,7 @@ struct ExactArgs {
     const uint8_t *pat;      // m ranks (device)
     const uint32_t *row_len; // windows mode: valid symbols per row; else null
     const uint32_t *row_seq; // windows mode: seq id per row; else null
+    const uint32_t *row_own; // windows mode: first owned end per row (hits ending earlier belong elsewhere); may be null
     uint32_t m;
     uint32_t J;              // filter depth = min(m, 8)
     uint32_t filt_syms;      // pattern symbol j at bits [2j, 2j+1], j < J
@@ -111,7 +112,7 @@ __device__ __forceinline__ void exact_emit(const ExactArgs &a, uint64_t gc, uint
         ok = ok && (end <= a.lay.n);
     } else {
         end = (uint64_t)col + a.m;
-        ok = ok && (R * RL < a.lay.n) && (end <= a.row_len[R]);
+        ok = ok && (R * RL < a.lay.n) && (end <= a.row_len[R]) && (!a.row_own || end >= a.row_own[R]);
         if (ok && a.row_seq) seq = a.row_seq[R];
     }
     uint32_t em = __ballot_sync(0xffffffffu, ok);

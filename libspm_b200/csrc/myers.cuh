@@ -121,7 +121,7 @@ __global__ void __launch_bounds__(128) myers_kernel(MyersArgs a)
         if (p < 0) { p = 0; cur_row = 0; cur_col = 0; }
         end_p = own_lo + RL + (W ? 32 : 0);
     } else {
-        own_lo = a.row_own ? (int64_t)a.row_own[R] : 0;
+        own_lo = a.row_own ? (int64_t)a.row_own[R] - 1 : 0; // row_own is an exclusive-end coordinate; j is the last symbol
         own_hi = (int64_t)a.row_len[R];
         if (a.row_seq) seq = a.row_seq[R];
         p = 0;

@@ -16,6 +16,7 @@
 #include "../../include/spmb.h"
 #include "exact.cuh"
 #include "hits.cuh"
+#include "jst.cuh"
 #include "layout.cuh"
 #include "myers.cuh"
 #include "pack.cuh"
@@ -525,9 +526,10 @@ static cudaError_t launch_myers(spmb_context *ctx, const spmb_store *s, const sp
     return cudaGetLastError();
 }
 
-static int enqueue_search(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p, spmb_hits *h)
+static int enqueue_search(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p, spmb_hits *h,
+                          bool reset = true, uint32_t seq_id = 0)
 {
-    CU(cudaMemsetAsync(h->d_count, 0, sizeof(unsigned long long), ctx->stream));
+    if (reset) CU(cudaMemsetAsync(h->d_count, 0, sizeof(unsigned long long), ctx->stream));
     HitSink sink{h->d_hits, h->d_count, h->cap};
     if (p->max_m == 0 || s->lay.n == 0) return SPMB_OK; // empty needle / haystack: no hits
     if (p->alg == SPMB_ALG_MYERS) {
@@ -539,7 +541,7 @@ static int enqueue_search(spmb_context *ctx, const spmb_store *s, const spmb_pat
         a.meta = p->d_meta;
         a.row_len = s->row_len; a.row_seq = s->row_seq; a.row_own = s->row_own;
         a.warm = p->warm;
-        a.seq_id = 0;
+        a.seq_id = seq_id;
         a.sink = sink;
         cudaError_t e = (s->lay.mode == SPMB_MODE_PLAIN) ? launch_myers<SPMB_MODE_PLAIN>(ctx, s, p, a)
                                                           : launch_myers<SPMB_MODE_WINDOWS>(ctx, s, p, a);
@@ -556,11 +558,11 @@ static int enqueue_search(spmb_context *ctx, const spmb_store *s, const spmb_pat
         a.lay = s->lay;
         a.n_tiles = s->lay.n_cols / 32;
         a.pat = p->d_ranks + p->off[i];
-        a.row_len = s->row_len; a.row_seq = s->row_seq;
+        a.row_len = s->row_len; a.row_seq = s->row_seq; a.row_own = s->row_own;
         a.m = p->len[i];
         a.J = std::min<uint32_t>(a.m, 8);
         a.filt_syms = p->filt[i];
-        a.seq_id = 0;
+        a.seq_id = seq_id;
         a.pattern_id = i;
         a.sink = sink;
         unsigned blocks = (unsigned)((a.n_tiles + 255) / 256);
@@ -637,6 +639,267 @@ extern "C" int spmb_search_host(spmb_context *ctx, const uint8_t *host_ranks, ui
     ctx->launches += pack_launches;
     spmb_store_destroy(s);
     return rc;
+}
+
+
+// ------------------------------------------------------------------------------------------
+// journaled string tree
+// ------------------------------------------------------------------------------------------
+struct JstBucket {
+    spmb_store *store = nullptr;
+    uint64_t first = 0, count = 0;
+};
+
+struct spmb_jst {
+    spmb_context *ctx = nullptr;
+    const spmb_store *ref = nullptr;
+    JstHost H;
+    spmb_journal_event *d_var = nullptr;
+    uint8_t *d_pool = nullptr;
+    JstFlatHost flat;
+    bool have_flat = false;
+    JstWindow *d_win = nullptr;
+    uint32_t *d_win_vars = nullptr;
+    std::vector<JstBucket> buckets;
+    uint64_t stats[4] = {0, 0, 0, 0};
+    double ms[4] = {0, 0, 0, 0};
+};
+
+static const uint32_t JST_REF_SEQ = 0xffffffffu;
+
+static void jst_drop_flat(spmb_jst *j)
+{
+    for (auto &b : j->buckets) spmb_store_destroy(b.store);
+    j->buckets.clear();
+    cudaFree(j->d_win); j->d_win = nullptr;
+    cudaFree(j->d_win_vars); j->d_win_vars = nullptr;
+    j->have_flat = false;
+}
+
+extern "C" int spmb_jst_create(spmb_context *ctx, const spmb_store *reference, const spmb_journal_event *variants,
+                               uint64_t n_var, const uint8_t *pool, uint64_t pool_len, const uint64_t *coverage,
+                               uint32_t n_hap, spmb_jst **out)
+{
+    if (!ctx || !reference || !out || n_hap == 0 || (n_var && (!variants || !coverage)) || (pool_len && !pool))
+        return SPMB_ERR_ARG;
+    if (reference->lay.mode != SPMB_MODE_PLAIN) return set_err(ctx, SPMB_ERR_ARG, "JST reference must be a plain store");
+    if (n_var >= (1ull << 32)) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "more than 2^32 variants");
+    CU(cudaSetDevice(ctx->device));
+    spmb_jst *j = new (std::nothrow) spmb_jst();
+    if (!j) return SPMB_ERR_OOM;
+    j->ctx = ctx; j->ref = reference;
+    JstHost &H = j->H;
+    H.n_hap = n_hap; H.wpr = (n_hap + 63) / 64; H.n_ref = reference->lay.n;
+    H.var.assign(variants, variants + n_var);
+    H.pool.assign(pool, pool + pool_len);
+    H.cov.assign(coverage, coverage + n_var * H.wpr);
+    if (n_hap % 64) {
+        const uint64_t mask = (1ull << (n_hap % 64)) - 1;
+        for (uint64_t v = 0; v < n_var; ++v) H.cov[v * H.wpr + H.wpr - 1] &= mask;
+    }
+    H.max_del = 0;
+    for (uint64_t v = 0; v < n_var; ++v) {
+        const spmb_journal_event &x = H.var[v];
+        if ((v && x.ref_pos < H.var[v - 1].ref_pos) || x.ref_pos + x.del_len > H.n_ref ||
+            (uint64_t)x.ins_off + x.ins_len > pool_len) {
+            delete j;
+            return set_err(ctx, SPMB_ERR_ARG, "JST variants must be sorted by ref_pos and lie inside the reference / pool");
+        }
+        H.max_del = std::max(H.max_del, x.del_len);
+    }
+    H.build_ckpt();
+    cudaError_t e = cudaMalloc(&j->d_var, (n_var ? n_var : 1) * sizeof(spmb_journal_event));
+    if (e == cudaSuccess) e = cudaMalloc(&j->d_pool, pool_len ? pool_len : 1);
+    if (e == cudaSuccess && n_var) e = cudaMemcpyAsync(j->d_var, H.var.data(), n_var * sizeof(spmb_journal_event), cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess && pool_len) e = cudaMemcpyAsync(j->d_pool, H.pool.data(), pool_len, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) { spmb_jst_destroy(j); return set_err(ctx, SPMB_ERR_CUDA, "JST upload", e); }
+    *out = j;
+    return SPMB_OK;
+}
+
+extern "C" int spmb_jst_destroy(spmb_jst *j)
+{
+    if (!j) return SPMB_OK;
+    if (j->ctx) cudaSetDevice(j->ctx->device);
+    jst_drop_flat(j);
+    cudaFree(j->d_var);
+    cudaFree(j->d_pool);
+    delete j;
+    return SPMB_OK;
+}
+
+extern "C" int spmb_jst_last_stats(const spmb_jst *j, uint64_t stats[4], double ms[4])
+{
+    if (!j) return SPMB_ERR_ARG;
+    for (int i = 0; i < 4; ++i) { if (stats) stats[i] = j->stats[i]; if (ms) ms[i] = j->ms[i]; }
+    return SPMB_OK;
+}
+
+// flatten for window size W (cached) and materialise the windows on the device, bucketed by length
+static int jst_prepare(spmb_context *ctx, spmb_jst *j, uint32_t W)
+{
+    if (j->have_flat && j->flat.W == W) { j->ms[0] = 0; j->ms[1] = 0; return SPMB_OK; }
+    jst_drop_flat(j);
+    jst_flatten(j->H, W, j->flat);
+    j->ms[0] = j->flat.flatten_ms;
+    std::vector<JstWindow> &wins = j->flat.wins;
+    const uint64_t nw = wins.size();
+    j->stats[0] = nw; j->stats[1] = j->flat.total_symbols;
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
+    CU(cudaEventRecord(e0, ctx->stream));
+    if (nw) {
+        // windows sorted by length; a row holds len symbols + up to 31 pad columns for the Myers score delay
+        std::stable_sort(wins.begin(), wins.end(), [](const JstWindow &a, const JstWindow &b) { return a.len < b.len; });
+        CU(cudaMalloc(&j->d_win, nw * sizeof(JstWindow)));
+        CU(cudaMalloc(&j->d_win_vars, (j->flat.win_vars.size() + 1) * sizeof(uint32_t)));
+        CU(cudaMemcpyAsync(j->d_win, wins.data(), nw * sizeof(JstWindow), cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaMemcpyAsync(j->d_win_vars, j->flat.win_vars.data(), j->flat.win_vars.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+        uint64_t first = 0;
+        while (first < nw) {
+            // geometric length classes: a bucket takes every window up to 1.25x its shortest row
+            const uint32_t rl_min = (wins[first].len + 32 + 31) / 32 * 32;
+            const uint32_t rl_cap = std::max<uint32_t>(rl_min, (uint32_t)((uint64_t)rl_min * 5 / 4 / 32 * 32));
+            uint64_t last = first;
+            while (last < nw && (wins[last].len + 32 + 31) / 32 * 32 <= rl_cap) ++last;
+            const uint32_t RL = (wins[last - 1].len + 32 + 31) / 32 * 32;
+            const uint64_t count = last - first;
+            const uint64_t rows = (count + 31) / 32 * 32;
+            JstBucket b;
+            b.first = first; b.count = count;
+            int rc = store_alloc(ctx, rows * RL, RL, SPMB_MODE_WINDOWS, &b.store);
+            if (rc) { cudaEventDestroy(e0); cudaEventDestroy(e1); return rc; }
+            j->buckets.push_back(b);
+            std::vector<uint32_t> rl(rows, 0), ro(rows, 0), rs(rows, 0);
+            for (uint64_t r = 0; r < count; ++r) {
+                rl[r] = wins[first + r].len; ro[r] = wins[first + r].own_lo; rs[r] = (uint32_t)(first + r);
+            }
+            CU(cudaMalloc(&b.store->row_len, rows * 4));
+            CU(cudaMalloc(&b.store->row_own, rows * 4));
+            CU(cudaMalloc(&b.store->row_seq, rows * 4));
+            CU(cudaMemcpy(b.store->row_len, rl.data(), rows * 4, cudaMemcpyHostToDevice));
+            CU(cudaMemcpy(b.store->row_own, ro.data(), rows * 4, cudaMemcpyHostToDevice));
+            CU(cudaMemcpy(b.store->row_seq, rs.data(), rows * 4, cudaMemcpyHostToDevice));
+            WindowSource src{j->ref->planes, j->ref->lay, j->d_var, j->d_pool, j->d_win + first, j->d_win_vars, count, b.store->lay};
+            rc = store_pack(ctx, b.store, src);
+            if (rc) { cudaEventDestroy(e0); cudaEventDestroy(e1); return rc; }
+            first = last;
+        }
+    }
+    CU(cudaEventRecord(e1, ctx->stream));
+    CU(cudaEventSynchronize(e1));
+    float t = 0;
+    cudaEventElapsedTime(&t, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    j->ms[1] = t;
+    j->stats[2] = j->buckets.size();
+    j->have_flat = true;
+    return SPMB_OK;
+}
+
+static int jst_enqueue(spmb_context *ctx, spmb_jst *j, const spmb_pattern *p, spmb_hits *h)
+{
+    int rc = enqueue_search(ctx, j->ref, p, h, true, JST_REF_SEQ); // one scan of the reference
+    if (rc) return rc;
+    for (auto &b : j->buckets) {                                   // + the branch-context windows
+        rc = enqueue_search(ctx, b.store, p, h, false, 0);
+        if (rc) return rc;
+    }
+    return SPMB_OK;
+}
+
+extern "C" int spmb_jst_search(spmb_context *ctx, spmb_jst *j, const spmb_pattern *p, spmb_hits *h)
+{
+    if (!ctx || !j || !p || !h) return SPMB_ERR_ARG;
+    CU(cudaSetDevice(ctx->device));
+    ctx->launches = 0;
+    h->count = 0;
+    h->host.clear();
+    const uint32_t W = spmb_pattern_window_size(p);
+    j->stats[3] = 0; j->ms[2] = j->ms[3] = 0;
+    if (W == 0) return SPMB_OK;
+    int rc = jst_prepare(ctx, j, W);
+    if (rc) return rc;
+
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
+    std::vector<spmb_hit> raw;
+    for (int attempt = 0;; ++attempt) {
+        CU(cudaEventRecord(e0, ctx->stream));
+        rc = jst_enqueue(ctx, j, p, h);
+        if (rc) return rc;
+        CU(cudaEventRecord(e1, ctx->stream));
+        CU(cudaMemcpyAsync(ctx->h_count, h->d_count, sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+        const unsigned long long cnt = *ctx->h_count;
+        if (cnt <= h->cap) {
+            raw.resize(cnt);
+            if (cnt) CU(cudaMemcpy(raw.data(), h->d_hits, cnt * sizeof(spmb_hit), cudaMemcpyDeviceToHost));
+            break;
+        }
+        if (attempt >= 3) return set_err(ctx, SPMB_ERR_CUDA, "hit buffer kept overflowing");
+        rc = hits_reserve(ctx, h, cnt + cnt / 8 + 1024);
+        if (rc) return rc;
+    }
+    float t = 0;
+    cudaEventElapsedTime(&t, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    j->ms[2] = t;
+    j->stats[3] = raw.size();
+
+    // ---- host: expand every device hit to the haplotypes it stands for ----
+    const auto t0 = std::chrono::steady_clock::now();
+    const JstHost &H = j->H;
+    std::sort(raw.begin(), raw.end(), [](const spmb_hit &a, const spmb_hit &b) {
+        if (a.seq_id != b.seq_id) return a.seq_id < b.seq_id;
+        if (a.end != b.end) return a.end < b.end;
+        return a.pattern_id < b.pattern_id;
+    });
+    std::vector<uint64_t> cov;
+    std::vector<int64_t> shift;
+    std::vector<spmb_hit> &out = h->host;
+    size_t i = 0;
+    while (i < raw.size()) {
+        size_t e = i;
+        uint64_t base_pos = 0;
+        if (raw[i].seq_id == JST_REF_SEQ) {
+            // all reference hits with the same end share the haplotype set and the shifts
+            while (e < raw.size() && raw[e].seq_id == JST_REF_SEQ && raw[e].end == raw[i].end) ++e;
+            const uint64_t E = raw[i].end;
+            H.clean_cov(E, W, cov);
+            const uint64_t hi = std::lower_bound(H.var.begin(), H.var.end(), E,
+                                                 [](const spmb_journal_event &x, uint64_t v) { return x.ref_pos < v; }) - H.var.begin();
+            H.shifts_before(hi, shift);
+        } else {
+            while (e < raw.size() && raw[e].seq_id == raw[i].seq_id) ++e;
+            const JstWindow &wd = j->flat.wins[raw[i].seq_id];
+            const uint32_t *ids = j->flat.win_vars.data() + wd.var_off;
+            H.window_cov(ids, wd.n_var, W, cov);
+            H.shifts_before(ids[0], shift);
+            base_pos = wd.ref_start;
+        }
+        for (uint32_t w = 0; w < H.wpr; ++w) {
+            uint64_t bits = cov[w];
+            while (bits) {
+                const uint32_t hap = w * 64 + (uint32_t)__builtin_ctzll(bits);
+                bits &= bits - 1;
+                if (hap >= H.n_hap) continue;
+                for (size_t q = i; q < e; ++q) {
+                    spmb_hit x = raw[q];
+                    x.end = (uint64_t)((int64_t)(raw[q].end + base_pos) + shift[hap]);
+                    x.seq_id = hap;
+                    out.push_back(x);
+                }
+            }
+        }
+        i = e;
+    }
+    std::sort(out.begin(), out.end(), hit_less);
+    h->count = out.size();
+    h->pend_store = nullptr; h->pend_pat = nullptr;
+    j->ms[3] = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return SPMB_OK;
 }
 
 // ------------------------------------------------------------------------------------------

@@ -76,3 +76,44 @@ def finish_snps(ev, pool, kinds, ref_at_snp: np.ndarray):
     o = ev["ins_off"][snp].astype(np.int64)
     pool[o] = (ref_at_snp.astype(np.int64) + 1 + (pool[o] % 3)) % 4
     return pool
+
+
+def jst(n_ref: int, n_var: int, n_hap: int, seed: int, p_snp: float = 0.9, p_ins: float = 0.05,
+        max_indel: int = 10, af_max: float = 0.5, chunk: int = 8192):
+    """C4-style journaled string tree: n_var variants at sorted, non-overlapping
+    seeded positions (90% SNP, 5% insertion U[1,max], 5% deletion U[1,max]); allele frequency ~
+    truncated 1/x on [1/n_hap, af_max]; membership Bernoulli(AF) per haplotype (no LD).
+    Returns (variants[EVENT_DTYPE], pool, kinds, coverage[n_var, ceil(n_hap/64)] uint64).
+    SNP alts are offsets to be fixed with finish_snps()."""
+    rng = np.random.default_rng(seed)
+    mean_gap = n_ref / (n_var + 1)
+    lo = max_indel + 2
+    hi = max(lo + 1, int(2 * mean_gap) - lo)
+    gaps = rng.integers(lo, hi + 1, size=n_var, dtype=np.int64)
+    pos = np.cumsum(gaps)
+    pos = pos[pos < n_ref - 2 * max_indel - 2]
+    n_var = len(pos)
+    u = rng.random(n_var)
+    kinds = np.where(u < p_snp, 0, np.where(u < p_snp + p_ins, 1, 2)).astype(np.uint8)
+    lens = rng.integers(1, max_indel + 1, size=n_var, dtype=np.uint32)
+    var = np.zeros(n_var, dtype=EVENT_DTYPE)
+    var["ref_pos"] = pos
+    var["del_len"] = np.where(kinds == 0, 1, np.where(kinds == 2, lens, 0))
+    var["ins_len"] = np.where(kinds == 0, 1, np.where(kinds == 1, lens, 0))
+    ins_len = var["ins_len"].astype(np.int64)
+    var["ins_off"] = np.cumsum(ins_len) - ins_len
+    pool = rng.integers(0, 4, size=int(ins_len.sum()), dtype=np.uint8)
+    af = np.exp(rng.uniform(np.log(1.0 / n_hap), np.log(af_max), size=n_var))
+    wpr = (n_hap + 63) // 64
+    cov = np.zeros((n_var, wpr), dtype=np.uint64)
+    thr = np.minimum((af * 65536.0).astype(np.int64), 65535).astype(np.uint16)
+    for o in range(0, n_var, chunk):
+        e = min(n_var, o + chunk)
+        bits = rng.integers(0, 65536, size=(e - o, wpr * 64), dtype=np.uint16) < thr[o:e, None]
+        bits[:, n_hap:] = False
+        # every variant is carried by at least one haplotype
+        none = ~bits.any(axis=1)
+        if none.any():
+            bits[np.nonzero(none)[0], rng.integers(0, n_hap, size=int(none.sum()))] = True
+        cov[o:e] = np.packbits(bits, axis=1, bitorder="little").view(np.uint64)
+    return var, pool, kinds, cov

@@ -57,6 +57,13 @@ def lib():
         L.orc_max_threads.restype = C.c_int
         L.orc_journal_apply.restype = C.c_uint64
         L.orc_journal_apply.argtypes = [u8p, C.c_uint64, C.c_void_p, C.c_uint64, u8p, u8p, C.c_uint64]
+        L.orc_jst_search.restype = C.c_uint64
+        L.orc_jst_search.argtypes = [C.c_int, u8p, C.c_uint64, C.c_void_p, C.c_uint64, u8p, C.c_void_p, C.c_uint32,
+                                     C.c_uint32, C.c_void_p, C.c_uint32, u8p, C.c_uint32, C.c_uint32, C.c_int,
+                                     C.c_void_p, C.c_uint64]
+        L.orc_jst_haplotype.restype = C.c_uint64
+        L.orc_jst_haplotype.argtypes = [u8p, C.c_uint64, C.c_void_p, C.c_uint64, u8p, C.c_void_p, C.c_uint32,
+                                        C.c_uint32, u8p, C.c_uint64]
         _lib = L
     return _lib
 
@@ -191,3 +198,42 @@ def journal_apply(ref, events, pool):
     out = np.empty(n, dtype=np.uint8)
     L.orc_journal_apply(rp, len(ref), ev.ctypes.data, len(ev), pp, out.ctypes.data, n)
     return out
+
+
+JST_HIT_DTYPE = np.dtype([("end", "<u8"), ("hap", "<u4"), ("err", "<u4")])
+
+
+def jst_haplotype(ref, variants, pool, cov, hap):
+    """cov: uint64 array [n_var, words_per_row]."""
+    L = lib()
+    ref, rp = _u8(ref)
+    pool, pp = _u8(pool if len(pool) else np.zeros(1, np.uint8))
+    var = np.ascontiguousarray(variants, dtype=EVENT_DTYPE)
+    cov = np.ascontiguousarray(cov, dtype=np.uint64)
+    wpr = cov.shape[1]
+    n = int(L.orc_jst_haplotype(rp, len(ref), var.ctypes.data, len(var), pp, cov.ctypes.data, wpr, int(hap), None, 0))
+    out = np.empty(n, dtype=np.uint8)
+    L.orc_jst_haplotype(rp, len(ref), var.ctypes.data, len(var), pp, cov.ctypes.data, wpr, int(hap), out.ctypes.data, n)
+    return out
+
+
+def jst_search(alg, ref, variants, pool, cov, n_hap, pat, k=0, haps=None, threads=None):
+    """materialise every (listed) haplotype and search it; returns JST_HIT_DTYPE sorted by (hap, end)."""
+    L = lib()
+    ref, rp = _u8(ref)
+    pool, pp = _u8(pool if len(pool) else np.zeros(1, np.uint8))
+    pat, tp = _u8(pat)
+    var = np.ascontiguousarray(variants, dtype=EVENT_DTYPE)
+    cov = np.ascontiguousarray(cov, dtype=np.uint64)
+    wpr = cov.shape[1]
+    hl = None if haps is None else np.ascontiguousarray(haps, dtype=np.uint32)
+    threads = int(threads or L.orc_max_threads())
+    cap = 1 << 16
+    while True:
+        out = np.empty(cap, dtype=JST_HIT_DTYPE)
+        cnt = int(L.orc_jst_search(alg, rp, len(ref), var.ctypes.data, len(var), pp, cov.ctypes.data, int(n_hap), wpr,
+                                   None if hl is None else hl.ctypes.data, 0 if hl is None else len(hl), tp, len(pat),
+                                   int(k), threads, out.ctypes.data, cap))
+        if cnt <= cap:
+            return out[:cnt].copy()
+        cap = cnt

@@ -448,3 +448,86 @@ uint64_t orc_journal_apply(const uint8_t *ref, uint64_t n, const orc_event_t *ev
     free(der);
     return total;
 }
+
+/* ------------------------------------------------------------------ */
+/* journaled string tree: per-haplotype materialise + search           */
+/* ------------------------------------------------------------------ */
+
+static uint64_t jst_collect(const orc_event_t *var, uint64_t n_var, const uint64_t *cov, uint32_t wpr,
+                            uint32_t hap, orc_event_t *out)
+{
+    uint64_t c = 0;
+    const uint64_t bit = 1ull << (hap & 63);
+    const uint32_t w = hap >> 6;
+    for (uint64_t v = 0; v < n_var; ++v)
+        if (cov[v * wpr + w] & bit) { if (out) out[c] = var[v]; ++c; }
+    return c;
+}
+
+uint64_t orc_jst_haplotype(const uint8_t *ref, uint64_t n, const orc_event_t *var, uint64_t n_var,
+                           const uint8_t *pool, const uint64_t *cov, uint32_t wpr, uint32_t hap,
+                           uint8_t *out, uint64_t out_cap)
+{
+    uint64_t c = jst_collect(var, n_var, cov, wpr, hap, NULL);
+    orc_event_t *ev = (orc_event_t *)malloc((c + 1) * sizeof(orc_event_t));
+    jst_collect(var, n_var, cov, wpr, hap, ev);
+    uint64_t len = orc_journal_apply(ref, n, ev, c, pool, out, out_cap);
+    free(ev);
+    return len;
+}
+
+static int jst_hit_cmp(const void *a, const void *b)
+{
+    const orc_jst_hit_t *x = (const orc_jst_hit_t *)a, *y = (const orc_jst_hit_t *)b;
+    if (x->hap != y->hap) return x->hap < y->hap ? -1 : 1;
+    if (x->end != y->end) return x->end < y->end ? -1 : 1;
+    return 0;
+}
+
+uint64_t orc_jst_search(int alg, const uint8_t *ref, uint64_t n, const orc_event_t *var, uint64_t n_var,
+                        const uint8_t *pool, const uint64_t *cov, uint32_t n_hap, uint32_t wpr,
+                        const uint32_t *haps, uint32_t n_list, const uint8_t *pat, uint32_t m, uint32_t k,
+                        int threads, orc_jst_hit_t *out, uint64_t cap)
+{
+    const uint32_t count = haps ? n_list : n_hap;
+    uint64_t total = 0;
+    if (threads < 1) threads = 1;
+#ifdef _OPENMP
+#pragma omp parallel for num_threads(threads) schedule(dynamic, 1)
+#endif
+    for (int64_t i = 0; i < (int64_t)count; ++i) {
+        const uint32_t h = haps ? haps[i] : (uint32_t)i;
+        uint64_t len = orc_jst_haplotype(ref, n, var, n_var, pool, cov, wpr, h, NULL, 0);
+        if (len == (uint64_t)-1) continue;
+        uint8_t *seq = (uint8_t *)malloc(len + 1);
+        orc_jst_haplotype(ref, n, var, n_var, pool, cov, wpr, h, seq, len);
+        uint64_t hc = 1024, c;
+        uint64_t *ends = NULL;
+        uint32_t *errs = NULL;
+        for (;;) {
+            ends = (uint64_t *)realloc(ends, hc * sizeof(uint64_t));
+            errs = (uint32_t *)realloc(errs, hc * sizeof(uint32_t));
+            if (alg == 3) c = orc_myers(seq, len, pat, m, k, ends, errs, hc);
+            else if (alg == 2) c = orc_shiftor(seq, len, pat, m, ends, hc);
+            else c = orc_horspool(seq, len, pat, m, ends, hc);
+            if (c <= hc) break;
+            hc = c;
+        }
+#ifdef _OPENMP
+#pragma omp critical
+#endif
+        {
+            for (uint64_t j = 0; j < c; ++j) {
+                if (total < cap && out) {
+                    out[total].end = ends[j];
+                    out[total].hap = h;
+                    out[total].err = (alg == 3) ? errs[j] : 0;
+                }
+                ++total;
+            }
+        }
+        free(ends); free(errs); free(seq);
+    }
+    if (out) qsort(out, total < cap ? total : cap, sizeof(orc_jst_hit_t), jst_hit_cmp);
+    return total;
+}

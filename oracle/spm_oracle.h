@@ -92,6 +92,21 @@ typedef struct { uint64_t ref_pos; uint32_t del_len; uint32_t ins_len; uint64_t 
 uint64_t orc_journal_apply(const uint8_t *ref, uint64_t n, const orc_event_t *ev, uint64_t n_ev,
                            const uint8_t *pool, uint8_t *out, uint64_t out_cap);
 
+/* ---- journaled string tree (a14): oracle = materialise every haplotype, then plain search ----
+ * var[]: n_var variants sorted by ref_pos (same record as a journal event); cov: n_var rows of
+ * words_per_row 64-bit words, bit h of row v set = haplotype h carries variant v.  A haplotype's
+ * carried variants must not overlap.  haps == NULL means all n_hap haplotypes, else the listed ones.
+ * Hits (haplotype, end in that haplotype's coordinates, errors), sorted by (hap, end). */
+typedef struct { uint64_t end; uint32_t hap; uint32_t err; } orc_jst_hit_t;
+uint64_t orc_jst_search(int alg, const uint8_t *ref, uint64_t n, const orc_event_t *var, uint64_t n_var,
+                        const uint8_t *pool, const uint64_t *cov, uint32_t n_hap, uint32_t words_per_row,
+                        const uint32_t *haps, uint32_t n_list, const uint8_t *pat, uint32_t m, uint32_t k,
+                        int threads, orc_jst_hit_t *out, uint64_t cap);
+/* one haplotype's sequence; returns its length (out may be NULL for a size query) */
+uint64_t orc_jst_haplotype(const uint8_t *ref, uint64_t n, const orc_event_t *var, uint64_t n_var,
+                           const uint8_t *pool, const uint64_t *cov, uint32_t words_per_row, uint32_t hap,
+                           uint8_t *out, uint64_t out_cap);
+
 #ifdef __cplusplus
 }
 #endif

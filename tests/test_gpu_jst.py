@@ -1,0 +1,105 @@
+"""JST search (host flattening into branch-context windows + one reference scan) against the
+oracle that materialises every haplotype and searches it."""
+import numpy as np
+import pytest
+
+import libspm_b200 as sp
+import oracle as orc
+from libspm_b200 import synth
+from tests.util import mutate, rand_text
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = sp.Context(0)
+    yield c
+    c.close()
+
+
+def make_jst(n_ref, n_var, n_hap, seed, **kw):
+    rng = np.random.default_rng(seed)
+    ref = rand_text(rng, n_ref)
+    var, pool, kinds, cov = synth.jst(n_ref, n_var, n_hap, seed, **kw)
+    pool = synth.finish_snps(var, pool, kinds, ref[var["ref_pos"][kinds == 0].astype(np.int64)])
+    return ref, var, pool, cov
+
+
+def compare(got, want, tag):
+    g = np.stack([got["seq_id"].astype(np.int64), got["end"].astype(np.int64), got["errors"].astype(np.int64)], 1)
+    w = np.stack([want["hap"].astype(np.int64), want["end"].astype(np.int64), want["err"].astype(np.int64)], 1)
+    if g.shape == w.shape and np.array_equal(g, w):
+        return
+    gs, ws = set(map(tuple, g.tolist())), set(map(tuple, w.tolist()))
+    raise AssertionError(f"{tag}: got {len(g)} want {len(w)}; missing {sorted(ws - gs)[:8]} extra {sorted(gs - ws)[:8]} "
+                         f"dup={len(g) - len(gs)}")
+
+
+@pytest.mark.parametrize("n_hap,n_var,seed", [(70, 600, 1), (64, 300, 2), (5, 900, 3), (130, 1500, 4)])
+def test_jst_vs_per_haplotype_oracle(ctx, n_hap, n_var, seed):
+    n_ref = 20_000
+    ref, var, pool, cov = make_jst(n_ref, n_var, n_hap, seed, p_snp=0.6, p_ins=0.2, max_indel=8, af_max=0.7)
+    rng = np.random.default_rng(seed + 100)
+    store = sp.Store.from_host(ctx, ref)
+    jst = sp.Jst(ctx, store, var, pool, cov, n_hap)
+    # haplotype materialisation sanity (oracle side): lengths differ by the carried indels
+    h0 = orc.jst_haplotype(ref, var.astype(orc.EVENT_DTYPE), pool, cov, 0)
+    assert abs(len(h0) - n_ref) < 10 * n_var
+    cases = []
+    for (alg, m, k) in [(sp.ALG_SHIFTOR, 12, 0), (sp.ALG_HORSPOOL, 33, 0), (sp.ALG_MYERS, 24, 2), (sp.ALG_MYERS, 40, 3),
+                        (sp.ALG_MYERS, 70, 5)]:
+        # needles cut from haplotypes (so that they cross variants) and from the reference
+        for src_h in (0, n_hap - 1, None):
+            seq = ref if src_h is None else orc.jst_haplotype(ref, var.astype(orc.EVENT_DTYPE), pool, cov, src_h)
+            s = int(rng.integers(0, len(seq) - m))
+            pat = seq[s:s + m].copy()
+            if alg == sp.ALG_MYERS:
+                pat = mutate(rng, pat, 1)
+            cases.append((alg, pat, k))
+    for alg, pat, k in cases:
+        p = sp.Pattern(ctx, alg, pat, k)
+        got = jst.search(p)
+        want = orc.jst_search(alg, ref, var.astype(orc.EVENT_DTYPE), pool, cov, n_hap, pat, k)
+        compare(got, want, f"alg={alg} m={len(pat)} k={k} haps={n_hap}")
+        assert len(want) >= 1
+    st = jst.last_stats()
+    assert st["windows"] > 0 and st["buckets"] >= 1
+    jst.close()
+
+
+def test_jst_edges(ctx):
+    # variants at the very start / end, adjacent indels, a haplotype without variants, no variants at all
+    rng = np.random.default_rng(9)
+    n_ref, n_hap = 3_000, 10
+    ref = rand_text(rng, n_ref)
+    pool = rand_text(rng, 64)
+    var = np.array([(0, 0, 3, 0), (0, 1, 1, 3), (5, 2, 0, 0), (7, 0, 4, 4), (40, 1, 1, 8), (41, 1, 1, 9),
+                    (1500, 6, 2, 10), (1506, 0, 5, 12), (2990, 3, 0, 0), (2999, 1, 1, 20)], dtype=sp.EVENT_DTYPE)
+    cov = np.zeros((len(var), 1), dtype=np.uint64)
+    sets = {0: [0, 1, 2, 3], 1: [0], 2: [1, 4, 5], 3: [2, 3, 6, 7], 4: [8, 9], 5: [9], 6: [4], 7: [5, 6], 8: [0, 1, 2, 3, 4, 5, 6, 7, 8, 9]}
+    for h, vs in sets.items():          # haplotype 9 carries nothing
+        for v in vs:
+            cov[v, 0] |= np.uint64(1 << h)
+    pool[3] = (ref[0] + 1) % 4
+    pool[8] = (ref[40] + 1) % 4
+    pool[9] = (ref[41] + 2) % 4
+    pool[20] = (ref[2999] + 1) % 4
+    store = sp.Store.from_host(ctx, ref)
+    jst = sp.Jst(ctx, store, var, pool, cov, n_hap)
+    ev = var.astype(orc.EVENT_DTYPE)
+    for h in (0, 3, 8):
+        seq = orc.jst_haplotype(ref, ev, pool, cov, h)
+        for (alg, m, k, s) in [(sp.ALG_SHIFTOR, 9, 0, 0), (sp.ALG_MYERS, 16, 2, 0), (sp.ALG_MYERS, 16, 2, len(seq) - 16),
+                               (sp.ALG_HORSPOOL, 30, 0, 1490), (sp.ALG_MYERS, 35, 4, 1480), (sp.ALG_SHIFTOR, 5, 0, len(seq) - 5)]:
+            pat = seq[s:s + m].copy()
+            got = jst.search(sp.Pattern(ctx, alg, pat, k))
+            want = orc.jst_search(alg, ref, ev, pool, cov, n_hap, pat, k)
+            compare(got, want, f"edges h={h} alg={alg} m={m} k={k} s={s}")
+    jst.close()
+    # no variants: every reference hit belongs to every haplotype
+    j0 = sp.Jst(ctx, store, np.zeros(0, sp.EVENT_DTYPE), np.zeros(0, np.uint8), np.zeros((0, 1), np.uint64), 3)
+    pat = ref[100:120].copy()
+    got = j0.search(sp.Pattern(ctx, sp.ALG_HORSPOOL, pat))
+    assert len(got) == 3 * len(orc.exact_bruteforce(ref, pat))
+    assert sorted(set(got["seq_id"].tolist())) == [0, 1, 2]
