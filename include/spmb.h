@@ -81,6 +81,12 @@ int spmb_context_destroy(spmb_context *ctx);
 void *spmb_context_stream(const spmb_context *ctx);
 const char *spmb_last_error(const spmb_context *ctx);
 int spmb_context_sync(spmb_context *ctx);
+/* Multi-GPU sharding: every later search on this context covers only shard
+ * `shard` of `n_shards` of each store it is given (contiguous ranges of super-tiles; a hit
+ * belongs to the shard that holds its begin (exact) / end (Myers) position).  The shards of one
+ * store partition its hit list: ranks search disjoint shards with no exchange, the driver
+ * concatenates the small hit lists afterwards.  Default (0, 1) = everything. */
+int spmb_context_set_shard(spmb_context *ctx, uint32_t shard, uint32_t n_shards);
 
 /* ---------------- sequence store (north_star item 1) ----------------
  * Replaces the haystack argument of seqan_pattern_base::operator()

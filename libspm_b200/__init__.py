@@ -37,6 +37,7 @@ EXPORTS = [
     "spmb_search_host", "spmb_last_launch_count", "spmb_stream_create", "spmb_stream_destroy",
     "spmb_stream_feed", "spmb_stream_capture", "spmb_stream_restore", "spmb_measure_int_peak",
     "spmb_device_info", "spmb_jst_create", "spmb_jst_destroy", "spmb_jst_search", "spmb_jst_last_stats",
+    "spmb_context_set_shard",
 ]
 
 
@@ -71,6 +72,7 @@ def lib():
             "spmb_context_stream": (vp, [vp]),
             "spmb_last_error": (C.c_char_p, [vp]),
             "spmb_context_sync": (i32, [vp]),
+            "spmb_context_set_shard": (i32, [vp, u32, u32]),
             "spmb_store_create": (i32, [vp, vp, u64, u32, pp]),
             "spmb_store_create_from_device": (i32, [vp, vp, u64, u32, pp]),
             "spmb_store_create_journaled": (i32, [vp, vp, vp, u64, vp, u64, u32, pp]),
@@ -141,6 +143,10 @@ class Context:
 
     def sync(self):
         self._check(lib().spmb_context_sync(self._h), "spmb_context_sync")
+
+    def set_shard(self, shard: int, n_shards: int):
+        """later searches cover only this shard (contiguous super-tile range) of every store."""
+        self._check(lib().spmb_context_set_shard(self._h, shard, n_shards), "spmb_context_set_shard")
 
     @property
     def stream(self) -> int:

@@ -23,7 +23,8 @@
 struct ExactArgs {
     const uint4 *planes;     // packed store viewed as uint4 (two columns)
     SpmbLayout lay;
-    uint64_t n_tiles;        // n_cols / 32 thread-rows
+    uint64_t n_tiles;        // one past the last thread-row of this launch
+    uint64_t tile0;          // first thread-row of this launch (shards cover disjoint super-tile ranges)
     const uint8_t *pat;      // m ranks (device)
     const uint32_t *row_len; // windows mode: valid symbols per row; else null
     const uint32_t *row_seq; // windows mode: seq id per row; else null
@@ -135,7 +136,7 @@ __global__ void __launch_bounds__(256, 2) exact_kernel(ExactArgs a)
 {
     __shared__ uint32_t sbuf[8][32][33];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint64_t tile = (uint64_t)blockIdx.x * 256 + threadIdx.x;
+    const uint64_t tile = a.tile0 + (uint64_t)blockIdx.x * 256 + threadIdx.x;
     const uint32_t J = a.J, fs = a.filt_syms;
     const uint32_t RL = a.lay.row_len;
     uint32_t acc[32];

@@ -40,6 +40,7 @@ struct MyersArgs {
     const uint32_t *row_own;  // windows mode: first owned end index (local), may be null
     uint32_t warm;            // plain mode: warm-up columns, multiple of 32, >= max(m+k-1)
     uint32_t seq_id;
+    uint64_t st0, st1;        // super-tile range of this launch
     HitSink sink;
 };
 
@@ -91,8 +92,8 @@ __global__ void __launch_bounds__(128) myers_kernel(MyersArgs a)
     __syncthreads();
     const MyersPatMeta pm = a.meta[pat];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint64_t st = (uint64_t)blockIdx.x * 4 + warp;
-    if (st >= a.lay.n_st) return;
+    const uint64_t st = a.st0 + (uint64_t)blockIdx.x * 4 + warp;
+    if (st >= a.st1) return;
     const uint32_t RL = a.lay.row_len;
     const uint64_t R = st * 32 + lane;
     if (R * RL >= a.lay.n) return; // no warp-synchronous operation below this line

@@ -32,6 +32,7 @@ struct spmb_context {
     uint32_t launches = 0;
     int sm_count = 0;
     unsigned long long *h_count = nullptr; // pinned (8 slots)
+    uint32_t shard = 0, n_shards = 1;      // searches cover super-tiles [n_st*shard/n, n_st*(shard+1)/n)
 };
 
 struct spmb_store {
@@ -159,6 +160,14 @@ extern "C" int spmb_context_destroy(spmb_context *ctx)
 extern "C" void *spmb_context_stream(const spmb_context *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
 extern "C" const char *spmb_last_error(const spmb_context *ctx) { return ctx ? ctx->err.c_str() : "null context"; }
 extern "C" uint32_t spmb_last_launch_count(const spmb_context *ctx) { return ctx ? ctx->launches : 0; }
+
+extern "C" int spmb_context_set_shard(spmb_context *ctx, uint32_t shard, uint32_t n_shards)
+{
+    if (!ctx || n_shards == 0 || shard >= n_shards) return SPMB_ERR_ARG;
+    ctx->shard = shard;
+    ctx->n_shards = n_shards;
+    return SPMB_OK;
+}
 
 extern "C" int spmb_context_sync(spmb_context *ctx)
 {
@@ -510,7 +519,9 @@ extern "C" const spmb_hit *spmb_hits_data(const spmb_hits *h) { return (h && !h-
 template <int MODE>
 static cudaError_t launch_myers(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p, const MyersArgs &a)
 {
-    dim3 grid((unsigned)((s->lay.n_st + 3) / 4), p->n_pat);
+    (void)s;
+    if (a.st1 <= a.st0) return cudaSuccess;
+    dim3 grid((unsigned)((a.st1 - a.st0 + 3) / 4), p->n_pat);
     switch (p->NW) {
     case 1: myers_kernel<1, MODE><<<grid, 128, 0, ctx->stream>>>(a); break;
     case 2: myers_kernel<2, MODE><<<grid, 128, 0, ctx->stream>>>(a); break;
@@ -532,6 +543,8 @@ static int enqueue_search(spmb_context *ctx, const spmb_store *s, const spmb_pat
     if (reset) CU(cudaMemsetAsync(h->d_count, 0, sizeof(unsigned long long), ctx->stream));
     HitSink sink{h->d_hits, h->d_count, h->cap};
     if (p->max_m == 0 || s->lay.n == 0) return SPMB_OK; // empty needle / haystack: no hits
+    const uint64_t st0 = s->lay.n_st * ctx->shard / ctx->n_shards;
+    const uint64_t st1 = s->lay.n_st * (ctx->shard + 1) / ctx->n_shards;
     if (p->alg == SPMB_ALG_MYERS) {
         if (p->n_pat > 65535) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "more than 65535 patterns in one Myers set");
         MyersArgs a;
@@ -542,6 +555,7 @@ static int enqueue_search(spmb_context *ctx, const spmb_store *s, const spmb_pat
         a.row_len = s->row_len; a.row_seq = s->row_seq; a.row_own = s->row_own;
         a.warm = p->warm;
         a.seq_id = seq_id;
+        a.st0 = st0; a.st1 = st1;
         a.sink = sink;
         cudaError_t e = (s->lay.mode == SPMB_MODE_PLAIN) ? launch_myers<SPMB_MODE_PLAIN>(ctx, s, p, a)
                                                           : launch_myers<SPMB_MODE_WINDOWS>(ctx, s, p, a);
@@ -556,7 +570,9 @@ static int enqueue_search(spmb_context *ctx, const spmb_store *s, const spmb_pat
         ExactArgs a;
         a.planes = reinterpret_cast<const uint4 *>(s->planes);
         a.lay = s->lay;
-        a.n_tiles = s->lay.n_cols / 32;
+        a.tile0 = st0 * (s->lay.row_len / 32);
+        a.n_tiles = st1 * (s->lay.row_len / 32);
+        if (a.n_tiles <= a.tile0) continue;
         a.pat = p->d_ranks + p->off[i];
         a.row_len = s->row_len; a.row_seq = s->row_seq; a.row_own = s->row_own;
         a.m = p->len[i];
@@ -565,7 +581,7 @@ static int enqueue_search(spmb_context *ctx, const spmb_store *s, const spmb_pat
         a.seq_id = seq_id;
         a.pattern_id = i;
         a.sink = sink;
-        unsigned blocks = (unsigned)((a.n_tiles + 255) / 256);
+        unsigned blocks = (unsigned)((a.n_tiles - a.tile0 + 255) / 256);
         if (s->lay.mode == SPMB_MODE_PLAIN) exact_kernel<SPMB_MODE_PLAIN><<<blocks, 256, 0, ctx->stream>>>(a);
         else exact_kernel<SPMB_MODE_WINDOWS><<<blocks, 256, 0, ctx->stream>>>(a);
         ctx->launches++;
