@@ -213,9 +213,12 @@ def run_ours(args):
 
         if world > 1:
             dist.barrier()
-        with ClockSampler(local) as clk:
-            total_ms, kern_ms, n_hits, launches = time_search(sp, torch, ctx, stream, js, pattern, hits,
-                                                              args.steps, args.warmup)
+        # clocks are sampled from the warm-up to the end of the e2e legs (the timed region of the
+        # headline alone is a few ms -- shorter than nvidia-smi's sampling period)
+        clk = ClockSampler(local)
+        clk.__enter__()
+        total_ms, kern_ms, n_hits, launches = time_search(sp, torch, ctx, stream, js, pattern, hits,
+                                                          args.steps, args.warmup)
         if world > 1:
             t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -239,7 +242,6 @@ def run_ours(args):
                          "kernel": "exact_kernel<plain>", "kernel_ms": kern_ms,
                          "algorithmic_bytes_per_launch": n_der * BYTES_PER_BP},
             "gpu_launches": launches * args.steps,
-            "clocks": clk.summary(),
         })
 
         # ---------------- e2e: host buffers -> hits through the C ABI ----------------
@@ -290,12 +292,16 @@ def run_ours(args):
                                "h2d_bytes_per_step": m, "d2h_bytes_per_step": int(8 + nh * 24),
                                "path": "spmb_pattern_create(host needle) + spmb_search on the resident store"}
 
+        clk.__exit__()
+        out["clocks"] = clk.summary()
+        out["clocks"]["window"] = "warm-up + timed steps + e2e legs of the headline workload"
+
         # ---------------- CPU baseline + cross-check (rank 0, N=1 only) ----------------
         if rank == 0 and world == 1 and not args.no_cpu:
             import oracle as orc
             s_n = int(min(n_der, args.cpu_sample))
             sample = js.read(0, s_n)
-            threads = orc.max_threads()
+            threads = orc.use_all_cores()
             best = 1e30
             for _ in range(3):
                 t0 = time.perf_counter()
@@ -320,7 +326,7 @@ def run_ours(args):
         dist.barrier()
         dist.destroy_process_group()
     if rank == 0:
-        print(json.dumps(out))
+        emit(out)
 
 
 def _store_from_ptr(sp, ctx, ptr, n):
@@ -371,7 +377,7 @@ def bench_myers(sp, synth, torch, ctx, dev, stream, hits, args, rank, world, hbm
     if rank == 0 and world == 1 and not args.no_cpu:
         import oracle as orc
         host = text.cpu().numpy()
-        threads = orc.max_threads()
+        threads = orc.use_all_cores()
         best = 1e30
         for _ in range(2):
             t0 = time.perf_counter()
@@ -449,7 +455,7 @@ def run_reference(args):
     pool = synth.finish_snps(ev, pool, kinds, ref[ev["ref_pos"][kinds == 0].astype(np.int64)])
     rng = np.random.default_rng(seed ^ 0xABCDEF)
     pat = rng.integers(0, 4, size=m, dtype=np.uint8)
-    threads = orc.max_threads()
+    threads = orc.use_all_cores()
     times = []
     hits = 0
     evo = ev.astype(orc.EVENT_DTYPE)
@@ -469,7 +475,7 @@ def run_reference(args):
     v_search = len(derived) * args.steps / sum(times_search) / 1e9
     sample = (f"{s_n} bp reference + 1% journal (bounded sample of the {args.n} bp workload); each step = host buffers "
               f"in, hit count out: oracle journal apply + oracle Shift-Or (32-bit blocks), both on {threads} threads")
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": "searched_gbp_per_s", "value": v, "unit": "Gbp/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": tot / args.steps * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
@@ -478,10 +484,30 @@ def run_reference(args):
                    "search_only_gbp_per_s": v_search},
         "cpu_baseline": {"value": v, "unit": "Gbp/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "Gbp/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    })
+
+
+def _claim_stdout():
+    """libraries (NCCL prints its version) must not pollute the one-JSON-line contract: route fd 1
+    to stderr for the whole run and hand back a private handle on the real stdout."""
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(os.dup(2), "w", buffering=1)
+    return os.fdopen(real, "w", buffering=1)
+
+
+_REAL_STDOUT = None
+
+
+def emit(obj):
+    _REAL_STDOUT.write(json.dumps(obj) + "\n")
+    _REAL_STDOUT.flush()
 
 
 def main():
+    global _REAL_STDOUT
+    _REAL_STDOUT = _claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)

@@ -55,6 +55,7 @@ def lib():
         L.orc_search_mt.argtypes = [C.c_int, u8p, C.c_uint64, u8p, C.c_uint32, C.c_uint32, C.c_int,
                                     u64p, u32p, C.c_uint64]
         L.orc_max_threads.restype = C.c_int
+        L.orc_set_threads.argtypes = [C.c_int]
         L.orc_journal_apply.restype = C.c_uint64
         L.orc_journal_apply.argtypes = [u8p, C.c_uint64, C.c_void_p, C.c_uint64, u8p, u8p, C.c_uint64]
         L.orc_jst_search.restype = C.c_uint64
@@ -138,6 +139,13 @@ def search_mt(alg, text, pat, k=0, threads=None, store=True, cap=None):
 
 def max_threads():
     return int(lib().orc_max_threads())
+
+
+def use_all_cores():
+    """torchrun exports OMP_NUM_THREADS=1; the CPU baseline is entitled to every core it may run on."""
+    n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    lib().orc_set_threads(n)
+    return n
 
 
 class ShiftOrState:

@@ -305,6 +305,15 @@ uint64_t orc_myers(const uint8_t *text, uint64_t n, const uint8_t *pat, uint32_t
 /* multi-threaded driver                                               */
 /* ------------------------------------------------------------------ */
 
+void orc_set_threads(int n)
+{
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 int orc_max_threads(void)
 {
 #ifdef _OPENMP

@@ -84,6 +84,7 @@ uint64_t orc_myers(const uint8_t *text, uint64_t n, const uint8_t *pat, uint32_t
 uint64_t orc_search_mt(int alg, const uint8_t *text, uint64_t n, const uint8_t *pat, uint32_t m,
                        uint32_t k, int threads, uint64_t *ends, uint32_t *errs, uint64_t cap);
 int orc_max_threads(void);
+void orc_set_threads(int n); /* launchers like torchrun export OMP_NUM_THREADS=1 */
 
 /* ---- journaled sequence (a14; semantics of specs/journaled_sequence_class_diagram.drawio:196,444) ---- */
 /* events sorted by ref_pos, non-overlapping: replace ref[ref_pos, ref_pos+del_len) by
