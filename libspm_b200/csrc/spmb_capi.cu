@@ -33,10 +33,44 @@ struct spmb_context {
     int sm_count = 0;
     unsigned long long *h_count = nullptr; // pinned (8 slots)
     uint32_t shard = 0, n_shards = 1;      // searches cover super-tiles [n_st*shard/n, n_st*(shard+1)/n)
+    // stores / patterns / hit lists / streams / JSTs keep a raw pointer to their context: the
+    // context outlives them (a destroy() with live children is deferred until the last one goes)
+    uint32_t children = 0;
+    bool closed = false;
+};
+
+static void context_free(spmb_context *ctx)
+{
+    cudaSetDevice(ctx->device);
+    if (ctx->own_stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
+    if (ctx->h_count) cudaFreeHost(ctx->h_count);
+    cudaGetLastError();
+    delete ctx;
+}
+
+static void ctx_adopt(spmb_context *ctx) { if (ctx) ctx->children++; }
+static void ctx_release(spmb_context *ctx)
+{
+    if (!ctx) return;
+    if (ctx->children) ctx->children--;
+    if (ctx->closed && ctx->children == 0) context_free(ctx);
+}
+
+
+// a child's counted pointer to its context (released after the child's device memory is freed)
+struct CtxRef {
+    spmb_context *p = nullptr;
+    CtxRef() = default;
+    CtxRef(const CtxRef &) = delete;
+    CtxRef &operator=(const CtxRef &) = delete;
+    CtxRef &operator=(spmb_context *c) { ctx_adopt(c); ctx_release(p); p = c; return *this; }
+    ~CtxRef() { ctx_release(p); }
+    operator spmb_context *() const { return p; }
+    spmb_context *operator->() const { return p; }
 };
 
 struct spmb_store {
-    spmb_context *ctx = nullptr;
+    CtxRef ctx;
     SpmbLayout lay{};
     uint2 *planes = nullptr;
     size_t bytes = 0;
@@ -45,7 +79,7 @@ struct spmb_store {
 };
 
 struct spmb_pattern {
-    spmb_context *ctx = nullptr;
+    CtxRef ctx;
     int alg = 0;
     uint32_t n_pat = 0, k = 0;
     std::vector<uint32_t> len, off;   // per pattern
@@ -60,7 +94,7 @@ struct spmb_pattern {
 };
 
 struct spmb_hits {
-    spmb_context *ctx = nullptr;
+    CtxRef ctx;
     spmb_hit *d_hits = nullptr;
     unsigned long long *d_count = nullptr;
     unsigned long long cap = 0;
@@ -71,7 +105,7 @@ struct spmb_hits {
 };
 
 struct spmb_stream {
-    spmb_context *ctx = nullptr;
+    CtxRef ctx;
     const spmb_pattern *pat = nullptr;
     uint64_t offset = 0;            // symbols consumed so far
     std::vector<uint8_t> tail;      // last window_size-1 symbols
@@ -97,6 +131,15 @@ static int set_err(spmb_context *ctx, int code, const char *what, cudaError_t e 
             cudaGetLastError();                                                       \
             return set_err(ctx, e__ == cudaErrorMemoryAllocation ? SPMB_ERR_OOM : SPMB_ERR_CUDA, #call, e__); \
         }                                                                             \
+    } while (0)
+
+// every entry point: select the context's device and drop any stale (non-sticky) error state so that
+// a later cudaGetLastError() reports only this call's launches
+#define ENTER(ctx)                                   \
+    do {                                             \
+        if ((ctx)->closed) return SPMB_ERR_ARG;      \
+        CU(cudaSetDevice((ctx)->device));            \
+        cudaGetLastError();                          \
     } while (0)
 
 extern "C" int spmb_version(void) { return SPMB_VERSION; }
@@ -149,11 +192,9 @@ extern "C" int spmb_context_create(int device, void *stream, spmb_context **out)
 
 extern "C" int spmb_context_destroy(spmb_context *ctx)
 {
-    if (!ctx) return SPMB_OK;
-    cudaSetDevice(ctx->device);
-    if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
-    if (ctx->h_count) cudaFreeHost(ctx->h_count);
-    delete ctx;
+    if (!ctx || ctx->closed) return SPMB_OK;
+    ctx->closed = true;
+    if (ctx->children == 0) context_free(ctx);
     return SPMB_OK;
 }
 
@@ -172,7 +213,7 @@ extern "C" int spmb_context_set_shard(spmb_context *ctx, uint32_t shard, uint32_
 extern "C" int spmb_context_sync(spmb_context *ctx)
 {
     if (!ctx) return SPMB_ERR_ARG;
-    CU(cudaSetDevice(ctx->device));
+    ENTER(ctx);
     CU(cudaStreamSynchronize(ctx->stream));
     return SPMB_OK;
 }
@@ -222,7 +263,7 @@ extern "C" int spmb_store_create_from_device(spmb_context *ctx, const uint8_t *d
                                              uint32_t row_len, spmb_store **out)
 {
     if (!ctx || !out || (!dev_ranks && n)) return SPMB_ERR_ARG;
-    CU(cudaSetDevice(ctx->device));
+    ENTER(ctx);
     spmb_store *s = nullptr;
     int rc = store_alloc(ctx, n, row_len, SPMB_MODE_PLAIN, &s);
     if (rc) return rc;
@@ -237,7 +278,7 @@ extern "C" int spmb_store_create(spmb_context *ctx, const uint8_t *host_ranks, u
                                  spmb_store **out)
 {
     if (!ctx || !out || (!host_ranks && n)) return SPMB_ERR_ARG;
-    CU(cudaSetDevice(ctx->device));
+    ENTER(ctx);
     uint8_t *d = nullptr;
     CU(cudaMallocAsync(&d, n ? n : 1, ctx->stream));
     cudaError_t e = cudaMemcpyAsync(d, host_ranks, n, cudaMemcpyHostToDevice, ctx->stream);
@@ -262,7 +303,7 @@ extern "C" int spmb_store_create_journaled(spmb_context *ctx, const spmb_store *
 {
     if (!ctx || !base || !out || (n_ev && !ev) || (pool_len && !pool)) return SPMB_ERR_ARG;
     if (base->lay.mode != SPMB_MODE_PLAIN) return set_err(ctx, SPMB_ERR_ARG, "journal base must be a plain store");
-    CU(cudaSetDevice(ctx->device));
+    ENTER(ctx);
     cudaStream_t sm = ctx->stream;
     const size_t ne = n_ev ? n_ev : 1;
     spmb_journal_event *d_ev = nullptr;
@@ -358,7 +399,7 @@ extern "C" int spmb_store_read(spmb_context *ctx, const spmb_store *s, uint64_t 
     if (s->lay.mode != SPMB_MODE_PLAIN) return set_err(ctx, SPMB_ERR_ARG, "read: plain stores only");
     if (begin + n > s->lay.n) return set_err(ctx, SPMB_ERR_ARG, "read range outside the sequence");
     if (n == 0) return SPMB_OK;
-    CU(cudaSetDevice(ctx->device));
+    ENTER(ctx);
     uint8_t *d = nullptr;
     CU(cudaMalloc(&d, n));
     unsigned blocks = (unsigned)((n + 255) / 256);
@@ -380,7 +421,7 @@ extern "C" int spmb_pattern_set_create(spmb_context *ctx, int alg, const uint8_t
 {
     if (!ctx || !out || !lengths || n_pat == 0) return SPMB_ERR_ARG;
     if (alg != SPMB_ALG_HORSPOOL && alg != SPMB_ALG_SHIFTOR && alg != SPMB_ALG_MYERS) return SPMB_ERR_ARG;
-    CU(cudaSetDevice(ctx->device));
+    ENTER(ctx);
     spmb_pattern *p = new (std::nothrow) spmb_pattern();
     if (!p) return SPMB_ERR_OOM;
     p->ctx = ctx; p->alg = alg; p->n_pat = n_pat; p->k = (alg == SPMB_ALG_MYERS) ? k : 0;
@@ -488,7 +529,7 @@ static int hits_reserve(spmb_context *ctx, spmb_hits *h, unsigned long long cap)
 extern "C" int spmb_hits_create(spmb_context *ctx, uint64_t capacity_hint, spmb_hits **out)
 {
     if (!ctx || !out) return SPMB_ERR_ARG;
-    CU(cudaSetDevice(ctx->device));
+    ENTER(ctx);
     spmb_hits *h = new (std::nothrow) spmb_hits();
     if (!h) return SPMB_ERR_OOM;
     h->ctx = ctx;
@@ -593,7 +634,7 @@ static int enqueue_search(spmb_context *ctx, const spmb_store *s, const spmb_pat
 extern "C" int spmb_search_launch(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p, spmb_hits *h)
 {
     if (!ctx || !s || !p || !h) return SPMB_ERR_ARG;
-    CU(cudaSetDevice(ctx->device));
+    ENTER(ctx);
     ctx->launches = 0;
     h->pend_store = s;
     h->pend_pat = p;
@@ -610,7 +651,7 @@ static bool hit_less(const spmb_hit &a, const spmb_hit &b)
 extern "C" int spmb_search_finish(spmb_context *ctx, spmb_hits *h)
 {
     if (!ctx || !h || !h->pend_store) return SPMB_ERR_ARG;
-    CU(cudaSetDevice(ctx->device));
+    ENTER(ctx);
     for (int attempt = 0; attempt < 4; ++attempt) {
         CU(cudaMemcpyAsync(ctx->h_count, h->d_count, sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
         CU(cudaStreamSynchronize(ctx->stream));
@@ -667,7 +708,7 @@ struct JstBucket {
 };
 
 struct spmb_jst {
-    spmb_context *ctx = nullptr;
+    CtxRef ctx;
     const spmb_store *ref = nullptr;
     JstHost H;
     spmb_journal_event *d_var = nullptr;
@@ -700,7 +741,7 @@ extern "C" int spmb_jst_create(spmb_context *ctx, const spmb_store *reference, c
         return SPMB_ERR_ARG;
     if (reference->lay.mode != SPMB_MODE_PLAIN) return set_err(ctx, SPMB_ERR_ARG, "JST reference must be a plain store");
     if (n_var >= (1ull << 32)) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "more than 2^32 variants");
-    CU(cudaSetDevice(ctx->device));
+    ENTER(ctx);
     spmb_jst *j = new (std::nothrow) spmb_jst();
     if (!j) return SPMB_ERR_OOM;
     j->ctx = ctx; j->ref = reference;
@@ -828,7 +869,7 @@ static int jst_enqueue(spmb_context *ctx, spmb_jst *j, const spmb_pattern *p, sp
 extern "C" int spmb_jst_search(spmb_context *ctx, spmb_jst *j, const spmb_pattern *p, spmb_hits *h)
 {
     if (!ctx || !j || !p || !h) return SPMB_ERR_ARG;
-    CU(cudaSetDevice(ctx->device));
+    ENTER(ctx);
     ctx->launches = 0;
     h->count = 0;
     h->host.clear();
@@ -993,7 +1034,7 @@ extern "C" int spmb_stream_restore(spmb_stream *st, const void *buf, size_t size
 extern "C" int spmb_measure_int_peak(spmb_context *ctx, double *lop3_gops, double *iadd3_gops)
 {
     if (!ctx) return SPMB_ERR_ARG;
-    CU(cudaSetDevice(ctx->device));
+    ENTER(ctx);
     uint32_t *d = nullptr;
     CU(cudaMalloc(&d, 4));
     cudaEvent_t e0, e1;
