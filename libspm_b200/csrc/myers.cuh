@@ -31,7 +31,7 @@ struct MyersPatMeta {
 };
 
 struct MyersArgs {
-    const uint4 *planes;
+    const uint2 *lanes;       // lane-chunk layout of the store (pack.cuh lanes_kernel)
     SpmbLayout lay;
     const uint32_t *eq;       // [n_pat][4][NWP]
     const MyersPatMeta *meta; // [n_pat]
@@ -41,6 +41,10 @@ struct MyersArgs {
     uint32_t warm;            // plain mode: warm-up columns, multiple of 32, >= max(m+k-1)
     uint32_t seq_id;
     uint64_t st0, st1;        // super-tile range of this launch
+    // run-time multipliers (4 and the byte size of one Eq row): ptxas cannot turn a multiply by an
+    // unknown into SHF/LEA, so the symbol pop and the table address are IMADs on the FMA pipe,
+    // which runs in the shadow of the ALU pipe the recurrence saturates (tools/ubench_pipes.cu)
+    uint32_t mul4, eq_stride;
     HitSink sink;
 };
 
@@ -133,48 +137,40 @@ __global__ void __launch_bounds__(128) myers_kernel(MyersArgs a)
         if (end_p > (int64_t)RL) end_p = RL;
     }
 
+    const uint32_t rl32 = RL >> 5;
+    const uint32_t mul4 = a.mul4, eq_stride = a.eq_stride;
+    const uint2 *__restrict__ lp = a.lanes;
+    // one uint2 = this row's next 32 symbols; fetched one whole block (32 columns) ahead
+    uint2 nxt = __ldg(lp + ((uint64_t)(cur_row >> 5) * rl32 + (cur_col >> 5)) * 32 + ((uint32_t)cur_row & 31u));
     while (p < end_p) {
-        const uint64_t g = (uint64_t)(cur_row >> 5) * RL + cur_col; // multiple of 32
-        const uint32_t bit = (uint32_t)cur_row & 31u;
-        const uint4 *src = a.planes + (g >> 10) * 512 + ((g >> 5) & 31);
+        const uint2 cur = nxt;
+        cur_col += 32;
+        if (cur_col == RL) { cur_col = 0; ++cur_row; }
+        if (p + 32 < end_p)
+            nxt = __ldg(lp + ((uint64_t)(cur_row >> 5) * rl32 + (cur_col >> 5)) * 32 + ((uint32_t)cur_row & 31u));
         uint32_t hp_acc = 0, hn_acc = 0;
-        uint4 q[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) q[i] = __ldg(src + i * 32);
+        for (int half = 0; half < 2; ++half) {
+            uint32_t w = half ? cur.y : cur.x;
 #pragma unroll
-        for (int grp = 0; grp < 4; ++grp) {
-            uint4 nq[4];
-            if (grp < 3) {
-#pragma unroll
-                for (int i = 0; i < 4; ++i) nq[i] = __ldg(src + (grp + 1) * 128 + i * 32);
-            }
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-#pragma unroll
-                for (int half = 0; half < 2; ++half) {
-                    const uint32_t hw = half ? q[i].z : q[i].x;
-                    const uint32_t lw = half ? q[i].w : q[i].y;
-                    const uint32_t c = (((hw >> bit) & 1u) << 1) | ((lw >> bit) & 1u);
-                    uint32_t eq[NW];
-                    const uint4 *e4 = reinterpret_cast<const uint4 *>(s_eq) + c * (NWP / 4);
-                    const uint4 e0 = e4[0];
-                    eq[0] = e0.x;
-                    if (NW > 1) eq[1 % NW] = e0.y;
-                    if (NW > 2) eq[2 % NW] = e0.z;
-                    if (NW > 3) eq[3 % NW] = e0.w;
-                    if (NW > 4) {
-                        const uint4 e1 = e4[NWP / 4 - 1];
-                        eq[4 % NW] = e1.x;
-                        if (NW > 5) eq[5 % NW] = e1.y;
-                        if (NW > 6) eq[6 % NW] = e1.z;
-                        if (NW > 7) eq[7 % NW] = e1.w;
-                    }
-                    myers_step<NW>(vp, vn, eq, hp_acc, hn_acc);
+            for (int j = 0; j < 16; ++j) {
+                const uint32_t c = w >> 30; // the one ALU instruction of the symbol fetch
+                w *= mul4;                  // IMAD
+                uint32_t eq[NW];
+                const uint4 *e4 = reinterpret_cast<const uint4 *>(reinterpret_cast<const char *>(s_eq) + c * eq_stride);
+                const uint4 e0 = e4[0];
+                eq[0] = e0.x;
+                if (NW > 1) eq[1 % NW] = e0.y;
+                if (NW > 2) eq[2 % NW] = e0.z;
+                if (NW > 3) eq[3 % NW] = e0.w;
+                if (NW > 4) {
+                    const uint4 e1 = e4[NWP / 4 - 1];
+                    eq[4 % NW] = e1.x;
+                    if (NW > 5) eq[5 % NW] = e1.y;
+                    if (NW > 6) eq[6 % NW] = e1.z;
+                    if (NW > 7) eq[7 % NW] = e1.w;
                 }
-            }
-            if (grp < 3) {
-#pragma unroll
-                for (int i = 0; i < 4; ++i) q[i] = nq[i];
+                myers_step<NW>(vp, vn, eq, hp_acc, hn_acc);
             }
         }
         // ---- every 32 columns: can the score have dipped to <= k anywhere in this block? ----
@@ -191,8 +187,6 @@ __global__ void __launch_bounds__(128) myers_kernel(MyersArgs a)
         }
         score += (int)__popc(hp_acc) - (int)__popc(hn_acc);
         p += 32;
-        cur_col += 32;
-        if (cur_col == RL) { cur_col = 0; ++cur_row; }
     }
 }
 

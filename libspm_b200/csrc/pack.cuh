@@ -178,6 +178,43 @@ __global__ void unpack_kernel(const uint2 *__restrict__ planes, SpmbLayout lay, 
     out[i] = (uint8_t)spmb_symbol_at(planes, lay, begin + i);
 }
 
+// planes -> "lane chunks", the layout the Myers kernels read: for the 32-column
+// group G (global columns 32G .. 32G+31) lane r of a super-tile owns ONE uint2 = the 32 symbols of
+// its row in those columns, 2-bit codes, first column in the top bits (.x = columns 0..15,
+// .y = columns 16..31).  A Myers lane then pops one symbol per column with a shift by 30 and an
+// IMAD by 4, and a warp's loads are one contiguous 256 B.  One warp transposes one group: lane j
+// loads column j's {H,L}, 64 ballots hand lane r the words of row r.
+__device__ __forceinline__ uint32_t spmb_spread16(uint32_t x)
+{
+    x &= 0xffffu;
+    x = (x | (x << 8)) & 0x00ff00ffu;
+    x = (x | (x << 4)) & 0x0f0f0f0fu;
+    x = (x | (x << 2)) & 0x33333333u;
+    x = (x | (x << 1)) & 0x55555555u;
+    return x;
+}
+
+__global__ void __launch_bounds__(256) lanes_kernel(const uint2 *__restrict__ planes, uint64_t n_groups,
+                                                    uint2 *__restrict__ lanes)
+{
+    const uint32_t lane = threadIdx.x & 31;
+    const uint64_t G = (uint64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (G >= n_groups) return; // warp-uniform
+    const uint2 c = __ldg(planes + spmb_perm(G * 32 + lane));
+    uint32_t myH = 0, myL = 0;
+#pragma unroll
+    for (int r = 0; r < 32; ++r) {
+        const uint32_t h = __ballot_sync(0xffffffffu, (c.x >> r) & 1u);
+        const uint32_t l = __ballot_sync(0xffffffffu, (c.y >> r) & 1u);
+        if (lane == r) { myH = h; myL = l; }
+    }
+    const uint32_t bh = __brev(myH), bl = __brev(myL); // column j at bit 31-j
+    uint2 o;
+    o.x = (spmb_spread16(bh >> 16) << 1) | spmb_spread16(bl >> 16);
+    o.y = (spmb_spread16(bh) << 1) | spmb_spread16(bl);
+    lanes[G * 32 + lane] = o;
+}
+
 __global__ void zero_kernel(uint4 *p, uint64_t n16)
 {
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;

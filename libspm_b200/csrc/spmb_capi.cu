@@ -74,6 +74,9 @@ struct spmb_store {
     SpmbLayout lay{};
     uint2 *planes = nullptr;
     size_t bytes = 0;
+    // lane-chunk copy of the same symbols for the Myers kernels, derived from the planes on the
+    // first Myers search of this store (same size as the planes)
+    mutable uint2 *lanes = nullptr;
     // windows mode
     uint32_t *row_len = nullptr, *row_seq = nullptr, *row_own = nullptr;
 };
@@ -382,6 +385,7 @@ extern "C" int spmb_store_destroy(spmb_store *s)
     if (!s) return SPMB_OK;
     if (s->ctx) cudaSetDevice(s->ctx->device);
     if (s->ctx) cudaFreeAsync(s->planes, s->ctx->stream); else cudaFree(s->planes);
+    if (s->lanes) { if (s->ctx) cudaFreeAsync(s->lanes, s->ctx->stream); else cudaFree(s->lanes); }
     cudaFree(s->row_len);
     cudaFree(s->row_seq);
     cudaFree(s->row_own);
@@ -391,7 +395,23 @@ extern "C" int spmb_store_destroy(spmb_store *s)
 
 extern "C" uint64_t spmb_store_length(const spmb_store *s) { return s ? s->lay.n : 0; }
 extern "C" uint32_t spmb_store_row_len(const spmb_store *s) { return s ? s->lay.row_len : 0; }
-extern "C" uint64_t spmb_store_device_bytes(const spmb_store *s) { return s ? s->bytes : 0; }
+extern "C" uint64_t spmb_store_device_bytes(const spmb_store *s) { return s ? s->bytes * (s->lanes ? 2 : 1) : 0; }
+
+// the Myers kernels read the lane-chunk layout: build it once per store, stream-ordered
+static int store_ensure_lanes(spmb_context *ctx, const spmb_store *s)
+{
+    if (s->lanes) return SPMB_OK;
+    uint2 *l = nullptr;
+    cudaError_t e = cudaMallocAsync(&l, s->bytes, ctx->stream);
+    if (e != cudaSuccess) { cudaGetLastError(); return set_err(ctx, SPMB_ERR_OOM, "cudaMallocAsync(lanes)", e); }
+    const uint64_t n_groups = s->lay.n_cols_alloc / 32;
+    lanes_kernel<<<(unsigned)((n_groups + 7) / 8), 256, 0, ctx->stream>>>(s->planes, n_groups, l);
+    ctx->launches++;
+    e = cudaGetLastError();
+    if (e != cudaSuccess) { cudaFreeAsync(l, ctx->stream); return set_err(ctx, SPMB_ERR_CUDA, "lanes_kernel launch", e); }
+    s->lanes = l;
+    return SPMB_OK;
+}
 
 extern "C" int spmb_store_read(spmb_context *ctx, const spmb_store *s, uint64_t begin, uint64_t n, uint8_t *host_out)
 {
@@ -588,8 +608,12 @@ static int enqueue_search(spmb_context *ctx, const spmb_store *s, const spmb_pat
     const uint64_t st1 = s->lay.n_st * (ctx->shard + 1) / ctx->n_shards;
     if (p->alg == SPMB_ALG_MYERS) {
         if (p->n_pat > 65535) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "more than 65535 patterns in one Myers set");
+        int rc = store_ensure_lanes(ctx, s);
+        if (rc) return rc;
         MyersArgs a;
-        a.planes = reinterpret_cast<const uint4 *>(s->planes);
+        a.lanes = s->lanes;
+        a.mul4 = 4;
+        a.eq_stride = (p->NW <= 4 ? 4 : 8) * 4;
         a.lay = s->lay;
         a.eq = p->d_eq;
         a.meta = p->d_meta;
