@@ -40,7 +40,15 @@ enum {
 enum {
     SPMB_ALG_HORSPOOL = 1, /* spm::horspool_matcher  libspm/libspm/matcher/horspool_matcher.hpp:20-44 */
     SPMB_ALG_SHIFTOR = 2,  /* spm::shiftor_matcher   libspm/libspm/matcher/shiftor_matcher.hpp:20-44  */
-    SPMB_ALG_MYERS = 3     /* spm::myers_matcher     libspm/libspm/matcher/myers_matcher.hpp:19-60     */
+    SPMB_ALG_MYERS = 3,    /* spm::myers_matcher     libspm/libspm/matcher/myers_matcher.hpp:19-60     */
+    /* SURVEY.md 8(f) "next" rows */
+    SPMB_ALG_PIGEONHOLE = 4,     /* spm::pigeonhole_matcher  libspm/libspm/matcher/pigeonhole_matcher.hpp:129-243
+                                    (create with spmb_pigeonhole_create) */
+    SPMB_ALG_MYERS_FILTERED = 5, /* the hit list of SPMB_ALG_MYERS, computed as pigeonhole seed filter +
+                                    windowed Myers verification (no reference counterpart: the reference
+                                    leaves verification to the callers of pigeonhole_matcher) */
+    SPMB_ALG_MYERS_PREFIX = 6    /* spm::restorable_myers_prefix_matcher
+                                    libspm/libspm/matcher/myers_prefix_matcher_restorable.hpp:117-160 */
 };
 
 typedef struct spmb_context spmb_context;
@@ -59,7 +67,8 @@ typedef struct spmb_hit {
     uint32_t seq_id;     /* sequence / haplotype id (0 for a plain store) */
     uint32_t pattern_id; /* index inside a pattern set (0 for a single pattern) */
     uint32_t errors;     /* 0 for the exact searchers */
-    uint32_t reserved;
+    uint32_t reserved;   /* SPMB_ALG_PIGEONHOLE: offset of the seed inside its needle
+                            (seqan2::PigeonholeSeedOnlyPosition::offset, pigeonhole_matcher.hpp:41-44); else 0 */
 } spmb_hit;
 
 /* journal event (a14; specs/journaled_sequence_class_diagram.drawio:196 record_sequence_edit):
@@ -124,9 +133,23 @@ int spmb_pattern_create(spmb_context *ctx, int alg, const uint8_t *ranks, uint32
 int spmb_pattern_set_create(spmb_context *ctx, int alg, const uint8_t *ranks,
                             const uint32_t *lengths, uint32_t n_patterns, uint32_t k,
                             spmb_pattern **out);
+/* spm::pigeonhole_matcher{needles, error_rate} (pigeonhole_matcher.hpp:157-180): q-gram seed search.
+ * q = min over needles of floor(len / (floor(error_rate*len) + 1)) (needles giving q < 3 are ignored, as
+ * SeqAn2's _patternInit does); every needle contributes the q-grams at offsets 0, q, 2q, ...; a hit is
+ * {end = begin + q, pattern_id = needle index, reserved = needle offset}, sorted by
+ * (seq_id, end, pattern_id, reserved) = haystack order like the reference's callback sequence
+ * (pigeonhole_matcher_test.cpp:30-33).  spmb_pattern_window_size() returns q (:200-202).
+ * Not reproduced: the Finder's masking of >= 1000-symbol period-1 repeats (:186-191). */
+int spmb_pigeonhole_create(spmb_context *ctx, const uint8_t *ranks, const uint32_t *lengths,
+                           uint32_t n_needles, double error_rate, spmb_pattern **out);
 int spmb_pattern_destroy(spmb_pattern *p);
+/* figures of a SPMB_ALG_PIGEONHOLE / SPMB_ALG_MYERS_FILTERED pattern: info[0] q, [1] seeds,
+ * [2] distinct q-grams, [3] log2 bitmap bits, [4] 1 if the filter is in use (0: q too short, the
+ * direct Myers kernel runs instead) */
+int spmb_pattern_filter_info(const spmb_pattern *p, uint32_t info[5]);
 /* spm::window_size(matcher): m for the exact searchers (seqan_pattern_base.hpp:97-99),
- * m + k for Myers (myers_matcher.hpp:51-53); 0 for an empty needle. */
+ * m + k for Myers (myers_matcher.hpp:51-53) and the prefix matcher
+ * (myers_prefix_matcher_restorable.hpp:151-153); q for the pigeonhole matcher; 0 for an empty needle. */
 uint32_t spmb_pattern_window_size(const spmb_pattern *p);
 uint32_t spmb_pattern_count(const spmb_pattern *p);
 
@@ -147,6 +170,13 @@ int spmb_search(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p, s
 /* the reference's call shape with a HOST haystack: upload + pack + search + hits back. */
 int spmb_search_host(spmb_context *ctx, const uint8_t *host_ranks, uint64_t n,
                      const spmb_pattern *p, spmb_hits *h);
+/* SPMB_ALG_MYERS_PREFIX with many anchors (what a seed-and-extend caller of
+ * restorable_myers_prefix_matcher does, one matcher call per seed): the needle(s) are aligned to the
+ * prefixes of the text starting at every anchors[i] (host array of text positions), scan clamped to
+ * m + k + 1 symbols; hit = {end (absolute, exclusive), seq_id = anchor index, pattern_id, errors}.
+ * spmb_search() with such a pattern is the single anchor 0 (the reference's call shape). */
+int spmb_search_anchored(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p,
+                         const uint64_t *anchors, uint64_t n_anchors, spmb_hits *h);
 /* number of kernel launches the last search enqueued (bench.py's gpu_launches). */
 uint32_t spmb_last_launch_count(const spmb_context *ctx);
 

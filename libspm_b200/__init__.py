@@ -14,12 +14,14 @@ import os
 import numpy as np
 
 __all__ = ["Context", "Store", "Pattern", "Hits", "Stream", "Jst", "SpmbError", "HIT_DTYPE", "EVENT_DTYPE",
-           "ALG_HORSPOOL", "ALG_SHIFTOR", "ALG_MYERS", "lib", "lib_path"]
+           "ALG_HORSPOOL", "ALG_SHIFTOR", "ALG_MYERS", "ALG_PIGEONHOLE", "ALG_MYERS_FILTERED",
+           "ALG_MYERS_PREFIX", "Pigeonhole", "search_anchored", "lib", "lib_path"]
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _SO = os.path.join(_HERE, "lib", "libspmb.so")
 
 ALG_HORSPOOL, ALG_SHIFTOR, ALG_MYERS = 1, 2, 3
+ALG_PIGEONHOLE, ALG_MYERS_FILTERED, ALG_MYERS_PREFIX = 4, 5, 6
 
 HIT_DTYPE = np.dtype([("end", "<u8"), ("seq_id", "<u4"), ("pattern_id", "<u4"), ("errors", "<u4"),
                       ("reserved", "<u4")])
@@ -37,7 +39,7 @@ EXPORTS = [
     "spmb_search_host", "spmb_last_launch_count", "spmb_stream_create", "spmb_stream_destroy",
     "spmb_stream_feed", "spmb_stream_capture", "spmb_stream_restore", "spmb_measure_int_peak",
     "spmb_device_info", "spmb_jst_create", "spmb_jst_destroy", "spmb_jst_search", "spmb_jst_last_stats",
-    "spmb_context_set_shard",
+    "spmb_context_set_shard", "spmb_pigeonhole_create", "spmb_pattern_filter_info", "spmb_search_anchored",
 ]
 
 
@@ -83,6 +85,9 @@ def lib():
             "spmb_store_read": (i32, [vp, vp, u64, u64, vp]),
             "spmb_pattern_create": (i32, [vp, i32, vp, u32, u32, pp]),
             "spmb_pattern_set_create": (i32, [vp, i32, vp, vp, u32, u32, pp]),
+            "spmb_pigeonhole_create": (i32, [vp, vp, vp, u32, C.c_double, pp]),
+            "spmb_pattern_filter_info": (i32, [vp, C.POINTER(u32 * 5)]),
+            "spmb_search_anchored": (i32, [vp, vp, vp, vp, u64, vp]),
             "spmb_pattern_destroy": (i32, [vp]),
             "spmb_pattern_window_size": (u32, [vp]),
             "spmb_pattern_count": (u32, [vp]),
@@ -260,6 +265,14 @@ class Pattern:
         return int(lib().spmb_pattern_window_size(self._h))
 
     @property
+    def filter_info(self):
+        """figures of the pigeonhole seed filter behind ALG_PIGEONHOLE / ALG_MYERS_FILTERED patterns."""
+        info = (C.c_uint32 * 5)()
+        lib().spmb_pattern_filter_info(self._h, C.byref(info))
+        return {"q": info[0], "seeds": info[1], "distinct_qgrams": info[2], "log2_bitmap_bits": info[3],
+                "filtered": bool(info[4])}
+
+    @property
     def count(self):
         return int(lib().spmb_pattern_count(self._h))
 
@@ -273,6 +286,23 @@ class Pattern:
             self.close()
         except Exception:
             pass
+
+
+class Pigeonhole(Pattern):
+    """spm::pigeonhole_matcher{needle(s), error_rate}: q-gram seed search (spmb_pigeonhole_create)."""
+
+    def __init__(self, ctx: Context, needles, error_rate: float = 0.0):
+        self.ctx = ctx
+        self._h = C.c_void_p()
+        if not (isinstance(needles, (list, tuple)) and len(needles) and not np.isscalar(needles[0])):
+            needles = [needles]
+        parts = [_ranks(p) for p in needles]
+        lens = np.array([p.size for p in parts], dtype=np.uint32)
+        cat = np.concatenate(parts) if parts else np.zeros(0, np.uint8)
+        ctx._check(lib().spmb_pigeonhole_create(ctx._h, cat.ctypes.data if cat.size else None, lens.ctypes.data,
+                                                len(parts), float(error_rate), C.byref(self._h)),
+                   "spmb_pigeonhole_create")
+        self.alg, self.k = ALG_PIGEONHOLE, 0
 
 
 class Hits:
@@ -309,6 +339,19 @@ def search(ctx: Context, store: Store, pattern: Pattern, hits: Hits | None = Non
     own = hits is None
     hits = hits or Hits(ctx)
     ctx._check(lib().spmb_search(ctx._h, store._h, pattern._h, hits._h), "spmb_search")
+    out = hits.array()
+    if own:
+        hits.close()
+    return out
+
+
+def search_anchored(ctx: Context, store: Store, pattern: Pattern, anchors, hits: Hits | None = None) -> np.ndarray:
+    """restorable_myers_prefix_matcher at many anchors: seq_id = anchor index, end absolute."""
+    own = hits is None
+    hits = hits or Hits(ctx)
+    a = np.ascontiguousarray(anchors, dtype=np.uint64)
+    ctx._check(lib().spmb_search_anchored(ctx._h, store._h, pattern._h, a.ctypes.data if a.size else None, a.size,
+                                          hits._h), "spmb_search_anchored")
     out = hits.array()
     if own:
         hits.close()

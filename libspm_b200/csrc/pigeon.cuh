@@ -1,0 +1,492 @@
+// pigeon.cuh -- pigeonhole q-gram seed filter + anchored verification.
+//
+// Reference anchors:
+//   spm::pigeonhole_matcher{needle(s), error_rate}   libspm/libspm/matcher/pigeonhole_matcher.hpp:129-243
+//     (SeqAn2 Pattern<Index<StringSet, IndexQGram<SimpleShape, OpenAddressing>>, Pigeonhole<SeedOnly>>:
+//      every needle is cut into q-grams at offsets 0, q, 2q, ..., the haystack is scanned once and every
+//      position whose q-gram equals one of them is reported as a seed hit {needle index, needle offset, q},
+//      pigeonhole_matcher.hpp:41-44,118-124; golden vectors pigeonhole_matcher_test.cpp:30-33)
+//   spm::restorable_myers_prefix_matcher{needle, k}  libspm/libspm/matcher/myers_prefix_matcher_restorable.hpp:47-61,117-160
+//     (SeqAn2 MyersUkkonenGlobal: the needle is aligned to PREFIXES of the haystack -- D[0][j] = j --
+//      and the scan is clamped to m + k + 1 symbols, :47-50)
+//
+// What is built on top (no reference counterpart; the reference leaves verification to its callers):
+//   SPMB_ALG_MYERS_FILTERED = the hit list of SPMB_ALG_MYERS, bit-exact, computed as
+//     filter  : every k-error occurrence of needle i contains one of its k+1 disjoint pieces of length
+//               q = floor(m_i / (k+1)) unchanged (pigeonhole), so only text positions whose q-gram is
+//               one of the (k+1)*n_pat seeds can belong to a hit;
+//     verify  : for a seed (needle i, offset o) found at text position p every occurrence through it
+//               lies inside [p-o-k, p-o+m_i+k): one Myers scan of that window from the initial state.
+//               A window score is an upper bound of the true score, and the window of the seed inside
+//               the optimal alignment reproduces it exactly, so the minimum over windows is exact
+//               (DESIGN.md 4b); duplicates across seeds are removed after the sort.
+//
+// Device side: ONE pass over the lane-chunk layout (pack.cuh lanes_kernel: one uint2 = 32 consecutive
+// symbols of a lane's row).  Per text position: the q-gram (<= 32 symbols = 64 bits, top-aligned) falls out
+// of two funnel shifts, a multiplicative hash (IMADs -- FMA pipe) indexes a bitmap held in shared
+// memory (<= 128 KB per CTA), the pass bits of 32 positions are collected in one register and only
+// survivors (a few %) probe the exact open-addressing table in L2.
+#pragma once
+#include <algorithm>
+#include <vector>
+
+#include "layout.cuh"
+#include "hits.cuh"
+#include "myers.cuh"
+
+// ------------------------------------------------------------------------------------------
+// shared host/device definitions
+// ------------------------------------------------------------------------------------------
+// q-gram key: symbol j of the q-gram at bits [63-2j, 62-2j] of (hi:lo), zero below (kq <= 32 symbols)
+SPMB_HD uint32_t pg_h1(uint32_t hi, uint32_t lo) { return hi * 0x9E3779B1u + lo * 0x85EBCA77u; }
+SPMB_HD uint32_t pg_h2(uint32_t hi, uint32_t lo)
+{
+    uint32_t h = (hi * 0xC2B2AE3Du) ^ (lo * 0x27D4EB2Fu);
+    h ^= h >> 15;
+    return h * 0x2C1B3C6Du;
+}
+
+static const uint32_t PG_EMPTY = 0xffffffffu;
+
+struct PigeonDev {
+    const uint32_t *bitmap;            // 2^B bits; bit for index x is bit 31-(x&31) of word x>>5
+    const unsigned long long *tab_key; // 2^T slots, linear probing
+    const uint32_t *tab_val;           // index of the unique q-gram, PG_EMPTY = free slot
+    const uint32_t *ufirst;            // [n_unique+1] -> range of seeds carrying that q-gram
+    const uint32_t *seed_pat;          // needle index of each seed
+    const uint32_t *seed_off;          // offset of the seed inside its needle
+    uint32_t q, kq, B, T;
+    uint32_t himask, lomask;           // the top 2*kq bits of (hi:lo)
+};
+
+struct PigeonCand {
+    uint64_t pos; // plain: text position of the seed's first symbol; windows: row*row_len + column
+    uint32_t u;   // unique q-gram index
+    uint32_t pad;
+};
+
+// ------------------------------------------------------------------------------------------
+// host: seed table
+// ------------------------------------------------------------------------------------------
+struct PigeonHost {
+    uint32_t q = 0, kq = 0, B = 0, T = 0;
+    std::vector<uint32_t> bitmap;
+    std::vector<unsigned long long> tab_key;
+    std::vector<uint32_t> tab_val, ufirst, seed_pat, seed_off;
+    uint64_t n_unique = 0;
+
+    static unsigned long long key_of(const uint8_t *s, uint32_t kq)
+    {
+        unsigned long long k = 0;
+        for (uint32_t j = 0; j < kq; ++j) k |= (unsigned long long)(s[j] & 3u) << (62 - 2 * j);
+        return k;
+    }
+
+    // seeds = (needle, offset) pairs; ranks/off/len describe the concatenated needles
+    void build(const std::vector<uint8_t> &ranks, const std::vector<uint32_t> &off,
+               const std::vector<std::pair<uint32_t, uint32_t>> &seeds, uint32_t q_)
+    {
+        q = q_;
+        kq = q < 32 ? q : 32;
+        struct S { unsigned long long key; uint32_t pat, o; };
+        std::vector<S> v;
+        v.reserve(seeds.size());
+        for (auto &s : seeds) v.push_back({key_of(ranks.data() + off[s.first] + s.second, kq), s.first, s.second});
+        std::sort(v.begin(), v.end(), [](const S &a, const S &b) {
+            if (a.key != b.key) return a.key < b.key;
+            if (a.pat != b.pat) return a.pat < b.pat;
+            return a.o < b.o;
+        });
+        seed_pat.clear(); seed_off.clear(); ufirst.clear();
+        std::vector<unsigned long long> ukeys;
+        for (size_t i = 0; i < v.size(); ++i) {
+            if (i == 0 || v[i].key != v[i - 1].key) { ufirst.push_back((uint32_t)i); ukeys.push_back(v[i].key); }
+            seed_pat.push_back(v[i].pat);
+            seed_off.push_back(v[i].o);
+        }
+        ufirst.push_back((uint32_t)v.size());
+        n_unique = ukeys.size();
+        // bitmap: ~32 bits per unique q-gram, 2^15 .. 2^20 bits (4 KB .. 128 KB of shared memory)
+        B = 15;
+        while (B < 20 && (1ull << B) < n_unique * 32) ++B;
+        // a q-gram of kq symbols has only 4^kq values: no point in more bits than that (x4)
+        bitmap.assign((size_t)1 << (B - 5), 0);
+        T = 4;
+        while ((1ull << T) < n_unique * 2 + 1) ++T;
+        tab_key.assign((size_t)1 << T, 0);
+        tab_val.assign((size_t)1 << T, PG_EMPTY);
+        const uint32_t tmask = (1u << T) - 1;
+        for (size_t u = 0; u < ukeys.size(); ++u) {
+            const uint32_t hi = (uint32_t)(ukeys[u] >> 32), lo = (uint32_t)ukeys[u];
+            const uint32_t x = pg_h1(hi, lo) >> (32 - B);
+            bitmap[x >> 5] |= 0x80000000u >> (x & 31);
+            uint32_t slot = pg_h2(hi, lo) >> (32 - T);
+            while (tab_val[slot] != PG_EMPTY) slot = (slot + 1) & tmask;
+            tab_key[slot] = ukeys[u];
+            tab_val[slot] = (uint32_t)u;
+        }
+    }
+
+    uint32_t himask() const { return kq >= 16 ? 0xffffffffu : (kq == 0 ? 0u : ~0u << (32 - 2 * kq)); }
+    uint32_t lomask() const { return kq <= 16 ? 0u : (kq >= 32 ? 0xffffffffu : ~0u << (64 - 2 * kq)); }
+};
+
+// ------------------------------------------------------------------------------------------
+// device: text access through the lane-chunk layout
+// ------------------------------------------------------------------------------------------
+// the chunk holding (row R, columns 32*c .. 32*c+31)
+__device__ __forceinline__ uint2 pg_chunk(const uint2 *__restrict__ lanes, uint32_t rl32, uint64_t R, uint32_t c)
+{
+    return __ldg(lanes + ((R >> 5) * rl32 + c) * 32 + ((uint32_t)R & 31u));
+}
+
+// symbol at (row R, column col) -- a sequential reader keeps the chunk of its current 32 columns
+struct PgReader {
+    const uint2 *__restrict__ lanes;
+    uint32_t rl32;
+    uint64_t R = ~0ull;
+    uint32_t c = ~0u;
+    uint2 w = make_uint2(0, 0);
+    __device__ __forceinline__ uint32_t at(uint64_t row, uint32_t col)
+    {
+        const uint32_t cc = col >> 5;
+        if (row != R || cc != c) { R = row; c = cc; w = pg_chunk(lanes, rl32, row, cc); }
+        const uint32_t j = col & 31u;
+        const uint32_t word = j < 16 ? w.x : w.y;
+        return (word >> (30 - 2 * (j & 15u))) & 3u;
+    }
+};
+
+// ------------------------------------------------------------------------------------------
+// filter kernel
+// ------------------------------------------------------------------------------------------
+struct PigeonFilterArgs {
+    const uint2 *lanes;
+    SpmbLayout lay;
+    PigeonDev pg;
+    const uint32_t *row_len; // windows mode
+    uint64_t st0, st1;       // super-tiles scanned by this launch
+    PigeonCand *cand;
+    unsigned long long *cand_count;
+    unsigned long long cand_cap;
+};
+
+// (hi:lo) = the 32 symbols starting at symbol j of the 64-symbol window (cur, nxt)
+__device__ __forceinline__ void pg_window(const uint2 cur, const uint2 nxt, uint32_t j, uint32_t &hi, uint32_t &lo)
+{
+    const uint32_t a = j < 16 ? cur.x : cur.y;
+    const uint32_t b = j < 16 ? cur.y : nxt.x;
+    const uint32_t c = j < 16 ? nxt.x : nxt.y;
+    const uint32_t s = 2 * (j & 15u);
+    hi = __funnelshift_l(b, a, s);
+    lo = __funnelshift_l(c, b, s);
+}
+
+// WIDE: kq > 16 (the key has a low word).  One warp = one unit of 32 rows x 32 chunks.
+template <int MODE, bool WIDE>
+__global__ void __launch_bounds__(1024, 1) pigeon_filter_kernel(PigeonFilterArgs a)
+{
+    extern __shared__ uint32_t s_bits[];
+    const uint32_t n_words = 1u << (a.pg.B - 5);
+    for (uint32_t i = threadIdx.x; i < n_words; i += blockDim.x) s_bits[i] = a.pg.bitmap[i];
+    __syncthreads();
+
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t RL = a.lay.row_len, rl32 = RL >> 5;
+    const uint32_t segs = (rl32 + 31) >> 5;
+    const uint64_t n_units = (a.st1 - a.st0) * segs;
+    const uint32_t shift = 32 - a.pg.B;
+    const uint32_t himask = a.pg.himask, lomask = a.pg.lomask;
+    const uint2 *__restrict__ lp = a.lanes;
+
+    for (uint64_t unit = (uint64_t)blockIdx.x * 32 + warp; unit < n_units; unit += (uint64_t)gridDim.x * 32) {
+        const uint64_t st = a.st0 + unit / segs;
+        const uint32_t c0 = (uint32_t)(unit % segs) * 32;
+        const uint32_t c1 = min(c0 + 32, rl32);
+        const uint64_t R = st * 32 + lane;
+        uint32_t rlen = RL; // valid symbols of this row
+        if (MODE == SPMB_MODE_PLAIN) {
+            const uint64_t r0 = R * RL;
+            if (r0 >= a.lay.n) rlen = 0;
+            // a row of the plain text continues in the next one: only the text end limits a q-gram
+        } else {
+            rlen = (R * RL < a.lay.n) ? a.row_len[R] : 0;
+        }
+        const uint2 *rowp = lp + (st * rl32) * 32 + lane;
+        uint2 cur = __ldg(rowp + (uint64_t)c0 * 32);
+        for (uint32_t c = c0; c < c1; ++c) {
+            uint2 nxt;
+            if (c + 1 < rl32) nxt = __ldg(rowp + (uint64_t)(c + 1) * 32);
+            else if (MODE == SPMB_MODE_PLAIN)
+                nxt = (lane < 31) ? __ldg(lp + (st * rl32) * 32 + lane + 1) : __ldg(lp + ((st + 1) * rl32) * 32);
+            else nxt = make_uint2(0, 0);
+            uint32_t acc = 0;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                uint32_t hi, lo;
+                pg_window(cur, nxt, j, hi, lo);
+                uint32_t h;
+                if (WIDE) h = pg_h1(hi, lo & lomask);
+                else h = (hi & himask) * 0x9E3779B1u;
+                const uint32_t x = h >> shift;
+                const uint32_t word = s_bits[x >> 5];
+                acc = __funnelshift_l(word << (x & 31u), acc, 1); // position j ends at bit 31-j
+            }
+            // ---- survivors of the bitmap: exact table in L2 ----
+            while (acc) {
+                const uint32_t j = __clz(acc);
+                acc &= ~(0x80000000u >> j);
+                const uint32_t col = c * 32 + j;
+                bool ok;
+                if (MODE == SPMB_MODE_PLAIN) ok = rlen && (R * RL + col + a.pg.q <= a.lay.n);
+                else ok = (col + a.pg.q <= rlen);
+                if (!ok) continue;
+                uint32_t hi, lo;
+                pg_window(cur, nxt, j, hi, lo);
+                hi &= himask; lo &= lomask;
+                const unsigned long long key = ((unsigned long long)hi << 32) | lo;
+                const uint32_t tmask = (1u << a.pg.T) - 1;
+                uint32_t slot = pg_h2(hi, lo) >> (32 - a.pg.T);
+                for (;;) {
+                    const uint32_t v = __ldg(a.pg.tab_val + slot);
+                    if (v == PG_EMPTY) break;
+                    if (__ldg(a.pg.tab_key + slot) == key) {
+                        const unsigned long long idx = atomicAdd(a.cand_count, 1ull);
+                        if (idx < a.cand_cap) {
+                            PigeonCand cd;
+                            cd.pos = R * RL + col; cd.u = v; cd.pad = 0;
+                            a.cand[idx] = cd;
+                        }
+                        break;
+                    }
+                    slot = (slot + 1) & tmask;
+                }
+            }
+            cur = nxt;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// candidates -> hits
+// ------------------------------------------------------------------------------------------
+struct PigeonVerifyArgs {
+    const uint2 *lanes;
+    SpmbLayout lay;
+    PigeonDev pg;
+    const PigeonCand *cand;
+    unsigned long long *counters; // [0] hits, [1] candidates of this launch, [2] max candidates of any launch
+    unsigned long long cand_cap;
+    const uint8_t *pat_ranks;     // concatenated needles
+    const uint32_t *pat_off;      // [n_pat]
+    const uint32_t *eq;           // [n_pat][4][NWP]
+    const MyersPatMeta *meta;     // [n_pat]
+    const uint32_t *row_len, *row_seq, *row_own; // windows mode
+    uint32_t seq_id;
+    uint64_t own_lo, own_hi;      // plain: owned range of (last symbol index of a hit | seed begin)
+    HitSink sink;
+};
+
+__device__ __forceinline__ void pg_emit(const HitSink &sink, uint64_t end, uint32_t seq, uint32_t pid, uint32_t err, uint32_t aux)
+{
+    unsigned long long idx = atomicAdd(sink.count, 1ull);
+    if (idx < sink.cap) {
+        spmb_hit h;
+        h.end = end; h.seq_id = seq; h.pattern_id = pid; h.errors = err; h.reserved = aux;
+        sink.hits[idx] = h;
+    }
+}
+
+// symbol at offset d (>= 0) from (row R, column col); a plain text runs on into the next rows
+template <int MODE>
+__device__ __forceinline__ uint32_t pg_text(PgReader &rd, uint32_t RL, uint64_t R, uint64_t col)
+{
+    if (MODE == SPMB_MODE_PLAIN) {
+        while (col >= RL) { col -= RL; ++R; }
+    }
+    return rd.at(R, (uint32_t)col);
+}
+
+// SPMB_ALG_PIGEONHOLE: every (candidate, seed) pair is a seed hit {end = begin + q, needle, offset}
+// (pigeonhole_matcher.hpp:118-124); seeds longer than the 32-symbol key are compared in full.
+template <int MODE>
+__global__ void __launch_bounds__(128) pigeon_seed_kernel(PigeonVerifyArgs a)
+{
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicMax(a.counters + 2, a.counters[1]);
+    const unsigned long long n_cand = min(a.counters[1], a.cand_cap);
+    const uint32_t RL = a.lay.row_len;
+    PgReader rd{a.lanes, RL >> 5};
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_cand;
+         i += (unsigned long long)gridDim.x * blockDim.x) {
+        const PigeonCand cd = a.cand[i];
+        const uint64_t R = spmb_div_rl(a.lay, cd.pos);
+        const uint32_t col = (uint32_t)(cd.pos - R * RL);
+        uint64_t end;
+        uint32_t seq = a.seq_id;
+        if (MODE == SPMB_MODE_PLAIN) {
+            end = cd.pos + a.pg.q;
+            if (cd.pos < a.own_lo || cd.pos >= a.own_hi) continue;
+        } else {
+            end = (uint64_t)col + a.pg.q;
+            if (a.row_own && end < a.row_own[R]) continue;
+            if (a.row_seq) seq = a.row_seq[R];
+        }
+        for (uint32_t s = a.pg.ufirst[cd.u]; s < a.pg.ufirst[cd.u + 1]; ++s) {
+            const uint32_t pid = a.pg.seed_pat[s], o = a.pg.seed_off[s];
+            bool same = true;
+            const uint8_t *pr = a.pat_ranks + a.pat_off[pid] + o;
+            for (uint32_t j = a.pg.kq; j < a.pg.q && same; ++j)
+                same = (pg_text<MODE>(rd, RL, R, (uint64_t)col + j) == pr[j]);
+            if (same) pg_emit(a.sink, end, seq, pid, 0, o);
+        }
+    }
+}
+
+// one Myers column over NW words; hp/hn (unshifted) are handed back for the score row.
+// GLOBAL: D[0][j] = j (MyersUkkonenGlobal, the anchored prefix matcher) -- a +1 enters at row 0.
+template <int NW, bool GLOBAL>
+__device__ __forceinline__ void pg_myers_col(uint32_t (&vp)[NW], uint32_t (&vn)[NW], const uint32_t (&eq)[NW],
+                                             uint32_t (&hp)[NW], uint32_t (&hn)[NW])
+{
+    uint32_t x[NW], t[NW], s[NW];
+#pragma unroll
+    for (int i = 0; i < NW; ++i) {
+        x[i] = eq[i] | vn[i];
+        t[i] = x[i] & vp[i];
+    }
+    spmb_add_chain<NW>(s, t, vp);
+    uint32_t hp_lo = GLOBAL ? 0x80000000u : 0u, hn_lo = 0;
+#pragma unroll
+    for (int i = 0; i < NW; ++i) {
+        const uint32_t d0 = (s[i] ^ vp[i]) | x[i];
+        hn[i] = vp[i] & d0;
+        hp[i] = vn[i] | ~(vp[i] | d0);
+        const uint32_t hps = __funnelshift_l(hp_lo, hp[i], 1);
+        const uint32_t hns = __funnelshift_l(hn_lo, hn[i], 1);
+        hp_lo = hp[i];
+        hn_lo = hn[i];
+        vn[i] = hps & d0;
+        vp[i] = hns | ~(hps | d0);
+    }
+}
+
+template <int NW>
+__device__ __forceinline__ int pg_score_delta(const uint32_t (&hp)[NW], const uint32_t (&hn)[NW], uint32_t m)
+{
+    const uint32_t wi = (m - 1) >> 5, bi = (m - 1) & 31u;
+    int d = 0;
+#pragma unroll
+    for (int i = 0; i < NW; ++i)
+        if ((uint32_t)i == wi) d = (int)((hp[i] >> bi) & 1u) - (int)((hn[i] >> bi) & 1u);
+    return d;
+}
+
+template <int NW>
+__device__ __forceinline__ void pg_load_eq(const uint32_t *__restrict__ eqp, uint32_t c, uint32_t (&eq)[NW])
+{
+    constexpr int NWP = (NW <= 4) ? 4 : 8;
+#pragma unroll
+    for (int i = 0; i < NW; ++i) eq[i] = __ldg(eqp + c * NWP + i);
+}
+
+// SPMB_ALG_MYERS_FILTERED: Myers over the window [p-o-k, p-o+m+k) of every (candidate, seed) pair.
+template <int NW, int MODE>
+__global__ void __launch_bounds__(128) pigeon_verify_kernel(PigeonVerifyArgs a)
+{
+    constexpr int NWP = (NW <= 4) ? 4 : 8;
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicMax(a.counters + 2, a.counters[1]);
+    const unsigned long long n_cand = min(a.counters[1], a.cand_cap);
+    const uint32_t RL = a.lay.row_len;
+    PgReader rd{a.lanes, RL >> 5};
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_cand;
+         i += (unsigned long long)gridDim.x * blockDim.x) {
+        const PigeonCand cd = a.cand[i];
+        const uint64_t R = spmb_div_rl(a.lay, cd.pos);
+        const uint32_t col = (uint32_t)(cd.pos - R * RL);
+        // coordinates: plain = absolute text positions, windows = columns of row R
+        const int64_t p = (MODE == SPMB_MODE_PLAIN) ? (int64_t)cd.pos : (int64_t)col;
+        const int64_t text_end = (MODE == SPMB_MODE_PLAIN) ? (int64_t)a.lay.n : (int64_t)a.row_len[R];
+        int64_t own_lo, own_hi; // of the last symbol index of a hit
+        uint32_t seq = a.seq_id;
+        if (MODE == SPMB_MODE_PLAIN) { own_lo = (int64_t)a.own_lo; own_hi = (int64_t)a.own_hi; }
+        else {
+            own_lo = a.row_own ? (int64_t)a.row_own[R] - 1 : 0;
+            own_hi = text_end;
+            if (a.row_seq) seq = a.row_seq[R];
+        }
+        for (uint32_t s = a.pg.ufirst[cd.u]; s < a.pg.ufirst[cd.u + 1]; ++s) {
+            const uint32_t pid = a.pg.seed_pat[s], o = a.pg.seed_off[s];
+            const MyersPatMeta pm = a.meta[pid];
+            const int k = (int)pm.k;
+            int64_t ws = p - (int64_t)o - k, we = p - (int64_t)o + (int64_t)pm.m + k;
+            if (ws < 0) ws = 0;
+            if (we > text_end) we = text_end;
+            if (we <= own_lo || ws >= own_hi) continue;
+            const uint32_t *eqp = a.eq + (size_t)pid * 4 * NWP;
+            uint32_t vp[NW], vn[NW];
+#pragma unroll
+            for (int w = 0; w < NW; ++w) { vp[w] = 0xffffffffu; vn[w] = 0; }
+            int score = (int)pm.m;
+            for (int64_t t = ws; t < we; ++t) {
+                uint32_t c;
+                if (MODE == SPMB_MODE_PLAIN) {
+                    const uint64_t Rt = spmb_div_rl(a.lay, (uint64_t)t);
+                    c = rd.at(Rt, (uint32_t)((uint64_t)t - Rt * RL));
+                } else c = rd.at(R, (uint32_t)t);
+                uint32_t eq[NW], hp[NW], hn[NW];
+                pg_load_eq<NW>(eqp, c, eq);
+                pg_myers_col<NW, false>(vp, vn, eq, hp, hn);
+                score += pg_score_delta<NW>(hp, hn, pm.m);
+                if (score <= k && t >= own_lo && t < own_hi) pg_emit(a.sink, (uint64_t)(t + 1), seq, pid, (uint32_t)score, 0);
+            }
+        }
+    }
+}
+
+// SPMB_ALG_MYERS_PREFIX (restorable_myers_prefix_matcher): the needle against the prefixes of the text
+// that starts at each anchor, scan clamped to m + k + 1 symbols (myers_prefix_matcher_restorable.hpp:47-50).
+struct PrefixArgs {
+    const uint2 *lanes;
+    SpmbLayout lay;
+    const uint64_t *anchors; // text positions; null = the single anchor 0
+    uint64_t n_anchors;
+    const uint32_t *eq;
+    const MyersPatMeta *meta;
+    uint32_t n_pat;
+    uint32_t seq_id;
+    HitSink sink;
+};
+
+template <int NW>
+__global__ void __launch_bounds__(128) prefix_kernel(PrefixArgs a)
+{
+    constexpr int NWP = (NW <= 4) ? 4 : 8;
+    const uint32_t RL = a.lay.row_len;
+    PgReader rd{a.lanes, RL >> 5};
+    const unsigned long long n_task = (unsigned long long)a.n_anchors * a.n_pat;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_task;
+         i += (unsigned long long)gridDim.x * blockDim.x) {
+        const uint64_t ai = i / a.n_pat;
+        const uint32_t pid = (uint32_t)(i % a.n_pat);
+        const uint64_t p0 = a.anchors ? a.anchors[ai] : 0;
+        const MyersPatMeta pm = a.meta[pid];
+        if (pm.m == 0 || p0 >= a.lay.n) continue;
+        const int k = (int)pm.k;
+        uint64_t we = p0 + pm.m + pm.k + 1;
+        if (we > a.lay.n) we = a.lay.n;
+        const uint32_t *eqp = a.eq + (size_t)pid * 4 * NWP;
+        uint32_t vp[NW], vn[NW];
+#pragma unroll
+        for (int w = 0; w < NW; ++w) { vp[w] = 0xffffffffu; vn[w] = 0; }
+        int score = (int)pm.m;
+        for (uint64_t t = p0; t < we; ++t) {
+            const uint64_t Rt = spmb_div_rl(a.lay, t);
+            const uint32_t c = rd.at(Rt, (uint32_t)(t - Rt * RL));
+            uint32_t eq[NW], hp[NW], hn[NW];
+            pg_load_eq<NW>(eqp, c, eq);
+            pg_myers_col<NW, true>(vp, vn, eq, hp, hn);
+            score += pg_score_delta<NW>(hp, hn, pm.m);
+            if (score <= k) pg_emit(a.sink, t + 1, a.anchors ? (uint32_t)ai : a.seq_id, pid, (uint32_t)score, 0);
+        }
+    }
+}

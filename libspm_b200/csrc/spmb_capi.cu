@@ -20,6 +20,7 @@
 #include "layout.cuh"
 #include "myers.cuh"
 #include "pack.cuh"
+#include "pigeon.cuh"
 
 // ------------------------------------------------------------------------------------------
 // objects
@@ -94,13 +95,21 @@ struct spmb_pattern {
     uint8_t *d_ranks = nullptr;
     uint32_t *d_eq = nullptr;
     MyersPatMeta *d_meta = nullptr;
+    // pigeonhole seed filter (SPMB_ALG_PIGEONHOLE, SPMB_ALG_MYERS_FILTERED)
+    PigeonHost pg;
+    bool filtered = false;            // the filter is in use (q long enough)
+    uint32_t *d_off = nullptr;        // needle offsets into d_ranks
+    uint32_t *d_pg_bitmap = nullptr, *d_pg_val = nullptr, *d_pg_ufirst = nullptr, *d_pg_pat = nullptr, *d_pg_soff = nullptr;
+    unsigned long long *d_pg_key = nullptr;
 };
 
 struct spmb_hits {
     CtxRef ctx;
     spmb_hit *d_hits = nullptr;
-    unsigned long long *d_count = nullptr;
+    unsigned long long *d_count = nullptr; // [0] hits, [1] filter candidates of the current launch, [2] their max
     unsigned long long cap = 0;
+    PigeonCand *d_cand = nullptr;          // candidate buffer of the seed filter (grown on demand)
+    unsigned long long cand_cap = 0;
     std::vector<spmb_hit> host;
     uint64_t count = 0;
     const spmb_store *pend_store = nullptr;
@@ -436,15 +445,73 @@ extern "C" int spmb_store_read(spmb_context *ctx, const spmb_store *s, uint64_t 
 // ------------------------------------------------------------------------------------------
 // patterns
 // ------------------------------------------------------------------------------------------
-extern "C" int spmb_pattern_set_create(spmb_context *ctx, int alg, const uint8_t *ranks, const uint32_t *lengths,
-                                       uint32_t n_pat, uint32_t k, spmb_pattern **out)
+// Eq tables + meta of a Myers needle set (direct kernel, windowed verification, prefix matcher)
+static cudaError_t pattern_upload_myers(spmb_context *ctx, spmb_pattern *p, uint32_t k)
+{
+    const uint32_t n_pat = p->n_pat;
+    const int NWP = p->NW <= 4 ? 4 : 8;
+    std::vector<uint32_t> eq((size_t)n_pat * 4 * NWP, 0);
+    std::vector<MyersPatMeta> meta(n_pat);
+    for (uint32_t i = 0; i < n_pat; ++i) {
+        const uint32_t m = p->len[i];
+        const uint8_t *pr = p->ranks.data() + p->off[i];
+        uint32_t *e4 = eq.data() + (size_t)i * 4 * NWP;
+        for (uint32_t j = 0; j < (uint32_t)p->NW * 32; ++j) {
+            for (int c = 0; c < 4; ++c) {
+                bool match = (j < m) ? (pr[j] == c) : true; // wildcard padding rows
+                if (match) e4[c * NWP + j / 32] |= 1u << (j % 32);
+            }
+        }
+        meta[i].m = m; meta[i].k = k; meta[i].pad = (uint32_t)p->NW * 32 - m; meta[i].pattern_id = i;
+    }
+    p->warm = (p->max_m + k - 1 + 31) / 32 * 32;
+    cudaError_t e = cudaMalloc(&p->d_eq, eq.size() * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&p->d_meta, meta.size() * sizeof(MyersPatMeta));
+    if (e == cudaSuccess) e = cudaMemcpyAsync(p->d_eq, eq.data(), eq.size() * 4, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(p->d_meta, meta.data(), meta.size() * sizeof(MyersPatMeta), cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream); // host vectors go out of scope
+    return e;
+}
+
+template <class T>
+static cudaError_t upload_vec(spmb_context *ctx, T **d, const std::vector<T> &v)
+{
+    cudaError_t e = cudaMalloc(d, (v.size() ? v.size() : 1) * sizeof(T));
+    if (e == cudaSuccess && !v.empty()) e = cudaMemcpyAsync(*d, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, ctx->stream);
+    return e;
+}
+
+// seed table of the pigeonhole filter -> device
+static cudaError_t pattern_upload_pigeon(spmb_context *ctx, spmb_pattern *p,
+                                         const std::vector<std::pair<uint32_t, uint32_t>> &seeds, uint32_t q)
+{
+    p->pg.build(p->ranks, p->off, seeds, q);
+    cudaError_t e = upload_vec(ctx, &p->d_pg_bitmap, p->pg.bitmap);
+    if (e == cudaSuccess) e = upload_vec(ctx, &p->d_pg_key, p->pg.tab_key);
+    if (e == cudaSuccess) e = upload_vec(ctx, &p->d_pg_val, p->pg.tab_val);
+    if (e == cudaSuccess) e = upload_vec(ctx, &p->d_pg_ufirst, p->pg.ufirst);
+    if (e == cudaSuccess) e = upload_vec(ctx, &p->d_pg_pat, p->pg.seed_pat);
+    if (e == cudaSuccess) e = upload_vec(ctx, &p->d_pg_soff, p->pg.seed_off);
+    if (e == cudaSuccess) e = upload_vec(ctx, &p->d_off, p->off);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    return e;
+}
+
+// shortest q for which the seed filter replaces the direct Myers kernel: 4^q must dwarf the number of
+// seeds (a 12-mer has 1.7e7 values)
+static const uint32_t SPMB_FILTER_MIN_Q = 12;
+
+static int pattern_build(spmb_context *ctx, int alg, const uint8_t *ranks, const uint32_t *lengths, uint32_t n_pat,
+                         uint32_t k, double error_rate, spmb_pattern **out)
 {
     if (!ctx || !out || !lengths || n_pat == 0) return SPMB_ERR_ARG;
-    if (alg != SPMB_ALG_HORSPOOL && alg != SPMB_ALG_SHIFTOR && alg != SPMB_ALG_MYERS) return SPMB_ERR_ARG;
+    if (alg < SPMB_ALG_HORSPOOL || alg > SPMB_ALG_MYERS_PREFIX) return SPMB_ERR_ARG;
+    if (alg == SPMB_ALG_PIGEONHOLE && !(error_rate >= 0.0 && error_rate < 1.0)) return SPMB_ERR_ARG;
     ENTER(ctx);
+    const bool myers_like = (alg == SPMB_ALG_MYERS || alg == SPMB_ALG_MYERS_FILTERED || alg == SPMB_ALG_MYERS_PREFIX);
     spmb_pattern *p = new (std::nothrow) spmb_pattern();
     if (!p) return SPMB_ERR_OOM;
-    p->ctx = ctx; p->alg = alg; p->n_pat = n_pat; p->k = (alg == SPMB_ALG_MYERS) ? k : 0;
+    p->ctx = ctx; p->alg = alg; p->n_pat = n_pat; p->k = myers_like ? k : 0;
     uint64_t total = 0;
     p->max_m = 0; p->min_m = 0xffffffffu;
     for (uint32_t i = 0; i < n_pat; ++i) {
@@ -462,37 +529,55 @@ extern "C" int spmb_pattern_set_create(spmb_context *ctx, int alg, const uint8_t
     cudaError_t e = cudaMalloc(&p->d_ranks, total ? total : 1);
     if (e == cudaSuccess && total) e = cudaMemcpyAsync(p->d_ranks, p->ranks.data(), total, cudaMemcpyHostToDevice, ctx->stream);
 
-    if (alg == SPMB_ALG_MYERS) {
+    if (myers_like) {
         // an empty needle matches nothing (window_size 0): keep NW = 0 and never launch
         if (p->max_m > 256) { spmb_pattern_destroy(p); return set_err(ctx, SPMB_ERR_UNSUPPORTED, "Myers needle longer than 256 symbols"); }
         p->NW = (int)((p->max_m + 31) / 32);
+        // the filtered path verifies needle by needle and reads the score at row m-1, so a set may mix
+        // word counts there; the direct kernel wants one word count per set
+        bool mixed = false;
         for (uint32_t i = 0; i < n_pat; ++i)
-            if (p->len[i] && (int)((p->len[i] + 31) / 32) != p->NW) {
-                spmb_pattern_destroy(p);
-                return set_err(ctx, SPMB_ERR_UNSUPPORTED, "all needles of a Myers set must share ceil(m/32)");
+            if (p->len[i] && (int)((p->len[i] + 31) / 32) != p->NW) mixed = true;
+        std::vector<std::pair<uint32_t, uint32_t>> seeds;
+        uint32_t q = 0;
+        if (alg == SPMB_ALG_MYERS_FILTERED && p->min_m > 0) {
+            q = p->min_m / (k + 1);
+            if (q >= SPMB_FILTER_MIN_Q) {
+                p->filtered = true;
+                for (uint32_t i = 0; i < n_pat; ++i)
+                    for (uint32_t piece = 0; piece <= k; ++piece) seeds.push_back({i, piece * q});
             }
+        }
+        if (mixed && !(p->filtered || alg == SPMB_ALG_MYERS_PREFIX)) {
+            spmb_pattern_destroy(p);
+            return set_err(ctx, SPMB_ERR_UNSUPPORTED, "all needles of a Myers set must share ceil(m/32)");
+        }
         if (p->NW > 0) {
-            const int NWP = p->NW <= 4 ? 4 : 8;
-            std::vector<uint32_t> eq((size_t)n_pat * 4 * NWP, 0);
-            std::vector<MyersPatMeta> meta(n_pat);
-            for (uint32_t i = 0; i < n_pat; ++i) {
-                const uint32_t m = p->len[i];
-                const uint8_t *pr = p->ranks.data() + p->off[i];
-                uint32_t *e4 = eq.data() + (size_t)i * 4 * NWP;
-                for (uint32_t j = 0; j < (uint32_t)p->NW * 32; ++j) {
-                    for (int c = 0; c < 4; ++c) {
-                        bool match = (j < m) ? (pr[j] == c) : true; // wildcard padding rows
-                        if (match) e4[c * NWP + j / 32] |= 1u << (j % 32);
-                    }
-                }
-                meta[i].m = m; meta[i].k = k; meta[i].pad = (uint32_t)p->NW * 32 - m; meta[i].pattern_id = i;
-            }
-            p->warm = (p->max_m + k - 1 + 31) / 32 * 32;
-            if (e == cudaSuccess) e = cudaMalloc(&p->d_eq, eq.size() * 4);
-            if (e == cudaSuccess) e = cudaMalloc(&p->d_meta, meta.size() * sizeof(MyersPatMeta));
-            if (e == cudaSuccess) e = cudaMemcpyAsync(p->d_eq, eq.data(), eq.size() * 4, cudaMemcpyHostToDevice, ctx->stream);
-            if (e == cudaSuccess) e = cudaMemcpyAsync(p->d_meta, meta.data(), meta.size() * sizeof(MyersPatMeta), cudaMemcpyHostToDevice, ctx->stream);
-            if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream); // host vectors go out of scope
+            if (e == cudaSuccess) e = pattern_upload_myers(ctx, p, k);
+            if (e == cudaSuccess && p->filtered) e = pattern_upload_pigeon(ctx, p, seeds, q);
+        }
+    } else if (alg == SPMB_ALG_PIGEONHOLE) {
+        // SeqAn2 _patternInit(Pattern<TIndex, Pigeonhole<TSpec>>, errorRate) (UNVERIFIED-UPSTREAM; pinned by
+        // the golden vectors of pigeonhole_matcher_test.cpp): delta = len / (floor(rate*len) + 1) per needle,
+        // deltas < 3 ignored, q = the smallest one, q-grams every q symbols
+        uint32_t q = 0xffffffffu;
+        for (uint32_t i = 0; i < n_pat; ++i) {
+            const uint32_t len = p->len[i];
+            if (len == 0) continue;
+            const uint32_t errors = (uint32_t)(error_rate * (double)len);
+            const uint32_t delta = len / (errors + 1);
+            if (delta < 3) continue;
+            q = std::min(q, delta);
+        }
+        if (q == 0xffffffffu) {
+            // no needle yields a usable q-gram: nothing can be found (window_size 0)
+            p->max_m = 0;
+        } else {
+            std::vector<std::pair<uint32_t, uint32_t>> seeds;
+            for (uint32_t i = 0; i < n_pat; ++i)
+                for (uint32_t o = 0; o + q <= p->len[i]; o += q) seeds.push_back({i, o});
+            p->filtered = true;
+            if (e == cudaSuccess) e = pattern_upload_pigeon(ctx, p, seeds, q);
         }
     } else {
         for (uint32_t i = 0; i < n_pat; ++i) {
@@ -505,6 +590,27 @@ extern "C" int spmb_pattern_set_create(spmb_context *ctx, int alg, const uint8_t
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     if (e != cudaSuccess) { spmb_pattern_destroy(p); return set_err(ctx, SPMB_ERR_CUDA, "pattern upload", e); }
     *out = p;
+    return SPMB_OK;
+}
+
+extern "C" int spmb_pattern_set_create(spmb_context *ctx, int alg, const uint8_t *ranks, const uint32_t *lengths,
+                                       uint32_t n_pat, uint32_t k, spmb_pattern **out)
+{
+    if (alg == SPMB_ALG_PIGEONHOLE) return ctx ? set_err(ctx, SPMB_ERR_ARG, "use spmb_pigeonhole_create") : SPMB_ERR_ARG;
+    return pattern_build(ctx, alg, ranks, lengths, n_pat, k, 0.0, out);
+}
+
+extern "C" int spmb_pigeonhole_create(spmb_context *ctx, const uint8_t *ranks, const uint32_t *lengths,
+                                      uint32_t n_needles, double error_rate, spmb_pattern **out)
+{
+    return pattern_build(ctx, SPMB_ALG_PIGEONHOLE, ranks, lengths, n_needles, 0, error_rate, out);
+}
+
+extern "C" int spmb_pattern_filter_info(const spmb_pattern *p, uint32_t info[5])
+{
+    if (!p || !info) return SPMB_ERR_ARG;
+    info[0] = p->pg.q; info[1] = (uint32_t)p->pg.seed_pat.size(); info[2] = (uint32_t)p->pg.n_unique;
+    info[3] = p->pg.B; info[4] = p->filtered ? 1u : 0u;
     return SPMB_OK;
 }
 
@@ -521,6 +627,9 @@ extern "C" int spmb_pattern_destroy(spmb_pattern *p)
     cudaFree(p->d_ranks);
     cudaFree(p->d_eq);
     cudaFree(p->d_meta);
+    cudaFree(p->d_off);
+    cudaFree(p->d_pg_bitmap); cudaFree(p->d_pg_key); cudaFree(p->d_pg_val);
+    cudaFree(p->d_pg_ufirst); cudaFree(p->d_pg_pat); cudaFree(p->d_pg_soff);
     delete p;
     return SPMB_OK;
 }
@@ -528,6 +637,7 @@ extern "C" int spmb_pattern_destroy(spmb_pattern *p)
 extern "C" uint32_t spmb_pattern_window_size(const spmb_pattern *p)
 {
     if (!p || p->max_m == 0) return 0;
+    if (p->alg == SPMB_ALG_PIGEONHOLE) return p->pg.q;
     return p->max_m + p->k;
 }
 extern "C" uint32_t spmb_pattern_count(const spmb_pattern *p) { return p ? p->n_pat : 0; }
@@ -546,6 +656,17 @@ static int hits_reserve(spmb_context *ctx, spmb_hits *h, unsigned long long cap)
     return SPMB_OK;
 }
 
+static int cand_reserve(spmb_context *ctx, spmb_hits *h, unsigned long long cap)
+{
+    if (cap <= h->cand_cap) return SPMB_OK;
+    cudaFree(h->d_cand);
+    h->d_cand = nullptr;
+    h->cand_cap = 0;
+    CU(cudaMalloc(&h->d_cand, cap * sizeof(PigeonCand)));
+    h->cand_cap = cap;
+    return SPMB_OK;
+}
+
 extern "C" int spmb_hits_create(spmb_context *ctx, uint64_t capacity_hint, spmb_hits **out)
 {
     if (!ctx || !out) return SPMB_ERR_ARG;
@@ -553,7 +674,8 @@ extern "C" int spmb_hits_create(spmb_context *ctx, uint64_t capacity_hint, spmb_
     spmb_hits *h = new (std::nothrow) spmb_hits();
     if (!h) return SPMB_ERR_OOM;
     h->ctx = ctx;
-    cudaError_t e = cudaMalloc(&h->d_count, sizeof(unsigned long long));
+    cudaError_t e = cudaMalloc(&h->d_count, 4 * sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMemset(h->d_count, 0, 4 * sizeof(unsigned long long));
     if (e != cudaSuccess) { delete h; return set_err(ctx, SPMB_ERR_OOM, "cudaMalloc(hit counter)", e); }
     int rc = hits_reserve(ctx, h, capacity_hint ? capacity_hint : (1ull << 16));
     if (rc) { cudaFree(h->d_count); delete h; return rc; }
@@ -567,6 +689,7 @@ extern "C" int spmb_hits_destroy(spmb_hits *h)
     if (h->ctx) cudaSetDevice(h->ctx->device);
     cudaFree(h->d_hits);
     cudaFree(h->d_count);
+    cudaFree(h->d_cand);
     delete h;
     return SPMB_OK;
 }
@@ -598,15 +721,147 @@ static cudaError_t launch_myers(spmb_context *ctx, const spmb_store *s, const sp
     return cudaGetLastError();
 }
 
+static PigeonDev pigeon_dev(const spmb_pattern *p)
+{
+    PigeonDev d;
+    d.bitmap = p->d_pg_bitmap; d.tab_key = p->d_pg_key; d.tab_val = p->d_pg_val;
+    d.ufirst = p->d_pg_ufirst; d.seed_pat = p->d_pg_pat; d.seed_off = p->d_pg_soff;
+    d.q = p->pg.q; d.kq = p->pg.kq; d.B = p->pg.B; d.T = p->pg.T;
+    d.himask = p->pg.himask(); d.lomask = p->pg.lomask();
+    return d;
+}
+
+template <int MODE, bool WIDE>
+static cudaError_t launch_filter_kernel(spmb_context *ctx, const PigeonFilterArgs &fa, unsigned grid, size_t smem)
+{
+    static bool attr_set[16] = {false};
+    if (ctx->device < 16 && !attr_set[ctx->device]) {
+        cudaError_t e = cudaFuncSetAttribute(pigeon_filter_kernel<MODE, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
+        if (e != cudaSuccess) return e;
+        attr_set[ctx->device] = true;
+    } else if (ctx->device >= 16) {
+        cudaFuncSetAttribute(pigeon_filter_kernel<MODE, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
+    }
+    pigeon_filter_kernel<MODE, WIDE><<<grid, 1024, smem, ctx->stream>>>(fa);
+    return cudaGetLastError();
+}
+
+template <int MODE>
+static cudaError_t launch_verify(spmb_context *ctx, const spmb_pattern *p, const PigeonVerifyArgs &va)
+{
+    const unsigned grid = (unsigned)ctx->sm_count * 8;
+    if (p->alg == SPMB_ALG_PIGEONHOLE) { pigeon_seed_kernel<MODE><<<grid, 128, 0, ctx->stream>>>(va); return cudaGetLastError(); }
+    switch (p->NW) {
+    case 1: pigeon_verify_kernel<1, MODE><<<grid, 128, 0, ctx->stream>>>(va); break;
+    case 2: pigeon_verify_kernel<2, MODE><<<grid, 128, 0, ctx->stream>>>(va); break;
+    case 3: pigeon_verify_kernel<3, MODE><<<grid, 128, 0, ctx->stream>>>(va); break;
+    case 4: pigeon_verify_kernel<4, MODE><<<grid, 128, 0, ctx->stream>>>(va); break;
+    case 5: pigeon_verify_kernel<5, MODE><<<grid, 128, 0, ctx->stream>>>(va); break;
+    case 6: pigeon_verify_kernel<6, MODE><<<grid, 128, 0, ctx->stream>>>(va); break;
+    case 7: pigeon_verify_kernel<7, MODE><<<grid, 128, 0, ctx->stream>>>(va); break;
+    case 8: pigeon_verify_kernel<8, MODE><<<grid, 128, 0, ctx->stream>>>(va); break;
+    default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
+// seed filter + (seed emission | windowed Myers verification) over the shard [st0, st1) of a store
+template <int MODE>
+static int enqueue_filtered(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p, spmb_hits *h,
+                            uint64_t st0, uint64_t st1, uint32_t seq_id, const HitSink &sink)
+{
+    if (st1 <= st0 || p->pg.seed_pat.empty()) return SPMB_OK;
+    int rc = store_ensure_lanes(ctx, s);
+    if (rc) return rc;
+    rc = cand_reserve(ctx, h, 1ull << 16);
+    if (rc) return rc;
+    CU(cudaMemsetAsync(h->d_count + 1, 0, sizeof(unsigned long long), ctx->stream));
+    const uint64_t per_st = 32ull * s->lay.row_len;
+    PigeonFilterArgs fa;
+    fa.lanes = s->lanes; fa.lay = s->lay; fa.pg = pigeon_dev(p);
+    fa.row_len = s->row_len;
+    fa.st0 = st0; fa.st1 = st1;
+    if (MODE == SPMB_MODE_PLAIN && p->alg == SPMB_ALG_MYERS_FILTERED && st0 > 0) {
+        // a hit owned by this shard may hang on a seed that begins up to m+k symbols before it
+        const uint64_t back = ((uint64_t)p->max_m + p->k + per_st - 1) / per_st;
+        fa.st0 = st0 > back ? st0 - back : 0;
+    }
+    fa.cand = h->d_cand; fa.cand_count = h->d_count + 1; fa.cand_cap = h->cand_cap;
+    const uint32_t segs = (s->lay.row_len / 32 + 31) / 32;
+    const uint64_t units = (fa.st1 - fa.st0) * segs;
+    unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)ctx->sm_count, (units + 31) / 32);
+    if (grid == 0) grid = 1;
+    const size_t smem = (size_t)4 << (p->pg.B - 5);
+    cudaError_t e = (p->pg.kq > 16) ? launch_filter_kernel<MODE, true>(ctx, fa, grid, smem)
+                                    : launch_filter_kernel<MODE, false>(ctx, fa, grid, smem);
+    if (e != cudaSuccess) return set_err(ctx, SPMB_ERR_CUDA, "pigeon_filter_kernel launch", e);
+    PigeonVerifyArgs va;
+    va.lanes = s->lanes; va.lay = s->lay; va.pg = fa.pg;
+    va.cand = h->d_cand; va.counters = h->d_count; va.cand_cap = h->cand_cap;
+    va.pat_ranks = p->d_ranks; va.pat_off = p->d_off; va.eq = p->d_eq; va.meta = p->d_meta;
+    va.row_len = s->row_len; va.row_seq = s->row_seq; va.row_own = s->row_own;
+    va.seq_id = seq_id;
+    va.own_lo = st0 * per_st;
+    va.own_hi = std::min<uint64_t>(s->lay.n, st1 * per_st);
+    va.sink = sink;
+    e = launch_verify<MODE>(ctx, p, va);
+    if (e != cudaSuccess) return set_err(ctx, SPMB_ERR_CUDA, "pigeon verify launch", e);
+    ctx->launches += 2;
+    return SPMB_OK;
+}
+
+template <int NWX>
+static void launch_prefix_nw(spmb_context *ctx, const PrefixArgs &pa, unsigned grid)
+{
+    prefix_kernel<NWX><<<grid, 128, 0, ctx->stream>>>(pa);
+}
+
+static int enqueue_prefix(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p, const uint64_t *d_anchors,
+                          uint64_t n_anchors, uint32_t seq_id, const HitSink &sink)
+{
+    if (s->lay.mode != SPMB_MODE_PLAIN) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "prefix matcher: plain stores only");
+    if (p->NW == 0 || n_anchors == 0) return SPMB_OK;
+    int rc = store_ensure_lanes(ctx, s);
+    if (rc) return rc;
+    PrefixArgs pa;
+    pa.lanes = s->lanes; pa.lay = s->lay; pa.anchors = d_anchors; pa.n_anchors = n_anchors;
+    pa.eq = p->d_eq; pa.meta = p->d_meta; pa.n_pat = p->n_pat; pa.seq_id = seq_id; pa.sink = sink;
+    const uint64_t tasks = n_anchors * p->n_pat;
+    const unsigned grid = (unsigned)std::min<uint64_t>((tasks + 127) / 128, (uint64_t)ctx->sm_count * 16);
+    switch (p->NW) {
+    case 1: launch_prefix_nw<1>(ctx, pa, grid); break;
+    case 2: launch_prefix_nw<2>(ctx, pa, grid); break;
+    case 3: launch_prefix_nw<3>(ctx, pa, grid); break;
+    case 4: launch_prefix_nw<4>(ctx, pa, grid); break;
+    case 5: launch_prefix_nw<5>(ctx, pa, grid); break;
+    case 6: launch_prefix_nw<6>(ctx, pa, grid); break;
+    case 7: launch_prefix_nw<7>(ctx, pa, grid); break;
+    case 8: launch_prefix_nw<8>(ctx, pa, grid); break;
+    default: return set_err(ctx, SPMB_ERR_UNSUPPORTED, "prefix matcher: needle too long");
+    }
+    ctx->launches++;
+    CU(cudaGetLastError());
+    return SPMB_OK;
+}
+
 static int enqueue_search(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p, spmb_hits *h,
                           bool reset = true, uint32_t seq_id = 0)
 {
-    if (reset) CU(cudaMemsetAsync(h->d_count, 0, sizeof(unsigned long long), ctx->stream));
+    if (reset) CU(cudaMemsetAsync(h->d_count, 0, 4 * sizeof(unsigned long long), ctx->stream));
     HitSink sink{h->d_hits, h->d_count, h->cap};
     if (p->max_m == 0 || s->lay.n == 0) return SPMB_OK; // empty needle / haystack: no hits
     const uint64_t st0 = s->lay.n_st * ctx->shard / ctx->n_shards;
     const uint64_t st1 = s->lay.n_st * (ctx->shard + 1) / ctx->n_shards;
-    if (p->alg == SPMB_ALG_MYERS) {
+    if (p->alg == SPMB_ALG_MYERS_PREFIX) {
+        if (ctx->shard != 0) return SPMB_OK; // the single anchor 0 belongs to shard 0
+        return enqueue_prefix(ctx, s, p, nullptr, 1, seq_id, sink);
+    }
+    if (p->filtered) { // SPMB_ALG_PIGEONHOLE, SPMB_ALG_MYERS_FILTERED with a usable q
+        return (s->lay.mode == SPMB_MODE_PLAIN) ? enqueue_filtered<SPMB_MODE_PLAIN>(ctx, s, p, h, st0, st1, seq_id, sink)
+                                                : enqueue_filtered<SPMB_MODE_WINDOWS>(ctx, s, p, h, st0, st1, seq_id, sink);
+    }
+    if (p->alg == SPMB_ALG_PIGEONHOLE) return SPMB_OK; // no usable q-gram
+    if (p->alg == SPMB_ALG_MYERS || p->alg == SPMB_ALG_MYERS_FILTERED) {
         if (p->n_pat > 65535) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "more than 65535 patterns in one Myers set");
         int rc = store_ensure_lanes(ctx, s);
         if (rc) return rc;
@@ -672,33 +927,105 @@ static bool hit_less(const spmb_hit &a, const spmb_hit &b)
     return a.end < b.end;
 }
 
+// order of the reference's callback sequence for the seed matcher: haystack position first
+static bool seed_hit_less(const spmb_hit &a, const spmb_hit &b)
+{
+    if (a.seq_id != b.seq_id) return a.seq_id < b.seq_id;
+    if (a.end != b.end) return a.end < b.end;
+    if (a.pattern_id != b.pattern_id) return a.pattern_id < b.pattern_id;
+    return a.reserved < b.reserved;
+}
+
+// sort a raw device hit list into the order handed back; the filtered Myers path reports an end once
+// per seed window it lies in -- keep the smallest error count (the exact one, pigeon.cuh)
+static void hits_order(std::vector<spmb_hit> &v, int alg)
+{
+    if (alg == SPMB_ALG_PIGEONHOLE) { std::sort(v.begin(), v.end(), seed_hit_less); return; }
+    if (alg == SPMB_ALG_MYERS_FILTERED) {
+        std::sort(v.begin(), v.end(), [](const spmb_hit &a, const spmb_hit &b) {
+            if (hit_less(a, b)) return true;
+            if (hit_less(b, a)) return false;
+            return a.errors < b.errors;
+        });
+        v.erase(std::unique(v.begin(), v.end(), [](const spmb_hit &a, const spmb_hit &b) {
+                    return a.pattern_id == b.pattern_id && a.seq_id == b.seq_id && a.end == b.end;
+                }), v.end());
+        return;
+    }
+    std::sort(v.begin(), v.end(), hit_less);
+}
+
+// wait for the enqueued search, regrow the hit / candidate buffers and re-run (`again`) while one of
+// them overflowed (the counters keep counting, so they hold the exact sizes needed), then copy the raw
+// hits to `raw`
+template <class Again>
+static int hits_collect(spmb_context *ctx, spmb_hits *h, std::vector<spmb_hit> &raw, Again again)
+{
+    for (int attempt = 0; attempt < 5; ++attempt) {
+        CU(cudaMemcpyAsync(ctx->h_count, h->d_count, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+        const unsigned long long cnt = ctx->h_count[0];
+        const unsigned long long cand = std::max(ctx->h_count[1], ctx->h_count[2]);
+        if (cnt <= h->cap && cand <= h->cand_cap) {
+            raw.resize(cnt);
+            if (cnt) {
+                CU(cudaMemcpyAsync(raw.data(), h->d_hits, cnt * sizeof(spmb_hit), cudaMemcpyDeviceToHost, ctx->stream));
+                CU(cudaStreamSynchronize(ctx->stream));
+            }
+            return SPMB_OK;
+        }
+        int rc = SPMB_OK;
+        if (cand > h->cand_cap) rc = cand_reserve(ctx, h, cand + cand / 8 + 1024);
+        // a truncated candidate list also truncates the hit count: size the hit buffer on the next pass
+        if (rc == SPMB_OK && cnt > h->cap) rc = hits_reserve(ctx, h, cnt + cnt / 8 + 1024);
+        if (rc) return rc;
+        rc = again();
+        if (rc) return rc;
+    }
+    return set_err(ctx, SPMB_ERR_CUDA, "hit buffer kept overflowing");
+}
+
 extern "C" int spmb_search_finish(spmb_context *ctx, spmb_hits *h)
 {
     if (!ctx || !h || !h->pend_store) return SPMB_ERR_ARG;
     ENTER(ctx);
-    for (int attempt = 0; attempt < 4; ++attempt) {
-        CU(cudaMemcpyAsync(ctx->h_count, h->d_count, sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
-        CU(cudaStreamSynchronize(ctx->stream));
-        unsigned long long cnt = *ctx->h_count;
-        if (cnt <= h->cap) {
-            h->count = cnt;
-            h->host.resize(cnt);
-            if (cnt) {
-                CU(cudaMemcpyAsync(h->host.data(), h->d_hits, cnt * sizeof(spmb_hit), cudaMemcpyDeviceToHost, ctx->stream));
-                CU(cudaStreamSynchronize(ctx->stream));
-                std::sort(h->host.begin(), h->host.end(), hit_less);
-            }
-            h->pend_store = nullptr;
-            h->pend_pat = nullptr;
-            return SPMB_OK;
-        }
-        // overflow: the counter kept counting, so it is the exact size needed
-        int rc = hits_reserve(ctx, h, cnt + cnt / 8 + 1024);
-        if (rc) return rc;
-        rc = enqueue_search(ctx, h->pend_store, h->pend_pat, h);
-        if (rc) return rc;
-    }
-    return set_err(ctx, SPMB_ERR_CUDA, "hit buffer kept overflowing");
+    const spmb_store *s = h->pend_store;
+    const spmb_pattern *p = h->pend_pat;
+    int rc = hits_collect(ctx, h, h->host, [&]() { return enqueue_search(ctx, s, p, h); });
+    if (rc) return rc;
+    hits_order(h->host, p->alg);
+    h->count = h->host.size();
+    h->pend_store = nullptr;
+    h->pend_pat = nullptr;
+    return SPMB_OK;
+}
+
+extern "C" int spmb_search_anchored(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p,
+                                    const uint64_t *anchors, uint64_t n_anchors, spmb_hits *h)
+{
+    if (!ctx || !s || !p || !h || (n_anchors && !anchors)) return SPMB_ERR_ARG;
+    if (p->alg != SPMB_ALG_MYERS_PREFIX) return set_err(ctx, SPMB_ERR_ARG, "anchored search takes a SPMB_ALG_MYERS_PREFIX pattern");
+    ENTER(ctx);
+    ctx->launches = 0;
+    h->host.clear();
+    h->count = 0;
+    uint64_t *d_anchors = nullptr;
+    CU(cudaMallocAsync(&d_anchors, (n_anchors ? n_anchors : 1) * 8, ctx->stream));
+    cudaError_t e = n_anchors ? cudaMemcpyAsync(d_anchors, anchors, n_anchors * 8, cudaMemcpyHostToDevice, ctx->stream) : cudaSuccess;
+    int rc = (e == cudaSuccess) ? SPMB_OK : set_err(ctx, SPMB_ERR_CUDA, "H2D anchors", e);
+    auto run = [&]() -> int {
+        CU(cudaMemsetAsync(h->d_count, 0, 4 * sizeof(unsigned long long), ctx->stream));
+        HitSink sink{h->d_hits, h->d_count, h->cap};
+        return enqueue_prefix(ctx, s, p, d_anchors, n_anchors, 0, sink);
+    };
+    if (rc == SPMB_OK) rc = run();
+    if (rc == SPMB_OK) rc = hits_collect(ctx, h, h->host, run);
+    cudaFreeAsync(d_anchors, ctx->stream);
+    cudaStreamSynchronize(ctx->stream);
+    if (rc) return rc;
+    hits_order(h->host, p->alg);
+    h->count = h->host.size();
+    return SPMB_OK;
 }
 
 extern "C" int spmb_search(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p, spmb_hits *h)
@@ -906,23 +1233,17 @@ extern "C" int spmb_jst_search(spmb_context *ctx, spmb_jst *j, const spmb_patter
     cudaEvent_t e0, e1;
     CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
     std::vector<spmb_hit> raw;
-    for (int attempt = 0;; ++attempt) {
+    auto run = [&]() -> int {
         CU(cudaEventRecord(e0, ctx->stream));
-        rc = jst_enqueue(ctx, j, p, h);
-        if (rc) return rc;
+        int r = jst_enqueue(ctx, j, p, h);
+        if (r) return r;
         CU(cudaEventRecord(e1, ctx->stream));
-        CU(cudaMemcpyAsync(ctx->h_count, h->d_count, sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
-        CU(cudaStreamSynchronize(ctx->stream));
-        const unsigned long long cnt = *ctx->h_count;
-        if (cnt <= h->cap) {
-            raw.resize(cnt);
-            if (cnt) CU(cudaMemcpy(raw.data(), h->d_hits, cnt * sizeof(spmb_hit), cudaMemcpyDeviceToHost));
-            break;
-        }
-        if (attempt >= 3) return set_err(ctx, SPMB_ERR_CUDA, "hit buffer kept overflowing");
-        rc = hits_reserve(ctx, h, cnt + cnt / 8 + 1024);
-        if (rc) return rc;
-    }
+        return SPMB_OK;
+    };
+    rc = run();
+    if (rc == SPMB_OK) rc = hits_collect(ctx, h, raw, run);
+    if (rc) { cudaEventDestroy(e0); cudaEventDestroy(e1); return rc; }
+    if (p->alg == SPMB_ALG_MYERS_FILTERED) hits_order(raw, p->alg); // one record per (window, end)
     float t = 0;
     cudaEventElapsedTime(&t, e0, e1);
     cudaEventDestroy(e0); cudaEventDestroy(e1);
@@ -976,7 +1297,7 @@ extern "C" int spmb_jst_search(spmb_context *ctx, spmb_jst *j, const spmb_patter
         }
         i = e;
     }
-    std::sort(out.begin(), out.end(), hit_less);
+    hits_order(out, p->alg);
     h->count = out.size();
     h->pend_store = nullptr; h->pend_pat = nullptr;
     j->ms[3] = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
@@ -1003,6 +1324,29 @@ extern "C" int spmb_stream_feed(spmb_context *ctx, spmb_stream *st, const uint8_
 {
     if (!ctx || !st || !h || (!host_ranks && n)) return SPMB_ERR_ARG;
     const uint32_t ws = spmb_pattern_window_size(st->pat);
+    if (st->pat->alg == SPMB_ALG_MYERS_PREFIX) {
+        // anchored at the stream start: the state is the prefix consumed so far, and nothing beyond
+        // m + k + 1 symbols is ever scanned (myers_prefix_matcher_restorable.hpp:47-50)
+        const size_t clamp = ws ? (size_t)ws + 1 : 0;
+        const size_t tl = st->tail.size();
+        h->host.clear();
+        h->count = 0;
+        if (st->offset >= clamp || n == 0) { st->offset += n; return SPMB_OK; }
+        const size_t take = std::min<size_t>(n, clamp - tl);
+        st->scratch.resize(tl + take);
+        if (tl) memcpy(st->scratch.data(), st->tail.data(), tl);
+        memcpy(st->scratch.data() + tl, host_ranks, take);
+        int rc = spmb_search_host(ctx, st->scratch.data(), st->scratch.size(), st->pat, h);
+        if (rc) return rc;
+        size_t w = 0;
+        for (size_t i = 0; i < h->host.size(); ++i)
+            if (h->host[i].end > tl) { spmb_hit x = h->host[i]; x.end -= tl; h->host[w++] = x; }
+        h->host.resize(w);
+        h->count = w;
+        st->tail = st->scratch;
+        st->offset += n;
+        return SPMB_OK;
+    }
     const size_t keep = ws ? ws - 1 : 0;
     const size_t tl = st->tail.size();
     st->scratch.resize(tl + n);

@@ -65,6 +65,13 @@ def lib():
         L.orc_jst_haplotype.restype = C.c_uint64
         L.orc_jst_haplotype.argtypes = [u8p, C.c_uint64, C.c_void_p, C.c_uint64, u8p, C.c_void_p, C.c_uint32,
                                         C.c_uint32, u8p, C.c_uint64]
+        L.orc_pigeonhole_q.restype = C.c_uint32
+        L.orc_pigeonhole_q.argtypes = [C.c_void_p, C.c_uint32, C.c_double]
+        L.orc_pigeonhole.restype = C.c_uint64
+        L.orc_pigeonhole.argtypes = [u8p, C.c_uint64, u8p, C.c_void_p, C.c_uint32, C.c_double, u64p, u32p, u32p,
+                                     C.c_uint64]
+        L.orc_myers_prefix.restype = C.c_uint64
+        L.orc_myers_prefix.argtypes = [u8p, C.c_uint64, u8p, C.c_uint32, C.c_uint32, u64p, u32p, C.c_uint64]
         _lib = L
     return _lib
 
@@ -245,3 +252,37 @@ def jst_search(alg, ref, variants, pool, cov, n_hap, pat, k=0, haps=None, thread
         if cnt <= cap:
             return out[:cnt].copy()
         cap = cnt
+
+
+SEED_DTYPE = np.dtype([("begin", "<u8"), ("needle", "<u4"), ("offset", "<u4")])
+
+
+def pigeonhole_q(lengths, error_rate=0.0):
+    ln = np.ascontiguousarray(lengths, dtype=np.uint32)
+    return int(lib().orc_pigeonhole_q(ln.ctypes.data, len(ln), float(error_rate)))
+
+
+def pigeonhole(text, needles, error_rate=0.0):
+    """seed hits of spm::pigeonhole_matcher{needles, error_rate}: SEED_DTYPE in haystack order."""
+    L = lib()
+    text, tp = _u8(text)
+    parts = [np.ascontiguousarray(x, dtype=np.uint8) for x in needles]
+    ln = np.array([len(x) for x in parts], dtype=np.uint32)
+    cat, cp = _u8(np.concatenate(parts) if parts else np.zeros(1, np.uint8))
+    cap = 1 << 16
+    while True:
+        b = np.empty(cap, dtype=np.uint64)
+        i = np.empty(cap, dtype=np.uint32)
+        o = np.empty(cap, dtype=np.uint32)
+        cnt = int(L.orc_pigeonhole(tp, len(text), cp, ln.ctypes.data, len(ln), float(error_rate), b.ctypes.data,
+                                   i.ctypes.data, o.ctypes.data, cap))
+        if cnt <= cap:
+            out = np.empty(cnt, dtype=SEED_DTYPE)
+            out["begin"], out["needle"], out["offset"] = b[:cnt], i[:cnt], o[:cnt]
+            return out
+        cap = cnt
+
+
+def myers_prefix(text, pat, k):
+    """restorable_myers_prefix_matcher: (ends, errors) of the needle against prefixes of text."""
+    return _run(lib().orc_myers_prefix, text, pat, (int(k),), with_err=True, cap=len(pat) + int(k) + 2)

@@ -18,6 +18,7 @@
 #include "spm_oracle.h"
 #include <stdlib.h>
 #include <string.h>
+#include <math.h>
 #ifdef _OPENMP
 #include <omp.h>
 #endif
@@ -539,4 +540,93 @@ uint64_t orc_jst_search(int alg, const uint8_t *ref, uint64_t n, const orc_event
     }
     if (out) qsort(out, total < cap ? total : cap, sizeof(orc_jst_hit_t), jst_hit_cmp);
     return total;
+}
+
+/* ------------------------------------------------------------------ */
+/* pigeonhole q-gram seed matcher + anchored (prefix) Myers            */
+/*                                          */
+/* ------------------------------------------------------------------ */
+
+/* q of spm::pigeonhole_matcher{needles, error_rate} (pigeonhole_matcher.hpp:157-180 -> SeqAn2
+ * _patternInit(Pattern<TIndex, Pigeonhole<TSpec>>, errorRate), UNVERIFIED-UPSTREAM: per needle
+ * delta = len / (floor(rate*len) + 1), deltas < 3 ignored, q = smallest delta, step = q).
+ * Pinned by pigeonhole_matcher_test.cpp:50-53 (window_size == 5 for needle GCACG, rate 0) and the
+ * multi-needle vector :31-33 (needles of 5 and 10 symbols -> q = 5, seeds at needle offsets 0 and 5). */
+uint32_t orc_pigeonhole_q(const uint32_t *lengths, uint32_t n_needles, double error_rate)
+{
+    uint32_t q = 0xffffffffu;
+    for (uint32_t i = 0; i < n_needles; ++i) {
+        uint32_t len = lengths[i];
+        if (len == 0) continue;
+        uint32_t errors = (uint32_t)floor(error_rate * (double)len);
+        uint32_t delta = len / (errors + 1);
+        if (delta < 3) continue;
+        if (delta < q) q = delta;
+    }
+    return q == 0xffffffffu ? 0 : q;
+}
+
+/* definitional: every haystack position whose q-gram equals the q-gram at offset 0, q, 2q, ... of a
+ * needle; hit = (begin, needle index, needle offset), in haystack order, ties by (needle, offset)
+ * (pigeonhole_matcher.hpp:118-124 position() = {index, offset, count = q}). */
+uint64_t orc_pigeonhole(const uint8_t *text, uint64_t n, const uint8_t *needles, const uint32_t *lengths,
+                        uint32_t n_needles, double error_rate, uint64_t *begins, uint32_t *needle_idx,
+                        uint32_t *needle_off, uint64_t cap)
+{
+    const uint32_t q = orc_pigeonhole_q(lengths, n_needles, error_rate);
+    uint64_t cnt = 0;
+    if (q == 0 || n < q) return 0;
+    for (uint64_t p = 0; p + q <= n; ++p) {
+        uint64_t base = 0;
+        for (uint32_t i = 0; i < n_needles; ++i) {
+            for (uint32_t o = 0; o + q <= lengths[i]; o += q) {
+                if (memcmp(text + p, needles + base + o, q) == 0) {
+                    if (cnt < cap) {
+                        if (begins) begins[cnt] = p;
+                        if (needle_idx) needle_idx[cnt] = i;
+                        if (needle_off) needle_off[cnt] = o;
+                    }
+                    ++cnt;
+                }
+            }
+            base += lengths[i];
+        }
+    }
+    return cnt;
+}
+
+/* definitional: restorable_myers_prefix_matcher (myers_prefix_matcher_restorable.hpp:47-61,117-160;
+ * SeqAn2 MyersUkkonenGlobal): edit distance of the needle to every PREFIX text[0..j) -- D[0][j] = j,
+ * D[i][0] = i -- scanning at most m + k + 1 symbols (:47-50); end = j, errors = D[m][j] <= k. */
+uint64_t orc_myers_prefix(const uint8_t *text, uint64_t n, const uint8_t *pat, uint32_t m, uint32_t k,
+                          uint64_t *ends, uint32_t *errs, uint64_t cap)
+{
+    uint64_t cnt = 0;
+    if (m == 0) return 0;
+    uint64_t lim = (uint64_t)m + k + 1;
+    if (lim > n) lim = n;
+    uint32_t *col = (uint32_t *)malloc((size_t)(m + 1) * sizeof(uint32_t));
+    for (uint32_t i = 0; i <= m; ++i) col[i] = i;
+    for (uint64_t j = 0; j < lim; ++j) {
+        uint32_t diag = col[0];
+        col[0] = (uint32_t)(j + 1);
+        uint8_t c = text[j];
+        for (uint32_t i = 1; i <= m; ++i) {
+            uint32_t up = col[i - 1], left = col[i];
+            uint32_t v = diag + (pat[i - 1] != c);
+            if (up + 1 < v) v = up + 1;
+            if (left + 1 < v) v = left + 1;
+            diag = left;
+            col[i] = v;
+        }
+        if (col[m] <= k) {
+            if (cnt < cap) {
+                if (ends) ends[cnt] = j + 1;
+                if (errs) errs[cnt] = col[m];
+            }
+            ++cnt;
+        }
+    }
+    free(col);
+    return cnt;
 }

@@ -108,6 +108,14 @@ uint64_t orc_jst_haplotype(const uint8_t *ref, uint64_t n, const orc_event_t *va
                            const uint8_t *pool, const uint64_t *cov, uint32_t words_per_row, uint32_t hap,
                            uint8_t *out, uint64_t out_cap);
 
+/* ---- "next" rows of SURVEY.md 8(f): pigeonhole seed matcher, anchored (prefix) Myers ---- */
+uint32_t orc_pigeonhole_q(const uint32_t *lengths, uint32_t n_needles, double error_rate);
+uint64_t orc_pigeonhole(const uint8_t *text, uint64_t n, const uint8_t *needles, const uint32_t *lengths,
+                        uint32_t n_needles, double error_rate, uint64_t *begins, uint32_t *needle_idx,
+                        uint32_t *needle_off, uint64_t cap);
+uint64_t orc_myers_prefix(const uint8_t *text, uint64_t n, const uint8_t *pat, uint32_t m, uint32_t k,
+                          uint64_t *ends, uint32_t *errs, uint64_t cap);
+
 #ifdef __cplusplus
 }
 #endif

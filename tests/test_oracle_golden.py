@@ -144,3 +144,58 @@ def test_journal_apply():
     out = orc.journal_apply(ref, ev, pool)
     #  AC [G->T] T [+GGG] ACG [-TA] C
     assert "".join("ACGT"[x] for x in out) == "ACTTGGGACGC"
+
+
+# ---- pigeonhole seed matcher -- the reference's own vectors ----
+# /root/reference/test/api/libspm/matcher/pigeonhole_matcher_test.cpp:25-33
+GOLD_NEEDLE2 = dna4("TGACTAGCAC")
+GOLD_MULTI_POSITIONS = [3, 8, 9, 14, 19, 20, 25, 30, 31, 36]
+GOLD_NEEDLE_POSITIONS = [(1, 0, 5), (1, 5, 5), (0, 0, 5), (1, 0, 5), (1, 5, 5),
+                         (0, 0, 5), (1, 0, 5), (1, 5, 5), (0, 0, 5), (1, 0, 5)]
+
+
+def test_pigeonhole_golden_single_needle():
+    # pigeonhole_matcher_test.cpp:50-53 (window_size == needle size at error rate 0), :55-64
+    assert orc.pigeonhole_q([len(GOLD_NEEDLE)], 0.0) == 5
+    hits = orc.pigeonhole(GOLD_HAYSTACK, [GOLD_NEEDLE], 0.0)
+    assert hits["begin"].tolist() == GOLD_EXACT_BEGIN
+
+
+def test_pigeonhole_golden_multi_needle():
+    # pigeonhole_matcher_test.cpp:66-86: begin positions and {index, offset, count} per callback
+    q = orc.pigeonhole_q([5, 10], 0.0)
+    assert q == 5
+    hits = orc.pigeonhole(GOLD_HAYSTACK, [GOLD_NEEDLE, GOLD_NEEDLE2], 0.0)
+    assert hits["begin"].tolist() == GOLD_MULTI_POSITIONS
+    assert [(int(h["needle"]), int(h["offset"]), q) for h in hits] == GOLD_NEEDLE_POSITIONS
+
+
+def test_pigeonhole_q_rule():
+    # delta = len / (floor(rate*len)+1); deltas < 3 are ignored; q = the smallest
+    assert orc.pigeonhole_q([100], 0.03) == 25
+    assert orc.pigeonhole_q([100, 60], 0.05) == 15
+    assert orc.pigeonhole_q([100, 4], 0.3) == 3      # 100/31 = 3; 4/2 = 2 is ignored
+    assert orc.pigeonhole_q([2], 0.0) == 0
+
+
+def test_myers_prefix_is_global_prefix_distance():
+    # restorable_myers_prefix_matcher (myers_prefix_matcher_restorable.hpp:47-61): needle vs prefixes
+    rng = np.random.default_rng(5)
+    for _ in range(50):
+        m = int(rng.integers(1, 40))
+        k = int(rng.integers(0, 6))
+        pat = rand_text(rng, m)
+        text = np.concatenate([mutate(rng, pat, int(rng.integers(0, k + 2))), rand_text(rng, 30)])
+        ends, errs = orc.myers_prefix(text, pat, k)
+        # brute force: plain edit distance of pat against text[:j]
+        for j in range(1, min(len(text), m + k + 1) + 1):
+            d = list(range(m + 1))
+            for c in text[:j]:
+                nd = [d[0] + 1]
+                for i in range(1, m + 1):
+                    nd.append(min(d[i - 1] + (pat[i - 1] != c), d[i] + 1, nd[i - 1] + 1))
+                d = nd
+            if d[m] <= k:
+                assert j in ends.tolist() and errs[ends.tolist().index(j)] == d[m]
+            else:
+                assert j not in ends.tolist()
