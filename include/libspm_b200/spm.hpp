@@ -6,6 +6,10 @@
 //   spm::myers_matcher{needle, k}            libspm/libspm/matcher/myers_matcher.hpp:19-60
 //   spm::restorable_myers_matcher{needle,k}  libspm/libspm/matcher/myers_matcher_restorable.hpp:110-156
 //   spm::restorable_shiftor_matcher{needle}  libspm/libspm/matcher/shiftor_matcher_restorable.hpp:89-129
+//   spm::pigeonhole_matcher{needle(s), rate} libspm/libspm/matcher/pigeonhole_matcher.hpp:129-243
+//   seqan2::PigeonholeSeedOnlyPosition       libspm/libspm/matcher/pigeonhole_matcher.hpp:41-57
+//   spm::restorable_myers_prefix_matcher{needle,k}  libspm/libspm/matcher/myers_prefix_matcher_restorable.hpp:117-160
+//   spm::filtered_myers_matcher{needles, k}  (new: myers_matcher's hit list through the pigeonhole seed filter)
 //   matcher(haystack, callback)              libspm/libspm/matcher/seqan_pattern_base.hpp:40-52
 //   spm::window_size / capture / restore     libspm/libspm/matcher/concept.hpp:27-102
 //   spm::window_matcher / restorable_matcher libspm/libspm/matcher/concept.hpp:126-148
@@ -21,6 +25,7 @@
 #pragma once
 
 #include <concepts>
+#include <cstddef>
 #include <cstdint>
 #include <memory>
 #include <ranges>
@@ -31,6 +36,21 @@
 #include <vector>
 
 #include "../spmb.h"
+
+namespace seqan2 {
+// what pigeonhole_matcher::position() returns (pigeonhole_matcher.hpp:41-57)
+struct PigeonholeSeedOnlyPosition {
+    std::ptrdiff_t index{};  // needle index
+    std::ptrdiff_t offset{}; // offset of the seed inside that needle
+    std::ptrdiff_t count{};  // seed length q
+    friend constexpr bool operator==(PigeonholeSeedOnlyPosition const &, PigeonholeSeedOnlyPosition const &) noexcept = default;
+    template <typename stream_t>
+    friend stream_t &operator<<(stream_t &stream, PigeonholeSeedOnlyPosition const &me) {
+        stream << "<" << me.index << ", " << me.offset << ", " << me.count << ">";
+        return stream;
+    }
+};
+} // namespace seqan2
 
 namespace spm {
 
@@ -402,6 +422,170 @@ public:
 };
 template <std::ranges::viewable_range N>
 restorable_shiftor_matcher(N &&) -> restorable_shiftor_matcher<std::views::all_t<N>>;
+
+// anchored (prefix) Myers: the needle against prefixes of the haystack, scan clamped to m+k+1 symbols
+// (myers_prefix_matcher_restorable.hpp:47-61); window_size = m + k (:151-153)
+template <std::ranges::random_access_range needle_t = std::vector<dna4>>
+class restorable_myers_prefix_matcher
+    : public restorable_base<restorable_myers_prefix_matcher<needle_t>, SPMB_ALG_MYERS_PREFIX> {
+public:
+    restorable_myers_prefix_matcher() = delete;
+    template <std::ranges::viewable_range N, std::unsigned_integral error_count_t>
+        requires (!std::same_as<std::remove_cvref_t<N>, restorable_myers_prefix_matcher>)
+    explicit restorable_myers_prefix_matcher(N &&needle, error_count_t const error_count) {
+        this->build_restorable(std::forward<N>(needle), error_count);
+    }
+};
+template <std::ranges::viewable_range N, std::unsigned_integral E>
+restorable_myers_prefix_matcher(N &&, E) -> restorable_myers_prefix_matcher<std::views::all_t<N>>;
+
+// ------------------------------------------------------------------------------------------
+// needle sets: pigeonhole seed matcher and the filtered Myers search built on it
+// ------------------------------------------------------------------------------------------
+namespace detail {
+template <typename R>
+concept needle_set = std::ranges::input_range<R> && std::ranges::input_range<std::ranges::range_reference_t<R>>;
+
+struct needle_pack {
+    std::vector<std::uint8_t> ranks;
+    std::vector<std::uint32_t> lengths;
+    template <typename R>
+    void add(R &&needle) {
+        std::uint32_t n = 0;
+        for (auto &&v : needle) { ranks.push_back(rank_of(v)); ++n; }
+        lengths.push_back(n);
+    }
+};
+} // namespace detail
+
+template <std::ranges::random_access_range needle_t = std::vector<dna4>>
+class pigeonhole_matcher {
+    std::shared_ptr<spmb_pattern> _pattern;
+    double _error_rate{};
+    seqan2::PigeonholeSeedOnlyPosition _position{};
+
+    void build(const detail::needle_pack &np) {
+        auto &d = detail::device();
+        spmb_pattern *p = nullptr;
+        detail::check(spmb_pigeonhole_create(d.ctx, np.ranks.data(), np.lengths.data(),
+                                             static_cast<std::uint32_t>(np.lengths.size()), _error_rate, &p),
+                      d.ctx, "spmb_pigeonhole_create");
+        _pattern.reset(p, detail::pattern_deleter{});
+    }
+
+    template <typename callback_t>
+    void replay(callback_t &&callback) {
+        auto &d = detail::device();
+        const spmb_hit *h = spmb_hits_data(d.hits);
+        const std::uint64_t n = spmb_hits_count(d.hits);
+        const std::size_t q = window_size();
+        for (std::uint64_t i = 0; i < n; ++i) {
+            const std::size_t e = static_cast<std::size_t>(h[i].end);
+            _position = {static_cast<std::ptrdiff_t>(h[i].pattern_id), static_cast<std::ptrdiff_t>(h[i].reserved),
+                         static_cast<std::ptrdiff_t>(q)};
+            callback(hit_cursor{e - q, e, 0, h[i].seq_id, h[i].pattern_id});
+        }
+    }
+
+public:
+    pigeonhole_matcher() = delete;
+    // one needle (pigeonhole_matcher.hpp:157-167)
+    template <std::ranges::viewable_range N>
+        requires (!std::same_as<std::remove_cvref_t<N>, pigeonhole_matcher> && !detail::needle_set<N>)
+    explicit pigeonhole_matcher(N &&needle, double error_rate = 0.0) : _error_rate{error_rate} {
+        detail::needle_pack np;
+        np.add(std::forward<N>(needle));
+        build(np);
+    }
+    // several needles (pigeonhole_matcher.hpp:169-180)
+    template <std::ranges::viewable_range M>
+        requires (!std::same_as<std::remove_cvref_t<M>, pigeonhole_matcher> && detail::needle_set<M>)
+    explicit pigeonhole_matcher(M &&multi_needle, double error_rate = 0.0) : _error_rate{error_rate} {
+        detail::needle_pack np;
+        for (auto &&needle : multi_needle) np.add(needle);
+        build(np);
+    }
+
+    // {needle index, needle offset, q} of the seed the running callback is looking at (:182-184)
+    constexpr auto position() const noexcept { return _position; }
+
+    template <std::ranges::viewable_range haystack_t, typename callback_t>
+        requires (!std::same_as<std::remove_cvref_t<haystack_t>, device_sequence>)
+    void operator()(haystack_t &&haystack, callback_t &&callback) {
+        auto &d = detail::device();
+        detail::rank_buffer<haystack_t> buf{std::forward<haystack_t>(haystack)};
+        detail::check(spmb_search_host(d.ctx, buf.ptr, buf.n, _pattern.get(), d.hits), d.ctx, "spmb_search_host");
+        replay(std::forward<callback_t>(callback));
+    }
+    template <typename callback_t>
+    void operator()(const device_sequence &haystack, callback_t &&callback) {
+        auto &d = detail::device();
+        detail::check(spmb_search(d.ctx, haystack.handle(), _pattern.get(), d.hits), d.ctx, "spmb_search");
+        replay(std::forward<callback_t>(callback));
+    }
+
+    // the q-gram length (pigeonhole_matcher.hpp:200-202)
+    std::size_t window_size() const noexcept { return spmb_pattern_window_size(_pattern.get()); }
+};
+template <std::ranges::viewable_range N> requires (!detail::needle_set<N>)
+pigeonhole_matcher(N &&) -> pigeonhole_matcher<std::views::all_t<N>>;
+template <std::ranges::viewable_range N> requires (!detail::needle_set<N>)
+pigeonhole_matcher(N &&, double) -> pigeonhole_matcher<std::views::all_t<N>>;
+template <std::ranges::viewable_range M> requires detail::needle_set<M>
+pigeonhole_matcher(M &&) -> pigeonhole_matcher<std::views::all_t<std::ranges::range_reference_t<M>>>;
+template <std::ranges::viewable_range M> requires detail::needle_set<M>
+pigeonhole_matcher(M &&, double) -> pigeonhole_matcher<std::views::all_t<std::ranges::range_reference_t<M>>>;
+
+// myers_matcher's hit list for a whole needle set in one pass: pigeonhole seed filter + windowed
+// verification on the device (SPMB_ALG_MYERS_FILTERED).  callback(cursor): cursor.pattern_id() names the
+// needle, hits ascend per needle.
+class filtered_myers_matcher {
+    std::shared_ptr<spmb_pattern> _pattern;
+    std::vector<std::uint32_t> _lengths;
+    std::size_t _errors{0};
+
+    template <typename callback_t>
+    void replay(callback_t &&callback) const {
+        auto &d = detail::device();
+        const spmb_hit *h = spmb_hits_data(d.hits);
+        const std::uint64_t n = spmb_hits_count(d.hits);
+        for (std::uint64_t i = 0; i < n; ++i) {
+            const std::size_t e = static_cast<std::size_t>(h[i].end), m = _lengths[h[i].pattern_id];
+            callback(hit_cursor{e >= m ? e - m : 0, e, h[i].errors, h[i].seq_id, h[i].pattern_id});
+        }
+    }
+
+public:
+    filtered_myers_matcher() = delete;
+    template <std::ranges::viewable_range M> requires detail::needle_set<M>
+    explicit filtered_myers_matcher(M &&multi_needle, std::size_t max_error_count = 0) : _errors{max_error_count} {
+        detail::needle_pack np;
+        for (auto &&needle : multi_needle) np.add(needle);
+        _lengths = np.lengths;
+        auto &d = detail::device();
+        spmb_pattern *p = nullptr;
+        detail::check(spmb_pattern_set_create(d.ctx, SPMB_ALG_MYERS_FILTERED, np.ranks.data(), np.lengths.data(),
+                                              static_cast<std::uint32_t>(np.lengths.size()),
+                                              static_cast<std::uint32_t>(max_error_count), &p),
+                      d.ctx, "spmb_pattern_set_create");
+        _pattern.reset(p, detail::pattern_deleter{});
+    }
+    template <std::ranges::viewable_range haystack_t, typename callback_t>
+        requires (!std::same_as<std::remove_cvref_t<haystack_t>, device_sequence>)
+    void operator()(haystack_t &&haystack, callback_t &&callback) {
+        auto &d = detail::device();
+        detail::rank_buffer<haystack_t> buf{std::forward<haystack_t>(haystack)};
+        detail::check(spmb_search_host(d.ctx, buf.ptr, buf.n, _pattern.get(), d.hits), d.ctx, "spmb_search_host");
+        replay(std::forward<callback_t>(callback));
+    }
+    template <typename callback_t>
+    void operator()(const device_sequence &haystack, callback_t &&callback) {
+        auto &d = detail::device();
+        detail::check(spmb_search(d.ctx, haystack.handle(), _pattern.get(), d.hits), d.ctx, "spmb_search");
+        replay(std::forward<callback_t>(callback));
+    }
+    std::size_t window_size() const noexcept { return spmb_pattern_window_size(_pattern.get()); }
+};
 
 } // namespace spm
 

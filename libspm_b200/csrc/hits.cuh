@@ -1,4 +1,4 @@
-// hits.cuh -- the compacted hit buffer kernels append to.
+// hits.cuh -- the compacted hit buffer kernels append to, and the device-side ordering of long hit lists.
 #pragma once
 #include <stdint.h>
 #include "../../include/spmb.h"
@@ -8,3 +8,56 @@ struct HitSink {
     unsigned long long *count;  // total hits produced (may exceed cap: finish() then grows and re-runs)
     unsigned long long cap;
 };
+
+// Hit order from atomics is nondeterministic; short lists are sorted on the host, long ones here:
+// every hit becomes one 64-bit key (its fields concatenated in comparison order), CUB radix-sorts
+// (key, index) pairs over the bits in use, and the hits are gathered in that order.  For the filtered
+// Myers path the last key field is the error count and runs that agree on everything else collapse
+// to their first element (the smallest error count = the exact one, pigeon.cuh).
+struct HitKeySpec {
+    int field[4]; // 0 pattern_id, 1 seq_id, 2 end, 3 errors, 4 reserved; -1 = unused
+    int bits[4];
+};
+
+__device__ __forceinline__ unsigned long long hit_field(const spmb_hit &h, int f)
+{
+    switch (f) {
+    case 0: return h.pattern_id;
+    case 1: return h.seq_id;
+    case 2: return h.end;
+    case 3: return h.errors;
+    default: return h.reserved;
+    }
+}
+
+__global__ void hit_keys_kernel(const spmb_hit *__restrict__ hits, uint32_t n, HitKeySpec spec,
+                                unsigned long long *__restrict__ keys, uint32_t *__restrict__ idx)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const spmb_hit h = hits[i];
+    unsigned long long k = 0;
+#pragma unroll
+    for (int f = 0; f < 4; ++f)
+        if (spec.field[f] >= 0) k = (k << spec.bits[f]) | hit_field(h, spec.field[f]);
+    keys[i] = k;
+    idx[i] = i;
+}
+
+// flag[i] = 1 if sorted element i starts a new run of keys >> drop_bits
+__global__ void hit_flags_kernel(const unsigned long long *__restrict__ keys, uint32_t n, int drop_bits,
+                                 uint8_t *__restrict__ flag)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    flag[i] = (i == 0) || ((keys[i] >> drop_bits) != (keys[i - 1] >> drop_bits));
+}
+
+__global__ void hit_gather_kernel(const spmb_hit *__restrict__ hits, const uint32_t *__restrict__ idx,
+                                  const uint32_t *__restrict__ n_ptr, uint32_t n_max, spmb_hit *__restrict__ out)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t n = n_ptr ? min(*n_ptr, n_max) : n_max;
+    if (i >= n) return;
+    out[i] = hits[idx[i]];
+}

@@ -38,6 +38,9 @@
 // shared host/device definitions
 // ------------------------------------------------------------------------------------------
 // q-gram key: symbol j of the q-gram at bits [63-2j, 62-2j] of (hi:lo), zero below (kq <= 32 symbols)
+// bitmap hash of a key (lo already masked to the key): two IMADs, FMA-pipe work that co-issues with the
+// ALU-pipe shifts of the scan loop (tools/ubench_pipes.cu: LOP3:IMAD 1:1 runs at 2 x 18.4 T/s, whereas
+// IMAD.HI is half rate and stalls the ALU pipe -- so no multiply-high anywhere in the loop)
 SPMB_HD uint32_t pg_h1(uint32_t hi, uint32_t lo) { return hi * 0x9E3779B1u + lo * 0x85EBCA77u; }
 SPMB_HD uint32_t pg_h2(uint32_t hi, uint32_t lo)
 {
@@ -118,8 +121,10 @@ struct PigeonHost {
         const uint32_t tmask = (1u << T) - 1;
         for (size_t u = 0; u < ukeys.size(); ++u) {
             const uint32_t hi = (uint32_t)(ukeys[u] >> 32), lo = (uint32_t)ukeys[u];
-            const uint32_t x = pg_h1(hi, lo) >> (32 - B);
+            const uint32_t h = kq > 16 ? pg_h1(hi, lo) : hi * 0x9E3779B1u;
+            const uint32_t x = h >> (32 - B);
             bitmap[x >> 5] |= 0x80000000u >> (x & 31);
+            if (kq > 16) bitmap[x >> 5] |= 0x80000000u >> (h & 31); // second bit, same word (wide keys)
             uint32_t slot = pg_h2(hi, lo) >> (32 - T);
             while (tab_val[slot] != PG_EMPTY) slot = (slot + 1) & tmask;
             tab_key[slot] = ukeys[u];
@@ -182,7 +187,52 @@ __device__ __forceinline__ void pg_window(const uint2 cur, const uint2 nxt, uint
     lo = __funnelshift_l(c, b, s);
 }
 
-// WIDE: kq > 16 (the key has a low word).  One warp = one unit of 32 rows x 32 chunks.
+// exact lookup of one bitmap survivor: (row R, chunk c, symbol j) -> candidate if its q-gram is a seed
+template <int MODE>
+__device__ __forceinline__ void pg_survivor(const PigeonFilterArgs &a, uint64_t st, uint32_t ln, uint32_t c, uint32_t j)
+{
+    const uint32_t RL = a.lay.row_len, rl32 = RL >> 5;
+    const uint64_t R = st * 32 + ln;
+    const uint32_t col = c * 32 + j;
+    bool ok;
+    if (MODE == SPMB_MODE_PLAIN) ok = (R * RL + col + a.pg.q <= a.lay.n);
+    else ok = (R * RL < a.lay.n) && (col + a.pg.q <= a.row_len[R]);
+    if (!ok) return;
+    const uint2 *__restrict__ lp = a.lanes;
+    const uint2 cur = __ldg(lp + (st * rl32 + c) * 32 + ln);
+    uint2 nxt;
+    if (c + 1 < rl32) nxt = __ldg(lp + (st * rl32 + c + 1) * 32 + ln);
+    else if (MODE == SPMB_MODE_PLAIN)
+        nxt = (ln < 31) ? __ldg(lp + (st * rl32) * 32 + ln + 1) : __ldg(lp + ((st + 1) * rl32) * 32);
+    else nxt = make_uint2(0, 0);
+    uint32_t hi, lo;
+    pg_window(cur, nxt, j, hi, lo);
+    hi &= a.pg.himask; lo &= a.pg.lomask;
+    const unsigned long long key = ((unsigned long long)hi << 32) | lo;
+    const uint32_t tmask = (1u << a.pg.T) - 1;
+    uint32_t slot = pg_h2(hi, lo) >> (32 - a.pg.T);
+    for (;;) {
+        const uint32_t v = __ldg(a.pg.tab_val + slot);
+        if (v == PG_EMPTY) return;
+        if (__ldg(a.pg.tab_key + slot) == key) {
+            const unsigned long long idx = atomicAdd(a.cand_count, 1ull);
+            if (idx < a.cand_cap) {
+                PigeonCand cd;
+                cd.pos = R * RL + col; cd.u = v; cd.pad = 0;
+                a.cand[idx] = cd;
+            }
+            return;
+        }
+        slot = (slot + 1) & tmask;
+    }
+}
+
+// WIDE: kq > 16 (the key has a low word; the bitmap then holds two bits per q-gram, both in one word).
+// One warp = one unit of 32 rows x 32 chunks.  Bitmap survivors (a few per 1024 positions) are not
+// looked up by the lane that found them -- that loop would run as long as the unluckiest lane of the
+// warp -- but parked in a per-warp queue in shared memory and drained 32 at a time, one per lane.
+static const uint32_t PG_QCAP = 256; // queue entries per warp (uint16: chunk-in-unit | lane | symbol)
+
 template <int MODE, bool WIDE>
 __global__ void __launch_bounds__(1024, 1) pigeon_filter_kernel(PigeonFilterArgs a)
 {
@@ -192,26 +242,31 @@ __global__ void __launch_bounds__(1024, 1) pigeon_filter_kernel(PigeonFilterArgs
     __syncthreads();
 
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint16_t *s_q = reinterpret_cast<uint16_t *>(s_bits + n_words) + warp * PG_QCAP;
     const uint32_t RL = a.lay.row_len, rl32 = RL >> 5;
     const uint32_t segs = (rl32 + 31) >> 5;
     const uint64_t n_units = (a.st1 - a.st0) * segs;
     const uint32_t shift = 32 - a.pg.B;
     const uint32_t himask = a.pg.himask, lomask = a.pg.lomask;
+    const uint32_t lt_mask = (1u << lane) - 1u;
     const uint2 *__restrict__ lp = a.lanes;
 
     for (uint64_t unit = (uint64_t)blockIdx.x * 32 + warp; unit < n_units; unit += (uint64_t)gridDim.x * 32) {
         const uint64_t st = a.st0 + unit / segs;
         const uint32_t c0 = (uint32_t)(unit % segs) * 32;
         const uint32_t c1 = min(c0 + 32, rl32);
-        const uint64_t R = st * 32 + lane;
-        uint32_t rlen = RL; // valid symbols of this row
-        if (MODE == SPMB_MODE_PLAIN) {
-            const uint64_t r0 = R * RL;
-            if (r0 >= a.lay.n) rlen = 0;
-            // a row of the plain text continues in the next one: only the text end limits a q-gram
-        } else {
-            rlen = (R * RL < a.lay.n) ? a.row_len[R] : 0;
-        }
+        uint32_t qn = 0; // queue fill, warp-uniform
+        auto drain = [&]() {
+            __syncwarp();
+            for (uint32_t b = 0; b < qn; b += 32) {
+                if (b + lane < qn) {
+                    const uint32_t e = s_q[b + lane];
+                    pg_survivor<MODE>(a, st, (e >> 5) & 31u, c0 + (e >> 10), e & 31u);
+                }
+            }
+            __syncwarp();
+            qn = 0;
+        };
         const uint2 *rowp = lp + (st * rl32) * 32 + lane;
         uint2 cur = __ldg(rowp + (uint64_t)c0 * 32);
         for (uint32_t c = c0; c < c1; ++c) {
@@ -225,45 +280,32 @@ __global__ void __launch_bounds__(1024, 1) pigeon_filter_kernel(PigeonFilterArgs
             for (int j = 0; j < 32; ++j) {
                 uint32_t hi, lo;
                 pg_window(cur, nxt, j, hi, lo);
-                uint32_t h;
-                if (WIDE) h = pg_h1(hi, lo & lomask);
-                else h = (hi & himask) * 0x9E3779B1u;
-                const uint32_t x = h >> shift;
-                const uint32_t word = s_bits[x >> 5];
-                acc = __funnelshift_l(word << (x & 31u), acc, 1); // position j ends at bit 31-j
-            }
-            // ---- survivors of the bitmap: exact table in L2 ----
-            while (acc) {
-                const uint32_t j = __clz(acc);
-                acc &= ~(0x80000000u >> j);
-                const uint32_t col = c * 32 + j;
-                bool ok;
-                if (MODE == SPMB_MODE_PLAIN) ok = rlen && (R * RL + col + a.pg.q <= a.lay.n);
-                else ok = (col + a.pg.q <= rlen);
-                if (!ok) continue;
-                uint32_t hi, lo;
-                pg_window(cur, nxt, j, hi, lo);
-                hi &= himask; lo &= lomask;
-                const unsigned long long key = ((unsigned long long)hi << 32) | lo;
-                const uint32_t tmask = (1u << a.pg.T) - 1;
-                uint32_t slot = pg_h2(hi, lo) >> (32 - a.pg.T);
-                for (;;) {
-                    const uint32_t v = __ldg(a.pg.tab_val + slot);
-                    if (v == PG_EMPTY) break;
-                    if (__ldg(a.pg.tab_key + slot) == key) {
-                        const unsigned long long idx = atomicAdd(a.cand_count, 1ull);
-                        if (idx < a.cand_cap) {
-                            PigeonCand cd;
-                            cd.pos = R * RL + col; cd.u = v; cd.pad = 0;
-                            a.cand[idx] = cd;
-                        }
-                        break;
-                    }
-                    slot = (slot + 1) & tmask;
+                if (WIDE) {
+                    const uint32_t h = pg_h1(hi, lo & lomask);
+                    const uint32_t word = s_bits[h >> (shift + 5)];
+                    const uint32_t t = (word << ((h >> shift) & 31u)) & (word << (h & 31u));
+                    acc = __funnelshift_l(t, acc, 1); // position j ends at bit 31-j
+                } else {
+                    const uint32_t h = (hi & himask) * 0x9E3779B1u;
+                    const uint32_t word = s_bits[h >> (shift + 5)];
+                    acc = __funnelshift_l(word << ((h >> shift) & 31u), acc, 1);
                 }
+            }
+            // ---- park the survivors of this chunk ----
+            uint32_t m = __ballot_sync(0xffffffffu, acc != 0);
+            while (m) {
+                if (qn + 32 > PG_QCAP) drain();
+                if (acc) {
+                    const uint32_t j = __clz(acc);
+                    acc &= ~(0x80000000u >> j);
+                    s_q[qn + __popc(m & lt_mask)] = (uint16_t)(((c - c0) << 10) | (lane << 5) | j);
+                }
+                qn += __popc(m);
+                m = __ballot_sync(0xffffffffu, acc != 0);
             }
             cur = nxt;
         }
+        drain();
     }
 }
 

@@ -4,10 +4,13 @@
 // There is no CPU search path in this file: if no CUDA device is present every entry point
 // fails with SPMB_ERR_NO_DEVICE.
 #include <cuda_runtime.h>
+#include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
+#include <cub/device/device_select.cuh>
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -736,11 +739,11 @@ static cudaError_t launch_filter_kernel(spmb_context *ctx, const PigeonFilterArg
 {
     static bool attr_set[16] = {false};
     if (ctx->device < 16 && !attr_set[ctx->device]) {
-        cudaError_t e = cudaFuncSetAttribute(pigeon_filter_kernel<MODE, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(pigeon_filter_kernel<MODE, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024 + 32 * PG_QCAP * 2);
         if (e != cudaSuccess) return e;
         attr_set[ctx->device] = true;
     } else if (ctx->device >= 16) {
-        cudaFuncSetAttribute(pigeon_filter_kernel<MODE, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
+        cudaFuncSetAttribute(pigeon_filter_kernel<MODE, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024 + 32 * PG_QCAP * 2);
     }
     pigeon_filter_kernel<MODE, WIDE><<<grid, 1024, smem, ctx->stream>>>(fa);
     return cudaGetLastError();
@@ -791,7 +794,7 @@ static int enqueue_filtered(spmb_context *ctx, const spmb_store *s, const spmb_p
     const uint64_t units = (fa.st1 - fa.st0) * segs;
     unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)ctx->sm_count, (units + 31) / 32);
     if (grid == 0) grid = 1;
-    const size_t smem = (size_t)4 << (p->pg.B - 5);
+    const size_t smem = ((size_t)4 << (p->pg.B - 5)) + 32 * PG_QCAP * 2; // bitmap + per-warp survivor queues
     cudaError_t e = (p->pg.kq > 16) ? launch_filter_kernel<MODE, true>(ctx, fa, grid, smem)
                                     : launch_filter_kernel<MODE, false>(ctx, fa, grid, smem);
     if (e != cudaSuccess) return set_err(ctx, SPMB_ERR_CUDA, "pigeon_filter_kernel launch", e);
@@ -955,11 +958,93 @@ static void hits_order(std::vector<spmb_hit> &v, int alg)
     std::sort(v.begin(), v.end(), hit_less);
 }
 
+static int bits_for(unsigned long long max_value)
+{
+    int b = 1;
+    while (b < 64 && (max_value >> b)) ++b;
+    return b;
+}
+
+// Long hit lists are ordered (and, for the filtered Myers path, deduplicated) on the device before
+// they travel: returns SPMB_OK with *done = true and `out` filled, or *done = false when the list is
+// short or its key does not fit 64 bits (the caller then sorts on the host).
+static int hits_order_device(spmb_context *ctx, spmb_hits *h, const spmb_store *s, const spmb_pattern *p,
+                             unsigned long long cnt, uint64_t n_seq, std::vector<spmb_hit> &out, bool *done)
+{
+    *done = false;
+    if (cnt < 4096 || cnt >= (1ull << 31)) return SPMB_OK;
+    const int alg = p->alg;
+    const uint64_t max_end = (s->lay.mode == SPMB_MODE_PLAIN) ? s->lay.n : s->lay.row_len;
+    HitKeySpec spec;
+    const int b_pat = bits_for(p->n_pat), b_seq = n_seq > 1 ? bits_for(n_seq) : 0, b_end = bits_for(max_end);
+    int drop = 0;
+    if (alg == SPMB_ALG_PIGEONHOLE) {
+        spec = {{1, 2, 0, 4}, {b_seq, b_end, b_pat, bits_for(p->max_m)}};
+    } else {
+        const int b_err = bits_for(p->k);
+        spec = {{0, 1, 2, 3}, {b_pat, b_seq, b_end, b_err}};
+        if (alg == SPMB_ALG_MYERS_FILTERED) drop = b_err;
+    }
+    if (b_seq == 0) { for (int f = 0; f < 4; ++f) if (spec.field[f] == 1) spec.field[f] = -1; }
+    int total_bits = 0;
+    for (int f = 0; f < 4; ++f) if (spec.field[f] >= 0) total_bits += spec.bits[f];
+    if (total_bits > 64) return SPMB_OK;
+
+    cudaStream_t sm = ctx->stream;
+    const uint32_t n = (uint32_t)cnt;
+    unsigned long long *k0 = nullptr, *k1 = nullptr;
+    uint32_t *i0 = nullptr, *i1 = nullptr, *isel = nullptr, *d_nsel = nullptr;
+    uint8_t *flag = nullptr;
+    spmb_hit *d_out = nullptr;
+    void *tmp = nullptr;
+    cudaError_t e = cudaSuccess;
+#define HCU(call) do { if (e == cudaSuccess) e = (call); } while (0)
+    HCU(cudaMallocAsync(&k0, n * 8ull, sm)); HCU(cudaMallocAsync(&k1, n * 8ull, sm));
+    HCU(cudaMallocAsync(&i0, n * 4ull, sm)); HCU(cudaMallocAsync(&i1, n * 4ull, sm));
+    HCU(cudaMallocAsync(&d_out, n * sizeof(spmb_hit), sm));
+    const unsigned blocks = (n + 255) / 256;
+    if (e == cudaSuccess) hit_keys_kernel<<<blocks, 256, 0, sm>>>(h->d_hits, n, spec, k0, i0);
+    size_t tb = 0, tb2 = 0;
+    HCU(cub::DeviceRadixSort::SortPairs(nullptr, tb, k0, k1, i0, i1, (int)n, 0, total_bits, sm));
+    if (drop) {
+        HCU(cudaMallocAsync(&flag, n, sm)); HCU(cudaMallocAsync(&isel, n * 4ull, sm)); HCU(cudaMallocAsync(&d_nsel, 4, sm));
+        HCU(cub::DeviceSelect::Flagged(nullptr, tb2, i1, flag, isel, d_nsel, (int)n, sm));
+    }
+    HCU(cudaMallocAsync(&tmp, std::max(tb, tb2) + 16, sm));
+    HCU(cub::DeviceRadixSort::SortPairs(tmp, tb, k0, k1, i0, i1, (int)n, 0, total_bits, sm));
+    uint32_t n_out = n;
+    if (drop) {
+        if (e == cudaSuccess) hit_flags_kernel<<<blocks, 256, 0, sm>>>(k1, n, drop, flag);
+        HCU(cub::DeviceSelect::Flagged(tmp, tb2, i1, flag, isel, d_nsel, (int)n, sm));
+        if (e == cudaSuccess) hit_gather_kernel<<<blocks, 256, 0, sm>>>(h->d_hits, isel, d_nsel, n, d_out);
+        HCU(cudaMemcpyAsync(&ctx->h_count[4], d_nsel, 4, cudaMemcpyDeviceToHost, sm));
+        HCU(cudaStreamSynchronize(sm));
+        if (e == cudaSuccess) n_out = (uint32_t)(ctx->h_count[4] & 0xffffffffu);
+        ctx->launches += 5;
+    } else {
+        if (e == cudaSuccess) hit_gather_kernel<<<blocks, 256, 0, sm>>>(h->d_hits, i1, nullptr, n, d_out);
+        ctx->launches += 3;
+    }
+    HCU(cudaGetLastError());
+    if (e == cudaSuccess) {
+        out.resize(n_out);
+        if (n_out) HCU(cudaMemcpyAsync(out.data(), d_out, n_out * sizeof(spmb_hit), cudaMemcpyDeviceToHost, sm));
+        HCU(cudaStreamSynchronize(sm));
+    }
+#undef HCU
+    cudaFreeAsync(k0, sm); cudaFreeAsync(k1, sm); cudaFreeAsync(i0, sm); cudaFreeAsync(i1, sm); cudaFreeAsync(isel, sm);
+    cudaFreeAsync(d_nsel, sm); cudaFreeAsync(flag, sm); cudaFreeAsync(d_out, sm); cudaFreeAsync(tmp, sm);
+    if (e != cudaSuccess) { cudaGetLastError(); return set_err(ctx, SPMB_ERR_CUDA, "device hit sort", e); }
+    *done = true;
+    return SPMB_OK;
+}
+
 // wait for the enqueued search, regrow the hit / candidate buffers and re-run (`again`) while one of
 // them overflowed (the counters keep counting, so they hold the exact sizes needed), then copy the raw
 // hits to `raw`
 template <class Again>
-static int hits_collect(spmb_context *ctx, spmb_hits *h, std::vector<spmb_hit> &raw, Again again)
+static int hits_collect(spmb_context *ctx, spmb_hits *h, std::vector<spmb_hit> &raw, Again again,
+                        unsigned long long *count_only = nullptr)
 {
     for (int attempt = 0; attempt < 5; ++attempt) {
         CU(cudaMemcpyAsync(ctx->h_count, h->d_count, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
@@ -967,6 +1052,7 @@ static int hits_collect(spmb_context *ctx, spmb_hits *h, std::vector<spmb_hit> &
         const unsigned long long cnt = ctx->h_count[0];
         const unsigned long long cand = std::max(ctx->h_count[1], ctx->h_count[2]);
         if (cnt <= h->cap && cand <= h->cand_cap) {
+            if (count_only) { *count_only = cnt; return SPMB_OK; } // the hits stay on the device for now
             raw.resize(cnt);
             if (cnt) {
                 CU(cudaMemcpyAsync(raw.data(), h->d_hits, cnt * sizeof(spmb_hit), cudaMemcpyDeviceToHost, ctx->stream));
@@ -991,9 +1077,21 @@ extern "C" int spmb_search_finish(spmb_context *ctx, spmb_hits *h)
     ENTER(ctx);
     const spmb_store *s = h->pend_store;
     const spmb_pattern *p = h->pend_pat;
-    int rc = hits_collect(ctx, h, h->host, [&]() { return enqueue_search(ctx, s, p, h); });
+    unsigned long long cnt = 0;
+    int rc = hits_collect(ctx, h, h->host, [&]() { return enqueue_search(ctx, s, p, h); }, &cnt);
     if (rc) return rc;
-    hits_order(h->host, p->alg);
+    bool done = false;
+    const uint64_t n_seq = (s->lay.mode == SPMB_MODE_PLAIN) ? 1 : s->lay.n_st * 32;
+    rc = hits_order_device(ctx, h, s, p, cnt, n_seq, h->host, &done);
+    if (rc) return rc;
+    if (!done) {
+        h->host.resize(cnt);
+        if (cnt) {
+            CU(cudaMemcpyAsync(h->host.data(), h->d_hits, cnt * sizeof(spmb_hit), cudaMemcpyDeviceToHost, ctx->stream));
+            CU(cudaStreamSynchronize(ctx->stream));
+        }
+        hits_order(h->host, p->alg);
+    }
     h->count = h->host.size();
     h->pend_store = nullptr;
     h->pend_pat = nullptr;

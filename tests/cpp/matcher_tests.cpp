@@ -4,6 +4,7 @@
 //   /root/reference/test/api/libspm/matcher/shiftor_matcher_test.cpp:19-52
 //   /root/reference/test/api/libspm/matcher/myers_matcher_test.cpp:19-53
 //   /root/reference/test/api/libspm/matcher/myers_matcher_restorable_test.cpp:19-74
+//   /root/reference/test/api/libspm/matcher/pigeonhole_matcher_test.cpp:19-86
 // (GoogleTest swapped for tests/cpp/mini_test.hpp).  Runs on the GPU box only.
 #include <algorithm>
 #include <cstddef>
@@ -139,6 +140,76 @@ MINI_TEST(empty_needle_and_haystack) {
     auto m2 = spm::shiftor_matcher{needle};
     m2(none, [&](auto const &) { ++calls; });
     EXPECT_EQ(calls, 0);
+}
+
+// ---- pigeonhole_matcher_test.cpp:19-86 ----
+using needle_position_t = seqan2::PigeonholeSeedOnlyPosition;
+static const sequence_t needle2 = "TGACTAGCAC"_dna4;
+static const std::vector<sequence_t> multi_needle{needle, needle2};
+static const std::vector<std::size_t> expected_multi_positions{3, 8, 9, 14, 19, 20, 25, 30, 31, 36};
+static const std::vector<needle_position_t> expected_needle_positions{{1, 0, 5}, {1, 5, 5}, {0, 0, 5}, {1, 0, 5}, {1, 5, 5},
+                                                                      {0, 0, 5}, {1, 0, 5}, {1, 5, 5}, {0, 0, 5}, {1, 0, 5}};
+
+MINI_TEST(pigeonhole_concept_and_window_size) {
+    double errors = 0.0;
+    auto matcher = spm::pigeonhole_matcher{needle, errors};
+    EXPECT_TRUE(spm::window_matcher<decltype(matcher)>);
+    EXPECT_EQ(spm::window_size(matcher), std::ranges::size(needle));
+}
+
+MINI_TEST(pigeonhole_dna4_pattern) {
+    auto matcher = spm::pigeonhole_matcher{needle, 0.0};
+    std::vector<std::size_t> actual_positions{};
+    matcher(haystack, [&](auto const &finder) { actual_positions.push_back(seqan2::beginPosition(finder)); });
+    EXPECT_TRUE(std::ranges::equal(actual_positions, exact_begin));
+}
+
+MINI_TEST(pigeonhole_dna4_multi_pattern) {
+    auto matcher = spm::pigeonhole_matcher{multi_needle, 0.0};
+    std::vector<std::size_t> actual_positions{};
+    matcher(haystack, [&](auto const &finder) { actual_positions.push_back(seqan2::beginPosition(finder)); });
+    EXPECT_TRUE(std::ranges::equal(actual_positions, expected_multi_positions));
+}
+
+MINI_TEST(pigeonhole_dna4_multi_pattern_position) {
+    auto matcher = spm::pigeonhole_matcher{multi_needle, 0.0};
+    std::vector<needle_position_t> actual_needle_positions{};
+    matcher(haystack, [&](auto const &) { actual_needle_positions.push_back(matcher.position()); });
+    EXPECT_TRUE(actual_needle_positions == expected_needle_positions);
+}
+
+// the prefix matcher has no test in the reference: needle vs haystack prefixes
+MINI_TEST(restorable_myers_prefix_matcher_anchored) {
+    auto matcher = spm::restorable_myers_prefix_matcher{"ACGTGA"_dna4, 1u};
+    EXPECT_TRUE(spm::restorable_matcher<decltype(matcher)>);
+    EXPECT_EQ(spm::window_size(matcher), 7u);
+    std::vector<std::size_t> ends{};
+    std::vector<unsigned> errs{};
+    matcher(haystack, [&](auto const &f) { ends.push_back(seqan2::endPosition(f)); errs.push_back(f.errors()); });
+    EXPECT_TRUE(std::ranges::equal(ends, std::vector<std::size_t>{5, 6, 7}));
+    EXPECT_TRUE(std::ranges::equal(errs, std::vector<unsigned>{1, 0, 1}));
+    // anchored: the same needle does not match at haystack position 11 unless the haystack starts there
+    auto m2 = spm::restorable_myers_prefix_matcher{"GCACG"_dna4, 0u};
+    int calls = 0;
+    m2(haystack, [&](auto const &) { ++calls; });
+    EXPECT_EQ(calls, 0);
+}
+
+MINI_TEST(filtered_myers_matcher_equals_myers_matcher) {
+    // 3 copies of a 48-symbol needle with 0, 1 and 2 edits inside filler
+    sequence_t pat = "ACGTTGCAAGCTTAGGCTAACGGTACCATGGATCCAGTCAAGTCCGTA"_dna4;
+    sequence_t text = "TTTTTTTTTT"_dna4;
+    auto app = [&](sequence_t const &x) { text.insert(text.end(), x.begin(), x.end()); };
+    app(pat); app("GGGGGGGGGGGG"_dna4);
+    sequence_t one = pat; one[20] = "T"_dna4[0]; app(one); app("CCCCCCCCCCCCC"_dna4);
+    sequence_t two = pat; two.erase(two.begin() + 7); two[30] = "A"_dna4[0]; app(two); app("AAAAAAAAAA"_dna4);
+    std::vector<std::pair<std::size_t, unsigned>> a{}, b{};
+    auto direct = spm::myers_matcher{pat, 2};
+    direct(text, [&](auto const &f) { a.emplace_back(seqan2::endPosition(f), f.errors()); });
+    auto filtered = spm::filtered_myers_matcher{std::vector<sequence_t>{pat}, 2};
+    filtered(text, [&](auto const &f) { b.emplace_back(seqan2::endPosition(f), f.errors()); });
+    EXPECT_TRUE(!a.empty());
+    EXPECT_TRUE(a == b);
 }
 
 int main() { return mini::run_all(); }

@@ -33,3 +33,26 @@ with torch.cuda.stream(stream):
             h = sp.search(ctx, st, p, hits)
         print("myers hits", len(h), "row_len", st.row_len)
         st.close()
+    if what == "filter":
+        # C5 shape: 10k patterns of 100 bp, k=3 through the pigeonhole seed filter
+        n_f = n_exact
+        t = synth.text_device(n_f, 5, dev)
+        rng = np.random.default_rng(5)
+        offs = np.sort(rng.integers(0, n_f - 200, size=10_000))
+        idx = (torch.from_numpy(offs).to(dev)[:, None] + torch.arange(100, device=dev)[None, :]).reshape(-1)
+        cut = t[idx].cpu().numpy().reshape(-1, 100)
+        pats = [synth.mutate(rng, c, int(rng.integers(0, 4))) for c in cut]
+        pats = [np.concatenate([q, c[:max(0, 97 - len(q))]]) for q, c in zip(pats, cut)]
+        st = sp.Store.from_device(ctx, t.data_ptr(), n_f); ctx.sync(); del t
+        p = sp.Pattern(ctx, sp.ALG_MYERS_FILTERED, pats, 3)
+        import time
+        for _ in range(4):
+            h = sp.search(ctx, st, p, hits)
+        print("filtered hits", len(h), p.filter_info)
+        for _ in range(3):
+            torch.cuda.synchronize(); t0 = time.perf_counter()
+            sp.search_launch(ctx, st, p, hits); t1 = time.perf_counter()
+            ctx.sync(); t2 = time.perf_counter()
+            h = sp.search_finish(ctx, hits); t3 = time.perf_counter()
+            print(f"launch {1e3*(t1-t0):.3f} ms  kernels {1e3*(t2-t1):.3f} ms  finish {1e3*(t3-t2):.3f} ms  total {1e3*(t3-t0):.3f} ms")
+        st.close()

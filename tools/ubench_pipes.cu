@@ -11,10 +11,12 @@
 #define LOP(a, b, c) asm volatile("lop3.b32 %0, %0, %1, %2, 0x6a;" : "+r"(a) : "r"(b), "r"(c))
 #define IMAD(a, b, c) asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a) : "r"(b), "r"(c))
 // 64-bit result {hi,lo} = a*b + {chi,clo}
+#define IMADHI(a, b, c) asm volatile("mad.hi.u32 %0, %0, %1, %2;" : "+r"(a) : "r"(b), "r"(c))
 #define IMADW(lo, hi, a, b) asm volatile("{ .reg .u64 t, u; mov.b64 u, {%0,%1}; mad.wide.u32 t, %2, %3, u; mov.b64 {%0,%1}, t; }" : "+r"(lo), "+r"(hi) : "r"(a), "r"(b))
 
 // MODE: 0 LOP3 only | 1 IMAD only | 2 IMAD.WIDE only | 3 LOP3:IMAD 4:1 | 4 LOP3:IMAD.WIDE 4:1
 //       5 LOP3:IMAD.WIDE 3:1 | 6 LOP3:IMAD.WIDE 2:1 | 7 LOP3:IMAD 2:1 | 8 LOP3:IMAD 1:1
+//       9 IMAD.HI only | 10 LOP3:IMAD.HI 1:1 | 11 LOP3:IMAD:IMAD.HI 2:1:1
 template <int MODE>
 __global__ void __launch_bounds__(256) k(uint32_t *out, int iters, uint32_t two, uint32_t k1)
 {
@@ -39,6 +41,9 @@ __global__ void __launch_bounds__(256) k(uint32_t *out, int iters, uint32_t two,
                 if (MODE == 6) { LOP(a[j], k1, a[(j + 1) & 7]); LOP(a[j], k1, a[(j + 2) & 7]); IMADW(b[j], h[j], b[j], two); }
                 if (MODE == 7) { LOP(a[j], k1, a[(j + 1) & 7]); LOP(a[j], k1, a[(j + 2) & 7]); IMAD(b[j], two, k1); }
                 if (MODE == 8) { LOP(a[j], k1, a[(j + 1) & 7]); IMAD(b[j], two, k1); }
+                if (MODE == 9) { IMADHI(b[j], k1, two); }
+                if (MODE == 10) { LOP(a[j], k1, a[(j + 1) & 7]); IMADHI(b[j], k1, two); }
+                if (MODE == 11) { LOP(a[j], k1, a[(j + 1) & 7]); LOP(a[j], k1, a[(j + 2) & 7]); IMAD(h[j], two, k1); IMADHI(b[j], k1, two); }
             }
         }
     }
@@ -49,10 +54,11 @@ __global__ void __launch_bounds__(256) k(uint32_t *out, int iters, uint32_t two,
 }
 
 struct Mode { const char *name; int lop, fma; };
-static const Mode modes[9] = {
+static const Mode modes[12] = {
     {"LOP3 only", 1, 0}, {"IMAD only", 0, 1}, {"IMAD.WIDE only", 0, 1}, {"LOP3:IMAD 4:1", 4, 1},
     {"LOP3:IMAD.WIDE 4:1", 4, 1}, {"LOP3:IMAD.WIDE 3:1", 3, 1}, {"LOP3:IMAD.WIDE 2:1", 2, 1},
-    {"LOP3:IMAD 2:1", 2, 1}, {"LOP3:IMAD 1:1", 1, 1}};
+    {"LOP3:IMAD 2:1", 2, 1}, {"LOP3:IMAD 1:1", 1, 1}, {"IMAD.HI only", 0, 1}, {"LOP3:IMAD.HI 1:1", 1, 1},
+    {"LOP3:IMAD:IMAD.HI 2:1:1", 2, 2}};
 
 template <int MODE>
 static void run(uint32_t *out, int sms)
@@ -95,6 +101,9 @@ int main()
     run<6>(out, p.multiProcessorCount);
     run<7>(out, p.multiProcessorCount);
     run<8>(out, p.multiProcessorCount);
+    run<9>(out, p.multiProcessorCount);
+    run<10>(out, p.multiProcessorCount);
+    run<11>(out, p.multiProcessorCount);
     cudaError_t e = cudaDeviceSynchronize();
     printf("status: %s\n", cudaGetErrorString(e));
     return e != cudaSuccess;
