@@ -1,6 +1,6 @@
 // pack.cuh -- kernels that build / read the packed store.
 //   pack_kernel<ByteSource>     1-byte dna4 ranks (a std::vector<spm::dna4> image)  -> strided bit planes
-//   pack_kernel<JournalSource>  base store + journal events (a14)                   -> planes of the derived sequence
+//   pack_chunks_kernel<JournalSource>  base store + journal events (a14)            -> planes (+ lane chunks) of the derived sequence
 //   unpack_kernel               planes -> 1-byte ranks (round trips, tests)
 // One CTA (32 warps) produces one 1024-column block (8 KB); warp w owns thread-row w of the
 // block (32 columns).  Lane b reads the 32 symbols of its row for those columns, the warp
@@ -49,12 +49,46 @@ struct ByteSource {
     }
 };
 
+// ---- lane-chunk helpers: one uint2 = 32 consecutive symbols of a row, 2 bits each, first symbol in the
+// top bits of .x (the layout lanes_kernel derives from the planes; the Myers and filter kernels read it) ----
+__device__ __forceinline__ uint2 spmb_chunk(const uint2 *__restrict__ lanes, uint32_t rl32, uint64_t R, uint32_t c)
+{
+    return __ldg(lanes + ((R >> 5) * rl32 + c) * 32 + ((uint32_t)R & 31u));
+}
+
+// 32 symbols starting o symbols into the 64-symbol window (w0, w1), 0 <= o < 32
+__device__ __forceinline__ uint2 spmb_chunk_shift(const uint2 w0, const uint2 w1, uint32_t o)
+{
+    const uint32_t a = o < 16 ? w0.x : w0.y;
+    const uint32_t b = o < 16 ? w0.y : w1.x;
+    const uint32_t c = o < 16 ? w1.x : w1.y;
+    const uint32_t sh = 2 * (o & 15u);
+    return make_uint2(__funnelshift_l(b, a, sh), __funnelshift_l(c, b, sh));
+}
+
+// the 32 symbols of a PLAIN store that start at absolute position p (any alignment; runs on into the
+// next row; positions past the end read the zero padding)
+__device__ __forceinline__ uint2 spmb_fetch32(const uint2 *__restrict__ lanes, const SpmbLayout &lay, uint64_t p)
+{
+    const uint32_t rl32 = lay.row_len >> 5;
+    const uint64_t R = spmb_div_rl(lay, p);
+    const uint32_t col = (uint32_t)(p - R * lay.row_len);
+    const uint32_t c = col >> 5, o = col & 31u;
+    const uint2 w0 = spmb_chunk(lanes, rl32, R, c);
+    if (o == 0) return w0;
+    const uint2 w1 = (c + 1 < rl32) ? spmb_chunk(lanes, rl32, R, c + 1) : spmb_chunk(lanes, rl32, R + 1, 0);
+    return spmb_chunk_shift(w0, w1, o);
+}
+
 // journaled sequence: derived position d -> base symbol or inserted symbol.
 // ev_der[i] = derived position where event i's inserted segment begins (device prefix sum);
 // blk_idx[b] = index of the last event with ev_der <= b*1024 (or -1): a lane finds its first
 // event with a <= 5-step search instead of a log2(n_ev)-deep chain of dependent loads.
+// A lane produces the 32 symbols of its row chunk as ONE packed word pair: every maximal run copied
+// from the base is one unaligned 32-symbol fetch from the base's lane chunks (two 8-byte loads), shifted
+// into place -- the base is read at ~2x its packed size instead of one 8-byte load per SYMBOL.
 struct JournalSource {
-    const uint2 *__restrict__ base_planes;
+    const uint2 *__restrict__ base_lanes;
     SpmbLayout base;
     const spmb_journal_event *__restrict__ ev;
     const uint64_t *__restrict__ ev_der;
@@ -63,11 +97,10 @@ struct JournalSource {
     uint64_t n_ev;
     uint64_t n; // derived length
 
-    __device__ __forceinline__ void load32(uint64_t d0, uint32_t (&w)[8]) const
+    __device__ __forceinline__ uint2 load_chunk(uint64_t d0) const
     {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) w[i] = 0;
-        if (d0 >= n) return;
+        unsigned long long out = 0;
+        if (d0 >= n) return make_uint2(0, 0);
         // last event with ev_der <= d0  (idx in [-1, n_ev-1])
         int64_t lo = blk_idx[d0 >> 10], hi = blk_idx[(d0 >> 10) + 1];
         while (lo < hi) {
@@ -82,21 +115,33 @@ struct JournalSource {
             const spmb_journal_event x = ev[e];
             seg_der = ev_der[e]; seg_ins = x.ins_len; seg_ref = x.ref_pos + x.del_len; seg_off = x.ins_off;
         }
-        for (int t = 0; t < 32; ++t) {
-            uint64_t d = d0 + t;
-            if (d >= n) break;
+        uint32_t t = 0;
+        const uint32_t t_end = (uint32_t)min((uint64_t)32, n - d0);
+        while (t < t_end) {
+            const uint64_t d = d0 + t;
             while (d >= next_der) { // enter the next event (several may start at the same d)
                 ++e;
                 const spmb_journal_event x = ev[e];
                 seg_der = next_der; seg_ins = x.ins_len; seg_ref = x.ref_pos + x.del_len; seg_off = x.ins_off;
                 next_der = (e + 1 < (int64_t)n_ev) ? ev_der[e + 1] : ~0ull;
             }
-            uint32_t s;
-            uint64_t o = d - seg_der;
-            if (e >= 0 && o < seg_ins) s = pool[seg_off + o] & 3u;
-            else s = spmb_symbol_at(base_planes, base, (e >= 0) ? seg_ref + (o - seg_ins) : d);
-            w[t >> 2] |= s << (8 * (t & 3));
+            const uint64_t o = d - seg_der;
+            if (e >= 0 && o < seg_ins) { // inside the inserted segment: one pool symbol
+                out |= (unsigned long long)(pool[seg_off + o] & 3u) << (62 - 2 * t);
+                ++t;
+                continue;
+            }
+            // a run copied from the base: up to the next event / the end of this chunk
+            const uint64_t b = (e >= 0) ? seg_ref + (o - seg_ins) : d;
+            uint32_t run = t_end - t;
+            if (next_der - d < run) run = (uint32_t)(next_der - d);
+            const uint2 w = spmb_fetch32(base_lanes, base, b);
+            unsigned long long W = ((unsigned long long)w.x << 32) | w.y;
+            if (run < 32) W &= ~(~0ull >> (2 * run)); // keep the first `run` symbols
+            out |= W >> (2 * t);
+            t += run;
         }
+        return make_uint2((uint32_t)(out >> 32), (uint32_t)out);
     }
 };
 
@@ -165,6 +210,38 @@ __global__ void __launch_bounds__(1024) pack_kernel(Source src, SpmbLayout lay, 
         if (lane == c) { myH = h; myL = l; }
     }
     // lane c holds column g0 + c  ->  permuted slot inside the block
+    tile[((lane >> 1) << 6) | (warp << 1) | (lane & 1)] = make_uint2(myH, myL);
+    __syncthreads();
+    planes[(uint64_t)blockIdx.x * 1024 + threadIdx.x] = tile[threadIdx.x];
+}
+
+// same block shape as pack_kernel for sources that deliver a lane chunk (32 symbols of a row, packed):
+// lane b holds row b's chunk, 64 ballots transpose it into the {H,L} column words; the chunk itself is
+// the store's lane-chunk layout, written as a by-product when `lanes_out` is given.
+template <class Source>
+__global__ void __launch_bounds__(1024) pack_chunks_kernel(Source src, SpmbLayout lay, uint2 *__restrict__ planes,
+                                                           uint2 *__restrict__ lanes_out)
+{
+    __shared__ uint2 tile[1024];
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint64_t g0 = (uint64_t)blockIdx.x * 1024 + warp * 32; // first column of this thread-row
+    uint2 w = make_uint2(0, 0);
+    if (g0 < lay.n_cols) {
+        uint64_t st = spmb_div_rl(lay, g0);
+        uint32_t col0 = (uint32_t)(g0 - st * lay.row_len);
+        uint64_t p0 = (st * 32 + lane) * (uint64_t)lay.row_len + col0;
+        if (p0 < lay.n) w = src.load_chunk(p0);
+    }
+    if (lanes_out) lanes_out[(g0 >> 5) * 32 + lane] = w; // group G = g0/32 (every group of the allocation is written)
+    uint32_t myH = 0, myL = 0;
+#pragma unroll
+    for (int c = 0; c < 32; ++c) {
+        const uint32_t word = c < 16 ? w.x : w.y;
+        const uint32_t s = word >> (30 - 2 * (c & 15));
+        uint32_t h = __ballot_sync(0xffffffffu, (s >> 1) & 1u);
+        uint32_t l = __ballot_sync(0xffffffffu, s & 1u);
+        if (lane == c) { myH = h; myL = l; }
+    }
     tile[((lane >> 1) << 6) | (warp << 1) | (lane & 1)] = make_uint2(myH, myL);
     __syncthreads();
     planes[(uint64_t)blockIdx.x * 1024 + threadIdx.x] = tile[threadIdx.x];

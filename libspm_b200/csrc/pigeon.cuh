@@ -33,6 +33,7 @@
 #include "layout.cuh"
 #include "hits.cuh"
 #include "myers.cuh"
+#include "pack.cuh"
 
 // ------------------------------------------------------------------------------------------
 // shared host/device definitions
@@ -139,12 +140,6 @@ struct PigeonHost {
 // ------------------------------------------------------------------------------------------
 // device: text access through the lane-chunk layout
 // ------------------------------------------------------------------------------------------
-// the chunk holding (row R, columns 32*c .. 32*c+31)
-__device__ __forceinline__ uint2 pg_chunk(const uint2 *__restrict__ lanes, uint32_t rl32, uint64_t R, uint32_t c)
-{
-    return __ldg(lanes + ((R >> 5) * rl32 + c) * 32 + ((uint32_t)R & 31u));
-}
-
 // symbol at (row R, column col) -- a sequential reader keeps the chunk of its current 32 columns
 struct PgReader {
     const uint2 *__restrict__ lanes;
@@ -155,7 +150,7 @@ struct PgReader {
     __device__ __forceinline__ uint32_t at(uint64_t row, uint32_t col)
     {
         const uint32_t cc = col >> 5;
-        if (row != R || cc != c) { R = row; c = cc; w = pg_chunk(lanes, rl32, row, cc); }
+        if (row != R || cc != c) { R = row; c = cc; w = spmb_chunk(lanes, rl32, row, cc); }
         const uint32_t j = col & 31u;
         const uint32_t word = j < 16 ? w.x : w.y;
         return (word >> (30 - 2 * (j & 15u))) & 3u;

@@ -311,6 +311,8 @@ extern "C" int spmb_store_create(spmb_context *ctx, const uint8_t *host_ranks, u
     return rc;
 }
 
+static int store_ensure_lanes(spmb_context *ctx, const spmb_store *s);
+
 extern "C" int spmb_store_create_journaled(spmb_context *ctx, const spmb_store *base,
                                            const spmb_journal_event *ev, uint64_t n_ev,
                                            const uint8_t *pool, uint64_t pool_len, uint32_t row_len,
@@ -377,8 +379,17 @@ extern "C" int spmb_store_create_journaled(spmb_context *ctx, const spmb_store *
     if (e == cudaSuccess) {
         journal_blkidx_kernel<<<(unsigned)((n_blk + 255) / 256), 256, 0, sm>>>(d_der, n_ev, n_blk, d_blk);
         ctx->launches++;
-        JournalSource src{base->planes, base->lay, d_ev, d_der, d_blk, d_pool, n_ev, n_der};
-        rc = store_pack(ctx, s, src);
+        // the gather reads the base through its lane chunks; the derived store gets its own for free
+        rc = store_ensure_lanes(ctx, base);
+        uint2 *l = nullptr;
+        if (rc == SPMB_OK && cudaMallocAsync(&l, s->bytes, sm) != cudaSuccess) { cudaGetLastError(); l = nullptr; }
+        if (rc == SPMB_OK) {
+            JournalSource src{base->lanes, base->lay, d_ev, d_der, d_blk, d_pool, n_ev, n_der};
+            pack_chunks_kernel<JournalSource><<<(unsigned)(s->lay.n_cols_alloc / 1024), 1024, 0, sm>>>(src, s->lay, s->planes, l);
+            ctx->launches++;
+            JCU(cudaGetLastError());
+            s->lanes = l;
+        }
     }
     cleanup();
     JCU(cudaStreamSynchronize(sm));
@@ -1255,13 +1266,32 @@ static int jst_prepare(spmb_context *ctx, spmb_jst *j, uint32_t W)
     cudaEvent_t e0, e1;
     CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
     CU(cudaEventRecord(e0, ctx->stream));
+    static const bool dbg = getenv("SPMB_DEBUG_TIMING") != nullptr;
+    const auto th0 = std::chrono::steady_clock::now();
+    auto lap = [&](const char *what) {
+        if (!dbg) return;
+        cudaStreamSynchronize(ctx->stream);
+        fprintf(stderr, "[spmb jst_prepare] %-28s %8.2f ms\n", what,
+                std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - th0).count());
+    };
     if (nw) {
         // windows sorted by length; a row holds len symbols + up to 31 pad columns for the Myers score delay
-        std::stable_sort(wins.begin(), wins.end(), [](const JstWindow &a, const JstWindow &b) { return a.len < b.len; });
+        {   // stable counting sort on the length (a comparison sort of millions of 32-byte records costs 0.2 s)
+            uint32_t max_len = 0;
+            for (const JstWindow &w : wins) max_len = std::max(max_len, w.len);
+            std::vector<uint64_t> start((size_t)max_len + 2, 0);
+            for (const JstWindow &w : wins) start[w.len + 1]++;
+            for (size_t i = 1; i < start.size(); ++i) start[i] += start[i - 1];
+            std::vector<JstWindow> sorted(nw);
+            for (const JstWindow &w : wins) sorted[start[w.len]++] = w;
+            wins.swap(sorted);
+        }
+        lap("sort windows by length");
         CU(cudaMalloc(&j->d_win, nw * sizeof(JstWindow)));
         CU(cudaMalloc(&j->d_win_vars, (j->flat.win_vars.size() + 1) * sizeof(uint32_t)));
         CU(cudaMemcpyAsync(j->d_win, wins.data(), nw * sizeof(JstWindow), cudaMemcpyHostToDevice, ctx->stream));
         CU(cudaMemcpyAsync(j->d_win_vars, j->flat.win_vars.data(), j->flat.win_vars.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+        lap("upload window table");
         uint64_t first = 0;
         while (first < nw) {
             // geometric length classes: a bucket takes every window up to 1.25x its shortest row
@@ -1288,8 +1318,10 @@ static int jst_prepare(spmb_context *ctx, spmb_jst *j, uint32_t W)
             CU(cudaMemcpy(b.store->row_own, ro.data(), rows * 4, cudaMemcpyHostToDevice));
             CU(cudaMemcpy(b.store->row_seq, rs.data(), rows * 4, cudaMemcpyHostToDevice));
             WindowSource src{j->ref->planes, j->ref->lay, j->d_var, j->d_pool, j->d_win + first, j->d_win_vars, count, b.store->lay};
+            lap("bucket rows up");
             rc = store_pack(ctx, b.store, src);
             if (rc) { cudaEventDestroy(e0); cudaEventDestroy(e1); return rc; }
+            lap("bucket pack kernel");
             first = last;
         }
     }

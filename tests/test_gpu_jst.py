@@ -103,3 +103,26 @@ def test_jst_edges(ctx):
     got = j0.search(sp.Pattern(ctx, sp.ALG_HORSPOOL, pat))
     assert len(got) == 3 * len(orc.exact_bruteforce(ref, pat))
     assert sorted(set(got["seq_id"].tolist())) == [0, 1, 2]
+
+
+@pytest.mark.parametrize("n_hap,n_var,seed", [(70, 600, 11), (130, 1500, 12)])
+def test_jst_filtered_myers_equals_oracle(ctx, n_hap, n_var, seed):
+    """the pigeonhole-filtered Myers path over JST branch windows (windows-mode filter + verification)."""
+    n_ref = 20_000
+    ref, var, pool, cov = make_jst(n_ref, n_var, n_hap, seed, p_snp=0.6, p_ins=0.2, max_indel=8, af_max=0.7)
+    rng = np.random.default_rng(seed + 100)
+    store = sp.Store.from_host(ctx, ref)
+    jst = sp.Jst(ctx, store, var, pool, cov, n_hap)
+    ev = var.astype(orc.EVENT_DTYPE)
+    for (m, k) in [(40, 2), (70, 4), (150, 2)]:
+        for src_h in (0, n_hap - 1, None):
+            seq = ref if src_h is None else orc.jst_haplotype(ref, ev, pool, cov, src_h)
+            s = int(rng.integers(0, len(seq) - m))
+            pat = mutate(rng, seq[s:s + m].copy(), 1)
+            p = sp.Pattern(ctx, sp.ALG_MYERS_FILTERED, [pat], k)
+            assert p.filter_info["filtered"]
+            got = jst.search(p)
+            want = orc.jst_search(sp.ALG_MYERS, ref, ev, pool, cov, n_hap, pat, k)
+            compare(got, want, f"filtered m={len(pat)} k={k} haps={n_hap}")
+            assert len(want) >= 1
+    jst.close()

@@ -56,3 +56,23 @@ with torch.cuda.stream(stream):
             h = sp.search_finish(ctx, hits); t3 = time.perf_counter()
             print(f"launch {1e3*(t1-t0):.3f} ms  kernels {1e3*(t2-t1):.3f} ms  finish {1e3*(t3-t2):.3f} ms  total {1e3*(t3-t0):.3f} ms")
         st.close()
+    if what == "e2e":
+        # per-call times of the headline e2e path: host ranks + journal -> hits
+        import time
+        n = n_exact
+        ref = synth.text_device(n, 2, dev)
+        ev, pool, kinds = synth.journal(n, 2)
+        pool = synth.finish_snps(ev, pool, kinds, ref[torch.from_numpy(ev["ref_pos"][kinds == 0].astype(np.int64)).to(dev)].cpu().numpy())
+        host = torch.empty(n, dtype=torch.uint8, pin_memory=True); host.copy_(ref); del ref
+        evp = torch.empty(ev.nbytes, dtype=torch.uint8, pin_memory=True); evp.numpy()[:] = ev.view(np.uint8)
+        evh = evp.numpy().view(sp.EVENT_DTYPE)
+        pp = torch.empty(pool.nbytes, dtype=torch.uint8, pin_memory=True); pp.numpy()[:] = pool
+        pat = np.random.default_rng(1).integers(0, 4, 64, dtype=np.uint8)
+        p = sp.Pattern(ctx, sp.ALG_SHIFTOR, pat)
+        for it in range(4):
+            torch.cuda.synchronize(); t0 = time.perf_counter()
+            b = sp.Store.from_host(ctx, host.numpy()); t1 = time.perf_counter()
+            j = b.journaled(evh, pp.numpy()); t2 = time.perf_counter()
+            h = sp.search(ctx, j, p, hits); t3 = time.perf_counter()
+            j.close(); b.close(); torch.cuda.synchronize(); t4 = time.perf_counter()
+            print(f"store_create {1e3*(t1-t0):.2f} ms ({n/(t1-t0)/1e9:.1f} GB/s)  journaled {1e3*(t2-t1):.2f} ms ({(ev.nbytes+pool.nbytes)/1e6:.0f} MB up)  search {1e3*(t3-t2):.3f} ms  close {1e3*(t4-t3):.2f} ms  total {1e3*(t4-t0):.2f} ms")
