@@ -9,9 +9,9 @@ HDRS := $(wildcard $(CSRC)/*.cuh) include/spmb.h
 
 all: $(LIB) oracle
 
-$(LIB): $(CSRC)/spmb_capi.cu $(HDRS)
+$(LIB): $(CSRC)/spmb_capi.cu $(CSRC)/ingest.cpp $(HDRS)
 	@mkdir -p libspm_b200/lib
-	$(NVCC) $(NVFLAGS) -o $@ $(CSRC)/spmb_capi.cu
+	$(NVCC) $(NVFLAGS) -o $@ $(CSRC)/spmb_capi.cu $(CSRC)/ingest.cpp -lz
 
 oracle:
 	$(MAKE) -C oracle

@@ -319,6 +319,8 @@ def run_ours(args):
         # ---------------- Myers k-error: C3 (m=100, k=4, 250 Mbp) ----------------
         if not args.no_myers:
             out["myers"] = bench_myers(sp, synth, torch, ctx, dev, stream, hits, args, rank, world, hbm_peak)
+        if not args.no_c5:
+            out["c5"] = bench_c5(sp, synth, torch, ctx, dev, stream, hits, args, rank, world)
         if rank == 0 and world == 1 and not args.no_small:
             out["small_configs"] = bench_small(sp, synth, torch, ctx, dev, stream, hits, args)
         out["setup_s"] = setup_s
@@ -389,6 +391,83 @@ def bench_myers(sp, synth, torch, ctx, dev, stream, hits, args, rank, world, hbm
                                "hits_match_gpu": bool(np.array_equal(g["end"], ce) and np.array_equal(g["errors"], cr))}
     store.close()
     del text, flush
+    torch.cuda.empty_cache()
+    return res
+
+
+def bench_c5(sp, synth, torch, ctx, dev, stream, hits, args, rank, world):
+    """configs[4]: 10k patterns of ~100 bp, k=3, over a 3 Gbp text, in ONE call through the pigeonhole seed
+    filter (SPMB_ALG_MYERS_FILTERED); with N ranks the SAME text is sharded (strong scaling), each rank
+    searching shard rank/N, no collective.  Cross-checked against the direct Myers kernel (16 patterns,
+    this rank's shard) and, at N=1, the CPU oracle on a 3 Mbp slice."""
+    n, n_pat, m, k = args.n_c5, 10_000, 100, 3
+    seed = synth.SEEDS["C5"]
+    text = synth.text_device(n, seed, dev)
+    rng = np.random.default_rng(seed)
+    offs = np.sort(rng.integers(0, n - 2 * m, size=n_pat))
+    idx = (torch.from_numpy(offs).to(dev)[:, None] + torch.arange(m, device=dev)[None, :]).reshape(-1)
+    cut = text[idx].cpu().numpy().reshape(n_pat, m)
+    pats = []
+    for i in range(n_pat):
+        q = synth.mutate(rng, cut[i], int(rng.integers(0, 6)))
+        if len(q) < 97:
+            q = np.concatenate([q, cut[i][:97 - len(q)]])
+        pats.append(q[:128])
+    store = sp.Store.from_device(ctx, text.data_ptr(), n)
+    ctx.sync()
+    pset = sp.Pattern(ctx, sp.ALG_MYERS_FILTERED, pats, k)
+    ctx.set_shard(rank, world)
+    sp.search(ctx, store, pset, hits)          # builds the lane-chunk copy of the store
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    total_ms, kern_ms, n_hits, launches = time_search(sp, torch, ctx, stream, store, pset, hits, args.steps, args.warmup)
+    if world > 1:
+        t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms = float(t.item())
+        c = torch.tensor([n_hits], device=dev, dtype=torch.int64)
+        dist.all_reduce(c)
+        n_hits = int(c.item())
+    got = sp.search(ctx, store, pset, hits)
+    step = n_pat // 16
+    sub = [pats[i] for i in range(0, n_pat, step)][:16]
+    direct = sp.Pattern(ctx, sp.ALG_MYERS, sub, k)
+    d = sp.search(ctx, store, direct, hits)
+    sel = got[np.isin(got["pattern_id"], np.arange(0, n_pat, step)[:16])]
+    same = bool(len(sel) == len(d) and np.array_equal(sel["pattern_id"] // step, d["pattern_id"]) and
+                np.array_equal(sel["end"], d["end"]) and np.array_equal(sel["errors"], d["errors"]))
+    ctx.set_shard(0, 1)
+    res = {"workload": f"C5: {n_pat} patterns of ~{m} bp, k={k}, over {n} bp in one call (seed filter + verification); "
+                       f"the text is sharded over {world} GPU(s)",
+           "value": n * args.steps / (total_ms * 1e-3) / 1e9, "unit": "Gbp/s (x 10k patterns)", "ms_per_step": total_ms / args.steps,
+           "kernels_ms": kern_ms, "cell_rate_T_per_s": n * n_pat * args.steps / (total_ms * 1e-3) / 1e12,
+           "hits": n_hits, "filter": pset.filter_info, "scaling": "strong",
+           "equals_direct_myers_kernel_16_patterns": same,
+           "text_gbytes_per_s_kernels": n / world * 0.25 / (kern_ms * 1e-3) / 1e9}
+    if rank == 0 and world == 1 and not args.no_cpu:
+        import oracle as orc
+        sl_n = 3_000_000
+        sl0 = int(offs[n_pat // 2]) // 1024 * 1024
+        sl0 = min(sl0, n - sl_n)
+        host = text[sl0:sl0 + sl_n].cpu().numpy()
+        st2 = sp.Store.from_host(ctx, host)
+        g2 = sp.search(ctx, st2, pset, hits)
+        ids = list(range(n_pat // 2 - 150, n_pat // 2 + 150))
+        threads = orc.use_all_cores()
+        t0 = time.perf_counter()
+        bad = 0
+        for i in ids:
+            _, we, wr = orc.search_mt(3, host, pats[i], k, threads=threads)
+            s2 = g2[g2["pattern_id"] == i]
+            bad += int(not (np.array_equal(s2["end"], we) and np.array_equal(s2["errors"], wr)))
+        cpu_s = time.perf_counter() - t0
+        res["cpu_baseline"] = {"value": sl_n * len(ids) / cpu_s / 1e12, "unit": "T cells/s", "cores": threads, "kind": "port",
+                               "sample": f"{len(ids)} patterns x a {sl_n} bp slice, oracle Myers, {threads} threads",
+                               "patterns_mismatching_gpu": bad}
+        st2.close()
+    store.close()
+    del text
     torch.cuda.empty_cache()
     return res
 
@@ -520,6 +599,8 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-myers", action="store_true")
     ap.add_argument("--no-small", action="store_true")
+    ap.add_argument("--no-c5", action="store_true")
+    ap.add_argument("--n-c5", type=int, default=3_000_000_000)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

@@ -218,6 +218,35 @@ int spmb_jst_search(spmb_context *ctx, spmb_jst *j, const spmb_pattern *p, spmb_
  * materialisation, [2] search kernels (reference + windows), [3] host expansion + sort */
 int spmb_jst_last_stats(const spmb_jst *j, uint64_t stats[4], double ms[4]);
 
+/* ---------------- ingest: FASTA / VCF -> store inputs ----------------
+ * Host-side readers for the formats of the reference's own test data (test/data/datasources.cmake:72-102:
+ * sim_ref_10Kb.fasta.gz + sim_ref_10Kb_{SNPs,SNP_INDELs}.vcf, whose shipped haplotype FASTAs are the known
+ * answer).  Plain or gzip files.  Characters outside ACGT(U) become rank 0 like seqan3::dna4 (counted).
+ * They need no device and no context. */
+typedef struct spmb_fasta spmb_fasta;
+int spmb_fasta_read(const char *path, spmb_fasta **out);
+int spmb_fasta_destroy(spmb_fasta *fa);
+uint64_t spmb_fasta_count(const spmb_fasta *fa);
+const char *spmb_fasta_name(const spmb_fasta *fa, uint64_t i);
+const uint8_t *spmb_fasta_ranks(const spmb_fasta *fa, uint64_t i, uint64_t *len); /* 1-byte ranks of record i */
+uint64_t spmb_fasta_unknown_symbols(const spmb_fasta *fa);
+/* VCF records of one contig (NULL = the contig of the first record) -> the arrays spmb_jst_create takes:
+ * one variant per ALT allele (common prefix with REF stripped: replace ref[pos, pos+del) by ins), sorted
+ * by position with insertions first on ties; coverage bit h = sample h/ploidy, allele h%ploidy carries
+ * it (GT a|b or a/b; '.' = reference).  Symbolic / breakend ALTs and records outside [0, ref_len) are
+ * skipped and counted (ref_len = 0: no bound check). */
+typedef struct spmb_vcf spmb_vcf;
+int spmb_vcf_read(const char *path, const char *contig, uint64_t ref_len, spmb_vcf **out);
+int spmb_vcf_destroy(spmb_vcf *v);
+uint64_t spmb_vcf_variant_count(const spmb_vcf *v);
+const spmb_journal_event *spmb_vcf_variants(const spmb_vcf *v);
+const uint8_t *spmb_vcf_pool(const spmb_vcf *v, uint64_t *len);
+const uint64_t *spmb_vcf_coverage(const spmb_vcf *v, uint32_t *words_per_row);
+uint32_t spmb_vcf_haplotype_count(const spmb_vcf *v);
+uint32_t spmb_vcf_sample_count(const spmb_vcf *v);
+const char *spmb_vcf_sample_name(const spmb_vcf *v, uint32_t i);
+int spmb_vcf_stats(const spmb_vcf *v, uint64_t stats[3]); /* [0] records of the contig, [1] skipped, [2] non-ACGT symbols */
+
 /* ---------------- measurement helpers ---------------- */
 /* INT32 ALU-pipe peak (LOP3 / IADD3 chains on all SMs), in 1e9 lane-instructions per second:
  * the roofline denominator for the Myers kernels. */

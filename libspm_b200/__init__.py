@@ -15,7 +15,7 @@ import numpy as np
 
 __all__ = ["Context", "Store", "Pattern", "Hits", "Stream", "Jst", "SpmbError", "HIT_DTYPE", "EVENT_DTYPE",
            "ALG_HORSPOOL", "ALG_SHIFTOR", "ALG_MYERS", "ALG_PIGEONHOLE", "ALG_MYERS_FILTERED",
-           "ALG_MYERS_PREFIX", "Pigeonhole", "search_anchored", "lib", "lib_path"]
+           "ALG_MYERS_PREFIX", "Pigeonhole", "search_anchored", "read_fasta", "read_vcf", "lib", "lib_path"]
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _SO = os.path.join(_HERE, "lib", "libspmb.so")
@@ -39,6 +39,10 @@ EXPORTS = [
     "spmb_search_host", "spmb_last_launch_count", "spmb_stream_create", "spmb_stream_destroy",
     "spmb_stream_feed", "spmb_stream_capture", "spmb_stream_restore", "spmb_measure_int_peak",
     "spmb_device_info", "spmb_jst_create", "spmb_jst_destroy", "spmb_jst_search", "spmb_jst_last_stats",
+    "spmb_fasta_read", "spmb_fasta_destroy", "spmb_fasta_count", "spmb_fasta_name", "spmb_fasta_ranks",
+    "spmb_fasta_unknown_symbols", "spmb_vcf_read", "spmb_vcf_destroy", "spmb_vcf_variant_count", "spmb_vcf_variants",
+    "spmb_vcf_pool", "spmb_vcf_coverage", "spmb_vcf_haplotype_count", "spmb_vcf_sample_count", "spmb_vcf_sample_name",
+    "spmb_vcf_stats",
     "spmb_context_set_shard", "spmb_pigeonhole_create", "spmb_pattern_filter_info", "spmb_search_anchored",
 ]
 
@@ -85,6 +89,22 @@ def lib():
             "spmb_store_read": (i32, [vp, vp, u64, u64, vp]),
             "spmb_pattern_create": (i32, [vp, i32, vp, u32, u32, pp]),
             "spmb_pattern_set_create": (i32, [vp, i32, vp, vp, u32, u32, pp]),
+            "spmb_fasta_read": (i32, [C.c_char_p, pp]),
+            "spmb_fasta_destroy": (i32, [vp]),
+            "spmb_fasta_count": (u64, [vp]),
+            "spmb_fasta_name": (C.c_char_p, [vp, u64]),
+            "spmb_fasta_ranks": (vp, [vp, u64, C.POINTER(u64)]),
+            "spmb_fasta_unknown_symbols": (u64, [vp]),
+            "spmb_vcf_read": (i32, [C.c_char_p, C.c_char_p, u64, pp]),
+            "spmb_vcf_destroy": (i32, [vp]),
+            "spmb_vcf_variant_count": (u64, [vp]),
+            "spmb_vcf_variants": (vp, [vp]),
+            "spmb_vcf_pool": (vp, [vp, C.POINTER(u64)]),
+            "spmb_vcf_coverage": (vp, [vp, C.POINTER(u32)]),
+            "spmb_vcf_haplotype_count": (u32, [vp]),
+            "spmb_vcf_sample_count": (u32, [vp]),
+            "spmb_vcf_sample_name": (C.c_char_p, [vp, u32]),
+            "spmb_vcf_stats": (i32, [vp, C.POINTER(u64 * 3)]),
             "spmb_pigeonhole_create": (i32, [vp, vp, vp, u32, C.c_double, pp]),
             "spmb_pattern_filter_info": (i32, [vp, C.POINTER(u32 * 5)]),
             "spmb_search_anchored": (i32, [vp, vp, vp, vp, u64, vp]),
@@ -466,3 +486,53 @@ class Jst:
             self.close()
         except Exception:
             pass
+
+
+def _np_from(ptr, n, dtype):
+    if not ptr or n == 0:
+        return np.zeros(0, dtype=dtype)
+    dt = np.dtype(dtype)
+    buf = (C.c_char * (n * dt.itemsize)).from_address(ptr)
+    return np.frombuffer(buf, dtype=dt, count=n).copy()
+
+
+def read_fasta(path: str):
+    """[(name, ranks)] of a FASTA file (plain or gzip) through spmb_fasta_read; also returns the number of
+    non-ACGT symbols (stored as rank 0 like seqan3::dna4)."""
+    h = C.c_void_p()
+    rc = lib().spmb_fasta_read(os.fsencode(path), C.byref(h))
+    if rc:
+        raise SpmbError(rc, "spmb_fasta_read", path)
+    try:
+        recs = []
+        for i in range(int(lib().spmb_fasta_count(h))):
+            n = C.c_uint64()
+            p = lib().spmb_fasta_ranks(h, i, C.byref(n))
+            recs.append((lib().spmb_fasta_name(h, i).decode(), _np_from(p, n.value, np.uint8)))
+        return recs, int(lib().spmb_fasta_unknown_symbols(h))
+    finally:
+        lib().spmb_fasta_destroy(h)
+
+
+def read_vcf(path: str, contig: str | None = None, ref_len: int = 0):
+    """VCF -> dict(variants[EVENT_DTYPE], pool, coverage[n_var, wpr], n_haplotypes, samples, stats): the
+    arguments of Jst(...) (spmb_vcf_read)."""
+    h = C.c_void_p()
+    rc = lib().spmb_vcf_read(os.fsencode(path), contig.encode() if contig else None, int(ref_len), C.byref(h))
+    if rc:
+        raise SpmbError(rc, "spmb_vcf_read", path)
+    try:
+        L = lib()
+        nv = int(L.spmb_vcf_variant_count(h))
+        pl, wpr = C.c_uint64(), C.c_uint32()
+        pool = _np_from(L.spmb_vcf_pool(h, C.byref(pl)), pl.value, np.uint8)
+        covp = L.spmb_vcf_coverage(h, C.byref(wpr))
+        cov = _np_from(covp, nv * wpr.value, np.uint64).reshape(nv, wpr.value)
+        st = (C.c_uint64 * 3)()
+        L.spmb_vcf_stats(h, C.byref(st))
+        return {"variants": _np_from(L.spmb_vcf_variants(h), nv, EVENT_DTYPE), "pool": pool, "coverage": cov,
+                "n_haplotypes": int(L.spmb_vcf_haplotype_count(h)),
+                "samples": [L.spmb_vcf_sample_name(h, i).decode() for i in range(int(L.spmb_vcf_sample_count(h)))],
+                "stats": {"records": st[0], "skipped": st[1], "unknown_symbols": st[2]}}
+    finally:
+        lib().spmb_vcf_destroy(h)
