@@ -916,8 +916,9 @@ static int enqueue_search(spmb_context *ctx, const spmb_store *s, const spmb_pat
         a.pattern_id = i;
         a.sink = sink;
         unsigned blocks = (unsigned)((a.n_tiles - a.tile0 + 255) / 256);
-        if (s->lay.mode == SPMB_MODE_PLAIN) exact_kernel<SPMB_MODE_PLAIN><<<blocks, 256, 0, ctx->stream>>>(a);
-        else exact_kernel<SPMB_MODE_WINDOWS><<<blocks, 256, 0, ctx->stream>>>(a);
+        const unsigned grid = std::min(blocks, 8u * (unsigned)ctx->sm_count); // grid-stride kernel
+        if (s->lay.mode == SPMB_MODE_PLAIN) exact_kernel<SPMB_MODE_PLAIN><<<grid, 256, 0, ctx->stream>>>(a);
+        else exact_kernel<SPMB_MODE_WINDOWS><<<grid, 256, 0, ctx->stream>>>(a);
         ctx->launches++;
         CU(cudaGetLastError());
     }

@@ -323,3 +323,40 @@ def test_journal_validation_errors(ctx):
     js = base.journaled(ev, pool)
     want = orc.journal_apply(ref, ev.astype(orc.EVENT_DTYPE), pool)
     assert np.array_equal(js.read(), want)
+
+
+@pytest.mark.parametrize("n,rl,m", [(170_000_000, 0, 64), (170_000_000, 1504, 20), (165_000_001, 4096, 7), (200_000_000, 8192, 33)])
+def test_exact_large_store(ctx, n, rl, m):
+    """stores of 165-200 Mbp (grid-stride exact kernel over many CTA tiles), unsharded and
+    sharded, against the multi-threaded oracle; needles planted across thread-row, row and super-tile seams."""
+    import torch
+    from libspm_b200 import synth
+    dev = torch.device("cuda", 0)
+    t = synth.text_device(n, n % 1000 + m, dev)
+    host = t.cpu().numpy()
+    rng = np.random.default_rng(m)
+    pat = rand_text(rng, m)
+    st = sp.Store.from_device(ctx, t.data_ptr(), n, rl)
+    ctx.sync()
+    RL = st.row_len
+    st.close()
+    spots = [0, n - m, RL - m // 2, 32 * RL - 3, 32 * RL - m + 1, 5 * 32 * RL + RL - 1, 1024 * 37 - 5, 256 * 32 * 9 - m // 2]
+    spots += [int(x) for x in rng.integers(0, n - m, size=200)]
+    for s_ in spots:
+        if 0 <= s_ <= n - m:
+            host[s_:s_ + m] = pat
+    t.copy_(torch.from_numpy(host))
+    st = sp.Store.from_device(ctx, t.data_ptr(), n, rl)
+    ctx.sync()
+    del t
+    _, want, _ = orc.search_mt(2, host, pat, 0)
+    p = sp.Pattern(ctx, sp.ALG_SHIFTOR, pat)
+    got = sp.search(ctx, st, p)
+    _diff(got["end"], want, f"large store n={n} rl={RL} m={m}")
+    parts = []
+    for sh in range(3):
+        ctx.set_shard(sh, 3)
+        parts.append(sp.search(ctx, st, p)["end"])
+    ctx.set_shard(0, 1)
+    _diff(np.sort(np.concatenate(parts)), want, f"large store sharded n={n} rl={RL} m={m}")
+    p.close(); st.close()
