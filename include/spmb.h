@@ -144,8 +144,9 @@ int spmb_pigeonhole_create(spmb_context *ctx, const uint8_t *ranks, const uint32
                            uint32_t n_needles, double error_rate, spmb_pattern **out);
 int spmb_pattern_destroy(spmb_pattern *p);
 /* figures of a SPMB_ALG_PIGEONHOLE / SPMB_ALG_MYERS_FILTERED pattern: info[0] q, [1] seeds,
- * [2] distinct q-grams, [3] log2 bitmap bits, [4] 1 if the filter is in use (0: q too short, the
- * direct Myers kernel runs instead) */
+ * [2] distinct q-grams, [3] log2 bitmap bits, [4] 0: q too short, the direct Myers kernel runs instead;
+ * else the sampling step of the scan (1, 2 or 4: every step-th text position is hashed against the
+ * step sub-seeds of each pigeonhole piece, q = piece length - step + 1) */
 int spmb_pattern_filter_info(const spmb_pattern *p, uint32_t info[5]);
 /* spm::window_size(matcher): m for the exact searchers (seqan_pattern_base.hpp:97-99),
  * m + k for Myers (myers_matcher.hpp:51-53) and the prefix matcher

@@ -290,7 +290,7 @@ class Pattern:
         info = (C.c_uint32 * 5)()
         lib().spmb_pattern_filter_info(self._h, C.byref(info))
         return {"q": info[0], "seeds": info[1], "distinct_qgrams": info[2], "log2_bitmap_bits": info[3],
-                "filtered": bool(info[4])}
+                "filtered": bool(info[4]), "step": info[4]}
 
     @property
     def count(self):

@@ -43,6 +43,12 @@
 // ALU-pipe shifts of the scan loop (tools/ubench_pipes.cu: LOP3:IMAD 1:1 runs at 2 x 18.4 T/s, whereas
 // IMAD.HI is half rate and stalls the ALU pipe -- so no multiply-high anywhere in the loop)
 SPMB_HD uint32_t pg_h1(uint32_t hi, uint32_t lo) { return hi * 0x9E3779B1u + lo * 0x85EBCA77u; }
+SPMB_HD uint32_t pg_h3(uint32_t hi, uint32_t lo) // second-level bitmap
+{
+    uint32_t h = (hi ^ 0x7F4A7C15u) * 0x85EBCA6Bu + (lo ^ 0x165667B1u) * 0xC2B2AE35u;
+    h ^= h >> 13;
+    return h * 0x27D4EB2Fu;
+}
 SPMB_HD uint32_t pg_h2(uint32_t hi, uint32_t lo)
 {
     uint32_t h = (hi * 0xC2B2AE3Du) ^ (lo * 0x27D4EB2Fu);
@@ -54,12 +60,13 @@ static const uint32_t PG_EMPTY = 0xffffffffu;
 
 struct PigeonDev {
     const uint32_t *bitmap;            // 2^B bits; bit for index x is bit 31-(x&31) of word x>>5
-    const unsigned long long *tab_key; // 2^T slots, linear probing
-    const uint32_t *tab_val;           // index of the unique q-gram, PG_EMPTY = free slot
+    const uint32_t *bitmap2;           // second level, 2^B2 bits in L2: one bit per q-gram, asked by bitmap survivors only
+    const ulonglong2 *tab;             // 2^T slots {key, value}, linear probing; value = index of the unique
+                                       // q-gram, PG_EMPTY = free slot
     const uint32_t *ufirst;            // [n_unique+1] -> range of seeds carrying that q-gram
     const uint32_t *seed_pat;          // needle index of each seed
     const uint32_t *seed_off;          // offset of the seed inside its needle
-    uint32_t q, kq, B, T;
+    uint32_t q, kq, B, T, B2;
     uint32_t himask, lomask;           // the top 2*kq bits of (hi:lo)
 };
 
@@ -73,10 +80,10 @@ struct PigeonCand {
 // host: seed table
 // ------------------------------------------------------------------------------------------
 struct PigeonHost {
-    uint32_t q = 0, kq = 0, B = 0, T = 0;
-    std::vector<uint32_t> bitmap;
-    std::vector<unsigned long long> tab_key;
-    std::vector<uint32_t> tab_val, ufirst, seed_pat, seed_off;
+    uint32_t q = 0, kq = 0, B = 0, T = 0, B2 = 0;
+    std::vector<uint32_t> bitmap, bitmap2;
+    std::vector<unsigned long long> tab; // {key, value} pairs
+    std::vector<uint32_t> ufirst, seed_pat, seed_off;
     uint64_t n_unique = 0;
 
     static unsigned long long key_of(const uint8_t *s, uint32_t kq)
@@ -117,8 +124,12 @@ struct PigeonHost {
         bitmap.assign((size_t)1 << (B - 5), 0);
         T = 4;
         while ((1ull << T) < n_unique * 2 + 1) ++T;
-        tab_key.assign((size_t)1 << T, 0);
-        tab_val.assign((size_t)1 << T, PG_EMPTY);
+        tab.assign((size_t)2 << T, 0);
+        for (size_t i = 0; i < ((size_t)1 << T); ++i) tab[2 * i + 1] = PG_EMPTY;
+        // second-level bitmap: <= 1/512 full, so that almost no first-level false positive reaches the table
+        B2 = 16;
+        while (B2 < 28 && (1ull << B2) < n_unique * 512) ++B2;
+        bitmap2.assign((size_t)1 << (B2 - 5), 0);
         const uint32_t tmask = (1u << T) - 1;
         for (size_t u = 0; u < ukeys.size(); ++u) {
             const uint32_t hi = (uint32_t)(ukeys[u] >> 32), lo = (uint32_t)ukeys[u];
@@ -126,10 +137,12 @@ struct PigeonHost {
             const uint32_t x = h >> (32 - B);
             bitmap[x >> 5] |= 0x80000000u >> (x & 31);
             if (kq > 16) bitmap[x >> 5] |= 0x80000000u >> (h & 31); // second bit, same word (wide keys)
+            const uint32_t x2 = pg_h3(hi, lo) >> (32 - B2);
+            bitmap2[x2 >> 5] |= 1u << (x2 & 31);
             uint32_t slot = pg_h2(hi, lo) >> (32 - T);
-            while (tab_val[slot] != PG_EMPTY) slot = (slot + 1) & tmask;
-            tab_key[slot] = ukeys[u];
-            tab_val[slot] = (uint32_t)u;
+            while (tab[2 * slot + 1] != PG_EMPTY) slot = (slot + 1) & tmask;
+            tab[2 * slot] = ukeys[u];
+            tab[2 * slot + 1] = (uint32_t)u;
         }
     }
 
@@ -203,13 +216,16 @@ __device__ __forceinline__ void pg_survivor(const PigeonFilterArgs &a, uint64_t 
     uint32_t hi, lo;
     pg_window(cur, nxt, j, hi, lo);
     hi &= a.pg.himask; lo &= a.pg.lomask;
+    const uint32_t x2 = pg_h3(hi, lo) >> (32 - a.pg.B2);
+    if (!((__ldg(a.pg.bitmap2 + (x2 >> 5)) >> (x2 & 31u)) & 1u)) return;
     const unsigned long long key = ((unsigned long long)hi << 32) | lo;
     const uint32_t tmask = (1u << a.pg.T) - 1;
     uint32_t slot = pg_h2(hi, lo) >> (32 - a.pg.T);
     for (;;) {
-        const uint32_t v = __ldg(a.pg.tab_val + slot);
+        const ulonglong2 ent = __ldg(a.pg.tab + slot);
+        const uint32_t v = (uint32_t)ent.y;
         if (v == PG_EMPTY) return;
-        if (__ldg(a.pg.tab_key + slot) == key) {
+        if (ent.x == key) {
             const unsigned long long idx = atomicAdd(a.cand_count, 1ull);
             if (idx < a.cand_cap) {
                 PigeonCand cd;
@@ -228,7 +244,11 @@ __device__ __forceinline__ void pg_survivor(const PigeonFilterArgs &a, uint64_t 
 // warp -- but parked in a per-warp queue in shared memory and drained 32 at a time, one per lane.
 static const uint32_t PG_QCAP = 256; // queue entries per warp (uint16: chunk-in-unit | lane | symbol)
 
-template <int MODE, bool WIDE>
+// STEP: only positions = 0 (mod STEP) of a row are looked at.  The filtered Myers path then indexes, for
+// every pigeonhole piece of length L, the STEP sub-seeds of length L-STEP+1 at offsets 0..STEP-1 inside it:
+// wherever the piece occurs, exactly one of them starts on a sampled position -- 1/STEP of the scan work
+// for STEP times the seeds.
+template <int MODE, bool WIDE, int STEP>
 __global__ void __launch_bounds__(1024, 1) pigeon_filter_kernel(PigeonFilterArgs a)
 {
     extern __shared__ uint32_t s_bits[];
@@ -272,31 +292,53 @@ __global__ void __launch_bounds__(1024, 1) pigeon_filter_kernel(PigeonFilterArgs
             else nxt = make_uint2(0, 0);
             uint32_t acc = 0;
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
+            for (int j = 0; j < 32; j += STEP) {
                 uint32_t hi, lo;
                 pg_window(cur, nxt, j, hi, lo);
                 if (WIDE) {
                     const uint32_t h = pg_h1(hi, lo & lomask);
                     const uint32_t word = s_bits[h >> (shift + 5)];
                     const uint32_t t = (word << ((h >> shift) & 31u)) & (word << (h & 31u));
-                    acc = __funnelshift_l(t, acc, 1); // position j ends at bit 31-j
+                    acc = __funnelshift_l(t, acc, 1); // sampled position k = j/STEP ends at bit 32/STEP-1-k
                 } else {
                     const uint32_t h = (hi & himask) * 0x9E3779B1u;
                     const uint32_t word = s_bits[h >> (shift + 5)];
                     acc = __funnelshift_l(word << ((h >> shift) & 31u), acc, 1);
                 }
             }
-            // ---- park the survivors of this chunk ----
-            uint32_t m = __ballot_sync(0xffffffffu, acc != 0);
-            while (m) {
-                if (qn + 32 > PG_QCAP) drain();
-                if (acc) {
-                    const uint32_t j = __clz(acc);
-                    acc &= ~(0x80000000u >> j);
-                    s_q[qn + __popc(m & lt_mask)] = (uint16_t)(((c - c0) << 10) | (lane << 5) | j);
+            // ---- park the survivors of this chunk: one warp prefix sum hands every lane its queue slots ----
+            const uint32_t cnt = __popc(acc);
+            uint32_t inc = cnt;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t up = __shfl_up_sync(0xffffffffu, inc, d);
+                if ((int)lane >= d) inc += up;
+            }
+            const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
+            if (total) {
+                if (qn + total > PG_QCAP) drain();
+                if (total <= PG_QCAP) {
+                    uint32_t slot = qn + inc - cnt;
+                    while (acc) {
+                        const uint32_t b = __clz(acc); // 32 - 32/STEP + k
+                        acc &= ~(0x80000000u >> b);
+                        s_q[slot++] = (uint16_t)(((c - c0) << 10) | (lane << 5) | ((b - (32 - 32 / STEP)) * STEP));
+                    }
+                    qn += total;
+                } else {
+                    // a chunk denser than the queue (low-complexity text): rounds of one survivor per lane
+                    uint32_t m = __ballot_sync(0xffffffffu, acc != 0);
+                    while (m) {
+                        if (qn + 32 > PG_QCAP) drain();
+                        if (acc) {
+                            const uint32_t b = __clz(acc);
+                            acc &= ~(0x80000000u >> b);
+                            s_q[qn + __popc(m & lt_mask)] = (uint16_t)(((c - c0) << 10) | (lane << 5) | ((b - (32 - 32 / STEP)) * STEP));
+                        }
+                        qn += __popc(m);
+                        m = __ballot_sync(0xffffffffu, acc != 0);
+                    }
                 }
-                qn += __popc(m);
-                m = __ballot_sync(0xffffffffu, acc != 0);
             }
             cur = nxt;
         }

@@ -101,9 +101,10 @@ struct spmb_pattern {
     // pigeonhole seed filter (SPMB_ALG_PIGEONHOLE, SPMB_ALG_MYERS_FILTERED)
     PigeonHost pg;
     bool filtered = false;            // the filter is in use (q long enough)
+    uint32_t filter_step = 1;         // text positions = 0 (mod step) are scanned (filtered Myers: 1, 2 or 4)
     uint32_t *d_off = nullptr;        // needle offsets into d_ranks
-    uint32_t *d_pg_bitmap = nullptr, *d_pg_val = nullptr, *d_pg_ufirst = nullptr, *d_pg_pat = nullptr, *d_pg_soff = nullptr;
-    unsigned long long *d_pg_key = nullptr;
+    uint32_t *d_pg_bitmap = nullptr, *d_pg_bitmap2 = nullptr, *d_pg_ufirst = nullptr, *d_pg_pat = nullptr, *d_pg_soff = nullptr;
+    unsigned long long *d_pg_tab = nullptr;
 };
 
 struct spmb_hits {
@@ -501,8 +502,8 @@ static cudaError_t pattern_upload_pigeon(spmb_context *ctx, spmb_pattern *p,
 {
     p->pg.build(p->ranks, p->off, seeds, q);
     cudaError_t e = upload_vec(ctx, &p->d_pg_bitmap, p->pg.bitmap);
-    if (e == cudaSuccess) e = upload_vec(ctx, &p->d_pg_key, p->pg.tab_key);
-    if (e == cudaSuccess) e = upload_vec(ctx, &p->d_pg_val, p->pg.tab_val);
+    if (e == cudaSuccess) e = upload_vec(ctx, &p->d_pg_bitmap2, p->pg.bitmap2);
+    if (e == cudaSuccess) e = upload_vec(ctx, &p->d_pg_tab, p->pg.tab);
     if (e == cudaSuccess) e = upload_vec(ctx, &p->d_pg_ufirst, p->pg.ufirst);
     if (e == cudaSuccess) e = upload_vec(ctx, &p->d_pg_pat, p->pg.seed_pat);
     if (e == cudaSuccess) e = upload_vec(ctx, &p->d_pg_soff, p->pg.seed_off);
@@ -555,11 +556,25 @@ static int pattern_build(spmb_context *ctx, int alg, const uint8_t *ranks, const
         std::vector<std::pair<uint32_t, uint32_t>> seeds;
         uint32_t q = 0;
         if (alg == SPMB_ALG_MYERS_FILTERED && p->min_m > 0) {
-            q = p->min_m / (k + 1);
-            if (q >= SPMB_FILTER_MIN_Q) {
+            const uint32_t L = p->min_m / (k + 1); // pigeonhole piece length
+            if (L >= SPMB_FILTER_MIN_Q) {
                 p->filtered = true;
+                // sample every step-th text position and index the step sub-seeds of length L-step+1 of each
+                // piece instead (pigeon.cuh): worth it while the sub-seeds stay selective (> 16 symbols) and
+                // the shared-memory bitmap (2^20 bits, two per seed) does not fill up
+                const uint64_t pieces = (uint64_t)n_pat * (k + 1);
+                uint32_t step = 1;
+                if (L >= 20 + 3 && pieces * 4 <= 200000) step = 4;
+                else if (L >= 18 + 1 && pieces * 2 <= 200000) step = 2;
+                if (const char *fs = getenv("SPMB_FILTER_STEP")) { // A/B switch for profiling
+                    const uint32_t v = (uint32_t)atoi(fs);
+                    if ((v == 1 || v == 2 || v == 4) && L >= 16 + v) step = v;
+                }
+                p->filter_step = step;
+                q = L - step + 1;
                 for (uint32_t i = 0; i < n_pat; ++i)
-                    for (uint32_t piece = 0; piece <= k; ++piece) seeds.push_back({i, piece * q});
+                    for (uint32_t piece = 0; piece <= k; ++piece)
+                        for (uint32_t d = 0; d < step; ++d) seeds.push_back({i, piece * L + d});
             }
         }
         if (mixed && !(p->filtered || alg == SPMB_ALG_MYERS_PREFIX)) {
@@ -624,7 +639,7 @@ extern "C" int spmb_pattern_filter_info(const spmb_pattern *p, uint32_t info[5])
 {
     if (!p || !info) return SPMB_ERR_ARG;
     info[0] = p->pg.q; info[1] = (uint32_t)p->pg.seed_pat.size(); info[2] = (uint32_t)p->pg.n_unique;
-    info[3] = p->pg.B; info[4] = p->filtered ? 1u : 0u;
+    info[3] = p->pg.B; info[4] = p->filtered ? p->filter_step : 0u;
     return SPMB_OK;
 }
 
@@ -642,7 +657,7 @@ extern "C" int spmb_pattern_destroy(spmb_pattern *p)
     cudaFree(p->d_eq);
     cudaFree(p->d_meta);
     cudaFree(p->d_off);
-    cudaFree(p->d_pg_bitmap); cudaFree(p->d_pg_key); cudaFree(p->d_pg_val);
+    cudaFree(p->d_pg_bitmap); cudaFree(p->d_pg_bitmap2); cudaFree(p->d_pg_tab);
     cudaFree(p->d_pg_ufirst); cudaFree(p->d_pg_pat); cudaFree(p->d_pg_soff);
     delete p;
     return SPMB_OK;
@@ -738,25 +753,25 @@ static cudaError_t launch_myers(spmb_context *ctx, const spmb_store *s, const sp
 static PigeonDev pigeon_dev(const spmb_pattern *p)
 {
     PigeonDev d;
-    d.bitmap = p->d_pg_bitmap; d.tab_key = p->d_pg_key; d.tab_val = p->d_pg_val;
+    d.bitmap = p->d_pg_bitmap; d.bitmap2 = p->d_pg_bitmap2; d.tab = reinterpret_cast<const ulonglong2 *>(p->d_pg_tab);
     d.ufirst = p->d_pg_ufirst; d.seed_pat = p->d_pg_pat; d.seed_off = p->d_pg_soff;
-    d.q = p->pg.q; d.kq = p->pg.kq; d.B = p->pg.B; d.T = p->pg.T;
+    d.q = p->pg.q; d.kq = p->pg.kq; d.B = p->pg.B; d.T = p->pg.T; d.B2 = p->pg.B2;
     d.himask = p->pg.himask(); d.lomask = p->pg.lomask();
     return d;
 }
 
-template <int MODE, bool WIDE>
+template <int MODE, bool WIDE, int STEP>
 static cudaError_t launch_filter_kernel(spmb_context *ctx, const PigeonFilterArgs &fa, unsigned grid, size_t smem)
 {
     static bool attr_set[16] = {false};
     if (ctx->device < 16 && !attr_set[ctx->device]) {
-        cudaError_t e = cudaFuncSetAttribute(pigeon_filter_kernel<MODE, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024 + 32 * PG_QCAP * 2);
+        cudaError_t e = cudaFuncSetAttribute(pigeon_filter_kernel<MODE, WIDE, STEP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024 + 32 * PG_QCAP * 2);
         if (e != cudaSuccess) return e;
         attr_set[ctx->device] = true;
     } else if (ctx->device >= 16) {
-        cudaFuncSetAttribute(pigeon_filter_kernel<MODE, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024 + 32 * PG_QCAP * 2);
+        cudaFuncSetAttribute(pigeon_filter_kernel<MODE, WIDE, STEP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024 + 32 * PG_QCAP * 2);
     }
-    pigeon_filter_kernel<MODE, WIDE><<<grid, 1024, smem, ctx->stream>>>(fa);
+    pigeon_filter_kernel<MODE, WIDE, STEP><<<grid, 1024, smem, ctx->stream>>>(fa);
     return cudaGetLastError();
 }
 
@@ -806,8 +821,11 @@ static int enqueue_filtered(spmb_context *ctx, const spmb_store *s, const spmb_p
     unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)ctx->sm_count, (units + 31) / 32);
     if (grid == 0) grid = 1;
     const size_t smem = ((size_t)4 << (p->pg.B - 5)) + 32 * PG_QCAP * 2; // bitmap + per-warp survivor queues
-    cudaError_t e = (p->pg.kq > 16) ? launch_filter_kernel<MODE, true>(ctx, fa, grid, smem)
-                                    : launch_filter_kernel<MODE, false>(ctx, fa, grid, smem);
+    cudaError_t e;
+    if (p->pg.kq <= 16) e = launch_filter_kernel<MODE, false, 1>(ctx, fa, grid, smem);
+    else if (p->filter_step == 4) e = launch_filter_kernel<MODE, true, 4>(ctx, fa, grid, smem);
+    else if (p->filter_step == 2) e = launch_filter_kernel<MODE, true, 2>(ctx, fa, grid, smem);
+    else e = launch_filter_kernel<MODE, true, 1>(ctx, fa, grid, smem);
     if (e != cudaSuccess) return set_err(ctx, SPMB_ERR_CUDA, "pigeon_filter_kernel launch", e);
     PigeonVerifyArgs va;
     va.lanes = s->lanes; va.lay = s->lay; va.pg = fa.pg;

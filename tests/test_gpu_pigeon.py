@@ -121,7 +121,26 @@ def test_filtered_myers_equals_direct(ctx, n, rl, m, k, n_pat):
     text[n - m + 3:] = pats[0][:m - 3]                # and one cut off by the text end
     st = sp.Store.from_host(ctx, text, rl)
     info = check_filtered(ctx, st, text, pats, k, f"n={n} rl={rl} m={m} k={k}")
-    assert info["filtered"] and info["q"] == m // (k + 1)
+    assert info["filtered"] and info["q"] == m // (k + 1) - info["step"] + 1 and info["step"] in (1, 2, 4)
+    st.close()
+
+
+@pytest.mark.parametrize("step", [1, 2, 4])
+def test_filtered_myers_every_sampling_step(ctx, step, monkeypatch):
+    """the scan's sampling step is a pure performance knob: every setting gives the direct kernel's hits"""
+    monkeypatch.setenv("SPMB_FILTER_STEP", str(step))
+    rng = np.random.default_rng(41 + step)
+    n, m, k = 90_000, 100, 3
+    text = rand_text(rng, n)
+    pats = [text[s:s + m].copy() for s in (100, 5000, 33333)]
+    for i in range(90):      # occurrences at every alignment mod 4, with 0..k+1 edits
+        pat = pats[i % 3]
+        mp = mutate(rng, pat, int(rng.integers(0, k + 2)))
+        s = 1000 + i * 900 + (i % 4)
+        text[s:s + len(mp)] = mp
+    st = sp.Store.from_host(ctx, text, 96)
+    info = check_filtered(ctx, st, text, pats, k, f"step={step}")
+    assert info["step"] == step and info["q"] == 25 - step + 1
     st.close()
 
 
