@@ -9,9 +9,9 @@ HDRS := $(wildcard $(CSRC)/*.cuh) include/spmb.h
 
 all: $(LIB) oracle
 
-$(LIB): $(CSRC)/spmb_capi.cu $(CSRC)/ingest.cpp $(HDRS)
+$(LIB): $(CSRC)/spmb_capi.cu $(CSRC)/ingest.cpp $(CSRC)/hostpack.cpp $(HDRS)
 	@mkdir -p libspm_b200/lib
-	$(NVCC) $(NVFLAGS) -o $@ $(CSRC)/spmb_capi.cu $(CSRC)/ingest.cpp -lz
+	$(NVCC) $(NVFLAGS) -o $@ $(CSRC)/spmb_capi.cu $(CSRC)/ingest.cpp $(CSRC)/hostpack.cpp -lz -lpthread
 
 oracle:
 	$(MAKE) -C oracle

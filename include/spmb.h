@@ -107,6 +107,16 @@ int spmb_store_create(spmb_context *ctx, const uint8_t *host_ranks, uint64_t n, 
                       spmb_store **out);
 int spmb_store_create_from_device(spmb_context *ctx, const uint8_t *dev_ranks, uint64_t n,
                                   uint32_t row_len, spmb_store **out);
+/* spmb_store_create with a long host haystack (>= SPMB_UPLOAD_MIN symbols, default 32 Mi) uploads in
+ * chunks through two movers at once: the copy engine takes raw chunks (1 B/symbol), host threads
+ * (SPMB_HOST_THREADS, default: available cpus - 1) pack chunks to 2 bits/symbol and send a quarter of the
+ * bytes; both claim from one queue, so the split follows the machine.
+ * stats[0] raw chunks, [1] host-packed chunks of the last such upload, [2] symbols per chunk, [3] host threads. */
+int spmb_upload_last_stats(const spmb_context *ctx, uint64_t stats[4]);
+/* the host packing loop itself (no device needed): ranks[0,n) -> out[0, ceil(n/32)), one 64-bit word per
+ * 32 symbols = the store's lane-chunk word (uint2 {x,y} in memory: 2-bit codes, first symbol in the top
+ * bits of x, symbols 16..31 in y); ranks are masked to 2 bits, symbols past n are 0. */
+void spmb_host_pack_chunks(const uint8_t *ranks, uint64_t n, uint64_t *out);
 /* journaled sequence: base + events, materialised on the device into a new packed store whose
  * coordinates are those of the derived sequence. */
 int spmb_store_create_journaled(spmb_context *ctx, const spmb_store *base,

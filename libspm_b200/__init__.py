@@ -44,6 +44,7 @@ EXPORTS = [
     "spmb_vcf_pool", "spmb_vcf_coverage", "spmb_vcf_haplotype_count", "spmb_vcf_sample_count", "spmb_vcf_sample_name",
     "spmb_vcf_stats",
     "spmb_context_set_shard", "spmb_pigeonhole_create", "spmb_pattern_filter_info", "spmb_search_anchored",
+    "spmb_upload_last_stats", "spmb_host_pack_chunks",
 ]
 
 
@@ -81,6 +82,8 @@ def lib():
             "spmb_context_set_shard": (i32, [vp, u32, u32]),
             "spmb_store_create": (i32, [vp, vp, u64, u32, pp]),
             "spmb_store_create_from_device": (i32, [vp, vp, u64, u32, pp]),
+            "spmb_upload_last_stats": (i32, [vp, C.POINTER(u64 * 4)]),
+            "spmb_host_pack_chunks": (None, [vp, u64, vp]),
             "spmb_store_create_journaled": (i32, [vp, vp, vp, u64, vp, u64, u32, pp]),
             "spmb_store_destroy": (i32, [vp]),
             "spmb_store_length": (u64, [vp]),
@@ -147,6 +150,15 @@ def _status(code):
         return "?"
 
 
+def host_pack_chunks(ranks) -> np.ndarray:
+    """the upload pipeline's host packing loop: 1-byte ranks -> one uint64 per 32 symbols
+    (low half = symbols 0..15 with the first on top, high half = symbols 16..31)."""
+    a = np.ascontiguousarray(ranks, dtype=np.uint8)
+    out = np.zeros((a.size + 31) // 32, dtype=np.uint64)
+    lib().spmb_host_pack_chunks(a.ctypes.data, a.size, out.ctypes.data)
+    return out
+
+
 def _ranks(a):
     a = np.ascontiguousarray(a, dtype=np.uint8)
     return a
@@ -180,6 +192,12 @@ class Context:
     @property
     def last_launch_count(self) -> int:
         return int(lib().spmb_last_launch_count(self._h))
+
+    def upload_last_stats(self):
+        """figures of the last chunked host upload (spmb_upload_last_stats)."""
+        st = (C.c_uint64 * 4)()
+        self._check(lib().spmb_upload_last_stats(self._h, C.byref(st)), "spmb_upload_last_stats")
+        return {"raw_chunks": st[0], "host_packed_chunks": st[1], "chunk_symbols": st[2], "host_threads": st[3]}
 
     def device_info(self):
         sm, khz, mem = C.c_int(), C.c_int(), C.c_uint64()

@@ -24,6 +24,7 @@
 #include "myers.cuh"
 #include "pack.cuh"
 #include "pigeon.cuh"
+#include "upload.cuh"
 
 // ------------------------------------------------------------------------------------------
 // objects
@@ -41,11 +42,13 @@ struct spmb_context {
     // context outlives them (a destroy() with live children is deferred until the last one goes)
     uint32_t children = 0;
     bool closed = false;
+    UploadPool *upload = nullptr;          // host-haystack upload pipeline (upload.cuh), created on first use
 };
 
 static void context_free(spmb_context *ctx)
 {
     cudaSetDevice(ctx->device);
+    delete ctx->upload;
     if (ctx->own_stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
     if (ctx->h_count) cudaFreeHost(ctx->h_count);
     cudaGetLastError();
@@ -290,11 +293,44 @@ extern "C" int spmb_store_create_from_device(spmb_context *ctx, const uint8_t *d
     return SPMB_OK;
 }
 
+// long host haystacks: chunked upload, raw over the copy engine and 2-bit packed by host threads at once
+static int store_create_pipelined(spmb_context *ctx, const uint8_t *host_ranks, uint64_t n, uint32_t row_len,
+                                  spmb_store **out)
+{
+    if (!ctx->upload) {
+        UploadPool *up = new (std::nothrow) UploadPool();
+        if (!up) return SPMB_ERR_OOM;
+        cudaError_t e = up->init(ctx->device);
+        if (e != cudaSuccess) { delete up; cudaGetLastError(); return set_err(ctx, SPMB_ERR_CUDA, "upload pool", e); }
+        ctx->upload = up;
+    }
+    spmb_store *s = nullptr;
+    int rc = store_alloc(ctx, n, row_len, SPMB_MODE_PLAIN, &s);
+    if (rc) return rc;
+    uint2 *d_chunks = nullptr;
+    cudaError_t e = cudaMallocAsync(&d_chunks, (n + 31) / 32 * sizeof(uint2), ctx->stream);
+    if (e != cudaSuccess) { cudaGetLastError(); spmb_store_destroy(s); return set_err(ctx, SPMB_ERR_OOM, "cudaMallocAsync(chunks)", e); }
+    e = ctx->upload->run(host_ranks, n, d_chunks, ctx->stream, &ctx->launches);
+    if (e == cudaSuccess) {
+        ChunkSource src{d_chunks, n};
+        pack_chunks_kernel<ChunkSource><<<(unsigned)(s->lay.n_cols_alloc / 1024), 1024, 0, ctx->stream>>>(src, s->lay, s->planes, nullptr);
+        ctx->launches++;
+        e = cudaGetLastError();
+    }
+    cudaFreeAsync(d_chunks, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) { cudaGetLastError(); spmb_store_destroy(s); return set_err(ctx, SPMB_ERR_CUDA, "store upload", e); }
+    *out = s;
+    return SPMB_OK;
+}
+
 extern "C" int spmb_store_create(spmb_context *ctx, const uint8_t *host_ranks, uint64_t n, uint32_t row_len,
                                  spmb_store **out)
 {
     if (!ctx || !out || (!host_ranks && n)) return SPMB_ERR_ARG;
     ENTER(ctx);
+    if (n >= UploadPool::env_u64("SPMB_UPLOAD_MIN", 32ull << 20) && n > 0)
+        return store_create_pipelined(ctx, host_ranks, n, row_len, out);
     uint8_t *d = nullptr;
     CU(cudaMallocAsync(&d, n ? n : 1, ctx->stream));
     cudaError_t e = cudaMemcpyAsync(d, host_ranks, n, cudaMemcpyHostToDevice, ctx->stream);
@@ -310,6 +346,19 @@ extern "C" int spmb_store_create(spmb_context *ctx, const uint8_t *host_ranks, u
         rc = set_err(ctx, SPMB_ERR_CUDA, "store_create", e);
     }
     return rc;
+}
+
+extern "C" int spmb_upload_last_stats(const spmb_context *ctx, uint64_t stats[4])
+{
+    if (!ctx || !stats) return SPMB_ERR_ARG;
+    stats[0] = stats[1] = stats[2] = stats[3] = 0;
+    if (ctx->upload) {
+        stats[0] = ctx->upload->last_raw;
+        stats[1] = ctx->upload->last_packed;
+        stats[2] = ctx->upload->chunk_sym;
+        stats[3] = (uint64_t)ctx->upload->n_workers;
+    }
+    return SPMB_OK;
 }
 
 static int store_ensure_lanes(spmb_context *ctx, const spmb_store *s);

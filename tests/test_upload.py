@@ -1,0 +1,124 @@
+"""The host-haystack upload pipeline (libspm_b200/csrc/upload.cuh + hostpack.cpp): the host packing loop
+against numpy on the CPU; on the GPU, stores built through the chunk queue (raw chunks over the copy
+engine + host-packed chunks) must read back symbol for symbol and give the oracle's hit lists."""
+import os
+
+import numpy as np
+import pytest
+
+import libspm_b200 as sp
+import oracle as orc
+from tests.util import mutate, rand_text
+
+
+def _pack_numpy(a):
+    n = a.size
+    b = np.zeros((n + 31) // 32 * 32, dtype=np.uint64)
+    b[:n] = a & 3
+    b = b.reshape(-1, 32)
+    x = np.zeros(len(b), dtype=np.uint64)
+    y = np.zeros(len(b), dtype=np.uint64)
+    for j in range(16):
+        x |= b[:, j] << np.uint64(30 - 2 * j)
+        y |= b[:, 16 + j] << np.uint64(30 - 2 * j)
+    return x | (y << np.uint64(32))
+
+
+@pytest.mark.parametrize("n", [0, 1, 31, 32, 33, 95, 127, 128, 129, 160, 1000, 4097, 100_003])
+def test_host_pack_chunks_matches_numpy(n):
+    rng = np.random.default_rng(n)
+    a = rng.integers(0, 256, size=n, dtype=np.uint8)       # values are masked to 2 bits
+    assert np.array_equal(sp.host_pack_chunks(a), _pack_numpy(a))
+
+
+def test_host_pack_chunks_unaligned_source():
+    rng = np.random.default_rng(5)
+    a = rng.integers(0, 4, size=5000, dtype=np.uint8)
+    for off in (1, 3, 17):
+        assert np.array_equal(sp.host_pack_chunks(a[off:]), _pack_numpy(a[off:]))
+
+
+# ------------------------------------------------------------------------------------------
+@pytest.fixture
+def small_chunks(monkeypatch):
+    """force the chunked path on test-sized inputs (the knobs are read when a context first uploads)"""
+    monkeypatch.setenv("SPMB_UPLOAD_MIN", "1")
+    monkeypatch.setenv("SPMB_UPLOAD_CHUNK", "65536")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("threads", [0, 1, 4])
+@pytest.mark.parametrize("n,rl", [(1, 0), (65536, 0), (65537, 64), (1_000_003, 0), (3_000_017, 1056)])
+def test_chunked_upload_round_trip(small_chunks, monkeypatch, threads, n, rl):
+    monkeypatch.setenv("SPMB_HOST_THREADS", str(threads))
+    ctx = sp.Context(0)
+    try:
+        rng = np.random.default_rng(n + threads)
+        text = rand_text(rng, n)
+        store = sp.Store.from_host(ctx, text, row_len=rl)
+        st = ctx.upload_last_stats()
+        assert st["chunk_symbols"] == 65536 and st["host_threads"] == threads
+        assert st["raw_chunks"] + st["host_packed_chunks"] == (n + 65535) // 65536
+        if threads == 0:
+            assert st["host_packed_chunks"] == 0
+        assert np.array_equal(store.read(), text)
+        store.close()
+    finally:
+        ctx.close()
+
+
+@pytest.mark.gpu
+def test_chunked_upload_search_parity(small_chunks, monkeypatch):
+    monkeypatch.setenv("SPMB_HOST_THREADS", "3")
+    ctx = sp.Context(0)
+    try:
+        rng = np.random.default_rng(77)
+        text = rand_text(rng, 2_500_000)
+        pat = text[1_234_567:1_234_567 + 64].copy()
+        for pos in (100, 65536 - 30, 131072 - 64, 2_400_000):     # copies across chunk seams
+            text[pos:pos + 64] = pat
+        pm = text[700_000:700_100].copy()
+        mm = mutate(rng, pm, 3)
+        text[65536 * 7 - 50:65536 * 7 - 50 + len(mm)] = mm
+        store = sp.Store.from_host(ctx, text)
+        want = orc.search_mt(2, text, pat)[1]
+        got = sp.search(ctx, store, sp.Pattern(ctx, sp.ALG_SHIFTOR, pat))
+        assert np.array_equal(got["end"], want) and len(want) >= 5
+        _, we, wr = orc.search_mt(3, text, pm, 4)
+        got = sp.search(ctx, store, sp.Pattern(ctx, sp.ALG_MYERS, pm, 4))
+        assert np.array_equal(got["end"], we) and np.array_equal(got["errors"], wr)
+        # several uploads through one pool, and the same result from the single-copy path
+        again = sp.Store.from_host(ctx, text[:1_000_000])
+        assert np.array_equal(again.read(), text[:1_000_000])
+    finally:
+        ctx.close()
+    monkeypatch.setenv("SPMB_UPLOAD_MIN", str(1 << 40))
+    ctx2 = sp.Context(0)
+    try:
+        s2 = sp.Store.from_host(ctx2, text)
+        assert ctx2.upload_last_stats()["chunk_symbols"] == 0      # pool never created
+        got2 = sp.search(ctx2, s2, sp.Pattern(ctx2, sp.ALG_SHIFTOR, pat))
+        assert np.array_equal(got2["end"], want)
+    finally:
+        ctx2.close()
+
+
+@pytest.mark.gpu
+def test_chunked_upload_default_geometry_large():
+    """default knobs (4 Mi-symbol chunks, all host threads) on a 100 Mbp haystack"""
+    for k in ("SPMB_UPLOAD_MIN", "SPMB_UPLOAD_CHUNK", "SPMB_HOST_THREADS"):
+        os.environ.pop(k, None)
+    ctx = sp.Context(0)
+    try:
+        rng = np.random.default_rng(9)
+        text = rand_text(rng, 100_000_001)
+        store = sp.Store.from_host(ctx, text)
+        st = ctx.upload_last_stats()
+        assert st["raw_chunks"] + st["host_packed_chunks"] == 24
+        for lo in (0, 4 * (1 << 20) - 1000, 50_000_000, 100_000_001 - 70_000):
+            assert np.array_equal(store.read(lo, 70_000), text[lo:lo + 70_000])
+        pat = text[99_999_000:99_999_064].copy()
+        got = sp.search(ctx, store, sp.Pattern(ctx, sp.ALG_HORSPOOL, pat))
+        assert np.array_equal(got["end"], orc.search_mt(1, text, pat)[1])
+    finally:
+        ctx.close()
