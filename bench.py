@@ -289,12 +289,19 @@ def run_ours(args):
         torch.cuda.synchronize()
         e2e_s = time.perf_counter() - t0
         text_h2d //= e2e_steps
+        us = ctx.upload_last_stats()
+        if us["events_per_chunk"]:                           # events: 24 B raw, 8 B (+16 per chunk) host-packed
+            epc = us["events_per_chunk"]
+            ev_h2d = (len(ev) - min(len(ev), us["event_host_packed_chunks"] * epc)) * 24 \
+                + us["event_host_packed_chunks"] * (16 + 8 * epc) + pool.nbytes
+        else:
+            ev_h2d = ev_bytes
         if world > 1:
             t = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             e2e_s = float(t.item())
         out["e2e"] = {"value": world * n_der * e2e_steps / e2e_s / 1e9, "unit": "Gbp/s",
-                      "h2d_bytes_per_step": int(text_h2d + ev_bytes + m), "d2h_bytes_per_step": int(8 + nh * 24),
+                      "h2d_bytes_per_step": int(text_h2d + ev_h2d + m), "d2h_bytes_per_step": int(8 + nh * 24),
                       "steps": e2e_steps, "ms_per_step": e2e_s / e2e_steps * 1e3,
                       "host_input_bytes_per_step": int(n + ev_bytes + m),
                       "upload": ctx.upload_last_stats(),

@@ -90,6 +90,9 @@ int spmb_context_destroy(spmb_context *ctx);
 void *spmb_context_stream(const spmb_context *ctx);
 const char *spmb_last_error(const spmb_context *ctx);
 int spmb_context_sync(spmb_context *ctx);
+/* give back what the context caches between calls (journal scratch block, upload threads and their pinned
+ * buffers, the stream-ordered pool's free memory); everything is re-created on demand. */
+int spmb_context_trim(spmb_context *ctx);
 /* Multi-GPU sharding: every later search on this context covers only shard
  * `shard` of `n_shards` of each store it is given (contiguous ranges of super-tiles; a hit
  * belongs to the shard that holds its begin (exact) / end (Myers) position).  The shards of one
@@ -111,8 +114,11 @@ int spmb_store_create_from_device(spmb_context *ctx, const uint8_t *dev_ranks, u
  * chunks through two movers at once: the copy engine takes raw chunks (1 B/symbol), host threads
  * (SPMB_HOST_THREADS, default: available cpus - 1) pack chunks to 2 bits/symbol and send a quarter of the
  * bytes; both claim from one queue, so the split follows the machine.
- * stats[0] raw chunks, [1] host-packed chunks of the last such upload, [2] symbols per chunk, [3] host threads. */
-int spmb_upload_last_stats(const spmb_context *ctx, uint64_t stats[4]);
+ * The event table of spmb_store_create_journaled takes the same queue once the context has uploaded a long
+ * haystack: host threads rewrite 24-byte events as 8-byte records where they fit, the device expands them.
+ * stats[0] raw chunks, [1] host-packed chunks of the last such upload, [2] symbols per chunk, [3] host threads,
+ * [4] raw / [5] host-packed event chunks of the last journal, [6] events per chunk, [7] 0. */
+int spmb_upload_last_stats(const spmb_context *ctx, uint64_t stats[8]);
 /* the host packing loop itself (no device needed): ranks[0,n) -> out[0, ceil(n/32)), one 64-bit word per
  * 32 symbols = the store's lane-chunk word (uint2 {x,y} in memory: 2-bit codes, first symbol in the top
  * bits of x, symbols 16..31 in y); ranks are masked to 2 bits, symbols past n are 0. */

@@ -44,7 +44,7 @@ EXPORTS = [
     "spmb_vcf_pool", "spmb_vcf_coverage", "spmb_vcf_haplotype_count", "spmb_vcf_sample_count", "spmb_vcf_sample_name",
     "spmb_vcf_stats",
     "spmb_context_set_shard", "spmb_pigeonhole_create", "spmb_pattern_filter_info", "spmb_search_anchored",
-    "spmb_upload_last_stats", "spmb_host_pack_chunks",
+    "spmb_upload_last_stats", "spmb_host_pack_chunks", "spmb_context_trim",
 ]
 
 
@@ -79,10 +79,11 @@ def lib():
             "spmb_context_stream": (vp, [vp]),
             "spmb_last_error": (C.c_char_p, [vp]),
             "spmb_context_sync": (i32, [vp]),
+            "spmb_context_trim": (i32, [vp]),
             "spmb_context_set_shard": (i32, [vp, u32, u32]),
             "spmb_store_create": (i32, [vp, vp, u64, u32, pp]),
             "spmb_store_create_from_device": (i32, [vp, vp, u64, u32, pp]),
-            "spmb_upload_last_stats": (i32, [vp, C.POINTER(u64 * 4)]),
+            "spmb_upload_last_stats": (i32, [vp, C.POINTER(u64 * 8)]),
             "spmb_host_pack_chunks": (None, [vp, u64, vp]),
             "spmb_store_create_journaled": (i32, [vp, vp, vp, u64, vp, u64, u32, pp]),
             "spmb_store_destroy": (i32, [vp]),
@@ -181,6 +182,10 @@ class Context:
     def sync(self):
         self._check(lib().spmb_context_sync(self._h), "spmb_context_sync")
 
+    def trim(self):
+        """release cached scratch / upload threads / pool memory (spmb_context_trim)."""
+        self._check(lib().spmb_context_trim(self._h), "spmb_context_trim")
+
     def set_shard(self, shard: int, n_shards: int):
         """later searches cover only this shard (contiguous super-tile range) of every store."""
         self._check(lib().spmb_context_set_shard(self._h, shard, n_shards), "spmb_context_set_shard")
@@ -195,9 +200,10 @@ class Context:
 
     def upload_last_stats(self):
         """figures of the last chunked host upload (spmb_upload_last_stats)."""
-        st = (C.c_uint64 * 4)()
+        st = (C.c_uint64 * 8)()
         self._check(lib().spmb_upload_last_stats(self._h, C.byref(st)), "spmb_upload_last_stats")
-        return {"raw_chunks": st[0], "host_packed_chunks": st[1], "chunk_symbols": st[2], "host_threads": st[3]}
+        return {"raw_chunks": st[0], "host_packed_chunks": st[1], "chunk_symbols": st[2], "host_threads": st[3],
+                "event_raw_chunks": st[4], "event_host_packed_chunks": st[5], "events_per_chunk": st[6]}
 
     def device_info(self):
         sm, khz, mem = C.c_int(), C.c_int(), C.c_uint64()

@@ -162,14 +162,15 @@ __global__ void journal_delta_kernel(const spmb_journal_event *__restrict__ ev, 
     if (!ok) atomicExch(bad, 1);
 }
 
-__global__ void journal_der_kernel(const spmb_journal_event *__restrict__ ev, uint64_t n_ev,
-                                   const long long *__restrict__ shift, const long long *__restrict__ delta,
-                                   uint64_t *__restrict__ der, long long *__restrict__ total)
+// shift[i] (exclusive prefix of the deltas) -> derived position of event i, in place
+__global__ void journal_der_kernel(const spmb_journal_event *__restrict__ ev, uint64_t n_ev, long long *shift_der,
+                                   const long long *__restrict__ delta, long long *__restrict__ total)
 {
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_ev) return;
-    der[i] = (uint64_t)((long long)ev[i].ref_pos + shift[i]);
-    if (i == n_ev - 1) *total = shift[i] + delta[i];
+    const long long sh = shift_der[i];
+    if (i == n_ev - 1) *total = sh + delta[i];
+    shift_der[i] = (long long)ev[i].ref_pos + sh;
 }
 
 __global__ void journal_blkidx_kernel(const uint64_t *__restrict__ der, uint64_t n_ev, uint64_t n_blk,
@@ -184,6 +185,43 @@ __global__ void journal_blkidx_kernel(const uint64_t *__restrict__ der, uint64_t
         if (der[mid] <= d) lo = mid; else hi = mid - 1;
     }
     blk_idx[b] = lo;
+}
+
+// ---- 32x32 bit-matrix transpose across a warp: lane r holds row r (bit c = element [r][c]); afterwards
+// lane c holds column c (bit r = element [r][c]).  Five butterfly steps, one shuffle each: step j swaps the
+// off-diagonal j x j blocks between lanes r and r^j.  Replaces 32 ballots + 32 predicated moves per word.
+__device__ __forceinline__ uint32_t spmb_transpose32(uint32_t x, uint32_t lane)
+{
+#pragma unroll
+    for (int j = 16; j >= 1; j >>= 1) {
+        // m_lo: bits c with (c & j) == 0
+        const uint32_t m_lo = j == 16 ? 0x0000ffffu : j == 8 ? 0x00ff00ffu : j == 4 ? 0x0f0f0f0fu : j == 2 ? 0x33333333u : 0x55555555u;
+        const uint32_t y = __shfl_xor_sync(0xffffffffu, x, j);
+        const bool up = (lane & j) != 0;
+        const uint32_t sh = up ? (y >> j) : (y << j);
+        const uint32_t keep = up ? ~m_lo : m_lo;
+        x = (x & keep) | (sh & ~keep);
+    }
+    return x;
+}
+
+// 16 two-bit codes (symbol j at bits 31-2j, 30-2j) -> the 16 high bits and the 16 low bits, symbol j at bit 15-j
+__device__ __forceinline__ uint32_t spmb_compress_even(uint32_t t) // even bit positions -> low 16 bits
+{
+    t = (t | (t >> 1)) & 0x33333333u;
+    t = (t | (t >> 2)) & 0x0f0f0f0fu;
+    t = (t | (t >> 4)) & 0x00ff00ffu;
+    t = (t | (t >> 8)) & 0x0000ffffu;
+    return t;
+}
+
+// lane-chunk word (32 symbols of one row) -> H / L words with symbol c at bit c
+__device__ __forceinline__ void spmb_chunk_to_bits(const uint2 w, uint32_t &H, uint32_t &L)
+{
+    const uint32_t hx = spmb_compress_even((w.x >> 1) & 0x55555555u), lx = spmb_compress_even(w.x & 0x55555555u);
+    const uint32_t hy = spmb_compress_even((w.y >> 1) & 0x55555555u), ly = spmb_compress_even(w.y & 0x55555555u);
+    H = __brev((hx << 16) | hy);
+    L = __brev((lx << 16) | ly);
 }
 
 template <class Source>
@@ -215,33 +253,39 @@ __global__ void __launch_bounds__(1024) pack_kernel(Source src, SpmbLayout lay, 
     planes[(uint64_t)blockIdx.x * 1024 + threadIdx.x] = tile[threadIdx.x];
 }
 
-// same block shape as pack_kernel for sources that deliver a lane chunk (32 symbols of a row, packed):
-// lane b holds row b's chunk, 64 ballots transpose it into the {H,L} column words; the chunk itself is
-// the store's lane-chunk layout, written as a by-product when `lanes_out` is given.
+// same block shape as pack_kernel for sources that deliver a lane chunk (32 symbols of a row, packed).
+// Fetch phase: warp r = row r of the super-tile, lane c = the c-th 32-column group of the block, so a warp
+// walks 1024 CONSECUTIVE symbols of one row: a linear source is read in 256-byte runs, and the lanes of a
+// journal lookup share their block index, their binary-search path and their event records (L1 hits instead
+// of a chain of DRAM round trips per lane).  The chunks change hands through shared memory; then warp c
+// holds group c with lane r = row r, the 2 x 32 x 32 bit transposition gives the {H,L} column words, and the
+// chunk itself -- the store's lane-chunk layout -- is written as a by-product when `lanes_out` is given.
 template <class Source>
 __global__ void __launch_bounds__(1024) pack_chunks_kernel(Source src, SpmbLayout lay, uint2 *__restrict__ planes,
                                                            uint2 *__restrict__ lanes_out)
 {
     __shared__ uint2 tile[1024];
+    __shared__ uint2 xchg[32][33];
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint64_t g0 = (uint64_t)blockIdx.x * 1024 + warp * 32; // first column of this thread-row
-    uint2 w = make_uint2(0, 0);
-    if (g0 < lay.n_cols) {
-        uint64_t st = spmb_div_rl(lay, g0);
-        uint32_t col0 = (uint32_t)(g0 - st * lay.row_len);
-        uint64_t p0 = (st * 32 + lane) * (uint64_t)lay.row_len + col0;
-        if (p0 < lay.n) w = src.load_chunk(p0);
+    {
+        const uint64_t gf = (uint64_t)blockIdx.x * 1024 + lane * 32; // first column of group `lane`
+        uint2 f = make_uint2(0, 0);
+        if (gf < lay.n_cols) {
+            const uint64_t st = spmb_div_rl(lay, gf);
+            const uint32_t col0 = (uint32_t)(gf - st * lay.row_len);
+            const uint64_t p0 = (st * 32 + warp) * (uint64_t)lay.row_len + col0;
+            if (p0 < lay.n) f = src.load_chunk(p0);
+        }
+        xchg[warp][lane] = f;
     }
+    __syncthreads();
+    const uint2 w = xchg[lane][warp];                                // row `lane`, group `warp`
+    const uint64_t g0 = (uint64_t)blockIdx.x * 1024 + warp * 32;     // first column of this thread-row
     if (lanes_out) lanes_out[(g0 >> 5) * 32 + lane] = w; // group G = g0/32 (every group of the allocation is written)
-    uint32_t myH = 0, myL = 0;
-#pragma unroll
-    for (int c = 0; c < 32; ++c) {
-        const uint32_t word = c < 16 ? w.x : w.y;
-        const uint32_t s = word >> (30 - 2 * (c & 15));
-        uint32_t h = __ballot_sync(0xffffffffu, (s >> 1) & 1u);
-        uint32_t l = __ballot_sync(0xffffffffu, s & 1u);
-        if (lane == c) { myH = h; myL = l; }
-    }
+    uint32_t myH, myL;
+    spmb_chunk_to_bits(w, myH, myL);          // row `lane`: bit c = column g0 + c
+    myH = spmb_transpose32(myH, lane);        // column g0 + lane: bit r = row r
+    myL = spmb_transpose32(myL, lane);
     tile[((lane >> 1) << 6) | (warp << 1) | (lane & 1)] = make_uint2(myH, myL);
     __syncthreads();
     planes[(uint64_t)blockIdx.x * 1024 + threadIdx.x] = tile[threadIdx.x];
@@ -278,13 +322,7 @@ __global__ void __launch_bounds__(256) lanes_kernel(const uint2 *__restrict__ pl
     const uint64_t G = (uint64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
     if (G >= n_groups) return; // warp-uniform
     const uint2 c = __ldg(planes + spmb_perm(G * 32 + lane));
-    uint32_t myH = 0, myL = 0;
-#pragma unroll
-    for (int r = 0; r < 32; ++r) {
-        const uint32_t h = __ballot_sync(0xffffffffu, (c.x >> r) & 1u);
-        const uint32_t l = __ballot_sync(0xffffffffu, (c.y >> r) & 1u);
-        if (lane == r) { myH = h; myL = l; }
-    }
+    const uint32_t myH = spmb_transpose32(c.x, lane), myL = spmb_transpose32(c.y, lane); // row `lane`: bit j = column j
     const uint32_t bh = __brev(myH), bl = __brev(myL); // column j at bit 31-j
     uint2 o;
     o.x = (spmb_spread16(bh >> 16) << 1) | spmb_spread16(bl >> 16);

@@ -37,20 +37,37 @@ struct spmb_context {
     uint32_t launches = 0;
     int sm_count = 0;
     unsigned long long *h_count = nullptr; // pinned (8 slots)
+    spmb_hit *h_spec = nullptr;            // pinned: the first SPEC_HITS hits travel with the counters (one round trip)
     uint32_t shard = 0, n_shards = 1;      // searches cover super-tiles [n_st*shard/n, n_st*(shard+1)/n)
     // stores / patterns / hit lists / streams / JSTs keep a raw pointer to their context: the
     // context outlives them (a destroy() with live children is deferred until the last one goes)
     uint32_t children = 0;
     bool closed = false;
     UploadPool *upload = nullptr;          // host-haystack upload pipeline (upload.cuh), created on first use
+    // grow-only device scratch for the journal's temporaries (event table, prefix arrays): the stream-ordered
+    // pool took 5-15 ms to hand out ~1.6 GB in seven pieces on every call; released by spmb_context_trim
+    uint8_t *scratch = nullptr;
+    size_t scratch_bytes = 0;
+    // free list of large device blocks (store planes / lane chunks / upload intermediates), by size class:
+    // a store that is re-created every call (the host-haystack call shape) gets its blocks back without a
+    // driver call; the stream-ordered pool spent 3-6 ms per call on the same five ~0.8 GB requests
+    struct Block { void *p; size_t bytes; };
+    std::vector<Block> blocks;
+    size_t blocks_bytes = 0, blocks_cap = 0;
 };
+
+enum { SPEC_HITS = 1024 };
 
 static void context_free(spmb_context *ctx)
 {
     cudaSetDevice(ctx->device);
     delete ctx->upload;
+    if (ctx->scratch) cudaFree(ctx->scratch);
+    for (auto &b : ctx->blocks) cudaFreeAsync(b.p, ctx->stream);
+    ctx->blocks.clear();
     if (ctx->own_stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
     if (ctx->h_count) cudaFreeHost(ctx->h_count);
+    if (ctx->h_spec) cudaFreeHost(ctx->h_spec);
     cudaGetLastError();
     delete ctx;
 }
@@ -121,6 +138,7 @@ struct spmb_hits {
     uint64_t count = 0;
     const spmb_store *pend_store = nullptr;
     const spmb_pattern *pend_pat = nullptr;
+    bool spec_done = false;                // hits_collect already brought the (short) raw list to `host`
 };
 
 struct spmb_stream {
@@ -204,7 +222,13 @@ extern "C" int spmb_context_create(int device, void *stream, spmb_context **out)
         }
         cudaGetLastError();
     }
-    if (cudaMallocHost(&ctx->h_count, 8 * sizeof(unsigned long long)) != cudaSuccess) { delete ctx; return SPMB_ERR_CUDA; }
+    if (cudaMallocHost(&ctx->h_count, 8 * sizeof(unsigned long long)) != cudaSuccess ||
+        cudaMallocHost(&ctx->h_spec, SPEC_HITS * sizeof(spmb_hit)) != cudaSuccess) {
+        if (ctx->h_count) cudaFreeHost(ctx->h_count);
+        cudaGetLastError();
+        delete ctx;
+        return SPMB_ERR_CUDA;
+    }
     *out = ctx;
     return SPMB_OK;
 }
@@ -226,6 +250,102 @@ extern "C" int spmb_context_set_shard(spmb_context *ctx, uint32_t shard, uint32_
     if (!ctx || n_shards == 0 || shard >= n_shards) return SPMB_ERR_ARG;
     ctx->shard = shard;
     ctx->n_shards = n_shards;
+    return SPMB_OK;
+}
+
+// ---- large blocks: size classes of 1/16 of a power of two (<= 6 % slack), exact-class reuse, all use is
+// ordered on the context's stream (so is the reuse)
+static size_t big_class(size_t bytes)
+{
+    size_t p2 = 1;
+    while (p2 * 2 <= bytes) p2 *= 2;
+    size_t g = std::max<size_t>(p2 / 16, (size_t)2 << 20);
+    return (bytes + g - 1) / g * g;
+}
+enum : size_t { BIG_MIN = (size_t)16 << 20 };
+
+static cudaError_t big_alloc(spmb_context *ctx, size_t bytes, void **out)
+{
+    if (bytes < BIG_MIN) return cudaMallocAsync(out, bytes ? bytes : 1, ctx->stream);
+    const size_t cls = big_class(bytes);
+    for (size_t i = 0; i < ctx->blocks.size(); ++i)
+        if (ctx->blocks[i].bytes == cls) {
+            *out = ctx->blocks[i].p;
+            ctx->blocks_bytes -= cls;
+            ctx->blocks.erase(ctx->blocks.begin() + i);
+            return cudaSuccess;
+        }
+    cudaError_t e = cudaMallocAsync(out, cls, ctx->stream);
+    if (e != cudaSuccess && !ctx->blocks.empty()) { // make room: give the cached blocks back and retry
+        cudaGetLastError();
+        for (auto &b : ctx->blocks) cudaFreeAsync(b.p, ctx->stream);
+        ctx->blocks.clear();
+        ctx->blocks_bytes = 0;
+        e = cudaMallocAsync(out, cls, ctx->stream);
+    }
+    return e;
+}
+
+static void big_free(spmb_context *ctx, void *p, size_t bytes)
+{
+    if (!p) return;
+    if (bytes >= BIG_MIN && !ctx->closed) {
+        const size_t cls = big_class(bytes);
+        if (ctx->blocks_cap == 0) {
+            size_t fr = 0, tot = 0;
+            if (cudaMemGetInfo(&fr, &tot) != cudaSuccess) { cudaGetLastError(); tot = 0; }
+            ctx->blocks_cap = tot / 4 + 1;
+        }
+        if (ctx->blocks.size() < 16 && ctx->blocks_bytes + cls <= ctx->blocks_cap) {
+            ctx->blocks.push_back({p, cls});
+            ctx->blocks_bytes += cls;
+            return;
+        }
+    }
+    cudaFreeAsync(p, ctx->stream);
+}
+
+static void big_release_all(spmb_context *ctx)
+{
+    for (auto &b : ctx->blocks) cudaFreeAsync(b.p, ctx->stream);
+    ctx->blocks.clear();
+    ctx->blocks_bytes = 0;
+}
+
+// the context's scratch block, at least `bytes` long; contents are only valid within one call
+static cudaError_t ctx_scratch(spmb_context *ctx, size_t bytes, uint8_t **out)
+{
+    if (bytes > ctx->scratch_bytes) {
+        cudaError_t e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess) return e;
+        if (ctx->scratch) cudaFree(ctx->scratch);
+        ctx->scratch = nullptr;
+        ctx->scratch_bytes = 0;
+        size_t want = bytes + bytes / 8;
+        e = cudaMalloc(&ctx->scratch, want);
+        if (e != cudaSuccess) { cudaGetLastError(); want = bytes; e = cudaMalloc(&ctx->scratch, want); }
+        if (e != cudaSuccess) { ctx->scratch = nullptr; return e; }
+        ctx->scratch_bytes = want;
+    }
+    *out = ctx->scratch;
+    return cudaSuccess;
+}
+
+extern "C" int spmb_context_trim(spmb_context *ctx)
+{
+    if (!ctx) return SPMB_ERR_ARG;
+    ENTER(ctx);
+    CU(cudaStreamSynchronize(ctx->stream));
+    if (ctx->scratch) cudaFree(ctx->scratch);
+    ctx->scratch = nullptr;
+    ctx->scratch_bytes = 0;
+    delete ctx->upload;
+    ctx->upload = nullptr;
+    big_release_all(ctx);
+    CU(cudaStreamSynchronize(ctx->stream));
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, ctx->device) == cudaSuccess) cudaMemPoolTrimTo(pool, 0);
+    cudaGetLastError();
     return SPMB_OK;
 }
 
@@ -261,7 +381,7 @@ static int store_alloc(spmb_context *ctx, uint64_t n, uint32_t row_len, uint32_t
     s->ctx = ctx;
     s->lay = spmb_make_layout(n, row_len, mode);
     s->bytes = (size_t)s->lay.n_cols_alloc * sizeof(uint2);
-    cudaError_t e = cudaMallocAsync(&s->planes, s->bytes, ctx->stream); // stream-ordered pool: cheap re-creation
+    cudaError_t e = big_alloc(ctx, s->bytes, (void **)&s->planes);
     if (e != cudaSuccess) { cudaGetLastError(); delete s; return set_err(ctx, SPMB_ERR_OOM, "cudaMallocAsync(store)", e); }
     *out = s;
     return SPMB_OK;
@@ -293,31 +413,43 @@ extern "C" int spmb_store_create_from_device(spmb_context *ctx, const uint8_t *d
     return SPMB_OK;
 }
 
+static int ensure_upload(spmb_context *ctx)
+{
+    if (ctx->upload) return SPMB_OK;
+    UploadPool *up = new (std::nothrow) UploadPool();
+    if (!up) return SPMB_ERR_OOM;
+    cudaError_t e = up->init(ctx->device);
+    if (e != cudaSuccess) { delete up; cudaGetLastError(); return set_err(ctx, SPMB_ERR_CUDA, "upload pool", e); }
+    ctx->upload = up;
+    return SPMB_OK;
+}
+
 // long host haystacks: chunked upload, raw over the copy engine and 2-bit packed by host threads at once
 static int store_create_pipelined(spmb_context *ctx, const uint8_t *host_ranks, uint64_t n, uint32_t row_len,
                                   spmb_store **out)
 {
-    if (!ctx->upload) {
-        UploadPool *up = new (std::nothrow) UploadPool();
-        if (!up) return SPMB_ERR_OOM;
-        cudaError_t e = up->init(ctx->device);
-        if (e != cudaSuccess) { delete up; cudaGetLastError(); return set_err(ctx, SPMB_ERR_CUDA, "upload pool", e); }
-        ctx->upload = up;
-    }
+    int rcu = ensure_upload(ctx);
+    if (rcu) return rcu;
     spmb_store *s = nullptr;
     int rc = store_alloc(ctx, n, row_len, SPMB_MODE_PLAIN, &s);
     if (rc) return rc;
     uint2 *d_chunks = nullptr;
-    cudaError_t e = cudaMallocAsync(&d_chunks, (n + 31) / 32 * sizeof(uint2), ctx->stream);
+    const size_t chunk_bytes = (n + 31) / 32 * sizeof(uint2);
+    cudaError_t e = big_alloc(ctx, chunk_bytes, (void **)&d_chunks);
     if (e != cudaSuccess) { cudaGetLastError(); spmb_store_destroy(s); return set_err(ctx, SPMB_ERR_OOM, "cudaMallocAsync(chunks)", e); }
     e = ctx->upload->run(host_ranks, n, d_chunks, ctx->stream, &ctx->launches);
     if (e == cudaSuccess) {
+        // the lane-chunk copy the Myers / journal kernels read is the same words in another order: write it
+        // now instead of deriving it from the planes later (skipped when memory is short)
+        uint2 *l = nullptr;
+        if (big_alloc(ctx, s->bytes, (void **)&l) != cudaSuccess) { cudaGetLastError(); l = nullptr; }
         ChunkSource src{d_chunks, n};
-        pack_chunks_kernel<ChunkSource><<<(unsigned)(s->lay.n_cols_alloc / 1024), 1024, 0, ctx->stream>>>(src, s->lay, s->planes, nullptr);
+        pack_chunks_kernel<ChunkSource><<<(unsigned)(s->lay.n_cols_alloc / 1024), 1024, 0, ctx->stream>>>(src, s->lay, s->planes, l);
+        s->lanes = l;
         ctx->launches++;
         e = cudaGetLastError();
     }
-    cudaFreeAsync(d_chunks, ctx->stream);
+    big_free(ctx, d_chunks, chunk_bytes);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     if (e != cudaSuccess) { cudaGetLastError(); spmb_store_destroy(s); return set_err(ctx, SPMB_ERR_CUDA, "store upload", e); }
     *out = s;
@@ -332,12 +464,12 @@ extern "C" int spmb_store_create(spmb_context *ctx, const uint8_t *host_ranks, u
     if (n >= UploadPool::env_u64("SPMB_UPLOAD_MIN", 32ull << 20) && n > 0)
         return store_create_pipelined(ctx, host_ranks, n, row_len, out);
     uint8_t *d = nullptr;
-    CU(cudaMallocAsync(&d, n ? n : 1, ctx->stream));
+    CU(big_alloc(ctx, n, (void **)&d));
     cudaError_t e = cudaMemcpyAsync(d, host_ranks, n, cudaMemcpyHostToDevice, ctx->stream);
     int rc = SPMB_OK;
     if (e != cudaSuccess) rc = set_err(ctx, SPMB_ERR_CUDA, "H2D haystack", e);
     if (rc == SPMB_OK) rc = spmb_store_create_from_device(ctx, d, n, row_len, out);
-    cudaFreeAsync(d, ctx->stream);
+    big_free(ctx, d, n);
     // the caller's buffer may be pinned (truly asynchronous copy): do not return before it is consumed
     e = cudaStreamSynchronize(ctx->stream);
     if (rc == SPMB_OK && e != cudaSuccess) {
@@ -348,15 +480,18 @@ extern "C" int spmb_store_create(spmb_context *ctx, const uint8_t *host_ranks, u
     return rc;
 }
 
-extern "C" int spmb_upload_last_stats(const spmb_context *ctx, uint64_t stats[4])
+extern "C" int spmb_upload_last_stats(const spmb_context *ctx, uint64_t stats[8])
 {
     if (!ctx || !stats) return SPMB_ERR_ARG;
-    stats[0] = stats[1] = stats[2] = stats[3] = 0;
+    for (int i = 0; i < 8; ++i) stats[i] = 0;
     if (ctx->upload) {
         stats[0] = ctx->upload->last_raw;
         stats[1] = ctx->upload->last_packed;
         stats[2] = ctx->upload->chunk_sym;
         stats[3] = (uint64_t)ctx->upload->n_workers;
+        stats[4] = ctx->upload->last_ev_raw;
+        stats[5] = ctx->upload->last_ev_packed;
+        stats[6] = ctx->upload->last_ev_chunk;
     }
     return SPMB_OK;
 }
@@ -380,34 +515,55 @@ extern "C" int spmb_store_create_journaled(spmb_context *ctx, const spmb_store *
     int *d_bad = nullptr;
     uint8_t *d_pool = nullptr;
     void *d_tmp = nullptr;
+    size_t d_tmp_bytes = 0;
     spmb_store *s = nullptr;
     int rc = SPMB_OK;
     cudaError_t e = cudaSuccess;
-    auto cleanup = [&]() {
-        cudaFreeAsync(d_ev, sm); cudaFreeAsync(d_delta, sm); cudaFreeAsync(d_shift, sm); cudaFreeAsync(d_total, sm);
-        cudaFreeAsync(d_der, sm); cudaFreeAsync(d_blk, sm); cudaFreeAsync(d_bad, sm); cudaFreeAsync(d_pool, sm);
-        cudaFreeAsync(d_tmp, sm);
-    };
+    size_t blk_bytes = 0;
+    auto cleanup = [&]() { big_free(ctx, d_blk, blk_bytes); d_blk = nullptr; }; // everything else lives in the context's scratch block
 #define JCU(call) do { if (e == cudaSuccess) e = (call); } while (0)
-    JCU(cudaMallocAsync(&d_ev, ne * sizeof(spmb_journal_event), sm));
-    JCU(cudaMallocAsync(&d_delta, ne * 8, sm));
-    JCU(cudaMallocAsync(&d_shift, ne * 8, sm));
-    JCU(cudaMallocAsync(&d_der, ne * 8, sm));
-    JCU(cudaMallocAsync(&d_total, 16, sm));
-    JCU(cudaMallocAsync(&d_bad, 16, sm));
-    JCU(cudaMallocAsync(&d_pool, pool_len ? pool_len : 1, sm));
+    const bool trace = UploadPool::env_u64("SPMB_UPLOAD_TRACE", 0) != 0;
+    auto tnow = [] { return std::chrono::steady_clock::now(); };
+    auto tms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+        return std::chrono::duration<double, std::milli>(b - a).count();
+    };
+    const auto tj0 = tnow();
+    {
+        size_t tmp_bytes = 0;
+        JCU(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, (long long *)nullptr, (long long *)nullptr, (int64_t)ne, sm));
+        auto up = [](size_t x) { return (x + 255) / 256 * 256; };
+        const size_t o_ev = 0, o_delta = o_ev + up(ne * sizeof(spmb_journal_event)), o_shift = o_delta + up(ne * 8),
+                     o_total = o_shift + up(ne * 8), o_bad = o_total + 256, o_pool = o_bad + 256,
+                     o_tmp = o_pool + up(pool_len + 1), o_end = o_tmp + up(tmp_bytes + 1);
+        uint8_t *sc = nullptr;
+        JCU(ctx_scratch(ctx, o_end, &sc));
+        if (e != cudaSuccess) { cudaGetLastError(); return set_err(ctx, SPMB_ERR_OOM, "journal scratch", e); }
+        d_ev = (spmb_journal_event *)(sc + o_ev);
+        d_delta = (long long *)(sc + o_delta);
+        d_shift = (long long *)(sc + o_shift);
+        d_der = (uint64_t *)d_shift;            // journal_der_kernel turns the shifts into derived positions in place
+        d_total = (long long *)(sc + o_total);
+        d_bad = (int *)(sc + o_bad);
+        d_pool = sc + o_pool;
+        d_tmp = sc + o_tmp;
+        d_tmp_bytes = tmp_bytes;
+    }
     JCU(cudaMemsetAsync(d_total, 0, 16, sm));
     JCU(cudaMemsetAsync(d_bad, 0, 16, sm));
-    if (n_ev) JCU(cudaMemcpyAsync(d_ev, ev, n_ev * sizeof(spmb_journal_event), cudaMemcpyHostToDevice, sm));
+    const auto tj1 = tnow();
     if (pool_len) JCU(cudaMemcpyAsync(d_pool, pool, pool_len, cudaMemcpyHostToDevice, sm));
+    // long event tables take the upload queue (copy engine + host threads that shrink 24-byte events to 8)
+    if (e == cudaSuccess && n_ev * sizeof(spmb_journal_event) >= UploadPool::env_u64("SPMB_UPLOAD_MIN", 32ull << 20) &&
+        ensure_upload(ctx) == SPMB_OK)
+        e = ctx->upload->run_events(ev, n_ev, pool_len, d_ev, sm, &ctx->launches);
+    else if (n_ev) JCU(cudaMemcpyAsync(d_ev, ev, n_ev * sizeof(spmb_journal_event), cudaMemcpyHostToDevice, sm));
+    const auto tj2 = tnow();
     if (e == cudaSuccess && n_ev) {
         unsigned blocks = (unsigned)((n_ev + 255) / 256);
         journal_delta_kernel<<<blocks, 256, 0, sm>>>(d_ev, n_ev, base->lay.n, pool_len, d_delta, d_bad);
-        size_t tmp_bytes = 0;
-        JCU(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, d_delta, d_shift, (int64_t)n_ev, sm));
-        JCU(cudaMallocAsync(&d_tmp, tmp_bytes ? tmp_bytes : 1, sm));
+        size_t tmp_bytes = d_tmp_bytes;
         JCU(cub::DeviceScan::ExclusiveSum(d_tmp, tmp_bytes, d_delta, d_shift, (int64_t)n_ev, sm));
-        journal_der_kernel<<<blocks, 256, 0, sm>>>(d_ev, n_ev, d_shift, d_delta, d_der, d_total);
+        journal_der_kernel<<<blocks, 256, 0, sm>>>(d_ev, n_ev, d_shift, d_delta, d_total);
         ctx->launches += 3;
         JCU(cudaGetLastError());
     }
@@ -420,19 +576,21 @@ extern "C" int spmb_store_create_journaled(spmb_context *ctx, const spmb_store *
         cleanup();
         return set_err(ctx, SPMB_ERR_ARG, "journal events must be sorted, non-overlapping, inside the reference and the pool");
     }
+    const auto tj3 = tnow();
     const long long total_shift = (long long)ctx->h_count[1];
     const uint64_t n_der = (uint64_t)((long long)base->lay.n + total_shift);
     rc = store_alloc(ctx, n_der, row_len, SPMB_MODE_PLAIN, &s);
     if (rc) { cleanup(); return rc; }
     const uint64_t n_blk = (n_der >> 10) + 2;
-    JCU(cudaMallocAsync(&d_blk, n_blk * 8, sm));
+    blk_bytes = n_blk * 8;
+    JCU(big_alloc(ctx, blk_bytes, (void **)&d_blk));
     if (e == cudaSuccess) {
         journal_blkidx_kernel<<<(unsigned)((n_blk + 255) / 256), 256, 0, sm>>>(d_der, n_ev, n_blk, d_blk);
         ctx->launches++;
         // the gather reads the base through its lane chunks; the derived store gets its own for free
         rc = store_ensure_lanes(ctx, base);
         uint2 *l = nullptr;
-        if (rc == SPMB_OK && cudaMallocAsync(&l, s->bytes, sm) != cudaSuccess) { cudaGetLastError(); l = nullptr; }
+        if (rc == SPMB_OK && big_alloc(ctx, s->bytes, (void **)&l) != cudaSuccess) { cudaGetLastError(); l = nullptr; }
         if (rc == SPMB_OK) {
             JournalSource src{base->lanes, base->lay, d_ev, d_der, d_blk, d_pool, n_ev, n_der};
             pack_chunks_kernel<JournalSource><<<(unsigned)(s->lay.n_cols_alloc / 1024), 1024, 0, sm>>>(src, s->lay, s->planes, l);
@@ -441,8 +599,12 @@ extern "C" int spmb_store_create_journaled(spmb_context *ctx, const spmb_store *
             s->lanes = l;
         }
     }
+    const auto tj4 = tnow();
     cleanup();
     JCU(cudaStreamSynchronize(sm));
+    if (trace)
+        fprintf(stderr, "[spmb journal] allocs %.2f ms  events+pool up %.2f  prefix (to host) %.2f  enqueue materialise %.2f  free+sync %.2f\n",
+                tms(tj0, tj1), tms(tj1, tj2), tms(tj2, tj3), tms(tj3, tj4), tms(tj4, tnow()));
 #undef JCU
     if (e != cudaSuccess || rc) {
         spmb_store_destroy(s);
@@ -457,8 +619,8 @@ extern "C" int spmb_store_destroy(spmb_store *s)
 {
     if (!s) return SPMB_OK;
     if (s->ctx) cudaSetDevice(s->ctx->device);
-    if (s->ctx) cudaFreeAsync(s->planes, s->ctx->stream); else cudaFree(s->planes);
-    if (s->lanes) { if (s->ctx) cudaFreeAsync(s->lanes, s->ctx->stream); else cudaFree(s->lanes); }
+    if (s->ctx) big_free(s->ctx, s->planes, s->bytes); else cudaFree(s->planes);
+    if (s->lanes) { if (s->ctx) big_free(s->ctx, s->lanes, s->bytes); else cudaFree(s->lanes); }
     cudaFree(s->row_len);
     cudaFree(s->row_seq);
     cudaFree(s->row_own);
@@ -475,13 +637,13 @@ static int store_ensure_lanes(spmb_context *ctx, const spmb_store *s)
 {
     if (s->lanes) return SPMB_OK;
     uint2 *l = nullptr;
-    cudaError_t e = cudaMallocAsync(&l, s->bytes, ctx->stream);
+    cudaError_t e = big_alloc(ctx, s->bytes, (void **)&l);
     if (e != cudaSuccess) { cudaGetLastError(); return set_err(ctx, SPMB_ERR_OOM, "cudaMallocAsync(lanes)", e); }
     const uint64_t n_groups = s->lay.n_cols_alloc / 32;
     lanes_kernel<<<(unsigned)((n_groups + 7) / 8), 256, 0, ctx->stream>>>(s->planes, n_groups, l);
     ctx->launches++;
     e = cudaGetLastError();
-    if (e != cudaSuccess) { cudaFreeAsync(l, ctx->stream); return set_err(ctx, SPMB_ERR_CUDA, "lanes_kernel launch", e); }
+    if (e != cudaSuccess) { big_free(ctx, l, s->bytes); return set_err(ctx, SPMB_ERR_CUDA, "lanes_kernel launch", e); }
     s->lanes = l;
     return SPMB_OK;
 }
@@ -1125,12 +1287,22 @@ template <class Again>
 static int hits_collect(spmb_context *ctx, spmb_hits *h, std::vector<spmb_hit> &raw, Again again,
                         unsigned long long *count_only = nullptr)
 {
+    h->spec_done = false;
     for (int attempt = 0; attempt < 5; ++attempt) {
         CU(cudaMemcpyAsync(ctx->h_count, h->d_count, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+        // short lists (the common case) ride along with the counters: one synchronisation instead of two
+        const unsigned long long n_spec = std::min<unsigned long long>(h->cap, SPEC_HITS);
+        if (n_spec) CU(cudaMemcpyAsync(ctx->h_spec, h->d_hits, n_spec * sizeof(spmb_hit), cudaMemcpyDeviceToHost, ctx->stream));
         CU(cudaStreamSynchronize(ctx->stream));
         const unsigned long long cnt = ctx->h_count[0];
         const unsigned long long cand = std::max(ctx->h_count[1], ctx->h_count[2]);
         if (cnt <= h->cap && cand <= h->cand_cap) {
+            if (cnt <= n_spec) {
+                raw.assign(ctx->h_spec, ctx->h_spec + cnt);
+                h->spec_done = true;
+                if (count_only) *count_only = cnt;
+                return SPMB_OK;
+            }
             if (count_only) { *count_only = cnt; return SPMB_OK; } // the hits stay on the device for now
             raw.resize(cnt);
             if (cnt) {
@@ -1165,7 +1337,7 @@ extern "C" int spmb_search_finish(spmb_context *ctx, spmb_hits *h)
     if (rc) return rc;
     if (!done) {
         h->host.resize(cnt);
-        if (cnt) {
+        if (cnt && !h->spec_done) {
             CU(cudaMemcpyAsync(h->host.data(), h->d_hits, cnt * sizeof(spmb_hit), cudaMemcpyDeviceToHost, ctx->stream));
             CU(cudaStreamSynchronize(ctx->stream));
         }

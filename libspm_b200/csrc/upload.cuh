@@ -15,9 +15,14 @@
 #include <cuda_runtime.h>
 #include <sched.h>
 
+#include "../../include/spmb.h"
+
 #include <atomic>
+#include <chrono>
+#include <cstdio>
 #include <condition_variable>
 #include <cstdlib>
+#include <cstring>
 #include <mutex>
 #include <thread>
 #include <vector>
@@ -68,6 +73,73 @@ __global__ void __launch_bounds__(256) bytes_to_chunks_kernel(const uint8_t *__r
     out[g] = o;
 }
 
+// ---- journal events (24 B each in the C ABI) cross the link the same way: a host thread rewrites a chunk
+// of events as 8-byte records, the device expands it back; chunks that do not fit the short form, and the
+// chunks the copy engine claims, travel as they are.  Short form: the chunk is cut into blocks of
+// EV_BLOCK events, each with a header {base_pos, base_off} (position of its first event, pool offset of
+// its first inserting event); a record holds the position and pool-offset deltas and the two lengths
+// (< 256).  An event that inserts nothing never reads the pool: its offset is only checked against the
+// pool length (like the device validation would) and comes back as base_off.
+enum { EV_BLOCK = 1024 };
+struct SpmbPackedEvent {
+    uint32_t dpos;
+    uint16_t doff;
+    uint8_t del_len, ins_len;
+};
+struct SpmbPackedEventHeader {
+    uint64_t base_pos, base_off;
+};
+
+// slot = [ceil(n / EV_BLOCK) headers][n records]
+__global__ void __launch_bounds__(256) expand_events_kernel(const uint8_t *__restrict__ slot, uint32_t n,
+                                                            spmb_journal_event *__restrict__ out)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t n_blk = (n + EV_BLOCK - 1) / EV_BLOCK;
+    const SpmbPackedEventHeader h = reinterpret_cast<const SpmbPackedEventHeader *>(slot)[i / EV_BLOCK];
+    const SpmbPackedEvent r = reinterpret_cast<const SpmbPackedEvent *>(slot + n_blk * sizeof(SpmbPackedEventHeader))[i];
+    spmb_journal_event e;
+    e.ref_pos = h.base_pos + r.dpos;
+    e.del_len = r.del_len;
+    e.ins_len = r.ins_len;
+    e.ins_off = h.base_off + r.doff;
+    out[i] = e;
+}
+
+static inline size_t spmb_packed_events_bytes(uint32_t n)
+{
+    return (size_t)((n + EV_BLOCK - 1) / EV_BLOCK) * sizeof(SpmbPackedEventHeader) + (size_t)n * sizeof(SpmbPackedEvent);
+}
+
+// host side of the above; false = some record does not fit (the chunk then travels raw)
+static inline bool spmb_host_pack_events(const spmb_journal_event *ev, uint32_t n, uint64_t pool_len, uint8_t *out)
+{
+    const uint32_t n_blk = (n + EV_BLOCK - 1) / EV_BLOCK;
+    SpmbPackedEventHeader *hdr = reinterpret_cast<SpmbPackedEventHeader *>(out);
+    SpmbPackedEvent *rec = reinterpret_cast<SpmbPackedEvent *>(out + n_blk * sizeof(SpmbPackedEventHeader));
+    uint64_t bad = 0;
+    for (uint32_t b = 0; b < n_blk; ++b) {
+        const uint32_t i0 = b * EV_BLOCK, i1 = (i0 + EV_BLOCK < n) ? i0 + EV_BLOCK : n;
+        SpmbPackedEventHeader h{ev[i0].ref_pos, 0};
+        for (uint32_t i = i0; i < i1; ++i)
+            if (ev[i].ins_len) { h.base_off = ev[i].ins_off; break; }
+        if (h.base_off > pool_len) return false;
+        hdr[b] = h;
+        for (uint32_t i = i0; i < i1; ++i) {
+            const uint64_t dp = ev[i].ref_pos - h.base_pos;
+            uint64_t dof = ev[i].ins_off - h.base_off;
+            if (ev[i].ins_len == 0) { bad |= (uint64_t)(ev[i].ins_off > pool_len); dof = 0; }
+            bad |= (dp >> 32) | (dof >> 16) | (ev[i].del_len >> 8) | (ev[i].ins_len >> 8);
+            rec[i].dpos = (uint32_t)dp;
+            rec[i].doff = (uint16_t)dof;
+            rec[i].del_len = (uint8_t)ev[i].del_len;
+            rec[i].ins_len = (uint8_t)ev[i].ins_len;
+        }
+    }
+    return bad == 0;
+}
+
 static inline int spmb_host_cpus()
 {
     cpu_set_t set;
@@ -83,22 +155,24 @@ static inline int spmb_host_cpus()
 // default: available cpus - 1, at most 31), SPMB_UPLOAD_CHUNK = symbols per chunk (default 4 Mi),
 // SPMB_UPLOAD_MIN = shortest haystack that takes this path (default 32 Mi symbols)
 struct UploadPool {
-    enum { SLOTS = 3 };
+    enum { SLOTS = 4 };
     int device = 0;
     uint64_t chunk_sym = 4ull << 20;
     uint64_t min_sym = 32ull << 20;
     int n_workers = 0;
+    bool trace = false;                         // SPMB_UPLOAD_TRACE=1: per-job timings on stderr
 
     struct Worker {
         std::thread th;
         cudaStream_t stream = nullptr;
         uint64_t *pinned[2] = {nullptr, nullptr};
+        uint8_t *d_slot[2] = {nullptr, nullptr};   // device landing area of a packed event chunk
         cudaEvent_t ev[2] = {nullptr, nullptr};
         bool used[2] = {false, false};
     };
     std::vector<Worker> workers;
-    uint8_t *d_slot[SLOTS] = {nullptr, nullptr, nullptr};
-    cudaEvent_t slot_ev[SLOTS] = {nullptr, nullptr, nullptr};
+    uint8_t *d_slot[SLOTS] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t slot_ev[SLOTS] = {nullptr, nullptr, nullptr, nullptr};
     bool ready = false;
 
     // job state
@@ -110,9 +184,16 @@ struct UploadPool {
     const uint8_t *src = nullptr;
     uint64_t n = 0, n_chunks = 0;
     uint2 *d_chunks = nullptr;
+    const spmb_journal_event *ev_src = nullptr; // events job (src == nullptr)
+    spmb_journal_event *d_ev = nullptr;
+    uint64_t ev_chunk = 0;                      // events per chunk
+    uint64_t ev_pool_len = 0;
     std::atomic<uint64_t> ends{0};  // head << 32 | tail: chunks [head, tail) are unclaimed
     std::atomic<int> cuda_err{0};
     std::atomic<uint64_t> packed_chunks{0};
+    std::atomic<uint64_t> unpackable_chunks{0};
+    std::atomic<uint32_t> worker_launches{0};
+    uint64_t last_ev_raw = 0, last_ev_packed = 0, last_ev_chunk = 0;
     // figures of the last upload (spmb_upload_last_stats)
     uint64_t last_raw = 0, last_packed = 0;
 
@@ -151,6 +232,9 @@ struct UploadPool {
         chunk_sym = (chunk_sym + 1023) / 1024 * 1024;
         if (chunk_sym < 1024) chunk_sym = 1024;
         min_sym = env_u64("SPMB_UPLOAD_MIN", min_sym);
+        trace = env_u64("SPMB_UPLOAD_TRACE", 0) != 0;
+        // SPMB_UPLOAD_SPIN=0: threads sleep while they wait for a slot instead of polling
+        const unsigned ev_flags = cudaEventDisableTiming | (env_u64("SPMB_UPLOAD_SPIN", 1) ? 0u : (unsigned)cudaEventBlockingSync);
         int dflt = spmb_host_cpus() - 1;
         if (dflt > 31) dflt = 31;
         if (dflt < 0) dflt = 0;
@@ -159,7 +243,7 @@ struct UploadPool {
         cudaError_t e = cudaSuccess;
         for (int s = 0; s < SLOTS && e == cudaSuccess; ++s) {
             e = cudaMalloc(&d_slot[s], chunk_sym);
-            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&slot_ev[s], cudaEventDisableTiming | cudaEventBlockingSync);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&slot_ev[s], ev_flags);
         }
         workers.resize(n_workers);
         for (int w = 0; w < n_workers && e == cudaSuccess; ++w) {
@@ -167,7 +251,8 @@ struct UploadPool {
             e = cudaStreamCreateWithFlags(&W.stream, cudaStreamNonBlocking);
             for (int b = 0; b < 2 && e == cudaSuccess; ++b) {
                 e = cudaHostAlloc((void **)&W.pinned[b], chunk_sym / 4, cudaHostAllocDefault);
-                if (e == cudaSuccess) e = cudaEventCreateWithFlags(&W.ev[b], cudaEventDisableTiming | cudaEventBlockingSync);
+                if (e == cudaSuccess) e = cudaMalloc(&W.d_slot[b], chunk_sym / 4);
+                if (e == cudaSuccess) e = cudaEventCreateWithFlags(&W.ev[b], ev_flags);
             }
         }
         if (e != cudaSuccess) return e;
@@ -191,19 +276,54 @@ struct UploadPool {
             int b = 0;
             uint64_t idx;
             cudaError_t e = cudaSuccess;
+            auto now = [] { return std::chrono::steady_clock::now(); };
+            auto us = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point c) {
+                return (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(c - a).count();
+            };
+            const auto tw0 = now();
+            uint64_t t_wait = 0, t_pack = 0, t_api = 0;
             while (e == cudaSuccess && cuda_err.load(std::memory_order_relaxed) == 0 && claim_tail(idx)) {
+                const auto ta = now();
                 if (W.used[b]) e = cudaEventSynchronize(W.ev[b]);
-                const uint64_t p0 = idx * chunk_sym;
-                const uint64_t len = (n - p0 < chunk_sym) ? n - p0 : chunk_sym;
-                spmb_host_pack_chunks(src + p0, len, W.pinned[b]);
-                if (e == cudaSuccess)
-                    e = cudaMemcpyAsync(d_chunks + p0 / 32, W.pinned[b], (len + 31) / 32 * 8, cudaMemcpyHostToDevice, W.stream);
+                const auto tb = now();
+                t_wait += us(ta, tb);
+                if (src) {
+                    const uint64_t p0 = idx * chunk_sym;
+                    const uint64_t len = (n - p0 < chunk_sym) ? n - p0 : chunk_sym;
+                    spmb_host_pack_chunks(src + p0, len, W.pinned[b]);
+                    t_pack += us(tb, now());
+                    if (e == cudaSuccess)
+                        e = cudaMemcpyAsync(d_chunks + p0 / 32, W.pinned[b], (len + 31) / 32 * 8, cudaMemcpyHostToDevice, W.stream);
+                } else {
+                    const uint64_t i0 = idx * ev_chunk;
+                    const uint32_t len = (uint32_t)((n - i0 < ev_chunk) ? n - i0 : ev_chunk);
+                    const bool fits = spmb_host_pack_events(ev_src + i0, len, ev_pool_len, (uint8_t *)W.pinned[b]);
+                    t_pack += us(tb, now());
+                    if (fits) {
+                        if (e == cudaSuccess)
+                            e = cudaMemcpyAsync(W.d_slot[b], W.pinned[b], spmb_packed_events_bytes(len), cudaMemcpyHostToDevice, W.stream);
+                        if (e == cudaSuccess) {
+                            expand_events_kernel<<<(len + 255) / 256, 256, 0, W.stream>>>(W.d_slot[b], len, d_ev + i0);
+                            e = cudaGetLastError();
+                            worker_launches.fetch_add(1, std::memory_order_relaxed);
+                        }
+                    } else if (e == cudaSuccess) {
+                        e = cudaMemcpyAsync(d_ev + i0, ev_src + i0, (size_t)len * sizeof(spmb_journal_event), cudaMemcpyHostToDevice, W.stream);
+                        unpackable_chunks.fetch_add(1, std::memory_order_relaxed);
+                    }
+                }
                 if (e == cudaSuccess) e = cudaEventRecord(W.ev[b], W.stream);
                 W.used[b] = true;
                 b ^= 1;
                 packed_chunks.fetch_add(1, std::memory_order_relaxed);
             }
+            const auto tc = now();
             if (e == cudaSuccess) e = cudaStreamSynchronize(W.stream);
+            if (trace) {
+                t_api = us(tw0, tc) - t_wait - t_pack;
+                fprintf(stderr, "[spmb upload] worker %d: total %.2f ms  pack %.2f  wait-slot %.2f  api %.2f  drain %.2f\n", w,
+                        us(tw0, now()) / 1e6, t_pack / 1e6, t_wait / 1e6, t_api / 1e6, us(tc, now()) / 1e6);
+            }
             W.used[0] = W.used[1] = false;
             if (e != cudaSuccess) cuda_err.store((int)e);
             {
@@ -213,22 +333,22 @@ struct UploadPool {
         }
     }
 
-    // fills dst[0, ceil(n/32)) (device, visible to `stream` and already allocated in its order) from
-    // host_ranks[0, n).  Returns when every byte of host_ranks has been consumed and all work of the
-    // packed path is complete; the raw path's last kernels are ordered on `stream`.
-    cudaError_t run(const uint8_t *host_ranks, uint64_t n_sym, uint2 *dst, cudaStream_t stream, uint32_t *launches)
+    // the calling thread's half of a job: start the workers, feed head chunks to the copy engine (at most
+    // SLOTS-1 ahead of the link, so the split stays adaptive), wait for the workers, drain `stream`
+    template <class RawChunk>
+    cudaError_t drive(cudaStream_t stream, uint64_t *raw_out, RawChunk raw_chunk)
     {
-        src = host_ranks;
-        n = n_sym;
-        d_chunks = dst;
-        n_chunks = (n_sym + chunk_sym - 1) / chunk_sym;
         cuda_err.store(0);
         packed_chunks.store(0);
+        unpackable_chunks.store(0);
+        worker_launches.store(0);
         ends.store(n_chunks & 0xffffffffull); // head 0, tail n_chunks
-        // dst comes from the stream-ordered allocator: the workers' streams may touch it only after
-        // the allocation point of `stream`
+        // the destination comes from the stream-ordered allocator: the workers' streams may touch it only
+        // after the allocation point of `stream`
+        const auto t0 = std::chrono::steady_clock::now();
         cudaError_t e = cudaStreamSynchronize(stream);
         if (e != cudaSuccess) return e;
+        const auto t1 = std::chrono::steady_clock::now();
         if (n_workers) {
             std::lock_guard<std::mutex> lk(mu);
             running = n_workers;
@@ -237,19 +357,11 @@ struct UploadPool {
         }
         uint64_t idx, raw = 0;
         int s = 0;
-        bool used[SLOTS] = {false, false, false};
+        bool used[SLOTS] = {false, false, false, false};
         while (e == cudaSuccess && cuda_err.load(std::memory_order_relaxed) == 0) {
-            if (used[s]) e = cudaEventSynchronize(slot_ev[s]); // at most SLOTS-1 raw chunks ahead of the link
+            if (used[s]) e = cudaEventSynchronize(slot_ev[s]);
             if (e != cudaSuccess || !claim_head(idx)) break;
-            const uint64_t p0 = idx * chunk_sym;
-            const uint64_t len = (n - p0 < chunk_sym) ? n - p0 : chunk_sym;
-            e = cudaMemcpyAsync(d_slot[s], src + p0, len, cudaMemcpyHostToDevice, stream);
-            if (e == cudaSuccess) {
-                const uint64_t groups = (len + 31) / 32;
-                bytes_to_chunks_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, stream>>>(d_slot[s], len, d_chunks + p0 / 32);
-                if (launches) ++*launches;
-                e = cudaGetLastError();
-            }
+            e = raw_chunk(idx, s);
             if (e == cudaSuccess) e = cudaEventRecord(slot_ev[s], stream);
             used[s] = true;
             s = (s + 1) % SLOTS;
@@ -259,16 +371,74 @@ struct UploadPool {
             cuda_err.store((int)e);
             ends.store(0);
         }
+        const auto t2 = std::chrono::steady_clock::now();
         if (n_workers) {
             std::unique_lock<std::mutex> lk(mu);
             cv_done.wait(lk, [&] { return running == 0; });
         }
+        const auto t3 = std::chrono::steady_clock::now();
         // the caller's buffer may be reused as soon as we return: the raw copies must have left it
         cudaError_t e2 = cudaStreamSynchronize(stream);
         if (e == cudaSuccess) e = e2;
         if (e == cudaSuccess && cuda_err.load() != 0) e = (cudaError_t)cuda_err.load();
-        last_raw = raw;
+        *raw_out = raw;
+        if (trace) {
+            auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point c) {
+                return std::chrono::duration<double, std::milli>(c - a).count();
+            };
+            fprintf(stderr, "[spmb upload] %s job: %llu chunks (%llu raw)  pre-sync %.2f ms  raw loop %.2f  wait workers %.2f  drain %.2f\n",
+                    src ? "text" : "events", (unsigned long long)n_chunks, (unsigned long long)raw, ms(t0, t1), ms(t1, t2), ms(t2, t3),
+                    ms(t3, std::chrono::steady_clock::now()));
+        }
+        return e;
+    }
+
+    // fills dst[0, ceil(n/32)) (device, allocated in `stream`'s order) from host_ranks[0, n).  Returns when
+    // every byte of host_ranks has been consumed and dst is complete.
+    cudaError_t run(const uint8_t *host_ranks, uint64_t n_sym, uint2 *dst, cudaStream_t stream, uint32_t *launches)
+    {
+        src = host_ranks;
+        ev_src = nullptr;
+        n = n_sym;
+        d_chunks = dst;
+        n_chunks = (n_sym + chunk_sym - 1) / chunk_sym;
+        cudaError_t e = drive(stream, &last_raw, [&](uint64_t idx, int s) -> cudaError_t {
+            const uint64_t p0 = idx * chunk_sym;
+            const uint64_t len = (n - p0 < chunk_sym) ? n - p0 : chunk_sym;
+            cudaError_t r = cudaMemcpyAsync(d_slot[s], src + p0, len, cudaMemcpyHostToDevice, stream);
+            if (r != cudaSuccess) return r;
+            const uint64_t groups = (len + 31) / 32;
+            bytes_to_chunks_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, stream>>>(d_slot[s], len, d_chunks + p0 / 32);
+            if (launches) ++*launches;
+            return cudaGetLastError();
+        });
         last_packed = packed_chunks.load();
+        return e;
+    }
+
+    // same queue for the journal's event table: dst[0, n_ev) <- ev[0, n_ev)
+    cudaError_t run_events(const spmb_journal_event *ev, uint64_t n_ev, uint64_t pool_len, spmb_journal_event *dst,
+                           cudaStream_t stream, uint32_t *launches)
+    {
+        ev_pool_len = pool_len;
+        src = nullptr;
+        ev_src = ev;
+        d_ev = dst;
+        n = n_ev;
+        // whole blocks that fit a worker's pinned buffer (chunk_sym / 4 bytes), at most 64 Ki events
+        ev_chunk = (chunk_sym / 4) / (EV_BLOCK * sizeof(SpmbPackedEvent) + sizeof(SpmbPackedEventHeader)) * EV_BLOCK;
+        if (ev_chunk > 65536) ev_chunk = 65536;
+        if (ev_chunk == 0) ev_chunk = 16;       // tiny test geometries: one partial block
+        n_chunks = (n_ev + ev_chunk - 1) / ev_chunk;
+        cudaError_t e = drive(stream, &last_ev_raw, [&](uint64_t idx, int) -> cudaError_t {
+            const uint64_t i0 = idx * ev_chunk;
+            const uint64_t len = (n - i0 < ev_chunk) ? n - i0 : ev_chunk;
+            return cudaMemcpyAsync(d_ev + i0, ev_src + i0, len * sizeof(spmb_journal_event), cudaMemcpyHostToDevice, stream);
+        });
+        last_ev_packed = packed_chunks.load() - unpackable_chunks.load();
+        last_ev_raw += unpackable_chunks.load();
+        last_ev_chunk = ev_chunk;
+        if (launches) *launches += worker_launches.load();
         return e;
     }
 
@@ -284,6 +454,7 @@ struct UploadPool {
         for (auto &W : workers) {
             for (int b = 0; b < 2; ++b) {
                 if (W.pinned[b]) cudaFreeHost(W.pinned[b]);
+                if (W.d_slot[b]) cudaFree(W.d_slot[b]);
                 if (W.ev[b]) cudaEventDestroy(W.ev[b]);
             }
             if (W.stream) cudaStreamDestroy(W.stream);

@@ -122,3 +122,57 @@ def test_chunked_upload_default_geometry_large():
         assert np.array_equal(got["end"], orc.search_mt(1, text, pat)[1])
     finally:
         ctx.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("threads", [0, 3])
+def test_event_table_through_upload_queue(small_chunks, monkeypatch, threads):
+    """journal events over the chunk queue (raw 24-byte events + chunks rewritten as 8-byte records by
+    host threads, expanded on the device): the derived sequence equals the oracle's journal_apply,
+    including chunks whose records do not fit the short form."""
+    from libspm_b200 import synth
+    monkeypatch.setenv("SPMB_HOST_THREADS", str(threads))
+    ctx = sp.Context(0)
+    try:
+        n = 2_000_000
+        ref = synth.text_host(n, 31)
+        ev, pool, kinds = synth.journal(n, 32)
+        pool = synth.finish_snps(ev, pool, kinds, ref[ev["ref_pos"][kinds == 0].astype(np.int64)])
+        ev = ev.copy()
+        # records that do not fit 8 bytes: a 300-symbol deletion, a 260-symbol insertion stored at the END of
+        # the pool (offset delta >= 2^16), and a pool offset that runs backwards
+        big = np.flatnonzero(kinds == 2)[len(ev) // 40]
+        nxt = int(ev["ref_pos"][big + 1])
+        ev["del_len"][big] = 300
+        keep = (ev["ref_pos"] < ev["ref_pos"][big]) | (ev["ref_pos"] >= ev["ref_pos"][big] + 300) | (np.arange(len(ev)) == big)
+        ev = ev[keep]
+        kinds = kinds[keep]
+        ins = np.flatnonzero(kinds == 1)[len(ev) // 30]
+        tail = np.random.default_rng(3).integers(0, 4, size=260, dtype=np.uint8)
+        ev["ins_len"][ins] = 260
+        ev["ins_off"][ins] = len(pool)
+        pool = np.concatenate([pool, tail])
+        back = np.flatnonzero(kinds == 0)[len(ev) // 2]
+        ev["ins_off"][back] = ev["ins_off"][np.flatnonzero(kinds == 0)[0]]
+        assert nxt > 0 and len(ev) * 24 > 65536
+        derived = orc.journal_apply(ref, ev.astype(orc.EVENT_DTYPE), pool)
+        base = sp.Store.from_host(ctx, ref)
+        js = base.journaled(ev, pool)
+        st = ctx.upload_last_stats()
+        n_chunks = (len(ev) + st["events_per_chunk"] - 1) // st["events_per_chunk"]
+        assert st["events_per_chunk"] == 1024
+        assert st["event_raw_chunks"] + st["event_host_packed_chunks"] == n_chunks
+        if threads == 0:
+            assert st["event_host_packed_chunks"] == 0
+        assert len(js) == len(derived)
+        assert np.array_equal(js.read(), derived)
+        pat = derived[len(derived) // 2:len(derived) // 2 + 64].copy()
+        got = sp.search(ctx, js, sp.Pattern(ctx, sp.ALG_SHIFTOR, pat))
+        assert np.array_equal(got["end"], orc.search_mt(2, derived, pat)[1])
+        # an unsorted table is still rejected after the trip through the queue
+        bad = ev.copy()
+        bad["ref_pos"][100] = bad["ref_pos"][5000]
+        with pytest.raises(sp.SpmbError):
+            base.journaled(bad, pool)
+    finally:
+        ctx.close()
