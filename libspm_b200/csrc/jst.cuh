@@ -37,9 +37,12 @@ struct JstWindow {
     uint32_t n_var;
 };
 
-// materialises window texts row by row (one row of a windows-mode store = one window)
-struct WindowSource {
-    const uint2 *__restrict__ base_planes;
+// materialises window texts (one row of a windows-mode store = one window) as lane-chunk words, 32 symbols
+// of a row per call, for pack_chunks_kernel: every maximal run copied from the reference is ONE unaligned
+// 32-symbol fetch from the reference's lane chunks (two 8-byte loads); inserted symbols come from the pool
+// one by one.
+struct WindowChunkSource {
+    const uint2 *__restrict__ base_lanes;
     SpmbLayout base;
     const spmb_journal_event *__restrict__ var;
     const uint8_t *__restrict__ pool;
@@ -48,35 +51,46 @@ struct WindowSource {
     uint64_t n_win;
     SpmbLayout lay; // of the windows store
 
-    __device__ __forceinline__ void load32(uint64_t p0, uint32_t (&w)[8]) const
+    __device__ __forceinline__ uint2 load_chunk(uint64_t p0) const
     {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) w[i] = 0;
         const uint64_t R = spmb_div_rl(lay, p0);
         const uint32_t col0 = (uint32_t)(p0 - R * lay.row_len);
-        if (R >= n_win) return;
+        if (R >= n_win) return make_uint2(0, 0);
         const JstWindow wd = win[R];
-        if (col0 >= wd.len) return;
+        if (col0 >= wd.len) return make_uint2(0, 0);
+        unsigned long long out = 0;
         uint32_t vi = 0;
         uint32_t seg_local = 0;          // local position where the current reference segment starts
         uint64_t seg_ref = wd.ref_start; // reference position at seg_local
-        for (int t = 0; t < 32; ++t) {
+        const uint32_t t_end = min(32u, wd.len - col0);
+        uint32_t t = 0;
+        while (t < t_end) {
             const uint32_t x = col0 + t;
-            if (x >= wd.len) break;
-            uint32_t s = 0;
-            bool found = false;
+            uint32_t lim = col0 + t_end;  // local end (exclusive) of the reference run that starts at x
+            bool inserted = false;
             while (vi < wd.n_var) {
                 const spmb_journal_event v = var[win_vars[wd.var_off + vi]];
                 const uint32_t lv = seg_local + (uint32_t)(v.ref_pos - seg_ref); // alt begins here
-                if (x < lv) break;
-                if (x < lv + v.ins_len) { s = pool[v.ins_off + (x - lv)] & 3u; found = true; break; }
+                if (x < lv) { lim = min(lim, lv); break; }
+                if (x < lv + v.ins_len) {
+                    out |= (unsigned long long)(pool[v.ins_off + (x - lv)] & 3u) << (62 - 2 * t);
+                    ++t;
+                    inserted = true;
+                    break;
+                }
                 seg_local = lv + v.ins_len;
                 seg_ref = v.ref_pos + v.del_len;
                 ++vi;
             }
-            if (!found) s = spmb_symbol_at(base_planes, base, seg_ref + (x - seg_local));
-            w[t >> 2] |= s << (8 * (t & 3));
+            if (inserted) continue;
+            const uint32_t run = lim - x;
+            const uint2 w = spmb_fetch32(base_lanes, base, seg_ref + (x - seg_local));
+            unsigned long long W = ((unsigned long long)w.x << 32) | w.y;
+            if (run < 32) W &= ~(~0ull >> (2 * run)); // keep the first `run` symbols
+            out |= W >> (2 * t);
+            t += run;
         }
+        return make_uint2((uint32_t)(out >> 32), (uint32_t)out);
     }
 };
 

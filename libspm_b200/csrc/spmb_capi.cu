@@ -33,6 +33,8 @@ struct spmb_context {
     int device = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
+    cudaStream_t copy_stream = nullptr;    // counters + short hit lists come back here, behind the launch's event:
+                                           // a later launch already queued on `stream` does not delay them
     std::string err;
     uint32_t launches = 0;
     int sm_count = 0;
@@ -65,6 +67,7 @@ static void context_free(spmb_context *ctx)
     if (ctx->scratch) cudaFree(ctx->scratch);
     for (auto &b : ctx->blocks) cudaFreeAsync(b.p, ctx->stream);
     ctx->blocks.clear();
+    if (ctx->copy_stream) { cudaStreamSynchronize(ctx->copy_stream); cudaStreamDestroy(ctx->copy_stream); }
     if (ctx->own_stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
     if (ctx->h_count) cudaFreeHost(ctx->h_count);
     if (ctx->h_spec) cudaFreeHost(ctx->h_spec);
@@ -139,6 +142,8 @@ struct spmb_hits {
     const spmb_store *pend_store = nullptr;
     const spmb_pattern *pend_pat = nullptr;
     bool spec_done = false;                // hits_collect already brought the (short) raw list to `host`
+    cudaEvent_t done = nullptr;            // recorded behind the kernels of spmb_search_launch
+    bool done_armed = false;
 };
 
 struct spmb_stream {
@@ -213,6 +218,7 @@ extern "C" int spmb_context_create(int device, void *stream, spmb_context **out)
         if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return SPMB_ERR_CUDA; }
         ctx->own_stream = true;
     }
+    if (cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess) { cudaGetLastError(); ctx->copy_stream = nullptr; }
     cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
     {
         cudaMemPool_t pool;
@@ -919,6 +925,7 @@ extern "C" int spmb_hits_create(spmb_context *ctx, uint64_t capacity_hint, spmb_
     if (e != cudaSuccess) { delete h; return set_err(ctx, SPMB_ERR_OOM, "cudaMalloc(hit counter)", e); }
     int rc = hits_reserve(ctx, h, capacity_hint ? capacity_hint : (1ull << 16));
     if (rc) { cudaFree(h->d_count); delete h; return rc; }
+    if (cudaEventCreateWithFlags(&h->done, cudaEventDisableTiming) != cudaSuccess) { cudaGetLastError(); h->done = nullptr; }
     *out = h;
     return SPMB_OK;
 }
@@ -930,6 +937,7 @@ extern "C" int spmb_hits_destroy(spmb_hits *h)
     cudaFree(h->d_hits);
     cudaFree(h->d_count);
     cudaFree(h->d_cand);
+    if (h->done) cudaEventDestroy(h->done);
     delete h;
     return SPMB_OK;
 }
@@ -1161,7 +1169,10 @@ extern "C" int spmb_search_launch(spmb_context *ctx, const spmb_store *s, const 
     ctx->launches = 0;
     h->pend_store = s;
     h->pend_pat = p;
-    return enqueue_search(ctx, s, p, h);
+    int rc = enqueue_search(ctx, s, p, h);
+    h->done_armed = rc == SPMB_OK && h->done && ctx->copy_stream &&
+                    cudaEventRecord(h->done, ctx->stream) == cudaSuccess;
+    return rc;
 }
 
 static bool hit_less(const spmb_hit &a, const spmb_hit &b)
@@ -1289,11 +1300,19 @@ static int hits_collect(spmb_context *ctx, spmb_hits *h, std::vector<spmb_hit> &
 {
     h->spec_done = false;
     for (int attempt = 0; attempt < 5; ++attempt) {
-        CU(cudaMemcpyAsync(ctx->h_count, h->d_count, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+        // the first look at a launched search goes through the copy stream, ordered behind the launch's event
+        // only: launches of other hit lists that were queued meanwhile keep running
+        cudaStream_t cs = ctx->stream;
+        if (h->done_armed) {
+            h->done_armed = false;
+            if (cudaStreamWaitEvent(ctx->copy_stream, h->done, 0) == cudaSuccess) cs = ctx->copy_stream;
+            else cudaGetLastError();
+        }
+        CU(cudaMemcpyAsync(ctx->h_count, h->d_count, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, cs));
         // short lists (the common case) ride along with the counters: one synchronisation instead of two
         const unsigned long long n_spec = std::min<unsigned long long>(h->cap, SPEC_HITS);
-        if (n_spec) CU(cudaMemcpyAsync(ctx->h_spec, h->d_hits, n_spec * sizeof(spmb_hit), cudaMemcpyDeviceToHost, ctx->stream));
-        CU(cudaStreamSynchronize(ctx->stream));
+        if (n_spec) CU(cudaMemcpyAsync(ctx->h_spec, h->d_hits, n_spec * sizeof(spmb_hit), cudaMemcpyDeviceToHost, cs));
+        CU(cudaStreamSynchronize(cs));
         const unsigned long long cnt = ctx->h_count[0];
         const unsigned long long cand = std::max(ctx->h_count[1], ctx->h_count[2]);
         if (cnt <= h->cap && cand <= h->cand_cap) {
@@ -1515,6 +1534,8 @@ static int jst_prepare(spmb_context *ctx, spmb_jst *j, uint32_t W)
                 std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - th0).count());
     };
     if (nw) {
+        int rcl = store_ensure_lanes(ctx, j->ref); // the window gather reads the reference's lane chunks
+        if (rcl) { cudaEventDestroy(e0); cudaEventDestroy(e1); return rcl; }
         // windows sorted by length; a row holds len symbols + up to 31 pad columns for the Myers score delay
         {   // stable counting sort on the length (a comparison sort of millions of 32-byte records costs 0.2 s)
             uint32_t max_len = 0;
@@ -1557,10 +1578,20 @@ static int jst_prepare(spmb_context *ctx, spmb_jst *j, uint32_t W)
             CU(cudaMemcpy(b.store->row_len, rl.data(), rows * 4, cudaMemcpyHostToDevice));
             CU(cudaMemcpy(b.store->row_own, ro.data(), rows * 4, cudaMemcpyHostToDevice));
             CU(cudaMemcpy(b.store->row_seq, rs.data(), rows * 4, cudaMemcpyHostToDevice));
-            WindowSource src{j->ref->planes, j->ref->lay, j->d_var, j->d_pool, j->d_win + first, j->d_win_vars, count, b.store->lay};
             lap("bucket rows up");
-            rc = store_pack(ctx, b.store, src);
-            if (rc) { cudaEventDestroy(e0); cudaEventDestroy(e1); return rc; }
+            {
+                // windows are gathered from the reference's lane chunks; the bucket's own lane chunks (what the
+                // windows-mode Myers kernels read) fall out of the same pass
+                uint2 *l = nullptr;
+                if (big_alloc(ctx, b.store->bytes, (void **)&l) != cudaSuccess) { cudaGetLastError(); l = nullptr; }
+                WindowChunkSource src{j->ref->lanes, j->ref->lay, j->d_var, j->d_pool, j->d_win + first, j->d_win_vars, count, b.store->lay};
+                pack_chunks_kernel<WindowChunkSource><<<(unsigned)(b.store->lay.n_cols_alloc / 1024), 1024, 0, ctx->stream>>>(
+                    src, b.store->lay, b.store->planes, l);
+                ctx->launches++;
+                b.store->lanes = l;
+                cudaError_t ek = cudaGetLastError();
+                if (ek != cudaSuccess) { cudaEventDestroy(e0); cudaEventDestroy(e1); return set_err(ctx, SPMB_ERR_CUDA, "window materialisation", ek); }
+            }
             lap("bucket pack kernel");
             first = last;
         }

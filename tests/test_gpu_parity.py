@@ -360,3 +360,35 @@ def test_exact_large_store(ctx, n, rl, m):
     ctx.set_shard(0, 1)
     _diff(np.sort(np.concatenate(parts)), want, f"large store sharded n={n} rl={RL} m={m}")
     p.close(); st.close()
+
+
+def test_pipelined_launch_finish_two_hit_lists(ctx):
+    """spmb_search_launch / spmb_search_finish interleaved over two hit lists (launch i+1 is queued before
+    the hits of i are collected): every list equals the one-call result -- short lists (counters + hits in
+    one copy), lists longer than the speculative copy, and a list that outgrows its buffer."""
+    rng = np.random.default_rng(404)
+    text = rand_text(rng, 3_000_000)
+    store = sp.Store.from_host(ctx, text)
+    pats = []
+    for i in range(6):
+        p = text[100_000 * (i + 1):100_000 * (i + 1) + 48].copy()
+        for c in range(3 + 700 * (i % 3)):                      # 3, 703, 1403 planted copies
+            pos = int(rng.integers(0, len(text) - 64))
+            text[pos:pos + 48] = p
+        pats.append(p)
+    store.close()
+    store = sp.Store.from_host(ctx, text)
+    pm = [sp.Pattern(ctx, sp.ALG_SHIFTOR if i % 2 else sp.ALG_MYERS, p, 0 if i % 2 else 2) for i, p in enumerate(pats)]
+    want = [sp.search(ctx, store, p).copy() for p in pm]
+    ha, hb = sp.Hits(ctx, 16), sp.Hits(ctx, 1 << 12)            # ha starts too small: regrowth inside finish
+    hl = (ha, hb)
+    sp.search_launch(ctx, store, pm[0], hl[0])
+    for i in range(len(pm)):
+        if i + 1 < len(pm):
+            sp.search_launch(ctx, store, pm[i + 1], hl[(i + 1) & 1])
+        got = sp.search_finish(ctx, hl[i & 1])
+        assert len(got) == len(want[i]) and len(got) >= 1
+        for f in ("end", "errors", "pattern_id", "seq_id"):
+            assert np.array_equal(got[f], want[i][f]), (i, f)
+    assert max(len(w) for w in want) > 1024 and min(len(w) for w in want) < 16
+    ha.close(); hb.close(); store.close()
