@@ -201,6 +201,34 @@ public:
     spmb_store *handle() const noexcept { return _store.get(); }
 };
 
+// journaled string tree (north_star items 1-2): a reference, its variants and the haplotype coverage.
+// matcher(tree, callback) reports every hit of every haplotype, cursor.sequence_id() = haplotype,
+// endPosition in that haplotype's coordinates -- what an external JST traverser computes by sizing branch
+// contexts with spm::window_size and running the matcher on each (concept.hpp:27-50).
+class journaled_string_tree {
+    device_sequence _reference;
+    std::shared_ptr<spmb_jst> _jst;
+    std::uint32_t _n_haplotypes{0};
+public:
+    struct jst_deleter { void operator()(spmb_jst *j) const noexcept { spmb_jst_destroy(j); } };
+    journaled_string_tree() = default;
+    // variants sorted by ref_pos (insertions first on ties); coverage: one row of ceil(n_haplotypes/64)
+    // 64-bit words per variant, bit h set = haplotype h carries the variant
+    journaled_string_tree(device_sequence reference, const std::vector<spmb_journal_event> &variants,
+                          const std::vector<std::uint8_t> &pool, const std::vector<std::uint64_t> &coverage,
+                          std::uint32_t n_haplotypes)
+        : _reference{std::move(reference)}, _n_haplotypes{n_haplotypes} {
+        auto &d = detail::device();
+        spmb_jst *j = nullptr;
+        detail::check(spmb_jst_create(d.ctx, _reference.handle(), variants.data(), variants.size(), pool.data(), pool.size(),
+                                      coverage.data(), n_haplotypes, &j), d.ctx, "spmb_jst_create");
+        _jst.reset(j, jst_deleter{});
+    }
+    std::uint32_t haplotype_count() const noexcept { return _n_haplotypes; }
+    const device_sequence &reference() const noexcept { return _reference; }
+    spmb_jst *handle() const noexcept { return _jst.get(); }
+};
+
 // ------------------------------------------------------------------------------------------
 // CPOs (concept.hpp:27-102): member-function dispatch is all the new matchers need
 // ------------------------------------------------------------------------------------------
@@ -276,7 +304,8 @@ public:
     // matcher(haystack, callback): every hit, ascending, callback(cursor) per hit
     // (seqan_pattern_base.hpp:40-52).  Non-const like the reference.
     template <std::ranges::viewable_range haystack_t, typename callback_t>
-        requires (!std::same_as<std::remove_cvref_t<haystack_t>, device_sequence>)
+        requires (!std::same_as<std::remove_cvref_t<haystack_t>, device_sequence> &&
+                  !std::same_as<std::remove_cvref_t<haystack_t>, journaled_string_tree>)
     void operator()(haystack_t &&haystack, callback_t &&callback) {
         auto &d = detail::device();
         detail::rank_buffer<haystack_t> buf{std::forward<haystack_t>(haystack)};
@@ -289,6 +318,14 @@ public:
     void operator()(const device_sequence &haystack, callback_t &&callback) {
         auto &d = detail::device();
         detail::check(spmb_search(d.ctx, haystack.handle(), _pattern.get(), d.hits), d.ctx, "spmb_search");
+        replay(std::forward<callback_t>(callback));
+    }
+
+    // same call over a journaled string tree: hits of all haplotypes, ordered by (haplotype, end)
+    template <typename callback_t>
+    void operator()(const journaled_string_tree &tree, callback_t &&callback) {
+        auto &d = detail::device();
+        detail::check(spmb_jst_search(d.ctx, tree.handle(), _pattern.get(), d.hits), d.ctx, "spmb_jst_search");
         replay(std::forward<callback_t>(callback));
     }
 

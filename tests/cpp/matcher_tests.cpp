@@ -142,6 +142,49 @@ MINI_TEST(empty_needle_and_haystack) {
     EXPECT_EQ(calls, 0);
 }
 
+// journaled sequence + journaled string tree behind the same matcher call: the hits of every haplotype
+// equal the matcher run over that haplotype's materialised text
+MINI_TEST(journaled_string_tree_equals_per_haplotype_search) {
+    // variants over the shared fixture (ACGTGACTAGCACGTGACTAGC...): SNP G->T at 12, insertion "CA" at 20,
+    // deletion of 2 at 30; pool = T, C, A
+    const std::vector<spmb_journal_event> variants{{12, 1, 1, 0}, {20, 0, 2, 1}, {30, 2, 0, 0}};
+    const std::vector<std::uint8_t> pool{3, 1, 0};
+    // haplotype 0: none, 1: SNP, 2: insertion + deletion, 3: all three
+    const std::vector<std::uint64_t> coverage{0b1010, 0b1100, 0b1100};
+    spm::device_sequence reference{haystack};
+    spm::journaled_string_tree tree{reference, variants, pool, coverage, 4};
+    EXPECT_EQ(tree.haplotype_count(), 4u);
+    auto apply = [&](unsigned h) {
+        sequence_t out{};
+        std::size_t r = 0;
+        for (std::size_t v = 0; v < variants.size(); ++v) {
+            if (!((coverage[v] >> h) & 1u)) continue;
+            for (; r < variants[v].ref_pos; ++r) out.push_back(haystack[r]);
+            for (std::uint32_t i = 0; i < variants[v].ins_len; ++i) { spm::dna4 s{}; s.assign_rank(pool[variants[v].ins_off + i]); out.push_back(s); }
+            r += variants[v].del_len;
+        }
+        for (; r < haystack.size(); ++r) out.push_back(haystack[r]);
+        return out;
+    };
+    for (int pass = 0; pass < 2; ++pass) {
+        std::vector<std::vector<std::size_t>> got(4), want(4);
+        if (pass == 0) {
+            auto matcher = spm::shiftor_matcher{needle};
+            matcher(tree, [&](auto const &f) { got[f.sequence_id()].push_back(seqan2::endPosition(f)); });
+            for (unsigned h = 0; h < 4; ++h) matcher(apply(h), [&](auto const &f) { want[h].push_back(seqan2::endPosition(f)); });
+        } else {
+            auto matcher = spm::myers_matcher{needle, 1};
+            matcher(tree, [&](auto const &f) { got[f.sequence_id()].push_back(seqan2::endPosition(f)); });
+            for (unsigned h = 0; h < 4; ++h) matcher(apply(h), [&](auto const &f) { want[h].push_back(seqan2::endPosition(f)); });
+        }
+        for (unsigned h = 0; h < 4; ++h) EXPECT_TRUE(std::ranges::equal(got[h], want[h]));
+        EXPECT_TRUE(!want[0].empty());
+    }
+    // the journaled sequence of haplotype 3 as a device-resident haystack
+    auto h3 = reference.journaled(variants, pool);
+    EXPECT_EQ(h3.size(), apply(3).size());
+}
+
 // ---- pigeonhole_matcher_test.cpp:19-86 ----
 using needle_position_t = seqan2::PigeonholeSeedOnlyPosition;
 static const sequence_t needle2 = "TGACTAGCAC"_dna4;
