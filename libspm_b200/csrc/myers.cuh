@@ -45,6 +45,7 @@ struct MyersArgs {
     // unknown into SHF/LEA, so the symbol pop and the table address are IMADs on the FMA pipe,
     // which runs in the shadow of the ALU pipe the recurrence saturates (tools/ubench_pipes.cu)
     uint32_t mul4, eq_stride;
+    uint32_t split;           // myers_cut_kernel, plain mode: pieces per row (>= 1)
     HitSink sink;
 };
 

@@ -22,6 +22,7 @@
 #include "jst.cuh"
 #include "layout.cuh"
 #include "myers.cuh"
+#include "myers_cut.cuh"
 #include "pack.cuh"
 #include "pigeon.cuh"
 #include "upload.cuh"
@@ -949,20 +950,36 @@ extern "C" const spmb_hit *spmb_hits_data(const spmb_hits *h) { return (h && !h-
 // search
 // ------------------------------------------------------------------------------------------
 template <int MODE>
-static cudaError_t launch_myers(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p, const MyersArgs &a)
+static cudaError_t launch_myers(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p, const MyersArgs &a_in)
 {
     (void)s;
-    if (a.st1 <= a.st0) return cudaSuccess;
-    dim3 grid((unsigned)((a.st1 - a.st0 + 3) / 4), p->n_pat);
+    if (a_in.st1 <= a_in.st0) return cudaSuccess;
+    // needles of two words and more run the cut-off form (myers_cut.cuh); SPMB_MYERS_FULL=1 keeps the
+    // full recurrence for A/B measurements
+    static const bool full = [] { const char *e = getenv("SPMB_MYERS_FULL"); return e && *e && *e != '0'; }();
+    const bool cut = p->NW >= 2 && !full;
+    static const int split_env = [] { const char *e = getenv("SPMB_MYERS_SPLIT"); return e ? atoi(e) : 0; }();
+    MyersArgs a = a_in;
+    a.split = 1;
+    if (cut && MODE == SPMB_MODE_PLAIN) {
+        // pieces per row (SPMB_MYERS_SPLIT): measured on B200 at 1 / 2 / 3 pieces (6 / 12 / 18 warps per
+        // scheduler), the gain per column (6-8 %) only pays for the extra warm-up, so the default is 1
+        uint32_t sp = split_env > 0 ? (uint32_t)split_env : 1u;
+        const uint32_t max_sp = a.lay.row_len / (4 * (a.warm + 32)); // keep the warm-up below a quarter of a piece
+        if (sp > max_sp) sp = max_sp;
+        if (sp < 1) sp = 1;
+        a.split = sp;
+    }
+    dim3 grid((unsigned)(((a.st1 - a.st0) * a.split + 3) / 4), p->n_pat);
+#define SPMB_MYERS_CASE(nw)                                                                       \
+    case nw:                                                                                      \
+        if (cut) myers_cut_kernel<(nw < 2 ? 2 : nw), MODE><<<grid, 128, 0, ctx->stream>>>(a);      \
+        else myers_kernel<nw, MODE><<<grid, 128, 0, ctx->stream>>>(a);                            \
+        break;
     switch (p->NW) {
-    case 1: myers_kernel<1, MODE><<<grid, 128, 0, ctx->stream>>>(a); break;
-    case 2: myers_kernel<2, MODE><<<grid, 128, 0, ctx->stream>>>(a); break;
-    case 3: myers_kernel<3, MODE><<<grid, 128, 0, ctx->stream>>>(a); break;
-    case 4: myers_kernel<4, MODE><<<grid, 128, 0, ctx->stream>>>(a); break;
-    case 5: myers_kernel<5, MODE><<<grid, 128, 0, ctx->stream>>>(a); break;
-    case 6: myers_kernel<6, MODE><<<grid, 128, 0, ctx->stream>>>(a); break;
-    case 7: myers_kernel<7, MODE><<<grid, 128, 0, ctx->stream>>>(a); break;
-    case 8: myers_kernel<8, MODE><<<grid, 128, 0, ctx->stream>>>(a); break;
+    SPMB_MYERS_CASE(1) SPMB_MYERS_CASE(2) SPMB_MYERS_CASE(3) SPMB_MYERS_CASE(4)
+    SPMB_MYERS_CASE(5) SPMB_MYERS_CASE(6) SPMB_MYERS_CASE(7) SPMB_MYERS_CASE(8)
+#undef SPMB_MYERS_CASE
     default: return cudaErrorInvalidValue;
     }
     ctx->launches++;
