@@ -403,21 +403,40 @@ def bench_myers(sp, synth, torch, ctx, dev, stream, hits, args, rank, world, hbm
     with ClockSampler(torch.cuda.current_device()) as clk:
         total_ms, kern_ms, n_hits, launches = time_search(sp, torch, ctx, stream, store, pattern, hits, args.steps,
                                                           args.warmup, flush=flush)
+    # the same search with the full recurrence (all ceil(m/32) words every column): the kernel the INT-pipe
+    # roofline is stated on; the default above is its Ukkonen cut-off form (myers_cut.cuh)
+    ctx.set_myers_cutoff(False)
+    full_total_ms, full_kern_ms, full_hits, _ = time_search(sp, torch, ctx, stream, store, pattern, hits, args.steps,
+                                                            args.warmup, flush=flush)
+    ctx.set_myers_cutoff(True)
     if world > 1:
-        t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
+        t = torch.tensor([total_ms, full_total_ms], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total_ms = float(t.item())
+        total_ms, full_total_ms = float(t[0].item()), float(t[1].item())
     peak = ctx.measure_int_peak()
     ops = myers_ops_per_bp(m)
-    achieved = n * ops / (kern_ms * 1e-3) / 1e9
+    ops_cut = 11            # one active word: 10 for the column update + the symbol pop (state of a warp on random text)
+    achieved = n * ops / (full_kern_ms * 1e-3) / 1e9
+    achieved_cut = n * ops_cut / (kern_ms * 1e-3) / 1e9
     res = {"workload": f"C3: Myers m={m} k={k} over {n} bp per GPU, 1000 planted mutated copies",
            "value": world * n * args.steps / (total_ms * 1e-3) / 1e9, "unit": "Gbp/s", "ms_per_step": total_ms / args.steps,
-           "kernel_ms": kern_ms, "hits": n_hits, "row_len": store.row_len, "l2": "256 MB flush write between iterations",
-           "roofline": {"bound": "int_alu", "achieved": achieved, "peak": peak["lop3_gops"], "unit": "Ginstr/s",
-                        "frac": achieved / peak["lop3_gops"], "traffic": ncu_traffic("myers_c3"),
+           "kernel_ms": kern_ms, "kernel_gbp_per_s": n / kern_ms / 1e6, "kernel": "myers_cut_kernel<4,plain>",
+           "hits": n_hits, "row_len": store.row_len, "l2": "256 MB flush write between iterations",
+           "roofline": {"bound": "int_alu", "achieved": achieved_cut, "peak": peak["lop3_gops"], "unit": "Ginstr/s",
+                        "frac": achieved_cut / peak["lop3_gops"], "traffic": ncu_traffic("myers_cut_c3"),
                         "peak_source": "measured live: spmb_measure_int_peak (LOP3 chains, all SMs)",
-                        "int_peak_iadd3": peak["iadd3_gops"], "algorithmic_int32_instr_per_bp": ops,
-                        "kernel": "myers_kernel<4,plain>"},
+                        "int_peak_iadd3": peak["iadd3_gops"], "algorithmic_int32_instr_per_bp": ops_cut,
+                        "note": "cut-off kernel: a warp updates only the words that can hold a cell <= k; 11 = one word "
+                                "(10) + symbol pop, the state of >= 99.9 % of the 8-column chunks on random DNA at k=4",
+                        "kernel": "myers_cut_kernel<4,plain>"},
+           "full_recurrence": {"value": world * n * args.steps / (full_total_ms * 1e-3) / 1e9, "unit": "Gbp/s",
+                               "kernel_ms": full_kern_ms, "kernel_gbp_per_s": n / full_kern_ms / 1e6,
+                               "hits_equal_cutoff": bool(full_hits == n_hits),
+                               "roofline": {"bound": "int_alu", "achieved": achieved, "peak": peak["lop3_gops"],
+                                            "unit": "Ginstr/s", "frac": achieved / peak["lop3_gops"],
+                                            "traffic": ncu_traffic("myers_c3"),
+                                            "algorithmic_int32_instr_per_bp": ops, "kernel": "myers_kernel<4,plain>"}},
+           "speedup_cutoff_vs_full_kernel": full_kern_ms / kern_ms,
            "clocks": clk.summary()}
     if rank == 0 and world == 1 and not args.no_cpu:
         import oracle as orc

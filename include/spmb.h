@@ -100,6 +100,13 @@ int spmb_context_trim(spmb_context *ctx);
  * concatenates the small hit lists afterwards.  Default (0, 1) = everything. */
 int spmb_context_set_shard(spmb_context *ctx, uint32_t shard, uint32_t n_shards);
 
+/* SPMB_ALG_MYERS with needles longer than 32 symbols runs the Ukkonen cut-off form of the column update
+ * (what SeqAn2's _findMyersLargePatterns does with `lastBlock`; reached from myers_matcher.hpp:47-49 for
+ * such needles): only the 32-row words that can still hold a cell <= k are updated.  Same hit list.
+ * enabled = 0 selects the full recurrence over all ceil(m/32) words (the kernel the INT-pipe roofline of
+ * DESIGN.md 4 is stated on); default 1, or 0 when the environment has SPMB_MYERS_FULL=1. */
+int spmb_context_set_myers_cutoff(spmb_context *ctx, int enabled);
+
 /* ---------------- sequence store (north_star item 1) ----------------
  * Replaces the haystack argument of seqan_pattern_base::operator()
  * (seqan_pattern_base.hpp:40-47, wrapped by spm::seqan_container_adapter,

@@ -43,7 +43,7 @@ EXPORTS = [
     "spmb_fasta_unknown_symbols", "spmb_vcf_read", "spmb_vcf_destroy", "spmb_vcf_variant_count", "spmb_vcf_variants",
     "spmb_vcf_pool", "spmb_vcf_coverage", "spmb_vcf_haplotype_count", "spmb_vcf_sample_count", "spmb_vcf_sample_name",
     "spmb_vcf_stats",
-    "spmb_context_set_shard", "spmb_pigeonhole_create", "spmb_pattern_filter_info", "spmb_search_anchored",
+    "spmb_context_set_shard", "spmb_context_set_myers_cutoff", "spmb_pigeonhole_create", "spmb_pattern_filter_info", "spmb_search_anchored",
     "spmb_upload_last_stats", "spmb_host_pack_chunks", "spmb_context_trim",
 ]
 
@@ -81,6 +81,7 @@ def lib():
             "spmb_context_sync": (i32, [vp]),
             "spmb_context_trim": (i32, [vp]),
             "spmb_context_set_shard": (i32, [vp, u32, u32]),
+            "spmb_context_set_myers_cutoff": (i32, [vp, i32]),
             "spmb_store_create": (i32, [vp, vp, u64, u32, pp]),
             "spmb_store_create_from_device": (i32, [vp, vp, u64, u32, pp]),
             "spmb_upload_last_stats": (i32, [vp, C.POINTER(u64 * 8)]),
@@ -185,6 +186,10 @@ class Context:
     def trim(self):
         """release cached scratch / upload threads / pool memory (spmb_context_trim)."""
         self._check(lib().spmb_context_trim(self._h), "spmb_context_trim")
+
+    def set_myers_cutoff(self, enabled: bool):
+        """Ukkonen cut-off for multi-word Myers needles (default on); off = the full recurrence."""
+        self._check(lib().spmb_context_set_myers_cutoff(self._h, 1 if enabled else 0), "spmb_context_set_myers_cutoff")
 
     def set_shard(self, shard: int, n_shards: int):
         """later searches cover only this shard (contiguous super-tile range) of every store."""

@@ -41,6 +41,7 @@ struct spmb_context {
     int sm_count = 0;
     unsigned long long *h_count = nullptr; // pinned (8 slots)
     spmb_hit *h_spec = nullptr;            // pinned: the first SPEC_HITS hits travel with the counters (one round trip)
+    bool myers_cutoff = true;              // spmb_context_set_myers_cutoff
     uint32_t shard = 0, n_shards = 1;      // searches cover super-tiles [n_st*shard/n, n_st*(shard+1)/n)
     // stores / patterns / hit lists / streams / JSTs keep a raw pointer to their context: the
     // context outlives them (a destroy() with live children is deferred until the last one goes)
@@ -142,6 +143,7 @@ struct spmb_hits {
     uint64_t count = 0;
     const spmb_store *pend_store = nullptr;
     const spmb_pattern *pend_pat = nullptr;
+    cudaStream_t collect_stream = nullptr; // the stream hits_collect last read this list on (copy stream or the context's)
     bool spec_done = false;                // hits_collect already brought the (short) raw list to `host`
     cudaEvent_t done = nullptr;            // recorded behind the kernels of spmb_search_launch
     bool done_armed = false;
@@ -251,6 +253,13 @@ extern "C" int spmb_context_destroy(spmb_context *ctx)
 extern "C" void *spmb_context_stream(const spmb_context *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
 extern "C" const char *spmb_last_error(const spmb_context *ctx) { return ctx ? ctx->err.c_str() : "null context"; }
 extern "C" uint32_t spmb_last_launch_count(const spmb_context *ctx) { return ctx ? ctx->launches : 0; }
+
+extern "C" int spmb_context_set_myers_cutoff(spmb_context *ctx, int enabled)
+{
+    if (!ctx) return SPMB_ERR_ARG;
+    ctx->myers_cutoff = enabled != 0;
+    return SPMB_OK;
+}
 
 extern "C" int spmb_context_set_shard(spmb_context *ctx, uint32_t shard, uint32_t n_shards)
 {
@@ -957,7 +966,7 @@ static cudaError_t launch_myers(spmb_context *ctx, const spmb_store *s, const sp
     // needles of two words and more run the cut-off form (myers_cut.cuh); SPMB_MYERS_FULL=1 keeps the
     // full recurrence for A/B measurements
     static const bool full = [] { const char *e = getenv("SPMB_MYERS_FULL"); return e && *e && *e != '0'; }();
-    const bool cut = p->NW >= 2 && !full;
+    const bool cut = p->NW >= 2 && !full && ctx->myers_cutoff;
     static const int split_env = [] { const char *e = getenv("SPMB_MYERS_SPLIT"); return e ? atoi(e) : 0; }();
     MyersArgs a = a_in;
     a.split = 1;
@@ -1325,6 +1334,7 @@ static int hits_collect(spmb_context *ctx, spmb_hits *h, std::vector<spmb_hit> &
             if (cudaStreamWaitEvent(ctx->copy_stream, h->done, 0) == cudaSuccess) cs = ctx->copy_stream;
             else cudaGetLastError();
         }
+        h->collect_stream = cs;
         CU(cudaMemcpyAsync(ctx->h_count, h->d_count, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, cs));
         // short lists (the common case) ride along with the counters: one synchronisation instead of two
         const unsigned long long n_spec = std::min<unsigned long long>(h->cap, SPEC_HITS);
@@ -1341,9 +1351,9 @@ static int hits_collect(spmb_context *ctx, spmb_hits *h, std::vector<spmb_hit> &
             }
             if (count_only) { *count_only = cnt; return SPMB_OK; } // the hits stay on the device for now
             raw.resize(cnt);
-            if (cnt) {
-                CU(cudaMemcpyAsync(raw.data(), h->d_hits, cnt * sizeof(spmb_hit), cudaMemcpyDeviceToHost, ctx->stream));
-                CU(cudaStreamSynchronize(ctx->stream));
+            if (cnt) { // on the stream of the first look: a later launch queued on the context's stream does not delay it
+                CU(cudaMemcpyAsync(raw.data(), h->d_hits, cnt * sizeof(spmb_hit), cudaMemcpyDeviceToHost, cs));
+                CU(cudaStreamSynchronize(cs));
             }
             return SPMB_OK;
         }
@@ -1374,8 +1384,9 @@ extern "C" int spmb_search_finish(spmb_context *ctx, spmb_hits *h)
     if (!done) {
         h->host.resize(cnt);
         if (cnt && !h->spec_done) {
-            CU(cudaMemcpyAsync(h->host.data(), h->d_hits, cnt * sizeof(spmb_hit), cudaMemcpyDeviceToHost, ctx->stream));
-            CU(cudaStreamSynchronize(ctx->stream));
+            cudaStream_t cs = h->collect_stream ? h->collect_stream : ctx->stream;
+            CU(cudaMemcpyAsync(h->host.data(), h->d_hits, cnt * sizeof(spmb_hit), cudaMemcpyDeviceToHost, cs));
+            CU(cudaStreamSynchronize(cs));
         }
         hits_order(h->host, p->alg);
     }

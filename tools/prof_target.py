@@ -31,7 +31,12 @@ with torch.cuda.stream(stream):
         p = sp.Pattern(ctx, sp.ALG_MYERS, pat, 4)
         for _ in range(6):
             h = sp.search(ctx, st, p, hits)
-        print("myers hits", len(h), "row_len", st.row_len)
+        print("myers (cut-off) hits", len(h), "row_len", st.row_len)
+        ctx.set_myers_cutoff(False)      # the full recurrence: myers_kernel<4,plain>
+        for _ in range(6):
+            h = sp.search(ctx, st, p, hits)
+        ctx.set_myers_cutoff(True)
+        print("myers (full recurrence) hits", len(h))
         st.close()
     if what == "filter":
         # C5 shape: 10k patterns of 100 bp, k=3 through the pigeonhole seed filter
