@@ -136,6 +136,17 @@ int spmb_store_create_journaled(spmb_context *ctx, const spmb_store *base,
                                 const spmb_journal_event *events, uint64_t n_events,
                                 const uint8_t *ins_pool, uint64_t pool_len, uint32_t row_len,
                                 spmb_store **out);
+/* 4-bit alphabets: spm::dna5 (ranks 0..4) and spm::dna15 (ranks 0..14), libspm/libspm/seqan/alphabet.hpp:119-120
+ * (seqan2::BitsPerValue = 3 / 4, :107-112).  One symbol = one byte holding the rank, as for dna4; on the device
+ * the sequence is TWO plane pairs in the dna4 geometry (bits 1..0 and bits 3..2 of every rank): 0.5 B per bp.
+ * bits = 3 or 4 (both stored as 4; 2 forwards to the dna4 entry point).  Such a store is searched with
+ * patterns from spmb_pattern_create_wide (SPMB_ALG_HORSPOOL / SHIFTOR / MYERS); mixing widths is SPMB_ERR_ARG;
+ * journals, the JST, streams, the seed filter and the prefix matcher stay dna4-only (SPMB_ERR_UNSUPPORTED). */
+int spmb_store_create_wide(spmb_context *ctx, const uint8_t *host_ranks, uint64_t n, uint32_t bits,
+                           uint32_t row_len, spmb_store **out);
+int spmb_store_create_wide_from_device(spmb_context *ctx, const uint8_t *dev_ranks, uint64_t n, uint32_t bits,
+                                       uint32_t row_len, spmb_store **out);
+uint32_t spmb_store_symbol_bits(const spmb_store *s); /* 2 or 4 */
 int spmb_store_destroy(spmb_store *s);
 uint64_t spmb_store_length(const spmb_store *s);
 uint32_t spmb_store_row_len(const spmb_store *s);
@@ -151,6 +162,10 @@ int spmb_store_read(spmb_context *ctx, const spmb_store *s, uint64_t begin, uint
  * The needle is copied (the reference only views it). */
 int spmb_pattern_create(spmb_context *ctx, int alg, const uint8_t *ranks, uint32_t m, uint32_t k,
                         spmb_pattern **out);
+/* the same constructors over a 4-bit alphabet (needle ranks 0..15; bits = 3 or 4) */
+int spmb_pattern_create_wide(spmb_context *ctx, int alg, const uint8_t *ranks, uint32_t m, uint32_t k,
+                             uint32_t bits, spmb_pattern **out);
+uint32_t spmb_pattern_symbol_bits(const spmb_pattern *p); /* 2 or 4 */
 /* a set of n_patterns needles searched in one pass (config C5); lengths[i] symbols each,
  * concatenated in ranks.  All must share ceil(len/32) for SPMB_ALG_MYERS. */
 int spmb_pattern_set_create(spmb_context *ctx, int alg, const uint8_t *ranks,
@@ -194,6 +209,9 @@ int spmb_search(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p, s
 /* the reference's call shape with a HOST haystack: upload + pack + search + hits back. */
 int spmb_search_host(spmb_context *ctx, const uint8_t *host_ranks, uint64_t n,
                      const spmb_pattern *p, spmb_hits *h);
+/* the same with a host haystack over a 4-bit alphabet (bits = 3 or 4) and a spmb_pattern_create_wide pattern */
+int spmb_search_host_wide(spmb_context *ctx, const uint8_t *host_ranks, uint64_t n, uint32_t bits,
+                          const spmb_pattern *p, spmb_hits *h);
 /* SPMB_ALG_MYERS_PREFIX with many anchors (what a seed-and-extend caller of
  * restorable_myers_prefix_matcher does, one matcher call per seed): the needle(s) are aligned to the
  * prefixes of the text starting at every anchors[i] (host array of text positions), scan clamped to

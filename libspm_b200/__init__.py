@@ -45,6 +45,8 @@ EXPORTS = [
     "spmb_vcf_stats",
     "spmb_context_set_shard", "spmb_context_set_myers_cutoff", "spmb_pigeonhole_create", "spmb_pattern_filter_info", "spmb_search_anchored",
     "spmb_upload_last_stats", "spmb_host_pack_chunks", "spmb_context_trim",
+    "spmb_store_create_wide", "spmb_store_create_wide_from_device", "spmb_store_symbol_bits",
+    "spmb_pattern_create_wide", "spmb_pattern_symbol_bits", "spmb_search_host_wide",
 ]
 
 
@@ -84,6 +86,12 @@ def lib():
             "spmb_context_set_myers_cutoff": (i32, [vp, i32]),
             "spmb_store_create": (i32, [vp, vp, u64, u32, pp]),
             "spmb_store_create_from_device": (i32, [vp, vp, u64, u32, pp]),
+            "spmb_store_create_wide": (i32, [vp, vp, u64, u32, u32, pp]),
+            "spmb_store_create_wide_from_device": (i32, [vp, vp, u64, u32, u32, pp]),
+            "spmb_store_symbol_bits": (u32, [vp]),
+            "spmb_pattern_create_wide": (i32, [vp, i32, vp, u32, u32, u32, pp]),
+            "spmb_pattern_symbol_bits": (u32, [vp]),
+            "spmb_search_host_wide": (i32, [vp, vp, u64, u32, vp, vp]),
             "spmb_upload_last_stats": (i32, [vp, C.POINTER(u64 * 8)]),
             "spmb_host_pack_chunks": (None, [vp, u64, vp]),
             "spmb_store_create_journaled": (i32, [vp, vp, vp, u64, vp, u64, u32, pp]),
@@ -253,6 +261,26 @@ class Store:
                    "spmb_store_create_from_device")
         return cls(ctx, h)
 
+    @classmethod
+    def from_host_wide(cls, ctx: Context, ranks, bits: int = 4, row_len: int = 0):
+        """4-bit alphabets (spm::dna5: bits=3, spm::dna15: bits=4): ranks 0..15, one byte each."""
+        r = np.ascontiguousarray(ranks, dtype=np.uint8).reshape(-1)
+        h = C.c_void_p()
+        ctx._check(lib().spmb_store_create_wide(ctx._h, r.ctypes.data, r.size, bits, row_len, C.byref(h)),
+                   "spmb_store_create_wide")
+        return cls(ctx, h)
+
+    @classmethod
+    def from_device_wide(cls, ctx: Context, dev_ptr: int, n: int, bits: int = 4, row_len: int = 0):
+        h = C.c_void_p()
+        ctx._check(lib().spmb_store_create_wide_from_device(ctx._h, C.c_void_p(dev_ptr), n, bits, row_len, C.byref(h)),
+                   "spmb_store_create_wide_from_device")
+        return cls(ctx, h)
+
+    @property
+    def symbol_bits(self):
+        return int(lib().spmb_store_symbol_bits(self._h))
+
     def journaled(self, events, pool, row_len: int = 0):
         ev = np.ascontiguousarray(events, dtype=EVENT_DTYPE)
         pl = _ranks(pool)
@@ -294,10 +322,14 @@ class Store:
 class Pattern:
     """compiled needle(s) (spmb_pattern) == horspool_matcher / shiftor_matcher / myers_matcher ctor."""
 
-    def __init__(self, ctx: Context, alg: int, needle, k: int = 0):
+    def __init__(self, ctx: Context, alg: int, needle, k: int = 0, bits: int = 2):
         self.ctx = ctx
         self._h = C.c_void_p()
-        if isinstance(needle, (list, tuple)) and len(needle) and not np.isscalar(needle[0]):
+        if bits != 2:   # spm::dna5 / spm::dna15 needles: ranks 0..15 (spmb_pattern_create_wide)
+            r = np.ascontiguousarray(needle, dtype=np.uint8).reshape(-1)
+            ctx._check(lib().spmb_pattern_create_wide(ctx._h, alg, r.ctypes.data if r.size else None, r.size, k, bits,
+                                                      C.byref(self._h)), "spmb_pattern_create_wide")
+        elif isinstance(needle, (list, tuple)) and len(needle) and not np.isscalar(needle[0]):
             parts = [_ranks(p) for p in needle]
             lens = np.array([p.size for p in parts], dtype=np.uint32)
             cat = np.concatenate(parts) if parts else np.zeros(0, np.uint8)
@@ -417,14 +449,17 @@ def search_finish(ctx: Context, hits: Hits) -> np.ndarray:
 
 
 def search_host(ctx: Context, haystack, pattern: Pattern, hits: Hits | None = None, ptr: int | None = None,
-                n: int | None = None) -> np.ndarray:
+                n: int | None = None, bits: int = 2) -> np.ndarray:
     """the reference's call shape: host haystack in, hits out (upload + pack + search)."""
     own = hits is None
     hits = hits or Hits(ctx)
     if ptr is None:
-        r = _ranks(haystack)
+        r = _ranks(haystack) if bits == 2 else np.ascontiguousarray(haystack, dtype=np.uint8).reshape(-1)
         ptr, n = r.ctypes.data, r.size
-    ctx._check(lib().spmb_search_host(ctx._h, C.c_void_p(ptr), n, pattern._h, hits._h), "spmb_search_host")
+    if bits != 2:
+        ctx._check(lib().spmb_search_host_wide(ctx._h, C.c_void_p(ptr), n, bits, pattern._h, hits._h), "spmb_search_host_wide")
+    else:
+        ctx._check(lib().spmb_search_host(ctx._h, C.c_void_p(ptr), n, pattern._h, hits._h), "spmb_search_host")
     out = hits.array()
     if own:
         hits.close()

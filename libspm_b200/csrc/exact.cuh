@@ -38,6 +38,10 @@ struct ExactArgs {
     uint32_t m;
     uint32_t J;              // filter depth = min(m, 8)
     uint32_t filt_syms;      // pattern symbol j at bits [2j, 2j+1], j < J
+    // 4-bit alphabets (spm::dna5 / spm::dna15, alphabet.hpp:119-120): a second plane pair holds bits 3..2 of
+    // every symbol, in the same geometry; the filter accumulates over both pairs
+    const uint4 *planes_hi;  // null for dna4
+    uint32_t filt_syms_hi;   // bits 3..2 of pattern symbol j at bits [2j, 2j+1]
     uint32_t seq_id;
     uint32_t pattern_id;
     HitSink sink;
@@ -67,10 +71,11 @@ __device__ __forceinline__ uint32_t exact_acc(uint32_t acc, uint32_t h, uint32_t
 // Warp-cooperative verification of the candidates in one column word.
 // gc = global column, cm = candidate bits (bit b = row b).  Lane i checks pattern offsets
 // J+i, J+i+32, ...; returns the surviving candidate mask (same value in every lane).
-template <int MODE>
+template <int MODE, bool WIDE>
 __device__ __forceinline__ uint32_t exact_verify(const ExactArgs &a, uint64_t gc, uint32_t cm, uint32_t lane)
 {
     const uint2 *P2 = reinterpret_cast<const uint2 *>(a.planes);
+    const uint2 *P2H = reinterpret_cast<const uint2 *>(a.planes_hi);
     const uint32_t RL = a.lay.row_len;
     uint64_t st = spmb_div_rl(a.lay, gc);
     uint32_t col = (uint32_t)(gc - st * RL);
@@ -86,6 +91,10 @@ __device__ __forceinline__ uint32_t exact_verify(const ExactArgs &a, uint64_t gc
                 h = v.x; l = v.y;
                 uint32_t s = a.pat[j];
                 mm = ~((h ^ (0u - ((s >> 1) & 1u))) | (l ^ (0u - (s & 1u))));
+                if (WIDE) {
+                    v = __ldg(P2H + spmb_perm(st * RL + x));
+                    mm &= ~((v.x ^ (0u - ((s >> 3) & 1u))) | (v.y ^ (0u - ((s >> 2) & 1u))));
+                }
             } else if (MODE == SPMB_MODE_PLAIN) {
                 // the pattern runs off the row end: row r continues in row r+1 (next bit),
                 // row 31 continues in row 0 of the next super-tile
@@ -95,6 +104,13 @@ __device__ __forceinline__ uint32_t exact_verify(const ExactArgs &a, uint64_t gc
                 l = __funnelshift_r(v0.y, v1.y, wraps);
                 uint32_t s = a.pat[j];
                 mm = ~((h ^ (0u - ((s >> 1) & 1u))) | (l ^ (0u - (s & 1u))));
+                if (WIDE) {
+                    v0 = __ldg(P2H + spmb_perm(st * RL + x));
+                    v1 = __ldg(P2H + spmb_perm((st + 1) * RL + x));
+                    h = __funnelshift_r(v0.x, v1.x, wraps);
+                    l = __funnelshift_r(v0.y, v1.y, wraps);
+                    mm &= ~((h ^ (0u - ((s >> 3) & 1u))) | (l ^ (0u - ((s >> 2) & 1u))));
+                }
             } else {
                 mm = 0; // windows do not continue: nothing can match past the row
             }
@@ -137,13 +153,56 @@ __device__ __forceinline__ void exact_emit(const ExactArgs &a, uint64_t gc, uint
     }
 }
 
+// one filter pass over one plane pair: load the thread-row (+ 8 halo columns) and OR the mismatches of the
+// first J pattern symbols (their two bits in this pair = fs) into acc
 template <int MODE>
+__device__ __forceinline__ void exact_filter_pass(const uint4 *__restrict__ planes, const SpmbLayout &lay, uint64_t tile,
+                                                  uint32_t J, uint32_t fs, uint32_t (&acc)[32])
+{
+    const uint32_t RL = lay.row_len;
+    uint32_t H[40], L[40];
+    // own thread-row: chunk k (columns 2k, 2k+1) of lane l sits at uint4 index blk*512 + k*32 + l
+    const uint4 *p = planes + (tile >> 5) * 512 + (tile & 31);
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        uint4 q = __ldg(p + k * 32);
+        H[2 * k] = q.x; L[2 * k] = q.y; H[2 * k + 1] = q.z; L[2 * k + 1] = q.w;
+    }
+    // halo: first 8 columns of the next thread-row
+    const uint64_t g0 = tile * 32;
+    const uint64_t st = spmb_div_rl(lay, g0);
+    const uint32_t col0 = (uint32_t)(g0 - st * RL);
+    if (col0 + 32 != RL) {
+        const uint4 *pn = planes + ((tile + 1) >> 5) * 512 + ((tile + 1) & 31);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            uint4 q = __ldg(pn + k * 32);
+            H[32 + 2 * k] = q.x; L[32 + 2 * k] = q.y; H[33 + 2 * k] = q.z; L[33 + 2 * k] = q.w;
+        }
+    } else if (MODE == SPMB_MODE_PLAIN) {
+        // last thread-row of a super-tile: row r continues in row r+1, i.e. the same
+        // columns 0..7 one bit up; row 31 continues in row 0 of the next super-tile.
+        const uint2 *P2 = reinterpret_cast<const uint2 *>(planes);
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+            uint2 v0 = __ldg(P2 + spmb_perm(st * RL + t));
+            uint2 v1 = __ldg(P2 + spmb_perm((st + 1) * RL + t));
+            H[32 + t] = (v0.x >> 1) | (v1.x << 31);
+            L[32 + t] = (v0.y >> 1) | (v1.y << 31);
+        }
+    } else {
+#pragma unroll
+        for (int t = 0; t < 8; ++t) { H[32 + t] = 0; L[32 + t] = 0; }
+    }
+    SPMB_EXACT_STEP(0) SPMB_EXACT_STEP(1) SPMB_EXACT_STEP(2) SPMB_EXACT_STEP(3)
+    SPMB_EXACT_STEP(4) SPMB_EXACT_STEP(5) SPMB_EXACT_STEP(6) SPMB_EXACT_STEP(7)
+}
+
+template <int MODE, bool WIDE = false>
 __global__ void __launch_bounds__(256, 2) exact_kernel(ExactArgs a)
 {
     __shared__ uint32_t sbuf[8][32][33];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t J = a.J, fs = a.filt_syms;
-    const uint32_t RL = a.lay.row_len;
     // grid-stride over CTA tiles of 256 thread-rows (8 CTAs per SM in the grid, 2 resident)
     for (uint64_t ct = blockIdx.x; a.tile0 + ct * 256 < a.n_tiles; ct += gridDim.x) {
     const uint64_t tile = a.tile0 + ct * 256 + threadIdx.x;
@@ -151,44 +210,10 @@ __global__ void __launch_bounds__(256, 2) exact_kernel(ExactArgs a)
     uint32_t all = 0xffffffffu;
 
     if (tile < a.n_tiles) {
-        uint32_t H[40], L[40];
-        // own thread-row: chunk k (columns 2k, 2k+1) of lane l sits at uint4 index blk*512 + k*32 + l
-        const uint4 *p = a.planes + (tile >> 5) * 512 + (tile & 31);
-#pragma unroll
-        for (int k = 0; k < 16; ++k) {
-            uint4 q = __ldg(p + k * 32);
-            H[2 * k] = q.x; L[2 * k] = q.y; H[2 * k + 1] = q.z; L[2 * k + 1] = q.w;
-        }
-        // halo: first 8 columns of the next thread-row
-        const uint64_t g0 = tile * 32;
-        const uint64_t st = spmb_div_rl(a.lay, g0);
-        const uint32_t col0 = (uint32_t)(g0 - st * RL);
-        if (col0 + 32 != RL) {
-            const uint4 *pn = a.planes + ((tile + 1) >> 5) * 512 + ((tile + 1) & 31);
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                uint4 q = __ldg(pn + k * 32);
-                H[32 + 2 * k] = q.x; L[32 + 2 * k] = q.y; H[33 + 2 * k] = q.z; L[33 + 2 * k] = q.w;
-            }
-        } else if (MODE == SPMB_MODE_PLAIN) {
-            // last thread-row of a super-tile: row r continues in row r+1, i.e. the same
-            // columns 0..7 one bit up; row 31 continues in row 0 of the next super-tile.
-            const uint2 *P2 = reinterpret_cast<const uint2 *>(a.planes);
-#pragma unroll
-            for (int t = 0; t < 8; ++t) {
-                uint2 v0 = __ldg(P2 + spmb_perm(st * RL + t));
-                uint2 v1 = __ldg(P2 + spmb_perm((st + 1) * RL + t));
-                H[32 + t] = (v0.x >> 1) | (v1.x << 31);
-                L[32 + t] = (v0.y >> 1) | (v1.y << 31);
-            }
-        } else {
-#pragma unroll
-            for (int t = 0; t < 8; ++t) { H[32 + t] = 0; L[32 + t] = 0; }
-        }
 #pragma unroll
         for (int c = 0; c < 32; ++c) acc[c] = 0;
-        SPMB_EXACT_STEP(0) SPMB_EXACT_STEP(1) SPMB_EXACT_STEP(2) SPMB_EXACT_STEP(3)
-        SPMB_EXACT_STEP(4) SPMB_EXACT_STEP(5) SPMB_EXACT_STEP(6) SPMB_EXACT_STEP(7)
+        exact_filter_pass<MODE>(a.planes, a.lay, tile, a.J, a.filt_syms, acc);
+        if (WIDE) exact_filter_pass<MODE>(a.planes_hi, a.lay, tile, a.J, a.filt_syms_hi, acc);
 #pragma unroll
         for (int c = 0; c < 32; ++c) all &= acc[c];
     }
@@ -214,7 +239,7 @@ __global__ void __launch_bounds__(256, 2) exact_kernel(ExactArgs a)
             cvote &= cvote - 1;
             uint32_t cm = __shfl_sync(0xffffffffu, w, c);
             const uint64_t gc = stile * 32 + c;
-            cm = exact_verify<MODE>(a, gc, cm, lane);
+            cm = exact_verify<MODE, WIDE>(a, gc, cm, lane);
             if (cm) exact_emit<MODE>(a, gc, cm, lane);
         }
     }

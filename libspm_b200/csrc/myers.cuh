@@ -32,8 +32,9 @@ struct MyersPatMeta {
 
 struct MyersArgs {
     const uint2 *lanes;       // lane-chunk layout of the store (pack.cuh lanes_kernel)
+    const uint2 *lanes_hi;    // 4-bit alphabets: lane chunks of bits 3..2 of every symbol (else null)
     SpmbLayout lay;
-    const uint32_t *eq;       // [n_pat][4][NWP]
+    const uint32_t *eq;       // [n_pat][4][NWP]  (4-bit alphabets: [n_pat][16][NWP])
     const MyersPatMeta *meta; // [n_pat]
     const uint32_t *row_len;  // windows mode
     const uint32_t *row_seq;  // windows mode
@@ -87,13 +88,14 @@ __device__ __forceinline__ void myers_emit(const HitSink &sink, uint64_t end, ui
     }
 }
 
-template <int NW, int MODE>
+template <int NW, int MODE, bool WIDE = false>
 __global__ void __launch_bounds__(128) myers_kernel(MyersArgs a)
 {
     constexpr int NWP = (NW <= 4) ? 4 : 8;
-    __shared__ __align__(16) uint32_t s_eq[4 * NWP];
+    constexpr int NSYM = WIDE ? 16 : 4;
+    __shared__ __align__(16) uint32_t s_eq[NSYM * NWP];
     const uint32_t pat = blockIdx.y;
-    if (threadIdx.x < 4 * NWP) s_eq[threadIdx.x] = a.eq[(size_t)pat * 4 * NWP + threadIdx.x];
+    for (uint32_t t = threadIdx.x; t < NSYM * NWP; t += blockDim.x) s_eq[t] = a.eq[(size_t)pat * NSYM * NWP + t];
     __syncthreads();
     const MyersPatMeta pm = a.meta[pat];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -141,22 +143,29 @@ __global__ void __launch_bounds__(128) myers_kernel(MyersArgs a)
     const uint32_t rl32 = RL >> 5;
     const uint32_t mul4 = a.mul4, eq_stride = a.eq_stride;
     const uint2 *__restrict__ lp = a.lanes;
+    const uint2 *__restrict__ lph = a.lanes_hi;
     // one uint2 = this row's next 32 symbols; fetched one whole block (32 columns) ahead
-    uint2 nxt = __ldg(lp + ((uint64_t)(cur_row >> 5) * rl32 + (cur_col >> 5)) * 32 + ((uint32_t)cur_row & 31u));
+    uint64_t li = ((uint64_t)(cur_row >> 5) * rl32 + (cur_col >> 5)) * 32 + ((uint32_t)cur_row & 31u);
+    uint2 nxt = __ldg(lp + li), nxt_hi = WIDE ? __ldg(lph + li) : make_uint2(0, 0);
     while (p < end_p) {
-        const uint2 cur = nxt;
+        const uint2 cur = nxt, cur_hi = nxt_hi;
         cur_col += 32;
         if (cur_col == RL) { cur_col = 0; ++cur_row; }
-        if (p + 32 < end_p)
-            nxt = __ldg(lp + ((uint64_t)(cur_row >> 5) * rl32 + (cur_col >> 5)) * 32 + ((uint32_t)cur_row & 31u));
+        if (p + 32 < end_p) {
+            li = ((uint64_t)(cur_row >> 5) * rl32 + (cur_col >> 5)) * 32 + ((uint32_t)cur_row & 31u);
+            nxt = __ldg(lp + li);
+            if (WIDE) nxt_hi = __ldg(lph + li);
+        }
         uint32_t hp_acc = 0, hn_acc = 0;
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
             uint32_t w = half ? cur.y : cur.x;
+            uint32_t wh = half ? cur_hi.y : cur_hi.x;
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
-                const uint32_t c = w >> 30; // the one ALU instruction of the symbol fetch
+                uint32_t c = w >> 30;       // the one ALU instruction of the symbol fetch
                 w *= mul4;                  // IMAD
+                if (WIDE) { c = (wh >> 30) * mul4 + c; wh *= mul4; }
                 uint32_t eq[NW];
                 const uint4 *e4 = reinterpret_cast<const uint4 *>(reinterpret_cast<const char *>(s_eq) + c * eq_stride);
                 const uint4 e0 = e4[0];

@@ -75,15 +75,16 @@ __device__ __forceinline__ uint4 spmb_lds128(uint32_t addr)
 
 // C = 8 columns on the first A words; w holds the symbols, next one in the top two bits; eq_base is the
 // shared-window address of the Eq table (rows of eq_stride bytes, one per symbol)
-template <int A, int NW, bool TRACK>
-__device__ __forceinline__ void myers_cut_chunk(uint32_t (&vp)[NW], uint32_t (&vn)[NW], uint32_t &w, uint32_t eq_base,
+template <int A, int NW, bool TRACK, bool WIDE>
+__device__ __forceinline__ void myers_cut_chunk(uint32_t (&vp)[NW], uint32_t (&vn)[NW], uint32_t &w, uint32_t &wh, uint32_t eq_base,
                                                 uint32_t mul4, uint32_t eq_stride, uint32_t &hp_acc, uint32_t &hn_acc)
 {
     constexpr int NWP = (NW <= 4) ? 4 : 8;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-        const uint32_t c = w >> 30;
+        uint32_t c = w >> 30;
         w *= mul4; // IMAD (FMA pipe), see MyersArgs
+        if (WIDE) { c = (wh >> 30) * mul4 + c; wh *= mul4; } // 4-bit alphabets: bits 3..2 come from the second chunk
         const uint32_t row = c * eq_stride + eq_base;
         uint32_t eq[A];
         if (A == 1) {
@@ -128,26 +129,27 @@ __device__ __forceinline__ int myers_cut_next(const uint32_t (&vp)[NW], const ui
     return res;
 }
 
-template <int A, int NW>
+template <int A, int NW, bool WIDE>
 struct MyersCutDispatch {
-    static __device__ __forceinline__ int run(int Acur, uint32_t (&vp)[NW], uint32_t (&vn)[NW], uint32_t &w, uint32_t s_eq,
+    static __device__ __forceinline__ int run(int Acur, uint32_t (&vp)[NW], uint32_t (&vn)[NW], uint32_t &w, uint32_t &wh, uint32_t s_eq,
                                               uint32_t mul4, uint32_t eq_stride, int k, uint32_t &hp_acc, uint32_t &hn_acc)
     {
         if (A == NW || Acur == A) {
-            myers_cut_chunk<A, NW, A == NW>(vp, vn, w, s_eq, mul4, eq_stride, hp_acc, hn_acc);
+            myers_cut_chunk<A, NW, A == NW, WIDE>(vp, vn, w, wh, s_eq, mul4, eq_stride, hp_acc, hn_acc);
             return myers_cut_next<A, NW>(vp, vn, k);
         }
-        return MyersCutDispatch<(A < NW ? A + 1 : NW), NW>::run(Acur, vp, vn, w, s_eq, mul4, eq_stride, k, hp_acc, hn_acc);
+        return MyersCutDispatch<(A < NW ? A + 1 : NW), NW, WIDE>::run(Acur, vp, vn, w, wh, s_eq, mul4, eq_stride, k, hp_acc, hn_acc);
     }
 };
 
-template <int NW, int MODE>
+template <int NW, int MODE, bool WIDE = false>
 __global__ void __launch_bounds__(128) myers_cut_kernel(MyersArgs a)
 {
     constexpr int NWP = (NW <= 4) ? 4 : 8;
-    __shared__ __align__(16) uint32_t s_eq[4 * NWP];
+    constexpr int NSYM = WIDE ? 16 : 4;
+    __shared__ __align__(16) uint32_t s_eq[NSYM * NWP];
     const uint32_t pat = blockIdx.y;
-    if (threadIdx.x < 4 * NWP) s_eq[threadIdx.x] = a.eq[(size_t)pat * 4 * NWP + threadIdx.x];
+    for (uint32_t t = threadIdx.x; t < NSYM * NWP; t += blockDim.x) s_eq[t] = a.eq[(size_t)pat * NSYM * NWP + t];
     __syncthreads();
     const MyersPatMeta pm = a.meta[pat];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -215,22 +217,27 @@ __global__ void __launch_bounds__(128) myers_cut_kernel(MyersArgs a)
     int A = __reduce_max_sync(0xffffffffu, myers_cut_next<NW, NW>(vp, vn, k));
     int score = 32 * NW; // meaningful while A == NW
 
-    uint2 nxt = __ldg(lp + ((uint64_t)(cur_row >> 5) * rl32 + (cur_col >> 5)) * 32 + ((uint32_t)cur_row & 31u));
+    const uint2 *__restrict__ lph = a.lanes_hi;
+    uint64_t li = ((uint64_t)(cur_row >> 5) * rl32 + (cur_col >> 5)) * 32 + ((uint32_t)cur_row & 31u);
+    uint2 nxt = __ldg(lp + li), nxt_hi = WIDE ? __ldg(lph + li) : make_uint2(0, 0);
     for (int blk = 0; blk < n_blocks; ++blk) {
-        const uint2 cur = nxt;
+        const uint2 cur = nxt, cur_hi = nxt_hi;
         cur_col += 32;
         if (cur_col == RL) { cur_col = 0; ++cur_row; }
-        if (blk + 1 < n_blocks)
-            nxt = __ldg(lp + ((uint64_t)(cur_row >> 5) * rl32 + (cur_col >> 5)) * 32 + ((uint32_t)cur_row & 31u));
-        uint32_t w = cur.x;
+        if (blk + 1 < n_blocks) {
+            li = ((uint64_t)(cur_row >> 5) * rl32 + (cur_col >> 5)) * 32 + ((uint32_t)cur_row & 31u);
+            nxt = __ldg(lp + li);
+            if (WIDE) nxt_hi = __ldg(lph + li);
+        }
+        uint32_t w = cur.x, wh = cur_hi.x;
         int q = 0;
         if (A == 1) {
             // the common state on random text: one word, no score row in reach (NW >= 2), no bookkeeping
 #pragma unroll
             for (int qq = 0; qq < 4; ++qq) {
-                if (qq == 2) w = cur.y;
+                if (qq == 2) { w = cur.y; wh = cur_hi.y; }
                 uint32_t d0 = 0, d1 = 0;
-                myers_cut_chunk<1, NW, false>(vp, vn, w, eq_base, mul4, eq_stride, d0, d1);
+                myers_cut_chunk<1, NW, false, WIDE>(vp, vn, w, wh, eq_base, mul4, eq_stride, d0, d1);
                 q = qq + 1;
                 const bool grow = (int)__popc(vp[0] & 0x00ffffffu) - (int)__popc(vn[0]) <= k;
                 if (__any_sync(0xffffffffu, grow)) {
@@ -244,9 +251,9 @@ __global__ void __launch_bounds__(128) myers_cut_kernel(MyersArgs a)
         }
 #pragma unroll 1
         for (; q < 4; ++q) {
-            if (q == 2) w = cur.y;
+            if (q == 2) { w = cur.y; wh = cur_hi.y; }
             uint32_t hp_acc = 0, hn_acc = 0;
-            int An = MyersCutDispatch<1, NW>::run(A, vp, vn, w, eq_base, mul4, eq_stride, k, hp_acc, hn_acc);
+            int An = MyersCutDispatch<1, NW, WIDE>::run(A, vp, vn, w, wh, eq_base, mul4, eq_stride, k, hp_acc, hn_acc);
             if (A == NW) {
                 if (score - (int)__popc(hn_acc) <= k) {
                     int s = score;

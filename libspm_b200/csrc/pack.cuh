@@ -25,6 +25,7 @@ __device__ __forceinline__ uint32_t spmb_symbol_at(const uint2 *__restrict__ pla
 struct ByteSource {
     const uint8_t *__restrict__ in;
     uint64_t n;
+    uint32_t shift; // which two bits of a symbol byte become {H,L}: 0 (dna4; low pair of a 4-bit alphabet) or 2 (its high pair)
     // 32 symbols of one row starting at absolute position p0 (p0 % 32 == 0), packed 4 per word
     __device__ __forceinline__ void load32(uint64_t p0, uint32_t (&w)[8]) const
     {
@@ -41,7 +42,7 @@ struct ByteSource {
                 for (int j = 0; j < 4; ++j) {
                     uint64_t p = p0 + 4 * i + j;
                     uint32_t s = (p < n) ? (uint32_t)in[p] : 0u;
-                    v |= (s & 3u) << (8 * j);
+                    v |= (s & 15u) << (8 * j);
                 }
                 w[i] = v;
             }
@@ -242,7 +243,7 @@ __global__ void __launch_bounds__(1024) pack_kernel(Source src, SpmbLayout lay, 
     uint32_t myH = 0, myL = 0;
 #pragma unroll
     for (int c = 0; c < 32; ++c) {
-        uint32_t s = w[c >> 2] >> (8 * (c & 3));
+        uint32_t s = w[c >> 2] >> (8 * (c & 3) + src.shift);
         uint32_t h = __ballot_sync(0xffffffffu, (s >> 1) & 1u);
         uint32_t l = __ballot_sync(0xffffffffu, s & 1u);
         if (lane == c) { myH = h; myL = l; }

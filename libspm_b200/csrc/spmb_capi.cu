@@ -108,6 +108,9 @@ struct spmb_store {
     mutable uint2 *lanes = nullptr;
     // windows mode
     uint32_t *row_len = nullptr, *row_seq = nullptr, *row_own = nullptr;
+    // 4-bit alphabets (spmb_store_create_wide): this store holds bits 1..0 of every symbol, `hi` bits 3..2
+    spmb_store *hi = nullptr;
+    uint32_t sym_bits = 2;
 };
 
 struct spmb_pattern {
@@ -119,6 +122,8 @@ struct spmb_pattern {
     std::vector<uint32_t> filt;       // exact: packed first min(m,8) symbols
     uint32_t max_m = 0, min_m = 0;
     int NW = 0;                       // myers: 32-bit words
+    uint32_t sym_bits = 2;            // 2 (dna4) or 4 (spmb_pattern_create_wide)
+    std::vector<uint32_t> filt_hi;    // exact, 4-bit alphabets: bits 3..2 of the first min(m,8) symbols
     uint32_t warm = 0;                // myers: warm-up columns (multiple of 32)
     uint8_t *d_ranks = nullptr;
     uint32_t *d_eq = nullptr;
@@ -414,20 +419,71 @@ static int store_pack(spmb_context *ctx, spmb_store *s, const Source &src)
     return SPMB_OK;
 }
 
-extern "C" int spmb_store_create_from_device(spmb_context *ctx, const uint8_t *dev_ranks, uint64_t n,
-                                             uint32_t row_len, spmb_store **out)
+static int store_from_device_bits(spmb_context *ctx, const uint8_t *dev_ranks, uint64_t n, uint32_t row_len,
+                                  uint32_t shift, spmb_store **out)
 {
-    if (!ctx || !out || (!dev_ranks && n)) return SPMB_ERR_ARG;
-    ENTER(ctx);
     spmb_store *s = nullptr;
     int rc = store_alloc(ctx, n, row_len, SPMB_MODE_PLAIN, &s);
     if (rc) return rc;
-    ByteSource src{dev_ranks, n};
+    ByteSource src{dev_ranks, n, shift};
     rc = store_pack(ctx, s, src);
     if (rc) { spmb_store_destroy(s); return rc; }
     *out = s;
     return SPMB_OK;
 }
+
+extern "C" int spmb_store_create_from_device(spmb_context *ctx, const uint8_t *dev_ranks, uint64_t n,
+                                             uint32_t row_len, spmb_store **out)
+{
+    if (!ctx || !out || (!dev_ranks && n)) return SPMB_ERR_ARG;
+    ENTER(ctx);
+    return store_from_device_bits(ctx, dev_ranks, n, row_len, 0, out);
+}
+
+// 4-bit alphabets: two plane pairs in the same geometry (bits 1..0 and bits 3..2 of every symbol)
+extern "C" int spmb_store_create_wide_from_device(spmb_context *ctx, const uint8_t *dev_ranks, uint64_t n, uint32_t bits,
+                                                  uint32_t row_len, spmb_store **out)
+{
+    if (!ctx || !out || (!dev_ranks && n)) return SPMB_ERR_ARG;
+    if (bits == 2) return spmb_store_create_from_device(ctx, dev_ranks, n, row_len, out);
+    if (bits != 3 && bits != 4) return set_err(ctx, SPMB_ERR_ARG, "symbol width must be 2, 3 or 4 bits");
+    ENTER(ctx);
+    spmb_store *lo = nullptr, *hi = nullptr;
+    int rc = store_from_device_bits(ctx, dev_ranks, n, row_len, 0, &lo);
+    if (rc) return rc;
+    rc = store_from_device_bits(ctx, dev_ranks, n, lo->lay.row_len, 2, &hi);
+    if (rc) { spmb_store_destroy(lo); return rc; }
+    lo->hi = hi;
+    lo->sym_bits = 4;
+    hi->sym_bits = 4;
+    *out = lo;
+    return SPMB_OK;
+}
+
+extern "C" int spmb_store_create_wide(spmb_context *ctx, const uint8_t *host_ranks, uint64_t n, uint32_t bits,
+                                      uint32_t row_len, spmb_store **out)
+{
+    if (!ctx || !out || (!host_ranks && n)) return SPMB_ERR_ARG;
+    if (bits == 2) return spmb_store_create(ctx, host_ranks, n, row_len, out);
+    if (bits != 3 && bits != 4) return set_err(ctx, SPMB_ERR_ARG, "symbol width must be 2, 3 or 4 bits");
+    ENTER(ctx);
+    uint8_t *d = nullptr;
+    CU(big_alloc(ctx, n ? n : 1, (void **)&d));
+    cudaError_t e = n ? cudaMemcpyAsync(d, host_ranks, n, cudaMemcpyHostToDevice, ctx->stream) : cudaSuccess;
+    int rc = SPMB_OK;
+    if (e != cudaSuccess) rc = set_err(ctx, SPMB_ERR_CUDA, "H2D haystack", e);
+    if (rc == SPMB_OK) rc = spmb_store_create_wide_from_device(ctx, d, n, bits, row_len, out);
+    big_free(ctx, d, n ? n : 1);
+    e = cudaStreamSynchronize(ctx->stream); // the caller's buffer may be pinned: consumed before we return
+    if (rc == SPMB_OK && e != cudaSuccess) {
+        spmb_store_destroy(*out);
+        *out = nullptr;
+        rc = set_err(ctx, SPMB_ERR_CUDA, "store_create_wide", e);
+    }
+    return rc;
+}
+
+extern "C" uint32_t spmb_store_symbol_bits(const spmb_store *s) { return s ? s->sym_bits : 0; }
 
 static int ensure_upload(spmb_context *ctx)
 {
@@ -521,6 +577,7 @@ extern "C" int spmb_store_create_journaled(spmb_context *ctx, const spmb_store *
 {
     if (!ctx || !base || !out || (n_ev && !ev) || (pool_len && !pool)) return SPMB_ERR_ARG;
     if (base->lay.mode != SPMB_MODE_PLAIN) return set_err(ctx, SPMB_ERR_ARG, "journal base must be a plain store");
+    if (base->sym_bits != 2) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "journaled stores are dna4 (2-bit) only");
     ENTER(ctx);
     cudaStream_t sm = ctx->stream;
     const size_t ne = n_ev ? n_ev : 1;
@@ -634,6 +691,7 @@ extern "C" int spmb_store_create_journaled(spmb_context *ctx, const spmb_store *
 extern "C" int spmb_store_destroy(spmb_store *s)
 {
     if (!s) return SPMB_OK;
+    if (s->hi) spmb_store_destroy(s->hi);
     if (s->ctx) cudaSetDevice(s->ctx->device);
     if (s->ctx) big_free(s->ctx, s->planes, s->bytes); else cudaFree(s->planes);
     if (s->lanes) { if (s->ctx) big_free(s->ctx, s->lanes, s->bytes); else cudaFree(s->lanes); }
@@ -646,7 +704,10 @@ extern "C" int spmb_store_destroy(spmb_store *s)
 
 extern "C" uint64_t spmb_store_length(const spmb_store *s) { return s ? s->lay.n : 0; }
 extern "C" uint32_t spmb_store_row_len(const spmb_store *s) { return s ? s->lay.row_len : 0; }
-extern "C" uint64_t spmb_store_device_bytes(const spmb_store *s) { return s ? s->bytes * (s->lanes ? 2 : 1) : 0; }
+extern "C" uint64_t spmb_store_device_bytes(const spmb_store *s)
+{
+    return s ? s->bytes * (s->lanes ? 2 : 1) + spmb_store_device_bytes(s->hi) : 0;
+}
 
 // the Myers kernels read the lane-chunk layout: build it once per store, stream-ordered
 static int store_ensure_lanes(spmb_context *ctx, const spmb_store *s)
@@ -681,6 +742,12 @@ extern "C" int spmb_store_read(spmb_context *ctx, const spmb_store *s, uint64_t 
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     cudaFree(d);
     if (e != cudaSuccess) return set_err(ctx, SPMB_ERR_CUDA, "store_read", e);
+    if (s->hi) { // 4-bit alphabet: bits 3..2 come from the second plane pair
+        std::vector<uint8_t> top(n);
+        int rc = spmb_store_read(ctx, s->hi, begin, n, top.data());
+        if (rc) return rc;
+        for (uint64_t i = 0; i < n; ++i) host_out[i] |= (uint8_t)(top[i] << 2);
+    }
     return SPMB_OK;
 }
 
@@ -692,14 +759,15 @@ static cudaError_t pattern_upload_myers(spmb_context *ctx, spmb_pattern *p, uint
 {
     const uint32_t n_pat = p->n_pat;
     const int NWP = p->NW <= 4 ? 4 : 8;
-    std::vector<uint32_t> eq((size_t)n_pat * 4 * NWP, 0);
+    const int NSYM = p->sym_bits == 4 ? 16 : 4;
+    std::vector<uint32_t> eq((size_t)n_pat * NSYM * NWP, 0);
     std::vector<MyersPatMeta> meta(n_pat);
     for (uint32_t i = 0; i < n_pat; ++i) {
         const uint32_t m = p->len[i];
         const uint8_t *pr = p->ranks.data() + p->off[i];
-        uint32_t *e4 = eq.data() + (size_t)i * 4 * NWP;
+        uint32_t *e4 = eq.data() + (size_t)i * NSYM * NWP;
         for (uint32_t j = 0; j < (uint32_t)p->NW * 32; ++j) {
-            for (int c = 0; c < 4; ++c) {
+            for (int c = 0; c < NSYM; ++c) {
                 bool match = (j < m) ? (pr[j] == c) : true; // wildcard padding rows
                 if (match) e4[c * NWP + j / 32] |= 1u << (j % 32);
             }
@@ -744,9 +812,13 @@ static cudaError_t pattern_upload_pigeon(spmb_context *ctx, spmb_pattern *p,
 static const uint32_t SPMB_FILTER_MIN_Q = 12;
 
 static int pattern_build(spmb_context *ctx, int alg, const uint8_t *ranks, const uint32_t *lengths, uint32_t n_pat,
-                         uint32_t k, double error_rate, spmb_pattern **out)
+                         uint32_t k, double error_rate, spmb_pattern **out, uint32_t sym_bits = 2)
 {
     if (!ctx || !out || !lengths || n_pat == 0) return SPMB_ERR_ARG;
+    if (sym_bits == 3) sym_bits = 4; // dna5 travels in the 4-bit layout
+    if (sym_bits != 2 && sym_bits != 4) return set_err(ctx, SPMB_ERR_ARG, "symbol width must be 2, 3 or 4 bits");
+    if (sym_bits == 4 && alg != SPMB_ALG_HORSPOOL && alg != SPMB_ALG_SHIFTOR && alg != SPMB_ALG_MYERS)
+        return set_err(ctx, SPMB_ERR_UNSUPPORTED, "4-bit alphabets: Horspool, Shift-Or and Myers only");
     if (alg < SPMB_ALG_HORSPOOL || alg > SPMB_ALG_MYERS_PREFIX) return SPMB_ERR_ARG;
     if (alg == SPMB_ALG_PIGEONHOLE && !(error_rate >= 0.0 && error_rate < 1.0)) return SPMB_ERR_ARG;
     ENTER(ctx);
@@ -754,6 +826,7 @@ static int pattern_build(spmb_context *ctx, int alg, const uint8_t *ranks, const
     spmb_pattern *p = new (std::nothrow) spmb_pattern();
     if (!p) return SPMB_ERR_OOM;
     p->ctx = ctx; p->alg = alg; p->n_pat = n_pat; p->k = myers_like ? k : 0;
+    p->sym_bits = sym_bits;
     uint64_t total = 0;
     p->max_m = 0; p->min_m = 0xffffffffu;
     for (uint32_t i = 0; i < n_pat; ++i) {
@@ -766,7 +839,7 @@ static int pattern_build(spmb_context *ctx, int alg, const uint8_t *ranks, const
     if (total && !ranks) { delete p; return SPMB_ERR_ARG; }
     if (total >= (1ull << 31)) { delete p; return set_err(ctx, SPMB_ERR_UNSUPPORTED, "pattern set too large"); }
     p->ranks.assign(ranks, ranks + total);
-    for (auto &c : p->ranks) c &= 3;
+    for (auto &c : p->ranks) c &= (sym_bits == 4 ? 15 : 3);
 
     cudaError_t e = cudaMalloc(&p->d_ranks, total ? total : 1);
     if (e == cudaSuccess && total) e = cudaMemcpyAsync(p->d_ranks, p->ranks.data(), total, cudaMemcpyHostToDevice, ctx->stream);
@@ -837,10 +910,14 @@ static int pattern_build(spmb_context *ctx, int alg, const uint8_t *ranks, const
         }
     } else {
         for (uint32_t i = 0; i < n_pat; ++i) {
-            uint32_t fs = 0;
+            uint32_t fs = 0, fh = 0;
             const uint32_t J = std::min<uint32_t>(p->len[i], 8);
-            for (uint32_t j = 0; j < J; ++j) fs |= (uint32_t)p->ranks[p->off[i] + j] << (2 * j);
+            for (uint32_t j = 0; j < J; ++j) {
+                fs |= (uint32_t)(p->ranks[p->off[i] + j] & 3) << (2 * j);
+                fh |= (uint32_t)(p->ranks[p->off[i] + j] >> 2) << (2 * j);
+            }
             p->filt.push_back(fs);
+            p->filt_hi.push_back(fh);
         }
     }
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
@@ -875,6 +952,15 @@ extern "C" int spmb_pattern_create(spmb_context *ctx, int alg, const uint8_t *ra
 {
     return spmb_pattern_set_create(ctx, alg, ranks, &m, 1, k, out);
 }
+
+extern "C" int spmb_pattern_create_wide(spmb_context *ctx, int alg, const uint8_t *ranks, uint32_t m, uint32_t k,
+                                        uint32_t bits, spmb_pattern **out)
+{
+    if (alg == SPMB_ALG_PIGEONHOLE) return ctx ? set_err(ctx, SPMB_ERR_UNSUPPORTED, "4-bit alphabets: no pigeonhole matcher") : SPMB_ERR_ARG;
+    return pattern_build(ctx, alg, ranks, &m, 1, k, 0.0, out, bits);
+}
+
+extern "C" uint32_t spmb_pattern_symbol_bits(const spmb_pattern *p) { return p ? p->sym_bits : 0; }
 
 extern "C" int spmb_pattern_destroy(spmb_pattern *p)
 {
@@ -980,6 +1066,25 @@ static cudaError_t launch_myers(spmb_context *ctx, const spmb_store *s, const sp
         a.split = sp;
     }
     dim3 grid((unsigned)(((a.st1 - a.st0) * a.split + 3) / 4), p->n_pat);
+    if (a.lanes_hi) {
+        // 4-bit alphabets (plain stores only): the cut-off kernel for two words and more, the full one for one
+        if (MODE != SPMB_MODE_PLAIN) return cudaErrorInvalidValue;
+        const bool wcut = p->NW >= 2;
+        if (!wcut) a.split = 1;
+        switch (p->NW) {
+        case 1: myers_kernel<1, SPMB_MODE_PLAIN, true><<<grid, 128, 0, ctx->stream>>>(a); break;
+        case 2: myers_cut_kernel<2, SPMB_MODE_PLAIN, true><<<grid, 128, 0, ctx->stream>>>(a); break;
+        case 3: myers_cut_kernel<3, SPMB_MODE_PLAIN, true><<<grid, 128, 0, ctx->stream>>>(a); break;
+        case 4: myers_cut_kernel<4, SPMB_MODE_PLAIN, true><<<grid, 128, 0, ctx->stream>>>(a); break;
+        case 5: myers_cut_kernel<5, SPMB_MODE_PLAIN, true><<<grid, 128, 0, ctx->stream>>>(a); break;
+        case 6: myers_cut_kernel<6, SPMB_MODE_PLAIN, true><<<grid, 128, 0, ctx->stream>>>(a); break;
+        case 7: myers_cut_kernel<7, SPMB_MODE_PLAIN, true><<<grid, 128, 0, ctx->stream>>>(a); break;
+        case 8: myers_cut_kernel<8, SPMB_MODE_PLAIN, true><<<grid, 128, 0, ctx->stream>>>(a); break;
+        default: return cudaErrorInvalidValue;
+        }
+        ctx->launches++;
+        return cudaGetLastError();
+    }
 #define SPMB_MYERS_CASE(nw)                                                                       \
     case nw:                                                                                      \
         if (cut) myers_cut_kernel<(nw < 2 ? 2 : nw), MODE><<<grid, 128, 0, ctx->stream>>>(a);      \
@@ -1126,6 +1231,10 @@ static int enqueue_search(spmb_context *ctx, const spmb_store *s, const spmb_pat
 {
     if (reset) CU(cudaMemsetAsync(h->d_count, 0, 4 * sizeof(unsigned long long), ctx->stream));
     HitSink sink{h->d_hits, h->d_count, h->cap};
+    if ((s->sym_bits == 4) != (p->sym_bits == 4))
+        return set_err(ctx, SPMB_ERR_ARG, "store and pattern differ in alphabet width (2-bit vs 4-bit)");
+    if (s->sym_bits == 4 && (s->lay.mode != SPMB_MODE_PLAIN || !s->hi))
+        return set_err(ctx, SPMB_ERR_UNSUPPORTED, "4-bit alphabets: plain stores only");
     if (p->max_m == 0 || s->lay.n == 0) return SPMB_OK; // empty needle / haystack: no hits
     const uint64_t st0 = s->lay.n_st * ctx->shard / ctx->n_shards;
     const uint64_t st1 = s->lay.n_st * (ctx->shard + 1) / ctx->n_shards;
@@ -1142,8 +1251,10 @@ static int enqueue_search(spmb_context *ctx, const spmb_store *s, const spmb_pat
         if (p->n_pat > 65535) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "more than 65535 patterns in one Myers set");
         int rc = store_ensure_lanes(ctx, s);
         if (rc) return rc;
+        if (s->hi) { rc = store_ensure_lanes(ctx, s->hi); if (rc) return rc; }
         MyersArgs a;
         a.lanes = s->lanes;
+        a.lanes_hi = s->hi ? s->hi->lanes : nullptr;
         a.mul4 = 4;
         a.eq_stride = (p->NW <= 4 ? 4 : 8) * 4;
         a.lay = s->lay;
@@ -1175,12 +1286,15 @@ static int enqueue_search(spmb_context *ctx, const spmb_store *s, const spmb_pat
         a.m = p->len[i];
         a.J = std::min<uint32_t>(a.m, 8);
         a.filt_syms = p->filt[i];
+        a.planes_hi = s->hi ? reinterpret_cast<const uint4 *>(s->hi->planes) : nullptr;
+        a.filt_syms_hi = s->hi ? p->filt_hi[i] : 0;
         a.seq_id = seq_id;
         a.pattern_id = i;
         a.sink = sink;
         unsigned blocks = (unsigned)((a.n_tiles - a.tile0 + 255) / 256);
         const unsigned grid = std::min(blocks, 8u * (unsigned)ctx->sm_count); // grid-stride kernel
-        if (s->lay.mode == SPMB_MODE_PLAIN) exact_kernel<SPMB_MODE_PLAIN><<<grid, 256, 0, ctx->stream>>>(a);
+        if (s->hi) exact_kernel<SPMB_MODE_PLAIN, true><<<grid, 256, 0, ctx->stream>>>(a);
+        else if (s->lay.mode == SPMB_MODE_PLAIN) exact_kernel<SPMB_MODE_PLAIN><<<grid, 256, 0, ctx->stream>>>(a);
         else exact_kernel<SPMB_MODE_WINDOWS><<<grid, 256, 0, ctx->stream>>>(a);
         ctx->launches++;
         CU(cudaGetLastError());
@@ -1401,6 +1515,7 @@ extern "C" int spmb_search_anchored(spmb_context *ctx, const spmb_store *s, cons
 {
     if (!ctx || !s || !p || !h || (n_anchors && !anchors)) return SPMB_ERR_ARG;
     if (p->alg != SPMB_ALG_MYERS_PREFIX) return set_err(ctx, SPMB_ERR_ARG, "anchored search takes a SPMB_ALG_MYERS_PREFIX pattern");
+    if (s->sym_bits != 2) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "anchored search is dna4 (2-bit) only");
     ENTER(ctx);
     ctx->launches = 0;
     h->host.clear();
@@ -1429,6 +1544,20 @@ extern "C" int spmb_search(spmb_context *ctx, const spmb_store *s, const spmb_pa
     int rc = spmb_search_launch(ctx, s, p, h);
     if (rc) return rc;
     return spmb_search_finish(ctx, h);
+}
+
+extern "C" int spmb_search_host_wide(spmb_context *ctx, const uint8_t *host_ranks, uint64_t n, uint32_t bits,
+                                     const spmb_pattern *p, spmb_hits *h)
+{
+    if (!ctx || !p || !h || (!host_ranks && n)) return SPMB_ERR_ARG;
+    spmb_store *s = nullptr;
+    int rc = spmb_store_create_wide(ctx, host_ranks, n, bits, 0, &s);
+    if (rc) return rc;
+    uint32_t pack_launches = ctx->launches;
+    rc = spmb_search(ctx, s, p, h);
+    ctx->launches += pack_launches;
+    spmb_store_destroy(s);
+    return rc;
 }
 
 extern "C" int spmb_search_host(spmb_context *ctx, const uint8_t *host_ranks, uint64_t n, const spmb_pattern *p,
@@ -1487,6 +1616,7 @@ extern "C" int spmb_jst_create(spmb_context *ctx, const spmb_store *reference, c
     if (!ctx || !reference || !out || n_hap == 0 || (n_var && (!variants || !coverage)) || (pool_len && !pool))
         return SPMB_ERR_ARG;
     if (reference->lay.mode != SPMB_MODE_PLAIN) return set_err(ctx, SPMB_ERR_ARG, "JST reference must be a plain store");
+    if (reference->sym_bits != 2) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "the JST is dna4 (2-bit) only");
     if (n_var >= (1ull << 32)) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "more than 2^32 variants");
     ENTER(ctx);
     spmb_jst *j = new (std::nothrow) spmb_jst();
@@ -1740,6 +1870,7 @@ extern "C" int spmb_stream_create(spmb_context *ctx, const spmb_pattern *p, spmb
 {
     if (!ctx || !p || !out) return SPMB_ERR_ARG;
     if (p->n_pat != 1) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "streams take a single pattern");
+    if (p->sym_bits != 2) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "streams are dna4 (2-bit) only");
     spmb_stream *st = new (std::nothrow) spmb_stream();
     if (!st) return SPMB_ERR_OOM;
     st->ctx = ctx; st->pat = p;

@@ -115,9 +115,9 @@ int orc_shiftor_init(orc_shiftor_t *s, const uint8_t *pat, uint32_t m)
     memset(s, 0, sizeof(*s));
     s->m = m;
     s->blocks = (m + 31) / 32;
-    for (int c = 0; c < 4; ++c)
+    for (int c = 0; c < ORC_SIGMA; ++c)
         for (uint32_t b = 0; b < s->blocks; ++b) s->mask[c][b] = 0xffffffffu;
-    for (uint32_t i = 0; i < m; ++i) s->mask[pat[i] & 3][i / 32] &= ~(1u << (i % 32));
+    for (uint32_t i = 0; i < m; ++i) s->mask[pat[i] & (ORC_SIGMA - 1)][i / 32] &= ~(1u << (i % 32));
     for (uint32_t b = 0; b < s->blocks; ++b) s->d[b] = 0xffffffffu;
     return 0;
 }
@@ -132,7 +132,7 @@ uint64_t orc_shiftor_run(orc_shiftor_t *s, const uint8_t *text, uint64_t n, uint
         uint32_t d = s->d[0];
         const uint32_t *b0 = &s->mask[0][0];
         for (uint64_t j = 0; j < n; ++j) {
-            d = (d << 1) | b0[(text[j] & 3) * 32];
+            d = (d << 1) | b0[(text[j] & (ORC_SIGMA - 1)) * 32];
             if (!(d & hit_bit)) {
                 if (ends && cnt < cap) ends[cnt] = base + j + 1;
                 ++cnt;
@@ -143,7 +143,7 @@ uint64_t orc_shiftor_run(orc_shiftor_t *s, const uint8_t *text, uint64_t n, uint
     }
     /* large needle: shift with carry across blocks (a 0 shifts into block 0) */
     for (uint64_t j = 0; j < n; ++j) {
-        const uint32_t *mk = s->mask[text[j] & 3];
+        const uint32_t *mk = s->mask[text[j] & (ORC_SIGMA - 1)];
         uint32_t carry = 0;
         for (uint32_t b = 0; b < nb; ++b) {
             uint32_t v = s->d[b];
@@ -179,7 +179,7 @@ int orc_myers_init(orc_myers_t *s, const uint8_t *pat, uint32_t m, uint32_t k)
     s->k = k;
     s->blocks = (m + 63) / 64;
     s->last_rows = m - 64 * (s->blocks - 1);
-    for (uint32_t i = 0; i < m; ++i) s->peq[pat[i] & 3][i / 64] |= 1ull << (i % 64);
+    for (uint32_t i = 0; i < m; ++i) s->peq[pat[i] & (ORC_SIGMA - 1)][i / 64] |= 1ull << (i % 64);
     /* _patternInit: VP = all ones, VN = 0, score = rows above */
     for (uint32_t b = 0; b < s->blocks; ++b) {
         s->vp[b] = ~0ull;
@@ -229,7 +229,7 @@ uint64_t orc_myers_run(orc_myers_t *s, const uint8_t *text, uint64_t n, uint64_t
         uint64_t vp = s->vp[0], vn = s->vn[0];
         int64_t score = s->score[0];
         for (uint64_t j = 0; j < n; ++j) {
-            uint64_t eq = s->peq[text[j] & 3][0];
+            uint64_t eq = s->peq[text[j] & (ORC_SIGMA - 1)][0];
             uint64_t x = eq | vn;
             uint64_t d0 = (((x & vp) + vp) ^ vp) | x;
             uint64_t hn = vp & d0;
@@ -255,7 +255,7 @@ uint64_t orc_myers_run(orc_myers_t *s, const uint8_t *text, uint64_t n, uint64_t
 
     int32_t lb = s->last_block;
     for (uint64_t j = 0; j < n; ++j) {
-        const uint64_t *eq = s->peq[text[j] & 3];
+        const uint64_t *eq = s->peq[text[j] & (ORC_SIGMA - 1)];
         int hin = 0, hout = 0;
         for (int32_t b = 0; b <= lb; ++b) {
             uint64_t ob = ((uint32_t)b + 1 == nb) ? last_bit : (1ull << 63);

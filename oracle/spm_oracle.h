@@ -48,9 +48,12 @@ uint64_t orc_horspool(const uint8_t *text, uint64_t n, const uint8_t *pat, uint3
 
 /* a9: Shift-Or, 32-bit blocks like SeqAn2 (blockCount = ceil(m/32)); resumable state =
  * prefSufMatch (libspm/libspm/matcher/shiftor_matcher_restorable.hpp:29,44-50). */
+/* symbols are 1-byte ranks; 16 covers spm::dna4 (4), spm::dna5 (5) and spm::dna15 (15)
+ * (libspm/libspm/seqan/alphabet.hpp:118-120) */
+#define ORC_SIGMA 16
 typedef struct {
     uint32_t m, blocks;
-    uint32_t mask[4][32];       /* B[c][block] : bit clear where pat[i]==c */
+    uint32_t mask[ORC_SIGMA][32]; /* B[c][block] : bit clear where pat[i]==c */
     uint32_t d[32];             /* state D (prefSufMatch) */
 } orc_shiftor_t;
 int      orc_shiftor_init(orc_shiftor_t *s, const uint8_t *pat, uint32_t m);
@@ -66,7 +69,7 @@ uint64_t orc_shiftor(const uint8_t *text, uint64_t n, const uint8_t *pat, uint32
 typedef struct {
     uint32_t m, k, blocks;
     uint32_t last_rows;                    /* rows in the last block (1..64) */
-    uint64_t peq[4][ORC_MAX_BLOCKS];
+    uint64_t peq[ORC_SIGMA][ORC_MAX_BLOCKS];
     /* --- state (capture/restore copies from here on) --- */
     uint64_t vp[ORC_MAX_BLOCKS], vn[ORC_MAX_BLOCKS];
     int64_t  score[ORC_MAX_BLOCKS];        /* D at the last row of each block */

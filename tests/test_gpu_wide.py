@@ -1,0 +1,179 @@
+"""GPU parity for the 4-bit alphabets (spm::dna5 / spm::dna15, libspm/libspm/seqan/alphabet.hpp:119-120) and for
+the two forms of the Myers kernel (Ukkonen cut-off = default, full recurrence): hit lists bit-exact against the
+CPU oracle (definitional: all-occurrence compare / Sellers DP; restated Horspool / Shift-Or / Myers)."""
+import numpy as np
+import pytest
+
+import libspm_b200 as sp
+import oracle as orc
+from tests.util import rand_text
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = sp.Context(0)
+    yield c
+    c.close()
+
+
+def _mutate(rng, pat, e, sigma):
+    p = list(pat)
+    for _ in range(e):
+        op = rng.integers(0, 3)
+        i = int(rng.integers(0, len(p)))
+        if op == 0:
+            p[i] = (p[i] + 1 + int(rng.integers(0, sigma - 1))) % sigma
+        elif op == 1:
+            p.insert(i, int(rng.integers(0, sigma)))
+        elif len(p) > 1:
+            del p[i]
+    return np.array(p, dtype=np.uint8)
+
+
+def _plant(rng, text, pat, copies, max_edits, sigma):
+    n = len(text)
+    for _ in range(copies):
+        q = _mutate(rng, pat, int(rng.integers(0, max_edits + 1)), sigma)
+        s = int(rng.integers(0, n - len(q)))
+        text[s:s + len(q)] = q
+
+
+@pytest.mark.parametrize("sigma,bits", [(5, 3), (15, 4), (16, 4)])
+@pytest.mark.parametrize("n,rl", [(37, 0), (5000, 32), (70001, 64), (400_003, 0)])
+def test_wide_round_trip_and_exact(ctx, sigma, bits, n, rl):
+    rng = np.random.default_rng(1000 * sigma + n)
+    text = rand_text(rng, n, sigma)
+    for m in (1, 5, 8, 9, 33, 70):
+        if m >= n:
+            continue
+        s0 = int(rng.integers(0, n - m))
+        pat = text[s0:s0 + m].copy()
+        if m >= 5:
+            _plant(rng, text, pat, 5, 0, sigma)
+    store = sp.Store.from_host_wide(ctx, text, bits, rl)
+    assert store.symbol_bits == 4 and len(store) == n
+    assert np.array_equal(store.read(), text)
+    for m in (1, 5, 8, 9, 33, 70):
+        if m >= n:
+            continue
+        s0 = int(rng.integers(0, n - m))
+        pat = text[s0:s0 + m].copy()
+        want = orc.exact_bruteforce(text, pat)
+        assert len(want) >= 1
+        # the restated searchers agree with the definition on this alphabet too
+        assert np.array_equal(orc.horspool(text, pat), want)
+        assert np.array_equal(orc.shiftor(text, pat), want)
+        for alg in (sp.ALG_HORSPOOL, sp.ALG_SHIFTOR):
+            p = sp.Pattern(ctx, alg, pat, bits=bits)
+            assert p.window_size == m
+            got = sp.search(ctx, store, p)
+            assert np.array_equal(got["end"], want), (sigma, n, rl, m, alg)
+            assert not got["errors"].any()
+            p.close()
+    store.close()
+
+
+def test_wide_symbols_that_differ_only_in_the_high_bits(ctx):
+    """ranks c and c+4 / c+8 / c+12 share their two low bits: the second plane pair must separate them."""
+    rng = np.random.default_rng(7)
+    n = 20000
+    low = rand_text(rng, n, 4)
+    text = (low + 4 * rand_text(rng, n, 4)).astype(np.uint8)
+    pat = text[1234:1234 + 24].copy()
+    twin = (pat ^ 4).astype(np.uint8)          # same low bits, other high bits
+    text[5000:5024] = twin
+    store = sp.Store.from_host_wide(ctx, text, 4)
+    p = sp.Pattern(ctx, sp.ALG_SHIFTOR, pat, bits=4)
+    got = sp.search(ctx, store, p)
+    assert np.array_equal(got["end"], orc.exact_bruteforce(text, pat))
+    assert 5024 not in got["end"].tolist()
+    pm = sp.Pattern(ctx, sp.ALG_MYERS, pat, 2, bits=4)
+    gm = sp.search(ctx, store, pm)
+    we, wr = orc.sellers(text, pat, 2)
+    assert np.array_equal(gm["end"], we) and np.array_equal(gm["errors"], wr)
+    p.close(); pm.close(); store.close()
+
+
+@pytest.mark.parametrize("sigma,bits", [(5, 3), (15, 4)])
+@pytest.mark.parametrize("m,k", [(7, 1), (32, 3), (33, 2), (64, 5), (100, 4), (150, 2), (200, 12), (256, 6)])
+def test_wide_myers(ctx, sigma, bits, m, k):
+    rng = np.random.default_rng(31 * m + k + sigma)
+    n = 150_000
+    text = rand_text(rng, n, sigma)
+    pat = rand_text(rng, m, sigma)
+    _plant(rng, text, pat, 40, k + 2, sigma)
+    store = sp.Store.from_host_wide(ctx, text, bits, 96 if m < 60 else 0)
+    _, we, wr = orc.search_mt(3, text, pat, k)
+    if m <= 64:   # the restated Myers against the definition (Sellers DP) on a slice
+        se, sr = orc.sellers(text[:15000], pat, k)
+        keep = we <= 15000
+        assert np.array_equal(we[keep], se) and np.array_equal(wr[keep], sr)
+    assert len(we) > 0
+    p = sp.Pattern(ctx, sp.ALG_MYERS, pat, k, bits=bits)
+    assert p.window_size == m + k
+    got = sp.search(ctx, store, p)
+    assert np.array_equal(got["end"], we), (sigma, m, k)
+    assert np.array_equal(got["errors"], wr)
+    # the reference's call shape: host haystack in, hits out
+    gh = sp.search_host(ctx, text, p, bits=bits)
+    assert np.array_equal(gh["end"], we) and np.array_equal(gh["errors"], wr)
+    p.close(); store.close()
+
+
+def test_width_mismatch_and_unsupported_paths_fail_loudly(ctx):
+    rng = np.random.default_rng(3)
+    text = rand_text(rng, 5000, 5)
+    wide = sp.Store.from_host_wide(ctx, text, 3)
+    narrow = sp.Store.from_host(ctx, text & 3)
+    p2 = sp.Pattern(ctx, sp.ALG_MYERS, text[10:50] & 3, 1)
+    p4 = sp.Pattern(ctx, sp.ALG_MYERS, text[10:50], 1, bits=3)
+    for st, p in ((wide, p2), (narrow, p4)):
+        with pytest.raises(sp.SpmbError) as ei:
+            sp.search(ctx, st, p)
+        assert ei.value.code == 1
+    with pytest.raises(sp.SpmbError) as ei:
+        sp.Pattern(ctx, sp.ALG_MYERS_FILTERED, text[10:110], 1, bits=4)
+    assert ei.value.code == 4
+    with pytest.raises(sp.SpmbError) as ei:
+        wide.journaled(np.zeros(0, sp.EVENT_DTYPE), np.zeros(0, np.uint8))
+    assert ei.value.code == 4
+    with pytest.raises(sp.SpmbError):
+        sp.Stream(ctx, p4)
+    for x in (p2, p4, wide, narrow):
+        x.close()
+
+
+# ---------------- the two forms of the Myers kernel ----------------
+def _adversarial_texts(rng, n):
+    yield "random", rand_text(rng, n)
+    yield "polyA", np.zeros(n, dtype=np.uint8)
+    per = rand_text(rng, 700)
+    yield "period-700", np.tile(per, n // 700 + 1)[:n].copy()
+    two = rand_text(rng, n, 2)
+    yield "binary", two
+
+
+@pytest.mark.parametrize("m,k", [(33, 0), (40, 3), (64, 8), (65, 1), (100, 4), (100, 29), (130, 10), (200, 3), (256, 20)])
+def test_myers_cutoff_equals_full_recurrence_and_oracle(ctx, m, k):
+    rng = np.random.default_rng(17 * m + k)
+    n = 120_000
+    for name, text in _adversarial_texts(rng, n):
+        s0 = int(rng.integers(0, n - m))
+        pat = text[s0:s0 + m].copy()
+        # needles a few substitutions off the text keep the active region deep without flooding the hit list
+        for i in rng.integers(0, m, size=max(1, k // 2 + 1)):
+            pat[i] = (pat[i] + 1) % 4
+        for rl in (0, 64):
+            store = sp.Store.from_host(ctx, text, rl)
+            p = sp.Pattern(ctx, sp.ALG_MYERS, pat, k)
+            ctx.set_myers_cutoff(True)
+            a = sp.search(ctx, store, p).copy()
+            ctx.set_myers_cutoff(False)
+            b = sp.search(ctx, store, p).copy()
+            ctx.set_myers_cutoff(True)
+            _, we, wr = orc.search_mt(3, text, pat, k)
+            assert np.array_equal(a["end"], b["end"]) and np.array_equal(a["errors"], b["errors"]), (name, m, k, rl)
+            assert np.array_equal(a["end"], we) and np.array_equal(a["errors"], wr), (name, m, k, rl)
+            p.close(); store.close()
