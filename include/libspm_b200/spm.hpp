@@ -14,6 +14,7 @@
 //   spm::window_size / capture / restore     libspm/libspm/matcher/concept.hpp:27-102
 //   spm::window_matcher / restorable_matcher libspm/libspm/matcher/concept.hpp:126-148
 //   spm::dna4, operator""_dna4               libspm/libspm/seqan/alphabet.hpp:34-83,118,122-135
+//   spm::dna5, spm::dna15, _dna5               libspm/libspm/seqan/alphabet.hpp:119-120,137-150
 //   seqan2::beginPosition / endPosition      (what the reference's callbacks call on the finder)
 // so that the reference's matcher tests read the same against this header.
 //
@@ -89,6 +90,53 @@ inline std::vector<dna4> operator""_dna4(const char *s, std::size_t n) {
     return v;
 }
 
+// spm::dna5 / spm::dna15 (alphabet.hpp:119-120 = alphabet_adaptor over seqan3::dna5 / seqan3::dna15): ranks in
+// seqan3's order (alphabetical: ACGNT, ABCDGHKMNRSTVWY), unknown characters convert to 'N'.  On the device
+// these travel in the 4-bit layout (two plane pairs; spmb_store_create_wide).
+namespace detail {
+template <std::size_t SIZE>
+class wide_nucleotide {
+    std::uint8_t _rank{0};
+    static constexpr const char *letters() noexcept { return SIZE == 5 ? "ACGNT" : "ABCDGHKMNRSTVWY"; }
+public:
+    constexpr wide_nucleotide() noexcept = default;
+    constexpr wide_nucleotide &assign_rank(std::uint8_t r) noexcept { _rank = r < SIZE ? r : std::uint8_t(SIZE - 1); return *this; }
+    constexpr wide_nucleotide &assign_char(char c) noexcept {
+        if (c >= 'a' && c <= 'z') c = static_cast<char>(c - 'a' + 'A');
+        if (c == 'U') c = 'T';
+        std::uint8_t n_rank = 0, found = 0xff;
+        for (std::uint8_t i = 0; i < SIZE; ++i) {
+            if (letters()[i] == 'N') n_rank = i;
+            if (letters()[i] == c) found = i;
+        }
+        _rank = found != 0xff ? found : n_rank;
+        return *this;
+    }
+    constexpr std::uint8_t to_rank() const noexcept { return _rank; }
+    constexpr char to_char() const noexcept { return letters()[_rank]; }
+    template <std::integral T> requires (!std::same_as<T, char>)
+    constexpr operator T() const noexcept { return static_cast<T>(_rank); }
+    constexpr operator char() const noexcept { return to_char(); }
+    friend constexpr bool operator==(wide_nucleotide a, wide_nucleotide b) noexcept { return a._rank == b._rank; }
+    friend constexpr auto operator<=>(wide_nucleotide a, wide_nucleotide b) noexcept { return a._rank <=> b._rank; }
+    static constexpr std::size_t alphabet_size = SIZE;
+};
+} // namespace detail
+using dna5 = detail::wide_nucleotide<5>;
+using dna15 = detail::wide_nucleotide<15>;
+static_assert(sizeof(dna5) == 1 && sizeof(dna15) == 1);
+
+inline std::vector<dna5> operator""_dna5(const char *s, std::size_t n) {
+    std::vector<dna5> v(n);
+    for (std::size_t i = 0; i < n; ++i) v[i].assign_char(s[i]);
+    return v;
+}
+inline std::vector<dna15> operator""_dna15(const char *s, std::size_t n) {
+    std::vector<dna15> v(n);
+    for (std::size_t i = 0; i < n; ++i) v[i].assign_char(s[i]);
+    return v;
+}
+
 // ------------------------------------------------------------------------------------------
 // errors + the process-wide device context
 // ------------------------------------------------------------------------------------------
@@ -130,6 +178,16 @@ constexpr std::uint8_t rank_of(const T &v) noexcept {
     if constexpr (requires { v.to_rank(); }) return static_cast<std::uint8_t>(v.to_rank());
     else return static_cast<std::uint8_t>(v) & 3u;
 }
+
+// symbol width of a range on the device: 2 bits for dna4 and plain integers, 4 for alphabets with more than
+// four letters (seqan2::BitsPerValue<dna5> = 3, <dna15> = 4, alphabet.hpp:107-112; both travel as 4)
+template <typename V>
+constexpr std::uint32_t symbol_bits() noexcept {
+    if constexpr (requires { V::alphabet_size; }) return V::alphabet_size > 4 ? 4u : 2u;
+    else return 2u;
+}
+template <typename R>
+constexpr std::uint32_t range_bits() noexcept { return symbol_bits<std::remove_cvref_t<std::ranges::range_value_t<R>>>(); }
 
 // a view of a range as contiguous 1-byte ranks: zero-copy for contiguous ranges of 1-byte
 // symbols (std::vector<spm::dna4>, std::span<uint8_t> ...), a packed temporary otherwise
@@ -183,9 +241,10 @@ public:
     template <std::ranges::input_range R>
     explicit device_sequence(R &&haystack) {
         auto &d = detail::device();
+        constexpr std::uint32_t bits = detail::range_bits<R>();
         detail::rank_buffer<R> buf{std::forward<R>(haystack)};
         spmb_store *s = nullptr;
-        detail::check(spmb_store_create(d.ctx, buf.ptr, buf.n, 0, &s), d.ctx, "spmb_store_create");
+        detail::check(spmb_store_create_wide(d.ctx, buf.ptr, buf.n, bits, 0, &s), d.ctx, "spmb_store_create");
         _store.reset(s, detail::store_deleter{});
     }
     explicit device_sequence(spmb_store *adopt) : _store(adopt, detail::store_deleter{}) {}
@@ -275,16 +334,22 @@ protected:
     std::shared_ptr<spmb_pattern> _pattern;
     std::size_t _needle_size{0};
     std::size_t _errors{0};
+    std::uint32_t _bits{2};
 
     template <std::ranges::input_range N>
     void build(N &&needle, std::size_t k) {
         auto &d = detail::device();
+        _bits = detail::range_bits<N>();
         detail::rank_buffer<N> buf{std::forward<N>(needle)};
         _needle_size = buf.n;
         _errors = k;
         spmb_pattern *p = nullptr;
-        detail::check(spmb_pattern_create(d.ctx, ALG, buf.ptr, static_cast<std::uint32_t>(buf.n),
-                                          static_cast<std::uint32_t>(k), &p), d.ctx, "spmb_pattern_create");
+        if (_bits == 2)
+            detail::check(spmb_pattern_create(d.ctx, ALG, buf.ptr, static_cast<std::uint32_t>(buf.n),
+                                              static_cast<std::uint32_t>(k), &p), d.ctx, "spmb_pattern_create");
+        else // spm::dna5 / spm::dna15 needles
+            detail::check(spmb_pattern_create_wide(d.ctx, ALG, buf.ptr, static_cast<std::uint32_t>(buf.n),
+                                                   static_cast<std::uint32_t>(k), _bits, &p), d.ctx, "spmb_pattern_create_wide");
         _pattern.reset(p, detail::pattern_deleter{});
     }
 
@@ -308,8 +373,12 @@ public:
                   !std::same_as<std::remove_cvref_t<haystack_t>, journaled_string_tree>)
     void operator()(haystack_t &&haystack, callback_t &&callback) {
         auto &d = detail::device();
+        constexpr std::uint32_t bits = detail::range_bits<haystack_t>();
         detail::rank_buffer<haystack_t> buf{std::forward<haystack_t>(haystack)};
-        detail::check(spmb_search_host(d.ctx, buf.ptr, buf.n, _pattern.get(), d.hits), d.ctx, "spmb_search_host");
+        if (bits == 2 && _bits == 2)
+            detail::check(spmb_search_host(d.ctx, buf.ptr, buf.n, _pattern.get(), d.hits), d.ctx, "spmb_search_host");
+        else // a needle and a haystack of different widths is the library's SPMB_ERR_ARG
+            detail::check(spmb_search_host_wide(d.ctx, buf.ptr, buf.n, bits, _pattern.get(), d.hits), d.ctx, "spmb_search_host_wide");
         replay(std::forward<callback_t>(callback));
     }
 

@@ -267,6 +267,10 @@ int spmb_jst_last_stats(const spmb_jst *j, uint64_t stats[4], double ms[4]);
  * They need no device and no context. */
 typedef struct spmb_fasta spmb_fasta;
 int spmb_fasta_read(const char *path, spmb_fasta **out);
+/* the same reader for spm::dna5 (bits = 3: ranks ACGNT = 0..4) or spm::dna15 (bits = 4: ABCDGHKMNRSTVWY = 0..14),
+ * seqan3's rank orders; characters outside the alphabet become N (counted); bits = 2 is spmb_fasta_read.
+ * The ranks feed spmb_store_create_wide. */
+int spmb_fasta_read_alphabet(const char *path, uint32_t bits, spmb_fasta **out);
 int spmb_fasta_destroy(spmb_fasta *fa);
 uint64_t spmb_fasta_count(const spmb_fasta *fa);
 const char *spmb_fasta_name(const spmb_fasta *fa, uint64_t i);

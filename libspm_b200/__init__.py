@@ -46,7 +46,7 @@ EXPORTS = [
     "spmb_context_set_shard", "spmb_context_set_myers_cutoff", "spmb_pigeonhole_create", "spmb_pattern_filter_info", "spmb_search_anchored",
     "spmb_upload_last_stats", "spmb_host_pack_chunks", "spmb_context_trim",
     "spmb_store_create_wide", "spmb_store_create_wide_from_device", "spmb_store_symbol_bits",
-    "spmb_pattern_create_wide", "spmb_pattern_symbol_bits", "spmb_search_host_wide",
+    "spmb_pattern_create_wide", "spmb_pattern_symbol_bits", "spmb_search_host_wide", "spmb_fasta_read_alphabet",
 ]
 
 
@@ -103,6 +103,7 @@ def lib():
             "spmb_pattern_create": (i32, [vp, i32, vp, u32, u32, pp]),
             "spmb_pattern_set_create": (i32, [vp, i32, vp, vp, u32, u32, pp]),
             "spmb_fasta_read": (i32, [C.c_char_p, pp]),
+            "spmb_fasta_read_alphabet": (i32, [C.c_char_p, u32, pp]),
             "spmb_fasta_destroy": (i32, [vp]),
             "spmb_fasta_count": (u64, [vp]),
             "spmb_fasta_name": (C.c_char_p, [vp, u64]),
@@ -560,11 +561,12 @@ def _np_from(ptr, n, dtype):
     return np.frombuffer(buf, dtype=dt, count=n).copy()
 
 
-def read_fasta(path: str):
+def read_fasta(path: str, bits: int = 2):
     """[(name, ranks)] of a FASTA file (plain or gzip) through spmb_fasta_read; also returns the number of
-    non-ACGT symbols (stored as rank 0 like seqan3::dna4)."""
+    symbols outside the alphabet (bits=2: dna4, stored as rank 0 like seqan3::dna4; bits=3 / 4: dna5 / dna15
+    in seqan3's rank order, stored as N)."""
     h = C.c_void_p()
-    rc = lib().spmb_fasta_read(os.fsencode(path), C.byref(h))
+    rc = lib().spmb_fasta_read_alphabet(os.fsencode(path), bits, C.byref(h))
     if rc:
         raise SpmbError(rc, "spmb_fasta_read", path)
     try:

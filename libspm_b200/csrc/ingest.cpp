@@ -31,6 +31,21 @@ inline int rank_of_char(char c, uint64_t &unknown)
     }
 }
 
+// seqan3 rank orders (alphabetical): dna5 = ACGNT, dna15 = ABCDGHKMNRSTVWY; unknown characters convert to N
+inline int rank_of_char_wide(char c, uint32_t bits, uint64_t &unknown)
+{
+    const char *letters = bits == 3 ? "ACGNT" : "ABCDGHKMNRSTVWY";
+    if (c >= 'a' && c <= 'z') c = (char)(c - 'a' + 'A');
+    if (c == 'U') c = 'T';
+    int n_rank = 0;
+    for (int i = 0; letters[i]; ++i) {
+        if (letters[i] == c) return i;
+        if (letters[i] == 'N') n_rank = i;
+    }
+    ++unknown;
+    return n_rank;
+}
+
 // line reader over gzopen (reads plain files too)
 struct LineReader {
     gzFile f = nullptr;
@@ -73,9 +88,11 @@ struct spmb_vcf {
     std::string contig;
 };
 
-extern "C" int spmb_fasta_read(const char *path, spmb_fasta **out)
+extern "C" int spmb_fasta_read(const char *path, spmb_fasta **out) { return spmb_fasta_read_alphabet(path, 2, out); }
+
+extern "C" int spmb_fasta_read_alphabet(const char *path, uint32_t bits, spmb_fasta **out)
 {
-    if (!path || !out) return SPMB_ERR_ARG;
+    if (!path || !out || bits < 2 || bits > 4) return SPMB_ERR_ARG;
     *out = nullptr;
     LineReader rd(path);
     if (!rd.ok()) return SPMB_ERR_ARG;
@@ -96,7 +113,8 @@ extern "C" int spmb_fasta_read(const char *path, spmb_fasta **out)
         if (line[0] == ';') continue;
         if (!have) { delete fa; return SPMB_ERR_ARG; } // sequence data before any header
         for (char c : line)
-            if (c != ' ' && c != '\t') fa->ranks.push_back((uint8_t)rank_of_char(c, fa->unknown));
+            if (c != ' ' && c != '\t')
+                fa->ranks.push_back((uint8_t)(bits == 2 ? rank_of_char(c, fa->unknown) : rank_of_char_wide(c, bits, fa->unknown)));
     }
     fa->offset.push_back(fa->ranks.size());
     *out = fa;

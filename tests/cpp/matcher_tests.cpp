@@ -255,4 +255,75 @@ MINI_TEST(filtered_myers_matcher_equals_myers_matcher) {
     EXPECT_TRUE(a == b);
 }
 
+// ---- spm::dna5 / spm::dna15 (alphabet.hpp:119-120; typed over all three alphabets in the reference's
+// test/api/libspm/seqan/alphabet_test.cpp:21-25): the same fixture with N / IUPAC letters mixed in ----
+MINI_TEST(alphabet_ranks_and_chars) {
+    using spm::operator""_dna5;
+    using spm::operator""_dna15;
+    auto s5 = "ACGNTx"_dna5;
+    EXPECT_EQ(s5[3].to_rank(), 3u);
+    EXPECT_EQ(s5[4].to_rank(), 4u);
+    EXPECT_EQ(s5[5].to_char(), 'N'); // unknown -> N like seqan3::dna5
+    auto s15 = "ABCDGHKMNRSTVWYu"_dna15;
+    for (std::size_t i = 0; i < 15; ++i) EXPECT_EQ(static_cast<std::size_t>(s15[i].to_rank()), i);
+    EXPECT_EQ(s15[15].to_char(), 'T');
+    EXPECT_EQ(spm::dna5::alphabet_size, 5u);
+    EXPECT_EQ(spm::dna15::alphabet_size, 15u);
+}
+
+MINI_TEST(dna5_patterns) {
+    using spm::operator""_dna5;
+    //                0         1         2         3         4
+    //                01234567890123456789012345678901234567890123
+    auto hay5    = "ACGTGACTAGCNCGTGACTAGCACGTGACTAGCNCGTGACTAGC"_dna5;
+    auto needle5 = "GCNCG"_dna5;
+    std::vector<std::size_t> begins{}, ends{};
+    spm::horspool_matcher h{needle5};
+    h(hay5, [&](auto const &f) { begins.push_back(seqan2::beginPosition(f)); });
+    EXPECT_TRUE(std::ranges::equal(begins, std::vector<std::size_t>{9, 31}));
+    begins.clear();
+    spm::shiftor_matcher so{needle5};
+    so(hay5, [&](auto const &f) { begins.push_back(seqan2::beginPosition(f)); });
+    EXPECT_TRUE(std::ranges::equal(begins, std::vector<std::size_t>{9, 31}));
+    // k = 1: the N occurrences within one error around 14 and 36, the GCACG at 20 by one substitution
+    spm::myers_matcher my{needle5, 1};
+    EXPECT_EQ(spm::window_size(my), 6u);
+    my(hay5, [&](auto const &f) { ends.push_back(seqan2::endPosition(f)); });
+    EXPECT_TRUE(std::ranges::equal(ends, std::vector<std::size_t>{13, 14, 15, 25, 35, 36, 37}));
+    // the same haystack resident on the device
+    spm::device_sequence dev{hay5};
+    ends.clear();
+    my(dev, [&](auto const &f) { ends.push_back(seqan2::endPosition(f)); });
+    EXPECT_TRUE(std::ranges::equal(ends, std::vector<std::size_t>{13, 14, 15, 25, 35, 36, 37}));
+}
+
+MINI_TEST(dna15_patterns) {
+    using spm::operator""_dna15;
+    auto hay15    = "ACGTRYACKMSWGTBDHVNACGTRYAC"_dna15;
+    auto needle15 = "RYAC"_dna15;
+    std::vector<std::size_t> begins{};
+    spm::shiftor_matcher so{needle15};
+    so(hay15, [&](auto const &f) { begins.push_back(seqan2::beginPosition(f)); });
+    EXPECT_TRUE(std::ranges::equal(begins, std::vector<std::size_t>{4, 23}));
+    // letters are symbols, not ambiguity sets: R does not match A or G (the reference compares ranks too)
+    auto needle_a = "AYAC"_dna15;
+    begins.clear();
+    spm::horspool_matcher h{needle_a};
+    h(hay15, [&](auto const &f) { begins.push_back(seqan2::beginPosition(f)); });
+    EXPECT_TRUE(begins.empty());
+}
+
+MINI_TEST(needle_and_haystack_of_different_alphabets_are_rejected) {
+    using spm::operator""_dna5;
+    auto needle5 = "GCNCG"_dna5;
+    spm::shiftor_matcher so{needle5};
+    bool threw = false;
+    try {
+        so(haystack, [&](auto const &) {});
+    } catch (spm::device_error const &e) {
+        threw = e.status == SPMB_ERR_ARG;
+    }
+    EXPECT_TRUE(threw);
+}
+
 int main() { return mini::run_all(); }

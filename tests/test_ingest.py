@@ -87,3 +87,18 @@ def test_ingest_of_reference_data_equals_committed_fixture(tag):
     ev = r["variants"].astype(orc.EVENT_DTYPE)
     for h in (0, 37, 99):
         assert np.array_equal(orc.jst_haplotype(recs[0][1], ev, r["pool"], r["coverage"], h), haps[h][1])
+
+
+def test_fasta_wide_alphabets(tmp_path):
+    """spmb_fasta_read_alphabet: seqan3's rank orders for dna5 (ACGNT) and dna15 (ABCDGHKMNRSTVWY)
+    (libspm/libspm/seqan/alphabet.hpp:119-120); characters outside the alphabet become N."""
+    p = tmp_path / "w.fa"
+    p.write_text(">r\nACGTNacgtnRYKMSWBDHVU-x\n")
+    got5, unk5 = sp.read_fasta(str(p), bits=3)
+    assert "".join("ACGNT"[x] for x in got5[0][1]) == "ACGTNACGTN" + "N" * 10 + "T" + "NN"
+    assert unk5 == 12
+    got15, unk15 = sp.read_fasta(str(p), bits=4)
+    assert "".join("ABCDGHKMNRSTVWY"[x] for x in got15[0][1]) == "ACGTNACGTNRYKMSWBDHVT" + "NN"
+    assert unk15 == 2
+    got4, unk4 = sp.read_fasta(str(p))
+    assert to_str(got4[0][1]) == "ACGTAACGTA" + "A" * 10 + "T" + "AA" and unk4 == 14
