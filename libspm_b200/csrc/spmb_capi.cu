@@ -1427,7 +1427,9 @@ static int hits_order_device(spmb_context *ctx, spmb_hits *h, const spmb_store *
     for (int f = 0; f < 4; ++f) if (spec.field[f] >= 0) total_bits += spec.bits[f];
     if (total_bits > 64) return SPMB_OK;
 
-    cudaStream_t sm = ctx->stream;
+    // on the stream that looked at the counters (the copy stream behind this launch's event): the sort of pass i
+    // then runs beside the kernels of pass i+1 instead of behind them
+    cudaStream_t sm = h->collect_stream ? h->collect_stream : ctx->stream;
     const uint32_t n = (uint32_t)cnt;
     unsigned long long *k0 = nullptr, *k1 = nullptr;
     uint32_t *i0 = nullptr, *i1 = nullptr, *isel = nullptr, *d_nsel = nullptr;

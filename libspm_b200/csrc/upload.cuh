@@ -161,6 +161,7 @@ struct UploadPool {
     uint64_t min_sym = 32ull << 20;
     int n_workers = 0;
     bool trace = false;                         // SPMB_UPLOAD_TRACE=1: per-job timings on stderr
+    uint64_t raw_pct_text = 100, raw_pct_events = 100; // SPMB_UPLOAD_RAW_PCT / SPMB_EVENT_RAW_PCT: most chunks (in %) the copy engine may take raw
 
     struct Worker {
         std::thread th;
@@ -228,6 +229,8 @@ struct UploadPool {
     cudaError_t init(int dev)
     {
         device = dev;
+        raw_pct_text = env_u64("SPMB_UPLOAD_RAW_PCT", raw_pct_text);
+        raw_pct_events = env_u64("SPMB_EVENT_RAW_PCT", raw_pct_events);
         chunk_sym = env_u64("SPMB_UPLOAD_CHUNK", chunk_sym);
         chunk_sym = (chunk_sym + 1023) / 1024 * 1024;
         if (chunk_sym < 1024) chunk_sym = 1024;
@@ -336,7 +339,7 @@ struct UploadPool {
     // the calling thread's half of a job: start the workers, feed head chunks to the copy engine (at most
     // SLOTS-1 ahead of the link, so the split stays adaptive), wait for the workers, drain `stream`
     template <class RawChunk>
-    cudaError_t drive(cudaStream_t stream, uint64_t *raw_out, RawChunk raw_chunk)
+    cudaError_t drive(cudaStream_t stream, uint64_t *raw_out, RawChunk raw_chunk, uint64_t raw_pct = 100)
     {
         cuda_err.store(0);
         packed_chunks.store(0);
@@ -360,6 +363,9 @@ struct UploadPool {
         bool used[SLOTS] = {false, false, false, false};
         while (e == cudaSuccess && cuda_err.load(std::memory_order_relaxed) == 0) {
             if (used[s]) e = cudaEventSynchronize(slot_ev[s]);
+            // a raw chunk costs the link 3-4x the bytes of a packed one: with packing threads at work the copy
+            // engine's share is capped (raw_pct of the chunks), or a fast link starves the packed copies
+            if (n_workers && raw * 100 >= raw_pct * n_chunks) break;
             if (e != cudaSuccess || !claim_head(idx)) break;
             e = raw_chunk(idx, s);
             if (e == cudaSuccess) e = cudaEventRecord(slot_ev[s], stream);
@@ -411,7 +417,7 @@ struct UploadPool {
             bytes_to_chunks_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, stream>>>(d_slot[s], len, d_chunks + p0 / 32);
             if (launches) ++*launches;
             return cudaGetLastError();
-        });
+        }, raw_pct_text);
         last_packed = packed_chunks.load();
         return e;
     }
@@ -434,7 +440,7 @@ struct UploadPool {
             const uint64_t i0 = idx * ev_chunk;
             const uint64_t len = (n - i0 < ev_chunk) ? n - i0 : ev_chunk;
             return cudaMemcpyAsync(d_ev + i0, ev_src + i0, len * sizeof(spmb_journal_event), cudaMemcpyHostToDevice, stream);
-        });
+        }, raw_pct_events);
         last_ev_packed = packed_chunks.load() - unpackable_chunks.load();
         last_ev_raw += unpackable_chunks.load();
         last_ev_chunk = ev_chunk;

@@ -177,3 +177,23 @@ def test_myers_cutoff_equals_full_recurrence_and_oracle(ctx, m, k):
             assert np.array_equal(a["end"], b["end"]) and np.array_equal(a["errors"], b["errors"]), (name, m, k, rl)
             assert np.array_equal(a["end"], we) and np.array_equal(a["errors"], wr), (name, m, k, rl)
             p.close(); store.close()
+
+
+def test_wide_empty_haystack_and_empty_needle(ctx):
+    """like the dna4 edge cases: nothing to find, no error (window_size 0 for an empty needle)."""
+    text = np.array([4, 0, 1, 4, 2], dtype=np.uint8)
+    empty = sp.Store.from_host_wide(ctx, np.zeros(0, np.uint8), 3)
+    store = sp.Store.from_host_wide(ctx, text, 3)
+    assert len(empty) == 0 and empty.symbol_bits == 4
+    for alg, k in ((sp.ALG_HORSPOOL, 0), (sp.ALG_SHIFTOR, 0), (sp.ALG_MYERS, 1)):
+        p = sp.Pattern(ctx, alg, text[1:4], k, bits=3)
+        assert len(sp.search(ctx, empty, p)) == 0
+        p.close()
+        p0 = sp.Pattern(ctx, alg, np.zeros(0, np.uint8), k, bits=3)
+        assert p0.window_size == 0
+        assert len(sp.search(ctx, store, p0)) == 0
+        p0.close()
+    # needle longer than the haystack
+    p = sp.Pattern(ctx, sp.ALG_SHIFTOR, np.array([4, 0, 1, 4, 2, 2], dtype=np.uint8), bits=3)
+    assert len(sp.search(ctx, store, p)) == 0
+    p.close(); empty.close(); store.close()
