@@ -161,7 +161,7 @@ struct UploadPool {
     uint64_t min_sym = 32ull << 20;
     int n_workers = 0;
     bool trace = false;                         // SPMB_UPLOAD_TRACE=1: per-job timings on stderr
-    uint64_t raw_pct_text = 100, raw_pct_events = 100; // SPMB_UPLOAD_RAW_PCT / SPMB_EVENT_RAW_PCT: most chunks (in %) the copy engine may take raw
+    uint64_t raw_pct_text = 100, raw_pct_events = 10; // SPMB_UPLOAD_RAW_PCT / SPMB_EVENT_RAW_PCT: most chunks (in %) the copy engine may take raw
 
     struct Worker {
         std::thread th;
