@@ -1053,7 +1053,7 @@ static cudaError_t launch_myers(spmb_context *ctx, const spmb_store *s, const sp
     // full recurrence for A/B measurements
     static const bool full = [] { const char *e = getenv("SPMB_MYERS_FULL"); return e && *e && *e != '0'; }();
     const bool cut = p->NW >= 2 && !full && ctx->myers_cutoff;
-    static const int split_env = [] { const char *e = getenv("SPMB_MYERS_SPLIT"); return e ? atoi(e) : 0; }();
+    const int split_env = [] { const char *e = getenv("SPMB_MYERS_SPLIT"); return e ? atoi(e) : 0; }(); // read per launch
     MyersArgs a = a_in;
     a.split = 1;
     if (cut && MODE == SPMB_MODE_PLAIN) {

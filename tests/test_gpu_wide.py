@@ -197,3 +197,24 @@ def test_wide_empty_haystack_and_empty_needle(ctx):
     p = sp.Pattern(ctx, sp.ALG_SHIFTOR, np.array([4, 0, 1, 4, 2, 2], dtype=np.uint8), bits=3)
     assert len(sp.search(ctx, store, p)) == 0
     p.close(); empty.close(); store.close()
+
+
+def test_myers_row_split_gives_the_same_hits(ctx, monkeypatch):
+    """SPMB_MYERS_SPLIT cuts every row into pieces with their own warm-up (one warp per piece): the hit list must
+    not change, including hits that straddle a piece seam."""
+    rng = np.random.default_rng(99)
+    n = 400_000
+    text = rand_text(rng, n)
+    pat = rand_text(rng, 90)
+    _plant(rng, text, pat, 300, 5, 4)
+    store = sp.Store.from_host(ctx, text, 2048)       # long rows: up to 3 pieces of >= 4 x (warm-up + 32) columns
+    p = sp.Pattern(ctx, sp.ALG_MYERS, pat, 4)
+    monkeypatch.delenv("SPMB_MYERS_SPLIT", raising=False)
+    base = sp.search(ctx, store, p).copy()
+    _, we, wr = orc.search_mt(3, text, pat, 4)
+    assert np.array_equal(base["end"], we) and np.array_equal(base["errors"], wr) and len(we) > 100
+    for split in ("2", "3", "8"):
+        monkeypatch.setenv("SPMB_MYERS_SPLIT", split)
+        got = sp.search(ctx, store, p)
+        assert np.array_equal(got["end"], we) and np.array_equal(got["errors"], wr), split
+    p.close(); store.close()
