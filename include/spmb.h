@@ -130,6 +130,12 @@ int spmb_upload_last_stats(const spmb_context *ctx, uint64_t stats[8]);
  * 32 symbols = the store's lane-chunk word (uint2 {x,y} in memory: 2-bit codes, first symbol in the top
  * bits of x, symbols 16..31 in y); ranks are masked to 2 bits, symbols past n are 0. */
 void spmb_host_pack_chunks(const uint8_t *ranks, uint64_t n, uint64_t *out);
+/* the host loop that rewrites a chunk of n 24-byte events as 8-byte records (no device needed; AVX2 where the CPU has
+ * it): out = ceil(n/1024) headers {uint64 base_pos, uint64 base_off} followed by n words
+ * {dpos:32 | doff:16 | del_len:8 | ins_len:8} (ref_pos - base_pos, ins_off - base_off of the block; an event that
+ * inserts nothing stores doff 0 and its offset is only checked against pool_len).  Returns 1, or 0 when some event
+ * does not fit this form (the chunk then travels as it is). */
+int spmb_host_pack_events(const spmb_journal_event *events, uint32_t n, uint64_t pool_len, uint8_t *out);
 /* journaled sequence: base + events, materialised on the device into a new packed store whose
  * coordinates are those of the derived sequence. */
 int spmb_store_create_journaled(spmb_context *ctx, const spmb_store *base,

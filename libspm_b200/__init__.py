@@ -47,6 +47,7 @@ EXPORTS = [
     "spmb_upload_last_stats", "spmb_host_pack_chunks", "spmb_context_trim",
     "spmb_store_create_wide", "spmb_store_create_wide_from_device", "spmb_store_symbol_bits",
     "spmb_pattern_create_wide", "spmb_pattern_symbol_bits", "spmb_search_host_wide", "spmb_fasta_read_alphabet",
+    "spmb_host_pack_events",
 ]
 
 
@@ -94,6 +95,7 @@ def lib():
             "spmb_search_host_wide": (i32, [vp, vp, u64, u32, vp, vp]),
             "spmb_upload_last_stats": (i32, [vp, C.POINTER(u64 * 8)]),
             "spmb_host_pack_chunks": (None, [vp, u64, vp]),
+            "spmb_host_pack_events": (i32, [vp, u32, u64, vp]),
             "spmb_store_create_journaled": (i32, [vp, vp, vp, u64, vp, u64, u32, pp]),
             "spmb_store_destroy": (i32, [vp]),
             "spmb_store_length": (u64, [vp]),
@@ -159,6 +161,18 @@ def _status(code):
         return lib().spmb_status_string(code).decode()
     except Exception:
         return "?"
+
+
+def host_pack_events(events, pool_len: int):
+    """spmb_host_pack_events: (headers uint64[n_blk, 2], records uint64[n]) or None when an event does not fit."""
+    ev = np.ascontiguousarray(events, dtype=EVENT_DTYPE)
+    n = ev.size
+    n_blk = (n + 1023) // 1024
+    out = np.zeros(2 * n_blk + n, dtype=np.uint64)
+    ok = lib().spmb_host_pack_events(ev.ctypes.data if n else None, n, pool_len, out.ctypes.data)
+    if not ok:
+        return None
+    return out[:2 * n_blk].reshape(n_blk, 2), out[2 * n_blk:]
 
 
 def host_pack_chunks(ranks) -> np.ndarray:

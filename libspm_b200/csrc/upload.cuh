@@ -112,33 +112,10 @@ static inline size_t spmb_packed_events_bytes(uint32_t n)
     return (size_t)((n + EV_BLOCK - 1) / EV_BLOCK) * sizeof(SpmbPackedEventHeader) + (size_t)n * sizeof(SpmbPackedEvent);
 }
 
-// host side of the above; false = some record does not fit (the chunk then travels raw)
-static inline bool spmb_host_pack_events(const spmb_journal_event *ev, uint32_t n, uint64_t pool_len, uint8_t *out)
-{
-    const uint32_t n_blk = (n + EV_BLOCK - 1) / EV_BLOCK;
-    SpmbPackedEventHeader *hdr = reinterpret_cast<SpmbPackedEventHeader *>(out);
-    SpmbPackedEvent *rec = reinterpret_cast<SpmbPackedEvent *>(out + n_blk * sizeof(SpmbPackedEventHeader));
-    uint64_t bad = 0;
-    for (uint32_t b = 0; b < n_blk; ++b) {
-        const uint32_t i0 = b * EV_BLOCK, i1 = (i0 + EV_BLOCK < n) ? i0 + EV_BLOCK : n;
-        SpmbPackedEventHeader h{ev[i0].ref_pos, 0};
-        for (uint32_t i = i0; i < i1; ++i)
-            if (ev[i].ins_len) { h.base_off = ev[i].ins_off; break; }
-        if (h.base_off > pool_len) return false;
-        hdr[b] = h;
-        for (uint32_t i = i0; i < i1; ++i) {
-            const uint64_t dp = ev[i].ref_pos - h.base_pos;
-            uint64_t dof = ev[i].ins_off - h.base_off;
-            if (ev[i].ins_len == 0) { bad |= (uint64_t)(ev[i].ins_off > pool_len); dof = 0; }
-            bad |= (dp >> 32) | (dof >> 16) | (ev[i].del_len >> 8) | (ev[i].ins_len >> 8);
-            rec[i].dpos = (uint32_t)dp;
-            rec[i].doff = (uint16_t)dof;
-            rec[i].del_len = (uint8_t)ev[i].del_len;
-            rec[i].ins_len = (uint8_t)ev[i].ins_len;
-        }
-    }
-    return bad == 0;
-}
+// host side of the above (hostpack.cpp; AVX2 where the CPU has it): 0 = some record does not fit, the chunk
+// then travels raw
+static_assert(sizeof(SpmbPackedEvent) == 8 && sizeof(SpmbPackedEventHeader) == 16, "short event form");
+extern "C" int spmb_host_pack_events(const spmb_journal_event *ev, uint32_t n, uint64_t pool_len, uint8_t *out);
 
 static inline int spmb_host_cpus()
 {

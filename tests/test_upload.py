@@ -176,3 +176,68 @@ def test_event_table_through_upload_queue(small_chunks, monkeypatch, threads):
             base.journaled(bad, pool)
     finally:
         ctx.close()
+
+
+# ---------------- the host loop of the event-table upload (no device needed) ----------------
+def _events(rng, n, *, big_gap_at=None):
+    ev = np.zeros(n, dtype=sp.EVENT_DTYPE)
+    kind = rng.integers(0, 10, n)
+    gaps = rng.integers(20, 200, n).astype(np.uint64)
+    if big_gap_at is not None:
+        gaps[big_gap_at] = 1 << 33
+    dl = np.where(kind < 8, 1, np.where(kind == 8, 0, rng.integers(1, 11, n))).astype(np.uint32)
+    il = np.where(kind < 8, 1, np.where(kind == 8, rng.integers(1, 11, n), 0)).astype(np.uint32)
+    ev["ref_pos"] = np.cumsum(gaps + np.concatenate([[0], dl[:-1]]).astype(np.uint64))
+    ev["del_len"], ev["ins_len"] = dl, il
+    off = np.concatenate([[0], np.cumsum(il)[:-1]]).astype(np.uint64)
+    ev["ins_off"] = np.where(il > 0, off, 0)
+    return ev, int(il.sum())
+
+
+def _pack_events_numpy(ev):
+    n = len(ev)
+    n_blk = (n + 1023) // 1024
+    hdr = np.zeros((n_blk, 2), dtype=np.uint64)
+    rec = np.zeros(n, dtype=np.uint64)
+    for b in range(n_blk):
+        blk = ev[b * 1024:(b + 1) * 1024]
+        ins = np.nonzero(blk["ins_len"])[0]
+        base_pos, base_off = blk["ref_pos"][0], (blk["ins_off"][ins[0]] if len(ins) else 0)
+        hdr[b] = (base_pos, base_off)
+        dof = np.where(blk["ins_len"] > 0, blk["ins_off"] - np.uint64(base_off), 0).astype(np.uint64)
+        rec[b * 1024:(b + 1) * 1024] = ((blk["ref_pos"] - base_pos) | (dof << np.uint64(32)) |
+                                        (blk["del_len"].astype(np.uint64) << np.uint64(48)) |
+                                        (blk["ins_len"].astype(np.uint64) << np.uint64(56)))
+    return hdr, rec
+
+
+@pytest.mark.parametrize("n", [1, 3, 4, 5, 1023, 1024, 1025, 4099, 70001])
+def test_host_pack_events_matches_numpy(n):
+    rng = np.random.default_rng(n)
+    ev, pool_len = _events(rng, n)
+    got = sp.host_pack_events(ev, pool_len)
+    assert got is not None
+    hdr, rec = _pack_events_numpy(ev)
+    assert np.array_equal(got[0], hdr) and np.array_equal(got[1], rec)
+
+
+def test_host_pack_events_rejects_what_does_not_fit():
+    rng = np.random.default_rng(5)
+    ev, pool_len = _events(rng, 5000)
+    assert sp.host_pack_events(ev, pool_len) is not None
+    for field, idx, val in (("del_len", 4001, 256), ("ins_len", 77, 300), ("del_len", 3, 1 << 20)):
+        bad = ev.copy()
+        bad[field][idx] = val
+        assert sp.host_pack_events(bad, pool_len + 1000) is None, (field, idx)
+    bad, pl = _events(rng, 5000, big_gap_at=2500)          # position delta >= 2^32 inside a block
+    assert sp.host_pack_events(bad, pl) is None
+    bad = ev.copy()                                          # an event that inserts nothing but points past the pool
+    i = int(np.nonzero(bad["ins_len"] == 0)[0][10])
+    bad["ins_off"][i] = pool_len + 1
+    assert sp.host_pack_events(bad, pool_len) is None
+    bad["ins_off"][i] = (1 << 63) + 5
+    assert sp.host_pack_events(bad, pool_len) is None
+    bad = ev.copy()                                          # pool offsets 2^16 apart inside one block
+    j = np.nonzero(bad["ins_len"])[0]
+    bad["ins_off"][j[50]:] += 1 << 16
+    assert sp.host_pack_events(bad, pool_len + (1 << 17)) is None
