@@ -11,8 +11,8 @@
 //   invariant   at a decision column all rows >= 32*A hold a true value D > k;
 //   diagonal    D[i][j] >= D[i-1][j-1], so a row r with D > k for all rows >= r at column j gives
 //               D > k for all rows >= r + t at column j + t;
-//   decision    the smallest a whose rows >= 32a - C are provably > k now (lower bound from popcounts:
-//               score below word a-1 + popc(VP[a-1] & rows 0..23) - every VN bit from word a-1 up)
+//   decision    the smallest a whose rows >= 32a - C are provably > k now (lower bounds from popcounts, word by
+//               word: see myers_cut_next)
 //               keeps rows >= 32a above k for the next C columns; if no a <= A qualifies, A grows by one
 //               word, initialised VP = ~0, VN = 0 (an upper bound of the true column, as in SeqAn2).
 // Computing words 0..A-1 alone is the exact recurrence of the needle prefix (carries only run upward),
@@ -108,23 +108,30 @@ __device__ __forceinline__ void myers_cut_chunk(uint32_t (&vp)[NW], uint32_t (&v
     }
 }
 
-// number of words this row needs for the next 8 columns, given words 0..A-1 are valid now
+// number of words this row needs for the next 8 columns, given words 0..A-1 are valid now.
+// Lower bounds from popcounts (S = value at the bottom of the previous word, P/N = VP/VN bits of a word):
+//   every row of word w            D >= S_{w-1} - N_w
+//   rows 24..31 of word a-1        D >= S_{a-2} + popc(VP_{a-1} & rows 0..23) - N_{a-1}
+// a words suffice when both kinds of rows from 32a - 8 upward are above k.  (Bounding the upper words one by one
+// instead of subtracting all their VN bits at once lets a warp fall back to one word right after an excursion:
+// with the coarse bound a return from 2 words to 1 was a coin toss at k = 4 and rare at k = 8.)
 template <int A, int NW>
 __device__ __forceinline__ int myers_cut_next(const uint32_t (&vp)[NW], const uint32_t (&vn)[NW], int k)
 {
-    int P[A], N[A];
-    int nt = 0; // VN bits from word a-1 upward
+    int N[A], S[A + 1];
+    S[0] = 0;
 #pragma unroll
-    for (int w = 0; w < A; ++w) { P[w] = __popc(vp[w]); N[w] = __popc(vn[w]); nt += N[w]; }
-    int S = 0;  // value at the bottom of word a-2
+    for (int w = 0; w < A; ++w) { N[w] = __popc(vn[w]); S[w + 1] = S[w] + __popc(vp[w]) - N[w]; }
+    int M[A + 1]; // M[w] = min over words v >= w of (S_{v-1} - N_v)
+    M[A] = 0x3fffffff;
+#pragma unroll
+    for (int w = A - 1; w >= 1; --w) M[w] = min(M[w + 1], S[w] - N[w]);
     int res = (A < NW) ? A + 1 : NW;
     bool found = false;
 #pragma unroll
     for (int a = 1; a <= A; ++a) {
-        const int lb = S + __popc(vp[a - 1] & 0x00ffffffu) - nt; // <= D of every valid row >= 32a - 8
+        const int lb = min(S[a - 1] + __popc(vp[a - 1] & 0x00ffffffu) - N[a - 1], M[a]);
         if (!found && lb > k) { res = a; found = true; }
-        S += P[a - 1] - N[a - 1];
-        nt -= N[a - 1];
     }
     return res;
 }
