@@ -136,17 +136,17 @@ def build_c2x(sp, synth, torch, ctx, dev, n, seed, m=64):
 
 def time_search(sp, torch, ctx, stream, store, pattern, hits, steps, warmup, flush=None):
     """returns (total_ms for `steps` launch+finish passes, mean kernel ms, n_hits, launches/step).
-    The passes are pipelined the way the launch/finish pair of the C ABI is meant to be used: pass i+1 is
-    queued (on a second hit list) before pass i's hits are collected, so the host's share of a pass
-    (D2H of the counters + short hit list, sort) runs under the next kernel.  Every pass still delivers its
+    The passes are pipelined the way the launch/finish pair of the C ABI is meant to be used: passes i+1 and
+    i+2 are queued (on their own hit lists) before pass i's hits are collected, so the host's share of a pass
+    (D2H of the counters + hit list, ordering) runs under the next kernels.  Every pass still delivers its
     sorted hit list to the host."""
-    hits_b = sp.Hits(ctx, 1 << 16)
-    hl = (hits, hits_b)
-    for _ in range(warmup):
+    DEPTH = 3                       # passes in flight: two queued behind the one being collected
+    hl = (hits,) + tuple(sp.Hits(ctx, 1 << 16) for _ in range(DEPTH - 1))
+    for w in range(max(warmup, 2 * DEPTH)):     # every hit list twice: buffers sized, long-list ordering armed
         if flush is not None:
             flush.add_(1)
-        sp.search_launch(ctx, store, pattern, hits)
-        sp.search_finish(ctx, hits)
+        sp.search_launch(ctx, store, pattern, hl[w % DEPTH])
+        sp.search_finish(ctx, hl[w % DEPTH])
     ks = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
     ke = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -159,14 +159,15 @@ def time_search(sp, torch, ctx, stream, store, pattern, hits, steps, warmup, flu
         if flush is not None:
             flush.add_(1)       # evict L2 between iterations (buffer > L2)
         ks[i].record(stream)
-        sp.search_launch(ctx, store, pattern, hl[i & 1])
+        sp.search_launch(ctx, store, pattern, hl[i % DEPTH])
         ke[i].record(stream)
 
-    launch(0)
+    for i in range(min(DEPTH - 1, steps)):
+        launch(i)
     for i in range(steps):
-        if i + 1 < steps:
-            launch(i + 1)
-        n_hits = len(sp.search_finish(ctx, hl[i & 1]))
+        if i + DEPTH - 1 < steps:
+            launch(i + DEPTH - 1)
+        n_hits = len(sp.search_finish(ctx, hl[i % DEPTH]))
     e1.record(stream)
     torch.cuda.synchronize()
     kern = [ks[i].elapsed_time(ke[i]) for i in range(steps)]
@@ -251,7 +252,7 @@ def run_ours(args):
                        "searched_bp_per_step_per_gpu": n_der, "pattern_len": m, "hits": n_hits,
                        "l2": f"inputs larger than L2 ({n_der * BYTES_PER_BP / 1e6:.0f} MB packed text vs 126 MB)",
                        "row_len": js.row_len, "journal_materialise_ms": journal_ms,
-                       "step": "kernel launch + hit count/list D2H + host sort; pass i+1 is queued before pass i's hits are "
+                       "step": "kernel launch + hit count/list D2H + host sort; passes i+1 and i+2 are queued before pass i's hits are "
                                "collected (spmb_search_launch / spmb_search_finish on two hit lists)"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                          "frac": achieved / hbm_peak, "traffic": ncu_traffic("exact_c2x"), "peak_source": peak_src,

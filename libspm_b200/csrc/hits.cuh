@@ -61,3 +61,45 @@ __global__ void hit_gather_kernel(const spmb_hit *__restrict__ hits, const uint3
     if (i >= n) return;
     out[i] = hits[idx[i]];
 }
+
+// ---- the same ordering enqueued WITH the search (spmb_search_launch on a hit list that saw a long list last
+// time): the list length is only known on the device, so the kernels run over the whole buffer (cap slots) and
+// read the count themselves; empty slots get a key above every real one (bit `pad_bit`).
+__global__ void hit_keys_dev_kernel(const spmb_hit *__restrict__ hits, const unsigned long long *__restrict__ count,
+                                    uint32_t cap, HitKeySpec spec, int pad_bit, unsigned long long *__restrict__ keys,
+                                    uint32_t *__restrict__ idx)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= cap) return;
+    const unsigned long long n = min(*count, (unsigned long long)cap);
+    unsigned long long k = 1ull << pad_bit;
+    if (i < n) {
+        const spmb_hit h = hits[i];
+        k = 0;
+#pragma unroll
+        for (int f = 0; f < 4; ++f)
+            if (spec.field[f] >= 0) k = (k << spec.bits[f]) | hit_field(h, spec.field[f]);
+    }
+    keys[i] = k;
+    idx[i] = i;
+}
+
+__global__ void hit_flags_dev_kernel(const unsigned long long *__restrict__ keys, const unsigned long long *__restrict__ count,
+                                     uint32_t cap, int drop_bits, uint8_t *__restrict__ flag)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= cap) return;
+    const unsigned long long n = min(*count, (unsigned long long)cap);
+    flag[i] = i < n && ((i == 0) || ((keys[i] >> drop_bits) != (keys[i - 1] >> drop_bits)));
+}
+
+// out[i] = hits[idx[i]] for i < n, n = *n_sel (deduplicated lists) or min(*count, cap), which is then also
+// written to *n_sel for the host
+__global__ void hit_gather_dev_kernel(const spmb_hit *__restrict__ hits, const uint32_t *__restrict__ idx,
+                                      const unsigned long long *__restrict__ count, uint32_t *__restrict__ n_sel,
+                                      int use_sel, uint32_t cap, spmb_hit *__restrict__ out)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t n = use_sel ? min(*n_sel, cap) : (uint32_t)min(*count, (unsigned long long)cap);
+    if (i < n) out[i] = hits[idx[i]];
+}

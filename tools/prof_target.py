@@ -60,6 +60,23 @@ with torch.cuda.stream(stream):
             ctx.sync(); t2 = time.perf_counter()
             h = sp.search_finish(ctx, hits); t3 = time.perf_counter()
             print(f"launch {1e3*(t1-t0):.3f} ms  kernels {1e3*(t2-t1):.3f} ms  finish {1e3*(t3-t2):.3f} ms  total {1e3*(t3-t0):.3f} ms")
+        # pipelined: two passes queued behind the one being collected; host time of every call
+        hl = [hits, sp.Hits(ctx, 1 << 16), sp.Hits(ctx, 1 << 16)]
+        for hh in hl + hl:
+            sp.search(ctx, st, p, hh)
+        steps = 12
+        torch.cuda.synchronize(); T0 = time.perf_counter()
+        log = []
+        for i in range(2):
+            a0 = time.perf_counter(); sp.search_launch(ctx, st, p, hl[i % 3]); log.append(("L", i, a0 - T0, time.perf_counter() - T0))
+        for i in range(steps):
+            if i + 2 < steps:
+                a0 = time.perf_counter(); sp.search_launch(ctx, st, p, hl[(i + 2) % 3]); log.append(("L", i + 2, a0 - T0, time.perf_counter() - T0))
+            a0 = time.perf_counter(); sp.search_finish(ctx, hl[i % 3]); log.append(("F", i, a0 - T0, time.perf_counter() - T0))
+        torch.cuda.synchronize(); T1 = time.perf_counter()
+        print(f"pipelined depth 3: {1e3*(T1-T0)/steps:.3f} ms per step")
+        for kind, i, a, b in log:
+            print(f"  {kind}{i:2d}  start {1e3*a:7.3f}  end {1e3*b:7.3f}  ({1e3*(b-a):.3f} ms)")
         st.close()
     if what == "e2e":
         # per-call times of the headline e2e path: host ranks + journal -> hits
