@@ -218,3 +218,59 @@ def test_myers_row_split_gives_the_same_hits(ctx, monkeypatch):
         got = sp.search(ctx, store, p)
         assert np.array_equal(got["end"], we) and np.array_equal(got["errors"], wr), split
     p.close(); store.close()
+
+
+def test_long_hit_lists_ordered_by_the_launch(ctx):
+    """A hit list that was long (>= 4096) once is sorted / deduplicated by the next launch itself
+    (spmb_search_launch enqueues the ordering behind the kernels): same lists as the first pass and the oracle,
+    through a reused Hits object, pipelined launches, and a later short list on the same object."""
+    rng = np.random.default_rng(2024)
+    n = 300_000
+    text = rand_text(rng, n, 2)                       # binary text: a short needle hits often
+    store = sp.Store.from_host(ctx, text)
+    hits = sp.Hits(ctx)
+    pat = text[1000:1012].copy()
+    want_exact = orc.exact_bruteforce(text, pat)
+    assert len(want_exact) >= 4096 // 64
+    pm = text[5000:5040].copy()                       # two words: the cut-off kernel, ~37 k hits
+    _, we, wr = orc.search_mt(3, text, pm, 10)
+    assert len(we) >= 4096
+    p = sp.Pattern(ctx, sp.ALG_MYERS, pm, 10)
+    for rep in range(4):                              # pass 0 arms the path, passes 1.. use it
+        got = sp.search(ctx, store, p, hits)
+        assert np.array_equal(got["end"], we) and np.array_equal(got["errors"], wr), rep
+    # two lists in flight
+    hits_b = sp.Hits(ctx)
+    sp.search(ctx, store, p, hits_b)
+    sp.search_launch(ctx, store, p, hits)
+    sp.search_launch(ctx, store, p, hits_b)
+    a = sp.search_finish(ctx, hits).copy()
+    b = sp.search_finish(ctx, hits_b).copy()
+    assert np.array_equal(a["end"], we) and np.array_equal(b["end"], we) and np.array_equal(b["errors"], wr)
+    # the same Hits object, now a short list (exact) and a long one again, then a pattern set through the filter
+    pe = sp.Pattern(ctx, sp.ALG_SHIFTOR, pat)
+    for rep in range(2):
+        got = sp.search(ctx, store, pe, hits)
+        assert np.array_equal(got["end"], want_exact)
+    got = sp.search(ctx, store, p, hits)
+    assert np.array_equal(got["end"], we) and np.array_equal(got["errors"], wr)
+    t4 = rand_text(rng, n)
+    needles = []
+    for i in range(40):
+        q = t4[5000 * i + 77:5000 * i + 77 + 100].copy()
+        needles.append(q)
+        for c in range(150):
+            s0 = int(rng.integers(0, n - 200))
+            t4[s0:s0 + 100] = q
+    st4 = sp.Store.from_host(ctx, t4)
+    pf = sp.Pattern(ctx, sp.ALG_MYERS_FILTERED, needles, 3)
+    pd = sp.Pattern(ctx, sp.ALG_MYERS, needles, 3)
+    direct = sp.search(ctx, st4, pd).copy()
+    assert len(direct) >= 4096
+    for rep in range(3):
+        got = sp.search(ctx, st4, pf, hits)
+        assert len(got) == len(direct), (rep, len(got), len(direct))
+        for f in ("pattern_id", "end", "errors"):
+            assert np.array_equal(got[f], direct[f]), (rep, f)
+    for x in (p, pe, pf, pd, hits, hits_b, store, st4):
+        x.close()
