@@ -140,7 +140,7 @@ def time_search(sp, torch, ctx, stream, store, pattern, hits, steps, warmup, flu
     i+2 are queued (on their own hit lists) before pass i's hits are collected, so the host's share of a pass
     (D2H of the counters + hit list, ordering) runs under the next kernels.  Every pass still delivers its
     sorted hit list to the host."""
-    DEPTH = 3                       # passes in flight: two queued behind the one being collected
+    DEPTH = int(os.environ.get("SPMB_BENCH_DEPTH", "3"))   # passes in flight: two queued behind the one being collected
     hl = (hits,) + tuple(sp.Hits(ctx, 1 << 16) for _ in range(DEPTH - 1))
     for w in range(max(warmup, 2 * DEPTH)):     # every hit list twice: buffers sized, long-list ordering armed
         if flush is not None:
