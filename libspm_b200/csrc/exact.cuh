@@ -19,7 +19,7 @@
 //
 // Tried and measured against this shape on B200 (3.2 Gbp, 800 MB): a persistent TMA ring
 // (cp.async.bulk + mbarriers, 3 x 72 KB and 5 x 40 KB stages, 512 consumer threads) 148 / 170 us, and
-// private cp.async (LDGSTS) slots with 160 KB in flight per SM 155 us, against 141-146 us here; the
+// private cp.async (LDGSTS) slots with 160 KB in flight per SM 155 us, against 141-146 us then and 126-131 us now; the
 // kernel is co-limited by the ALU pipe (8 LOP3 per column = 70 us) and DRAM (114 us for a pure read,
 // tools/ubench_read.cu), and independent load-then-compute warps overlap the two best.
 #pragma once
