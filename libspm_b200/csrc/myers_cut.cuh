@@ -255,6 +255,30 @@ __global__ void __launch_bounds__(128) myers_cut_kernel(MyersArgs a)
                 }
             }
             p += 8 * q;
+        } else if (NW > 2 && A == 2) {
+            // two words (k around 10, or the columns right after an excursion): same shape, the warp leaves as
+            // soon as its word count changes
+#pragma unroll
+            for (int qq = 0; qq < 4; ++qq) {
+                if (qq == 2) { w = cur.y; wh = cur_hi.y; }
+                uint32_t d0 = 0, d1 = 0;
+                myers_cut_chunk<2, NW, false, WIDE>(vp, vn, w, wh, eq_base, mul4, eq_stride, d0, d1);
+                q = qq + 1;
+                const int An = __reduce_max_sync(0xffffffffu, myers_cut_next<(NW > 2 ? 2 : 1), NW>(vp, vn, k));
+                if (An != 2) {
+                    if (An > 2) {
+                        vp[2 % NW] = 0xffffffffu; vn[2 % NW] = 0;
+                        if (NW == 3) {
+                            score = 0;
+#pragma unroll
+                            for (int i = 0; i < NW; ++i) score += (int)__popc(vp[i]) - (int)__popc(vn[i]);
+                        }
+                    }
+                    A = An;
+                    break;
+                }
+            }
+            p += 8 * q;
         }
 #pragma unroll 1
         for (; q < 4; ++q) {
