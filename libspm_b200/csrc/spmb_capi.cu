@@ -34,6 +34,8 @@ struct spmb_context {
     int device = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
+    cudaStream_t aux_stream = nullptr;     // small JST buckets run here beside the large ones (jst_enqueue)
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     cudaStream_t copy_stream = nullptr;    // counters + short hit lists come back here, behind the launch's event:
                                            // a later launch already queued on `stream` does not delay them
     std::string err;
@@ -74,6 +76,9 @@ static void context_free(spmb_context *ctx)
     for (auto &b : ctx->blocks) cudaFreeAsync(b.p, ctx->stream);
     ctx->blocks.clear();
     if (ctx->copy_stream) { cudaStreamSynchronize(ctx->copy_stream); cudaStreamDestroy(ctx->copy_stream); }
+    if (ctx->aux_stream) { cudaStreamSynchronize(ctx->aux_stream); cudaStreamDestroy(ctx->aux_stream); }
+    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+    if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
     if (ctx->own_stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
     if (ctx->h_count) cudaFreeHost(ctx->h_count);
     if (ctx->h_spec) cudaFreeHost(ctx->h_spec);
@@ -243,6 +248,13 @@ extern "C" int spmb_context_create(int device, void *stream, spmb_context **out)
     else {
         if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return SPMB_ERR_CUDA; }
         ctx->own_stream = true;
+    }
+    if (cudaStreamCreateWithFlags(&ctx->aux_stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming) != cudaSuccess) {
+        cudaGetLastError();
+        if (ctx->aux_stream) cudaStreamDestroy(ctx->aux_stream);
+        ctx->aux_stream = nullptr;
     }
     {   // highest priority: the small ordering kernels of a finished pass go ahead of the next pass's search kernels
         int prio_lo = 0, prio_hi = 0;
@@ -1957,11 +1969,35 @@ static int jst_enqueue(spmb_context *ctx, spmb_jst *j, const spmb_pattern *p, sp
 {
     int rc = enqueue_search(ctx, j->ref, p, h, true, JST_REF_SEQ); // one scan of the reference
     if (rc) return rc;
-    for (auto &b : j->buckets) {                                   // + the branch-context windows
+    // + the branch-context windows, one launch per length bucket.  Buckets of a few long windows fill a fraction
+    // of the device for tens of microseconds each (C4: 4 of 7 buckets, 130 of 1010 us): the direct kernels only
+    // share the hit sink (atomics), so those launches go to a second stream beside the large ones.
+    const bool direct = !p->filtered && p->alg != SPMB_ALG_PIGEONHOLE && p->alg != SPMB_ALG_MYERS_PREFIX &&
+                        !getenv("SPMB_JST_SERIAL");
+    cudaStream_t main_stream = ctx->stream;
+    bool forked = false;
+    for (auto &b : j->buckets) {
+        const bool small = direct && ctx->aux_stream && b.store->lanes &&
+                           b.store->lay.n_st < 16ull * (uint64_t)ctx->sm_count; // fewer than 4 CTAs per SM
+        if (small) {
+            if (!forked) {
+                if (cudaEventRecord(ctx->ev_fork, main_stream) != cudaSuccess ||
+                    cudaStreamWaitEvent(ctx->aux_stream, ctx->ev_fork, 0) != cudaSuccess)
+                    return set_err(ctx, SPMB_ERR_CUDA, "jst fork", cudaGetLastError());
+                forked = true;
+            }
+            ctx->stream = ctx->aux_stream;
+        }
         rc = enqueue_search(ctx, b.store, p, h, false, 0);
-        if (rc) return rc;
+        ctx->stream = main_stream;
+        if (rc) break;
     }
-    return SPMB_OK;
+    if (forked) {
+        if (cudaEventRecord(ctx->ev_join, ctx->aux_stream) != cudaSuccess ||
+            cudaStreamWaitEvent(main_stream, ctx->ev_join, 0) != cudaSuccess)
+            return set_err(ctx, SPMB_ERR_CUDA, "jst join", cudaGetLastError());
+    }
+    return rc;
 }
 
 extern "C" int spmb_jst_search(spmb_context *ctx, spmb_jst *j, const spmb_pattern *p, spmb_hits *h)
