@@ -126,3 +126,33 @@ def test_jst_filtered_myers_equals_oracle(ctx, n_hap, n_var, seed):
             compare(got, want, f"filtered m={len(pat)} k={k} haps={n_hap}")
             assert len(want) >= 1
     jst.close()
+
+
+def test_jst_small_buckets_beside_large_ones(ctx):
+    # enough variants that the common window lengths fill the device (main stream) while the few long windows
+    # make small buckets (second stream, jst_enqueue): same hits as the serial order and as the oracle
+    import os
+    n_ref, n_var, n_hap = 8_000_000, 700_000, 16
+    ref, var, pool, cov = make_jst(n_ref, n_var, n_hap, 77, p_snp=0.85, p_ins=0.08, max_indel=60, af_max=0.6)
+    store = sp.Store.from_host(ctx, ref)
+    jst = sp.Jst(ctx, store, var, pool, cov, n_hap)
+    rng = np.random.default_rng(78)
+    hap = orc.jst_haplotype(ref, var.astype(orc.EVENT_DTYPE), pool, cov, 3)
+    for alg, m, k in [(sp.ALG_MYERS, 40, 2), (sp.ALG_SHIFTOR, 20, 0), (sp.ALG_MYERS, 90, 3)]:
+        s = int(rng.integers(0, len(hap) - m))
+        pat = hap[s:s + m].copy()
+        p = sp.Pattern(ctx, alg, pat, k)
+        got = jst.search(p)
+        os.environ["SPMB_JST_SERIAL"] = "1"
+        try:
+            serial = jst.search(p)
+        finally:
+            del os.environ["SPMB_JST_SERIAL"]
+        for f in ("seq_id", "end", "errors"):
+            assert np.array_equal(got[f], serial[f]), f
+        want = orc.jst_search(alg, ref, var.astype(orc.EVENT_DTYPE), pool, cov, n_hap, pat, k)
+        compare(got, want, f"alg={alg} m={m} k={k}")
+        assert len(want) >= 1
+    st = jst.last_stats()
+    assert st["buckets"] >= 2 and st["windows"] > 2 * 16 * 32 * 148   # at least one bucket past 4 CTAs per SM
+    jst.close()
