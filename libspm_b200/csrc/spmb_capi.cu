@@ -1967,36 +1967,36 @@ static int jst_prepare(spmb_context *ctx, spmb_jst *j, uint32_t W)
 
 static int jst_enqueue(spmb_context *ctx, spmb_jst *j, const spmb_pattern *p, spmb_hits *h)
 {
-    int rc = enqueue_search(ctx, j->ref, p, h, true, JST_REF_SEQ); // one scan of the reference
-    if (rc) return rc;
-    // + the branch-context windows, one launch per length bucket.  Buckets of a few long windows fill a fraction
-    // of the device for tens of microseconds each (C4: 4 of 7 buckets, 130 of 1010 us): the direct kernels only
-    // share the hit sink (atomics), so those launches go to a second stream beside the large ones.
+    // One scan of the reference + the branch-context windows, one launch per length bucket.  The reference scan
+    // and the buckets of a few long windows fill a fraction of the device for tens of microseconds each (C4: the
+    // scan + 4 of 7 buckets, 190 of 1010 us): the direct kernels only share the hit sink (atomics), so those
+    // launches go to a second stream beside the large buckets.
     const bool direct = !p->filtered && p->alg != SPMB_ALG_PIGEONHOLE && p->alg != SPMB_ALG_MYERS_PREFIX &&
-                        !getenv("SPMB_JST_SERIAL");
+                        ctx->aux_stream && !j->buckets.empty() && !getenv("SPMB_JST_SERIAL");
     cudaStream_t main_stream = ctx->stream;
-    bool forked = false;
+    if (!direct) {
+        int rc = enqueue_search(ctx, j->ref, p, h, true, JST_REF_SEQ);
+        if (rc) return rc;
+        for (auto &b : j->buckets) { rc = enqueue_search(ctx, b.store, p, h, false, 0); if (rc) return rc; }
+        return SPMB_OK;
+    }
+    if (cudaMemsetAsync(h->d_count, 0, 4 * sizeof(unsigned long long), main_stream) != cudaSuccess ||
+        cudaEventRecord(ctx->ev_fork, main_stream) != cudaSuccess ||
+        cudaStreamWaitEvent(ctx->aux_stream, ctx->ev_fork, 0) != cudaSuccess)
+        return set_err(ctx, SPMB_ERR_CUDA, "jst fork", cudaGetLastError());
+    ctx->stream = ctx->aux_stream;
+    int rc = enqueue_search(ctx, j->ref, p, h, false, JST_REF_SEQ);
+    ctx->stream = main_stream;
     for (auto &b : j->buckets) {
-        const bool small = direct && ctx->aux_stream && b.store->lanes &&
-                           b.store->lay.n_st < 16ull * (uint64_t)ctx->sm_count; // fewer than 4 CTAs per SM
-        if (small) {
-            if (!forked) {
-                if (cudaEventRecord(ctx->ev_fork, main_stream) != cudaSuccess ||
-                    cudaStreamWaitEvent(ctx->aux_stream, ctx->ev_fork, 0) != cudaSuccess)
-                    return set_err(ctx, SPMB_ERR_CUDA, "jst fork", cudaGetLastError());
-                forked = true;
-            }
-            ctx->stream = ctx->aux_stream;
-        }
+        if (rc) break;
+        const bool small = b.store->lanes && b.store->lay.n_st < 16ull * (uint64_t)ctx->sm_count; // under 4 CTAs per SM
+        if (small) ctx->stream = ctx->aux_stream;
         rc = enqueue_search(ctx, b.store, p, h, false, 0);
         ctx->stream = main_stream;
-        if (rc) break;
     }
-    if (forked) {
-        if (cudaEventRecord(ctx->ev_join, ctx->aux_stream) != cudaSuccess ||
-            cudaStreamWaitEvent(main_stream, ctx->ev_join, 0) != cudaSuccess)
-            return set_err(ctx, SPMB_ERR_CUDA, "jst join", cudaGetLastError());
-    }
+    if (cudaEventRecord(ctx->ev_join, ctx->aux_stream) != cudaSuccess ||
+        cudaStreamWaitEvent(main_stream, ctx->ev_join, 0) != cudaSuccess)
+        return set_err(ctx, SPMB_ERR_CUDA, "jst join", cudaGetLastError());
     return rc;
 }
 
