@@ -253,8 +253,10 @@ int spmb_stream_restore(spmb_stream *st, const void *buf, size_t size);
  * is expanded to (haplotype id = seq_id, end in that haplotype's coordinates, errors).
  * variants: sorted by ref_pos (insertions first on ties); coverage: n_variants rows of
  * ceil(n_haplotypes/64) 64-bit words, bit h of row v set = haplotype h carries variant v; the
- * variants carried by one haplotype must form a valid journal (sorted, non-overlapping).
- * The reference store must outlive the JST. */
+ * variants carried by one haplotype must form a valid journal (sorted, non-overlapping: every carried variant
+ * starts at or behind the end of the previous one, which puts insertions first on ties); spmb_jst_create checks
+ * this per haplotype and returns SPMB_ERR_ARG otherwise (spmb_vcf_read never produces such input: it clears the
+ * later of two overlapping calls, spmb_vcf_dropped_calls).  The reference store must outlive the JST. */
 typedef struct spmb_jst spmb_jst;
 int spmb_jst_create(spmb_context *ctx, const spmb_store *reference, const spmb_journal_event *variants,
                     uint64_t n_variants, const uint8_t *ins_pool, uint64_t pool_len,
@@ -298,6 +300,9 @@ uint32_t spmb_vcf_haplotype_count(const spmb_vcf *v);
 uint32_t spmb_vcf_sample_count(const spmb_vcf *v);
 const char *spmb_vcf_sample_name(const spmb_vcf *v, uint32_t i);
 int spmb_vcf_stats(const spmb_vcf *v, uint64_t stats[3]); /* [0] records of the contig, [1] skipped, [2] non-ACGT symbols */
+/* (variant, haplotype) calls cleared because they overlap an earlier call of the same haplotype (a SNP inside a
+ * called deletion ...): the first call wins, so that every haplotype's variants form a valid journal */
+uint64_t spmb_vcf_dropped_calls(const spmb_vcf *v);
 
 /* ---------------- measurement helpers ---------------- */
 /* INT32 ALU-pipe peak (LOP3 / IADD3 chains on all SMs), in 1e9 lane-instructions per second:

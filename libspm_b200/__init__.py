@@ -47,7 +47,7 @@ EXPORTS = [
     "spmb_upload_last_stats", "spmb_host_pack_chunks", "spmb_context_trim",
     "spmb_store_create_wide", "spmb_store_create_wide_from_device", "spmb_store_symbol_bits",
     "spmb_pattern_create_wide", "spmb_pattern_symbol_bits", "spmb_search_host_wide", "spmb_fasta_read_alphabet",
-    "spmb_host_pack_events",
+    "spmb_host_pack_events", "spmb_vcf_dropped_calls",
 ]
 
 
@@ -121,6 +121,7 @@ def lib():
             "spmb_vcf_sample_count": (u32, [vp]),
             "spmb_vcf_sample_name": (C.c_char_p, [vp, u32]),
             "spmb_vcf_stats": (i32, [vp, C.POINTER(u64 * 3)]),
+            "spmb_vcf_dropped_calls": (u64, [vp]),
             "spmb_pigeonhole_create": (i32, [vp, vp, vp, u32, C.c_double, pp]),
             "spmb_pattern_filter_info": (i32, [vp, C.POINTER(u32 * 5)]),
             "spmb_search_anchored": (i32, [vp, vp, vp, vp, u64, vp]),
@@ -613,6 +614,7 @@ def read_vcf(path: str, contig: str | None = None, ref_len: int = 0):
         return {"variants": _np_from(L.spmb_vcf_variants(h), nv, EVENT_DTYPE), "pool": pool, "coverage": cov,
                 "n_haplotypes": int(L.spmb_vcf_haplotype_count(h)),
                 "samples": [L.spmb_vcf_sample_name(h, i).decode() for i in range(int(L.spmb_vcf_sample_count(h)))],
-                "stats": {"records": st[0], "skipped": st[1], "unknown_symbols": st[2]}}
+                "stats": {"records": st[0], "skipped": st[1], "unknown_symbols": st[2],
+                          "dropped_calls": int(L.spmb_vcf_dropped_calls(h))}}
     finally:
         lib().spmb_vcf_destroy(h)

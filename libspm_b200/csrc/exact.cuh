@@ -37,7 +37,11 @@ struct ExactArgs {
     const uint32_t *row_own; // windows mode: first owned end per row (hits ending earlier belong elsewhere); may be null
     uint32_t m;
     uint32_t J;              // filter depth = min(m, 8)
-    uint32_t filt_syms;      // pattern symbol j at bits [2j, 2j+1], j < J
+    uint32_t fo;             // offset of the filter window inside the needle: a candidate at column c is the alignment
+                             // that begins at column c - fo.  The host picks the least repetitive 8-symbol window of
+                             // the needle (pattern_build): on low-complexity text (poly-A, satellites) the FIRST eight
+                             // symbols may match everywhere while a later window still rejects almost every alignment
+    uint32_t filt_syms;      // pattern symbol fo + j at bits [2j, 2j+1], j < J
     // 4-bit alphabets (spm::dna5 / spm::dna15, alphabet.hpp:119-120): a second plane pair holds bits 3..2 of
     // every symbol, in the same geometry; the filter accumulates over both pairs
     const uint4 *planes_hi;  // null for dna4
@@ -69,50 +73,70 @@ __device__ __forceinline__ uint32_t exact_acc(uint32_t acc, uint32_t h, uint32_t
     }
 
 // Warp-cooperative verification of the candidates in one column word.
-// gc = global column, cm = candidate bits (bit b = row b).  Lane i checks pattern offsets
-// J+i, J+i+32, ...; returns the surviving candidate mask (same value in every lane).
+// gc = global column of the candidates (= alignment begin + fo), cm = candidate bits (bit b = row b).  Lane i checks
+// pattern offsets i, i+32, ...; returns the surviving candidate mask (same value in every lane).
+// Needle symbol j of the alignment sits at column col - fo + j of the same row: past the row end it continues in
+// the next row(s) (one bit up; row 31 continues in row 0 of the next super-tile), before the row start in the
+// previous row(s) (one bit down).
 template <int MODE, bool WIDE>
 __device__ __forceinline__ uint32_t exact_verify(const ExactArgs &a, uint64_t gc, uint32_t cm, uint32_t lane)
 {
     const uint2 *P2 = reinterpret_cast<const uint2 *>(a.planes);
     const uint2 *P2H = reinterpret_cast<const uint2 *>(a.planes_hi);
-    const uint32_t RL = a.lay.row_len;
-    uint64_t st = spmb_div_rl(a.lay, gc);
-    uint32_t col = (uint32_t)(gc - st * RL);
-    for (uint32_t j0 = a.J; j0 < a.m && cm; j0 += 32) {
-        uint32_t j = j0 + lane;
+    const int64_t RL = (int64_t)a.lay.row_len;
+    const uint64_t st = spmb_div_rl(a.lay, gc);
+    const int64_t col = (int64_t)(gc - st * (uint64_t)RL);
+    {   // alignments that begin before the first row of the text (plain) / before their own row (windows)
+        const int64_t x0 = col - (int64_t)a.fo;
+        if (x0 < 0) {
+            if (MODE != SPMB_MODE_PLAIN) return 0;
+            const uint32_t back = (uint32_t)((-x0 + RL - 1) / RL);
+            if (st == 0) cm &= (back >= 32) ? 0u : ~((1u << back) - 1u);
+        }
+    }
+    for (uint32_t j0 = 0; j0 < a.m && cm; j0 += 32) {
+        const uint32_t j = j0 + lane;
         uint32_t mm = 0xffffffffu;
         if (j < a.m) {
-            uint32_t x = col + j, wraps = 0;
-            if (x >= RL) { wraps = x / RL; x -= wraps * RL; }
-            uint32_t h, l;
+            const int64_t xi = col - (int64_t)a.fo + (int64_t)j;
+            int64_t wraps = xi >= 0 ? xi / RL : -((-xi + RL - 1) / RL);
+            const uint64_t x = (uint64_t)(xi - wraps * RL);
+            const uint32_t s = a.pat[j];
+            uint32_t h, l, hh = 0, lh = 0;
             if (wraps == 0) {
-                uint2 v = __ldg(P2 + spmb_perm(st * RL + x));
+                const uint2 v = __ldg(P2 + spmb_perm(st * RL + x));
                 h = v.x; l = v.y;
-                uint32_t s = a.pat[j];
-                mm = ~((h ^ (0u - ((s >> 1) & 1u))) | (l ^ (0u - (s & 1u))));
+                if (WIDE) { const uint2 u = __ldg(P2H + spmb_perm(st * RL + x)); hh = u.x; lh = u.y; }
+            } else if (MODE != SPMB_MODE_PLAIN) {
+                h = l = 0;
+                mm = 0; // windows do not continue: nothing can match outside the row
+            } else if (wraps > 0) {
+                const uint2 v0 = __ldg(P2 + spmb_perm(st * RL + x));
+                const uint2 v1 = __ldg(P2 + spmb_perm((st + 1) * RL + x));
+                h = __funnelshift_r(v0.x, v1.x, (uint32_t)wraps);
+                l = __funnelshift_r(v0.y, v1.y, (uint32_t)wraps);
                 if (WIDE) {
-                    v = __ldg(P2H + spmb_perm(st * RL + x));
-                    mm &= ~((v.x ^ (0u - ((s >> 3) & 1u))) | (v.y ^ (0u - ((s >> 2) & 1u))));
-                }
-            } else if (MODE == SPMB_MODE_PLAIN) {
-                // the pattern runs off the row end: row r continues in row r+1 (next bit),
-                // row 31 continues in row 0 of the next super-tile
-                uint2 v0 = __ldg(P2 + spmb_perm(st * RL + x));
-                uint2 v1 = __ldg(P2 + spmb_perm((st + 1) * RL + x));
-                h = __funnelshift_r(v0.x, v1.x, wraps);
-                l = __funnelshift_r(v0.y, v1.y, wraps);
-                uint32_t s = a.pat[j];
-                mm = ~((h ^ (0u - ((s >> 1) & 1u))) | (l ^ (0u - (s & 1u))));
-                if (WIDE) {
-                    v0 = __ldg(P2H + spmb_perm(st * RL + x));
-                    v1 = __ldg(P2H + spmb_perm((st + 1) * RL + x));
-                    h = __funnelshift_r(v0.x, v1.x, wraps);
-                    l = __funnelshift_r(v0.y, v1.y, wraps);
-                    mm &= ~((h ^ (0u - ((s >> 3) & 1u))) | (l ^ (0u - ((s >> 2) & 1u))));
+                    const uint2 u0 = __ldg(P2H + spmb_perm(st * RL + x));
+                    const uint2 u1 = __ldg(P2H + spmb_perm((st + 1) * RL + x));
+                    hh = __funnelshift_r(u0.x, u1.x, (uint32_t)wraps);
+                    lh = __funnelshift_r(u0.y, u1.y, (uint32_t)wraps);
                 }
             } else {
-                mm = 0; // windows do not continue: nothing can match past the row
+                const uint32_t w = (uint32_t)(-wraps);
+                const uint2 v0 = __ldg(P2 + spmb_perm(st * RL + x));
+                const uint2 vp = st ? __ldg(P2 + spmb_perm((st - 1) * RL + x)) : make_uint2(0, 0);
+                h = __funnelshift_l(vp.x, v0.x, w);
+                l = __funnelshift_l(vp.y, v0.y, w);
+                if (WIDE) {
+                    const uint2 u0 = __ldg(P2H + spmb_perm(st * RL + x));
+                    const uint2 up = st ? __ldg(P2H + spmb_perm((st - 1) * RL + x)) : make_uint2(0, 0);
+                    hh = __funnelshift_l(up.x, u0.x, w);
+                    lh = __funnelshift_l(up.y, u0.y, w);
+                }
+            }
+            if (mm) {
+                mm = ~((h ^ (0u - ((s >> 1) & 1u))) | (l ^ (0u - (s & 1u))));
+                if (WIDE) mm &= ~((hh ^ (0u - ((s >> 3) & 1u))) | (lh ^ (0u - ((s >> 2) & 1u))));
             }
         }
         cm &= __reduce_and_sync(0xffffffffu, mm);
@@ -131,11 +155,12 @@ __device__ __forceinline__ void exact_emit(const ExactArgs &a, uint64_t gc, uint
     uint64_t end;
     uint32_t seq = a.seq_id;
     if (MODE == SPMB_MODE_PLAIN) {
-        end = R * RL + col + a.m;
-        ok = ok && (end <= a.lay.n);
+        const int64_t begin = (int64_t)(R * RL + col) - (int64_t)a.fo;
+        end = (uint64_t)(begin + (int64_t)a.m);
+        ok = ok && begin >= 0 && (end <= a.lay.n);
     } else {
-        end = (uint64_t)col + a.m;
-        ok = ok && (R * RL < a.lay.n) && (end <= a.row_len[R]) && (!a.row_own || end >= a.row_own[R]);
+        end = (uint64_t)col + a.m - a.fo;
+        ok = ok && (col >= a.fo) && (R * RL < a.lay.n) && (end <= a.row_len[R]) && (!a.row_own || end >= a.row_own[R]);
         if (ok && a.row_seq) seq = a.row_seq[R];
     }
     uint32_t em = __ballot_sync(0xffffffffu, ok);

@@ -9,6 +9,20 @@ struct HitSink {
     unsigned long long cap;
 };
 
+#ifdef __CUDACC__
+#include <cooperative_groups.h>
+// next free slot of a compacted buffer, warp-aggregated: the lanes that reach the append together (a divergent
+// branch of a scan loop) share ONE atomicAdd -- on a hit-dense text all 32 lanes of a warp report in the same
+// column, and 32 atomics on one address per column would serialise in L2
+__device__ __forceinline__ unsigned long long spmb_append_slot(unsigned long long *count)
+{
+    const cooperative_groups::coalesced_group g = cooperative_groups::coalesced_threads();
+    unsigned long long base = 0;
+    if (g.thread_rank() == 0) base = atomicAdd(count, (unsigned long long)g.size());
+    return g.shfl(base, 0) + g.thread_rank();
+}
+#endif
+
 // Hit order from atomics is nondeterministic; short lists are sorted on the host, long ones here:
 // every hit becomes one 64-bit key (its fields concatenated in comparison order), CUB radix-sorts
 // (key, index) pairs over the bits in use, and the hits are gathered in that order.  For the filtered
@@ -93,8 +107,8 @@ __global__ void hit_flags_dev_kernel(const unsigned long long *__restrict__ keys
     flag[i] = i < n && ((i == 0) || ((keys[i] >> drop_bits) != (keys[i - 1] >> drop_bits)));
 }
 
-// out[i] = hits[idx[i]] for i < n, n = *n_sel (deduplicated lists) or min(*count, cap), which is then also
-// written to *n_sel for the host
+// out[i] = hits[idx[i]] for i < n, n = *n_sel (deduplicated lists: use_sel) or min(*count, cap).  *n_sel is only
+// written by the deduplication (DeviceSelect) -- without it the host takes the length from *count
 __global__ void hit_gather_dev_kernel(const spmb_hit *__restrict__ hits, const uint32_t *__restrict__ idx,
                                       const unsigned long long *__restrict__ count, uint32_t *__restrict__ n_sel,
                                       int use_sel, uint32_t cap, spmb_hit *__restrict__ out)

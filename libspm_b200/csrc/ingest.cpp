@@ -85,6 +85,7 @@ struct spmb_vcf {
     std::vector<std::string> samples;
     uint32_t n_hap = 0, ploidy = 0, wpr = 0;
     uint64_t records = 0, skipped = 0, unknown = 0;
+    uint64_t dropped_calls = 0; // (variant, haplotype) calls cleared because they overlap an earlier call of that haplotype
     std::string contig;
 };
 
@@ -232,6 +233,23 @@ extern "C" int spmb_vcf_read(const char *path, const char *contig, uint64_t ref_
         return (a.del != 0) < (b.del != 0);
     });
     if (v->n_hap == 0) { v->n_hap = (uint32_t)v->samples.size() * (v->ploidy ? v->ploidy : 2); v->wpr = (v->n_hap + 63) / 64; }
+    // a haplotype's calls must form a valid journal (spmb_jst_create's contract): where one ALT overlaps an
+    // earlier call of the same haplotype (a SNP inside a called deletion, two ALTs of one multi-allelic site
+    // through different records), the first call wins and the later one is cleared for that haplotype
+    {
+        std::vector<uint64_t> last_end(v->n_hap, 0);
+        for (Rec &r : recs)
+            for (uint32_t w = 0; w < v->wpr; ++w) {
+                uint64_t bits = r.cov[w];
+                while (bits) {
+                    const uint32_t h = w * 64 + (uint32_t)__builtin_ctzll(bits);
+                    bits &= bits - 1;
+                    if (h >= v->n_hap) continue;
+                    if (r.pos < last_end[h]) { r.cov[w] &= ~(1ull << (h & 63)); ++v->dropped_calls; }
+                    else last_end[h] = r.pos + r.del;
+                }
+            }
+    }
     for (const Rec &r : recs) {
         spmb_journal_event e;
         e.ref_pos = r.pos; e.del_len = r.del; e.ins_len = (uint32_t)r.ins.size(); e.ins_off = v->pool.size();
@@ -259,6 +277,7 @@ extern "C" const uint64_t *spmb_vcf_coverage(const spmb_vcf *v, uint32_t *words_
 extern "C" uint32_t spmb_vcf_haplotype_count(const spmb_vcf *v) { return v ? v->n_hap : 0; }
 extern "C" uint32_t spmb_vcf_sample_count(const spmb_vcf *v) { return v ? (uint32_t)v->samples.size() : 0; }
 extern "C" const char *spmb_vcf_sample_name(const spmb_vcf *v, uint32_t i) { return (v && i < v->samples.size()) ? v->samples[i].c_str() : nullptr; }
+extern "C" uint64_t spmb_vcf_dropped_calls(const spmb_vcf *v) { return v ? v->dropped_calls : 0; }
 extern "C" int spmb_vcf_stats(const spmb_vcf *v, uint64_t stats[3])
 {
     if (!v || !stats) return SPMB_ERR_ARG;

@@ -220,6 +220,7 @@ struct JstHost {
 
 struct JstFlatHost {
     uint32_t W = 0;
+    bool overflow = false; // a window longer than 2^32-1 symbols or more than 2^32-1 window-variant ids: not representable
     std::vector<JstWindow> wins;
     std::vector<uint32_t> win_vars;
     uint64_t total_symbols = 0;
@@ -238,6 +239,7 @@ struct JstDfs {
     std::vector<uint32_t> &ids_out;
     std::vector<uint64_t> arena;
     std::vector<uint32_t> ids;
+    bool overflow = false;
 
     void emit()
     {
@@ -251,6 +253,7 @@ struct JstDfs {
             prev_end = x.ref_pos + x.del_len;
         }
         len += std::min<uint64_t>(W - 1, J.n_ref - prev_end);
+        if (len > 0xffffffffull || ids_out.size() + ids.size() > 0xffffffffull) { overflow = true; return; }
         JstWindow wd;
         wd.ref_start = rs;
         wd.len = (uint32_t)len;
@@ -261,45 +264,65 @@ struct JstDfs {
         wins.push_back(wd);
     }
 
-    void dfs(size_t depth, uint64_t next_u, uint64_t last_end)
+    // Depth-first walk with an explicit stack (a chain of densely called variants is as deep as it is long:
+    // no recursion, so no stack limit of the flattening threads applies).  Frame d owns the coverage vector at
+    // arena[d*wpr ..) and ids[0..d]; arena[0 ..) holds the starting coverage of ids[0] on entry.
+    struct Frame { uint64_t u, last_end; bool stop; };
+    std::vector<Frame> stack;
+
+    void walk(uint64_t v1)
     {
         const uint32_t wpr = J.wpr;
         const uint64_t nv = J.var.size();
-        if (arena.size() < (depth + 2) * wpr) arena.resize((depth + 2) * wpr);
-        for (uint64_t u = next_u; u < nv && J.var[u].ref_pos < last_end + W; ++u) {
-            if (J.var[u].ref_pos < last_end) continue; // overlaps the chain: cannot be carried with it
-            const uint64_t *ru = J.row(u);
-            uint64_t *c = arena.data() + depth * wpr;
-            uint64_t *c1 = arena.data() + (depth + 1) * wpr;
-            uint64_t any1 = 0, any0 = 0;
-            for (uint32_t w = 0; w < wpr; ++w) {
-                c1[w] = c[w] & ru[w];
-                any1 |= c1[w];
-                c[w] &= ~ru[w];
-                any0 |= c[w];
+        ids.clear();
+        ids.push_back((uint32_t)v1);
+        stack.clear();
+        stack.push_back({v1 + 1, J.var[v1].ref_pos + J.var[v1].del_len, false});
+        while (!stack.empty()) {
+            if (stack.back().stop) { stack.pop_back(); ids.pop_back(); continue; } // nobody was left without the child's variant
+            const size_t depth = stack.size() - 1;
+            if (arena.size() < (depth + 2) * wpr) arena.resize((depth + 2) * wpr);
+            bool descended = false;
+            while (stack[depth].u < nv && J.var[stack[depth].u].ref_pos < stack[depth].last_end + W) {
+                const uint64_t u = stack[depth].u++;
+                if (J.var[u].ref_pos < stack[depth].last_end) continue; // overlaps the chain: cannot be carried with it
+                const uint64_t *ru = J.row(u);
+                uint64_t *c = arena.data() + depth * wpr;
+                uint64_t *c1 = arena.data() + (depth + 1) * wpr;
+                uint64_t any1 = 0, any0 = 0;
+                for (uint32_t w = 0; w < wpr; ++w) {
+                    c1[w] = c[w] & ru[w];
+                    any1 |= c1[w];
+                    c[w] &= ~ru[w];
+                    any0 |= c[w];
+                }
+                if (!any0) stack[depth].stop = true; // after the child: nobody is left without u
+                if (any1) {
+                    ids.push_back((uint32_t)u);
+                    stack.push_back({u + 1, J.var[u].ref_pos + J.var[u].del_len, false});
+                    descended = true;
+                    break;
+                }
+                if (!any0) break;
             }
-            if (any1) {
-                ids.push_back((uint32_t)u);
-                dfs(depth + 1, u + 1, J.var[u].ref_pos + J.var[u].del_len);
-                ids.pop_back();
-            }
-            if (!any0) return; // nobody left without u
+            if (descended) continue;
+            if (!stack[depth].stop) emit();
+            stack.pop_back();
+            ids.pop_back();
         }
-        emit();
     }
 };
 
-static void jst_flatten_range(const JstHost &J, uint32_t W, uint64_t v_begin, uint64_t v_end,
+static bool jst_flatten_range(const JstHost &J, uint32_t W, uint64_t v_begin, uint64_t v_end,
                               std::vector<JstWindow> &wins, std::vector<uint32_t> &ids_out)
 {
     JstDfs d{J, W, wins, ids_out, {}, {}};
     d.arena.resize(64 * J.wpr);
     for (uint64_t v1 = v_begin; v1 < v_end; ++v1) {
         if (!J.start_cov(v1, W, d.arena.data())) continue;
-        d.ids.clear();
-        d.ids.push_back((uint32_t)v1);
-        d.dfs(0, v1 + 1, J.var[v1].ref_pos + J.var[v1].del_len);
+        d.walk(v1);
     }
+    return !d.overflow;
 }
 
 static void jst_flatten(const JstHost &J, uint32_t W, JstFlatHost &out)
@@ -318,11 +341,12 @@ static void jst_flatten(const JstHost &J, uint32_t W, JstFlatHost &out)
     std::vector<std::vector<JstWindow>> pw(n_chunks);
     std::vector<std::vector<uint32_t>> pi(n_chunks);
     std::atomic<uint64_t> next{0};
+    std::atomic<int> bad{0};
     auto work = [&]() {
         for (;;) {
             const uint64_t c = next.fetch_add(1);
             if (c >= n_chunks) break;
-            jst_flatten_range(J, W, c * chunk, std::min(nv, (c + 1) * chunk), pw[c], pi[c]);
+            if (!jst_flatten_range(J, W, c * chunk, std::min(nv, (c + 1) * chunk), pw[c], pi[c])) bad.store(1);
         }
     };
     std::vector<std::thread> th;
@@ -331,6 +355,8 @@ static void jst_flatten(const JstHost &J, uint32_t W, JstFlatHost &out)
     for (auto &t : th) t.join();
     uint64_t total_w = 0, total_i = 0;
     for (uint64_t c = 0; c < n_chunks; ++c) { total_w += pw[c].size(); total_i += pi[c].size(); }
+    out.overflow = bad.load() != 0 || total_i > 0xffffffffull;
+    if (out.overflow) return;
     out.wins.reserve(total_w);
     out.win_vars.reserve(total_i);
     out.total_symbols = 0;

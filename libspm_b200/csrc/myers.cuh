@@ -80,7 +80,7 @@ __device__ __forceinline__ void myers_step(uint32_t (&vp)[NW], uint32_t (&vn)[NW
 
 __device__ __forceinline__ void myers_emit(const HitSink &sink, uint64_t end, uint32_t seq, uint32_t pid, uint32_t err)
 {
-    unsigned long long idx = atomicAdd(sink.count, 1ull);
+    const unsigned long long idx = spmb_append_slot(sink.count);
     if (idx < sink.cap) {
         spmb_hit h;
         h.end = end; h.seq_id = seq; h.pattern_id = pid; h.errors = err; h.reserved = 0;

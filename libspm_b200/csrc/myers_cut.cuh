@@ -108,6 +108,28 @@ __device__ __forceinline__ void myers_cut_chunk(uint32_t (&vp)[NW], uint32_t (&v
     }
 }
 
+// the A = 1 fast path for 2-bit alphabets: 8 columns on word 0, TWO symbols per table access.  eq2_base is the
+// shared-window address of a 16-row table {Eq0[first], Eq0[second]} indexed by a symbol pair (4 text bits):
+// one SHF + two IMADs + one LDS.64 per two columns instead of that per column.  A half-warp's 16 possible rows
+// cover the 32 banks exactly once, so the access is conflict-free whatever the symbols are.
+template <int NW>
+__device__ __forceinline__ void myers_cut_chunk1_pairs(uint32_t (&vp)[NW], uint32_t (&vn)[NW], uint32_t &w, uint32_t eq2_base,
+                                                       uint32_t mul16, uint32_t mul8)
+{
+    uint32_t d0 = 0, d1 = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const uint32_t c2 = w >> 28;
+        w *= mul16; // IMAD (FMA pipe)
+        const uint2 e = spmb_lds64(c2 * mul8 + eq2_base);
+        uint32_t eq[1];
+        eq[0] = e.x;
+        myers_cut_step<1, NW, false>(vp, vn, eq, d0, d1);
+        eq[0] = e.y;
+        myers_cut_step<1, NW, false>(vp, vn, eq, d0, d1);
+    }
+}
+
 // number of words this row needs for the next 8 columns, given words 0..A-1 are valid now.
 // Lower bounds from popcounts (S = value at the bottom of the previous word, P/N = VP/VN bits of a word):
 //   every row of word w            D >= S_{w-1} - N_w
@@ -155,8 +177,13 @@ __global__ void __launch_bounds__(128) myers_cut_kernel(MyersArgs a)
     constexpr int NWP = (NW <= 4) ? 4 : 8;
     constexpr int NSYM = WIDE ? 16 : 4;
     __shared__ __align__(16) uint32_t s_eq[NSYM * NWP];
+    __shared__ __align__(8) uint32_t s_eq2[32]; // word 0 of Eq for a symbol PAIR: row (first << 2 | second) = {Eq0[first], Eq0[second]}
     const uint32_t pat = blockIdx.y;
     for (uint32_t t = threadIdx.x; t < NSYM * NWP; t += blockDim.x) s_eq[t] = a.eq[(size_t)pat * NSYM * NWP + t];
+    if (!WIDE && threadIdx.x < 32) {
+        const uint32_t pair = threadIdx.x >> 1, sym = (threadIdx.x & 1) ? (pair & 3u) : (pair >> 2);
+        s_eq2[threadIdx.x] = a.eq[(size_t)pat * NSYM * NWP + sym * NWP];
+    }
     __syncthreads();
     const MyersPatMeta pm = a.meta[pat];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -221,6 +248,9 @@ __global__ void __launch_bounds__(128) myers_cut_kernel(MyersArgs a)
     const uint2 *__restrict__ lp = a.lanes;
     uint32_t eq_base; // pinned in a register: ptxas otherwise re-derives the shared window (S2R + LEA) per block
     asm volatile("mov.u32 %0, %1;" : "=r"(eq_base) : "r"((uint32_t)__cvta_generic_to_shared(s_eq)));
+    uint32_t eq2_base;
+    asm volatile("mov.u32 %0, %1;" : "=r"(eq2_base) : "r"((uint32_t)__cvta_generic_to_shared(s_eq2)));
+    const uint32_t mul16 = mul4 * mul4, mul8 = mul4 + mul4; // run-time multipliers: the shifts stay IMADs (MyersArgs)
     int A = __reduce_max_sync(0xffffffffu, myers_cut_next<NW, NW>(vp, vn, k));
     int score = 32 * NW; // meaningful while A == NW
 
@@ -243,8 +273,12 @@ __global__ void __launch_bounds__(128) myers_cut_kernel(MyersArgs a)
 #pragma unroll
             for (int qq = 0; qq < 4; ++qq) {
                 if (qq == 2) { w = cur.y; wh = cur_hi.y; }
-                uint32_t d0 = 0, d1 = 0;
-                myers_cut_chunk<1, NW, false, WIDE>(vp, vn, w, wh, eq_base, mul4, eq_stride, d0, d1);
+                if (WIDE) {
+                    uint32_t d0 = 0, d1 = 0;
+                    myers_cut_chunk<1, NW, false, WIDE>(vp, vn, w, wh, eq_base, mul4, eq_stride, d0, d1);
+                } else {
+                    myers_cut_chunk1_pairs<NW>(vp, vn, w, eq2_base, mul16, mul8);
+                }
                 q = qq + 1;
                 const bool grow = (int)__popc(vp[0] & 0x00ffffffu) - (int)__popc(vn[0]) <= k;
                 if (__any_sync(0xffffffffu, grow)) {

@@ -226,7 +226,7 @@ __device__ __forceinline__ void pg_survivor(const PigeonFilterArgs &a, uint64_t 
         const uint32_t v = (uint32_t)ent.y;
         if (v == PG_EMPTY) return;
         if (ent.x == key) {
-            const unsigned long long idx = atomicAdd(a.cand_count, 1ull);
+            const unsigned long long idx = spmb_append_slot(a.cand_count);
             if (idx < a.cand_cap) {
                 PigeonCand cd;
                 cd.pos = R * RL + col; cd.u = v; cd.pad = 0;
@@ -239,10 +239,13 @@ __device__ __forceinline__ void pg_survivor(const PigeonFilterArgs &a, uint64_t 
 }
 
 // WIDE: kq > 16 (the key has a low word; the bitmap then holds two bits per q-gram, both in one word).
-// One warp = one unit of 32 rows x 32 chunks.  Bitmap survivors (a few per 1024 positions) are not
-// looked up by the lane that found them -- that loop would run as long as the unluckiest lane of the
-// warp -- but parked in a per-warp queue in shared memory and drained 32 at a time, one per lane.
-static const uint32_t PG_QCAP = 256; // queue entries per warp (uint16: chunk-in-unit | lane | symbol)
+// Work item = one chunk-column: 32 rows x 32 symbols of one super-tile.  Every warp of the (persistent, one CTA
+// per SM) grid takes an EQUAL CONTIGUOUS share of the launch's chunk-columns -- round 1 handed out units of 32
+// chunk-columns round-robin, which at 1/8 of the C5 text left 2.4 units per warp: three rounds where 2.4 would do
+// (+25 % kernel time, the bulk of the poor strong scaling).  Bitmap survivors (a few per 1024 positions) are not
+// looked up by the lane that found them -- that loop would run as long as the unluckiest lane of the warp -- but
+// parked in a per-warp queue in shared memory and drained 32 at a time, one per lane.
+static const uint32_t PG_QCAP = 256; // queue entries per warp (uint32: chunk-column in the warp's share | lane | symbol)
 
 // STEP: only positions = 0 (mod STEP) of a row are looked at.  The filtered Myers path then indexes, for
 // every pigeonhole piece of length L, the STEP sub-seeds of length L-STEP+1 at offsets 0..STEP-1 inside it:
@@ -257,93 +260,104 @@ __global__ void __launch_bounds__(1024, 1) pigeon_filter_kernel(PigeonFilterArgs
     __syncthreads();
 
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint16_t *s_q = reinterpret_cast<uint16_t *>(s_bits + n_words) + warp * PG_QCAP;
+    uint32_t *s_q = s_bits + n_words + warp * PG_QCAP;
     const uint32_t RL = a.lay.row_len, rl32 = RL >> 5;
-    const uint32_t segs = (rl32 + 31) >> 5;
-    const uint64_t n_units = (a.st1 - a.st0) * segs;
     const uint32_t shift = 32 - a.pg.B;
     const uint32_t himask = a.pg.himask, lomask = a.pg.lomask;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint2 *__restrict__ lp = a.lanes;
 
-    for (uint64_t unit = (uint64_t)blockIdx.x * 32 + warp; unit < n_units; unit += (uint64_t)gridDim.x * 32) {
-        const uint64_t st = a.st0 + unit / segs;
-        const uint32_t c0 = (uint32_t)(unit % segs) * 32;
-        const uint32_t c1 = min(c0 + 32, rl32);
-        uint32_t qn = 0; // queue fill, warp-uniform
-        auto drain = [&]() {
-            __syncwarp();
-            for (uint32_t b = 0; b < qn; b += 32) {
-                if (b + lane < qn) {
-                    const uint32_t e = s_q[b + lane];
-                    pg_survivor<MODE>(a, st, (e >> 5) & 31u, c0 + (e >> 10), e & 31u);
-                }
+    // this warp's share [t0, t1) of the chunk-columns (st - st0) * rl32 + c
+    const uint64_t T = (a.st1 - a.st0) * rl32;
+    const uint64_t n_warps = (uint64_t)gridDim.x * 32, gw = (uint64_t)blockIdx.x * 32 + warp;
+    const uint64_t t0 = T / n_warps * gw + min(gw, T % n_warps);
+    const uint64_t t1 = t0 + T / n_warps + (gw < T % n_warps ? 1 : 0);
+    if (t0 >= t1) return; // no block-wide synchronisation below
+    (void)himask;
+
+    uint32_t qn = 0; // queue fill, warp-uniform
+    auto drain = [&]() {
+        __syncwarp();
+        for (uint32_t b = 0; b < qn; b += 32) {
+            if (b + lane < qn) {
+                const uint32_t e = s_q[b + lane];
+                const uint64_t t = t0 + (e >> 10);
+                const uint64_t sst = t / rl32;
+                pg_survivor<MODE>(a, a.st0 + sst, (e >> 5) & 31u, (uint32_t)(t - sst * rl32), e & 31u);
             }
-            __syncwarp();
-            qn = 0;
-        };
-        const uint2 *rowp = lp + (st * rl32) * 32 + lane;
-        uint2 cur = __ldg(rowp + (uint64_t)c0 * 32);
-        for (uint32_t c = c0; c < c1; ++c) {
-            uint2 nxt;
-            if (c + 1 < rl32) nxt = __ldg(rowp + (uint64_t)(c + 1) * 32);
-            else if (MODE == SPMB_MODE_PLAIN)
-                nxt = (lane < 31) ? __ldg(lp + (st * rl32) * 32 + lane + 1) : __ldg(lp + ((st + 1) * rl32) * 32);
-            else nxt = make_uint2(0, 0);
-            uint32_t acc = 0;
-#pragma unroll
-            for (int j = 0; j < 32; j += STEP) {
-                uint32_t hi, lo;
-                pg_window(cur, nxt, j, hi, lo);
-                if (WIDE) {
-                    const uint32_t h = pg_h1(hi, lo & lomask);
-                    const uint32_t word = s_bits[h >> (shift + 5)];
-                    const uint32_t t = (word << ((h >> shift) & 31u)) & (word << (h & 31u));
-                    acc = __funnelshift_l(t, acc, 1); // sampled position k = j/STEP ends at bit 32/STEP-1-k
-                } else {
-                    const uint32_t h = (hi & himask) * 0x9E3779B1u;
-                    const uint32_t word = s_bits[h >> (shift + 5)];
-                    acc = __funnelshift_l(word << ((h >> shift) & 31u), acc, 1);
-                }
-            }
-            // ---- park the survivors of this chunk: one warp prefix sum hands every lane its queue slots ----
-            const uint32_t cnt = __popc(acc);
-            uint32_t inc = cnt;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const uint32_t up = __shfl_up_sync(0xffffffffu, inc, d);
-                if ((int)lane >= d) inc += up;
-            }
-            const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
-            if (total) {
-                if (qn + total > PG_QCAP) drain();
-                if (total <= PG_QCAP) {
-                    uint32_t slot = qn + inc - cnt;
-                    while (acc) {
-                        const uint32_t b = __clz(acc); // 32 - 32/STEP + k
-                        acc &= ~(0x80000000u >> b);
-                        s_q[slot++] = (uint16_t)(((c - c0) << 10) | (lane << 5) | ((b - (32 - 32 / STEP)) * STEP));
-                    }
-                    qn += total;
-                } else {
-                    // a chunk denser than the queue (low-complexity text): rounds of one survivor per lane
-                    uint32_t m = __ballot_sync(0xffffffffu, acc != 0);
-                    while (m) {
-                        if (qn + 32 > PG_QCAP) drain();
-                        if (acc) {
-                            const uint32_t b = __clz(acc);
-                            acc &= ~(0x80000000u >> b);
-                            s_q[qn + __popc(m & lt_mask)] = (uint16_t)(((c - c0) << 10) | (lane << 5) | ((b - (32 - 32 / STEP)) * STEP));
-                        }
-                        qn += __popc(m);
-                        m = __ballot_sync(0xffffffffu, acc != 0);
-                    }
-                }
-            }
-            cur = nxt;
         }
-        drain();
+        __syncwarp();
+        qn = 0;
+    };
+    uint64_t st = a.st0 + t0 / rl32;
+    uint32_t c = (uint32_t)(t0 % rl32);
+    const uint2 *rowp = lp + (st * rl32) * 32 + lane;
+    uint2 cur = __ldg(rowp + (uint64_t)c * 32);
+    for (uint64_t t = t0; t < t1; ++t) {
+        uint2 nxt;
+        if (c + 1 < rl32) nxt = __ldg(rowp + (uint64_t)(c + 1) * 32);
+        else if (MODE == SPMB_MODE_PLAIN)
+            nxt = (lane < 31) ? __ldg(lp + (st * rl32) * 32 + lane + 1) : __ldg(lp + ((st + 1) * rl32) * 32);
+        else nxt = make_uint2(0, 0);
+        uint32_t acc = 0;
+#pragma unroll
+        for (int j = 0; j < 32; j += STEP) {
+            uint32_t hi, lo;
+            pg_window(cur, nxt, j, hi, lo);
+            if (WIDE) {
+                const uint32_t h = pg_h1(hi, lo & lomask);
+                const uint32_t word = s_bits[h >> (shift + 5)];
+                const uint32_t tt = (word << ((h >> shift) & 31u)) & (word << (h & 31u));
+                acc = __funnelshift_l(tt, acc, 1); // sampled position k = j/STEP ends at bit 32/STEP-1-k
+            } else {
+                const uint32_t h = (hi & himask) * 0x9E3779B1u;
+                const uint32_t word = s_bits[h >> (shift + 5)];
+                acc = __funnelshift_l(word << ((h >> shift) & 31u), acc, 1);
+            }
+        }
+        // ---- park the survivors of this chunk: one warp prefix sum hands every lane its queue slots ----
+        const uint32_t cnt = __popc(acc);
+        uint32_t inc = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t up = __shfl_up_sync(0xffffffffu, inc, d);
+            if ((int)lane >= d) inc += up;
+        }
+        const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
+        if (total) {
+            const uint32_t tag = ((uint32_t)(t - t0) << 10) | (lane << 5);
+            if (qn + total > PG_QCAP) drain();
+            if (total <= PG_QCAP) {
+                uint32_t slot = qn + inc - cnt;
+                while (acc) {
+                    const uint32_t b = __clz(acc); // 32 - 32/STEP + k
+                    acc &= ~(0x80000000u >> b);
+                    s_q[slot++] = tag | ((b - (32 - 32 / STEP)) * STEP);
+                }
+                qn += total;
+            } else {
+                // a chunk denser than the queue (low-complexity text): rounds of one survivor per lane
+                uint32_t m = __ballot_sync(0xffffffffu, acc != 0);
+                while (m) {
+                    if (qn + 32 > PG_QCAP) drain();
+                    if (acc) {
+                        const uint32_t b = __clz(acc);
+                        acc &= ~(0x80000000u >> b);
+                        s_q[qn + __popc(m & lt_mask)] = tag | ((b - (32 - 32 / STEP)) * STEP);
+                    }
+                    qn += __popc(m);
+                    m = __ballot_sync(0xffffffffu, acc != 0);
+                }
+            }
+        }
+        if (++c == rl32) { // next super-tile: its rows are other sequences' rows, nothing carries over
+            c = 0;
+            ++st;
+            rowp = lp + (st * rl32) * 32 + lane;
+            if (t + 1 < t1) cur = __ldg(rowp);
+        } else cur = nxt;
     }
+    drain();
 }
 
 // ------------------------------------------------------------------------------------------
@@ -368,7 +382,7 @@ struct PigeonVerifyArgs {
 
 __device__ __forceinline__ void pg_emit(const HitSink &sink, uint64_t end, uint32_t seq, uint32_t pid, uint32_t err, uint32_t aux)
 {
-    unsigned long long idx = atomicAdd(sink.count, 1ull);
+    const unsigned long long idx = spmb_append_slot(sink.count);
     if (idx < sink.cap) {
         spmb_hit h;
         h.end = end; h.seq_id = seq; h.pattern_id = pid; h.errors = err; h.reserved = aux;

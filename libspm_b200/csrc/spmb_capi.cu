@@ -128,7 +128,8 @@ struct spmb_pattern {
     uint32_t n_pat = 0, k = 0;
     std::vector<uint32_t> len, off;   // per pattern
     std::vector<uint8_t> ranks;       // host copy, concatenated
-    std::vector<uint32_t> filt;       // exact: packed first min(m,8) symbols
+    std::vector<uint32_t> filt;       // exact: the min(m,8) symbols of the filter window, packed
+    std::vector<uint32_t> filt_off;   // exact: offset of the filter window inside the needle (exact_window_offset)
     uint32_t max_m = 0, min_m = 0;
     int NW = 0;                       // myers: 32-bit words
     uint32_t sym_bits = 2;            // 2 (dna4) or 4 (spmb_pattern_create_wide)
@@ -841,6 +842,41 @@ static cudaError_t pattern_upload_pigeon(spmb_context *ctx, spmb_pattern *p,
     return e;
 }
 
+// The exact kernel rejects alignments on ONE window of 8 needle symbols (exact.cuh).  Which window: the first one
+// costs nothing on random text, but real genomes are full of low-complexity runs (poly-A, dinucleotide repeats,
+// satellites) -- a needle that starts inside one would send every alignment of every such run to the slow
+// warp-cooperative verification.  So the host takes the LEAST REPETITIVE window: most distinct 3-mers, then most
+// distinct 2-mers, then the leftmost (SPMB_EXACT_WINDOW=first restores offset 0 for A/B runs).
+static uint32_t exact_window_offset(const uint8_t *pat, uint32_t m)
+{
+    if (m <= 8) return 0;
+    static const bool first = [] { const char *e = getenv("SPMB_EXACT_WINDOW"); return e && e[0] == 'f'; }();
+    if (first) return 0;
+    uint32_t best = 0;
+    int best_score = -1;
+    const uint32_t last = std::min<uint32_t>(m - 8, 4096);
+    for (uint32_t o = 0; o <= last; ++o) {
+        uint32_t k3[6], k2[7];
+        int d3 = 0, d2 = 0;
+        for (uint32_t j = 0; j + 1 < 8; ++j) {
+            const uint32_t c2 = ((uint32_t)pat[o + j] << 8) | pat[o + j + 1];
+            bool dup = false;
+            for (int t = 0; t < d2; ++t) dup |= k2[t] == c2;
+            if (!dup) k2[d2++] = c2;
+            if (j + 2 < 8) {
+                const uint32_t c3 = (c2 << 8) | pat[o + j + 2];
+                dup = false;
+                for (int t = 0; t < d3; ++t) dup |= k3[t] == c3;
+                if (!dup) k3[d3++] = c3;
+            }
+        }
+        const int score = d3 * 16 + d2;
+        if (score > best_score) { best_score = score; best = o; }
+        if (score == 6 * 16 + 7) break; // all distinct: nothing better to find
+    }
+    return best;
+}
+
 // shortest q for which the seed filter replaces the direct Myers kernel: 4^q must dwarf the number of
 // seeds (a 12-mer has 1.7e7 values)
 static const uint32_t SPMB_FILTER_MIN_Q = 12;
@@ -946,12 +982,14 @@ static int pattern_build(spmb_context *ctx, int alg, const uint8_t *ranks, const
         for (uint32_t i = 0; i < n_pat; ++i) {
             uint32_t fs = 0, fh = 0;
             const uint32_t J = std::min<uint32_t>(p->len[i], 8);
+            const uint32_t fo = exact_window_offset(p->ranks.data() + p->off[i], p->len[i]);
             for (uint32_t j = 0; j < J; ++j) {
-                fs |= (uint32_t)(p->ranks[p->off[i] + j] & 3) << (2 * j);
-                fh |= (uint32_t)(p->ranks[p->off[i] + j] >> 2) << (2 * j);
+                fs |= (uint32_t)(p->ranks[p->off[i] + fo + j] & 3) << (2 * j);
+                fh |= (uint32_t)(p->ranks[p->off[i] + fo + j] >> 2) << (2 * j);
             }
             p->filt.push_back(fs);
             p->filt_hi.push_back(fh);
+            p->filt_off.push_back(fo);
         }
     }
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
@@ -1111,17 +1149,15 @@ static cudaError_t launch_myers(spmb_context *ctx, const spmb_store *s, const sp
     if (a.lanes_hi) {
         // 4-bit alphabets (plain stores only): the cut-off kernel for two words and more, the full one for one
         if (MODE != SPMB_MODE_PLAIN) return cudaErrorInvalidValue;
-        const bool wcut = p->NW >= 2;
-        if (!wcut) a.split = 1;
+#define SPMB_MYERS_WIDE_CASE(nw)                                                                                  \
+    case nw:                                                                                                      \
+        if (cut) myers_cut_kernel<(nw < 2 ? 2 : nw), SPMB_MODE_PLAIN, true><<<grid, 128, 0, ctx->stream>>>(a);      \
+        else myers_kernel<nw, SPMB_MODE_PLAIN, true><<<grid, 128, 0, ctx->stream>>>(a);                           \
+        break;
         switch (p->NW) {
-        case 1: myers_kernel<1, SPMB_MODE_PLAIN, true><<<grid, 128, 0, ctx->stream>>>(a); break;
-        case 2: myers_cut_kernel<2, SPMB_MODE_PLAIN, true><<<grid, 128, 0, ctx->stream>>>(a); break;
-        case 3: myers_cut_kernel<3, SPMB_MODE_PLAIN, true><<<grid, 128, 0, ctx->stream>>>(a); break;
-        case 4: myers_cut_kernel<4, SPMB_MODE_PLAIN, true><<<grid, 128, 0, ctx->stream>>>(a); break;
-        case 5: myers_cut_kernel<5, SPMB_MODE_PLAIN, true><<<grid, 128, 0, ctx->stream>>>(a); break;
-        case 6: myers_cut_kernel<6, SPMB_MODE_PLAIN, true><<<grid, 128, 0, ctx->stream>>>(a); break;
-        case 7: myers_cut_kernel<7, SPMB_MODE_PLAIN, true><<<grid, 128, 0, ctx->stream>>>(a); break;
-        case 8: myers_cut_kernel<8, SPMB_MODE_PLAIN, true><<<grid, 128, 0, ctx->stream>>>(a); break;
+        SPMB_MYERS_WIDE_CASE(1) SPMB_MYERS_WIDE_CASE(2) SPMB_MYERS_WIDE_CASE(3) SPMB_MYERS_WIDE_CASE(4)
+        SPMB_MYERS_WIDE_CASE(5) SPMB_MYERS_WIDE_CASE(6) SPMB_MYERS_WIDE_CASE(7) SPMB_MYERS_WIDE_CASE(8)
+#undef SPMB_MYERS_WIDE_CASE
         default: return cudaErrorInvalidValue;
         }
         ctx->launches++;
@@ -1157,11 +1193,11 @@ static cudaError_t launch_filter_kernel(spmb_context *ctx, const PigeonFilterArg
 {
     static bool attr_set[16] = {false};
     if (ctx->device < 16 && !attr_set[ctx->device]) {
-        cudaError_t e = cudaFuncSetAttribute(pigeon_filter_kernel<MODE, WIDE, STEP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024 + 32 * PG_QCAP * 2);
+        cudaError_t e = cudaFuncSetAttribute(pigeon_filter_kernel<MODE, WIDE, STEP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024 + 32 * PG_QCAP * 4);
         if (e != cudaSuccess) return e;
         attr_set[ctx->device] = true;
     } else if (ctx->device >= 16) {
-        cudaFuncSetAttribute(pigeon_filter_kernel<MODE, WIDE, STEP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024 + 32 * PG_QCAP * 2);
+        cudaFuncSetAttribute(pigeon_filter_kernel<MODE, WIDE, STEP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024 + 32 * PG_QCAP * 4);
     }
     pigeon_filter_kernel<MODE, WIDE, STEP><<<grid, 1024, smem, ctx->stream>>>(fa);
     return cudaGetLastError();
@@ -1208,11 +1244,11 @@ static int enqueue_filtered(spmb_context *ctx, const spmb_store *s, const spmb_p
         fa.st0 = st0 > back ? st0 - back : 0;
     }
     fa.cand = h->d_cand; fa.cand_count = h->d_count + 1; fa.cand_cap = h->cand_cap;
-    const uint32_t segs = (s->lay.row_len / 32 + 31) / 32;
-    const uint64_t units = (fa.st1 - fa.st0) * segs;
-    unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)ctx->sm_count, (units + 31) / 32);
+    // one persistent CTA per SM; every warp takes an equal contiguous share of the chunk-columns (at least ~8 each)
+    const uint64_t chunk_cols = (fa.st1 - fa.st0) * (s->lay.row_len / 32);
+    unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)ctx->sm_count, (chunk_cols + 255) / 256);
     if (grid == 0) grid = 1;
-    const size_t smem = ((size_t)4 << (p->pg.B - 5)) + 32 * PG_QCAP * 2; // bitmap + per-warp survivor queues
+    const size_t smem = ((size_t)4 << (p->pg.B - 5)) + 32 * PG_QCAP * 4; // bitmap + per-warp survivor queues
     cudaError_t e;
     if (p->pg.kq <= 16) e = launch_filter_kernel<MODE, false, 1>(ctx, fa, grid, smem);
     else if (p->filter_step == 4) e = launch_filter_kernel<MODE, true, 4>(ctx, fa, grid, smem);
@@ -1327,6 +1363,7 @@ static int enqueue_search(spmb_context *ctx, const spmb_store *s, const spmb_pat
         a.row_len = s->row_len; a.row_seq = s->row_seq; a.row_own = s->row_own;
         a.m = p->len[i];
         a.J = std::min<uint32_t>(a.m, 8);
+        a.fo = p->filt_off[i];
         a.filt_syms = p->filt[i];
         a.planes_hi = s->hi ? reinterpret_cast<const uint4 *>(s->hi->planes) : nullptr;
         a.filt_syms_hi = s->hi ? p->filt_hi[i] : 0;
@@ -1841,6 +1878,42 @@ extern "C" int spmb_jst_create(spmb_context *ctx, const spmb_store *reference, c
         }
         H.max_del = std::max(H.max_del, x.del_len);
     }
+    {   // every haplotype's carried variants must be a valid journal: the flattening, the coordinate shifts and the
+        // clean-coverage test all count a carried variant, so an overlapping one would shift later hits silently.
+        // Threads split the coverage words (64 haplotypes each); one pass over the matrix.
+        unsigned nt = std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u);
+        const uint32_t n_grp = (H.wpr + 7) / 8; // 8 words = one cache line of a coverage row
+        nt = std::min<unsigned>(nt, n_grp);
+        if (n_var * (uint64_t)H.wpr < (1u << 16)) nt = 1;
+        std::atomic<int> bad{0};
+        auto check = [&](unsigned t) {
+            std::vector<uint64_t> last_end(512);
+            for (uint32_t g = t; g < n_grp && !bad.load(std::memory_order_relaxed); g += nt) {
+                std::fill(last_end.begin(), last_end.end(), 0);
+                const uint32_t w0 = g * 8, w1 = std::min(H.wpr, w0 + 8);
+                for (uint64_t v = 0; v < n_var; ++v) {
+                    const uint64_t p = H.var[v].ref_pos, e = p + H.var[v].del_len;
+                    for (uint32_t w = w0; w < w1; ++w) {
+                        uint64_t bits = H.cov[v * H.wpr + w];
+                        while (bits) {
+                            const int b = (int)(w - w0) * 64 + __builtin_ctzll(bits);
+                            bits &= bits - 1;
+                            if (p < last_end[b]) { bad.store(1); return; }
+                            last_end[b] = e;
+                        }
+                    }
+                }
+            }
+        };
+        std::vector<std::thread> th;
+        for (unsigned t = 1; t < nt; ++t) th.emplace_back(check, t);
+        check(0);
+        for (auto &x : th) x.join();
+        if (bad.load()) {
+            delete j;
+            return set_err(ctx, SPMB_ERR_ARG, "JST: the variants carried by one haplotype overlap (or a replacement precedes an insertion at the same position)");
+        }
+    }
     H.build_ckpt();
     cudaError_t e = cudaMalloc(&j->d_var, (n_var ? n_var : 1) * sizeof(spmb_journal_event));
     if (e == cudaSuccess) e = cudaMalloc(&j->d_pool, pool_len ? pool_len : 1);
@@ -1876,6 +1949,7 @@ static int jst_prepare(spmb_context *ctx, spmb_jst *j, uint32_t W)
     if (j->have_flat && j->flat.W == W) { j->ms[0] = 0; j->ms[1] = 0; return SPMB_OK; }
     jst_drop_flat(j);
     jst_flatten(j->H, W, j->flat);
+    if (j->flat.overflow) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "JST: a branch context exceeds 2^32-1 symbols / the window-variant list 2^32-1 entries");
     j->ms[0] = j->flat.flatten_ms;
     std::vector<JstWindow> &wins = j->flat.wins;
     const uint64_t nw = wins.size();

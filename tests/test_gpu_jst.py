@@ -21,8 +21,7 @@ def ctx():
 def make_jst(n_ref, n_var, n_hap, seed, **kw):
     rng = np.random.default_rng(seed)
     ref = rand_text(rng, n_ref)
-    var, pool, kinds, cov = synth.jst(n_ref, n_var, n_hap, seed, **kw)
-    pool = synth.finish_snps(var, pool, kinds, ref[var["ref_pos"][kinds == 0].astype(np.int64)])
+    var, pool, kinds, cov = synth.jst(ref, n_var, n_hap, seed, **kw)
     return ref, var, pool, cov
 
 
@@ -156,3 +155,43 @@ def test_jst_small_buckets_beside_large_ones(ctx):
     st = jst.last_stats()
     assert st["buckets"] >= 2 and st["windows"] > 2 * 16 * 32 * 148   # at least one bucket past 4 CTAs per SM
     jst.close()
+
+
+@pytest.mark.gpu
+def test_jst_create_rejects_overlapping_variants_of_one_haplotype(ctx):
+    """a haplotype that carries a deletion [100, 110) and an indel at 105 is not a valid journal; the
+    flattening would skip the second variant while the coordinate shifts still count it.  The oracle rejects the
+    input (journal_apply: unsorted / overlapping), so does spmb_jst_create -- per haplotype, so the same two
+    variants on DIFFERENT haplotypes are fine."""
+    rng = np.random.default_rng(11)
+    ref = rand_text(rng, 4000)
+    var = np.zeros(3, dtype=sp.EVENT_DTYPE)
+    var["ref_pos"] = [100, 105, 300]
+    var["del_len"] = [10, 0, 1]
+    var["ins_len"] = [0, 3, 1]
+    var["ins_off"] = [0, 0, 3]
+    pool = np.array([1, 2, 3, 0], dtype=np.uint8)
+    store = sp.Store.from_host(ctx, ref, 64)
+    ok_cov = np.array([[0b01], [0b10], [0b11]], dtype=np.uint64)
+    j = sp.Jst(ctx, store, var, pool, ok_cov, 2)
+    j.close()
+    bad_cov = np.array([[0b01], [0b01], [0b11]], dtype=np.uint64)
+    with pytest.raises(sp.SpmbError) as ei:
+        sp.Jst(ctx, store, var, pool, bad_cov, 2)
+    assert ei.value.code == 1
+    with pytest.raises(ValueError):
+        orc.journal_apply(ref, var[:2].astype(orc.EVENT_DTYPE), pool)
+    # tie order: a replacement before an insertion at the same position is an overlap, the other order is not
+    var2 = np.zeros(2, dtype=sp.EVENT_DTYPE)
+    var2["ref_pos"] = [50, 50]
+    var2["del_len"] = [1, 0]
+    var2["ins_len"] = [1, 2]
+    var2["ins_off"] = [0, 1]
+    both = np.array([[1], [1]], dtype=np.uint64)
+    with pytest.raises(sp.SpmbError):
+        sp.Jst(ctx, store, var2, pool, both, 1)
+    var2["del_len"] = [0, 1]
+    var2["ins_len"] = [2, 1]
+    var2["ins_off"] = [1, 0]
+    sp.Jst(ctx, store, var2, pool, both, 1).close()
+    store.close()

@@ -67,8 +67,7 @@ def test_jst_shards(ctx):
     rng = np.random.default_rng(5)
     n_ref, n_hap = 30_000, 40
     ref = rand_text(rng, n_ref)
-    var, pool, kinds, cov = synth.jst(n_ref, 900, n_hap, 5, p_snp=0.7, p_ins=0.15, af_max=0.6)
-    pool = synth.finish_snps(var, pool, kinds, ref[var["ref_pos"][kinds == 0].astype(np.int64)])
+    var, pool, kinds, cov = synth.jst(ref, 900, n_hap, 5, p_snp=0.7, p_ins=0.15, af_max=0.6)
     store = sp.Store.from_host(ctx, ref, 64)
     jst = sp.Jst(ctx, store, var, pool, cov, n_hap)
     hap = orc.jst_haplotype(ref, var.astype(orc.EVENT_DTYPE), pool, cov, 3)

@@ -56,7 +56,7 @@ def test_vcf_events_and_coverage(tmp_path):
     p.write_text(vcf)
     r = sp.read_vcf(str(p), None, 12)
     assert r["n_haplotypes"] == 6 and r["samples"] == ["s0", "s1", "s2"]
-    assert r["stats"] == {"records": 4, "skipped": 1, "unknown_symbols": 0}
+    assert r["stats"] == {"records": 4, "skipped": 1, "unknown_symbols": 0, "dropped_calls": 0}
     v = r["variants"]
     assert [(int(x["ref_pos"]), int(x["del_len"]), int(x["ins_len"])) for x in v] == [(2, 1, 1), (2, 1, 1), (5, 0, 3), (5, 2, 0)]
     assert to_str(r["pool"]) == "ATGGA"
@@ -102,3 +102,31 @@ def test_fasta_wide_alphabets(tmp_path):
     assert unk15 == 2
     got4, unk4 = sp.read_fasta(str(p))
     assert to_str(got4[0][1]) == "ACGTAACGTA" + "A" * 10 + "T" + "AA" and unk4 == 14
+
+
+def test_vcf_overlapping_calls_first_wins(tmp_path):
+    """one haplotype calls a 5-symbol deletion AND a SNP inside it (and an insertion behind a replacement at the
+    same position): the later call is cleared for that haplotype and counted, so every haplotype's variants form a
+    valid journal -- the input spmb_jst_create demands (it rejects overlapping variants, as the oracle does)."""
+    vcf = "\n".join([
+        "##fileformat=VCFv4.1",
+        "#CHROM\tPOS\tID\tREF\tALT\tQUAL\tFILTER\tINFO\tFORMAT\ts0\ts1",
+        "1\t4\t.\tACGTAC\tA\t.\tPASS\t.\tGT\t1|0\t0|0",     # deletion of 0-based [4, 9) on haplotype 0
+        "1\t7\t.\tT\tG\t.\tPASS\t.\tGT\t1|1\t0|1",          # SNP at 6: inside the deletion for haplotype 0
+        "1\t12\t.\tC\tT\t.\tPASS\t.\tGT\t0|0\t1|0",         # SNP at 11 on haplotype 2 ...
+        "1\t12\t.\tC\tCA\t.\tPASS\t.\tGT\t0|0\t1|0",        # ... and an insertion at 12 on the same haplotype: fine
+    ]) + "\n"
+    p = tmp_path / "o.vcf"
+    p.write_text(vcf)
+    r = sp.read_vcf(str(p), None, 40)
+    v = r["variants"]
+    assert list(v["ref_pos"]) == [4, 6, 11, 12]
+    cov = r["coverage"][:, 0]
+    assert list(cov) == [0b0001, 0b1010, 0b0100, 0b0100]      # haplotype 0 lost the SNP at 6
+    assert r["stats"]["dropped_calls"] == 1
+    # every haplotype's list is now a valid journal for the oracle
+    import oracle as orc
+    ref = np.arange(40, dtype=np.uint8) % 4
+    for h in range(4):
+        hap = orc.jst_haplotype(ref, v.astype(orc.EVENT_DTYPE), r["pool"], r["coverage"], h)
+        assert len(hap) == 40 + sum(int(v["ins_len"][i]) - int(v["del_len"][i]) for i in range(4) if (int(cov[i]) >> h) & 1)

@@ -136,8 +136,7 @@ def test_event_table_through_upload_queue(small_chunks, monkeypatch, threads):
     try:
         n = 2_000_000
         ref = synth.text_host(n, 31)
-        ev, pool, kinds = synth.journal(n, 32)
-        pool = synth.finish_snps(ev, pool, kinds, ref[ev["ref_pos"][kinds == 0].astype(np.int64)])
+        ev, pool, kinds = synth.journal(ref, 32)
         ev = ev.copy()
         # records that do not fit 8 bytes: a 300-symbol deletion, a 260-symbol insertion stored at the END of
         # the pool (offset delta >= 2^16), and a pool offset that runs backwards

@@ -83,8 +83,7 @@ with torch.cuda.stream(stream):
         import time
         n = n_exact
         ref = synth.text_device(n, 2, dev)
-        ev, pool, kinds = synth.journal(n, 2)
-        pool = synth.finish_snps(ev, pool, kinds, ref[torch.from_numpy(ev["ref_pos"][kinds == 0].astype(np.int64)).to(dev)].cpu().numpy())
+        ev, pool, kinds = synth.journal(ref.cpu().numpy(), 2)
         host = torch.empty(n, dtype=torch.uint8, pin_memory=True); host.copy_(ref); del ref
         evp = torch.empty(ev.nbytes, dtype=torch.uint8, pin_memory=True); evp.numpy()[:] = ev.view(np.uint8)
         evh = evp.numpy().view(sp.EVENT_DTYPE)
