@@ -11,9 +11,9 @@ HDRS := $(wildcard $(CSRC)/*.cuh) include/spmb.h
 
 all: $(LIB) $(SYNTH) oracle
 
-$(LIB): $(CSRC)/spmb_capi.cu $(CSRC)/ingest.cpp $(CSRC)/hostpack.cpp $(HDRS)
+$(LIB): $(CSRC)/spmb_capi.cu $(CSRC)/ingest.cpp $(CSRC)/hostpack.cpp $(CSRC)/multi.cpp $(HDRS)
 	@mkdir -p libspm_b200/lib
-	$(NVCC) $(NVFLAGS) -o $@ $(CSRC)/spmb_capi.cu $(CSRC)/ingest.cpp $(CSRC)/hostpack.cpp -lz -lpthread
+	$(NVCC) $(NVFLAGS) -o $@ $(CSRC)/spmb_capi.cu $(CSRC)/ingest.cpp $(CSRC)/hostpack.cpp $(CSRC)/multi.cpp -lz -lpthread
 
 # the synthetic-input generator shared by the oracle side and the GPU harness (harness code, no CUDA)
 $(SYNTH): $(CSRC)/synth.cpp include/spmb_synth.h

@@ -4,12 +4,14 @@
     python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
     python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU algorithms (oracle port)
 
-A "step" is one search pass (kernel launch -> sorted hit list on the host) over one resident
-sequence store.  Headline workload = BASELINE.json configs[1] at steady-state scale ("C2x"):
-Shift-Or exact search, m=64, over a journaled sequence (reference + 1% SNP/indel journal),
-N = 3.2 Gbp per GPU so that the packed text (0.25 B/bp = 800 MB) exceeds the 126 MB L2.
-The same line also carries the Myers k-error measurement (configs[2], "C3": m=100, k=4,
-250 Mbp) with its INT-pipe roofline, and the as-specified small configs C1/C2.
+A "step" is one search pass (kernel launch -> sorted hit list on the host; at N > 1 also the gather of every
+rank's hit list to rank 0) over one resident sequence store.  Headline workload = BASELINE.json configs[1] at
+steady-state scale ("C2x"): Shift-Or exact search, m=64, over a journaled sequence (reference + 1% SNP/indel
+journal), N = 3.2 Gbp per GPU so that the packed text (0.25 B/bp = 800 MB) exceeds the 126 MB L2.
+The same line also carries: the end-to-end legs (host buffers in, hits out: one GPU per rank, ONE host haystack
+over all GPUs through the single-process multi-GPU driver, chunked streaming), Myers k-error (configs[2], "C3"),
+the JST config (configs[3], "C4"), the batched multi-pattern config (configs[4], "C5") and the as-specified
+small configs C1/C2.  All inputs come from the one xoshiro256** generator (libspm_b200/synth.py).
 Prints ONE JSON line on rank 0.
 """
 from __future__ import annotations
@@ -27,12 +29,21 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-ALG_NAMES = {1: "horspool", 2: "shiftor", 3: "myers"}
 BYTES_PER_BP = 0.25                 # 2-bit packed text read once
+M_EXACT = 64
 
 
 def myers_ops_per_bp(m):            # INT32 instructions per (bp x pattern), SURVEY.md 8(d)
     return 10 * ((m + 31) // 32) + 4
+
+
+def headline_config(n):
+    """identical in both arms (--impl ours / reference): the workload, not the run."""
+    return {"workload": f"C2x: Shift-Or exact search m={M_EXACT} over a journaled sequence ({n} bp reference + 1% SNP/indel "
+                        "journal; needle cut from the derived sequence, 100 more copies planted, 25 of them across an edit) "
+                        "per GPU; BASELINE configs[1] generator (xoshiro256**, seed 0x5EED0002 + rank) at steady-state scale",
+            "pattern_len": M_EXACT, "reference_bp_per_gpu": n, "journal_density": 0.01,
+            "l2": f"inputs larger than L2 ({n * BYTES_PER_BP / 1e6:.0f} MB packed text vs 126 MB)"}
 
 
 # ------------------------------------------------------------------------------------------
@@ -44,8 +55,9 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)", {}
 
 
-def ncu_traffic(key):
-    """per-launch DRAM bytes of the dominant kernel from the committed ncu --set full capture."""
+def ncu_capture(key):
+    """figures of the committed ncu --set full captures (profiles/roofline_traffic.json): constants READ FROM
+    THE PROFILE, not measured in this run -- every use is labelled so."""
     p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(p):
         try:
@@ -118,35 +130,70 @@ def dist_env():
     return rank, world, local
 
 
-def build_c2x(sp, synth, torch, ctx, dev, n, seed, m=64):
-    """reference (device RNG) + 1% journal (host RNG) -> base store + journaled store + pattern."""
-    ref = synth.text_device(n, seed, dev)
-    rng = np.random.default_rng(seed ^ 0xABCDEF)
-    pat = rng.integers(0, 4, size=m, dtype=np.uint8)
-    # plant copies of the needle at seeded reference offsets (about half survive the journal)
-    n_plant = 100
-    starts = np.sort(rng.integers(0, n - m, size=n_plant)).astype(np.int64)
-    idx = (torch.from_numpy(starts).to(dev)[:, None] + torch.arange(m, device=dev)[None, :]).reshape(-1)
-    ref[idx] = torch.from_numpy(np.tile(pat, n_plant)).to(dev)
-    ev, pool, kinds = synth.journal(n, seed)
-    snp_pos = torch.from_numpy(ev["ref_pos"][kinds == 0].astype(np.int64)).to(dev)
-    pool = synth.finish_snps(ev, pool, kinds, ref[snp_pos].cpu().numpy())
-    return ref, ev, pool, pat
+class HitGather:
+    """the final gather of the ranks' small hit lists, inside the timed step: after a pass's
+    sorted hit list has reached the host, its first CAP records go pinned -> device -> all_gather -> pinned on a
+    side stream, so the collective of pass i runs beside the search kernels of pass i+1; rank 0 reads the merged
+    list one step later.  No collective touches the search itself."""
+    def __init__(self, torch, dist, dev, world, depth, cap=2048):
+        self.torch, self.dist, self.world, self.depth, self.CAP = torch, dist, world, depth, cap
+        self.stream = torch.cuda.Stream(device=dev)
+        nbytes = 8 + self.CAP * 24
+        self.pin_in = [torch.zeros(nbytes, dtype=torch.uint8, pin_memory=True) for _ in range(depth)]
+        self.dev_in = [torch.zeros(nbytes, dtype=torch.uint8, device=dev) for _ in range(depth)]
+        self.dev_out = [torch.zeros(nbytes * world, dtype=torch.uint8, device=dev) for _ in range(depth)]
+        self.pin_out = [torch.zeros(nbytes * world, dtype=torch.uint8, pin_memory=True) for _ in range(depth)]
+        self.done = [torch.cuda.Event() for _ in range(depth)]
+        self.armed = [False] * depth
+        self.nbytes = nbytes
+        self.gathered = 0
+
+    def submit(self, slot, hits):
+        torch = self.torch
+        n = min(len(hits), self.CAP)
+        buf = self.pin_in[slot].numpy()
+        buf[:8].view(np.uint64)[0] = n
+        if n:
+            buf[8:8 + n * 24] = np.ascontiguousarray(hits[:n]).view(np.uint8)
+        with torch.cuda.stream(self.stream):
+            self.dev_in[slot].copy_(self.pin_in[slot], non_blocking=True)
+            self.dist.all_gather_into_tensor(self.dev_out[slot], self.dev_in[slot])
+            self.pin_out[slot].copy_(self.dev_out[slot], non_blocking=True)
+            self.done[slot].record(self.stream)
+        self.armed[slot] = True
+
+    def collect(self, slot, hit_dtype):
+        """merged list of the pass that used `slot` (every rank waits for its copy; rank 0's is the product)."""
+        if not self.armed[slot]:
+            return None
+        self.done[slot].synchronize()
+        self.armed[slot] = False
+        raw = self.pin_out[slot].numpy()
+        parts = []
+        for r in range(self.world):
+            b = raw[r * self.nbytes:(r + 1) * self.nbytes]
+            n = int(b[:8].view(np.uint64)[0])
+            parts.append(b[8:8 + n * 24].view(hit_dtype))
+        self.gathered += 1
+        return np.concatenate(parts)
 
 
-def time_search(sp, torch, ctx, stream, store, pattern, hits, steps, warmup, flush=None):
+def time_search(sp, torch, ctx, stream, store, pattern, hits, steps, warmup, flush=None, gather=None):
     """returns (total_ms for `steps` launch+finish passes, mean kernel ms, n_hits, launches/step).
     The passes are pipelined the way the launch/finish pair of the C ABI is meant to be used: passes i+1 and
     i+2 are queued (on their own hit lists) before pass i's hits are collected, so the host's share of a pass
     (D2H of the counters + hit list, ordering) runs under the next kernels.  Every pass still delivers its
-    sorted hit list to the host."""
+    sorted hit list to the host; with `gather` (N > 1) every pass's list also travels to rank 0."""
     DEPTH = int(os.environ.get("SPMB_BENCH_DEPTH", "3"))   # passes in flight: two queued behind the one being collected
     hl = (hits,) + tuple(sp.Hits(ctx, 1 << 16) for _ in range(DEPTH - 1))
     for w in range(max(warmup, 2 * DEPTH)):     # every hit list twice: buffers sized, long-list ordering armed
         if flush is not None:
             flush.add_(1)
         sp.search_launch(ctx, store, pattern, hl[w % DEPTH])
-        sp.search_finish(ctx, hl[w % DEPTH])
+        h = sp.search_finish(ctx, hl[w % DEPTH])
+        if gather is not None:
+            gather.submit(w % DEPTH, h)
+            gather.collect(w % DEPTH, sp.HIT_DTYPE)
     ks = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
     ke = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -154,6 +201,7 @@ def time_search(sp, torch, ctx, stream, store, pattern, hits, steps, warmup, flu
     flush_ms = 0.0
     e0.record(stream)
     n_hits = 0
+    merged_hits = None
 
     def launch(i):
         if flush is not None:
@@ -167,7 +215,16 @@ def time_search(sp, torch, ctx, stream, store, pattern, hits, steps, warmup, flu
     for i in range(steps):
         if i + DEPTH - 1 < steps:
             launch(i + DEPTH - 1)
-        n_hits = len(sp.search_finish(ctx, hl[i % DEPTH]))
+        h = sp.search_finish(ctx, hl[i % DEPTH])
+        n_hits = len(h)
+        if gather is not None:
+            got = gather.collect(i % DEPTH, sp.HIT_DTYPE)      # the list of pass i - DEPTH
+            merged_hits = len(got) if got is not None else merged_hits
+            gather.submit(i % DEPTH, h)
+    if gather is not None:
+        for s in range(DEPTH):                                 # the last DEPTH gathers belong to the timed steps
+            got = gather.collect(s, sp.HIT_DTYPE)
+            merged_hits = len(got) if got is not None else merged_hits
     e1.record(stream)
     torch.cuda.synchronize()
     kern = [ks[i].elapsed_time(ke[i]) for i in range(steps)]
@@ -180,7 +237,28 @@ def time_search(sp, torch, ctx, stream, store, pattern, hits, steps, warmup, flu
         f1.record(stream)
         torch.cuda.synchronize()
         flush_ms = f0.elapsed_time(f1)
+    for h in hl[1:]:
+        h.close()
+    time_search.merged_hits = merged_hits
     return max(total - flush_ms, 1e-6), float(np.mean(kern)), n_hits, ctx.last_launch_count
+
+
+def allmax(torch, dev, world, *vals):
+    if world == 1:
+        return vals if len(vals) > 1 else vals[0]
+    import torch.distributed as dist
+    t = torch.tensor(list(vals), device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    out = [float(x) for x in t.tolist()]
+    return out if len(out) > 1 else out[0]
+
+
+def host_barrier(world, group):
+    """ranks that only wait use a gloo (CPU) barrier: an NCCL barrier would park a spinning kernel on their GPUs
+    while rank 0 drives all of them through the single-process multi-GPU driver."""
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier(group=group)
 
 
 def run_ours(args):
@@ -193,31 +271,37 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device -- libspm_b200 has no CPU path to measure")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    gloo = None
+    dist = None
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
+        gloo = dist.new_group(backend="gloo")
     stream = torch.cuda.Stream(device=dev)
     hbm_peak, peak_src, _ = measured_peaks()
     out = {}
+    cpus = len(os.sched_getaffinity(0))
     if world > 1 and "SPMB_HOST_THREADS" not in os.environ:
         # the ranks of one box share its host cores: split the upload's packing threads between them
-        os.environ["SPMB_HOST_THREADS"] = str(max(0, len(os.sched_getaffinity(0)) // world - 1))
+        os.environ["SPMB_HOST_THREADS"] = str(max(0, cpus // world - 1))
+    synth.lib().spms_set_threads(max(1, cpus // world))
     with torch.cuda.stream(stream):
         ctx = sp.Context(local, stream=stream.cuda_stream)
         hits = sp.Hits(ctx, 1 << 16)
         n = args.n
-        m = 64
+        m = M_EXACT
         # ---------------- headline: C2x exact search over a journaled sequence ----------------
         t0 = time.perf_counter()
-        ref, ev, pool, pat = build_c2x(sp, synth, torch, ctx, dev, n, synth.SEEDS["C2"] + rank, m)
         host_ref = torch.empty(n, dtype=torch.uint8, pin_memory=True)
-        host_ref.copy_(ref)
-        torch.cuda.synchronize()
-        base = sp.Store.from_device(ctx, ref.data_ptr(), n)
-        ctx.sync()
-        del ref
-        torch.cuda.empty_cache()
+        cfg = synth.c2(n, seed=synth.SEEDS["C2"] + rank, m=m, ref=host_ref.numpy())
+        ev, pool, pat = cfg["events"], cfg["pool"], cfg["pattern"]
+        gen_s = time.perf_counter() - t0
+        hp = host_ref.data_ptr()
+        base = sp.Store(ctx, _store_from_ptr(sp, ctx, hp, n))
         j0, j1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        js = base.journaled(ev, pool)          # first call sizes the context's scratch
+        js.close()
+        torch.cuda.synchronize()
         j0.record(stream)
         js = base.journaled(ev, pool)
         j1.record(stream)
@@ -227,6 +311,7 @@ def run_ours(args):
         pattern = sp.Pattern(ctx, sp.ALG_SHIFTOR, pat)
         setup_s = time.perf_counter() - t0
 
+        gather = HitGather(torch, dist, dev, world, int(os.environ.get("SPMB_BENCH_DEPTH", "3"))) if world > 1 else None
         if world > 1:
             dist.barrier()
         # clocks are sampled from the warm-up to the end of the e2e legs (the timed region of the
@@ -234,28 +319,32 @@ def run_ours(args):
         clk = ClockSampler(local)
         clk.__enter__()
         total_ms, kern_ms, n_hits, launches = time_search(sp, torch, ctx, stream, js, pattern, hits,
-                                                          args.steps, args.warmup)
-        if world > 1:
-            t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            total_ms = float(t.item())
+                                                          args.steps, args.warmup, gather=gather)
+        total_ms = allmax(torch, dev, world, total_ms)
         value = world * n_der * args.steps / (total_ms * 1e-3) / 1e9
         achieved = n_der * BYTES_PER_BP / (kern_ms * 1e-3) / 1e9
+        cap = ncu_capture("exact_c2x") or {}
         out.update({
             "metric": "searched_gbp_per_s", "value": value, "unit": "Gbp/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32",
             "data": "synthetic",
-            "config": {"workload": "C2x: Shift-Or exact search m=64 over a journaled sequence "
-                                   f"({n} bp reference + 1% SNP/indel journal, {len(ev)} events) per GPU; "
-                                   "BASELINE configs[1] generator at steady-state scale",
-                       "searched_bp_per_step_per_gpu": n_der, "pattern_len": m, "hits": n_hits,
-                       "l2": f"inputs larger than L2 ({n_der * BYTES_PER_BP / 1e6:.0f} MB packed text vs 126 MB)",
+            "config": headline_config(n),
+            "detail": {"searched_bp_per_step_per_gpu": n_der, "hits": n_hits, "planted": cfg["planted"],
+                       "planted_across_an_edit": cfg["straddling"], "journal_events": int(len(ev)),
                        "row_len": js.row_len, "journal_materialise_ms": journal_ms,
-                       "step": "kernel launch + hit count/list D2H + host sort; passes i+1 and i+2 are queued before pass i's hits are "
-                               "collected (spmb_search_launch / spmb_search_finish on two hit lists)"},
+                       "journal_materialise_note": "spmb_store_create_journaled on a resident base, events from pinned host "
+                                                   "memory: event upload + prefix + pack_chunks_kernel<JournalSource>",
+                       "hit_lists_gathered_per_step": bool(gather), "merged_hits_rank0": getattr(time_search, "merged_hits", None),
+                       "step": "kernel launch + hit count/list D2H + host sort; passes i+1 and i+2 are queued before pass i's "
+                               "hits are collected (spmb_search_launch / spmb_search_finish on three hit lists)"
+                               + ("; every pass's hit list is all-gathered to rank 0 inside the timed region" if gather else "")},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": achieved / hbm_peak, "traffic": ncu_traffic("exact_c2x"), "peak_source": peak_src,
+                         "frac": achieved / hbm_peak,
+                         "traffic": cap.get("dram_bytes") if isinstance(cap, dict) else cap,
+                         "traffic_source": "constant read from the committed ncu --set full capture (profiles/roofline_traffic.json), "
+                                           "not measured in this run",
+                         "peak_source": peak_src,
                          "kernel": "exact_kernel<plain>", "kernel_ms": kern_ms,
                          "algorithmic_bytes_per_launch": n_der * BYTES_PER_BP},
             "gpu_launches": launches * args.steps,
@@ -263,7 +352,6 @@ def run_ours(args):
 
         # ---------------- e2e: host buffers -> hits through the C ABI ----------------
         e2e_steps = max(1, min(args.steps, args.e2e_steps))
-        hp = host_ref.data_ptr()
         ev_bytes = ev.nbytes + pool.nbytes
         # the step's host inputs live in pinned memory: reference ranks, journal events, insertion pool
         ev_pin = torch.empty(ev.nbytes, dtype=torch.uint8, pin_memory=True)
@@ -275,9 +363,9 @@ def run_ours(args):
 
         phase = np.zeros(3)                                  # upload+pack | journal | search (each call syncs)
 
-        def e2e_once():
+        def e2e_once(ptr=hp):
             ta = time.perf_counter()
-            b2 = sp.Store(ctx, _store_from_ptr(sp, ctx, hp, n))
+            b2 = sp.Store(ctx, _store_from_ptr(sp, ctx, ptr, n))
             tb = time.perf_counter()
             j2 = b2.journaled(ev, pool)
             tc = time.perf_counter()
@@ -310,10 +398,7 @@ def run_ours(args):
                 + us["event_host_packed_chunks"] * (16 + 8 * epc) + pool.nbytes
         else:
             ev_h2d = ev_bytes
-        if world > 1:
-            t = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            e2e_s = float(t.item())
+        e2e_s = allmax(torch, dev, world, e2e_s)
         out["e2e"] = {"value": world * n_der * e2e_steps / e2e_s / 1e9, "unit": "Gbp/s",
                       "h2d_bytes_per_step": int(text_h2d + ev_h2d + m), "d2h_bytes_per_step": int(8 + nh * 24),
                       "steps": e2e_steps, "ms_per_step": e2e_s / e2e_steps * 1e3,
@@ -323,7 +408,21 @@ def run_ours(args):
                                    "store_create_journaled": phase[1] / e2e_steps * 1e3,
                                    "search": phase[2] / e2e_steps * 1e3},
                       "path": "spmb_store_create(host ranks: raw chunks over the copy engine + chunks 2-bit packed by "
-                              "host threads) + spmb_store_create_journaled + spmb_search"}
+                              "host threads) + spmb_store_create_journaled + spmb_search; inputs in pinned host memory"}
+        # the same step with the haystack in PAGEABLE memory (what a libspm caller's std::vector<spm::dna4> is)
+        if rank == 0 and world == 1 and not args.no_pageable:
+            pageable = np.empty(n, dtype=np.uint8)
+            pageable[:] = host_ref.numpy()
+            e2e_once(pageable.ctypes.data)
+            t0 = time.perf_counter()
+            for _ in range(2):
+                e2e_once(pageable.ctypes.data)
+            torch.cuda.synchronize()
+            dt = (time.perf_counter() - t0) / 2
+            out["e2e_pageable"] = {"value": n_der / dt / 1e9, "unit": "Gbp/s", "ms_per_step": dt * 1e3, "steps": 2,
+                                   "path": "the e2e step with the reference ranks in pageable host memory (numpy array); "
+                                           "events and pool pinned as before"}
+            del pageable
         # resident-store e2e: the store is the persistent object; per step only the needle goes up
         torch.cuda.synchronize()
         t0 = time.perf_counter()
@@ -341,6 +440,7 @@ def run_ours(args):
         out["clocks"]["window"] = "warm-up + timed steps + e2e legs of the headline workload"
 
         # ---------------- CPU baseline + cross-check (rank 0, N=1 only) ----------------
+        want_hits = None
         if rank == 0 and world == 1 and not args.no_cpu:
             import oracle as orc
             s_n = int(min(n_der, args.cpu_sample))
@@ -351,23 +451,43 @@ def run_ours(args):
                 t0 = time.perf_counter()
                 cnt, ce, _ = orc.search_mt(2, sample, pat, 0, threads=threads)
                 best = min(best, time.perf_counter() - t0)
+            s1 = sample[:min(s_n, 200_000_000)]
+            t0 = time.perf_counter()
+            orc.search_mt(2, s1, pat, 0, threads=1, store=False)
+            one = time.perf_counter() - t0
             g = sp.search(ctx, js, pattern, hits)
             ge = g["end"][g["end"] <= s_n]
             out["cpu_baseline"] = {"value": s_n / best / 1e9, "unit": "Gbp/s", "cores": threads, "kind": "port",
                                    "sample": f"first {s_n} bp of the derived sequence, oracle Shift-Or (32-bit blocks), "
                                              f"{threads} threads, best of 3; journal already applied",
-                                   "hits_match_gpu": bool(np.array_equal(ge, ce))}
-            del sample
-        js.close(); base.close(); del host_ref
+                                   "one_thread_gbp_per_s": len(s1) / one / 1e9,
+                                   "one_thread_sample": f"first {len(s1)} bp, 1 thread (the reference is single-threaded)",
+                                   "hits_match_gpu": bool(np.array_equal(ge, ce)), "hits_in_sample": int(len(ce))}
+            del sample, s1
+
+        # ---------------- streaming (f1) and the single-process multi-GPU driver: rank 0 only ----------------
+        plain_host = host_ref.numpy()
+        if rank == 0 and not args.no_stream and hasattr(sp, "stream_leg"):
+            out["stream"] = sp.stream_leg(ctx, plain_host, pat, hits, chunk=args.stream_chunk)
+        js.close(); base.close()
+        if not args.no_multi and hasattr(sp, "Multi"):
+            host_barrier(world, gloo)                        # every rank has released its big stores
+            if rank == 0:
+                out["e2e_multi"] = bench_multi(sp, torch, args, world, plain_host, ev, pool, pat, n_der)
+            host_barrier(world, gloo)
+        del host_ref, plain_host
 
         # ---------------- Myers k-error: C3 (m=100, k=4, 250 Mbp) ----------------
         if not args.no_myers:
             out["myers"] = bench_myers(sp, synth, torch, ctx, dev, stream, hits, args, rank, world, hbm_peak)
+        if not args.no_c4:
+            out["c4"] = bench_c4(sp, synth, torch, ctx, dev, stream, hits, args, rank, world)
         if not args.no_c5:
             out["c5"] = bench_c5(sp, synth, torch, ctx, dev, stream, hits, args, rank, world)
         if rank == 0 and world == 1 and not args.no_small:
             out["small_configs"] = bench_small(sp, synth, torch, ctx, dev, stream, hits, args)
         out["setup_s"] = setup_s
+        out["generate_s"] = gen_s
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -382,19 +502,57 @@ def _store_from_ptr(sp, ctx, ptr, n):
     return h
 
 
+def bench_multi(sp, torch, args, n_dev, host, ev, pool, pat, n_der):
+    """ONE host haystack (+ its journal) -> hits through the single-process multi-GPU driver of the C ABI
+    (spmb_multi_*): the haystack is cut into n_dev contiguous shards with window_size-1 symbols of left context,
+    every shard crosses its own PCIe link, the journal's events are split at the cuts, every device searches its
+    shard, the hit lists come back per device and are merged on the host -- the final gather, no NCCL."""
+    n_dev = max(1, min(n_dev, torch.cuda.device_count()))
+    mg = sp.Multi(list(range(n_dev)))
+    try:
+        pset = mg.pattern(sp.ALG_SHIFTOR, pat)
+        res = None
+
+        def once():
+            base = mg.store(host)
+            js = base.journaled(ev, pool)
+            h = mg.search(js, pset)
+            st = mg.last_stats()
+            js.close(); base.close()
+            return h, st
+
+        once()
+        steps = max(1, min(args.steps, args.e2e_steps))
+        acc = np.zeros(4)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            h, st = once()
+            acc += st
+        dt = (time.perf_counter() - t0) / steps
+        # the plain (unjournaled) call shape too: spmb_multi_search_host
+        mg.search_host(host, pset)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            hp = mg.search_host(host, pset)
+        dt_plain = (time.perf_counter() - t0) / steps
+        res = {"value": n_der / dt / 1e9, "unit": "Gbp/s", "n_devices": n_dev, "ms_per_step": dt * 1e3, "steps": steps,
+               "hits": int(len(h)), "scaling": "strong (one host haystack of %d bp whatever the device count)" % len(host),
+               "phase_ms": {"upload": acc[0] / steps, "journal": acc[1] / steps, "search": acc[2] / steps, "merge": acc[3] / steps},
+               "plain": {"value": len(host) / dt_plain / 1e9, "unit": "Gbp/s", "ms_per_step": dt_plain * 1e3, "hits": int(len(hp)),
+                         "path": "spmb_multi_search_host: host ranks -> shards -> hits, no journal"},
+               "path": "spmb_multi_store_create + spmb_multi_store_create_journaled + spmb_multi_search (one process, "
+                       "one context and upload pipeline per device, host merge of the per-device hit lists inside the step)"}
+        pset.close()
+        return res
+    finally:
+        mg.close()
+
+
 def bench_myers(sp, synth, torch, ctx, dev, stream, hits, args, rank, world, hbm_peak):
     n, m, k = args.n_myers, 100, 4
-    seed = synth.SEEDS["C3"] + rank
-    text = synth.text_device(n, seed, dev)
-    rng = np.random.default_rng(seed)
-    s0 = int(rng.integers(0, n - m))
-    pat = text[s0:s0 + m].cpu().numpy().copy()
-    # 1000 planted copies, each with e in U{0..6} random edits (0..4 hit, 5..6 are decoys)
-    starts = np.sort(rng.integers(0, n - 2 * m, size=1000)).astype(np.int64)
-    for st in starts:
-        mp = synth.mutate(rng, pat, int(rng.integers(0, 7)))
-        text[int(st):int(st) + len(mp)] = torch.from_numpy(mp).to(dev)
-    store = sp.Store.from_device(ctx, text.data_ptr(), n)
+    cfg = synth.c3(n, seed=synth.SEEDS["C3"] + rank, m=m, k=k)
+    pat = cfg["pattern"]
+    store = sp.Store.from_host(ctx, cfg["text"])
     ctx.sync()
     pattern = sp.Pattern(ctx, sp.ALG_MYERS, pat, k)
     flush = torch.zeros(64 << 20, dtype=torch.int32, device=dev)   # 256 MB > L2
@@ -410,50 +568,157 @@ def bench_myers(sp, synth, torch, ctx, dev, stream, hits, args, rank, world, hbm
     full_total_ms, full_kern_ms, full_hits, _ = time_search(sp, torch, ctx, stream, store, pattern, hits, args.steps,
                                                             args.warmup, flush=flush)
     ctx.set_myers_cutoff(True)
-    if world > 1:
-        t = torch.tensor([total_ms, full_total_ms], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total_ms, full_total_ms = float(t[0].item()), float(t[1].item())
+    total_ms, full_total_ms = allmax(torch, dev, world, total_ms, full_total_ms)
     peak = ctx.measure_int_peak()
     ops = myers_ops_per_bp(m)
-    ops_cut = 11            # one active word: 10 for the column update + the symbol pop (state of a warp on random text)
     achieved = n * ops / (full_kern_ms * 1e-3) / 1e9
-    achieved_cut = n * ops_cut / (kern_ms * 1e-3) / 1e9
-    res = {"workload": f"C3: Myers m={m} k={k} over {n} bp per GPU, 1000 planted mutated copies",
+    sm = ctx.device_info()
+    issue_ceiling = 128.0 * sm["sm_count"] * sm["sm_clock_khz"] * 1e3 / 1e9   # Ginstr/s: 4 schedulers x 32 lanes per clock
+    cut_cap = ncu_capture("myers_cut_c3_counters") or {}
+    res = {"workload": f"C3: Myers m={m} k={k} over {n} bp per GPU, 1000 planted copies with 0..6 random edits",
            "value": world * n * args.steps / (total_ms * 1e-3) / 1e9, "unit": "Gbp/s", "ms_per_step": total_ms / args.steps,
-           "kernel_ms": kern_ms, "kernel_gbp_per_s": n / kern_ms / 1e6, "kernel": "myers_cut_kernel<4,plain>",
+           "kernel_ms": kern_ms, "kernel_gbp_per_s": n / kern_ms / 1e6, "kernel": "myers_cut_kernel<4,plain> (Ukkonen cut-off, the default)",
            "hits": n_hits, "row_len": store.row_len, "l2": "256 MB flush write between iterations",
-           "roofline": {"bound": "int_alu", "achieved": achieved_cut, "peak": peak["lop3_gops"], "unit": "Ginstr/s",
-                        "frac": achieved_cut / peak["lop3_gops"], "traffic": ncu_traffic("myers_cut_c3"),
-                        "peak_source": "measured live: spmb_measure_int_peak (LOP3 chains, all SMs)",
-                        "int_peak_iadd3": peak["iadd3_gops"], "algorithmic_int32_instr_per_bp": ops_cut,
-                        "note": "cut-off kernel: a warp updates only the words that can hold a cell <= k; 11 = one word "
-                                "(10) + symbol pop, the state of >= 99.9 % of the 8-column chunks on random DNA at k=4",
-                        "kernel": "myers_cut_kernel<4,plain>"},
+           # THE INT roofline figure: the full recurrence on SURVEY 8(d)'s 10*ceil(m/32)+4 instructions per bp
+           "roofline": {"bound": "int_alu", "achieved": achieved, "peak": peak["lop3_gops"], "unit": "Ginstr/s",
+                        "frac": achieved / peak["lop3_gops"], "traffic": None,
+                        "peak_source": "measured live: spmb_measure_int_peak (LOP3 chains, all SMs) = the ALU pipe, 64 lanes/SM/clk",
+                        "issue_slot_ceiling": issue_ceiling, "int_peak_iadd3": peak["iadd3_gops"],
+                        "algorithmic_int32_instr_per_bp": ops, "kernel": "myers_kernel<4,plain> (full recurrence)",
+                        "kernel_ms": full_kern_ms},
            "full_recurrence": {"value": world * n * args.steps / (full_total_ms * 1e-3) / 1e9, "unit": "Gbp/s",
                                "kernel_ms": full_kern_ms, "kernel_gbp_per_s": n / full_kern_ms / 1e6,
-                               "hits_equal_cutoff": bool(full_hits == n_hits),
-                               "roofline": {"bound": "int_alu", "achieved": achieved, "peak": peak["lop3_gops"],
-                                            "unit": "Ginstr/s", "frac": achieved / peak["lop3_gops"],
-                                            "traffic": ncu_traffic("myers_c3"),
-                                            "algorithmic_int32_instr_per_bp": ops, "kernel": "myers_kernel<4,plain>"}},
-           "speedup_cutoff_vs_full_kernel": full_kern_ms / kern_ms,
+                               "hits_equal_cutoff": bool(full_hits == n_hits)},
+           # the cut-off kernel skips words, so an algorithmic-count fraction would exceed 1: what it executes instead
+           "cutoff_kernel": {"kernel_ms": kern_ms, "speedup_vs_full_kernel": full_kern_ms / kern_ms,
+                             "equivalent_fraction_on_full_count": n * ops / (kern_ms * 1e-3) / 1e9 / peak["lop3_gops"],
+                             "equivalent_fraction_note": "44 instr/bp the kernel did NOT execute, over the ALU peak: > 1 means words skipped, not a roofline fraction",
+                             "ncu": cut_cap,
+                             "ncu_source": "constants of the committed ncu --set full capture of this kernel on this workload "
+                                           "(profiles/roofline_traffic.json), not measured in this run",
+                             "alu_pipe_ceiling_ginstr": peak["lop3_gops"], "issue_slot_ceiling_ginstr": issue_ceiling},
            "clocks": clk.summary()}
+    if isinstance(cut_cap, dict) and cut_cap.get("executed_lane_instr_per_bp"):
+        res["cutoff_kernel"]["executed_ginstr_per_s"] = n * cut_cap["executed_lane_instr_per_bp"] / (kern_ms * 1e-3) / 1e9
+        res["cutoff_kernel"]["issue_slot_fraction"] = res["cutoff_kernel"]["executed_ginstr_per_s"] / issue_ceiling
     if rank == 0 and world == 1 and not args.no_cpu:
         import oracle as orc
-        host = text.cpu().numpy()
+        host = cfg["text"]
         threads = orc.use_all_cores()
         best = 1e30
         for _ in range(2):
             t0 = time.perf_counter()
             cnt, ce, cr = orc.search_mt(3, host, pat, k, threads=threads)
             best = min(best, time.perf_counter() - t0)
+        s1 = host[:min(n, 50_000_000)]
+        t0 = time.perf_counter()
+        orc.search_mt(3, s1, pat, k, threads=1, store=False)
+        one = time.perf_counter() - t0
         g = sp.search(ctx, store, pattern, hits)
         res["cpu_baseline"] = {"value": n / best / 1e9, "unit": "Gbp/s", "cores": threads, "kind": "port",
                                "sample": f"whole {n} bp text, oracle Myers (64-bit blocks, Ukkonen cut-off), {threads} threads",
+                               "one_thread_gbp_per_s": len(s1) / one / 1e9,
+                               "one_thread_sample": f"first {len(s1)} bp, 1 thread",
                                "hits_match_gpu": bool(np.array_equal(g["end"], ce) and np.array_equal(g["errors"], cr))}
     store.close()
-    del text, flush
+    del flush
+    torch.cuda.empty_cache()
+    return res
+
+
+def bench_c4(sp, synth, torch, ctx, dev, stream, hits, args, rank, world):
+    """configs[3]: JST search, 2504 haplotypes over a 50 Mbp reference with 1 M variants, Myers m=150 k=2.
+    Every rank builds the tree (host flattening + window materialisation, both reported) and searches shard
+    rank/N of the reference scan and of every window bucket (spmb_context_set_shard): strong scaling, no
+    collective; the timed step is the warm search (kernels + expansion of the raw hits to haplotypes + sort)."""
+    import hashlib
+    d = synth.c4(args.c4_scale)
+    n_ref, n_hap, m, k = len(d["ref"]), d["n_hap"], len(d["pattern"]), d["k"]
+    store = sp.Store.from_host(ctx, d["ref"])
+    t0 = time.perf_counter()
+    jst = sp.Jst(ctx, store, d["variants"], d["pool"], d["coverage"], n_hap)
+    create_s = time.perf_counter() - t0
+    p = sp.Pattern(ctx, sp.ALG_MYERS, d["pattern"], k)
+    whole = jst.search(p, hits)                 # unsharded, once: flatten + materialise + search
+    st_first = jst.last_stats()
+    ctx.set_shard(rank, world)
+    jst.search(p, hits)
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    steps = args.steps
+    kms, ems = [], []
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        got = jst.search(p, hits)
+        st = jst.last_stats()
+        kms.append(st["kernels_ms"]); ems.append(st["expand_ms"])
+    torch.cuda.synchronize()
+    warm_ms = (time.perf_counter() - t0) * 1e3 / steps
+    warm_ms, kern_ms = allmax(torch, dev, world, warm_ms, float(np.mean(kms)))
+    # the full recurrence on this shard (the kernel SURVEY 8(d)'s 54 instr/bp is stated on)
+    ctx.set_myers_cutoff(False)
+    jst.search(p, hits)
+    full_k = []
+    for _ in range(3):
+        jst.search(p, hits)
+        full_k.append(jst.last_stats()["kernels_ms"])
+    ctx.set_myers_cutoff(True)
+    ctx.set_shard(0, 1)
+    full_kern_ms = allmax(torch, dev, world, float(np.mean(full_k)))
+    streamed = n_ref + st_first["window_symbols"]
+    effective = float(n_ref) * n_hap
+    peak = ctx.measure_int_peak()
+    ops = myers_ops_per_bp(m)
+    res = {"workload": f"C4: JST search, {n_hap} haplotypes over a {n_ref} bp reference with {len(d['variants'])} variants, "
+                       f"Myers m={m} k={k}; window array sharded over {world} GPU(s)",
+           "value": effective / (warm_ms * 1e-3) / 1e9, "unit": "effective Gbp/s (sum of haplotype lengths per warm search)",
+           "ms_per_step": warm_ms, "scaling": "strong", "steps": steps,
+           "kernels_ms": kern_ms, "expand_ms": float(np.mean(ems)),
+           "streamed_bp": int(streamed), "effective_bp": effective,
+           "streamed_gbp_per_s_kernels": streamed / (kern_ms * 1e-3) / 1e9,
+           "one_off": {"jst_create_s": create_s, "flatten_ms": st_first["flatten_ms"], "materialise_ms": st_first["materialise_ms"],
+                       "windows": int(st_first["windows"]), "window_symbols": int(st_first["window_symbols"]),
+                       "buckets": int(st_first["buckets"])},
+           "hits": int(len(whole)), "hits_this_shard": int(len(got)), "raw_device_hits": int(st_first["raw_hits"]),
+           "full_recurrence": {"kernels_ms": full_kern_ms, "int32_instr_per_bp": ops,
+                               "achieved_ginstr_per_s": streamed / world * ops / (full_kern_ms * 1e-3) / 1e9,
+                               "frac_of_alu_peak": streamed / world * ops / (full_kern_ms * 1e-3) / 1e9 / peak["lop3_gops"],
+                               "note": "all launches of the search (reference scan + every window bucket, two streams) "
+                                       "over the streamed symbols of this shard"},
+           "cutoff_kernel_executed_lane_instr_per_bp": (ncu_capture("myers_cut_c3_counters") or {}).get("executed_lane_instr_per_bp")}
+    # parity: the WHOLE hit list against the committed full-size oracle pass (tests/golden/c4_hits.npz)
+    gp = os.path.join(ROOT, "tests", "golden", "c4_hits.npz")
+    if args.c4_scale == 1.0 and os.path.exists(gp):
+        g = np.load(gp)
+        h = hashlib.sha256()
+        for key in ("ref", "variants", "pool", "coverage", "pattern"):
+            h.update(np.ascontiguousarray(d[key]).view(np.uint8).tobytes())
+        same_in = h.hexdigest() == str(g["input_sha256"])
+        res["parity"] = bool(same_in and len(whole) == len(g["hap"]) and np.array_equal(whole["seq_id"], g["hap"]) and
+                             np.array_equal(whole["end"], g["end"]) and np.array_equal(whole["errors"], g["err"].astype(np.uint32)))
+        res["parity_against"] = (f"all {len(g['hap'])} hits of the oracle's pass over all {n_hap} haplotypes "
+                                 f"(tests/golden/c4_hits.npz, {float(g['oracle_seconds']):.0f} s on {int(g['oracle_threads'])} threads); "
+                                 f"inputs identical: {same_in}")
+    if rank == 0 and world == 1 and not args.no_cpu:
+        import oracle as orc
+        sample = np.sort(np.unique(np.append(synth.uniform(d["seed"], synth.STREAM_USER + 9, 32, 0, n_hap).astype(np.uint32),
+                                             np.uint32(d["source_haplotype"]))))
+        threads = orc.use_all_cores()
+        t0 = time.perf_counter()
+        want = orc.jst_search(3, d["ref"], d["variants"].astype(orc.EVENT_DTYPE), d["pool"], d["coverage"], n_hap,
+                              d["pattern"], k, haps=sample, threads=threads)
+        dt = time.perf_counter() - t0
+        sel = whole[np.isin(whole["seq_id"], sample)]
+        res["cpu_baseline"] = {"value": float(len(sample)) * n_ref / dt / 1e9, "unit": "effective Gbp/s", "cores": threads,
+                               "kind": "port", "sample": f"{len(sample)} sampled haplotypes materialised and searched by the "
+                                                         f"oracle (Myers, 64-bit blocks, cut-off), {threads} threads",
+                               "hits_match_gpu": bool(len(sel) == len(want) and np.array_equal(sel["seq_id"], want["hap"]) and
+                                                      np.array_equal(sel["end"], want["end"]) and
+                                                      np.array_equal(sel["errors"], want["err"])),
+                               "hits_in_sample": int(len(want))}
+    jst.close(); p.close(); store.close()
     torch.cuda.empty_cache()
     return res
 
@@ -461,74 +726,90 @@ def bench_myers(sp, synth, torch, ctx, dev, stream, hits, args, rank, world, hbm
 def bench_c5(sp, synth, torch, ctx, dev, stream, hits, args, rank, world):
     """configs[4]: 10k patterns of ~100 bp, k=3, over a 3 Gbp text, in ONE call through the pigeonhole seed
     filter (SPMB_ALG_MYERS_FILTERED); with N ranks the SAME text is sharded (strong scaling), each rank
-    searching shard rank/N, no collective.  Cross-checked against the direct Myers kernel (16 patterns,
-    this rank's shard) and, at N=1, the CPU oracle on a 3 Mbp slice."""
-    n, n_pat, m, k = args.n_c5, 10_000, 100, 3
+    searching shard rank/N, no collective on the search; every pass's hit list is gathered to rank 0.
+    Parity at N=1 as SURVEY.md 8(c) specifies: all patterns x a 3 Mbp slice and 16 patterns x the full text,
+    both against the CPU oracle; at N > 1 per-pattern equality with the direct Myers kernel on this rank's shard."""
+    n, n_pat, m, k = args.n_c5, args.c5_patterns, 100, 3
     seed = synth.SEEDS["C5"]
-    text = synth.text_device(n, seed, dev)
-    rng = np.random.default_rng(seed)
-    offs = np.sort(rng.integers(0, n - 2 * m, size=n_pat))
-    idx = (torch.from_numpy(offs).to(dev)[:, None] + torch.arange(m, device=dev)[None, :]).reshape(-1)
-    cut = text[idx].cpu().numpy().reshape(n_pat, m)
-    pats = []
-    for i in range(n_pat):
-        q = synth.mutate(rng, cut[i], int(rng.integers(0, 6)))
-        if len(q) < 97:
-            q = np.concatenate([q, cut[i][:97 - len(q)]])
-        pats.append(q[:128])
-    store = sp.Store.from_device(ctx, text.data_ptr(), n)
+    text = synth.text_host(n, seed)
+
+    def text_at(offs, mm):
+        return np.stack([text[int(o):int(o) + mm] for o in offs])
+
+    offs, pats = synth.c5_patterns(text_at, n, n_pat, m, seed)
+    store = sp.Store.from_host(ctx, text)
     ctx.sync()
     pset = sp.Pattern(ctx, sp.ALG_MYERS_FILTERED, pats, k)
     ctx.set_shard(rank, world)
     sp.search(ctx, store, pset, hits)          # builds the lane-chunk copy of the store
+    gather = None
     if world > 1:
         import torch.distributed as dist
+        gather = HitGather(torch, dist, dev, world, int(os.environ.get("SPMB_BENCH_DEPTH", "3")), cap=8192)
         dist.barrier()
-    total_ms, kern_ms, n_hits, launches = time_search(sp, torch, ctx, stream, store, pset, hits, args.steps, args.warmup)
+    total_ms, kern_ms, n_hits, launches = time_search(sp, torch, ctx, stream, store, pset, hits, args.steps, args.warmup,
+                                                      gather=gather)
+    total_ms = allmax(torch, dev, world, total_ms)
     if world > 1:
-        t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total_ms = float(t.item())
         c = torch.tensor([n_hits], device=dev, dtype=torch.int64)
         dist.all_reduce(c)
         n_hits = int(c.item())
     got = sp.search(ctx, store, pset, hits)
-    step = n_pat // 16
-    sub = [pats[i] for i in range(0, n_pat, step)][:16]
+    step = max(1, n_pat // 16)
+    ids16 = list(range(0, n_pat, step))[:16]
+    sub = [pats[i] for i in ids16]
     direct = sp.Pattern(ctx, sp.ALG_MYERS, sub, k)
-    d = sp.search(ctx, store, direct, hits)
-    sel = got[np.isin(got["pattern_id"], np.arange(0, n_pat, step)[:16])]
-    same = bool(len(sel) == len(d) and np.array_equal(sel["pattern_id"] // step, d["pattern_id"]) and
-                np.array_equal(sel["end"], d["end"]) and np.array_equal(sel["errors"], d["errors"]))
+    dd = sp.search(ctx, store, direct, hits)
+    sel = got[np.isin(got["pattern_id"], ids16)]
+    same = bool(len(sel) == len(dd) and np.array_equal(sel["pattern_id"] // step, dd["pattern_id"]) and
+                np.array_equal(sel["end"], dd["end"]) and np.array_equal(sel["errors"], dd["errors"]))
     ctx.set_shard(0, 1)
     res = {"workload": f"C5: {n_pat} patterns of ~{m} bp, k={k}, over {n} bp in one call (seed filter + verification); "
                        f"the text is sharded over {world} GPU(s)",
            "value": n * args.steps / (total_ms * 1e-3) / 1e9, "unit": "Gbp/s (x 10k patterns)", "ms_per_step": total_ms / args.steps,
            "kernels_ms": kern_ms, "cell_rate_T_per_s": n * n_pat * args.steps / (total_ms * 1e-3) / 1e12,
            "hits": n_hits, "filter": pset.filter_info, "scaling": "strong",
-           "equals_direct_myers_kernel_16_patterns": same,
+           "hit_lists_gathered_per_step": bool(gather), "merged_hits_rank0": getattr(time_search, "merged_hits", None),
+           "equals_direct_myers_kernel_16_patterns_this_shard": same,
            "text_gbytes_per_s_kernels": n / world * 0.25 / (kern_ms * 1e-3) / 1e9}
     if rank == 0 and world == 1 and not args.no_cpu:
         import oracle as orc
-        sl_n = 3_000_000
-        sl0 = int(offs[n_pat // 2]) // 1024 * 1024
-        sl0 = min(sl0, n - sl_n)
-        host = text[sl0:sl0 + sl_n].cpu().numpy()
+        threads = orc.use_all_cores()
+        # (i) ALL patterns x a 3 Mbp slice
+        sl_n = min(n, 3_000_000)
+        sl0 = min(int(offs[n_pat // 2]) // 1024 * 1024, n - sl_n)
+        host = text[sl0:sl0 + sl_n].copy()
         st2 = sp.Store.from_host(ctx, host)
         g2 = sp.search(ctx, st2, pset, hits)
-        ids = list(range(n_pat // 2 - 150, n_pat // 2 + 150))
-        threads = orc.use_all_cores()
+        order = np.argsort(g2["pattern_id"], kind="stable")
+        g2 = g2[order]
+        lo = np.searchsorted(g2["pattern_id"], np.arange(n_pat), "left")
+        hi = np.searchsorted(g2["pattern_id"], np.arange(n_pat), "right")
         t0 = time.perf_counter()
         bad = 0
-        for i in ids:
+        slice_hits = 0
+        for i in range(n_pat):
             _, we, wr = orc.search_mt(3, host, pats[i], k, threads=threads)
-            s2 = g2[g2["pattern_id"] == i]
+            s2 = g2[lo[i]:hi[i]]
+            slice_hits += len(we)
             bad += int(not (np.array_equal(s2["end"], we) and np.array_equal(s2["errors"], wr)))
         cpu_s = time.perf_counter() - t0
-        res["cpu_baseline"] = {"value": sl_n * len(ids) / cpu_s / 1e12, "unit": "T cells/s", "cores": threads, "kind": "port",
-                               "sample": f"{len(ids)} patterns x a {sl_n} bp slice, oracle Myers, {threads} threads",
-                               "patterns_mismatching_gpu": bad}
         st2.close()
+        # (ii) 16 patterns x the FULL text
+        t0 = time.perf_counter()
+        bad16 = 0
+        for j, i in enumerate(ids16):
+            _, we, wr = orc.search_mt(3, text, pats[i], k, threads=threads)
+            s2 = got[got["pattern_id"] == i]
+            bad16 += int(not (np.array_equal(s2["end"], we) and np.array_equal(s2["errors"], wr)))
+        cpu16_s = time.perf_counter() - t0
+        res["cpu_baseline"] = {"value": (sl_n * n_pat + n * len(ids16)) / (cpu_s + cpu16_s) / 1e12, "unit": "T cells/s",
+                               "cores": threads, "kind": "port",
+                               "sample": f"all {n_pat} patterns x a {sl_n} bp slice ({cpu_s:.1f} s) + {len(ids16)} patterns x the full "
+                                         f"{n} bp text ({cpu16_s:.1f} s), oracle Myers, {threads} threads",
+                               "slice_patterns_mismatching_gpu": bad, "slice_hits": slice_hits,
+                               "full_text_patterns_mismatching_gpu": bad16}
+        res["parity"] = bool(bad == 0 and bad16 == 0 and same)
     store.close()
     del text
     torch.cuda.empty_cache()
@@ -536,46 +817,48 @@ def bench_c5(sp, synth, torch, ctx, dev, stream, hits, args, rank, world):
 
 
 def bench_small(sp, synth, torch, ctx, dev, stream, hits, args):
-    """C1 and C2 exactly as BASELINE.json specifies them (they fit in L2: flushed between iterations)."""
+    """C1 and C2 exactly as SURVEY.md 8(d) specifies them (they fit in L2: flushed between iterations)."""
     import oracle as orc
     res = {}
     flush = torch.zeros(64 << 20, dtype=torch.int32, device=dev)
-    # C1: Horspool m=32 over 1 Mbp
-    n = 1_000_000
-    text = synth.text_host(n, synth.SEEDS["C1"])
-    pat = text[333_333:333_333 + 32].copy()
-    rng = np.random.default_rng(synth.SEEDS["C1"])
-    for st in rng.integers(0, n - 32, size=99):
-        text[int(st):int(st) + 32] = pat
+    # C1: Horspool m=32 over 1 Mbp, 100 occurrences; the period-4 run with 9 overlapping hits of ACGTx8
+    d = synth.c1()
+    text, pat = d["text"], d["pattern"]
+    n = len(text)
     store = sp.Store.from_host(ctx, text)
     p = sp.Pattern(ctx, sp.ALG_HORSPOOL, pat)
     tot, kern, nh, _ = time_search(sp, torch, ctx, stream, store, p, hits, args.steps, args.warmup, flush=flush)
     want = orc.horspool(text, pat)
     got = sp.search(ctx, store, p, hits)
+    p2 = sp.Pattern(ctx, sp.ALG_HORSPOOL, d["pattern_overlap"])
+    got2 = sp.search(ctx, store, p2, hits)
+    want2 = orc.horspool(text, d["pattern_overlap"])
     t0 = time.perf_counter(); orc.horspool(text, pat); cpu_s = time.perf_counter() - t0
-    res["C1"] = {"workload": "Horspool m=32, 1 Mbp", "kernel_us": kern * 1e3, "step_us": tot / args.steps * 1e3,
-                 "gbp_per_s_kernel": n / (kern * 1e-3) / 1e9, "hits": nh, "parity": bool(np.array_equal(got["end"], want)),
+    res["C1"] = {"workload": "Horspool m=32, 1 Mbp, needle + 99 planted copies; ACGTx8 over a planted ACGTx16 run",
+                 "kernel_us": kern * 1e3, "step_us": tot / args.steps * 1e3,
+                 "gbp_per_s_kernel": n / (kern * 1e-3) / 1e9, "hits": nh, "overlapping_hits": int(len(got2)),
+                 "parity": bool(np.array_equal(got["end"], want) and np.array_equal(got2["end"], want2) and len(want) >= 100 and len(want2) >= 9),
                  "cpu_1thread_gbp_per_s": n / cpu_s / 1e9}
-    store.close()
-    # C2: Shift-Or m=64 over 50 Mbp + 1% journal
-    n = 50_000_000
-    ref = synth.text_host(n, synth.SEEDS["C2"])
-    ev, pool, kinds = synth.journal(n, synth.SEEDS["C2"])
-    pool = synth.finish_snps(ev, pool, kinds, ref[ev["ref_pos"][kinds == 0].astype(np.int64)])
+    store.close(); p.close(); p2.close()
+    # C2: Shift-Or m=64 over 50 Mbp + 1% journal, 1 + 100 occurrences, 25 across an edit
+    d = synth.c2()
+    ref, ev, pool, pat = d["ref"], d["events"], d["pool"], d["pattern"]
     base = sp.Store.from_host(ctx, ref)
     js = base.journaled(ev, pool)
     nd = len(js)
-    pat = js.read(nd // 3, 64)
     p = sp.Pattern(ctx, sp.ALG_SHIFTOR, pat)
     tot, kern, nh, _ = time_search(sp, torch, ctx, stream, js, p, hits, args.steps, args.warmup, flush=flush)
     derived = orc.journal_apply(ref, ev.astype(orc.EVENT_DTYPE), pool)
     same_text = bool(np.array_equal(js.read(), derived))
     cnt, ce, _ = orc.search_mt(2, derived, pat, 0)
     got = sp.search(ctx, js, p, hits)
-    res["C2"] = {"workload": "Shift-Or m=64, 50 Mbp + 1% journal", "kernel_us": kern * 1e3,
-                 "step_us": tot / args.steps * 1e3, "gbp_per_s_kernel": nd / (kern * 1e-3) / 1e9, "hits": nh,
+    t0 = time.perf_counter(); orc.search_mt(2, derived, pat, 0, threads=1, store=False); cpu_s = time.perf_counter() - t0
+    res["C2"] = {"workload": "Shift-Or m=64, 50 Mbp + 1% journal; needle from the derived sequence + 100 planted copies",
+                 "kernel_us": kern * 1e3, "step_us": tot / args.steps * 1e3, "gbp_per_s_kernel": nd / (kern * 1e-3) / 1e9,
+                 "hits": nh, "planted": d["planted"], "planted_across_an_edit": d["straddling"],
                  "journal_events": int(len(ev)), "derived_text_matches_oracle": same_text,
-                 "parity": bool(np.array_equal(got["end"], ce))}
+                 "parity": bool(np.array_equal(got["end"], ce) and len(ce) >= 1 + d["planted"]),
+                 "cpu_1thread_gbp_per_s": nd / cpu_s / 1e9}
     js.close(); base.close()
     return res
 
@@ -583,23 +866,19 @@ def bench_small(sp, synth, torch, ctx, dev, stream, hits, args):
 # ------------------------------------------------------------------------------------------
 def run_reference(args):
     """The reference's CPU algorithms for the path (the oracle port: SeqAn2 is not on this machine,
-    SURVEY.md 8(c)), all host threads, bounded sample of the same workload per step."""
+    SURVEY.md 8(c)), all host threads.  Same workload, same generator, same planted needles as the CUDA arm:
+    each step is a bounded sample -- the first `--cpu-sample` bp of the SAME reference stream with the journal
+    events and the planted copies that fall into it."""
     rank, world, _ = dist_env()
     if rank != 0:
         return
     import oracle as orc
     from libspm_b200 import synth
-    m = 64
+    m = M_EXACT
     s_n = int(min(args.n, args.cpu_sample))
-    seed = synth.SEEDS["C2"]
-    ref = synth.text_host(s_n, seed)
-    ev, pool, kinds = synth.journal(s_n, seed)
-    pool = synth.finish_snps(ev, pool, kinds, ref[ev["ref_pos"][kinds == 0].astype(np.int64)])
-    rng = np.random.default_rng(seed ^ 0xABCDEF)
-    pat = rng.integers(0, 4, size=m, dtype=np.uint8)
+    cfg = synth.c2(s_n, seed=synth.SEEDS["C2"], m=m)
+    ref, ev, pool, pat = cfg["ref"], cfg["events"], cfg["pool"], cfg["pattern"]
     threads = orc.use_all_cores()
-    times = []
-    hits = 0
     evo = ev.astype(orc.EVENT_DTYPE)
     times, times_search = [], []
     hits = 0
@@ -615,15 +894,19 @@ def run_reference(args):
     tot = sum(times)
     v = len(derived) * args.steps / tot / 1e9
     v_search = len(derived) * args.steps / sum(times_search) / 1e9
-    sample = (f"{s_n} bp reference + 1% journal (bounded sample of the {args.n} bp workload); each step = host buffers "
-              f"in, hit count out: oracle journal apply + oracle Shift-Or (32-bit blocks), both on {threads} threads")
+    t0 = time.perf_counter()
+    orc.search_mt(2, derived[:min(len(derived), 200_000_000)], pat, 0, threads=1, store=False)
+    one = min(len(derived), 200_000_000) / (time.perf_counter() - t0) / 1e9
+    sample = (f"bounded sample: the first {s_n} bp of the {args.n} bp reference stream with its journal ({len(ev)} events) and "
+              f"planted needles ({cfg['planted']} copies, {cfg['straddling']} across an edit); each step = host buffers in, hit count "
+              f"out: oracle journal apply + oracle Shift-Or (32-bit blocks), both on {threads} threads")
     emit({
         "impl": "reference", "metric": "searched_gbp_per_s", "value": v, "unit": "Gbp/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": tot / args.steps * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-        "config": {"workload": "C2x: Shift-Or exact search m=64 over a journaled sequence (CPU, bounded sample)",
-                   "searched_bp_per_step": int(len(derived)), "pattern_len": m, "hits": int(hits),
-                   "search_only_gbp_per_s": v_search},
+        "config": headline_config(args.n),
+        "detail": {"searched_bp_per_step": int(len(derived)), "hits": int(hits), "search_only_gbp_per_s": v_search,
+                   "one_thread_search_gbp_per_s": one},
         "cpu_baseline": {"value": v, "unit": "Gbp/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "Gbp/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     })
@@ -659,11 +942,18 @@ def main():
     ap.add_argument("--n-myers", type=int, default=250_000_000)
     ap.add_argument("--cpu-sample", type=int, default=1_000_000_000)
     ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--stream-chunk", type=int, default=64 << 20)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-myers", action="store_true")
     ap.add_argument("--no-small", action="store_true")
+    ap.add_argument("--no-c4", action="store_true")
     ap.add_argument("--no-c5", action="store_true")
+    ap.add_argument("--no-multi", action="store_true")
+    ap.add_argument("--no-stream", action="store_true")
+    ap.add_argument("--no-pageable", action="store_true")
     ap.add_argument("--n-c5", type=int, default=3_000_000_000)
+    ap.add_argument("--c5-patterns", type=int, default=10_000)
+    ap.add_argument("--c4-scale", type=float, default=1.0)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

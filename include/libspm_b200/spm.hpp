@@ -28,6 +28,7 @@
 #include <concepts>
 #include <cstddef>
 #include <cstdint>
+#include <cstring>
 #include <memory>
 #include <ranges>
 #include <stdexcept>
@@ -335,6 +336,7 @@ protected:
     std::size_t _needle_size{0};
     std::size_t _errors{0};
     std::uint32_t _bits{2};
+    std::vector<std::uint8_t> _ranks; // the needle's ranks (device_group builds the pattern on every device from them)
 
     template <std::ranges::input_range N>
     void build(N &&needle, std::size_t k) {
@@ -343,6 +345,7 @@ protected:
         detail::rank_buffer<N> buf{std::forward<N>(needle)};
         _needle_size = buf.n;
         _errors = k;
+        _ranks.assign(buf.ptr, buf.ptr + buf.n);
         spmb_pattern *p = nullptr;
         if (_bits == 2)
             detail::check(spmb_pattern_create(d.ctx, ALG, buf.ptr, static_cast<std::uint32_t>(buf.n),
@@ -399,6 +402,10 @@ public:
     }
 
     bool empty() const noexcept { return _needle_size == 0; }
+    static constexpr int algorithm = ALG;
+    const std::vector<std::uint8_t> &needle_ranks() const noexcept { return _ranks; }
+    std::size_t max_error_count() const noexcept { return _errors; }
+    std::uint32_t symbol_bits() const noexcept { return _bits; }
 
     // seqan_pattern_base.hpp:97-99 (+ myers_matcher.hpp:51-53 through _errors)
     std::size_t window_size() const noexcept { return empty() ? 0 : _needle_size + _errors; }
@@ -438,8 +445,20 @@ template <std::ranges::viewable_range N> myers_matcher(N &&, std::size_t) -> mye
 // The state is the carried context (last window_size-1 symbols + offset).  It is a value type
 // (semiregular) like the reference's TPatternState / prefSufMatch copies.
 struct matcher_state {
-    std::vector<std::uint8_t> blob;
+    std::vector<std::uint8_t> blob; // spmb_stream_capture: {u64 offset, u32 tail_len, u32 n_patterns, u32 errors[], u8 tail[]}
     friend bool operator==(const matcher_state &, const matcher_state &) = default;
+    // what the reference's captured state shows a caller: the score at the current column
+    // (capture().errors, myers_matcher_restorable.hpp:57-59); 0 for the exact searchers
+    std::uint32_t errors() const noexcept {
+        std::uint32_t e = 0;
+        if (blob.size() >= 20) std::memcpy(&e, blob.data() + 16, 4);
+        return e;
+    }
+    std::uint64_t offset() const noexcept {
+        std::uint64_t o = 0;
+        if (blob.size() >= 8) std::memcpy(&o, blob.data(), 8);
+        return o;
+    }
 };
 
 template <typename derived_t, int ALG>
@@ -691,6 +710,54 @@ public:
         replay(std::forward<callback_t>(callback));
     }
     std::size_t window_size() const noexcept { return spmb_pattern_window_size(_pattern.get()); }
+};
+
+// ------------------------------------------------------------------------------------------
+// every GPU of the box behind one matcher call (north_star item 4; spmb_multi_*): ONE process, ONE host haystack.
+//   spm::device_group gpus;                       // all visible devices
+//   gpus.search(matcher, haystack, callback);     // == matcher(haystack, callback), hits merged and replayed ascending
+// The haystack is cut into one shard per device (with window_size-1 symbols of left context), every shard crosses
+// its own PCIe link, the per-device hit lists are merged on the host; no NCCL anywhere.
+// ------------------------------------------------------------------------------------------
+class device_group {
+    spmb_multi *_m{nullptr};
+    spmb_hits *_hits{nullptr};
+    void check(int rc, const char *where) const {
+        if (rc == SPMB_OK) return;
+        throw device_error(rc, std::string(where) + ": " + spmb_status_string(rc) + " (" + spmb_multi_last_error(_m) + ")");
+    }
+public:
+    explicit device_group(const std::vector<int> &devices = {}) {
+        detail::check(spmb_multi_create(devices.empty() ? nullptr : devices.data(), static_cast<std::uint32_t>(devices.size()), &_m),
+                      nullptr, "spmb_multi_create");
+        int rc = spmb_hits_create(spmb_multi_context(_m, 0), 0, &_hits);
+        if (rc) { spmb_multi_destroy(_m); detail::check(rc, nullptr, "spmb_hits_create"); }
+    }
+    ~device_group() { spmb_hits_destroy(_hits); spmb_multi_destroy(_m); }
+    device_group(const device_group &) = delete;
+    device_group &operator=(const device_group &) = delete;
+    std::uint32_t size() const noexcept { return spmb_multi_device_count(_m); }
+    spmb_multi *handle() const noexcept { return _m; }
+
+    template <typename matcher_t, std::ranges::viewable_range haystack_t, typename callback_t>
+    void search(const matcher_t &matcher, haystack_t &&haystack, callback_t &&callback) {
+        if (matcher.symbol_bits() != 2) throw device_error(SPMB_ERR_UNSUPPORTED, "device_group: dna4 needles only");
+        detail::rank_buffer<haystack_t> buf{std::forward<haystack_t>(haystack)};
+        const std::vector<std::uint8_t> &nr = matcher.needle_ranks();
+        const std::uint32_t len = static_cast<std::uint32_t>(nr.size());
+        spmb_multi_pattern *p = nullptr;
+        check(spmb_multi_pattern_create(_m, matcher_t::algorithm, nr.data(), &len, 1,
+                                        static_cast<std::uint32_t>(matcher.max_error_count()), &p), "spmb_multi_pattern_create");
+        int rc = spmb_multi_search_host(_m, buf.ptr, buf.n, p, _hits);
+        spmb_multi_pattern_destroy(p);
+        check(rc, "spmb_multi_search_host");
+        const spmb_hit *h = spmb_hits_data(_hits);
+        const std::uint64_t n = spmb_hits_count(_hits);
+        for (std::uint64_t i = 0; i < n; ++i) {
+            const std::size_t e = static_cast<std::size_t>(h[i].end);
+            callback(hit_cursor{e >= nr.size() ? e - nr.size() : 0, e, h[i].errors, h[i].seq_id, h[i].pattern_id});
+        }
+    }
 };
 
 } // namespace spm

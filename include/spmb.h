@@ -95,10 +95,16 @@ int spmb_context_sync(spmb_context *ctx);
 int spmb_context_trim(spmb_context *ctx);
 /* Multi-GPU sharding: every later search on this context covers only shard
  * `shard` of `n_shards` of each store it is given (contiguous ranges of super-tiles; a hit
- * belongs to the shard that holds its begin (exact) / end (Myers) position).  The shards of one
+ * belongs to the shard that holds the first symbol of its filter window (exact: a fixed offset from
+ * its begin) / its end (Myers).  The shards of one
  * store partition its hit list: ranks search disjoint shards with no exchange, the driver
  * concatenates the small hit lists afterwards.  Default (0, 1) = everything. */
 int spmb_context_set_shard(spmb_context *ctx, uint32_t shard, uint32_t n_shards);
+/* host threads that pack chunks of a long host haystack for this context's upload pipeline;
+ * -1 = default (SPMB_HOST_THREADS, else available cpus - 1).  A process that drives several devices gives
+ * every context its share of the cores (the multi-GPU driver below does). */
+int spmb_context_set_upload_threads(spmb_context *ctx, int n_threads);
+int spmb_device_count(void); /* CUDA devices visible to this process (0: none -- nothing here works without one) */
 
 /* SPMB_ALG_MYERS with needles longer than 32 symbols runs the Ukkonen cut-off form of the column update
  * (what SeqAn2's _findMyersLargePatterns does with `lastBlock`; reached from myers_matcher.hpp:47-49 for
@@ -231,18 +237,36 @@ uint32_t spmb_last_launch_count(const spmb_context *ctx);
 /* ---------------- resumable search (capture / restore) ----------------
  * restorable_myers_matcher / restorable_shiftor_matcher
  * (myers_matcher_restorable.hpp:57-63,72-82; shiftor_matcher_restorable.hpp:44-63):
- * feed the haystack in chunks; the concatenated hit list equals the unchunked one.
- * The state is the carried context (the last window_size-1 symbols + stream offset), which
- * determines every later hit exactly. */
+ * feed the haystack in chunks of any size; the concatenated hit list equals the unchunked one.
+ * The carried state is the last window_size-1 symbols of the stream (Myers: the last 2m, which also determine the
+ * score at the current column) -- it determines every later hit exactly -- and it lives ON THE
+ * DEVICE as packed words: a feed uploads only its new chunk (long chunks through both movers of the upload
+ * queue), splices it behind the carried symbols, searches, and leaves the new tail on the device.
+ * Pattern sets are allowed (hits carry pattern_id); dna4 only.
+ * feed   = submit + collect: the hits of this chunk, ends relative to the chunk start like the reference's fresh
+ *          Finder on each chunk (myers_matcher_restorable_test.cpp:66-69).
+ * submit / collect: the asynchronous pair for streaming at full rate -- submit returns as soon as the host buffer
+ *          has been consumed (search kernels still running), collect hands back the hits of the OLDEST chunk in
+ *          flight; at most two chunks may be in flight, so chunk i+1 uploads while chunk i is searched.
+ * SPMB_ALG_MYERS_PREFIX streams (restorable_myers_prefix_matcher) are anchored at the START OF THE STREAM: the scan is
+ * clamped to the first m + k + 1 symbols of the whole stream, whereas the reference clamps every call on its own
+ * haystack (myers_prefix_matcher_restorable.hpp:53-54); a caller that restores a state and feeds a fresh context
+ * should create a fresh stream instead.  Their state is that short prefix, kept on the host; feed only. */
 int spmb_stream_create(spmb_context *ctx, const spmb_pattern *p, spmb_stream **out);
 int spmb_stream_destroy(spmb_stream *st);
-/* hits of this chunk; end positions are relative to the chunk start like the reference's
- * fresh Finder on each chunk (myers_matcher_restorable_test.cpp:66-69) */
 int spmb_stream_feed(spmb_context *ctx, spmb_stream *st, const uint8_t *host_ranks, uint64_t n,
                      spmb_hits *h);
-/* capture(): copies the state into buf (size query when buf==NULL); restore(): sets it. */
+int spmb_stream_submit(spmb_context *ctx, spmb_stream *st, const uint8_t *host_ranks, uint64_t n);
+int spmb_stream_collect(spmb_context *ctx, spmb_stream *st, spmb_hits *h);
+/* capture(): copies the state into buf (size query when buf==NULL); restore(): sets it.
+ * blob = {u64 offset, u32 tail_len, u32 n_patterns, u32 errors[n_patterns], u8 tail[tail_len]}: `errors` is what
+ * the reference's captured state shows a caller (capture().errors, myers_matcher_restorable.hpp:57-59) -- the
+ * score of each needle at the current column, computed on the device from the carried symbols when the state is
+ * captured (0 for the exact searchers).  No chunk may be in flight. */
 int spmb_stream_capture(const spmb_stream *st, void *buf, size_t *size);
 int spmb_stream_restore(spmb_stream *st, const void *buf, size_t size);
+int spmb_stream_errors(spmb_stream *st, uint32_t pattern_index, uint32_t *errors);
+uint64_t spmb_stream_offset(const spmb_stream *st); /* symbols consumed so far */
 
 /* ---------------- journaled string tree (north_star items 1-2; a14) ----------------
  * What an external JST traverser does with the reference's matchers (it sizes branch contexts
@@ -267,6 +291,49 @@ int spmb_jst_search(spmb_context *ctx, spmb_jst *j, const spmb_pattern *p, spmb_
  * [3] raw device hits before expansion; ms[0] host flattening (0 when cached), [1] window
  * materialisation, [2] search kernels (reference + windows), [3] host expansion + sort */
 int spmb_jst_last_stats(const spmb_jst *j, uint64_t stats[4], double ms[4]);
+
+/* ---------------- multi-GPU driver (north_star item 4) ----------------
+ * What a single-process libspm caller (seqan_pattern_base::operator(), seqan_pattern_base.hpp:40-52: one host
+ * haystack, one callback sequence) needs to use every GPU of the box: one context, stream and upload pipeline per
+ * device inside ONE process; a host haystack is cut into contiguous shards, one per device, each with `overlap`
+ * symbols of left context (a hit belongs to the shard that holds its END; the window_size-1 symbols before it --
+ * the seam rule of myers_matcher.hpp:51-53 -- are in the context), every shard crosses its own PCIe link; the
+ * search runs on all devices at once and the per-device hit lists are copied back and merged on the host into one
+ * list sorted like spmb_search's.  No NCCL, no collective: the only exchange is this final gather of the hit lists.
+ * devices = NULL: devices 0..n_devices-1; n_devices = 0: every visible device.  overlap = 0: 4096 symbols.
+ * Searching with window_size - 1 > overlap is SPMB_ERR_UNSUPPORTED.  `merged` is a hit list of device 0
+ * (spmb_hits_create(spmb_multi_context(m, 0), ...)). */
+typedef struct spmb_multi spmb_multi;
+typedef struct spmb_multi_store spmb_multi_store;
+typedef struct spmb_multi_pattern spmb_multi_pattern;
+int spmb_multi_create(const int *devices, uint32_t n_devices, spmb_multi **out);
+int spmb_multi_destroy(spmb_multi *m);
+uint32_t spmb_multi_device_count(const spmb_multi *m);
+spmb_context *spmb_multi_context(spmb_multi *m, uint32_t i);
+const char *spmb_multi_last_error(const spmb_multi *m);
+int spmb_multi_store_create(spmb_multi *m, const uint8_t *host_ranks, uint64_t n, uint32_t overlap,
+                            spmb_multi_store **out);
+/* journaled sequence over a sharded base: `events` (sorted, non-overlapping, coordinates of the whole base) is split
+ * at the shard cuts -- every device reads its slice of the caller's array -- and every device materialises its part
+ * of the derived sequence; hits come back in the coordinates of the whole derived sequence.  An event that deletes
+ * more than `overlap` symbols across a cut is SPMB_ERR_UNSUPPORTED. */
+int spmb_multi_store_create_journaled(spmb_multi *m, const spmb_multi_store *base, const spmb_journal_event *events,
+                                      uint64_t n_events, const uint8_t *ins_pool, uint64_t pool_len,
+                                      spmb_multi_store **out);
+int spmb_multi_store_destroy(spmb_multi_store *s);
+uint64_t spmb_multi_store_length(const spmb_multi_store *s);
+uint32_t spmb_multi_store_shards(const spmb_multi_store *s);
+/* the needle (set) on every device: spmb_pattern_set_create's arguments */
+int spmb_multi_pattern_create(spmb_multi *m, int alg, const uint8_t *ranks, const uint32_t *lengths,
+                              uint32_t n_patterns, uint32_t k, spmb_multi_pattern **out);
+int spmb_multi_pattern_destroy(spmb_multi_pattern *p);
+int spmb_multi_search(spmb_multi *m, const spmb_multi_store *s, const spmb_multi_pattern *p, spmb_hits *merged);
+/* the reference's call shape over all devices: host haystack in, merged hits out */
+int spmb_multi_search_host(spmb_multi *m, const uint8_t *host_ranks, uint64_t n, const spmb_multi_pattern *p,
+                           spmb_hits *merged);
+/* wall-clock of the last calls in ms: [0] store_create (all uploads), [1] store_create_journaled, [2] search
+ * (first launch -> last device's hit list on the host), [3] host merge */
+int spmb_multi_last_stats(const spmb_multi *m, double ms[4]);
 
 /* ---------------- ingest: FASTA / VCF -> store inputs ----------------
  * Host-side readers for the formats of the reference's own test data (test/data/datasources.cmake:72-102:

@@ -13,7 +13,7 @@ import os
 
 import numpy as np
 
-__all__ = ["Context", "Store", "Pattern", "Hits", "Stream", "Jst", "SpmbError", "HIT_DTYPE", "EVENT_DTYPE",
+__all__ = ["Context", "Store", "Pattern", "Hits", "Stream", "Jst", "Multi", "SpmbError", "HIT_DTYPE", "EVENT_DTYPE",
            "ALG_HORSPOOL", "ALG_SHIFTOR", "ALG_MYERS", "ALG_PIGEONHOLE", "ALG_MYERS_FILTERED",
            "ALG_MYERS_PREFIX", "Pigeonhole", "search_anchored", "read_fasta", "read_vcf", "lib", "lib_path"]
 
@@ -48,6 +48,12 @@ EXPORTS = [
     "spmb_store_create_wide", "spmb_store_create_wide_from_device", "spmb_store_symbol_bits",
     "spmb_pattern_create_wide", "spmb_pattern_symbol_bits", "spmb_search_host_wide", "spmb_fasta_read_alphabet",
     "spmb_host_pack_events", "spmb_vcf_dropped_calls",
+    "spmb_context_set_upload_threads", "spmb_device_count",
+    "spmb_stream_submit", "spmb_stream_collect", "spmb_stream_errors", "spmb_stream_offset",
+    "spmb_multi_create", "spmb_multi_destroy", "spmb_multi_device_count", "spmb_multi_context", "spmb_multi_last_error",
+    "spmb_multi_store_create", "spmb_multi_store_create_journaled", "spmb_multi_store_destroy", "spmb_multi_store_length",
+    "spmb_multi_store_shards", "spmb_multi_pattern_create", "spmb_multi_pattern_destroy", "spmb_multi_search",
+    "spmb_multi_search_host", "spmb_multi_last_stats",
 ]
 
 
@@ -122,6 +128,27 @@ def lib():
             "spmb_vcf_sample_name": (C.c_char_p, [vp, u32]),
             "spmb_vcf_stats": (i32, [vp, C.POINTER(u64 * 3)]),
             "spmb_vcf_dropped_calls": (u64, [vp]),
+            "spmb_context_set_upload_threads": (i32, [vp, i32]),
+            "spmb_device_count": (i32, []),
+            "spmb_stream_submit": (i32, [vp, vp, vp, u64]),
+            "spmb_stream_collect": (i32, [vp, vp, vp]),
+            "spmb_stream_errors": (i32, [vp, u32, C.POINTER(u32)]),
+            "spmb_stream_offset": (u64, [vp]),
+            "spmb_multi_create": (i32, [vp, u32, pp]),
+            "spmb_multi_destroy": (i32, [vp]),
+            "spmb_multi_device_count": (u32, [vp]),
+            "spmb_multi_context": (vp, [vp, u32]),
+            "spmb_multi_last_error": (C.c_char_p, [vp]),
+            "spmb_multi_store_create": (i32, [vp, vp, u64, u32, pp]),
+            "spmb_multi_store_create_journaled": (i32, [vp, vp, vp, u64, vp, u64, pp]),
+            "spmb_multi_store_destroy": (i32, [vp]),
+            "spmb_multi_store_length": (u64, [vp]),
+            "spmb_multi_store_shards": (u32, [vp]),
+            "spmb_multi_pattern_create": (i32, [vp, i32, vp, vp, u32, u32, pp]),
+            "spmb_multi_pattern_destroy": (i32, [vp]),
+            "spmb_multi_search": (i32, [vp, vp, vp, vp]),
+            "spmb_multi_search_host": (i32, [vp, vp, u64, vp, vp]),
+            "spmb_multi_last_stats": (i32, [vp, C.POINTER(C.c_double * 4)]),
             "spmb_pigeonhole_create": (i32, [vp, vp, vp, u32, C.c_double, pp]),
             "spmb_pattern_filter_info": (i32, [vp, C.POINTER(u32 * 5)]),
             "spmb_search_anchored": (i32, [vp, vp, vp, vp, u64, vp]),
@@ -214,6 +241,10 @@ class Context:
     def set_myers_cutoff(self, enabled: bool):
         """Ukkonen cut-off for multi-word Myers needles (default on); off = the full recurrence."""
         self._check(lib().spmb_context_set_myers_cutoff(self._h, 1 if enabled else 0), "spmb_context_set_myers_cutoff")
+
+    def set_upload_threads(self, n: int):
+        """host threads that pack chunks for this context's upload pipeline (-1 = default)."""
+        self._check(lib().spmb_context_set_upload_threads(self._h, n), "spmb_context_set_upload_threads")
 
     def set_shard(self, shard: int, n_shards: int):
         """later searches cover only this shard (contiguous super-tile range) of every store."""
@@ -497,6 +528,27 @@ class Stream:
                                                self._hits._h), "spmb_stream_feed")
         return self._hits.array()
 
+    def submit(self, chunk=None, ptr: int | None = None, n: int | None = None):
+        """asynchronous feed: returns when the host buffer is consumed; the hits come from collect()."""
+        if ptr is None:
+            r = _ranks(chunk)
+            ptr, n = (r.ctypes.data if r.size else None), r.size
+        self.ctx._check(lib().spmb_stream_submit(self.ctx._h, self._h, C.c_void_p(ptr) if ptr else None, n), "spmb_stream_submit")
+
+    def collect(self) -> np.ndarray:
+        self.ctx._check(lib().spmb_stream_collect(self.ctx._h, self._h, self._hits._h), "spmb_stream_collect")
+        return self._hits.array()
+
+    def errors(self, pattern_index: int = 0) -> int:
+        """the score of a needle at the current column (capture().errors of restorable_myers_matcher)."""
+        e = C.c_uint32()
+        self.ctx._check(lib().spmb_stream_errors(self._h, pattern_index, C.byref(e)), "spmb_stream_errors")
+        return int(e.value)
+
+    @property
+    def offset(self) -> int:
+        return int(lib().spmb_stream_offset(self._h))
+
     def capture(self) -> bytes:
         sz = C.c_size_t(0)
         lib().spmb_stream_capture(self._h, None, C.byref(sz))
@@ -618,3 +670,186 @@ def read_vcf(path: str, contig: str | None = None, ref_len: int = 0):
                           "dropped_calls": int(L.spmb_vcf_dropped_calls(h))}}
     finally:
         lib().spmb_vcf_destroy(h)
+
+
+def stream_leg(ctx: Context, host: np.ndarray, pat, hits: Hits, chunk: int = 64 << 20, k: int = 0, alg: int = ALG_SHIFTOR):
+    """bench.py's streaming leg: a host haystack fed in `chunk`-symbol pieces through spmb_stream_submit /
+    spmb_stream_collect (two chunks in flight), beside the one-shot spmb_search_host of the same haystack."""
+    import time
+    n = host.size
+    base = host.ctypes.data
+    p = Pattern(ctx, alg, pat, k)
+    st = Stream(ctx, p)
+    total_hits = 0
+
+    def run():
+        nonlocal total_hits
+        total_hits = 0
+        inflight = 0
+        for o in range(0, n, chunk):
+            ln = min(chunk, n - o)
+            if inflight == 2:
+                total_hits += len(st.collect())
+                inflight -= 1
+            st.submit(ptr=base + o, n=ln)
+            inflight += 1
+        while inflight:
+            total_hits += len(st.collect())
+            inflight -= 1
+
+    run()                                   # warm: buffers sized
+    st.close()
+    st = Stream(ctx, p)
+    ctx.sync()
+    t0 = time.perf_counter()
+    run()
+    ctx.sync()
+    dt = time.perf_counter() - t0
+    st.close()
+    one = search_host(ctx, None, p, hits, ptr=base, n=n)
+    ctx.sync()
+    t0 = time.perf_counter()
+    one = search_host(ctx, None, p, hits, ptr=base, n=n)
+    ctx.sync()
+    dt1 = time.perf_counter() - t0
+    # a sync feed() of the same chunks (what a caller of the reference's restorable matchers does)
+    st = Stream(ctx, p)
+    t0 = time.perf_counter()
+    fh = 0
+    for o in range(0, n, chunk):
+        ln = min(chunk, n - o)
+        ctx._check(lib().spmb_stream_feed(ctx._h, st._h, C.c_void_p(base + o), ln, st._hits._h), "spmb_stream_feed")
+        fh += len(st._hits)
+    dt2 = time.perf_counter() - t0
+    st.close()
+    p.close()
+    return {"value": n / dt / 1e9, "unit": "Gbp/s", "chunk_symbols": chunk, "chunks": (n + chunk - 1) // chunk,
+            "ms_total": dt * 1e3, "hits": int(total_hits), "one_shot_gbp_per_s": n / dt1 / 1e9, "one_shot_ms": dt1 * 1e3,
+            "one_shot_hits": int(len(one)), "ratio_to_one_shot": dt1 / dt, "hits_equal_one_shot": bool(total_hits == len(one) == fh),
+            "sync_feed_gbp_per_s": n / dt2 / 1e9,
+            "path": "spmb_stream_submit / spmb_stream_collect, two chunks in flight: device-resident tail, only the new chunk "
+                    "crosses PCIe (both movers of the upload queue); one-shot = spmb_search_host of the same plain haystack"}
+
+
+class _MultiStore:
+    def __init__(self, multi, handle):
+        self.multi, self._h = multi, handle
+
+    def journaled(self, events, pool):
+        ev = np.ascontiguousarray(events, dtype=EVENT_DTYPE)
+        pl = _ranks(pool)
+        h = C.c_void_p()
+        self.multi._check(lib().spmb_multi_store_create_journaled(self.multi._h, self._h, ev.ctypes.data if ev.size else None,
+                                                                  ev.size, pl.ctypes.data if pl.size else None, pl.size,
+                                                                  C.byref(h)), "spmb_multi_store_create_journaled")
+        s = _MultiStore(self.multi, h)
+        s._keep = (ev, pl)
+        return s
+
+    def __len__(self):
+        return int(lib().spmb_multi_store_length(self._h))
+
+    @property
+    def shards(self):
+        return int(lib().spmb_multi_store_shards(self._h))
+
+    def close(self):
+        if self._h:
+            lib().spmb_multi_store_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class _MultiPattern:
+    def __init__(self, multi, handle):
+        self.multi, self._h = multi, handle
+
+    def close(self):
+        if self._h:
+            lib().spmb_multi_pattern_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Multi:
+    """the single-process multi-GPU driver (spmb_multi_*): one context per device, host haystacks sharded with
+    left context, per-device hit lists merged on the host."""
+
+    def __init__(self, devices=None):
+        self._h = C.c_void_p()
+        if devices is None:
+            rc = lib().spmb_multi_create(None, 0, C.byref(self._h))
+        else:
+            arr = (C.c_int * len(devices))(*devices)
+            rc = lib().spmb_multi_create(arr, len(devices), C.byref(self._h))
+        if rc:
+            raise SpmbError(rc, "spmb_multi_create")
+        self.n_devices = int(lib().spmb_multi_device_count(self._h))
+        ctx0 = Context.__new__(Context)
+        ctx0._h = C.c_void_p(lib().spmb_multi_context(self._h, 0))
+        ctx0.device = 0
+        ctx0.close = lambda: None          # owned by the driver
+        self._ctx0 = ctx0
+        self._hits = Hits(ctx0, 1 << 12)
+
+    def _check(self, rc, where):
+        if rc:
+            raise SpmbError(rc, where, (lib().spmb_multi_last_error(self._h) or b"").decode())
+
+    def store(self, host, overlap: int = 0, ptr: int | None = None, n: int | None = None):
+        if ptr is None:
+            r = _ranks(host)
+            ptr, n = r.ctypes.data, r.size
+        h = C.c_void_p()
+        self._check(lib().spmb_multi_store_create(self._h, C.c_void_p(ptr), n, overlap, C.byref(h)), "spmb_multi_store_create")
+        return _MultiStore(self, h)
+
+    def pattern(self, alg: int, needle, k: int = 0):
+        if isinstance(needle, (list, tuple)) and len(needle) and not np.isscalar(needle[0]):
+            parts = [_ranks(p) for p in needle]
+        else:
+            parts = [_ranks(needle)]
+        lens = np.array([p.size for p in parts], dtype=np.uint32)
+        cat = np.concatenate(parts) if parts else np.zeros(0, np.uint8)
+        h = C.c_void_p()
+        self._check(lib().spmb_multi_pattern_create(self._h, alg, cat.ctypes.data if cat.size else None, lens.ctypes.data,
+                                                    len(parts), k, C.byref(h)), "spmb_multi_pattern_create")
+        return _MultiPattern(self, h)
+
+    def search(self, store, pattern) -> np.ndarray:
+        self._check(lib().spmb_multi_search(self._h, store._h, pattern._h, self._hits._h), "spmb_multi_search")
+        return self._hits.array()
+
+    def search_host(self, host, pattern, ptr: int | None = None, n: int | None = None) -> np.ndarray:
+        if ptr is None:
+            r = _ranks(host)
+            ptr, n = r.ctypes.data, r.size
+        self._check(lib().spmb_multi_search_host(self._h, C.c_void_p(ptr), n, pattern._h, self._hits._h), "spmb_multi_search_host")
+        return self._hits.array()
+
+    def last_stats(self):
+        ms = (C.c_double * 4)()
+        lib().spmb_multi_last_stats(self._h, C.byref(ms))
+        return np.array(list(ms))
+
+    def close(self):
+        if self._h:
+            self._hits.close()
+            lib().spmb_multi_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

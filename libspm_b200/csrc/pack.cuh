@@ -228,6 +228,16 @@ __global__ void journal_delta_kernel(const spmb_journal_event *__restrict__ ev, 
     if (!ok) atomicExch(bad, 1);
 }
 
+// events given in the coordinates of a longer sequence of which the base store holds [bias, ...): make them local
+__global__ void journal_bias_kernel(spmb_journal_event *__restrict__ ev, uint64_t n_ev, uint64_t bias, int *__restrict__ bad)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_ev) return;
+    const uint64_t p = ev[i].ref_pos;
+    if (p < bias) atomicExch(bad, 1);
+    ev[i].ref_pos = p - bias;
+}
+
 // shift[i] (exclusive prefix of the deltas) -> derived position of event i, in place
 __global__ void journal_der_kernel(const spmb_journal_event *__restrict__ ev, uint64_t n_ev, long long *shift_der,
                                    const long long *__restrict__ delta, long long *__restrict__ total)

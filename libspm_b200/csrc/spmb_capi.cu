@@ -26,6 +26,7 @@
 #include "pack.cuh"
 #include "pigeon.cuh"
 #include "upload.cuh"
+#include "stream.cuh"
 
 // ------------------------------------------------------------------------------------------
 // objects
@@ -50,6 +51,7 @@ struct spmb_context {
     uint32_t children = 0;
     bool closed = false;
     UploadPool *upload = nullptr;          // host-haystack upload pipeline (upload.cuh), created on first use
+    int upload_threads = -1;               // spmb_context_set_upload_threads (-1: SPMB_HOST_THREADS / available cpus - 1)
     // grow-only device scratch for the journal's temporaries (event table, prefix arrays): the stream-ordered
     // pool took 5-15 ms to hand out ~1.6 GB in seven pieces on every call; released by spmb_context_trim
     uint8_t *scratch = nullptr;
@@ -182,7 +184,26 @@ struct spmb_stream {
     CtxRef ctx;
     const spmb_pattern *pat = nullptr;
     uint64_t offset = 0;            // symbols consumed so far
-    std::vector<uint8_t> tail;      // last window_size-1 symbols
+    uint32_t keep = 0;              // symbols carried from feed to feed (window_size-1; Myers: at least 2m for `errors`)
+    uint32_t tail_len = 0;          // symbols in d_tail right now
+    uint2 *d_tail = nullptr;        // the carried symbols as lane-chunk words, on the device
+    uint32_t *d_err = nullptr;      // stream_score_kernel's output
+    std::vector<uint8_t> host_tail; // the same symbols for capture() (copied from the caller's chunks, never searched)
+    // two chunks may be in flight (spmb_stream_submit): the upload of one runs beside the search of the other
+    struct Slot {
+        uint2 *d_words = nullptr;   // [tail | chunk] as lane-chunk words
+        size_t words_bytes = 0;
+        uint8_t *d_raw = nullptr;   // landing area of short chunks (1 B per symbol)
+        size_t raw_bytes = 0;
+        spmb_store *store = nullptr;
+        spmb_hits *hits = nullptr;
+        uint64_t t = 0, n = 0, total = 0;
+        uint32_t launches = 0;
+        bool busy = false, empty = false;
+    } slot[2];
+    int next_submit = 0, next_collect = 0;
+    // anchored (prefix) streams: the state is the short prefix itself, on the host
+    std::vector<uint8_t> tail;
     std::vector<uint8_t> scratch;
 };
 
@@ -299,6 +320,26 @@ extern "C" int spmb_context_set_myers_cutoff(spmb_context *ctx, int enabled)
     if (!ctx) return SPMB_ERR_ARG;
     ctx->myers_cutoff = enabled != 0;
     return SPMB_OK;
+}
+
+extern "C" int spmb_context_set_upload_threads(spmb_context *ctx, int n_threads)
+{
+    if (!ctx || n_threads < -1) return SPMB_ERR_ARG;
+    if (ctx->upload && ctx->upload->n_workers != n_threads) { // the pool is re-created with the new thread count on the next upload
+        ENTER(ctx);
+        CU(cudaStreamSynchronize(ctx->stream));
+        delete ctx->upload;
+        ctx->upload = nullptr;
+    }
+    ctx->upload_threads = n_threads;
+    return SPMB_OK;
+}
+
+extern "C" int spmb_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
 }
 
 extern "C" int spmb_context_set_shard(spmb_context *ctx, uint32_t shard, uint32_t n_shards)
@@ -525,7 +566,7 @@ static int ensure_upload(spmb_context *ctx)
     if (ctx->upload) return SPMB_OK;
     UploadPool *up = new (std::nothrow) UploadPool();
     if (!up) return SPMB_ERR_OOM;
-    cudaError_t e = up->init(ctx->device);
+    cudaError_t e = up->init(ctx->device, ctx->upload_threads);
     if (e != cudaSuccess) { delete up; cudaGetLastError(); return set_err(ctx, SPMB_ERR_CUDA, "upload pool", e); }
     ctx->upload = up;
     return SPMB_OK;
@@ -594,7 +635,7 @@ extern "C" int spmb_upload_last_stats(const spmb_context *ctx, uint64_t stats[8]
     if (ctx->upload) {
         stats[0] = ctx->upload->last_raw;
         stats[1] = ctx->upload->last_packed;
-        stats[2] = ctx->upload->chunk_sym;
+        stats[2] = ctx->upload->job_chunk;
         stats[3] = (uint64_t)ctx->upload->n_workers;
         stats[4] = ctx->upload->last_ev_raw;
         stats[5] = ctx->upload->last_ev_packed;
@@ -605,10 +646,12 @@ extern "C" int spmb_upload_last_stats(const spmb_context *ctx, uint64_t stats[8]
 
 static int store_ensure_lanes(spmb_context *ctx, const spmb_store *s);
 
-extern "C" int spmb_store_create_journaled(spmb_context *ctx, const spmb_store *base,
-                                           const spmb_journal_event *ev, uint64_t n_ev,
-                                           const uint8_t *pool, uint64_t pool_len, uint32_t row_len,
-                                           spmb_store **out)
+// ref_bias: the events' ref_pos are coordinates of a longer sequence of which `base` holds [ref_bias, ...) (the
+// shards of the multi-GPU driver pass slices of ONE caller-owned event table); probe: *probe_der = derived position
+// of event `probe_index` (where its inserted segment begins), or the derived length when probe_index == n_ev
+int spmb_store_create_journaled_ex(spmb_context *ctx, const spmb_store *base, const spmb_journal_event *ev, uint64_t n_ev,
+                                   const uint8_t *pool, uint64_t pool_len, uint32_t row_len, uint64_t ref_bias,
+                                   uint64_t probe_index, uint64_t *probe_der, spmb_store **out)
 {
     if (!ctx || !base || !out || (n_ev && !ev) || (pool_len && !pool)) return SPMB_ERR_ARG;
     if (base->lay.mode != SPMB_MODE_PLAIN) return set_err(ctx, SPMB_ERR_ARG, "journal base must be a plain store");
@@ -668,6 +711,7 @@ extern "C" int spmb_store_create_journaled(spmb_context *ctx, const spmb_store *
     const auto tj2 = tnow();
     if (e == cudaSuccess && n_ev) {
         unsigned blocks = (unsigned)((n_ev + 255) / 256);
+        if (ref_bias) { journal_bias_kernel<<<blocks, 256, 0, sm>>>(d_ev, n_ev, ref_bias, d_bad); ctx->launches++; }
         journal_delta_kernel<<<blocks, 256, 0, sm>>>(d_ev, n_ev, base->lay.n, pool_len, d_delta, d_bad);
         size_t tmp_bytes = d_tmp_bytes;
         JCU(cub::DeviceScan::ExclusiveSum(d_tmp, tmp_bytes, d_delta, d_shift, (int64_t)n_ev, sm));
@@ -678,6 +722,7 @@ extern "C" int spmb_store_create_journaled(spmb_context *ctx, const spmb_store *
     // derived length (and the validation verdict) must reach the host before the store is sized
     JCU(cudaMemcpyAsync(&ctx->h_count[1], d_total, 8, cudaMemcpyDeviceToHost, sm));
     JCU(cudaMemcpyAsync(&ctx->h_count[2], d_bad, 4, cudaMemcpyDeviceToHost, sm));
+    if (probe_der && probe_index < n_ev) JCU(cudaMemcpyAsync(&ctx->h_count[5], d_der + probe_index, 8, cudaMemcpyDeviceToHost, sm));
     JCU(cudaStreamSynchronize(sm));
     if (e != cudaSuccess) { cleanup(); cudaGetLastError(); return set_err(ctx, SPMB_ERR_CUDA, "journal upload/prefix", e); }
     if ((int)(ctx->h_count[2] & 0xffffffffu) != 0) {
@@ -687,6 +732,7 @@ extern "C" int spmb_store_create_journaled(spmb_context *ctx, const spmb_store *
     const auto tj3 = tnow();
     const long long total_shift = (long long)ctx->h_count[1];
     const uint64_t n_der = (uint64_t)((long long)base->lay.n + total_shift);
+    if (probe_der) *probe_der = probe_index < n_ev ? (uint64_t)ctx->h_count[5] : n_der;
     rc = store_alloc(ctx, n_der, row_len, SPMB_MODE_PLAIN, &s);
     if (rc) { cleanup(); return rc; }
     const uint64_t n_blk = (n_der >> 10) + 2;
@@ -721,6 +767,14 @@ extern "C" int spmb_store_create_journaled(spmb_context *ctx, const spmb_store *
     }
     *out = s;
     return SPMB_OK;
+}
+
+extern "C" int spmb_store_create_journaled(spmb_context *ctx, const spmb_store *base,
+                                           const spmb_journal_event *ev, uint64_t n_ev,
+                                           const uint8_t *pool, uint64_t pool_len, uint32_t row_len,
+                                           spmb_store **out)
+{
+    return spmb_store_create_journaled_ex(ctx, base, ev, n_ev, pool, pool_len, row_len, 0, 0, nullptr, out);
 }
 
 extern "C" int spmb_store_destroy(spmb_store *s)
@@ -1110,6 +1164,18 @@ extern "C" int spmb_hits_destroy(spmb_hits *h)
     if (h->pinned) cudaFreeHost(h->pinned);
     if (h->done) cudaEventDestroy(h->done);
     delete h;
+    return SPMB_OK;
+}
+
+// the multi-GPU driver hands its merged list over through a hit object of device 0
+int spmb_hits_set_host(spmb_hits *h, std::vector<spmb_hit> &&list)
+{
+    if (!h) return SPMB_ERR_ARG;
+    h->host = std::move(list);
+    h->count = h->host.size();
+    h->view = nullptr;
+    h->pend_store = nullptr;
+    h->pend_pat = nullptr;
     return SPMB_OK;
 }
 
@@ -2162,83 +2228,293 @@ extern "C" int spmb_jst_search(spmb_context *ctx, spmb_jst *j, const spmb_patter
 }
 
 // ------------------------------------------------------------------------------------------
-// resumable search: the carried state is the last window_size-1 symbols
+// resumable search: the carried state is the last `keep` symbols of the stream, resident on the device
 // ------------------------------------------------------------------------------------------
+static uint32_t stream_keep(const spmb_pattern *p)
+{
+    const uint32_t ws = spmb_pattern_window_size(p);
+    uint32_t keep = ws ? ws - 1 : 0;
+    // Myers: 2m symbols determine the score at the current column (capture().errors, stream.cuh)
+    if (p->alg == SPMB_ALG_MYERS || p->alg == SPMB_ALG_MYERS_FILTERED) keep = std::max(keep, 2 * p->max_m);
+    return keep;
+}
+
 extern "C" int spmb_stream_create(spmb_context *ctx, const spmb_pattern *p, spmb_stream **out)
 {
     if (!ctx || !p || !out) return SPMB_ERR_ARG;
-    if (p->n_pat != 1) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "streams take a single pattern");
     if (p->sym_bits != 2) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "streams are dna4 (2-bit) only");
+    if (p->alg == SPMB_ALG_MYERS_PREFIX && p->n_pat != 1) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "an anchored stream takes a single pattern");
+    ENTER(ctx);
     spmb_stream *st = new (std::nothrow) spmb_stream();
     if (!st) return SPMB_ERR_OOM;
     st->ctx = ctx; st->pat = p;
+    st->keep = stream_keep(p);
+    cudaError_t e = cudaMalloc(&st->d_tail, ((size_t)st->keep / 32 + 2) * sizeof(uint2));
+    if (e == cudaSuccess) e = cudaMemset(st->d_tail, 0, ((size_t)st->keep / 32 + 2) * sizeof(uint2));
+    if (e == cudaSuccess) e = cudaMalloc(&st->d_err, (p->n_pat ? p->n_pat : 1) * sizeof(uint32_t));
+    for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
+        int rc = spmb_hits_create(ctx, 1 << 12, &st->slot[i].hits);
+        if (rc) { spmb_stream_destroy(st); return rc; }
+    }
+    if (e != cudaSuccess) { spmb_stream_destroy(st); return set_err(ctx, SPMB_ERR_OOM, "stream state", e); }
     *out = st;
     return SPMB_OK;
 }
 
-extern "C" int spmb_stream_destroy(spmb_stream *st) { delete st; return SPMB_OK; }
-
-extern "C" int spmb_stream_feed(spmb_context *ctx, spmb_stream *st, const uint8_t *host_ranks, uint64_t n, spmb_hits *h)
+static void stream_slot_release(spmb_stream *st, int i)
 {
-    if (!ctx || !st || !h || (!host_ranks && n)) return SPMB_ERR_ARG;
-    const uint32_t ws = spmb_pattern_window_size(st->pat);
-    if (st->pat->alg == SPMB_ALG_MYERS_PREFIX) {
-        // anchored at the stream start: the state is the prefix consumed so far, and nothing beyond
-        // m + k + 1 symbols is ever scanned (myers_prefix_matcher_restorable.hpp:47-50)
-        const size_t clamp = ws ? (size_t)ws + 1 : 0;
-        const size_t tl = st->tail.size();
-        h->host.clear();
-        h->count = 0;
-        if (st->offset >= clamp || n == 0) { st->offset += n; return SPMB_OK; }
-        const size_t take = std::min<size_t>(n, clamp - tl);
-        st->scratch.resize(tl + take);
-        if (tl) memcpy(st->scratch.data(), st->tail.data(), tl);
-        memcpy(st->scratch.data() + tl, host_ranks, take);
-        int rc = spmb_search_host(ctx, st->scratch.data(), st->scratch.size(), st->pat, h);
-        if (rc) return rc;
-        size_t w = 0;
-        for (size_t i = 0; i < h->host.size(); ++i)
-            if (h->host[i].end > tl) { spmb_hit x = h->host[i]; x.end -= tl; h->host[w++] = x; }
-        h->host.resize(w);
-        h->count = w;
-        st->tail = st->scratch;
-        st->offset += n;
-        return SPMB_OK;
+    spmb_stream::Slot &S = st->slot[i];
+    if (S.store) { spmb_store_destroy(S.store); S.store = nullptr; }
+    S.busy = false;
+}
+
+extern "C" int spmb_stream_destroy(spmb_stream *st)
+{
+    if (!st) return SPMB_OK;
+    if (st->ctx) { cudaSetDevice(st->ctx->device); cudaStreamSynchronize(st->ctx->stream); }
+    for (int i = 0; i < 2; ++i) {
+        stream_slot_release(st, i);
+        if (st->slot[i].d_words && st->ctx) big_free(st->ctx, st->slot[i].d_words, st->slot[i].words_bytes);
+        cudaFree(st->slot[i].d_raw);
+        spmb_hits_destroy(st->slot[i].hits);
     }
-    const size_t keep = ws ? ws - 1 : 0;
+    cudaFree(st->d_tail);
+    cudaFree(st->d_err);
+    delete st;
+    return SPMB_OK;
+}
+
+// the anchored matcher scans at most m + k + 1 symbols from the stream start (myers_prefix_matcher_restorable.hpp:47-50):
+// the whole state is that short prefix, kept on the host
+static int stream_feed_prefix(spmb_context *ctx, spmb_stream *st, const uint8_t *host_ranks, uint64_t n, spmb_hits *h)
+{
+    const uint32_t ws = spmb_pattern_window_size(st->pat);
+    const size_t clamp = ws ? (size_t)ws + 1 : 0;
     const size_t tl = st->tail.size();
-    st->scratch.resize(tl + n);
+    h->host.clear();
+    h->count = 0;
+    h->view = nullptr;
+    if (st->offset >= clamp || n == 0) { st->offset += n; return SPMB_OK; }
+    const size_t take = std::min<size_t>(n, clamp - tl);
+    st->scratch.resize(tl + take);
     if (tl) memcpy(st->scratch.data(), st->tail.data(), tl);
-    if (n) memcpy(st->scratch.data() + tl, host_ranks, n);
+    memcpy(st->scratch.data() + tl, host_ranks, take);
     int rc = spmb_search_host(ctx, st->scratch.data(), st->scratch.size(), st->pat, h);
     if (rc) return rc;
-    // hits ending inside the carried context were reported by an earlier feed
     size_t w = 0;
-    for (size_t i = 0; i < h->host.size(); ++i) {
-        if (h->host[i].end > tl) {
-            spmb_hit x = h->host[i];
-            x.end -= tl;
-            h->host[w++] = x;
-        }
-    }
+    for (size_t i = 0; i < h->host.size(); ++i)
+        if (h->host[i].end > tl) { spmb_hit x = h->host[i]; x.end -= tl; h->host[w++] = x; }
     h->host.resize(w);
     h->count = w;
-    const size_t total = st->scratch.size();
-    const size_t nk = std::min(keep, total);
-    st->tail.assign(st->scratch.begin() + (total - nk), st->scratch.end());
+    st->tail = st->scratch;
     st->offset += n;
     return SPMB_OK;
 }
 
-extern "C" int spmb_stream_capture(const spmb_stream *st, void *buf, size_t *size)
+// enqueue one chunk: [device tail | chunk] -> lane-chunk words -> store -> search kernels -> new tail.  Returns when
+// the host buffer has been consumed; the hits are fetched by spmb_stream_collect.
+extern "C" int spmb_stream_submit(spmb_context *ctx, spmb_stream *st, const uint8_t *host_ranks, uint64_t n)
 {
-    if (!st || !size) return SPMB_ERR_ARG;
-    const size_t need = 16 + st->tail.size();
+    if (!ctx || !st || (!host_ranks && n)) return SPMB_ERR_ARG;
+    if (st->pat->alg == SPMB_ALG_MYERS_PREFIX) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "anchored streams are fed with spmb_stream_feed");
+    ENTER(ctx);
+    const int si = st->next_submit;
+    spmb_stream::Slot &S = st->slot[si];
+    if (S.busy) return set_err(ctx, SPMB_ERR_ARG, "two chunks are in flight: collect one first");
+    cudaStream_t sm = ctx->stream;
+    const uint64_t t = st->tail_len, total = t + n;
+    S.t = t; S.n = n; S.total = total; S.launches = 0;
+    st->next_submit ^= 1;
+    S.busy = true;
+    S.empty = (total == 0 || st->pat->max_m == 0);
+    // host mirror of the tail (serialised by capture(); the searches never read it)
+    {
+        std::vector<uint8_t> &ht = st->host_tail;
+        const size_t nk = (size_t)std::min<uint64_t>(st->keep, total);
+        if (n >= nk) ht.assign(host_ranks + (n - nk), host_ranks + n);
+        else {
+            const size_t from_old = nk - (size_t)n;
+            ht.erase(ht.begin(), ht.end() - from_old);
+            ht.insert(ht.end(), host_ranks, host_ranks + n);
+        }
+        for (auto &c : ht) c &= 3;
+    }
+    if (total == 0) { st->offset += n; return SPMB_OK; }
+    const uint32_t launches0 = ctx->launches;
+    // ---- [tail | chunk] as lane-chunk words ----
+    const size_t words = (size_t)((total + 31) / 32) + 2;
+    if (words * sizeof(uint2) > S.words_bytes) {
+        if (S.d_words) big_free(ctx, S.d_words, S.words_bytes);
+        S.d_words = nullptr; S.words_bytes = 0;
+        const size_t want = words * sizeof(uint2) + (words * sizeof(uint2)) / 8;
+        CU(big_alloc(ctx, want, (void **)&S.d_words));
+        S.words_bytes = want;
+    }
+    if (t) CU(cudaMemcpyAsync(S.d_words, st->d_tail, ((size_t)(t + 31) / 32) * sizeof(uint2), cudaMemcpyDeviceToDevice, sm));
+    uint64_t a = (32 - (t & 31u)) & 31u; // symbols that complete the tail's partial word
+    if (a > n) a = n;
+    if (a) {
+        StreamHead hd;
+        memset(&hd, 0, sizeof(hd));
+        memcpy(hd.sym, host_ranks, (size_t)a);
+        stream_head_kernel<<<1, 32, 0, sm>>>(S.d_words, t, hd, (uint32_t)a);
+        ctx->launches++;
+    }
+    const uint64_t bulk = n - a;
+    uint2 *dst = S.d_words + (t + a) / 32;
+    if (bulk >= UploadPool::env_u64("SPMB_UPLOAD_MIN", 32ull << 20) && ensure_upload(ctx) == SPMB_OK) {
+        // both movers of the upload queue, cut fine enough that every mover gets several chunks of this feed
+        const uint64_t movers = (uint64_t)ctx->upload->n_workers + 1;
+        uint64_t chunk = bulk / (4 * movers);
+        if (chunk < (256u << 10)) chunk = 256u << 10;
+        cudaError_t e = ctx->upload->run(host_ranks + a, bulk, dst, sm, &ctx->launches, chunk);
+        if (e != cudaSuccess) { cudaGetLastError(); S.busy = false; return set_err(ctx, SPMB_ERR_CUDA, "stream upload", e); }
+    } else if (bulk) {
+        if (bulk > S.raw_bytes) {
+            cudaFree(S.d_raw);
+            S.d_raw = nullptr; S.raw_bytes = 0;
+            CU(cudaMalloc(&S.d_raw, bulk + bulk / 8 + 64));
+            S.raw_bytes = bulk + bulk / 8 + 64;
+        }
+        CU(cudaMemcpyAsync(S.d_raw, host_ranks + a, bulk, cudaMemcpyHostToDevice, sm));
+        const uint64_t groups = (bulk + 31) / 32;
+        bytes_to_chunks_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, sm>>>(S.d_raw, bulk, dst);
+        ctx->launches++;
+        CU(cudaGetLastError());
+    }
+    // ---- the words as a store (planes for the exact kernel, lane chunks for the others) ----
+    if (S.store) { spmb_store_destroy(S.store); S.store = nullptr; }
+    int rc = store_alloc(ctx, total, 0, SPMB_MODE_PLAIN, &S.store);
+    if (rc) { S.busy = false; return rc; }
+    {
+        uint2 *l = nullptr;
+        const bool want_lanes = !(st->pat->alg == SPMB_ALG_HORSPOOL || st->pat->alg == SPMB_ALG_SHIFTOR);
+        if (want_lanes && big_alloc(ctx, S.store->bytes, (void **)&l) != cudaSuccess) { cudaGetLastError(); l = nullptr; }
+        ChunkSource src{S.d_words, total};
+        pack_chunks_kernel<ChunkSource><<<(unsigned)(S.store->lay.n_cols_alloc / 1024), 1024, 0, sm>>>(src, S.store->lay, S.store->planes, l);
+        S.store->lanes = l;
+        ctx->launches++;
+        CU(cudaGetLastError());
+    }
+    // ---- the state for the next feed ----
+    const uint32_t nk = (uint32_t)std::min<uint64_t>(st->keep, total);
+    if (nk) {
+        stream_carry_kernel<<<(nk / 32 + 1 + 63) / 64, 64, 0, sm>>>(S.d_words, total, nk, st->d_tail);
+        ctx->launches++;
+        CU(cudaGetLastError());
+    }
+    st->tail_len = nk;
+    st->offset += n;
+    const uint32_t pre = ctx->launches - launches0;
+    // ---- search ----
+    if (!S.empty) {
+        rc = spmb_search_launch(ctx, S.store, st->pat, S.hits); // resets ctx->launches
+        ctx->launches += pre;
+        if (rc) { S.busy = false; return rc; }
+    }
+    S.launches = ctx->launches;
+    // the pageable / pinned host chunk of the small path must have left before we return
+    if (bulk && bulk < UploadPool::env_u64("SPMB_UPLOAD_MIN", 32ull << 20)) {
+        // cudaMemcpyAsync from pageable memory returns after staging; a pinned source needs the copy to finish
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, host_ranks) == cudaSuccess && at.type == cudaMemoryTypeHost) CU(cudaStreamSynchronize(sm));
+        else cudaGetLastError();
+    }
+    return SPMB_OK;
+}
+
+// hits of the oldest chunk in flight; ends are relative to that chunk's start, like the reference's fresh Finder on
+// every chunk (myers_matcher_restorable_test.cpp:66-69)
+extern "C" int spmb_stream_collect(spmb_context *ctx, spmb_stream *st, spmb_hits *h)
+{
+    if (!ctx || !st || !h) return SPMB_ERR_ARG;
+    ENTER(ctx);
+    const int si = st->next_collect;
+    spmb_stream::Slot &S = st->slot[si];
+    if (!S.busy) return set_err(ctx, SPMB_ERR_ARG, "no chunk in flight");
+    st->next_collect ^= 1;
+    h->host.clear();
+    h->count = 0;
+    h->view = nullptr;
+    h->pend_store = nullptr; h->pend_pat = nullptr;
+    int rc = SPMB_OK;
+    if (!S.empty) {
+        rc = spmb_search_finish(ctx, S.hits);
+        if (rc == SPMB_OK) {
+            const spmb_hit *d = spmb_hits_data(S.hits);
+            const uint64_t cnt = spmb_hits_count(S.hits);
+            h->host.reserve(cnt);
+            // hits ending inside the carried context were reported by an earlier feed
+            for (uint64_t i = 0; i < cnt; ++i)
+                if (d[i].end > S.t) { spmb_hit x = d[i]; x.end -= S.t; h->host.push_back(x); }
+            h->count = h->host.size();
+        }
+    }
+    ctx->launches = S.launches;
+    stream_slot_release(st, si);
+    return rc;
+}
+
+extern "C" int spmb_stream_feed(spmb_context *ctx, spmb_stream *st, const uint8_t *host_ranks, uint64_t n, spmb_hits *h)
+{
+    if (!ctx || !st || !h || (!host_ranks && n)) return SPMB_ERR_ARG;
+    if (st->pat->alg == SPMB_ALG_MYERS_PREFIX) return stream_feed_prefix(ctx, st, host_ranks, n, h);
+    if (st->slot[0].busy || st->slot[1].busy) return set_err(ctx, SPMB_ERR_ARG, "chunks submitted with spmb_stream_submit are still in flight");
+    int rc = spmb_stream_submit(ctx, st, host_ranks, n);
+    if (rc) return rc;
+    return spmb_stream_collect(ctx, st, h);
+}
+
+// the score of every needle at the current column (Myers streams; 0 for the exact searchers)
+static int stream_errors(spmb_stream *st, std::vector<uint32_t> &err)
+{
+    const spmb_pattern *p = st->pat;
+    err.assign(p->n_pat, 0);
+    if (!(p->alg == SPMB_ALG_MYERS || p->alg == SPMB_ALG_MYERS_FILTERED) || p->NW == 0) return SPMB_OK;
+    spmb_context *ctx = st->ctx;
+    ENTER(ctx);
+    StreamScoreArgs a{st->d_tail, st->tail_len, p->d_eq, p->d_meta, p->n_pat, st->d_err};
+    const unsigned grid = (p->n_pat + 63) / 64;
+    switch (p->NW) {
+    case 1: stream_score_kernel<1><<<grid, 64, 0, ctx->stream>>>(a); break;
+    case 2: stream_score_kernel<2><<<grid, 64, 0, ctx->stream>>>(a); break;
+    case 3: stream_score_kernel<3><<<grid, 64, 0, ctx->stream>>>(a); break;
+    case 4: stream_score_kernel<4><<<grid, 64, 0, ctx->stream>>>(a); break;
+    case 5: stream_score_kernel<5><<<grid, 64, 0, ctx->stream>>>(a); break;
+    case 6: stream_score_kernel<6><<<grid, 64, 0, ctx->stream>>>(a); break;
+    case 7: stream_score_kernel<7><<<grid, 64, 0, ctx->stream>>>(a); break;
+    case 8: stream_score_kernel<8><<<grid, 64, 0, ctx->stream>>>(a); break;
+    default: return set_err(ctx, SPMB_ERR_UNSUPPORTED, "stream score: needle too long");
+    }
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(err.data(), st->d_err, p->n_pat * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return SPMB_OK;
+}
+
+// state blob: {u64 offset, u32 tail_len, u32 n_patterns, u32 errors[n_patterns], u8 tail[tail_len]}
+extern "C" int spmb_stream_capture(const spmb_stream *st_c, void *buf, size_t *size)
+{
+    if (!st_c || !size) return SPMB_ERR_ARG;
+    spmb_stream *st = const_cast<spmb_stream *>(st_c);
+    const bool prefix = st->pat->alg == SPMB_ALG_MYERS_PREFIX;
+    const std::vector<uint8_t> &tl = prefix ? st->tail : st->host_tail;
+    const uint32_t np = st->pat->n_pat;
+    const size_t need = 16 + 4 * (size_t)np + tl.size();
     if (!buf) { *size = need; return SPMB_OK; }
     if (*size < need) { *size = need; return SPMB_ERR_ARG; }
-    uint64_t hdr[2] = {st->offset, (uint64_t)st->tail.size()};
-    memcpy(buf, hdr, 16);
-    if (!st->tail.empty()) memcpy((char *)buf + 16, st->tail.data(), st->tail.size());
+    std::vector<uint32_t> err(np, 0);
+    if (!prefix) {
+        if (st->slot[0].busy || st->slot[1].busy) return SPMB_ERR_ARG; // collect first: the state is that of the last chunk
+        int rc = stream_errors(st, err);
+        if (rc) return rc;
+    }
+    char *o = (char *)buf;
+    const uint64_t off = st->offset;
+    const uint32_t tlen = (uint32_t)tl.size();
+    memcpy(o, &off, 8); memcpy(o + 8, &tlen, 4); memcpy(o + 12, &np, 4);
+    if (np) memcpy(o + 16, err.data(), 4 * (size_t)np);
+    if (tlen) memcpy(o + 16 + 4 * (size_t)np, tl.data(), tlen);
     *size = need;
     return SPMB_OK;
 }
@@ -2246,13 +2522,43 @@ extern "C" int spmb_stream_capture(const spmb_stream *st, void *buf, size_t *siz
 extern "C" int spmb_stream_restore(spmb_stream *st, const void *buf, size_t size)
 {
     if (!st || !buf || size < 16) return SPMB_ERR_ARG;
-    uint64_t hdr[2];
-    memcpy(hdr, buf, 16);
-    if (size < 16 + hdr[1]) return SPMB_ERR_ARG;
-    st->offset = hdr[0];
-    st->tail.assign((const uint8_t *)buf + 16, (const uint8_t *)buf + 16 + hdr[1]);
+    const char *in = (const char *)buf;
+    uint64_t off; uint32_t tlen, np;
+    memcpy(&off, in, 8); memcpy(&tlen, in + 8, 4); memcpy(&np, in + 12, 4);
+    if (np != st->pat->n_pat || size < 16 + 4 * (size_t)np + tlen) return SPMB_ERR_ARG;
+    const uint8_t *tb = (const uint8_t *)in + 16 + 4 * (size_t)np;
+    if (st->pat->alg == SPMB_ALG_MYERS_PREFIX) {
+        st->offset = off;
+        st->tail.assign(tb, tb + tlen);
+        return SPMB_OK;
+    }
+    if (tlen > st->keep || st->slot[0].busy || st->slot[1].busy) return SPMB_ERR_ARG;
+    spmb_context *ctx = st->ctx;
+    ENTER(ctx);
+    std::vector<uint64_t> words((size_t)st->keep / 32 + 2, 0);
+    if (tlen) spmb_host_pack_chunks(tb, tlen, words.data()); // format conversion only (hostpack.cpp)
+    CU(cudaMemcpyAsync(st->d_tail, words.data(), words.size() * 8, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    st->host_tail.assign(tb, tb + tlen);
+    for (auto &c : st->host_tail) c &= 3;
+    st->tail_len = tlen;
+    st->offset = off;
     return SPMB_OK;
 }
+
+// the score of needle `pattern_index` at the current column of a Myers stream (capture().errors of the reference)
+extern "C" int spmb_stream_errors(spmb_stream *st, uint32_t pattern_index, uint32_t *errors)
+{
+    if (!st || !errors || pattern_index >= st->pat->n_pat) return SPMB_ERR_ARG;
+    if (st->pat->alg == SPMB_ALG_MYERS_PREFIX || st->slot[0].busy || st->slot[1].busy) return SPMB_ERR_ARG;
+    std::vector<uint32_t> err;
+    int rc = stream_errors(st, err);
+    if (rc) return rc;
+    *errors = err[pattern_index];
+    return SPMB_OK;
+}
+
+extern "C" uint64_t spmb_stream_offset(const spmb_stream *st) { return st ? st->offset : 0; }
 
 // ------------------------------------------------------------------------------------------
 // measurement helpers

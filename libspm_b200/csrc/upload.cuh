@@ -17,6 +17,7 @@
 
 #include "../../include/spmb.h"
 
+#include <algorithm>
 #include <atomic>
 #include <chrono>
 #include <cstdio>
@@ -134,7 +135,8 @@ static inline int spmb_host_cpus()
 struct UploadPool {
     enum { SLOTS = 4 };
     int device = 0;
-    uint64_t chunk_sym = 4ull << 20;
+    uint64_t chunk_sym = 4ull << 20;            // capacity of a staging buffer, and the chunk size of one-shot uploads
+    uint64_t job_chunk = 4ull << 20;            // chunk size of the current text job (<= chunk_sym; stream feeds use smaller ones)
     uint64_t min_sym = 32ull << 20;
     int n_workers = 0;
     bool trace = false;                         // SPMB_UPLOAD_TRACE=1: per-job timings on stderr
@@ -203,7 +205,7 @@ struct UploadPool {
         }
     }
 
-    cudaError_t init(int dev)
+    cudaError_t init(int dev, int threads_override = -1)
     {
         device = dev;
         raw_pct_text = env_u64("SPMB_UPLOAD_RAW_PCT", raw_pct_text);
@@ -219,6 +221,7 @@ struct UploadPool {
         if (dflt > 31) dflt = 31;
         if (dflt < 0) dflt = 0;
         n_workers = (int)env_u64("SPMB_HOST_THREADS", (uint64_t)dflt);
+        if (threads_override >= 0) n_workers = threads_override; // spmb_context_set_upload_threads
         if (n_workers > 256) n_workers = 256;
         cudaError_t e = cudaSuccess;
         for (int s = 0; s < SLOTS && e == cudaSuccess; ++s) {
@@ -268,8 +271,8 @@ struct UploadPool {
                 const auto tb = now();
                 t_wait += us(ta, tb);
                 if (src) {
-                    const uint64_t p0 = idx * chunk_sym;
-                    const uint64_t len = (n - p0 < chunk_sym) ? n - p0 : chunk_sym;
+                    const uint64_t p0 = idx * job_chunk;
+                    const uint64_t len = (n - p0 < job_chunk) ? n - p0 : job_chunk;
                     spmb_host_pack_chunks(src + p0, len, W.pinned[b]);
                     t_pack += us(tb, now());
                     if (e == cudaSuccess)
@@ -378,16 +381,19 @@ struct UploadPool {
 
     // fills dst[0, ceil(n/32)) (device, allocated in `stream`'s order) from host_ranks[0, n).  Returns when
     // every byte of host_ranks has been consumed and dst is complete.
-    cudaError_t run(const uint8_t *host_ranks, uint64_t n_sym, uint2 *dst, cudaStream_t stream, uint32_t *launches)
+    // chunk = 0: chunk_sym; else the chunk size of this job (multiple of 1024, <= chunk_sym): a short job (one feed
+    // of a stream) is cut finer so that every mover gets several chunks
+    cudaError_t run(const uint8_t *host_ranks, uint64_t n_sym, uint2 *dst, cudaStream_t stream, uint32_t *launches, uint64_t chunk = 0)
     {
         src = host_ranks;
         ev_src = nullptr;
         n = n_sym;
         d_chunks = dst;
-        n_chunks = (n_sym + chunk_sym - 1) / chunk_sym;
+        job_chunk = (chunk == 0 || chunk > chunk_sym) ? chunk_sym : std::max<uint64_t>(1024, chunk / 1024 * 1024);
+        n_chunks = (n_sym + job_chunk - 1) / job_chunk;
         cudaError_t e = drive(stream, &last_raw, [&](uint64_t idx, int s) -> cudaError_t {
-            const uint64_t p0 = idx * chunk_sym;
-            const uint64_t len = (n - p0 < chunk_sym) ? n - p0 : chunk_sym;
+            const uint64_t p0 = idx * job_chunk;
+            const uint64_t len = (n - p0 < job_chunk) ? n - p0 : job_chunk;
             cudaError_t r = cudaMemcpyAsync(d_slot[s], src + p0, len, cudaMemcpyHostToDevice, stream);
             if (r != cudaSuccess) return r;
             const uint64_t groups = (len + 31) / 32;

@@ -326,4 +326,47 @@ MINI_TEST(needle_and_haystack_of_different_alphabets_are_rejected) {
     EXPECT_TRUE(threw);
 }
 
+// ---- round 2: what the captured state shows, and the matcher call over a group of devices ----
+MINI_TEST(restorable_myers_state_exposes_errors) {
+    // capture().errors of the reference's state (myers_matcher_restorable.hpp:57-59): the score at the current column
+    auto matcher = spm::restorable_myers_matcher{needle, 1u};
+    EXPECT_EQ(spm::capture(matcher).errors(), std::ranges::size(needle)); // nothing read yet
+    sequence_t first(haystack.begin(), haystack.begin() + 13);           // ACGTGACTAGCAC: GCAC matches GCACG up to one deletion
+    matcher(first, [](auto const &) {});
+    EXPECT_EQ(spm::capture(matcher).errors(), 1u);
+    EXPECT_EQ(spm::capture(matcher).offset(), 13u);
+    sequence_t next(haystack.begin() + 13, haystack.begin() + 14);       // ...G: an exact occurrence ends here
+    matcher(next, [](auto const &) {});
+    EXPECT_EQ(spm::capture(matcher).errors(), 0u);
+}
+
+MINI_TEST(device_group_equals_single_device) {
+    // a long haystack (the golden one repeated with a seeded twist) over three shards; two of them share device 0
+    sequence_t big;
+    std::uint32_t x = 12345;
+    for (int r = 0; r < 20000; ++r) {
+        for (auto c : haystack) big.push_back(c);
+        x = x * 1664525u + 1013904223u;
+        big.push_back(spm::dna4{}.assign_rank(static_cast<std::uint8_t>(x >> 30)));
+    }
+    spm::device_group gpus{std::vector<int>{0, 0, 0}};
+    EXPECT_EQ(gpus.size(), 3u);
+    {
+        auto matcher = spm::horspool_matcher{needle};
+        std::vector<std::size_t> one, many;
+        matcher(big, [&](auto const &f) { one.push_back(seqan2::beginPosition(f)); });
+        gpus.search(matcher, big, [&](auto const &f) { many.push_back(seqan2::beginPosition(f)); });
+        EXPECT_TRUE(one.size() > 50000);
+        EXPECT_TRUE(one == many);
+    }
+    {
+        auto matcher = spm::myers_matcher{needle, 1};
+        std::vector<std::size_t> one, many;
+        matcher(big, [&](auto const &f) { one.push_back(seqan2::endPosition(f) * 4 + f.errors()); });
+        gpus.search(matcher, big, [&](auto const &f) { many.push_back(seqan2::endPosition(f) * 4 + f.errors()); });
+        EXPECT_TRUE(one.size() > 150000);
+        EXPECT_TRUE(one == many);
+    }
+}
+
 int main() { return mini::run_all(); }
