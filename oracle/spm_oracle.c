@@ -361,8 +361,9 @@ uint64_t orc_search_mt(int alg, const uint8_t *text, uint64_t n, const uint8_t *
         if (b > n) b = n;
         uint64_t s0 = (a > overlap) ? a - overlap : 0;
         uint64_t len = b - s0;
-        /* chunk-local scan with a bounded local buffer, refilled as needed */
-        const uint64_t LB = 1 << 16;
+        /* chunk-local scan in steps of 2^20 symbols; the local buffer holds one hit per symbol of a step, so a
+         * hit-dense text (every position a hit) is stored completely */
+        const uint64_t LB = 1 << 20;
         uint64_t *le = (uint64_t *)malloc(LB * sizeof(uint64_t));
         uint32_t *lr = (uint32_t *)malloc(LB * sizeof(uint32_t));
         uint64_t cnt = 0;
@@ -376,7 +377,7 @@ uint64_t orc_search_mt(int alg, const uint8_t *text, uint64_t n, const uint8_t *
                 uint64_t lim = c < LB ? c : LB;
                 for (uint64_t i = 0; i < lim; ++i)
                     if (le[i] > a) { ++cnt; if (store) hv_push(&per[t], le[i], lr[i]); }
-                if (c > LB) cnt += c - LB; /* overflow only possible in pathological inputs */
+                if (c > LB) cnt += c - LB; /* cannot happen: at most one hit per symbol */
                 off += step;
             }
             free(ms);
@@ -394,12 +395,17 @@ uint64_t orc_search_mt(int alg, const uint8_t *text, uint64_t n, const uint8_t *
                 off += step;
             }
         } else {
-            /* Horspool is stateless: windows starting in [s0, b-m] */
-            uint64_t c = orc_horspool(text + s0, len, pat, m, le, LB);
-            uint64_t lim = c < LB ? c : LB;
-            for (uint64_t i = 0; i < lim; ++i)
-                if (le[i] + s0 > a) { ++cnt; if (store) hv_push(&per[t], le[i] + s0, 0); }
-            if (c > LB) cnt += c - LB;
+            /* Horspool is stateless: windows starting in [s0, b-m], taken in steps of 2^20 start positions */
+            uint64_t off = 0;
+            while (off + m <= len) {
+                uint64_t span = len - off < (1u << 20) + (uint64_t)m - 1 ? len - off : (1u << 20) + (uint64_t)m - 1;
+                uint64_t c = orc_horspool(text + s0 + off, span, pat, m, le, LB);
+                uint64_t lim = c < LB ? c : LB;
+                for (uint64_t i = 0; i < lim; ++i)
+                    if (le[i] + s0 + off > a) { ++cnt; if (store) hv_push(&per[t], le[i] + s0 + off, 0); }
+                if (c > LB) cnt += c - LB;
+                off += 1u << 20;
+            }
         }
         free(le);
         free(lr);

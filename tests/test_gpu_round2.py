@@ -90,7 +90,7 @@ def test_exact_needle_that_starts_in_a_repeat(ctx, rl):
         tail = rand_text(rng, int(rng.integers(8, 60)))
         pat = np.concatenate([np.tile(np.array(unit, dtype=np.uint8), head)[:head], tail]).astype(np.uint8)
         # plant it a few times, also right at the start and the end of the text
-        for s in (0, 1, 31, 32, 33, 5000, 77_777, n - len(pat)):
+        for s in (0, 1001, 2031, 3032, 4033, 5000, 77_777, n - len(pat)):
             text[s:s + len(pat)] = pat
         store.close()
         store = sp.Store.from_host(ctx, text, rl)
