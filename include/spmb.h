@@ -179,7 +179,12 @@ int spmb_pattern_create_wide(spmb_context *ctx, int alg, const uint8_t *ranks, u
                              uint32_t bits, spmb_pattern **out);
 uint32_t spmb_pattern_symbol_bits(const spmb_pattern *p); /* 2 or 4 */
 /* a set of n_patterns needles searched in one pass (config C5); lengths[i] symbols each,
- * concatenated in ranks.  All must share ceil(len/32) for SPMB_ALG_MYERS. */
+ * concatenated in ranks.  SPMB_ALG_MYERS / SPMB_ALG_MYERS_FILTERED take any mix of lengths up to 8192 symbols
+ * (the reference takes any needle, myers_matcher.hpp:37-43): needles are grouped by ceil(len/32) and searched
+ * one group per launch; needles longer than 256 symbols run their first 256 symbols through the same kernels
+ * as a filter and the whole needle, its words chained across the lanes of a warp, over every candidate
+ * (libspm_b200/csrc/myers_chain.cuh).  Hits carry the index of the needle in this call's order.
+ * SPMB_ALG_MYERS_PREFIX and the 4-bit alphabets stay at 256 symbols (SPMB_ERR_UNSUPPORTED beyond). */
 int spmb_pattern_set_create(spmb_context *ctx, int alg, const uint8_t *ranks,
                             const uint32_t *lengths, uint32_t n_patterns, uint32_t k,
                             spmb_pattern **out);
@@ -245,9 +250,10 @@ uint32_t spmb_last_launch_count(const spmb_context *ctx);
  * Pattern sets are allowed (hits carry pattern_id); dna4 only.
  * feed   = submit + collect: the hits of this chunk, ends relative to the chunk start like the reference's fresh
  *          Finder on each chunk (myers_matcher_restorable_test.cpp:66-69).
- * submit / collect: the asynchronous pair for streaming at full rate -- submit returns as soon as the host buffer
- *          has been consumed (search kernels still running), collect hands back the hits of the OLDEST chunk in
- *          flight; at most two chunks may be in flight, so chunk i+1 uploads while chunk i is searched.
+ * submit / collect: the asynchronous pair for streaming at full rate -- submit hands the chunk to the upload pipeline
+ *          and returns at once; THE HOST BUFFER MUST STAY VALID UNTIL THAT CHUNK HAS BEEN COLLECTED.  collect hands
+ *          back the hits of the OLDEST chunk in flight; at most two chunks may be in flight, so the packing threads
+ *          and the copy engine run on from chunk i into chunk i+1 while chunk i is searched and its hits travel.
  * SPMB_ALG_MYERS_PREFIX streams (restorable_myers_prefix_matcher) are anchored at the START OF THE STREAM: the scan is
  * clamped to the first m + k + 1 symbols of the whole stream, whereas the reference clamps every call on its own
  * haystack (myers_prefix_matcher_restorable.hpp:53-54); a caller that restores a state and feeds a fresh context

@@ -521,6 +521,7 @@ class Stream:
         self._h = C.c_void_p()
         ctx._check(lib().spmb_stream_create(ctx._h, pattern._h, C.byref(self._h)), "spmb_stream_create")
         self._hits = Hits(ctx)
+        self._held = []   # arrays of the chunks in flight: the C ABI reads them until collect()
 
     def feed(self, chunk) -> np.ndarray:
         r = _ranks(chunk)
@@ -529,14 +530,19 @@ class Stream:
         return self._hits.array()
 
     def submit(self, chunk=None, ptr: int | None = None, n: int | None = None):
-        """asynchronous feed: returns when the host buffer is consumed; the hits come from collect()."""
+        """asynchronous feed: the chunk goes to the upload pipeline, the hits come from collect(); a raw `ptr` must
+        stay valid until then (arrays passed as `chunk` are held here)."""
+        r = None
         if ptr is None:
             r = _ranks(chunk)
             ptr, n = (r.ctypes.data if r.size else None), r.size
         self.ctx._check(lib().spmb_stream_submit(self.ctx._h, self._h, C.c_void_p(ptr) if ptr else None, n), "spmb_stream_submit")
+        self._held.append(r)
 
     def collect(self) -> np.ndarray:
         self.ctx._check(lib().spmb_stream_collect(self.ctx._h, self._h, self._hits._h), "spmb_stream_collect")
+        if self._held:
+            self._held.pop(0)
         return self._hits.array()
 
     def errors(self, pattern_index: int = 0) -> int:

@@ -378,6 +378,11 @@ struct PigeonVerifyArgs {
     uint32_t seq_id;
     uint64_t own_lo, own_hi;      // plain: owned range of (last symbol index of a hit | seed begin)
     HitSink sink;
+    // duplicate suppression of the filtered Myers path (pg_emit_min); dd_keys == null: off
+    unsigned long long *dd_keys;  // [2^dd_bits] 0 = free, else key + 1
+    uint32_t *dd_idx;             // [2^dd_bits] 0 = not published yet, else index of the hit record + 1
+    uint32_t dd_bits, dd_end_bits;
+    uint64_t dd_nseq;
 };
 
 __device__ __forceinline__ void pg_emit(const HitSink &sink, uint64_t end, uint32_t seq, uint32_t pid, uint32_t err, uint32_t aux)
@@ -388,6 +393,47 @@ __device__ __forceinline__ void pg_emit(const HitSink &sink, uint64_t end, uint3
         h.end = end; h.seq_id = seq; h.pattern_id = pid; h.errors = err; h.reserved = aux;
         sink.hits[idx] = h;
     }
+}
+
+// SPMB_ALG_MYERS_FILTERED: the k+1 pieces of a needle (and neighbouring diagonals) verify overlapping windows, so the
+// same (needle, sequence, end) is found up to ~(k+1) times, each time with an upper bound of the true score whose
+// minimum is exact.  Sorting the raw list to drop them cost more than the search at small shards (C5 at 1/8 of the
+// text: 13 ordering kernels, 0.12 ms, behind 0.2 ms of search).  So the first thread to report a hit claims a slot of a
+// hash table (CAS on the key), appends the record and publishes its index; later finders only atomicMin the record's
+// error count.  A table miss (4 probes), a not-yet-published index or a key that does not fit 63 bits fall back to a
+// plain append: the ordering downstream still removes those few duplicates, this table only removes the volume.
+__device__ __forceinline__ void pg_emit_min(const PigeonVerifyArgs &a, uint64_t end, uint32_t seq, uint32_t pid, uint32_t err)
+{
+    if (a.dd_keys) {
+        const unsigned long long key = ((((unsigned long long)pid * a.dd_nseq + seq) << a.dd_end_bits) | end) + 1ull;
+        const uint32_t mask = (1u << a.dd_bits) - 1u;
+        uint32_t slot = pg_h2((uint32_t)(key >> 32), (uint32_t)key) >> (32 - a.dd_bits);
+        for (int probe = 0; probe < 4; ++probe) {
+            const unsigned long long old = atomicCAS(a.dd_keys + slot, 0ull, key);
+            if (old == 0ull) {
+                const unsigned long long idx = spmb_append_slot(a.sink.count);
+                if (idx < a.sink.cap) {
+                    spmb_hit h;
+                    h.end = end; h.seq_id = seq; h.pattern_id = pid; h.errors = err; h.reserved = 0;
+                    a.sink.hits[idx] = h;
+                    __threadfence();
+                    atomicExch(a.dd_idx + slot, (uint32_t)idx + 1u);
+                }
+                return;
+            }
+            if (old == key) {
+                const uint32_t pi = *reinterpret_cast<volatile uint32_t *>(a.dd_idx + slot);
+                if (pi) {
+                    __threadfence();
+                    atomicMin(&a.sink.hits[pi - 1].errors, err);
+                    return;
+                }
+                break;
+            }
+            slot = (slot + 1) & mask;
+        }
+    }
+    pg_emit(a.sink, end, seq, pid, err, 0);
 }
 
 // symbol at offset d (>= 0) from (row R, column col); a plain text runs on into the next rows
@@ -530,7 +576,7 @@ __global__ void __launch_bounds__(128) pigeon_verify_kernel(PigeonVerifyArgs a)
                 pg_load_eq<NW>(eqp, c, eq);
                 pg_myers_col<NW, false>(vp, vn, eq, hp, hn);
                 score += pg_score_delta<NW>(hp, hn, pm.m);
-                if (score <= k && t >= own_lo && t < own_hi) pg_emit(a.sink, (uint64_t)(t + 1), seq, pid, (uint32_t)score, 0);
+                if (score <= k && t >= own_lo && t < own_hi) pg_emit_min(a, (uint64_t)(t + 1), seq, pid, (uint32_t)score);
             }
         }
     }

@@ -23,6 +23,7 @@
 #include "layout.cuh"
 #include "myers.cuh"
 #include "myers_cut.cuh"
+#include "myers_chain.cuh"
 #include "pack.cuh"
 #include "pigeon.cuh"
 #include "upload.cuh"
@@ -119,6 +120,7 @@ struct spmb_store {
     mutable uint2 *lanes = nullptr;
     // windows mode
     uint32_t *row_len = nullptr, *row_seq = nullptr, *row_own = nullptr;
+    uint32_t seq_base = 0;          // row_seq[r] = seq_base + r (window buckets of a JST)
     // 4-bit alphabets (spmb_store_create_wide): this store holds bits 1..0 of every symbol, `hi` bits 3..2
     spmb_store *hi = nullptr;
     uint32_t sym_bits = 2;
@@ -145,6 +147,15 @@ struct spmb_pattern {
     bool filtered = false;            // the filter is in use (q long enough)
     uint32_t filter_step = 1;         // text positions = 0 (mod step) are scanned (filtered Myers: 1, 2 or 4)
     uint32_t *d_off = nullptr;        // needle offsets into d_ranks
+    // Myers sets the one-lane kernels cannot take in one launch (needles that differ in ceil(m/32); needles longer than
+    // 256 symbols): one child set per word count, hits carry the caller's pattern ids (MyersPatMeta.pattern_id)
+    std::vector<spmb_pattern *> subs;  // children of 1..8 words, searched directly
+    spmb_pattern *long_prefix = nullptr; // child over the first 256 symbols of the long needles: the candidate filter
+    std::vector<uint32_t> ids;        // child: the caller's pattern id of every needle (empty = identity)
+    uint32_t n_long = 0;              // needles longer than 256 symbols
+    int chain_wpl = 0;                // words per lane of the lane-chained verification (myers_chain.cuh)
+    uint32_t *d_chain_eq = nullptr;
+    MyersPatMeta *d_chain_meta = nullptr;
     uint32_t *d_pg_bitmap = nullptr, *d_pg_bitmap2 = nullptr, *d_pg_ufirst = nullptr, *d_pg_pat = nullptr, *d_pg_soff = nullptr;
     unsigned long long *d_pg_tab = nullptr;
 };
@@ -156,6 +167,8 @@ struct spmb_hits {
     unsigned long long cap = 0;
     PigeonCand *d_cand = nullptr;          // candidate buffer of the seed filter (grown on demand)
     unsigned long long cand_cap = 0;
+    unsigned long long *d_dd_keys = nullptr; // duplicate-suppression table of the filtered Myers path (pigeon.cuh pg_emit_min)
+    uint32_t *d_dd_idx = nullptr;
     std::vector<spmb_hit> host;
     uint64_t count = 0;
     const spmb_store *pend_store = nullptr;
@@ -200,6 +213,13 @@ struct spmb_stream {
         uint64_t t = 0, n = 0, total = 0;
         uint32_t launches = 0;
         bool busy = false, empty = false;
+        // handed in by spmb_stream_submit, turned into device work by spmb_stream_collect
+        const uint8_t *host = nullptr;  // the chunk behind the symbols that complete the tail's partial word
+        uint64_t bulk = 0;
+        uint32_t a = 0;
+        StreamHead hd;
+        bool job = false;               // the bulk is a job of the upload pool
+        uint64_t job_seq = 0;
     } slot[2];
     int next_submit = 0, next_collect = 0;
     // anchored (prefix) streams: the state is the short prefix itself, on the host
@@ -326,6 +346,7 @@ extern "C" int spmb_context_set_upload_threads(spmb_context *ctx, int n_threads)
 {
     if (!ctx || n_threads < -1) return SPMB_ERR_ARG;
     if (ctx->upload && ctx->upload->n_workers != n_threads) { // the pool is re-created with the new thread count on the next upload
+        if (ctx->upload->in_flight()) return set_err(ctx, SPMB_ERR_ARG, "chunks of a stream are still in flight");
         ENTER(ctx);
         CU(cudaStreamSynchronize(ctx->stream));
         delete ctx->upload;
@@ -861,7 +882,8 @@ static cudaError_t pattern_upload_myers(spmb_context *ctx, spmb_pattern *p, uint
                 if (match) e4[c * NWP + j / 32] |= 1u << (j % 32);
             }
         }
-        meta[i].m = m; meta[i].k = k; meta[i].pad = (uint32_t)p->NW * 32 - m; meta[i].pattern_id = i;
+        meta[i].m = m; meta[i].k = k; meta[i].pad = (uint32_t)p->NW * 32 - m;
+        meta[i].pattern_id = p->ids.empty() ? i : p->ids[i];
     }
     p->warm = (p->max_m + k - 1 + 31) / 32 * 32;
     cudaError_t e = cudaMalloc(&p->d_eq, eq.size() * 4);
@@ -935,8 +957,71 @@ static uint32_t exact_window_offset(const uint8_t *pat, uint32_t m)
 // seeds (a 12-mer has 1.7e7 values)
 static const uint32_t SPMB_FILTER_MIN_Q = 12;
 
+static const uint32_t SPMB_CHAIN_PREFIX = 256; // symbols of a long needle the one-lane kernels filter on
+
 static int pattern_build(spmb_context *ctx, int alg, const uint8_t *ranks, const uint32_t *lengths, uint32_t n_pat,
-                         uint32_t k, double error_rate, spmb_pattern **out, uint32_t sym_bits = 2)
+                         uint32_t k, double error_rate, spmb_pattern **out, uint32_t sym_bits = 2, const uint32_t *ids = nullptr);
+
+// A Myers set with needles of different word counts, or longer than 256 symbols: one child set per word count
+// (searched by the one-lane kernels as before), and for the long needles a child over their first 256 symbols
+// whose hits are the candidates of the lane-chained verification (myers_chain.cuh).  The reference takes any
+// needle (myers_matcher.hpp:37-43).
+static int pattern_build_buckets(spmb_context *ctx, spmb_pattern *p, uint32_t k)
+{
+    std::vector<uint32_t> group[9]; // [1..8]: needles of that many words; [0]: longer ones
+    for (uint32_t i = 0; i < p->n_pat; ++i) {
+        if (p->len[i] == 0) continue;
+        const uint32_t nw = (p->len[i] + 31) / 32;
+        group[nw > 8 ? 0 : nw].push_back(i);
+    }
+    for (int g = 1; g <= 8; ++g) {
+        if (group[g].empty()) continue;
+        std::vector<uint8_t> r;
+        std::vector<uint32_t> l, id;
+        for (uint32_t i : group[g]) {
+            r.insert(r.end(), p->ranks.begin() + p->off[i], p->ranks.begin() + p->off[i] + p->len[i]);
+            l.push_back(p->len[i]);
+            id.push_back(p->ids.empty() ? i : p->ids[i]);
+        }
+        spmb_pattern *c = nullptr;
+        int rc = pattern_build(ctx, SPMB_ALG_MYERS, r.data(), l.data(), (uint32_t)l.size(), k, 0.0, &c, p->sym_bits, id.data());
+        if (rc) return rc;
+        p->subs.push_back(c);
+    }
+    if (group[0].empty()) return SPMB_OK;
+    if (p->sym_bits != 2) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "4-bit alphabets: Myers needles up to 256 symbols");
+    const uint32_t words = (p->max_m + 31) / 32;
+    const int wpl = words <= 32 ? 1 : words <= 64 ? 2 : words <= 128 ? 4 : words <= 256 ? 8 : 0;
+    if (!wpl) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "Myers needle longer than 8192 symbols");
+    p->chain_wpl = wpl;
+    p->n_long = (uint32_t)group[0].size();
+    const uint32_t NWT = 32u * (uint32_t)wpl;
+    std::vector<uint32_t> eq((size_t)p->n_long * 4 * NWT, 0);
+    std::vector<MyersPatMeta> meta(p->n_long);
+    std::vector<uint8_t> r;
+    std::vector<uint32_t> l, id;
+    for (uint32_t q = 0; q < p->n_long; ++q) {
+        const uint32_t i = group[0][q];
+        const uint8_t *pr = p->ranks.data() + p->off[i];
+        uint32_t *e = eq.data() + (size_t)q * 4 * NWT;
+        for (uint32_t j = 0; j < p->len[i]; ++j) e[(pr[j] & 3u) * NWT + j / 32] |= 1u << (j % 32);
+        meta[q].m = p->len[i]; meta[q].k = k; meta[q].pad = 0;
+        meta[q].pattern_id = p->ids.empty() ? i : p->ids[i];
+        r.insert(r.end(), pr, pr + SPMB_CHAIN_PREFIX);
+        l.push_back(SPMB_CHAIN_PREFIX);
+        id.push_back(q); // a candidate names its needle by the index into the chain tables
+    }
+    int rc = pattern_build(ctx, SPMB_ALG_MYERS, r.data(), l.data(), p->n_long, k, 0.0, &p->long_prefix, 2, id.data());
+    if (rc) return rc;
+    cudaError_t e = upload_vec(ctx, &p->d_chain_eq, eq);
+    if (e == cudaSuccess) e = upload_vec(ctx, &p->d_chain_meta, meta);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) return set_err(ctx, SPMB_ERR_CUDA, "chain table upload", e);
+    return SPMB_OK;
+}
+
+static int pattern_build(spmb_context *ctx, int alg, const uint8_t *ranks, const uint32_t *lengths, uint32_t n_pat,
+                         uint32_t k, double error_rate, spmb_pattern **out, uint32_t sym_bits, const uint32_t *ids)
 {
     if (!ctx || !out || !lengths || n_pat == 0) return SPMB_ERR_ARG;
     if (sym_bits == 3) sym_bits = 4; // dna5 travels in the 4-bit layout
@@ -964,22 +1049,27 @@ static int pattern_build(spmb_context *ctx, int alg, const uint8_t *ranks, const
     if (total >= (1ull << 31)) { delete p; return set_err(ctx, SPMB_ERR_UNSUPPORTED, "pattern set too large"); }
     p->ranks.assign(ranks, ranks + total);
     for (auto &c : p->ranks) c &= (sym_bits == 4 ? 15 : 3);
+    if (ids) p->ids.assign(ids, ids + n_pat);
 
     cudaError_t e = cudaMalloc(&p->d_ranks, total ? total : 1);
     if (e == cudaSuccess && total) e = cudaMemcpyAsync(p->d_ranks, p->ranks.data(), total, cudaMemcpyHostToDevice, ctx->stream);
 
     if (myers_like) {
         // an empty needle matches nothing (window_size 0): keep NW = 0 and never launch
-        if (p->max_m > 256) { spmb_pattern_destroy(p); return set_err(ctx, SPMB_ERR_UNSUPPORTED, "Myers needle longer than 256 symbols"); }
-        p->NW = (int)((p->max_m + 31) / 32);
+        const bool too_long = p->max_m > SPMB_CHAIN_PREFIX;
+        if (too_long && alg == SPMB_ALG_MYERS_PREFIX) {
+            spmb_pattern_destroy(p);
+            return set_err(ctx, SPMB_ERR_UNSUPPORTED, "anchored Myers: needles up to 256 symbols");
+        }
+        p->NW = (int)((std::min<uint32_t>(p->max_m, SPMB_CHAIN_PREFIX) + 31) / 32);
         // the filtered path verifies needle by needle and reads the score at row m-1, so a set may mix
-        // word counts there; the direct kernel wants one word count per set
+        // word counts there; the direct kernel wants one word count per launch
         bool mixed = false;
         for (uint32_t i = 0; i < n_pat; ++i)
             if (p->len[i] && (int)((p->len[i] + 31) / 32) != p->NW) mixed = true;
         std::vector<std::pair<uint32_t, uint32_t>> seeds;
         uint32_t q = 0;
-        if (alg == SPMB_ALG_MYERS_FILTERED && p->min_m > 0) {
+        if (alg == SPMB_ALG_MYERS_FILTERED && p->min_m > 0 && !too_long) {
             const uint32_t L = p->min_m / (k + 1); // pigeonhole piece length
             if (L >= SPMB_FILTER_MIN_Q) {
                 p->filtered = true;
@@ -1001,11 +1091,11 @@ static int pattern_build(spmb_context *ctx, int alg, const uint8_t *ranks, const
                         for (uint32_t d = 0; d < step; ++d) seeds.push_back({i, piece * L + d});
             }
         }
-        if (mixed && !(p->filtered || alg == SPMB_ALG_MYERS_PREFIX)) {
-            spmb_pattern_destroy(p);
-            return set_err(ctx, SPMB_ERR_UNSUPPORTED, "all needles of a Myers set must share ceil(m/32)");
-        }
-        if (p->NW > 0) {
+        if ((too_long || mixed) && !(p->filtered || alg == SPMB_ALG_MYERS_PREFIX)) {
+            if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+            int rc = (e == cudaSuccess) ? pattern_build_buckets(ctx, p, k) : set_err(ctx, SPMB_ERR_CUDA, "pattern upload", e);
+            if (rc) { spmb_pattern_destroy(p); return rc; }
+        } else if (p->NW > 0) {
             if (e == cudaSuccess) e = pattern_upload_myers(ctx, p, k);
             if (e == cudaSuccess && p->filtered) e = pattern_upload_pigeon(ctx, p, seeds, q);
         }
@@ -1098,6 +1188,9 @@ extern "C" int spmb_pattern_destroy(spmb_pattern *p)
     cudaFree(p->d_off);
     cudaFree(p->d_pg_bitmap); cudaFree(p->d_pg_bitmap2); cudaFree(p->d_pg_tab);
     cudaFree(p->d_pg_ufirst); cudaFree(p->d_pg_pat); cudaFree(p->d_pg_soff);
+    cudaFree(p->d_chain_eq); cudaFree(p->d_chain_meta);
+    for (spmb_pattern *c : p->subs) spmb_pattern_destroy(c);
+    spmb_pattern_destroy(p->long_prefix);
     delete p;
     return SPMB_OK;
 }
@@ -1130,7 +1223,8 @@ static int cand_reserve(spmb_context *ctx, spmb_hits *h, unsigned long long cap)
     cudaFree(h->d_cand);
     h->d_cand = nullptr;
     h->cand_cap = 0;
-    CU(cudaMalloc(&h->d_cand, cap * sizeof(PigeonCand)));
+    static_assert(sizeof(spmb_hit) >= sizeof(PigeonCand), "the candidate buffer holds either record");
+    CU(cudaMalloc((void **)&h->d_cand, cap * sizeof(spmb_hit)));
     h->cand_cap = cap;
     return SPMB_OK;
 }
@@ -1158,6 +1252,7 @@ extern "C" int spmb_hits_destroy(spmb_hits *h)
     if (h->ctx) cudaSetDevice(h->ctx->device);
     cudaFree(h->d_hits);
     cudaFree(h->d_count);
+    cudaFree(h->d_dd_keys); cudaFree(h->d_dd_idx);
     cudaFree(h->d_cand);
     cudaFree(h->ord_k0); cudaFree(h->ord_k1); cudaFree(h->ord_i0); cudaFree(h->ord_i1); cudaFree(h->ord_isel);
     cudaFree(h->ord_flag); cudaFree(h->ord_out); cudaFree(h->ord_tmp);
@@ -1288,6 +1383,9 @@ static cudaError_t launch_verify(spmb_context *ctx, const spmb_pattern *p, const
     return cudaGetLastError();
 }
 
+static int bits_for(unsigned long long max_value);
+enum { SPMB_DD_BITS = 19 }; // slots of the duplicate-suppression table (6 MB, cleared per launch)
+
 // seed filter + (seed emission | windowed Myers verification) over the shard [st0, st1) of a store
 template <int MODE>
 static int enqueue_filtered(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p, spmb_hits *h,
@@ -1330,6 +1428,28 @@ static int enqueue_filtered(spmb_context *ctx, const spmb_store *s, const spmb_p
     va.own_lo = st0 * per_st;
     va.own_hi = std::min<uint64_t>(s->lay.n, st1 * per_st);
     va.sink = sink;
+    va.dd_keys = nullptr; va.dd_idx = nullptr; va.dd_bits = SPMB_DD_BITS; va.dd_end_bits = 0; va.dd_nseq = 1;
+    static const bool dd_off = getenv("SPMB_NO_DEDUP") != nullptr; // A/B switch
+    if (p->alg == SPMB_ALG_MYERS_FILTERED && !dd_off && h->cap < (1ull << 31)) {
+        const uint64_t n_seq = (MODE == SPMB_MODE_PLAIN) ? 1 : (uint64_t)s->seq_base + s->lay.n_st * 32;
+        const uint64_t max_end = (MODE == SPMB_MODE_PLAIN) ? s->lay.n : s->lay.row_len;
+        const int eb = bits_for(max_end + 1);
+        if (bits_for((uint64_t)p->n_pat * n_seq) + eb <= 62) {
+            if (!h->d_dd_keys) {
+                if (cudaMalloc(&h->d_dd_keys, sizeof(unsigned long long) << SPMB_DD_BITS) != cudaSuccess ||
+                    cudaMalloc(&h->d_dd_idx, sizeof(uint32_t) << SPMB_DD_BITS) != cudaSuccess) {
+                    cudaGetLastError();
+                    cudaFree(h->d_dd_keys); cudaFree(h->d_dd_idx);
+                    h->d_dd_keys = nullptr; h->d_dd_idx = nullptr;
+                }
+            }
+            if (h->d_dd_keys) {
+                CU(cudaMemsetAsync(h->d_dd_keys, 0, sizeof(unsigned long long) << SPMB_DD_BITS, ctx->stream));
+                CU(cudaMemsetAsync(h->d_dd_idx, 0, sizeof(uint32_t) << SPMB_DD_BITS, ctx->stream));
+                va.dd_keys = h->d_dd_keys; va.dd_idx = h->d_dd_idx; va.dd_end_bits = (uint32_t)eb; va.dd_nseq = n_seq;
+            }
+        }
+    }
     e = launch_verify<MODE>(ctx, p, va);
     if (e != cudaSuccess) return set_err(ctx, SPMB_ERR_CUDA, "pigeon verify launch", e);
     ctx->launches += 2;
@@ -1370,6 +1490,88 @@ static int enqueue_prefix(spmb_context *ctx, const spmb_store *s, const spmb_pat
     return SPMB_OK;
 }
 
+// the one-lane Myers kernels over the super-tiles [st0, st1) of a store
+static int enqueue_myers_direct(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p, const HitSink &sink,
+                                uint64_t st0, uint64_t st1, uint32_t seq_id, bool row_own)
+{
+    if (p->n_pat > 65535) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "more than 65535 patterns in one Myers set");
+    int rc = store_ensure_lanes(ctx, s);
+    if (rc) return rc;
+    if (s->hi) { rc = store_ensure_lanes(ctx, s->hi); if (rc) return rc; }
+    MyersArgs a;
+    a.lanes = s->lanes;
+    a.lanes_hi = s->hi ? s->hi->lanes : nullptr;
+    a.mul4 = 4;
+    a.eq_stride = (p->NW <= 4 ? 4 : 8) * 4;
+    a.lay = s->lay;
+    a.eq = p->d_eq;
+    a.meta = p->d_meta;
+    a.row_len = s->row_len; a.row_seq = s->row_seq; a.row_own = row_own ? s->row_own : nullptr;
+    a.warm = p->warm;
+    a.seq_id = seq_id;
+    a.st0 = st0; a.st1 = st1;
+    a.sink = sink;
+    cudaError_t e = (s->lay.mode == SPMB_MODE_PLAIN) ? launch_myers<SPMB_MODE_PLAIN>(ctx, s, p, a)
+                                                      : launch_myers<SPMB_MODE_WINDOWS>(ctx, s, p, a);
+    if (e != cudaSuccess) return set_err(ctx, SPMB_ERR_CUDA, "myers_kernel launch", e);
+    return SPMB_OK;
+}
+
+template <int MODE>
+static cudaError_t launch_chain_verify(spmb_context *ctx, int wpl, const ChainArgs &ca)
+{
+    const unsigned grid = (unsigned)ctx->sm_count * 8;
+    switch (wpl) {
+    case 1: myers_chain_verify_kernel<1, MODE><<<grid, 128, 0, ctx->stream>>>(ca); break;
+    case 2: myers_chain_verify_kernel<2, MODE><<<grid, 128, 0, ctx->stream>>>(ca); break;
+    case 4: myers_chain_verify_kernel<4, MODE><<<grid, 128, 0, ctx->stream>>>(ca); break;
+    case 8: myers_chain_verify_kernel<8, MODE><<<grid, 128, 0, ctx->stream>>>(ca); break;
+    default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
+// needles longer than 256 symbols (myers_chain.cuh): the one-lane kernels search their 256-symbol prefixes into the
+// candidate buffer, one warp per candidate then runs the whole needle with its words chained across the lanes
+static int enqueue_chain(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p, spmb_hits *h,
+                         uint64_t st0, uint64_t st1, uint32_t seq_id, const HitSink &sink)
+{
+    if (st1 <= st0) return SPMB_OK;
+    int rc = cand_reserve(ctx, h, 1ull << 16);
+    if (rc) return rc;
+    CU(cudaMemsetAsync(h->d_count + 1, 0, sizeof(unsigned long long), ctx->stream));
+    const uint64_t per_st = 32ull * s->lay.row_len;
+    // a hit owned by this shard hangs on the prefix occurrence that ends m - 256 symbols before it
+    uint64_t f0 = st0;
+    if (s->lay.mode == SPMB_MODE_PLAIN && st0 > 0) {
+        const uint64_t back = ((uint64_t)p->max_m - SPMB_CHAIN_PREFIX + per_st - 1) / per_st;
+        f0 = st0 > back ? st0 - back : 0;
+    }
+    HitSink cand_sink{reinterpret_cast<spmb_hit *>(h->d_cand), h->d_count + 1, h->cand_cap};
+    rc = enqueue_myers_direct(ctx, s, p->long_prefix, cand_sink, f0, st1, seq_id, false);
+    if (rc) return rc;
+    ChainArgs ca;
+    memset(&ca, 0, sizeof(ca));
+    ca.lanes = s->lanes; ca.lay = s->lay;
+    ca.eq = p->d_chain_eq; ca.meta = p->d_chain_meta;
+    ca.cand = reinterpret_cast<const spmb_hit *>(h->d_cand);
+    ca.counters = h->d_count; ca.cand_cap = h->cand_cap;
+    ca.prefix_m = SPMB_CHAIN_PREFIX;
+    ca.row_len = s->row_len; ca.row_own = s->row_own;
+    ca.seq_base = 0;
+    ca.n_needles = p->n_long;
+    ca.seq_id = seq_id;
+    ca.own_lo = st0 * per_st;
+    ca.own_hi = std::min<uint64_t>(s->lay.n, st1 * per_st);
+    ca.sink = sink;
+    ca.seq_base = s->seq_base; // rows of a window bucket carry consecutive window indices: row = seq_id - seq_base
+    cudaError_t e = (s->lay.mode == SPMB_MODE_PLAIN) ? launch_chain_verify<SPMB_MODE_PLAIN>(ctx, p->chain_wpl, ca)
+                                                      : launch_chain_verify<SPMB_MODE_WINDOWS>(ctx, p->chain_wpl, ca);
+    if (e != cudaSuccess) return set_err(ctx, SPMB_ERR_CUDA, "myers_chain_verify_kernel launch", e);
+    ctx->launches++;
+    return SPMB_OK;
+}
+
 static int enqueue_search(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p, spmb_hits *h,
                           bool reset = true, uint32_t seq_id = 0)
 {
@@ -1392,26 +1594,12 @@ static int enqueue_search(spmb_context *ctx, const spmb_store *s, const spmb_pat
     }
     if (p->alg == SPMB_ALG_PIGEONHOLE) return SPMB_OK; // no usable q-gram
     if (p->alg == SPMB_ALG_MYERS || p->alg == SPMB_ALG_MYERS_FILTERED) {
-        if (p->n_pat > 65535) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "more than 65535 patterns in one Myers set");
-        int rc = store_ensure_lanes(ctx, s);
-        if (rc) return rc;
-        if (s->hi) { rc = store_ensure_lanes(ctx, s->hi); if (rc) return rc; }
-        MyersArgs a;
-        a.lanes = s->lanes;
-        a.lanes_hi = s->hi ? s->hi->lanes : nullptr;
-        a.mul4 = 4;
-        a.eq_stride = (p->NW <= 4 ? 4 : 8) * 4;
-        a.lay = s->lay;
-        a.eq = p->d_eq;
-        a.meta = p->d_meta;
-        a.row_len = s->row_len; a.row_seq = s->row_seq; a.row_own = s->row_own;
-        a.warm = p->warm;
-        a.seq_id = seq_id;
-        a.st0 = st0; a.st1 = st1;
-        a.sink = sink;
-        cudaError_t e = (s->lay.mode == SPMB_MODE_PLAIN) ? launch_myers<SPMB_MODE_PLAIN>(ctx, s, p, a)
-                                                          : launch_myers<SPMB_MODE_WINDOWS>(ctx, s, p, a);
-        if (e != cudaSuccess) return set_err(ctx, SPMB_ERR_CUDA, "myers_kernel launch", e);
+        if (p->subs.empty() && !p->long_prefix) return enqueue_myers_direct(ctx, s, p, sink, st0, st1, seq_id, true);
+        for (const spmb_pattern *c : p->subs) {
+            int rc = enqueue_myers_direct(ctx, s, c, sink, st0, st1, seq_id, true);
+            if (rc) return rc;
+        }
+        if (p->long_prefix) return enqueue_chain(ctx, s, p, h, st0, st1, seq_id, sink);
         return SPMB_OK;
     }
     // exact searchers (Horspool and Shift-Or share the bit-sliced kernel)
@@ -2065,6 +2253,7 @@ static int jst_prepare(spmb_context *ctx, spmb_jst *j, uint32_t W)
             b.first = first; b.count = count;
             int rc = store_alloc(ctx, rows * RL, RL, SPMB_MODE_WINDOWS, &b.store);
             if (rc) { cudaEventDestroy(e0); cudaEventDestroy(e1); return rc; }
+            b.store->seq_base = (uint32_t)first;
             j->buckets.push_back(b);
             std::vector<uint32_t> rl(rows, 0), ro(rows, 0), rs(rows, 0);
             for (uint64_t r = 0; r < count; ++r) {
@@ -2111,7 +2300,7 @@ static int jst_enqueue(spmb_context *ctx, spmb_jst *j, const spmb_pattern *p, sp
     // and the buckets of a few long windows fill a fraction of the device for tens of microseconds each (C4: the
     // scan + 4 of 7 buckets, 190 of 1010 us): the direct kernels only share the hit sink (atomics), so those
     // launches go to a second stream beside the large buckets.
-    const bool direct = !p->filtered && p->alg != SPMB_ALG_PIGEONHOLE && p->alg != SPMB_ALG_MYERS_PREFIX &&
+    const bool direct = !p->filtered && !p->long_prefix && p->alg != SPMB_ALG_PIGEONHOLE && p->alg != SPMB_ALG_MYERS_PREFIX &&
                         ctx->aux_stream && !j->buckets.empty() && !getenv("SPMB_JST_SERIAL");
     cudaStream_t main_stream = ctx->stream;
     if (!direct) {
@@ -2272,6 +2461,12 @@ extern "C" int spmb_stream_destroy(spmb_stream *st)
 {
     if (!st) return SPMB_OK;
     if (st->ctx) { cudaSetDevice(st->ctx->device); cudaStreamSynchronize(st->ctx->stream); }
+    // chunks handed in but never collected: their upload jobs still write into this stream's buffers
+    for (int i = 0, si = st->next_collect; i < 2; ++i, si ^= 1)
+        if (st->slot[si].busy && st->slot[si].job && st->ctx && st->ctx->upload) {
+            st->ctx->upload->wait(st->slot[si].job_seq, st->ctx->stream, true, nullptr);
+            st->slot[si].job = false;
+        }
     for (int i = 0; i < 2; ++i) {
         stream_slot_release(st, i);
         if (st->slot[i].d_words && st->ctx) big_free(st->ctx, st->slot[i].d_words, st->slot[i].words_bytes);
@@ -2311,8 +2506,10 @@ static int stream_feed_prefix(spmb_context *ctx, spmb_stream *st, const uint8_t 
     return SPMB_OK;
 }
 
-// enqueue one chunk: [device tail | chunk] -> lane-chunk words -> store -> search kernels -> new tail.  Returns when
-// the host buffer has been consumed; the hits are fetched by spmb_stream_collect.
+// hand one chunk in.  The bulk of a long chunk goes to the upload pool as an asynchronous job (the packing threads
+// and the copy engine start on it at once and run on into the next chunk's job); everything that depends on the
+// previous chunk's state -- [device tail | chunk] -> store -> search kernels -> new tail -- is enqueued by
+// spmb_stream_collect, in order.  The host buffer must stay valid until that chunk has been collected.
 extern "C" int spmb_stream_submit(spmb_context *ctx, spmb_stream *st, const uint8_t *host_ranks, uint64_t n)
 {
     if (!ctx || !st || (!host_ranks && n)) return SPMB_ERR_ARG;
@@ -2321,11 +2518,9 @@ extern "C" int spmb_stream_submit(spmb_context *ctx, spmb_stream *st, const uint
     const int si = st->next_submit;
     spmb_stream::Slot &S = st->slot[si];
     if (S.busy) return set_err(ctx, SPMB_ERR_ARG, "two chunks are in flight: collect one first");
-    cudaStream_t sm = ctx->stream;
     const uint64_t t = st->tail_len, total = t + n;
     S.t = t; S.n = n; S.total = total; S.launches = 0;
-    st->next_submit ^= 1;
-    S.busy = true;
+    S.job = false; S.host = nullptr; S.bulk = 0; S.a = 0;
     S.empty = (total == 0 || st->pat->max_m == 0);
     // host mirror of the tail (serialised by capture(); the searches never read it)
     {
@@ -2339,53 +2534,73 @@ extern "C" int spmb_stream_submit(spmb_context *ctx, spmb_stream *st, const uint
         }
         for (auto &c : ht) c &= 3;
     }
-    if (total == 0) { st->offset += n; return SPMB_OK; }
-    const uint32_t launches0 = ctx->launches;
-    // ---- [tail | chunk] as lane-chunk words ----
-    const size_t words = (size_t)((total + 31) / 32) + 2;
-    if (words * sizeof(uint2) > S.words_bytes) {
-        if (S.d_words) big_free(ctx, S.d_words, S.words_bytes);
-        S.d_words = nullptr; S.words_bytes = 0;
-        const size_t want = words * sizeof(uint2) + (words * sizeof(uint2)) / 8;
-        CU(big_alloc(ctx, want, (void **)&S.d_words));
-        S.words_bytes = want;
+    if (total) {
+        // ---- room for [tail | chunk] as lane-chunk words ----
+        const size_t words = (size_t)((total + 31) / 32) + 2;
+        if (words * sizeof(uint2) > S.words_bytes) {
+            if (S.d_words) big_free(ctx, S.d_words, S.words_bytes);
+            S.d_words = nullptr; S.words_bytes = 0;
+            const size_t want = words * sizeof(uint2) + (words * sizeof(uint2)) / 8;
+            CU(big_alloc(ctx, want, (void **)&S.d_words));
+            S.words_bytes = want;
+            CU(cudaStreamSynchronize(ctx->stream)); // the movers' streams may touch a fresh stream-ordered block only now
+        }
+        uint64_t a = (32 - (t & 31u)) & 31u; // symbols that complete the tail's partial word
+        if (a > n) a = n;
+        S.a = (uint32_t)a;
+        memset(&S.hd, 0, sizeof(S.hd));
+        if (a) memcpy(S.hd.sym, host_ranks, (size_t)a);
+        S.bulk = n - a;
+        S.host = host_ranks + a;
+        if (S.bulk >= UploadPool::env_u64("SPMB_UPLOAD_MIN", 32ull << 20) && ensure_upload(ctx) == SPMB_OK) {
+            // cut fine enough that every mover gets several chunks of this feed
+            const uint64_t movers = (uint64_t)ctx->upload->n_workers + 1;
+            uint64_t chunk = S.bulk / (8 * movers);
+            if (chunk < (256u << 10)) chunk = 256u << 10;
+            if (!ctx->upload->submit_text(S.host, S.bulk, S.d_words + (t + a) / 32, chunk, &S.job_seq))
+                return set_err(ctx, SPMB_ERR_CUDA, "stream upload: job ring full");
+            S.job = true;
+        }
     }
-    if (t) CU(cudaMemcpyAsync(S.d_words, st->d_tail, ((size_t)(t + 31) / 32) * sizeof(uint2), cudaMemcpyDeviceToDevice, sm));
-    uint64_t a = (32 - (t & 31u)) & 31u; // symbols that complete the tail's partial word
-    if (a > n) a = n;
-    if (a) {
-        StreamHead hd;
-        memset(&hd, 0, sizeof(hd));
-        memcpy(hd.sym, host_ranks, (size_t)a);
-        stream_head_kernel<<<1, 32, 0, sm>>>(S.d_words, t, hd, (uint32_t)a);
-        ctx->launches++;
-    }
-    const uint64_t bulk = n - a;
-    uint2 *dst = S.d_words + (t + a) / 32;
-    if (bulk >= UploadPool::env_u64("SPMB_UPLOAD_MIN", 32ull << 20) && ensure_upload(ctx) == SPMB_OK) {
-        // both movers of the upload queue, cut fine enough that every mover gets several chunks of this feed
-        const uint64_t movers = (uint64_t)ctx->upload->n_workers + 1;
-        uint64_t chunk = bulk / (4 * movers);
-        if (chunk < (256u << 10)) chunk = 256u << 10;
-        cudaError_t e = ctx->upload->run(host_ranks + a, bulk, dst, sm, &ctx->launches, chunk);
-        if (e != cudaSuccess) { cudaGetLastError(); S.busy = false; return set_err(ctx, SPMB_ERR_CUDA, "stream upload", e); }
-    } else if (bulk) {
-        if (bulk > S.raw_bytes) {
+    st->next_submit ^= 1;
+    S.busy = true;
+    st->tail_len = (uint32_t)std::min<uint64_t>(st->keep, total);
+    st->offset += n;
+    return SPMB_OK;
+}
+
+// the device side of the oldest chunk in flight, in stream order behind the previous chunk's
+static int stream_enqueue(spmb_context *ctx, spmb_stream *st, spmb_stream::Slot &S)
+{
+    cudaStream_t sm = ctx->stream;
+    const uint64_t t = S.t, total = S.total;
+    ctx->launches = 0;
+    if (S.job) {
+        cudaError_t e = ctx->upload->wait(S.job_seq, sm, false, &ctx->launches);
+        S.job = false;
+        if (e != cudaSuccess) { cudaGetLastError(); return set_err(ctx, SPMB_ERR_CUDA, "stream upload", e); }
+    } else if (S.bulk) {
+        if (S.bulk > S.raw_bytes) {
             cudaFree(S.d_raw);
             S.d_raw = nullptr; S.raw_bytes = 0;
-            CU(cudaMalloc(&S.d_raw, bulk + bulk / 8 + 64));
-            S.raw_bytes = bulk + bulk / 8 + 64;
+            CU(cudaMalloc(&S.d_raw, S.bulk + S.bulk / 8 + 64));
+            S.raw_bytes = S.bulk + S.bulk / 8 + 64;
         }
-        CU(cudaMemcpyAsync(S.d_raw, host_ranks + a, bulk, cudaMemcpyHostToDevice, sm));
-        const uint64_t groups = (bulk + 31) / 32;
-        bytes_to_chunks_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, sm>>>(S.d_raw, bulk, dst);
+        CU(cudaMemcpyAsync(S.d_raw, S.host, S.bulk, cudaMemcpyHostToDevice, sm));
+        const uint64_t groups = (S.bulk + 31) / 32;
+        bytes_to_chunks_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, sm>>>(S.d_raw, S.bulk, S.d_words + (t + S.a) / 32);
         ctx->launches++;
         CU(cudaGetLastError());
+    }
+    if (t) CU(cudaMemcpyAsync(S.d_words, st->d_tail, ((size_t)(t + 31) / 32) * sizeof(uint2), cudaMemcpyDeviceToDevice, sm));
+    if (S.a) {
+        stream_head_kernel<<<1, 32, 0, sm>>>(S.d_words, t, S.hd, S.a);
+        ctx->launches++;
     }
     // ---- the words as a store (planes for the exact kernel, lane chunks for the others) ----
     if (S.store) { spmb_store_destroy(S.store); S.store = nullptr; }
     int rc = store_alloc(ctx, total, 0, SPMB_MODE_PLAIN, &S.store);
-    if (rc) { S.busy = false; return rc; }
+    if (rc) return rc;
     {
         uint2 *l = nullptr;
         const bool want_lanes = !(st->pat->alg == SPMB_ALG_HORSPOOL || st->pat->alg == SPMB_ALG_SHIFTOR);
@@ -2396,30 +2611,20 @@ extern "C" int spmb_stream_submit(spmb_context *ctx, spmb_stream *st, const uint
         ctx->launches++;
         CU(cudaGetLastError());
     }
-    // ---- the state for the next feed ----
+    // ---- the state for the next chunk ----
     const uint32_t nk = (uint32_t)std::min<uint64_t>(st->keep, total);
     if (nk) {
         stream_carry_kernel<<<(nk / 32 + 1 + 63) / 64, 64, 0, sm>>>(S.d_words, total, nk, st->d_tail);
         ctx->launches++;
         CU(cudaGetLastError());
     }
-    st->tail_len = nk;
-    st->offset += n;
-    const uint32_t pre = ctx->launches - launches0;
-    // ---- search ----
+    const uint32_t pre = ctx->launches;
     if (!S.empty) {
         rc = spmb_search_launch(ctx, S.store, st->pat, S.hits); // resets ctx->launches
         ctx->launches += pre;
-        if (rc) { S.busy = false; return rc; }
+        if (rc) return rc;
     }
     S.launches = ctx->launches;
-    // the pageable / pinned host chunk of the small path must have left before we return
-    if (bulk && bulk < UploadPool::env_u64("SPMB_UPLOAD_MIN", 32ull << 20)) {
-        // cudaMemcpyAsync from pageable memory returns after staging; a pinned source needs the copy to finish
-        cudaPointerAttributes at;
-        if (cudaPointerGetAttributes(&at, host_ranks) == cudaSuccess && at.type == cudaMemoryTypeHost) CU(cudaStreamSynchronize(sm));
-        else cudaGetLastError();
-    }
     return SPMB_OK;
 }
 
@@ -2438,7 +2643,8 @@ extern "C" int spmb_stream_collect(spmb_context *ctx, spmb_stream *st, spmb_hits
     h->view = nullptr;
     h->pend_store = nullptr; h->pend_pat = nullptr;
     int rc = SPMB_OK;
-    if (!S.empty) {
+    if (S.total) rc = stream_enqueue(ctx, st, S);
+    if (rc == SPMB_OK && !S.empty) {
         rc = spmb_search_finish(ctx, S.hits);
         if (rc == SPMB_OK) {
             const spmb_hit *d = spmb_hits_data(S.hits);
@@ -2449,6 +2655,14 @@ extern "C" int spmb_stream_collect(spmb_context *ctx, spmb_stream *st, spmb_hits
                 if (d[i].end > S.t) { spmb_hit x = d[i]; x.end -= S.t; h->host.push_back(x); }
             h->count = h->host.size();
         }
+    } else if (rc == SPMB_OK && S.total) {
+        // nothing to search for, but the caller's buffer must have left before we return
+        cudaError_t e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess) rc = set_err(ctx, SPMB_ERR_CUDA, "stream sync", e);
+    }
+    if (rc != SPMB_OK && S.job) { // leave no job of a failed chunk behind
+        ctx->upload->wait(S.job_seq, ctx->stream, true, nullptr);
+        S.job = false;
     }
     ctx->launches = S.launches;
     stream_slot_release(st, si);
@@ -2473,18 +2687,33 @@ static int stream_errors(spmb_stream *st, std::vector<uint32_t> &err)
     if (!(p->alg == SPMB_ALG_MYERS || p->alg == SPMB_ALG_MYERS_FILTERED) || p->NW == 0) return SPMB_OK;
     spmb_context *ctx = st->ctx;
     ENTER(ctx);
-    StreamScoreArgs a{st->d_tail, st->tail_len, p->d_eq, p->d_meta, p->n_pat, st->d_err};
-    const unsigned grid = (p->n_pat + 63) / 64;
-    switch (p->NW) {
-    case 1: stream_score_kernel<1><<<grid, 64, 0, ctx->stream>>>(a); break;
-    case 2: stream_score_kernel<2><<<grid, 64, 0, ctx->stream>>>(a); break;
-    case 3: stream_score_kernel<3><<<grid, 64, 0, ctx->stream>>>(a); break;
-    case 4: stream_score_kernel<4><<<grid, 64, 0, ctx->stream>>>(a); break;
-    case 5: stream_score_kernel<5><<<grid, 64, 0, ctx->stream>>>(a); break;
-    case 6: stream_score_kernel<6><<<grid, 64, 0, ctx->stream>>>(a); break;
-    case 7: stream_score_kernel<7><<<grid, 64, 0, ctx->stream>>>(a); break;
-    case 8: stream_score_kernel<8><<<grid, 64, 0, ctx->stream>>>(a); break;
-    default: return set_err(ctx, SPMB_ERR_UNSUPPORTED, "stream score: needle too long");
+    CU(cudaMemsetAsync(st->d_err, 0, p->n_pat * sizeof(uint32_t), ctx->stream)); // empty needles of a bucketed set
+    std::vector<const spmb_pattern *> sets(p->subs.begin(), p->subs.end());
+    if (sets.empty() && !p->long_prefix) sets.push_back(p);
+    for (const spmb_pattern *q : sets) {
+        StreamScoreArgs a{st->d_tail, st->tail_len, q->d_eq, q->d_meta, q->n_pat, st->d_err};
+        const unsigned grid = (q->n_pat + 63) / 64;
+        switch (q->NW) {
+        case 1: stream_score_kernel<1><<<grid, 64, 0, ctx->stream>>>(a); break;
+        case 2: stream_score_kernel<2><<<grid, 64, 0, ctx->stream>>>(a); break;
+        case 3: stream_score_kernel<3><<<grid, 64, 0, ctx->stream>>>(a); break;
+        case 4: stream_score_kernel<4><<<grid, 64, 0, ctx->stream>>>(a); break;
+        case 5: stream_score_kernel<5><<<grid, 64, 0, ctx->stream>>>(a); break;
+        case 6: stream_score_kernel<6><<<grid, 64, 0, ctx->stream>>>(a); break;
+        case 7: stream_score_kernel<7><<<grid, 64, 0, ctx->stream>>>(a); break;
+        case 8: stream_score_kernel<8><<<grid, 64, 0, ctx->stream>>>(a); break;
+        default: return set_err(ctx, SPMB_ERR_UNSUPPORTED, "stream score: needle too long");
+        }
+    }
+    if (p->long_prefix) { // needles longer than 256 symbols: one warp each
+        StreamScoreArgs a{st->d_tail, st->tail_len, p->d_chain_eq, p->d_chain_meta, p->n_long, st->d_err};
+        const unsigned grid = (p->n_long + 3) / 4;
+        switch (p->chain_wpl) {
+        case 1: stream_score_chain_kernel<1><<<grid, 128, 0, ctx->stream>>>(a); break;
+        case 2: stream_score_chain_kernel<2><<<grid, 128, 0, ctx->stream>>>(a); break;
+        case 4: stream_score_chain_kernel<4><<<grid, 128, 0, ctx->stream>>>(a); break;
+        default: stream_score_chain_kernel<8><<<grid, 128, 0, ctx->stream>>>(a); break;
+        }
     }
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(err.data(), st->d_err, p->n_pat * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));

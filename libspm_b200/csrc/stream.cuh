@@ -9,6 +9,7 @@
 #include "layout.cuh"
 #include "pack.cuh"
 #include "pigeon.cuh"
+#include "myers_chain.cuh"
 
 // up to 31 symbols passed by value: they complete the partial word at the end of the carried tail
 struct StreamHead {
@@ -77,7 +78,7 @@ __global__ void stream_score_kernel(StreamScoreArgs a)
     const uint32_t pid = blockIdx.x * blockDim.x + threadIdx.x;
     if (pid >= a.n_pat) return;
     const MyersPatMeta pm = a.meta[pid];
-    if (pm.m == 0) { a.out[pid] = 0; return; }
+    if (pm.m == 0) { a.out[pm.pattern_id] = 0; return; }
     const uint32_t *eqp = a.eq + (size_t)pid * 4 * NWP;
     uint32_t vp[NW], vn[NW];
 #pragma unroll
@@ -94,5 +95,41 @@ __global__ void stream_score_kernel(StreamScoreArgs a)
         pg_myers_col<NW, false>(vp, vn, eq, hp, hn);
         score += pg_score_delta<NW>(hp, hn, pm.m);
     }
-    a.out[pid] = (uint32_t)score;
+    a.out[pm.pattern_id] = (uint32_t)score; // the caller's pattern id (children of a bucketed set: spmb_capi.cu)
+}
+
+// the same for needles longer than 256 symbols: one warp per needle, words chained across the lanes (myers_chain.cuh)
+template <int WPL>
+__global__ void __launch_bounds__(128) stream_score_chain_kernel(StreamScoreArgs a)
+{
+    constexpr uint32_t NWT = 32 * WPL;
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t ci = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (ci >= a.n_pat) return; // warp-uniform
+    const MyersPatMeta pm = a.meta[ci];
+    const uint32_t *eqp = a.eq + (size_t)ci * 4 * NWT + lane * WPL;
+    const uint32_t top = (pm.m - 1) >> 5;
+    const bool owner = (top / WPL) == lane;
+    const uint32_t ow = top % WPL, ob = (pm.m - 1) & 31u;
+    uint32_t vp[WPL], vn[WPL];
+#pragma unroll
+    for (int w = 0; w < WPL; ++w) { vp[w] = 0xffffffffu; vn[w] = 0; }
+    int score = (int)pm.m;
+    const uint32_t span = min(a.tail_len, 2u * pm.m);
+    for (uint32_t t = a.tail_len - span; t < a.tail_len; ++t) {
+        const uint2 wv = a.tail[t >> 5];
+        const uint32_t j = t & 31u;
+        const uint32_t word = j < 16 ? wv.x : wv.y;
+        const uint32_t c = (word >> (30 - 2 * (j & 15u))) & 3u;
+        uint32_t eq[WPL], hp[WPL], hn[WPL];
+#pragma unroll
+        for (int w = 0; w < WPL; ++w) eq[w] = __ldg(eqp + c * NWT + w);
+        myers_chain_step<WPL>(vp, vn, eq, lane, hp, hn);
+        uint32_t hpw = hp[0], hnw = hn[0];
+#pragma unroll
+        for (int w = 1; w < WPL; ++w)
+            if ((uint32_t)w == ow) { hpw = hp[w]; hnw = hn[w]; }
+        score += (int)((hpw >> ob) & 1u) - (int)((hnw >> ob) & 1u);
+    }
+    if (owner) a.out[pm.pattern_id] = (uint32_t)score;
 }

@@ -132,15 +132,42 @@ static inline int spmb_host_cpus()
 // knobs (environment, read once per context): SPMB_HOST_THREADS = packing threads (0 = raw only;
 // default: available cpus - 1, at most 31), SPMB_UPLOAD_CHUNK = symbols per chunk (default 4 Mi),
 // SPMB_UPLOAD_MIN = shortest haystack that takes this path (default 32 Mi symbols)
+//
+// Jobs are ASYNCHRONOUS (round 2): submit_*() puts a job into a ring and returns; the packing threads and one raw-mover
+// thread (which feeds the copy engine from the head of the chunk queue) take the jobs in order and move on to the
+// next job the moment the current one has no chunk left to claim -- a stream of feeds (spmb_stream_submit) keeps every
+// mover busy across feed boundaries instead of ramping the pool up and down per feed (measured before: 64 Mi-symbol
+// feeds at 0.53 of the one-shot rate).  wait() blocks until every copy of the job has been ENQUEUED, makes the caller's
+// stream wait for the movers' events, and (host_sync) for the copies themselves.  The source buffer of a job must
+// stay valid until its wait() returned.
 struct UploadPool {
-    enum { SLOTS = 4 };
+    enum { SLOTS = 4, RING = 4 };
     int device = 0;
     uint64_t chunk_sym = 4ull << 20;            // capacity of a staging buffer, and the chunk size of one-shot uploads
-    uint64_t job_chunk = 4ull << 20;            // chunk size of the current text job (<= chunk_sym; stream feeds use smaller ones)
+    uint64_t job_chunk = 4ull << 20;            // chunk size of the last text job (<= chunk_sym; stream feeds use smaller ones)
     uint64_t min_sym = 32ull << 20;
     int n_workers = 0;
     bool trace = false;                         // SPMB_UPLOAD_TRACE=1: per-job timings on stderr
     uint64_t raw_pct_text = 100, raw_pct_events = 10; // SPMB_UPLOAD_RAW_PCT / SPMB_EVENT_RAW_PCT: most chunks (in %) the copy engine may take raw
+    uint64_t spin_us = 200;                     // SPMB_UPLOAD_IDLE_SPIN_US: an idle mover polls this long for the next job before it sleeps
+
+    struct Job {
+        const uint8_t *src = nullptr;           // text job
+        uint2 *d_chunks = nullptr;
+        const spmb_journal_event *ev_src = nullptr; // events job (src == nullptr)
+        spmb_journal_event *d_ev = nullptr;
+        uint64_t n = 0, n_chunks = 0, chunk = 0, ev_pool_len = 0, raw_pct = 100;
+        std::atomic<uint64_t> ends{0};          // head << 32 | tail: chunks [head, tail) are unclaimed
+        std::atomic<int> cuda_err{0};
+        std::atomic<uint64_t> packed_chunks{0}, unpackable_chunks{0}, raw_chunks{0};
+        std::atomic<uint32_t> launches{0};
+        int movers_left = 0;                    // guarded by mu
+        bool issued = false;                    // guarded by mu: every mover has left the job, all its copies are enqueued
+        std::chrono::steady_clock::time_point t_submit;
+    };
+    Job jobs[RING];
+    std::atomic<uint64_t> submitted{0};         // jobs handed in so far; job s lives in jobs[s % RING]
+    uint64_t retired = 0;                       // jobs waited for (in order)
 
     struct Worker {
         std::thread th;
@@ -149,30 +176,21 @@ struct UploadPool {
         uint8_t *d_slot[2] = {nullptr, nullptr};   // device landing area of a packed event chunk
         cudaEvent_t ev[2] = {nullptr, nullptr};
         bool used[2] = {false, false};
+        cudaEvent_t job_ev[RING] = {nullptr, nullptr, nullptr, nullptr}; // behind this mover's last copy of a job
     };
     std::vector<Worker> workers;
+    // the raw mover: staging slots on the device, its own stream
+    std::thread raw_th;
+    cudaStream_t raw_stream = nullptr;
     uint8_t *d_slot[SLOTS] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t slot_ev[SLOTS] = {nullptr, nullptr, nullptr, nullptr};
+    bool slot_used[SLOTS] = {false, false, false, false};
+    cudaEvent_t raw_job_ev[RING] = {nullptr, nullptr, nullptr, nullptr};
     bool ready = false;
 
-    // job state
     std::mutex mu;
     std::condition_variable cv_job, cv_done;
-    uint64_t gen = 0;
     bool quit = false;
-    int running = 0;
-    const uint8_t *src = nullptr;
-    uint64_t n = 0, n_chunks = 0;
-    uint2 *d_chunks = nullptr;
-    const spmb_journal_event *ev_src = nullptr; // events job (src == nullptr)
-    spmb_journal_event *d_ev = nullptr;
-    uint64_t ev_chunk = 0;                      // events per chunk
-    uint64_t ev_pool_len = 0;
-    std::atomic<uint64_t> ends{0};  // head << 32 | tail: chunks [head, tail) are unclaimed
-    std::atomic<int> cuda_err{0};
-    std::atomic<uint64_t> packed_chunks{0};
-    std::atomic<uint64_t> unpackable_chunks{0};
-    std::atomic<uint32_t> worker_launches{0};
     uint64_t last_ev_raw = 0, last_ev_packed = 0, last_ev_chunk = 0;
     // figures of the last upload (spmb_upload_last_stats)
     uint64_t last_raw = 0, last_packed = 0;
@@ -186,22 +204,22 @@ struct UploadPool {
         return end && end != v ? (uint64_t)x : dflt;
     }
 
-    bool claim_head(uint64_t &idx)
+    static bool claim_head(Job &J, uint64_t &idx)
     {
-        uint64_t v = ends.load(std::memory_order_relaxed);
+        uint64_t v = J.ends.load(std::memory_order_relaxed);
         for (;;) {
             const uint64_t h = v >> 32, t = v & 0xffffffffull;
             if (h >= t) return false;
-            if (ends.compare_exchange_weak(v, ((h + 1) << 32) | t, std::memory_order_acq_rel)) { idx = h; return true; }
+            if (J.ends.compare_exchange_weak(v, ((h + 1) << 32) | t, std::memory_order_acq_rel)) { idx = h; return true; }
         }
     }
-    bool claim_tail(uint64_t &idx)
+    static bool claim_tail(Job &J, uint64_t &idx)
     {
-        uint64_t v = ends.load(std::memory_order_relaxed);
+        uint64_t v = J.ends.load(std::memory_order_relaxed);
         for (;;) {
             const uint64_t h = v >> 32, t = v & 0xffffffffull;
             if (h >= t) return false;
-            if (ends.compare_exchange_weak(v, (h << 32) | (t - 1), std::memory_order_acq_rel)) { idx = t - 1; return true; }
+            if (J.ends.compare_exchange_weak(v, (h << 32) | (t - 1), std::memory_order_acq_rel)) { idx = t - 1; return true; }
         }
     }
 
@@ -215,6 +233,7 @@ struct UploadPool {
         if (chunk_sym < 1024) chunk_sym = 1024;
         min_sym = env_u64("SPMB_UPLOAD_MIN", min_sym);
         trace = env_u64("SPMB_UPLOAD_TRACE", 0) != 0;
+        spin_us = env_u64("SPMB_UPLOAD_IDLE_SPIN_US", spin_us);
         // SPMB_UPLOAD_SPIN=0: threads sleep while they wait for a slot instead of polling
         const unsigned ev_flags = cudaEventDisableTiming | (env_u64("SPMB_UPLOAD_SPIN", 1) ? 0u : (unsigned)cudaEventBlockingSync);
         int dflt = spmb_host_cpus() - 1;
@@ -223,11 +242,12 @@ struct UploadPool {
         n_workers = (int)env_u64("SPMB_HOST_THREADS", (uint64_t)dflt);
         if (threads_override >= 0) n_workers = threads_override; // spmb_context_set_upload_threads
         if (n_workers > 256) n_workers = 256;
-        cudaError_t e = cudaSuccess;
+        cudaError_t e = cudaStreamCreateWithFlags(&raw_stream, cudaStreamNonBlocking);
         for (int s = 0; s < SLOTS && e == cudaSuccess; ++s) {
             e = cudaMalloc(&d_slot[s], chunk_sym);
             if (e == cudaSuccess) e = cudaEventCreateWithFlags(&slot_ev[s], ev_flags);
         }
+        for (int r = 0; r < RING && e == cudaSuccess; ++r) e = cudaEventCreateWithFlags(&raw_job_ev[r], cudaEventDisableTiming);
         workers.resize(n_workers);
         for (int w = 0; w < n_workers && e == cudaSuccess; ++w) {
             Worker &W = workers[w];
@@ -237,221 +257,276 @@ struct UploadPool {
                 if (e == cudaSuccess) e = cudaMalloc(&W.d_slot[b], chunk_sym / 4);
                 if (e == cudaSuccess) e = cudaEventCreateWithFlags(&W.ev[b], ev_flags);
             }
+            for (int r = 0; r < RING && e == cudaSuccess; ++r) e = cudaEventCreateWithFlags(&W.job_ev[r], cudaEventDisableTiming);
         }
         if (e != cudaSuccess) return e;
-        for (int w = 0; w < n_workers; ++w) workers[w].th = std::thread([this, w] { worker_main(w); });
+        for (int w = 0; w < n_workers; ++w) workers[w].th = std::thread([this, w] { mover_main(w); });
+        raw_th = std::thread([this] { mover_main(-1); });
         ready = true;
         return cudaSuccess;
     }
 
-    void worker_main(int w)
+    // wait for job `seq` to be submitted (a short poll first: a stream of feeds hands in the next job within
+    // microseconds, and a condition-variable wake-up costs 30-60 us per mover and feed); false = quit
+    bool next_job(uint64_t seq)
     {
-        Worker &W = workers[w];
+        if (submitted.load(std::memory_order_acquire) > seq) return true;
+        const auto t0 = std::chrono::steady_clock::now();
+        while (std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t0).count() < (long long)spin_us) {
+            if (submitted.load(std::memory_order_acquire) > seq) return true;
+#if defined(__x86_64__)
+            __builtin_ia32_pause();
+#endif
+        }
+        std::unique_lock<std::mutex> lk(mu);
+        cv_job.wait(lk, [&] { return quit || submitted.load(std::memory_order_acquire) > seq; });
+        return !quit || submitted.load(std::memory_order_acquire) > seq;
+    }
+
+    void leave_job(Job &J)
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        if (--J.movers_left == 0) { J.issued = true; cv_done.notify_all(); }
+    }
+
+    // w >= 0: packing thread w (claims from the tail); w < 0: the raw mover (claims from the head)
+    void mover_main(int w)
+    {
         cudaSetDevice(device);
-        uint64_t seen = 0;
-        for (;;) {
-            {
-                std::unique_lock<std::mutex> lk(mu);
-                cv_job.wait(lk, [&] { return quit || gen != seen; });
-                if (quit) return;
-                seen = gen;
-            }
-            int b = 0;
-            uint64_t idx;
+        auto now = [] { return std::chrono::steady_clock::now(); };
+        auto ns = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point c) {
+            return (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(c - a).count();
+        };
+        int b = 0, s = 0; // next pinned buffer (packing thread) / staging slot (raw mover): carried from job to job
+        for (uint64_t seq = 0;; ++seq) {
+            if (!next_job(seq)) return;
+            Job &J = jobs[seq % RING];
+            const int r = (int)(seq % RING);
             cudaError_t e = cudaSuccess;
-            auto now = [] { return std::chrono::steady_clock::now(); };
-            auto us = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point c) {
-                return (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(c - a).count();
-            };
+            uint64_t idx;
             const auto tw0 = now();
-            uint64_t t_wait = 0, t_pack = 0, t_api = 0;
-            while (e == cudaSuccess && cuda_err.load(std::memory_order_relaxed) == 0 && claim_tail(idx)) {
-                const auto ta = now();
-                if (W.used[b]) e = cudaEventSynchronize(W.ev[b]);
-                const auto tb = now();
-                t_wait += us(ta, tb);
-                if (src) {
-                    const uint64_t p0 = idx * job_chunk;
-                    const uint64_t len = (n - p0 < job_chunk) ? n - p0 : job_chunk;
-                    spmb_host_pack_chunks(src + p0, len, W.pinned[b]);
-                    t_pack += us(tb, now());
-                    if (e == cudaSuccess)
-                        e = cudaMemcpyAsync(d_chunks + p0 / 32, W.pinned[b], (len + 31) / 32 * 8, cudaMemcpyHostToDevice, W.stream);
-                } else {
-                    const uint64_t i0 = idx * ev_chunk;
-                    const uint32_t len = (uint32_t)((n - i0 < ev_chunk) ? n - i0 : ev_chunk);
-                    const bool fits = spmb_host_pack_events(ev_src + i0, len, ev_pool_len, (uint8_t *)W.pinned[b]);
-                    t_pack += us(tb, now());
-                    if (fits) {
+            uint64_t t_wait = 0, t_pack = 0, n_mine = 0;
+            if (w >= 0) {
+                Worker &W = workers[w];
+                while (e == cudaSuccess && J.cuda_err.load(std::memory_order_relaxed) == 0 && claim_tail(J, idx)) {
+                    const auto ta = now();
+                    if (W.used[b]) e = cudaEventSynchronize(W.ev[b]);
+                    const auto tb = now();
+                    t_wait += ns(ta, tb);
+                    if (J.src) {
+                        const uint64_t p0 = idx * J.chunk;
+                        const uint64_t len = (J.n - p0 < J.chunk) ? J.n - p0 : J.chunk;
+                        spmb_host_pack_chunks(J.src + p0, len, W.pinned[b]);
+                        t_pack += ns(tb, now());
                         if (e == cudaSuccess)
-                            e = cudaMemcpyAsync(W.d_slot[b], W.pinned[b], spmb_packed_events_bytes(len), cudaMemcpyHostToDevice, W.stream);
-                        if (e == cudaSuccess) {
-                            expand_events_kernel<<<(len + 255) / 256, 256, 0, W.stream>>>(W.d_slot[b], len, d_ev + i0);
-                            e = cudaGetLastError();
-                            worker_launches.fetch_add(1, std::memory_order_relaxed);
+                            e = cudaMemcpyAsync(J.d_chunks + p0 / 32, W.pinned[b], (len + 31) / 32 * 8, cudaMemcpyHostToDevice, W.stream);
+                    } else {
+                        const uint64_t i0 = idx * J.chunk;
+                        const uint32_t len = (uint32_t)((J.n - i0 < J.chunk) ? J.n - i0 : J.chunk);
+                        const bool fits = spmb_host_pack_events(J.ev_src + i0, len, J.ev_pool_len, (uint8_t *)W.pinned[b]);
+                        t_pack += ns(tb, now());
+                        if (fits) {
+                            if (e == cudaSuccess)
+                                e = cudaMemcpyAsync(W.d_slot[b], W.pinned[b], spmb_packed_events_bytes(len), cudaMemcpyHostToDevice, W.stream);
+                            if (e == cudaSuccess) {
+                                expand_events_kernel<<<(len + 255) / 256, 256, 0, W.stream>>>(W.d_slot[b], len, J.d_ev + i0);
+                                e = cudaGetLastError();
+                                J.launches.fetch_add(1, std::memory_order_relaxed);
+                            }
+                        } else if (e == cudaSuccess) {
+                            e = cudaMemcpyAsync(J.d_ev + i0, J.ev_src + i0, (size_t)len * sizeof(spmb_journal_event), cudaMemcpyHostToDevice, W.stream);
+                            J.unpackable_chunks.fetch_add(1, std::memory_order_relaxed);
                         }
-                    } else if (e == cudaSuccess) {
-                        e = cudaMemcpyAsync(d_ev + i0, ev_src + i0, (size_t)len * sizeof(spmb_journal_event), cudaMemcpyHostToDevice, W.stream);
-                        unpackable_chunks.fetch_add(1, std::memory_order_relaxed);
                     }
+                    if (e == cudaSuccess) e = cudaEventRecord(W.ev[b], W.stream);
+                    W.used[b] = true;
+                    b ^= 1;
+                    ++n_mine;
+                    J.packed_chunks.fetch_add(1, std::memory_order_relaxed);
                 }
-                if (e == cudaSuccess) e = cudaEventRecord(W.ev[b], W.stream);
-                W.used[b] = true;
-                b ^= 1;
-                packed_chunks.fetch_add(1, std::memory_order_relaxed);
+                if (e == cudaSuccess) e = cudaEventRecord(W.job_ev[r], W.stream);
+            } else {
+                while (e == cudaSuccess && J.cuda_err.load(std::memory_order_relaxed) == 0) {
+                    const auto ta = now();
+                    if (slot_used[s]) e = cudaEventSynchronize(slot_ev[s]);
+                    t_wait += ns(ta, now());
+                    // a raw chunk costs the link 3-4x the bytes of a packed one: with packing threads at work the copy
+                    // engine's share is capped (raw_pct of the chunks), or a fast link starves the packed copies
+                    if (n_workers && n_mine * 100 >= J.raw_pct * J.n_chunks) break;
+                    if (e != cudaSuccess || !claim_head(J, idx)) break;
+                    if (J.src) {
+                        const uint64_t p0 = idx * J.chunk;
+                        const uint64_t len = (J.n - p0 < J.chunk) ? J.n - p0 : J.chunk;
+                        e = cudaMemcpyAsync(d_slot[s], J.src + p0, len, cudaMemcpyHostToDevice, raw_stream);
+                        if (e == cudaSuccess) {
+                            const uint64_t groups = (len + 31) / 32;
+                            bytes_to_chunks_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, raw_stream>>>(d_slot[s], len, J.d_chunks + p0 / 32);
+                            e = cudaGetLastError();
+                            J.launches.fetch_add(1, std::memory_order_relaxed);
+                        }
+                    } else {
+                        const uint64_t i0 = idx * J.chunk;
+                        const uint64_t len = (J.n - i0 < J.chunk) ? J.n - i0 : J.chunk;
+                        e = cudaMemcpyAsync(J.d_ev + i0, J.ev_src + i0, len * sizeof(spmb_journal_event), cudaMemcpyHostToDevice, raw_stream);
+                    }
+                    if (e == cudaSuccess) e = cudaEventRecord(slot_ev[s], raw_stream);
+                    slot_used[s] = true;
+                    s = (s + 1) % SLOTS;
+                    ++n_mine;
+                }
+                J.raw_chunks.store(n_mine);
+                if (e == cudaSuccess) e = cudaEventRecord(raw_job_ev[r], raw_stream);
             }
-            const auto tc = now();
-            if (e == cudaSuccess) e = cudaStreamSynchronize(W.stream);
-            if (trace) {
-                t_api = us(tw0, tc) - t_wait - t_pack;
-                fprintf(stderr, "[spmb upload] worker %d: total %.2f ms  pack %.2f  wait-slot %.2f  api %.2f  drain %.2f\n", w,
-                        us(tw0, now()) / 1e6, t_pack / 1e6, t_wait / 1e6, t_api / 1e6, us(tc, now()) / 1e6);
+            if (e != cudaSuccess) { // stop the other movers early: nothing left to claim
+                J.cuda_err.store((int)e);
+                J.ends.store(0);
             }
-            W.used[0] = W.used[1] = false;
-            if (e != cudaSuccess) cuda_err.store((int)e);
-            {
-                std::lock_guard<std::mutex> lk(mu);
-                if (--running == 0) cv_done.notify_all();
-            }
+            if (trace)
+                fprintf(stderr, "[spmb upload] job %llu mover %d: %llu chunks  total %.3f ms  pack %.3f  wait-slot %.3f  (since submit %.3f)\n",
+                        (unsigned long long)seq, w, (unsigned long long)n_mine, ns(tw0, now()) / 1e6, t_pack / 1e6, t_wait / 1e6,
+                        ns(J.t_submit, now()) / 1e6);
+            leave_job(J);
         }
     }
 
-    // the calling thread's half of a job: start the workers, feed head chunks to the copy engine (at most
-    // SLOTS-1 ahead of the link, so the split stays adaptive), wait for the workers, drain `stream`
-    template <class RawChunk>
-    cudaError_t drive(cudaStream_t stream, uint64_t *raw_out, RawChunk raw_chunk, uint64_t raw_pct = 100)
+    // ---- job hand-in ----
+    Job *begin_job(uint64_t &seq)
     {
-        cuda_err.store(0);
-        packed_chunks.store(0);
-        unpackable_chunks.store(0);
-        worker_launches.store(0);
-        ends.store(n_chunks & 0xffffffffull); // head 0, tail n_chunks
-        // the destination comes from the stream-ordered allocator: the workers' streams may touch it only
-        // after the allocation point of `stream`
-        const auto t0 = std::chrono::steady_clock::now();
-        cudaError_t e = cudaStreamSynchronize(stream);
-        if (e != cudaSuccess) return e;
-        const auto t1 = std::chrono::steady_clock::now();
-        if (n_workers) {
+        // the ring holds RING jobs that have not been waited for
+        seq = submitted.load(std::memory_order_relaxed);
+        if (seq - retired >= RING) return nullptr;
+        Job &J = jobs[seq % RING];
+        J.src = nullptr; J.d_chunks = nullptr; J.ev_src = nullptr; J.d_ev = nullptr;
+        J.cuda_err.store(0); J.packed_chunks.store(0); J.unpackable_chunks.store(0); J.raw_chunks.store(0); J.launches.store(0);
+        J.movers_left = n_workers + 1;
+        J.issued = false;
+        J.t_submit = std::chrono::steady_clock::now();
+        return &J;
+    }
+    void commit_job(Job &J)
+    {
+        J.ends.store(J.n_chunks & 0xffffffffull); // head 0, tail n_chunks
+        {
             std::lock_guard<std::mutex> lk(mu);
-            running = n_workers;
-            ++gen;
-            cv_job.notify_all();
+            submitted.fetch_add(1, std::memory_order_release);
         }
-        uint64_t idx, raw = 0;
-        int s = 0;
-        bool used[SLOTS] = {false, false, false, false};
-        while (e == cudaSuccess && cuda_err.load(std::memory_order_relaxed) == 0) {
-            if (used[s]) e = cudaEventSynchronize(slot_ev[s]);
-            // a raw chunk costs the link 3-4x the bytes of a packed one: with packing threads at work the copy
-            // engine's share is capped (raw_pct of the chunks), or a fast link starves the packed copies
-            if (n_workers && raw * 100 >= raw_pct * n_chunks) break;
-            if (e != cudaSuccess || !claim_head(idx)) break;
-            e = raw_chunk(idx, s);
-            if (e == cudaSuccess) e = cudaEventRecord(slot_ev[s], stream);
-            used[s] = true;
-            s = (s + 1) % SLOTS;
-            ++raw;
-        }
-        if (e != cudaSuccess) { // stop the workers early: nothing left to claim
-            cuda_err.store((int)e);
-            ends.store(0);
-        }
-        const auto t2 = std::chrono::steady_clock::now();
-        if (n_workers) {
+        cv_job.notify_all();
+    }
+
+    // host_ranks[0, n_sym) -> dst[0, ceil(n/32)) (device memory every stream may touch already).  chunk = 0: chunk_sym;
+    // else the chunk size of this job (multiple of 1024, <= chunk_sym).  false: the ring is full (wait() first).
+    bool submit_text(const uint8_t *host_ranks, uint64_t n_sym, uint2 *dst, uint64_t chunk, uint64_t *seq_out)
+    {
+        uint64_t seq;
+        Job *J = begin_job(seq);
+        if (!J) return false;
+        J->src = host_ranks; J->n = n_sym; J->d_chunks = dst;
+        J->chunk = (chunk == 0 || chunk > chunk_sym) ? chunk_sym : std::max<uint64_t>(1024, chunk / 1024 * 1024);
+        J->n_chunks = (n_sym + J->chunk - 1) / J->chunk;
+        J->raw_pct = raw_pct_text;
+        job_chunk = J->chunk;
+        commit_job(*J);
+        *seq_out = seq;
+        return true;
+    }
+
+    // every copy of job `seq` is enqueued; `stream` waits for them; host_sync: they have completed (the source
+    // buffer is free again).  Jobs are waited for in the order they were submitted.
+    cudaError_t wait(uint64_t seq, cudaStream_t stream, bool host_sync, uint32_t *launches)
+    {
+        Job &J = jobs[seq % RING];
+        const int r = (int)(seq % RING);
+        {
             std::unique_lock<std::mutex> lk(mu);
-            cv_done.wait(lk, [&] { return running == 0; });
+            cv_done.wait(lk, [&] { return J.issued; });
         }
-        const auto t3 = std::chrono::steady_clock::now();
-        // the caller's buffer may be reused as soon as we return: the raw copies must have left it
-        cudaError_t e2 = cudaStreamSynchronize(stream);
-        if (e == cudaSuccess) e = e2;
-        if (e == cudaSuccess && cuda_err.load() != 0) e = (cudaError_t)cuda_err.load();
-        *raw_out = raw;
-        if (trace) {
-            auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point c) {
-                return std::chrono::duration<double, std::milli>(c - a).count();
-            };
-            fprintf(stderr, "[spmb upload] %s job: %llu chunks (%llu raw)  pre-sync %.2f ms  raw loop %.2f  wait workers %.2f  drain %.2f\n",
-                    src ? "text" : "events", (unsigned long long)n_chunks, (unsigned long long)raw, ms(t0, t1), ms(t1, t2), ms(t2, t3),
-                    ms(t3, std::chrono::steady_clock::now()));
+        cudaError_t e = J.cuda_err.load() ? (cudaError_t)J.cuda_err.load() : cudaSuccess;
+        for (int w = 0; w < n_workers && e == cudaSuccess; ++w) e = cudaStreamWaitEvent(stream, workers[w].job_ev[r], 0);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(stream, raw_job_ev[r], 0);
+        if (e == cudaSuccess && host_sync) e = cudaStreamSynchronize(stream);
+        if (e != cudaSuccess) { // leave no copy of this job in flight
+            for (auto &W : workers) cudaStreamSynchronize(W.stream);
+            cudaStreamSynchronize(raw_stream);
+            cudaGetLastError();
         }
+        if (launches) *launches += J.launches.load();
+        if (J.src) { last_raw = J.raw_chunks.load(); last_packed = J.packed_chunks.load(); }
+        else {
+            last_ev_packed = J.packed_chunks.load() - J.unpackable_chunks.load();
+            last_ev_raw = J.raw_chunks.load() + J.unpackable_chunks.load();
+            last_ev_chunk = J.chunk;
+        }
+        if (trace)
+            fprintf(stderr, "[spmb upload] job %llu (%s): %llu chunks (%llu raw)  submit -> waited %.3f ms\n", (unsigned long long)seq,
+                    J.src ? "text" : "events", (unsigned long long)J.n_chunks, (unsigned long long)J.raw_chunks.load(),
+                    std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - J.t_submit).count());
+        ++retired;
         return e;
     }
 
     // fills dst[0, ceil(n/32)) (device, allocated in `stream`'s order) from host_ranks[0, n).  Returns when
     // every byte of host_ranks has been consumed and dst is complete.
-    // chunk = 0: chunk_sym; else the chunk size of this job (multiple of 1024, <= chunk_sym): a short job (one feed
-    // of a stream) is cut finer so that every mover gets several chunks
     cudaError_t run(const uint8_t *host_ranks, uint64_t n_sym, uint2 *dst, cudaStream_t stream, uint32_t *launches, uint64_t chunk = 0)
     {
-        src = host_ranks;
-        ev_src = nullptr;
-        n = n_sym;
-        d_chunks = dst;
-        job_chunk = (chunk == 0 || chunk > chunk_sym) ? chunk_sym : std::max<uint64_t>(1024, chunk / 1024 * 1024);
-        n_chunks = (n_sym + job_chunk - 1) / job_chunk;
-        cudaError_t e = drive(stream, &last_raw, [&](uint64_t idx, int s) -> cudaError_t {
-            const uint64_t p0 = idx * job_chunk;
-            const uint64_t len = (n - p0 < job_chunk) ? n - p0 : job_chunk;
-            cudaError_t r = cudaMemcpyAsync(d_slot[s], src + p0, len, cudaMemcpyHostToDevice, stream);
-            if (r != cudaSuccess) return r;
-            const uint64_t groups = (len + 31) / 32;
-            bytes_to_chunks_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, stream>>>(d_slot[s], len, d_chunks + p0 / 32);
-            if (launches) ++*launches;
-            return cudaGetLastError();
-        }, raw_pct_text);
-        last_packed = packed_chunks.load();
-        return e;
+        // the destination comes from the stream-ordered allocator: the movers' streams may touch it only
+        // after the allocation point of `stream`
+        cudaError_t e = cudaStreamSynchronize(stream);
+        if (e != cudaSuccess) return e;
+        uint64_t seq;
+        if (!submit_text(host_ranks, n_sym, dst, chunk, &seq)) return cudaErrorNotReady; // jobs of a stream still in flight
+        return wait(seq, stream, true, launches);
     }
 
     // same queue for the journal's event table: dst[0, n_ev) <- ev[0, n_ev)
     cudaError_t run_events(const spmb_journal_event *ev, uint64_t n_ev, uint64_t pool_len, spmb_journal_event *dst,
                            cudaStream_t stream, uint32_t *launches)
     {
-        ev_pool_len = pool_len;
-        src = nullptr;
-        ev_src = ev;
-        d_ev = dst;
-        n = n_ev;
+        cudaError_t e = cudaStreamSynchronize(stream);
+        if (e != cudaSuccess) return e;
+        uint64_t seq;
+        Job *J = begin_job(seq);
+        if (!J) return cudaErrorNotReady;
+        J->ev_pool_len = pool_len;
+        J->ev_src = ev; J->d_ev = dst; J->n = n_ev;
         // whole blocks that fit a worker's pinned buffer (chunk_sym / 4 bytes), at most 64 Ki events
-        ev_chunk = (chunk_sym / 4) / (EV_BLOCK * sizeof(SpmbPackedEvent) + sizeof(SpmbPackedEventHeader)) * EV_BLOCK;
-        if (ev_chunk > 65536) ev_chunk = 65536;
-        if (ev_chunk == 0) ev_chunk = 16;       // tiny test geometries: one partial block
-        n_chunks = (n_ev + ev_chunk - 1) / ev_chunk;
-        cudaError_t e = drive(stream, &last_ev_raw, [&](uint64_t idx, int) -> cudaError_t {
-            const uint64_t i0 = idx * ev_chunk;
-            const uint64_t len = (n - i0 < ev_chunk) ? n - i0 : ev_chunk;
-            return cudaMemcpyAsync(d_ev + i0, ev_src + i0, len * sizeof(spmb_journal_event), cudaMemcpyHostToDevice, stream);
-        }, raw_pct_events);
-        last_ev_packed = packed_chunks.load() - unpackable_chunks.load();
-        last_ev_raw += unpackable_chunks.load();
-        last_ev_chunk = ev_chunk;
-        if (launches) *launches += worker_launches.load();
-        return e;
+        J->chunk = (chunk_sym / 4) / (EV_BLOCK * sizeof(SpmbPackedEvent) + sizeof(SpmbPackedEventHeader)) * EV_BLOCK;
+        if (J->chunk > 65536) J->chunk = 65536;
+        if (J->chunk == 0) J->chunk = 16;       // tiny test geometries: one partial block
+        J->n_chunks = (n_ev + J->chunk - 1) / J->chunk;
+        J->raw_pct = raw_pct_events;
+        commit_job(*J);
+        return wait(seq, stream, true, launches);
     }
+
+    uint64_t in_flight() const { return submitted.load(std::memory_order_relaxed) - retired; }
 
     ~UploadPool()
     {
         {
             std::lock_guard<std::mutex> lk(mu);
             quit = true;
-            cv_job.notify_all();
         }
+        cv_job.notify_all();
         for (auto &W : workers) if (W.th.joinable()) W.th.join();
+        if (raw_th.joinable()) raw_th.join();
         cudaSetDevice(device);
         for (auto &W : workers) {
+            if (W.stream) cudaStreamSynchronize(W.stream);
             for (int b = 0; b < 2; ++b) {
                 if (W.pinned[b]) cudaFreeHost(W.pinned[b]);
                 if (W.d_slot[b]) cudaFree(W.d_slot[b]);
                 if (W.ev[b]) cudaEventDestroy(W.ev[b]);
             }
+            for (int r = 0; r < RING; ++r) if (W.job_ev[r]) cudaEventDestroy(W.job_ev[r]);
             if (W.stream) cudaStreamDestroy(W.stream);
         }
+        if (raw_stream) cudaStreamSynchronize(raw_stream);
         for (int s = 0; s < SLOTS; ++s) {
             if (d_slot[s]) cudaFree(d_slot[s]);
             if (slot_ev[s]) cudaEventDestroy(slot_ev[s]);
         }
+        for (int r = 0; r < RING; ++r) if (raw_job_ev[r]) cudaEventDestroy(raw_job_ev[r]);
+        if (raw_stream) cudaStreamDestroy(raw_stream);
         cudaGetLastError();
     }
 };

@@ -79,7 +79,7 @@ def lib():
 EVENT_DTYPE = np.dtype([("ref_pos", "<u8"), ("del_len", "<u4"), ("ins_len", "<u4"), ("ins_off", "<u8")])
 
 _SHIFTOR_BYTES = 4 * 2 + 16 * 32 * 4 + 32 * 4
-_MYERS_BYTES = 4096  # >= sizeof(orc_myers_t)
+_MYERS_BYTES = 32768  # >= sizeof(orc_myers_t) (128 blocks: 19.5 KB)
 
 
 def _u8(a):

@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define ORC_MAX_BLOCKS 16 /* 64-bit blocks: patterns up to 1024 symbols */
+#define ORC_MAX_BLOCKS 128 /* 64-bit blocks: patterns up to 8192 symbols */
 
 /* ---- definitional oracles (authoritative semantics) ---- */
 /* every i with text[i..i+m) == pat; writes end=i+m.  Returns hit count (may exceed cap). */
