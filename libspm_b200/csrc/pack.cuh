@@ -1,6 +1,7 @@
 // pack.cuh -- kernels that build / read the packed store.
 //   pack_kernel<ByteSource>     1-byte dna4 ranks (a std::vector<spm::dna4> image)  -> strided bit planes
-//   pack_chunks_kernel<JournalSource>  base store + journal events (a14)            -> planes (+ lane chunks) of the derived sequence
+//   journal_derive_kernel       base store + journal events (a14)                   -> linear lane-chunk words of the derived sequence
+//   pack_chunks_kernel<Source>  lane-chunk words (upload, journal, JST windows)     -> planes (+ lane chunks)
 //   unpack_kernel               planes -> 1-byte ranks (round trips, tests)
 // One CTA (32 warps) produces one 1024-column block (8 KB); warp w owns thread-row w of the
 // block (32 columns).  Lane b reads the 32 symbols of its row for those columns, the warp
@@ -84,132 +85,258 @@ __device__ __forceinline__ uint2 spmb_fetch32(const uint2 *__restrict__ lanes, c
 // journaled sequence: derived position d -> base symbol or inserted symbol.
 // ev_der[i] = derived position where event i's inserted segment begins (device prefix sum);
 // blk_idx[b] = index of the last event with ev_der <= b*1024 (or -1).
-// A lane produces the 32 symbols of its row chunk as ONE packed word pair: every maximal run copied
-// from the base is one unaligned 32-symbol fetch from the base's lane chunks (two 8-byte loads), shifted
-// into place -- the base is read at ~2x its packed size instead of one 8-byte load per SYMBOL.
 //
-// The event lookup is WARP-COOPERATIVE (round 2): the 32 lanes of a fetch warp cover up to 1024 consecutive
-// derived symbols of one row, i.e. ~10 events at a 1 % journal.  Round 1 let every lane binary-search the event
-// table on its own: ~10 dependent L2 round trips per 32 symbols (blk_idx x2, 4-5 search steps, the event, the
-// next event's position, the base words), 2.9 ms for 3.2 Gbp where the bytes moved take 0.4 ms.  Now the warp
-// reads blk_idx once, loads ONE batch of 32 consecutive event records with a coalesced access into shared
-// memory, and every lane finds and walks its events there (5 LDS steps); the dependent chain is
-// blk_idx -> batch -> base words.  Lanes whose events run past the batch fall back to global reads.
-struct JournalSource {
+// Materialisation is two kernels (round 2, second form): journal_derive_kernel writes the derived sequence as LINEAR
+// lane-chunk words (out[d/32] = the 32 symbols at d, the intermediate the upload path also produces), and the plain
+// pack_chunks_kernel<ChunkSource> turns those into planes + lane chunks.  History: round 1 fetched inside the pack
+// kernel with one binary search per 32-symbol chunk (2.9 ms for 3.2 Gbp + 32 M events); the first round-2 form
+// shared one event batch per warp but still sat in the pack kernel's 1024-thread CTA -- 60 registers = ONE CTA per
+// SM, every warp a chain of 5-6 dependent memory round trips (block index -> batch -> one base fetch after the
+// other -> pool bytes) and a block-wide barrier behind the slowest: 5.1 ms under ncu.  Here a warp owns one
+// 1024-symbol block of the derived sequence on its own (no barrier, 256-thread CTAs, ~5 CTAs per SM):
+//   1. blk_idx[b], blk_idx[b+1]                     -> the block's events are [first, first + nb)        (one trip)
+//   2. the warp loads those records coalesced into shared memory                                         (one trip)
+//   3. every lane lists the (up to 32) source runs of its chunk from shared memory alone, ISSUES THE LOADS OF THREE
+//      RUNS AT A TIME (base lane chunks; inserted symbols come from a 2-bit packed copy of the pool, so both kinds
+//      of run are the same unaligned 32-symbol fetch) and only then shifts / masks / ORs them into place  (one trip)
+// Coordinates inside a block are 32-bit offsets from its first derived position D0 (rel), and an event is kept as
+// what a run needs: where its inserted segment begins / ends (rel, ins_end) and the two constants that turn a derived
+// position into a source position -- base position = d + shift behind the event, pool position = d + pshift inside
+// its insertion.
+struct JournalRec {
+    int32_t rel, ins_end;
+    long long shift, pshift;
+};
+
+struct JournalDeriveArgs {
     const uint2 *__restrict__ base_lanes;
     SpmbLayout base;
     const spmb_journal_event *__restrict__ ev;
     const uint64_t *__restrict__ ev_der;
     const int64_t *__restrict__ blk_idx;
-    const uint8_t *__restrict__ pool;
+    const uint2 *__restrict__ pool_words; // the insertion pool, 32 symbols per word pair, one spare pair behind the end
     uint64_t n_ev;
-    uint64_t n; // derived length
-
-    enum { BATCH = 32 };
-    struct Rec { uint64_t der, ref_end, ins_off; uint32_t ins_len, pad; };
-    enum { WARP_SMEM = BATCH * 32 };
-
-    __device__ __forceinline__ Rec fetch(int64_t i, const Rec *sm, int64_t b, uint32_t nb) const
-    {
-        const int64_t k = i - b;
-        if (k >= 0 && k < (int64_t)nb) return sm[k];
-        const spmb_journal_event x = ev[i];
-        Rec r;
-        r.der = ev_der[i]; r.ref_end = x.ref_pos + x.del_len; r.ins_off = x.ins_off; r.ins_len = x.ins_len; r.pad = 0;
-        return r;
-    }
-
-    // the 32 symbols at derived position d0; batch = events [b, b + nb) in sm (der[b] <= d0 or b == 0)
-    __device__ __forceinline__ uint2 walk(uint64_t d0, const Rec *sm, int64_t b, uint32_t nb) const
-    {
-        // number of batch events with der <= d0 (sorted): branch-free binary search over <= 32 entries
-        uint32_t cnt = 0;
-#pragma unroll
-        for (uint32_t step = 16; step >= 1; step >>= 1)
-            if (cnt + step <= nb && sm[cnt + step - 1].der <= d0) cnt += step;
-        if (cnt < nb && sm[cnt].der <= d0) ++cnt; // nb == 32: the last entry
-        int64_t e = b + (int64_t)cnt - 1;
-        if (cnt == nb) // the lane's event may lie past the batch (dense journal): finish the search in global memory
-            while (e + 1 < (int64_t)n_ev && ev_der[e + 1] <= d0) ++e;
-        uint64_t seg_der = 0, seg_ref = 0, seg_off = 0;
-        uint32_t seg_ins = 0;
-        if (e >= 0) {
-            const Rec r = fetch(e, sm, b, nb);
-            seg_der = r.der; seg_ins = r.ins_len; seg_ref = r.ref_end; seg_off = r.ins_off;
-        }
-        Rec nx;
-        nx.der = ~0ull;
-        if (e + 1 < (int64_t)n_ev) nx = fetch(e + 1, sm, b, nb);
-        unsigned long long out = 0;
-        uint32_t t = 0;
-        const uint32_t t_end = (uint32_t)min((uint64_t)32, n - d0);
-        while (t < t_end) {
-            const uint64_t d = d0 + t;
-            while (d >= nx.der) { // enter the next event (several may start at the same d)
-                ++e;
-                seg_der = nx.der; seg_ins = nx.ins_len; seg_ref = nx.ref_end; seg_off = nx.ins_off;
-                nx.der = ~0ull;
-                if (e + 1 < (int64_t)n_ev) nx = fetch(e + 1, sm, b, nb);
-            }
-            const uint64_t o = d - seg_der;
-            if (e >= 0 && o < seg_ins) { // inside the inserted segment: one pool symbol
-                out |= (unsigned long long)(pool[seg_off + o] & 3u) << (62 - 2 * t);
-                ++t;
-                continue;
-            }
-            // a run copied from the base: up to the next event / the end of this chunk
-            const uint64_t bp = (e >= 0) ? seg_ref + (o - seg_ins) : d;
-            uint32_t run = t_end - t;
-            if (nx.der - d < run) run = (uint32_t)(nx.der - d);
-            const uint2 w = spmb_fetch32(base_lanes, base, bp);
-            unsigned long long W = ((unsigned long long)w.x << 32) | w.y;
-            if (run < 32) W &= ~(~0ull >> (2 * run)); // keep the first `run` symbols
-            out |= W >> (2 * t);
-            t += run;
-        }
-        return make_uint2((uint32_t)(out >> 32), (uint32_t)out);
-    }
-
-    // all 32 lanes of a warp call this together; lane l wants the chunk at derived position d0 (active) of the
-    // row segment seg_key (lanes of one segment hold ascending, consecutive chunks).  sm = this warp's batch area.
-    __device__ __forceinline__ uint2 load_chunk_warp(bool active, uint64_t d0, uint64_t seg_key, void *smem, uint32_t lane) const
-    {
-        Rec *sm = reinterpret_cast<Rec *>(smem);
-        uint2 out = make_uint2(0, 0);
-        uint32_t todo = __ballot_sync(0xffffffffu, active && d0 < n);
-        while (todo) {
-            const int leader = __ffs(todo) - 1;
-            const uint64_t key = __shfl_sync(0xffffffffu, seg_key, leader);
-            const bool mine = ((todo >> lane) & 1u) && seg_key == key;
-            const uint32_t grp = __ballot_sync(0xffffffffu, mine);
-            const uint64_t Dlo = __shfl_sync(0xffffffffu, d0, leader);
-            int64_t b = blk_idx[Dlo >> 10];
-            if (b < 0) b = 0;
-            uint32_t nb;
-            for (;;) {
-                nb = (uint32_t)min((uint64_t)BATCH, n_ev - (uint64_t)b);
-                if (lane < nb) {
-                    const spmb_journal_event x = ev[b + lane];
-                    Rec r;
-                    r.der = ev_der[b + lane]; r.ref_end = x.ref_pos + x.del_len; r.ins_off = x.ins_off; r.ins_len = x.ins_len; r.pad = 0;
-                    sm[lane] = r;
-                }
-                __syncwarp();
-                const uint32_t le = __ballot_sync(0xffffffffu, lane < nb && sm[lane].der <= Dlo);
-                if (le == 0xffffffffu && (uint64_t)b + BATCH < n_ev) { // every event of the batch lies before the segment: slide
-                    b += BATCH - 1;
-                    __syncwarp();
-                    continue;
-                }
-                break;
-            }
-            if (mine) out = walk(d0, sm, b, nb);
-            __syncwarp();
-            todo &= ~grp;
-        }
-        return out;
-    }
+    uint64_t n;                           // derived length
+    uint2 *__restrict__ out;              // [ceil(n / 32)]
 };
+
+enum { JOURNAL_BATCH = 64, JOURNAL_NSEG = 3 };
+
+__device__ __forceinline__ int32_t journal_clamp(long long x)
+{
+    return (int32_t)max(-(1ll << 30), min(1ll << 30, x));
+}
+
+__device__ __forceinline__ JournalRec journal_rec(const spmb_journal_event &x, uint64_t der, uint64_t D0)
+{
+    JournalRec r;
+    r.rel = journal_clamp((long long)der - (long long)D0);
+    r.ins_end = journal_clamp((long long)der + (long long)x.ins_len - (long long)D0);
+    r.shift = (long long)(x.ref_pos + x.del_len) - (long long)der - (long long)x.ins_len;
+    r.pshift = (long long)x.ins_off - (long long)der;
+    return r;
+}
+
+// source words of a run: the two lane-chunk words that hold the 32 symbols from `src` on, and where they begin
+__device__ __forceinline__ void journal_issue(const JournalDeriveArgs &a, bool pool, uint64_t src, uint2 &w0, uint2 &w1, uint32_t &o)
+{
+    if (pool) {
+        w0 = __ldg(a.pool_words + (src >> 5));
+        w1 = __ldg(a.pool_words + (src >> 5) + 1);
+        o = (uint32_t)src & 31u;
+    } else {
+        const uint32_t rl32 = a.base.row_len >> 5;
+        const uint64_t R = spmb_div_rl(a.base, src);
+        const uint32_t col = (uint32_t)(src - R * a.base.row_len);
+        const uint32_t c = col >> 5;
+        w0 = spmb_chunk(a.base_lanes, rl32, R, c);
+        w1 = (c + 1 < rl32) ? spmb_chunk(a.base_lanes, rl32, R, c + 1) : spmb_chunk(a.base_lanes, rl32, R + 1, 0);
+        o = col & 31u;
+    }
+}
+
+__device__ __forceinline__ unsigned long long journal_place(const uint2 w0, const uint2 w1, uint32_t o, uint32_t t, uint32_t len)
+{
+    const uint2 w = spmb_chunk_shift(w0, w1, o);
+    unsigned long long W = ((unsigned long long)w.x << 32) | w.y;
+    if (len < 32) W &= ~(~0ull >> (2 * len)); // keep the first `len` symbols
+    return W >> (2 * t);
+}
+
+// One chunk from a batch in shared memory: sm = events [0, nb) of the block (rel ascending), e = index of the last
+// one with rel <= lane * 32 (or -1), D0 / n_rel = the block's first derived position / symbols left from there.
+__device__ __forceinline__ uint2 journal_chunk(const JournalDeriveArgs &a, const JournalRec *sm, int nb, int e, uint64_t D0, int32_t n_rel,
+                                               uint32_t lane)
+{
+    const int32_t c0 = (int32_t)lane * 32;
+    int32_t cur = c0;
+    const int32_t end = min(c0 + 32, n_rel);
+    long long shift = 0, pshift = 0;
+    int32_t ins_end = INT32_MIN, next_rel = INT32_MAX;
+    if (e >= 0) { const JournalRec r = sm[e]; shift = r.shift; pshift = r.pshift; ins_end = r.ins_end; }
+    if (e + 1 < nb) next_rel = sm[e + 1].rel;
+    unsigned long long out = 0;
+    while (cur < end) {
+        // ---- up to JOURNAL_NSEG runs: their loads are issued together, then they are placed ----
+        uint2 w0[JOURNAL_NSEG], w1[JOURNAL_NSEG];
+        uint32_t so[JOURNAL_NSEG], st[JOURNAL_NSEG], sl[JOURNAL_NSEG];
+#pragma unroll
+        for (int q = 0; q < JOURNAL_NSEG; ++q) {
+            sl[q] = 0; st[q] = 0; so[q] = 0;
+            w0[q] = make_uint2(0, 0); w1[q] = make_uint2(0, 0);
+            if (cur < end) {
+                while (cur >= next_rel) { // enter the next event (several may begin at the same position)
+                    ++e;
+                    const JournalRec r = sm[e];
+                    shift = r.shift; pshift = r.pshift; ins_end = r.ins_end;
+                    next_rel = (e + 1 < nb) ? sm[e + 1].rel : INT32_MAX;
+                }
+                const bool pool = cur < ins_end;
+                const int32_t stop = pool ? min(end, ins_end) : min(end, next_rel);
+                journal_issue(a, pool, (uint64_t)((long long)D0 + cur + (pool ? pshift : shift)), w0[q], w1[q], so[q]);
+                st[q] = (uint32_t)(cur - c0); sl[q] = (uint32_t)(stop - cur);
+                cur = stop;
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < JOURNAL_NSEG; ++q)
+            if (sl[q]) out |= journal_place(w0[q], w1[q], so[q], st[q], sl[q]);
+    }
+    return make_uint2((uint32_t)(out >> 32), (uint32_t)out);
+}
+
+// The same without a batch (a block with more events than JOURNAL_BATCH: every record comes from global memory).
+__device__ __noinline__ uint2 journal_chunk_dense(const JournalDeriveArgs &a, int64_t first, int64_t last, uint64_t D0, int32_t n_rel,
+                                                  uint32_t lane)
+{
+    const uint64_t d0 = D0 + lane * 32;
+    // last event with der <= d0 among [first, last] (der[first] <= D0 unless first == 0)
+    int64_t lo = first - 1, hi = last;
+    while (lo < hi) {
+        const int64_t mid = (lo + hi + 1) >> 1;
+        if (a.ev_der[mid] <= d0) lo = mid; else hi = mid - 1;
+    }
+    int64_t e = lo;
+    const int32_t c0 = (int32_t)lane * 32;
+    int32_t cur = c0;
+    const int32_t end = min(c0 + 32, n_rel);
+    long long shift = 0, pshift = 0;
+    int32_t ins_end = INT32_MIN, next_rel = INT32_MAX;
+    if (e >= 0) { const JournalRec r = journal_rec(a.ev[e], a.ev_der[e], D0); shift = r.shift; pshift = r.pshift; ins_end = r.ins_end; }
+    if (e + 1 < (int64_t)a.n_ev) next_rel = journal_clamp((long long)a.ev_der[e + 1] - (long long)D0);
+    unsigned long long out = 0;
+    while (cur < end) {
+        while (cur >= next_rel) {
+            ++e;
+            const JournalRec r = journal_rec(a.ev[e], a.ev_der[e], D0);
+            shift = r.shift; pshift = r.pshift; ins_end = r.ins_end;
+            next_rel = (e + 1 < (int64_t)a.n_ev) ? journal_clamp((long long)a.ev_der[e + 1] - (long long)D0) : INT32_MAX;
+        }
+        const bool pool = cur < ins_end;
+        const int32_t stop = pool ? min(end, ins_end) : min(end, next_rel);
+        uint2 w0, w1;
+        uint32_t o;
+        journal_issue(a, pool, (uint64_t)((long long)D0 + cur + (pool ? pshift : shift)), w0, w1, o);
+        out |= journal_place(w0, w1, o, (uint32_t)(cur - c0), (uint32_t)(stop - cur));
+        cur = stop;
+    }
+    return make_uint2((uint32_t)(out >> 32), (uint32_t)out);
+}
+
+// One warp = one 1024-symbol block of the derived sequence at a time, software-pipelined over the warp's blocks:
+// while block j is derived from the records in shared memory, the event records of block j+1 are on their way into
+// registers and the block index of block j+2 is being read -- the only memory round trip left on a block's critical
+// path is the fetch of its source words.
+__global__ void __launch_bounds__(256, 4) journal_derive_kernel(JournalDeriveArgs a)
+{
+    __shared__ JournalRec s_rec[8][JOURNAL_BATCH];
+    __shared__ int s_last[8][32];
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    JournalRec *sm = s_rec[warp];
+    int *last_of = s_last[warp];
+    const uint64_t n_blk = (a.n + 1023) >> 10;
+    const uint64_t stride = (uint64_t)gridDim.x * 8;
+    uint64_t blk = (uint64_t)blockIdx.x * 8 + warp;
+    if (blk >= n_blk) return; // no block-wide synchronisation anywhere
+
+    // events [first, first + want) matter to a block: the one in effect at its start, those inside, one behind
+    auto span = [&](int64_t i_lo, int64_t i_hi, int64_t &first, uint64_t &want) {
+        first = i_lo < 0 ? 0 : i_lo;
+        want = (uint64_t)(i_hi + 2 - first);
+        if (want > a.n_ev - (uint64_t)first) want = a.n_ev - (uint64_t)first;
+    };
+    // registers of the block in flight
+    spmb_journal_event xe[2];
+    uint64_t xd[2];
+    auto load_events = [&](int64_t first, uint64_t want) {
+        if (lane < want) { xe[0] = a.ev[first + lane]; xd[0] = a.ev_der[first + lane]; }
+        if (want > 32 && lane + 32 < want && lane + 32 < JOURNAL_BATCH) { xe[1] = a.ev[first + lane + 32]; xd[1] = a.ev_der[first + lane + 32]; }
+    };
+    // records -> shared memory; returns this lane's e0 = last event with rel <= lane * 32
+    auto stage = [&](uint64_t want, uint64_t D0) -> int {
+        const uint32_t nb = (uint32_t)min((uint64_t)JOURNAL_BATCH, want);
+        last_of[lane] = -1;
+        const int halves = nb > 32 ? 2 : 1; // warp-uniform: most blocks hold a dozen events
+        for (int h = 0; h < halves; ++h) {
+            const uint32_t k = lane + 32 * h;
+            if (k < nb) sm[k] = journal_rec(h ? xe[1] : xe[0], h ? xd[1] : xd[0], D0);
+        }
+        __syncwarp();
+        for (int h = 0; h < halves; ++h) {
+            const uint32_t k = lane + 32 * h;
+            if (k < nb) {
+                const int32_t r = sm[k].rel;
+                const int32_t c = r <= 0 ? 0 : (r + 31) >> 5; // first chunk whose start lies at or behind the event
+                int32_t cn = 64;
+                if (k + 1 < nb) { const int32_t rn = sm[k + 1].rel; cn = rn <= 0 ? 0 : (rn + 31) >> 5; }
+                if (c < 32 && cn != c) last_of[c] = (int)k;
+            }
+        }
+        __syncwarp();
+        int v = last_of[lane];
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int up = __shfl_up_sync(0xffffffffu, v, d);
+            if ((int)lane >= d) v = max(v, up);
+        }
+        return v;
+    };
+
+    // prologue: block index of the first two blocks, events of the first
+    int64_t lo = a.blk_idx[blk], hi = a.blk_idx[blk + 1];
+    int64_t first;
+    uint64_t want;
+    span(lo, hi, first, want);
+    load_events(first, want);
+    int64_t nlo = -1, nhi = -1;
+    if (blk + stride < n_blk) { nlo = a.blk_idx[blk + stride]; nhi = a.blk_idx[blk + stride + 1]; }
+    int e0 = stage(want, blk << 10);
+    for (;;) {
+        const uint64_t D0 = blk << 10;
+        const bool has_next = blk + stride < n_blk;
+        // ---- stage 1 for the next block, stage 0 for the one after ----
+        int64_t nfirst = 0;
+        uint64_t nwant = 0;
+        if (has_next) {
+            span(nlo, nhi, nfirst, nwant);
+            load_events(nfirst, nwant);
+            if (blk + 2 * stride < n_blk) { nlo = a.blk_idx[blk + 2 * stride]; nhi = a.blk_idx[blk + 2 * stride + 1]; }
+        }
+        // ---- this block ----
+        const int32_t n_rel = (int32_t)min((uint64_t)1024, a.n - D0);
+        if ((int32_t)lane * 32 < n_rel) {
+            uint2 o;
+            if (want <= JOURNAL_BATCH) o = journal_chunk(a, sm, (int)want, e0, D0, n_rel, lane);
+            else o = journal_chunk_dense(a, first, first + (int64_t)want - 1, D0, n_rel, lane);
+            a.out[(D0 >> 5) + lane] = o;
+        }
+        if (!has_next) break;
+        __syncwarp();
+        blk += stride;
+        first = nfirst; want = nwant;
+        e0 = stage(want, blk << 10);
+    }
+}
 
 // journal preparation on the device: validation + (ins - del) deltas, then an exclusive scan
 // (CUB) gives every event's shift; ev_der = ref_pos + shift.
@@ -281,29 +408,10 @@ __device__ __forceinline__ uint32_t spmb_transpose32(uint32_t x, uint32_t lane)
     return x;
 }
 
-// 16 two-bit codes (symbol j at bits 31-2j, 30-2j) -> the 16 high bits and the 16 low bits, symbol j at bit 15-j
-__device__ __forceinline__ uint32_t spmb_compress_even(uint32_t t) // even bit positions -> low 16 bits
-{
-    t = (t | (t >> 1)) & 0x33333333u;
-    t = (t | (t >> 2)) & 0x0f0f0f0fu;
-    t = (t | (t >> 4)) & 0x00ff00ffu;
-    t = (t | (t >> 8)) & 0x0000ffffu;
-    return t;
-}
-
-// lane-chunk word (32 symbols of one row) -> H / L words with symbol c at bit c
-__device__ __forceinline__ void spmb_chunk_to_bits(const uint2 w, uint32_t &H, uint32_t &L)
-{
-    const uint32_t hx = spmb_compress_even((w.x >> 1) & 0x55555555u), lx = spmb_compress_even(w.x & 0x55555555u);
-    const uint32_t hy = spmb_compress_even((w.y >> 1) & 0x55555555u), ly = spmb_compress_even(w.y & 0x55555555u);
-    H = __brev((hx << 16) | hy);
-    L = __brev((lx << 16) | ly);
-}
-
 template <class Source>
 __global__ void __launch_bounds__(1024) pack_kernel(Source src, SpmbLayout lay, uint2 *__restrict__ planes)
 {
-    __shared__ uint2 tile[1024];
+    __shared__ uint2 tile[1024 + 16]; // one pad entry per 64: see pack_chunks_kernel
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint64_t g0 = (uint64_t)blockIdx.x * 1024 + warp * 32; // first column of this thread-row
     uint32_t w[8];
@@ -324,49 +432,35 @@ __global__ void __launch_bounds__(1024) pack_kernel(Source src, SpmbLayout lay, 
         if (lane == c) { myH = h; myL = l; }
     }
     // lane c holds column g0 + c  ->  permuted slot inside the block
-    tile[((lane >> 1) << 6) | (warp << 1) | (lane & 1)] = make_uint2(myH, myL);
+    const uint32_t ti = ((lane >> 1) << 6) | (warp << 1) | (lane & 1);
+    tile[ti + (ti >> 6)] = make_uint2(myH, myL);
     __syncthreads();
-    planes[(uint64_t)blockIdx.x * 1024 + threadIdx.x] = tile[threadIdx.x];
+    planes[(uint64_t)blockIdx.x * 1024 + threadIdx.x] = tile[threadIdx.x + (threadIdx.x >> 6)];
 }
 
 // same block shape as pack_kernel for sources that deliver a lane chunk (32 symbols of a row, packed).
 // Fetch phase: warp r = row r of the super-tile, lane c = the c-th 32-column group of the block, so a warp
-// walks 1024 CONSECUTIVE symbols of one row: a linear source is read in 256-byte runs, and the lanes of a
-// journal lookup share their block index, their binary-search path and their event records (L1 hits instead
-// of a chain of DRAM round trips per lane).  The chunks change hands through shared memory; then warp c
+// walks 1024 CONSECUTIVE symbols of one row: a linear source is read in 256-byte runs.  The chunks change hands
+// through shared memory; then warp c
 // holds group c with lane r = row r, the 2 x 32 x 32 bit transposition gives the {H,L} column words, and the
 // chunk itself -- the store's lane-chunk layout -- is written as a by-product when `lanes_out` is given.
-template <class Source, class = void>
-struct SpmbWarpSmem { enum { value = 0 }; };
-template <class Source>
-struct SpmbWarpSmem<Source, decltype((void)Source::WARP_SMEM)> { enum { value = Source::WARP_SMEM }; };
-
 template <class Source>
 __global__ void __launch_bounds__(1024) pack_chunks_kernel(Source src, SpmbLayout lay, uint2 *__restrict__ planes,
                                                            uint2 *__restrict__ lanes_out)
 {
-    // the fetch phase's per-warp event batches and the store phase's tile share one block of shared memory
-    constexpr uint32_t BATCH_BYTES = 32u * SpmbWarpSmem<Source>::value;
-    constexpr uint32_t UNION_BYTES = BATCH_BYTES > 8192u ? BATCH_BYTES : 8192u;
-    __shared__ __align__(16) unsigned char s_union[UNION_BYTES];
+    // the tile is the block in the store's permuted column order, so the final copy is one coalesced 8 KB burst; one
+    // pad entry per 64 keeps the scattered writes of a warp (stride 64 entries) off a single bank pair
+    __shared__ uint2 tile[1024 + 16];
     __shared__ uint2 xchg[32][33];
-    uint2 *tile = reinterpret_cast<uint2 *>(s_union);
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     {
         const uint64_t gf = (uint64_t)blockIdx.x * 1024 + lane * 32; // first column of group `lane`
         uint2 f = make_uint2(0, 0);
-        bool active = false;
-        uint64_t p0 = 0, st = 0;
         if (gf < lay.n_cols) {
-            st = spmb_div_rl(lay, gf);
+            const uint64_t st = spmb_div_rl(lay, gf);
             const uint32_t col0 = (uint32_t)(gf - st * lay.row_len);
-            p0 = (st * 32 + warp) * (uint64_t)lay.row_len + col0;
-            active = p0 < lay.n;
-        }
-        if constexpr (SpmbWarpSmem<Source>::value != 0) {
-            f = src.load_chunk_warp(active, p0, st, s_union + warp * SpmbWarpSmem<Source>::value, lane);
-        } else {
-            if (active) f = src.load_chunk(p0);
+            const uint64_t p0 = (st * 32 + warp) * (uint64_t)lay.row_len + col0;
+            if (p0 < lay.n) f = src.load_chunk(p0);
         }
         xchg[warp][lane] = f;
     }
@@ -374,13 +468,17 @@ __global__ void __launch_bounds__(1024) pack_chunks_kernel(Source src, SpmbLayou
     const uint2 w = xchg[lane][warp];                                // row `lane`, group `warp`
     const uint64_t g0 = (uint64_t)blockIdx.x * 1024 + warp * 32;     // first column of this thread-row
     if (lanes_out) lanes_out[(g0 >> 5) * 32 + lane] = w; // group G = g0/32 (every group of the allocation is written)
-    uint32_t myH, myL;
-    spmb_chunk_to_bits(w, myH, myL);          // row `lane`: bit c = column g0 + c
-    myH = spmb_transpose32(myH, lane);        // column g0 + lane: bit r = row r
-    myL = spmb_transpose32(myL, lane);
-    tile[((lane >> 1) << 6) | (warp << 1) | (lane & 1)] = make_uint2(myH, myL);
+    // bit j of a chunk word is the high (j odd) or low (j even) bit of symbol (31 - j) / 2, so the 32 x 32 bit
+    // transposes of the two words ARE the plane words: lane j ends up with one plane of column s = (31 - j) / 2
+    // (from .x) and of column 16 + s (from .y), bit r = row r -- no separate de-interleaving of the 2-bit codes
+    const uint32_t tx = spmb_transpose32(w.x, lane), ty = spmb_transpose32(w.y, lane);
+    const uint32_t s = (31u - lane) >> 1, plane = (lane & 1u) ^ 1u; // .x of a column entry = H, .y = L
+    uint32_t *tile32 = reinterpret_cast<uint32_t *>(tile);
+    const uint32_t i0 = ((s >> 1) << 6) | (warp << 1) | (s & 1u), i1 = (((16u + s) >> 1) << 6) | (warp << 1) | (s & 1u);
+    tile32[2 * (i0 + (i0 >> 6)) + plane] = tx;
+    tile32[2 * (i1 + (i1 >> 6)) + plane] = ty;
     __syncthreads();
-    planes[(uint64_t)blockIdx.x * 1024 + threadIdx.x] = tile[threadIdx.x];
+    planes[(uint64_t)blockIdx.x * 1024 + threadIdx.x] = tile[threadIdx.x + (threadIdx.x >> 6)];
 }
 
 __global__ void unpack_kernel(const uint2 *__restrict__ planes, SpmbLayout lay, uint64_t begin, uint64_t n,

@@ -379,8 +379,8 @@ struct PigeonVerifyArgs {
     uint64_t own_lo, own_hi;      // plain: owned range of (last symbol index of a hit | seed begin)
     HitSink sink;
     // duplicate suppression of the filtered Myers path (pg_emit_min); dd_keys == null: off
-    unsigned long long *dd_keys;  // [2^dd_bits] 0 = free, else key + 1
-    uint32_t *dd_idx;             // [2^dd_bits] 0 = not published yet, else index of the hit record + 1
+    unsigned long long *dd_keys;  // [2^dd_bits] 0 = free, else key + 1 (cleared before every launch)
+    uint32_t *dd_err;             // [2^dd_bits] 256 - smallest error count reported for the key (0 = none yet)
     uint32_t dd_bits, dd_end_bits;
     uint64_t dd_nseq;
 };
@@ -398,42 +398,91 @@ __device__ __forceinline__ void pg_emit(const HitSink &sink, uint64_t end, uint3
 // SPMB_ALG_MYERS_FILTERED: the k+1 pieces of a needle (and neighbouring diagonals) verify overlapping windows, so the
 // same (needle, sequence, end) is found up to ~(k+1) times, each time with an upper bound of the true score whose
 // minimum is exact.  Sorting the raw list to drop them cost more than the search at small shards (C5 at 1/8 of the
-// text: 13 ordering kernels, 0.12 ms, behind 0.2 ms of search).  So the first thread to report a hit claims a slot of a
-// hash table (CAS on the key), appends the record and publishes its index; later finders only atomicMin the record's
-// error count.  A table miss (4 probes), a not-yet-published index or a key that does not fit 63 bits fall back to a
-// plain append: the ordering downstream still removes those few duplicates, this table only removes the volume.
-__device__ __forceinline__ void pg_emit_min(const PigeonVerifyArgs &a, uint64_t end, uint32_t seq, uint32_t pid, uint32_t err)
+// text: 13 ordering kernels, 0.12 ms, behind 0.2 ms of search).  So every finder of a hit goes through a hash table:
+// the first one claims a slot (CAS on the key) and appends the record, with the slot number in `reserved`; ALL of
+// them fold their error count into the slot's minimum (one atomicMax, fire and forget); when the kernel is done,
+// pigeon_fixup_kernel writes each record's minimum back and clears `reserved`.  Nobody waits for anybody.  A table
+// miss (4 probes) or a key that does not fit falls back to a plain append: the ordering downstream still removes
+// those few duplicates, this table only removes the volume.
+//
+// A window's hits (2(k - e) + 1 neighbouring ends, typically) are collected first and reported TOGETHER behind the
+// scan (PgHitBatch): the claims of all of them are in flight at once and one atomicAdd reserves their records --
+// two memory round trips per candidate.  Reported one by one from inside the scan, every hit cost its warp a chain
+// of three to four dependent atomics (profile of the first form: 60 % of the kernel's stall samples).
+struct PgHitBatch {
+    enum { CAP = 8 };
+    unsigned long long ent[CAP]; // (end << 8) | errors
+    int n = 0;
+};
+
+__device__ __forceinline__ void pg_batch_flush(const PigeonVerifyArgs &a, PgHitBatch &b, uint32_t seq, uint32_t pid)
 {
-    if (a.dd_keys) {
-        const unsigned long long key = ((((unsigned long long)pid * a.dd_nseq + seq) << a.dd_end_bits) | end) + 1ull;
-        const uint32_t mask = (1u << a.dd_bits) - 1u;
-        uint32_t slot = pg_h2((uint32_t)(key >> 32), (uint32_t)key) >> (32 - a.dd_bits);
-        for (int probe = 0; probe < 4; ++probe) {
-            const unsigned long long old = atomicCAS(a.dd_keys + slot, 0ull, key);
-            if (old == 0ull) {
-                const unsigned long long idx = spmb_append_slot(a.sink.count);
-                if (idx < a.sink.cap) {
-                    spmb_hit h;
-                    h.end = end; h.seq_id = seq; h.pattern_id = pid; h.errors = err; h.reserved = 0;
-                    a.sink.hits[idx] = h;
-                    __threadfence();
-                    atomicExch(a.dd_idx + slot, (uint32_t)idx + 1u);
-                }
-                return;
-            }
-            if (old == key) {
-                const uint32_t pi = *reinterpret_cast<volatile uint32_t *>(a.dd_idx + slot);
-                if (pi) {
-                    __threadfence();
-                    atomicMin(&a.sink.hits[pi - 1].errors, err);
-                    return;
-                }
-                break;
-            }
-            slot = (slot + 1) & mask;
+    if (b.n == 0) return;
+    const uint32_t mask = (1u << a.dd_bits) - 1u;
+    unsigned long long key[PgHitBatch::CAP], seen[PgHitBatch::CAP];
+    uint32_t slot[PgHitBatch::CAP];
+    // ---- claims, all in flight together ----
+#pragma unroll
+    for (int j = 0; j < PgHitBatch::CAP; ++j) {
+        seen[j] = ~0ull; key[j] = 0; slot[j] = 0;
+        if (j < b.n && a.dd_keys) {
+            key[j] = ((((unsigned long long)pid * a.dd_nseq + seq) << a.dd_end_bits) | (b.ent[j] >> 8)) + 1ull;
+            slot[j] = pg_h2((uint32_t)(key[j] >> 32), (uint32_t)key[j]) >> (32 - a.dd_bits);
+            seen[j] = atomicCAS(a.dd_keys + slot[j], 0ull, key[j]);
         }
     }
-    pg_emit(a.sink, end, seq, pid, err, 0);
+    // ---- who appends a record: the claimers, and whoever found no slot ----
+    uint32_t rec = 0; // bit j: hit j gets a record
+#pragma unroll
+    for (int j = 0; j < PgHitBatch::CAP; ++j) {
+        if (j < b.n) {
+            bool mine = false, dup = false;
+            if (a.dd_keys) {
+                mine = seen[j] == 0ull;
+                dup = seen[j] == key[j];
+                for (int probe = 1; probe < 4 && !mine && !dup; ++probe) { // the slot holds another key: next ones
+                    slot[j] = (slot[j] + 1) & mask;
+                    const unsigned long long sn = atomicCAS(a.dd_keys + slot[j], 0ull, key[j]);
+                    mine = sn == 0ull;
+                    dup = sn == key[j];
+                }
+                if (mine || dup) atomicMax(a.dd_err + slot[j], 256u - (uint32_t)(b.ent[j] & 255ull));
+                else slot[j] = 0xffffffffu; // no slot: a plain record
+            } else slot[j] = 0xffffffffu;
+            if (!dup) rec |= 1u << j;
+        }
+    }
+    if (rec) {
+        const unsigned long long base = atomicAdd(a.sink.count, (unsigned long long)__popc(rec));
+        uint32_t o = 0;
+#pragma unroll
+        for (int j = 0; j < PgHitBatch::CAP; ++j) {
+            if ((rec >> j) & 1u) {
+                const unsigned long long idx = base + o++;
+                if (idx < a.sink.cap) {
+                    spmb_hit h;
+                    h.end = b.ent[j] >> 8; h.seq_id = seq; h.pattern_id = pid; h.errors = (uint32_t)(b.ent[j] & 255ull);
+                    h.reserved = slot[j] + 1u; // 0 for a plain record
+                    a.sink.hits[idx] = h;
+                }
+            }
+        }
+    }
+    b.n = 0;
+}
+
+// behind pigeon_verify_kernel: the records that claimed a slot take the slot's minimum
+__global__ void __launch_bounds__(256) pigeon_fixup_kernel(spmb_hit *__restrict__ hits, const unsigned long long *__restrict__ count,
+                                                           unsigned long long cap, const uint32_t *__restrict__ dd_err)
+{
+    const unsigned long long n = min(*count, cap);
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * blockDim.x) {
+        const uint32_t r = hits[i].reserved;
+        if (r) {
+            hits[i].errors = 256u - dd_err[r - 1];
+            hits[i].reserved = 0;
+        }
+    }
 }
 
 // symbol at offset d (>= 0) from (row R, column col); a plain text runs on into the next rows
@@ -529,29 +578,36 @@ __device__ __forceinline__ void pg_load_eq(const uint32_t *__restrict__ eqp, uin
 }
 
 // SPMB_ALG_MYERS_FILTERED: Myers over the window [p-o-k, p-o+m+k) of every (candidate, seed) pair.
+// One thread per candidate; the kernel is a chain of ~m+2k dependent column updates per thread, so what counts is
+// the latency of one column, not the instruction count: round 1 fetched the needle's Eq row with four global loads
+// per column and located the text symbol with a division per column -- 76 us for the C5 text, and just as long for
+// 1/8 of it (a latency chain does not shrink with the shard: the bulk of C5's poor strong scaling).  Now the Eq rows
+// of the thread's needle sit in shared memory (one LDS.128 per column), the text is walked chunk by chunk (32
+// symbols per 8-byte load, the next chunk already on its way), and rows advance without a division.
 template <int NW, int MODE>
 __global__ void __launch_bounds__(128) pigeon_verify_kernel(PigeonVerifyArgs a)
 {
     constexpr int NWP = (NW <= 4) ? 4 : 8;
+    __shared__ __align__(16) uint32_t s_eq[128][4 * NWP + 4]; // +4 words: rows of neighbouring threads on different banks
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicMax(a.counters + 2, a.counters[1]);
     const unsigned long long n_cand = min(a.counters[1], a.cand_cap);
-    const uint32_t RL = a.lay.row_len;
-    PgReader rd{a.lanes, RL >> 5};
+    const uint32_t RL = a.lay.row_len, rl32 = RL >> 5;
+    uint32_t *my_eq = s_eq[threadIdx.x];
     for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_cand;
          i += (unsigned long long)gridDim.x * blockDim.x) {
         const PigeonCand cd = a.cand[i];
-        const uint64_t R = spmb_div_rl(a.lay, cd.pos);
-        const uint32_t col = (uint32_t)(cd.pos - R * RL);
-        // coordinates: plain = absolute text positions, windows = columns of row R
+        const uint64_t R0 = spmb_div_rl(a.lay, cd.pos);
+        const uint32_t col = (uint32_t)(cd.pos - R0 * RL);
+        // coordinates: plain = absolute text positions, windows = columns of row R0
         const int64_t p = (MODE == SPMB_MODE_PLAIN) ? (int64_t)cd.pos : (int64_t)col;
-        const int64_t text_end = (MODE == SPMB_MODE_PLAIN) ? (int64_t)a.lay.n : (int64_t)a.row_len[R];
+        const int64_t text_end = (MODE == SPMB_MODE_PLAIN) ? (int64_t)a.lay.n : (int64_t)a.row_len[R0];
         int64_t own_lo, own_hi; // of the last symbol index of a hit
         uint32_t seq = a.seq_id;
         if (MODE == SPMB_MODE_PLAIN) { own_lo = (int64_t)a.own_lo; own_hi = (int64_t)a.own_hi; }
         else {
-            own_lo = a.row_own ? (int64_t)a.row_own[R] - 1 : 0;
+            own_lo = a.row_own ? (int64_t)a.row_own[R0] - 1 : 0;
             own_hi = text_end;
-            if (a.row_seq) seq = a.row_seq[R];
+            if (a.row_seq) seq = a.row_seq[R0];
         }
         for (uint32_t s = a.pg.ufirst[cd.u]; s < a.pg.ufirst[cd.u + 1]; ++s) {
             const uint32_t pid = a.pg.seed_pat[s], o = a.pg.seed_off[s];
@@ -561,23 +617,67 @@ __global__ void __launch_bounds__(128) pigeon_verify_kernel(PigeonVerifyArgs a)
             if (ws < 0) ws = 0;
             if (we > text_end) we = text_end;
             if (we <= own_lo || ws >= own_hi) continue;
-            const uint32_t *eqp = a.eq + (size_t)pid * 4 * NWP;
+            {   // this needle's Eq rows -> the thread's shared-memory row
+                const uint4 *eg = reinterpret_cast<const uint4 *>(a.eq + (size_t)pid * 4 * NWP);
+#pragma unroll
+                for (int q = 0; q < NWP; ++q) reinterpret_cast<uint4 *>(my_eq)[q] = __ldg(eg + q);
+            }
+            // first chunk of the window: row / chunk index / offset inside the chunk
+            uint64_t Rw = R0;
+            uint32_t cw, ow;
+            if (MODE == SPMB_MODE_PLAIN) {
+                Rw = spmb_div_rl(a.lay, (uint64_t)ws);
+                const uint32_t c0 = (uint32_t)((uint64_t)ws - Rw * RL);
+                cw = c0 >> 5; ow = c0 & 31u;
+            } else { cw = (uint32_t)ws >> 5; ow = (uint32_t)ws & 31u; }
+            uint2 cur = spmb_chunk(a.lanes, rl32, Rw, cw);
             uint32_t vp[NW], vn[NW];
 #pragma unroll
             for (int w = 0; w < NW; ++w) { vp[w] = 0xffffffffu; vn[w] = 0; }
             int score = (int)pm.m;
-            for (int64_t t = ws; t < we; ++t) {
-                uint32_t c;
-                if (MODE == SPMB_MODE_PLAIN) {
-                    const uint64_t Rt = spmb_div_rl(a.lay, (uint64_t)t);
-                    c = rd.at(Rt, (uint32_t)((uint64_t)t - Rt * RL));
-                } else c = rd.at(R, (uint32_t)t);
-                uint32_t eq[NW], hp[NW], hn[NW];
-                pg_load_eq<NW>(eqp, c, eq);
-                pg_myers_col<NW, false>(vp, vn, eq, hp, hn);
-                score += pg_score_delta<NW>(hp, hn, pm.m);
-                if (score <= k && t >= own_lo && t < own_hi) pg_emit_min(a, (uint64_t)(t + 1), seq, pid, (uint32_t)score);
+            int64_t t = ws;
+            PgHitBatch hb;
+            while (t < we) {
+                // the chunk behind this one (plain text: rows follow one another; a window row simply ends)
+                uint32_t cn = cw + 1;
+                uint64_t Rn = Rw;
+                if (cn == rl32 && MODE == SPMB_MODE_PLAIN) { cn = 0; ++Rn; }
+                const int nb = (int)min((int64_t)(32 - ow), we - t);
+                uint2 nxt = make_uint2(0, 0);
+                if (t + nb < we) nxt = spmb_chunk(a.lanes, rl32, Rn, cn);
+                unsigned long long W = (((unsigned long long)cur.x << 32) | cur.y) << (2 * ow);
+                for (int j = 0; j < nb; ++j) {
+                    const uint32_t c = (uint32_t)(W >> 62);
+                    W <<= 2;
+                    uint32_t eq[NW], hp[NW], hn[NW];
+                    const uint4 e0 = *reinterpret_cast<const uint4 *>(my_eq + c * NWP);
+                    eq[0] = e0.x;
+                    if (NW > 1) eq[1 % NW] = e0.y;
+                    if (NW > 2) eq[2 % NW] = e0.z;
+                    if (NW > 3) eq[3 % NW] = e0.w;
+                    if (NW > 4) {
+                        const uint4 e1 = *reinterpret_cast<const uint4 *>(my_eq + c * NWP + 4);
+                        eq[4 % NW] = e1.x;
+                        if (NW > 5) eq[5 % NW] = e1.y;
+                        if (NW > 6) eq[6 % NW] = e1.z;
+                        if (NW > 7) eq[7 % NW] = e1.w;
+                    }
+                    pg_myers_col<NW, false>(vp, vn, eq, hp, hn);
+                    score += pg_score_delta<NW>(hp, hn, pm.m);
+                    const int64_t tt = t + j;
+                    if (score <= k && tt >= own_lo && tt < own_hi) {
+                        if (hb.n == PgHitBatch::CAP) pg_batch_flush(a, hb, seq, pid); // a hit-dense window
+                        // constant indices only: the batch stays in registers
+#pragma unroll
+                        for (int q = 0; q < PgHitBatch::CAP; ++q)
+                            if (q == hb.n) hb.ent[q] = ((unsigned long long)(tt + 1) << 8) | (unsigned long long)min(score, 255);
+                        ++hb.n;
+                    }
+                }
+                t += nb;
+                ow = 0; cw = cn; Rw = Rn; cur = nxt;
             }
+            pg_batch_flush(a, hb, seq, pid);
         }
     }
 }

@@ -168,7 +168,6 @@ struct spmb_hits {
     PigeonCand *d_cand = nullptr;          // candidate buffer of the seed filter (grown on demand)
     unsigned long long cand_cap = 0;
     unsigned long long *d_dd_keys = nullptr; // duplicate-suppression table of the filtered Myers path (pigeon.cuh pg_emit_min)
-    uint32_t *d_dd_idx = nullptr;
     std::vector<spmb_hit> host;
     uint64_t count = 0;
     const spmb_store *pend_store = nullptr;
@@ -686,13 +685,18 @@ int spmb_store_create_journaled_ex(spmb_context *ctx, const spmb_store *base, co
     int64_t *d_blk = nullptr;
     int *d_bad = nullptr;
     uint8_t *d_pool = nullptr;
+    uint2 *d_poolw = nullptr, *d_chunks = nullptr; // the pool as 2-bit words; the derived sequence as linear lane-chunk words
+    size_t chunk_bytes = 0;
     void *d_tmp = nullptr;
     size_t d_tmp_bytes = 0;
     spmb_store *s = nullptr;
     int rc = SPMB_OK;
     cudaError_t e = cudaSuccess;
     size_t blk_bytes = 0;
-    auto cleanup = [&]() { big_free(ctx, d_blk, blk_bytes); d_blk = nullptr; }; // everything else lives in the context's scratch block
+    auto cleanup = [&]() { // everything else lives in the context's scratch block
+        big_free(ctx, d_blk, blk_bytes); d_blk = nullptr;
+        big_free(ctx, d_chunks, chunk_bytes); d_chunks = nullptr;
+    };
 #define JCU(call) do { if (e == cudaSuccess) e = (call); } while (0)
     const bool trace = UploadPool::env_u64("SPMB_UPLOAD_TRACE", 0) != 0;
     auto tnow = [] { return std::chrono::steady_clock::now(); };
@@ -706,7 +710,8 @@ int spmb_store_create_journaled_ex(spmb_context *ctx, const spmb_store *base, co
         auto up = [](size_t x) { return (x + 255) / 256 * 256; };
         const size_t o_ev = 0, o_delta = o_ev + up(ne * sizeof(spmb_journal_event)), o_shift = o_delta + up(ne * 8),
                      o_total = o_shift + up(ne * 8), o_bad = o_total + 256, o_pool = o_bad + 256,
-                     o_tmp = o_pool + up(pool_len + 1), o_end = o_tmp + up(tmp_bytes + 1);
+                     o_poolw = o_pool + up(pool_len + 1), o_tmp = o_poolw + up(((pool_len + 31) / 32 + 2) * sizeof(uint2)),
+                     o_end = o_tmp + up(tmp_bytes + 1);
         uint8_t *sc = nullptr;
         JCU(ctx_scratch(ctx, o_end, &sc));
         if (e != cudaSuccess) { cudaGetLastError(); return set_err(ctx, SPMB_ERR_OOM, "journal scratch", e); }
@@ -717,13 +722,21 @@ int spmb_store_create_journaled_ex(spmb_context *ctx, const spmb_store *base, co
         d_total = (long long *)(sc + o_total);
         d_bad = (int *)(sc + o_bad);
         d_pool = sc + o_pool;
+        d_poolw = (uint2 *)(sc + o_poolw);
         d_tmp = sc + o_tmp;
         d_tmp_bytes = tmp_bytes;
     }
     JCU(cudaMemsetAsync(d_total, 0, 16, sm));
     JCU(cudaMemsetAsync(d_bad, 0, 16, sm));
     const auto tj1 = tnow();
-    if (pool_len) JCU(cudaMemcpyAsync(d_pool, pool, pool_len, cudaMemcpyHostToDevice, sm));
+    JCU(cudaMemsetAsync(d_poolw, 0, ((pool_len + 31) / 32 + 2) * sizeof(uint2), sm));
+    if (pool_len) {
+        JCU(cudaMemcpyAsync(d_pool, pool, pool_len, cudaMemcpyHostToDevice, sm));
+        if (e == cudaSuccess) { // inserted runs are fetched like base runs: 32 symbols per word pair
+            bytes_to_chunks_kernel<<<(unsigned)(((pool_len + 31) / 32 + 255) / 256), 256, 0, sm>>>(d_pool, pool_len, d_poolw);
+            ctx->launches++;
+        }
+    }
     // long event tables take the upload queue (copy engine + host threads that shrink 24-byte events to 8)
     if (e == cudaSuccess && n_ev * sizeof(spmb_journal_event) >= UploadPool::env_u64("SPMB_UPLOAD_MIN", 32ull << 20) &&
         ensure_upload(ctx) == SPMB_OK)
@@ -766,12 +779,20 @@ int spmb_store_create_journaled_ex(spmb_context *ctx, const spmb_store *base, co
         rc = store_ensure_lanes(ctx, base);
         uint2 *l = nullptr;
         if (rc == SPMB_OK && big_alloc(ctx, s->bytes, (void **)&l) != cudaSuccess) { cudaGetLastError(); l = nullptr; }
-        if (rc == SPMB_OK) {
-            JournalSource src{base->lanes, base->lay, d_ev, d_der, d_blk, d_pool, n_ev, n_der};
-            pack_chunks_kernel<JournalSource><<<(unsigned)(s->lay.n_cols_alloc / 1024), 1024, 0, sm>>>(src, s->lay, s->planes, l);
-            ctx->launches++;
+        chunk_bytes = ((n_der + 31) / 32 + 2) * sizeof(uint2);
+        if (rc == SPMB_OK) JCU(big_alloc(ctx, chunk_bytes, (void **)&d_chunks));
+        if (rc == SPMB_OK && e == cudaSuccess) {
+            JournalDeriveArgs ja{base->lanes, base->lay, d_ev, d_der, d_blk, d_poolw, n_ev, n_der, d_chunks};
+            const uint64_t warps = (n_der + 1023) >> 10;
+            const unsigned grid = (unsigned)std::min<uint64_t>((warps + 7) / 8, (uint64_t)ctx->sm_count * 32);
+            if (n_der) journal_derive_kernel<<<grid, 256, 0, sm>>>(ja);
+            ChunkSource src{d_chunks, n_der};
+            pack_chunks_kernel<ChunkSource><<<(unsigned)(s->lay.n_cols_alloc / 1024), 1024, 0, sm>>>(src, s->lay, s->planes, l);
+            ctx->launches += 2;
             JCU(cudaGetLastError());
             s->lanes = l;
+        } else if (l) {
+            big_free(ctx, l, s->bytes);
         }
     }
     const auto tj4 = tnow();
@@ -1252,7 +1273,7 @@ extern "C" int spmb_hits_destroy(spmb_hits *h)
     if (h->ctx) cudaSetDevice(h->ctx->device);
     cudaFree(h->d_hits);
     cudaFree(h->d_count);
-    cudaFree(h->d_dd_keys); cudaFree(h->d_dd_idx);
+    cudaFree(h->d_dd_keys);
     cudaFree(h->d_cand);
     cudaFree(h->ord_k0); cudaFree(h->ord_k1); cudaFree(h->ord_i0); cudaFree(h->ord_i1); cudaFree(h->ord_isel);
     cudaFree(h->ord_flag); cudaFree(h->ord_out); cudaFree(h->ord_tmp);
@@ -1384,19 +1405,19 @@ static cudaError_t launch_verify(spmb_context *ctx, const spmb_pattern *p, const
 }
 
 static int bits_for(unsigned long long max_value);
-enum { SPMB_DD_BITS = 19 }; // slots of the duplicate-suppression table (6 MB, cleared per launch)
+enum { SPMB_DD_BITS = 17 }; // slots of the duplicate-suppression table (1.5 MB, cleared before every launch)
 
 // seed filter + (seed emission | windowed Myers verification) over the shard [st0, st1) of a store
 template <int MODE>
 static int enqueue_filtered(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p, spmb_hits *h,
-                            uint64_t st0, uint64_t st1, uint32_t seq_id, const HitSink &sink)
+                            uint64_t st0, uint64_t st1, uint32_t seq_id, const HitSink &sink, bool counters_fresh)
 {
     if (st1 <= st0 || p->pg.seed_pat.empty()) return SPMB_OK;
     int rc = store_ensure_lanes(ctx, s);
     if (rc) return rc;
     rc = cand_reserve(ctx, h, 1ull << 16);
     if (rc) return rc;
-    CU(cudaMemsetAsync(h->d_count + 1, 0, sizeof(unsigned long long), ctx->stream));
+    if (!counters_fresh) CU(cudaMemsetAsync(h->d_count + 1, 0, sizeof(unsigned long long), ctx->stream));
     const uint64_t per_st = 32ull * s->lay.row_len;
     PigeonFilterArgs fa;
     fa.lanes = s->lanes; fa.lay = s->lay; fa.pg = pigeon_dev(p);
@@ -1428,31 +1449,33 @@ static int enqueue_filtered(spmb_context *ctx, const spmb_store *s, const spmb_p
     va.own_lo = st0 * per_st;
     va.own_hi = std::min<uint64_t>(s->lay.n, st1 * per_st);
     va.sink = sink;
-    va.dd_keys = nullptr; va.dd_idx = nullptr; va.dd_bits = SPMB_DD_BITS; va.dd_end_bits = 0; va.dd_nseq = 1;
+    va.dd_keys = nullptr; va.dd_err = nullptr; va.dd_bits = SPMB_DD_BITS; va.dd_end_bits = 0; va.dd_nseq = 1;
     static const bool dd_off = getenv("SPMB_NO_DEDUP") != nullptr; // A/B switch
-    if (p->alg == SPMB_ALG_MYERS_FILTERED && !dd_off && h->cap < (1ull << 31)) {
+    if (p->alg == SPMB_ALG_MYERS_FILTERED && !dd_off && h->cap < (1ull << 31) && p->k < 255) {
         const uint64_t n_seq = (MODE == SPMB_MODE_PLAIN) ? 1 : (uint64_t)s->seq_base + s->lay.n_st * 32;
         const uint64_t max_end = (MODE == SPMB_MODE_PLAIN) ? s->lay.n : s->lay.row_len;
         const int eb = bits_for(max_end + 1);
         if (bits_for((uint64_t)p->n_pat * n_seq) + eb <= 62) {
-            if (!h->d_dd_keys) {
-                if (cudaMalloc(&h->d_dd_keys, sizeof(unsigned long long) << SPMB_DD_BITS) != cudaSuccess ||
-                    cudaMalloc(&h->d_dd_idx, sizeof(uint32_t) << SPMB_DD_BITS) != cudaSuccess) {
-                    cudaGetLastError();
-                    cudaFree(h->d_dd_keys); cudaFree(h->d_dd_idx);
-                    h->d_dd_keys = nullptr; h->d_dd_idx = nullptr;
-                }
+            if (!h->d_dd_keys && cudaMalloc(&h->d_dd_keys, (size_t)12 << SPMB_DD_BITS) != cudaSuccess) { // 8-byte keys, 4-byte minima
+                cudaGetLastError();
+                h->d_dd_keys = nullptr;
             }
             if (h->d_dd_keys) {
-                CU(cudaMemsetAsync(h->d_dd_keys, 0, sizeof(unsigned long long) << SPMB_DD_BITS, ctx->stream));
-                CU(cudaMemsetAsync(h->d_dd_idx, 0, sizeof(uint32_t) << SPMB_DD_BITS, ctx->stream));
-                va.dd_keys = h->d_dd_keys; va.dd_idx = h->d_dd_idx; va.dd_end_bits = (uint32_t)eb; va.dd_nseq = n_seq;
+                CU(cudaMemsetAsync(h->d_dd_keys, 0, (size_t)12 << SPMB_DD_BITS, ctx->stream));
+                va.dd_keys = h->d_dd_keys; va.dd_err = reinterpret_cast<uint32_t *>(h->d_dd_keys + ((size_t)1 << SPMB_DD_BITS));
+                va.dd_end_bits = (uint32_t)eb; va.dd_nseq = n_seq;
             }
         }
     }
     e = launch_verify<MODE>(ctx, p, va);
     if (e != cudaSuccess) return set_err(ctx, SPMB_ERR_CUDA, "pigeon verify launch", e);
     ctx->launches += 2;
+    if (va.dd_keys) { // every record that claimed a table slot takes the slot's minimum
+        const unsigned fgrid = (unsigned)std::min<unsigned long long>((sink.cap + 255) / 256, (unsigned long long)ctx->sm_count * 4);
+        pigeon_fixup_kernel<<<fgrid ? fgrid : 1, 256, 0, ctx->stream>>>(sink.hits, sink.count, sink.cap, va.dd_err);
+        ctx->launches++;
+        CU(cudaGetLastError());
+    }
     return SPMB_OK;
 }
 
@@ -1589,8 +1612,8 @@ static int enqueue_search(spmb_context *ctx, const spmb_store *s, const spmb_pat
         return enqueue_prefix(ctx, s, p, nullptr, 1, seq_id, sink);
     }
     if (p->filtered) { // SPMB_ALG_PIGEONHOLE, SPMB_ALG_MYERS_FILTERED with a usable q
-        return (s->lay.mode == SPMB_MODE_PLAIN) ? enqueue_filtered<SPMB_MODE_PLAIN>(ctx, s, p, h, st0, st1, seq_id, sink)
-                                                : enqueue_filtered<SPMB_MODE_WINDOWS>(ctx, s, p, h, st0, st1, seq_id, sink);
+        return (s->lay.mode == SPMB_MODE_PLAIN) ? enqueue_filtered<SPMB_MODE_PLAIN>(ctx, s, p, h, st0, st1, seq_id, sink, reset)
+                                                : enqueue_filtered<SPMB_MODE_WINDOWS>(ctx, s, p, h, st0, st1, seq_id, sink, reset);
     }
     if (p->alg == SPMB_ALG_PIGEONHOLE) return SPMB_OK; // no usable q-gram
     if (p->alg == SPMB_ALG_MYERS || p->alg == SPMB_ALG_MYERS_FILTERED) {
@@ -1821,7 +1844,7 @@ static int hits_order_device(spmb_context *ctx, spmb_hits *h, const spmb_store *
                              unsigned long long cnt, uint64_t n_seq, std::vector<spmb_hit> &out, bool *done)
 {
     *done = false;
-    if (cnt < 4096 || cnt >= (1ull << 31)) return SPMB_OK;
+    if (cnt < SPMB_ORDER_AT_LAUNCH_MIN || cnt >= (1ull << 31)) return SPMB_OK; // shorter lists: host radix sort (~10 ns per hit)
     const int alg = p->alg;
     const uint64_t max_end = (s->lay.mode == SPMB_MODE_PLAIN) ? s->lay.n : s->lay.row_len;
     HitKeySpec spec;
@@ -2552,12 +2575,20 @@ extern "C" int spmb_stream_submit(spmb_context *ctx, spmb_stream *st, const uint
         if (a) memcpy(S.hd.sym, host_ranks, (size_t)a);
         S.bulk = n - a;
         S.host = host_ranks + a;
-        if (S.bulk >= UploadPool::env_u64("SPMB_UPLOAD_MIN", 32ull << 20) && ensure_upload(ctx) == SPMB_OK) {
-            // cut fine enough that every mover gets several chunks of this feed
+        // the pool stays warm from feed to feed, so a stream takes it from 4 Mi symbols on (a one-shot upload: 32 Mi)
+        const uint64_t pool_min = UploadPool::env_u64("SPMB_STREAM_UPLOAD_MIN", std::min<uint64_t>(4ull << 20, UploadPool::env_u64("SPMB_UPLOAD_MIN", 32ull << 20)));
+        if (S.bulk >= pool_min && ensure_upload(ctx) == SPMB_OK) {
+            // about two chunks per mover and feed: the movers run on into the next feed's job, so a feed needs no fine
+            // cut to keep them level, and every chunk costs three driver calls that all movers' threads contend for
+            // (512 Ki-symbol chunks: 64 Mi-symbol feeds at 0.52 of the one-shot rate).  The copy engine's share of RAW
+            // chunks is capped: a one-shot upload finds its share (~16 % here) by racing the packing threads, but in a
+            // stream the raw mover reaches the next job while they are still in the previous one and would take half of
+            // it at four times the PCIe bytes per symbol (traced: 8 of 17 chunks, packing threads idle).
             const uint64_t movers = (uint64_t)ctx->upload->n_workers + 1;
-            uint64_t chunk = S.bulk / (8 * movers);
-            if (chunk < (256u << 10)) chunk = 256u << 10;
-            if (!ctx->upload->submit_text(S.host, S.bulk, S.d_words + (t + a) / 32, chunk, &S.job_seq))
+            uint64_t chunk = S.bulk / (2 * movers);
+            if (chunk < (1u << 20)) chunk = 1u << 20;
+            static const uint64_t raw_pct = UploadPool::env_u64("SPMB_STREAM_RAW_PCT", 15);
+            if (!ctx->upload->submit_text(S.host, S.bulk, S.d_words + (t + a) / 32, chunk, &S.job_seq, raw_pct))
                 return set_err(ctx, SPMB_ERR_CUDA, "stream upload: job ring full");
             S.job = true;
         }

@@ -415,7 +415,7 @@ struct UploadPool {
 
     // host_ranks[0, n_sym) -> dst[0, ceil(n/32)) (device memory every stream may touch already).  chunk = 0: chunk_sym;
     // else the chunk size of this job (multiple of 1024, <= chunk_sym).  false: the ring is full (wait() first).
-    bool submit_text(const uint8_t *host_ranks, uint64_t n_sym, uint2 *dst, uint64_t chunk, uint64_t *seq_out)
+    bool submit_text(const uint8_t *host_ranks, uint64_t n_sym, uint2 *dst, uint64_t chunk, uint64_t *seq_out, uint64_t raw_pct = 0)
     {
         uint64_t seq;
         Job *J = begin_job(seq);
@@ -423,7 +423,7 @@ struct UploadPool {
         J->src = host_ranks; J->n = n_sym; J->d_chunks = dst;
         J->chunk = (chunk == 0 || chunk > chunk_sym) ? chunk_sym : std::max<uint64_t>(1024, chunk / 1024 * 1024);
         J->n_chunks = (n_sym + J->chunk - 1) / J->chunk;
-        J->raw_pct = raw_pct_text;
+        J->raw_pct = raw_pct ? std::min(raw_pct, raw_pct_text) : raw_pct_text;
         job_chunk = J->chunk;
         commit_job(*J);
         *seq_out = seq;

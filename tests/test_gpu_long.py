@@ -49,7 +49,7 @@ def test_long_needles_equal_the_oracle(ctx, m, k):
     text[n - m + 7:] = pat[:m - 7]
     store = sp.Store.from_host(ctx, text)
     we, wr = orc.myers(text, pat, k)
-    assert len(we) > 20
+    assert len(we) > (20 if k else 1)
     p = sp.Pattern(ctx, sp.ALG_MYERS, pat, k)
     assert p.window_size == m + k
     got = sp.search(ctx, store, p)

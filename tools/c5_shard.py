@@ -20,6 +20,7 @@ ap.add_argument("--n", type=int, default=3_000_000_000)
 ap.add_argument("--patterns", type=int, default=10_000)
 ap.add_argument("--steps", type=int, default=20)
 ap.add_argument("--out", default="profiles/r02_c5_shards.json")
+ap.add_argument("--only", type=int, default=0, help="one shard count only (launch lists)")
 args = ap.parse_args()
 dev = torch.device("cuda", 0)
 stream = torch.cuda.Stream(device=dev)
@@ -33,7 +34,7 @@ with torch.cuda.stream(stream):
     del text
     pset = sp.Pattern(ctx, sp.ALG_MYERS_FILTERED, pats, 3)
     sp.search(ctx, store, pset, hits)
-    for N in (1, 2, 4, 8):
+    for N in ((args.only,) if args.only else (1, 2, 4, 8)):
         worst = None
         for r in sorted({0, N // 2, N - 1}):
             ctx.set_shard(r, N)
@@ -44,8 +45,8 @@ with torch.cuda.stream(stream):
         res["shards"][str(N)] = worst
         print(N, worst, flush=True)
     ctx.set_shard(0, 1)
-    one = res["shards"]["1"]["ms_per_step"]
-    for N in (2, 4, 8):
+    one = res["shards"].get("1", {}).get("ms_per_step", 0.0)
+    for N in (() if args.only else (2, 4, 8)):
         res["shards"][str(N)]["efficiency"] = one / (N * res["shards"][str(N)]["ms_per_step"])
 os.makedirs(os.path.dirname(args.out) or ".", exist_ok=True)
 json.dump(res, open(args.out, "w"), indent=1)

@@ -1,0 +1,10 @@
+#!/bin/bash
+set -u
+mkdir -p gpurun_out
+timeout 1200 python -m pytest tests -m gpu -q --maxfail=10 -p no:cacheprovider > gpurun_out/pytest6.log 2>&1
+echo "pytest rc=$?"; tail -4 gpurun_out/pytest6.log
+timeout 600 python tools/c5_shard.py --out gpurun_out/c5_shards6.json > gpurun_out/c5_shards6.log 2>&1
+echo "c5 rc=$?"; tail -5 gpurun_out/c5_shards6.log | head -4
+timeout 600 python tools/c5_shard.py --steps 4 --only 8 --out gpurun_out/c5_tmp.json > /dev/null 2>&1 &&
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/c5_n8_launches6.csv python tools/c5_shard.py --steps 4 --only 8 --out gpurun_out/c5_tmp.json > /dev/null 2>&1
+echo "c5 launches rc=$?"
