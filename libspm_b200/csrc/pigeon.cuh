@@ -39,10 +39,13 @@
 // shared host/device definitions
 // ------------------------------------------------------------------------------------------
 // q-gram key: symbol j of the q-gram at bits [63-2j, 62-2j] of (hi:lo), zero below (kq <= 32 symbols)
-// bitmap hash of a key (lo already masked to the key): two IMADs, FMA-pipe work that co-issues with the
-// ALU-pipe shifts of the scan loop (tools/ubench_pipes.cu: LOP3:IMAD 1:1 runs at 2 x 18.4 T/s, whereas
-// IMAD.HI is half rate and stalls the ALU pipe -- so no multiply-high anywhere in the loop)
-SPMB_HD uint32_t pg_h1(uint32_t hi, uint32_t lo) { return hi * 0x9E3779B1u + lo * 0x85EBCA77u; }
+// First-level bitmap (shared memory): hashed on the key's first min(kq, 16) symbols only -- `hi`, already in a
+// register, one IMAD; a q-gram longer than 16 symbols differs from a seed behind them once in 4^16 positions, and
+// the exact lookup behind the bitmap compares the whole key anyway.  The bitmap holds 2^B bits (B <= 20: 128 KB):
+// x = h >> (32 - B) picks the word (x >> 5) and one bit (x & 31), h & 31 a second one for wide keys.  A bitmap of
+// any size through a multiply-high of the hash (192 KB would halve the false positives) was measured and dropped:
+// IMAD.HI made the scan 36 % slower, whatever the size.
+SPMB_HD uint32_t pg_h1(uint32_t hi) { return hi * 0x9E3779B1u; }
 SPMB_HD uint32_t pg_h3(uint32_t hi, uint32_t lo) // second-level bitmap
 {
     uint32_t h = (hi ^ 0x7F4A7C15u) * 0x85EBCA6Bu + (lo ^ 0x165667B1u) * 0xC2B2AE35u;
@@ -120,7 +123,6 @@ struct PigeonHost {
         // bitmap: ~32 bits per unique q-gram, 2^15 .. 2^20 bits (4 KB .. 128 KB of shared memory)
         B = 15;
         while (B < 20 && (1ull << B) < n_unique * 32) ++B;
-        // a q-gram of kq symbols has only 4^kq values: no point in more bits than that (x4)
         bitmap.assign((size_t)1 << (B - 5), 0);
         T = 4;
         while ((1ull << T) < n_unique * 2 + 1) ++T;
@@ -133,7 +135,7 @@ struct PigeonHost {
         const uint32_t tmask = (1u << T) - 1;
         for (size_t u = 0; u < ukeys.size(); ++u) {
             const uint32_t hi = (uint32_t)(ukeys[u] >> 32), lo = (uint32_t)ukeys[u];
-            const uint32_t h = kq > 16 ? pg_h1(hi, lo) : hi * 0x9E3779B1u;
+            const uint32_t h = pg_h1(hi);
             const uint32_t x = h >> (32 - B);
             bitmap[x >> 5] |= 0x80000000u >> (x & 31);
             if (kq > 16) bitmap[x >> 5] |= 0x80000000u >> (h & 31); // second bit, same word (wide keys)
@@ -263,7 +265,7 @@ __global__ void __launch_bounds__(1024, 1) pigeon_filter_kernel(PigeonFilterArgs
     uint32_t *s_q = s_bits + n_words + warp * PG_QCAP;
     const uint32_t RL = a.lay.row_len, rl32 = RL >> 5;
     const uint32_t shift = 32 - a.pg.B;
-    const uint32_t himask = a.pg.himask, lomask = a.pg.lomask;
+    const uint32_t himask = a.pg.himask;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint2 *__restrict__ lp = a.lanes;
 
@@ -273,7 +275,6 @@ __global__ void __launch_bounds__(1024, 1) pigeon_filter_kernel(PigeonFilterArgs
     const uint64_t t0 = T / n_warps * gw + min(gw, T % n_warps);
     const uint64_t t1 = t0 + T / n_warps + (gw < T % n_warps ? 1 : 0);
     if (t0 >= t1) return; // no block-wide synchronisation below
-    (void)himask;
 
     uint32_t qn = 0; // queue fill, warp-uniform
     auto drain = [&]() {
@@ -302,18 +303,16 @@ __global__ void __launch_bounds__(1024, 1) pigeon_filter_kernel(PigeonFilterArgs
         uint32_t acc = 0;
 #pragma unroll
         for (int j = 0; j < 32; j += STEP) {
-            uint32_t hi, lo;
-            pg_window(cur, nxt, j, hi, lo);
-            if (WIDE) {
-                const uint32_t h = pg_h1(hi, lo & lomask);
-                const uint32_t word = s_bits[h >> (shift + 5)];
-                const uint32_t tt = (word << ((h >> shift) & 31u)) & (word << (h & 31u));
-                acc = __funnelshift_l(tt, acc, 1); // sampled position k = j/STEP ends at bit 32/STEP-1-k
-            } else {
-                const uint32_t h = (hi & himask) * 0x9E3779B1u;
-                const uint32_t word = s_bits[h >> (shift + 5)];
-                acc = __funnelshift_l(word << ((h >> shift) & 31u), acc, 1);
-            }
+            // the 16 symbols from symbol j on (compile-time j: one funnel shift)
+            const uint32_t wa = j < 16 ? cur.x : cur.y, wb = j < 16 ? cur.y : nxt.x;
+            const uint32_t hi = __funnelshift_l(wb, wa, 2 * (j & 15));
+            const uint32_t h = pg_h1(WIDE ? hi : (hi & himask));
+            const uint32_t x = h >> shift;
+            const uint32_t word = s_bits[x >> 5];
+            // bit b of the word is its bit 31-b: shifted to the top (a funnel shift takes its amount mod 32)
+            uint32_t tt = __funnelshift_l(0u, word, x);
+            if (WIDE) tt &= __funnelshift_l(0u, word, h);
+            acc = __funnelshift_l(tt, acc, 1); // sampled position k = j/STEP ends at bit 32/STEP-1-k
         }
         // ---- park the survivors of this chunk: one warp prefix sum hands every lane its queue slots ----
         const uint32_t cnt = __popc(acc);

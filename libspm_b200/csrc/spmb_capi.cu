@@ -229,6 +229,7 @@ struct spmb_stream {
 // ------------------------------------------------------------------------------------------
 // helpers
 // ------------------------------------------------------------------------------------------
+static int bits_for(unsigned long long max_value);
 static int set_err(spmb_context *ctx, int code, const char *what, cudaError_t e = cudaSuccess)
 {
     if (ctx) {

@@ -243,9 +243,13 @@ struct UploadPool {
         if (threads_override >= 0) n_workers = threads_override; // spmb_context_set_upload_threads
         if (n_workers > 256) n_workers = 256;
         cudaError_t e = cudaStreamCreateWithFlags(&raw_stream, cudaStreamNonBlocking);
+        // the raw mover spends its life waiting for the link: it sleeps in those waits (blocking events) and leaves
+        // its core to the caller's thread -- packing threads + raw mover + caller are one thread more than the default
+        // thread count leaves cores, and a packing thread that lost its core for a time slice held a whole stream
+        // feed back by 0.3-0.6 ms (traced)
         for (int s = 0; s < SLOTS && e == cudaSuccess; ++s) {
             e = cudaMalloc(&d_slot[s], chunk_sym);
-            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&slot_ev[s], ev_flags);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&slot_ev[s], cudaEventDisableTiming | cudaEventBlockingSync);
         }
         for (int r = 0; r < RING && e == cudaSuccess; ++r) e = cudaEventCreateWithFlags(&raw_job_ev[r], cudaEventDisableTiming);
         workers.resize(n_workers);
@@ -268,11 +272,11 @@ struct UploadPool {
 
     // wait for job `seq` to be submitted (a short poll first: a stream of feeds hands in the next job within
     // microseconds, and a condition-variable wake-up costs 30-60 us per mover and feed); false = quit
-    bool next_job(uint64_t seq)
+    bool next_job(uint64_t seq, bool spin)
     {
         if (submitted.load(std::memory_order_acquire) > seq) return true;
         const auto t0 = std::chrono::steady_clock::now();
-        while (std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t0).count() < (long long)spin_us) {
+        while (spin && std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - t0).count() < (long long)spin_us) {
             if (submitted.load(std::memory_order_acquire) > seq) return true;
 #if defined(__x86_64__)
             __builtin_ia32_pause();
@@ -299,7 +303,7 @@ struct UploadPool {
         };
         int b = 0, s = 0; // next pinned buffer (packing thread) / staging slot (raw mover): carried from job to job
         for (uint64_t seq = 0;; ++seq) {
-            if (!next_job(seq)) return;
+            if (!next_job(seq, w >= 0)) return;
             Job &J = jobs[seq % RING];
             const int r = (int)(seq % RING);
             cudaError_t e = cudaSuccess;
