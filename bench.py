@@ -131,59 +131,78 @@ def dist_env():
 
 
 class HitGather:
-    """the final gather of the ranks' small hit lists, inside the timed step: after a pass's
-    sorted hit list has reached the host, its first CAP records go pinned -> device -> all_gather -> pinned on a
-    side stream, so the collective of pass i runs beside the search kernels of pass i+1; rank 0 reads the merged
-    list one step later.  No collective touches the search itself."""
-    def __init__(self, torch, dist, dev, world, depth, cap=2048):
-        self.torch, self.dist, self.world, self.depth, self.CAP = torch, dist, world, depth, cap
+    """the final gather of the ranks' small hit lists (north_star item 4: "only a final gather of the
+    small hit lists"), INSIDE the timed region: every pass's sorted hit list is copied into a pinned buffer on its
+    rank as it arrives; when the last pass has been collected the lists of all passes travel in one piece -- pinned
+    -> device -> ONE all_gather -> pinned -- and every rank holds the merged lists before the region's closing event
+    is recorded.  No collective touches the search itself.  Buffers are sized during warm-up (largest per-pass list
+    over the ranks, with slack).  (A gather per pass was measured first: five torch calls and a collective per
+    0.14 ms pass made the step host-bound, 0.31 ms at N = 8.)"""
+    def __init__(self, torch, dist, dev, world):
+        self.torch, self.dist, self.dev, self.world = torch, dist, dev, world
         self.stream = torch.cuda.Stream(device=dev)
-        nbytes = 8 + self.CAP * 24
-        self.pin_in = [torch.zeros(nbytes, dtype=torch.uint8, pin_memory=True) for _ in range(depth)]
-        self.dev_in = [torch.zeros(nbytes, dtype=torch.uint8, device=dev) for _ in range(depth)]
-        self.dev_out = [torch.zeros(nbytes * world, dtype=torch.uint8, device=dev) for _ in range(depth)]
-        self.pin_out = [torch.zeros(nbytes * world, dtype=torch.uint8, pin_memory=True) for _ in range(depth)]
-        self.done = [torch.cuda.Event() for _ in range(depth)]
-        self.armed = [False] * depth
-        self.nbytes = nbytes
-        self.gathered = 0
+        self.cap = 0
+        self.gathers = 0
+        self.overflow = False
 
-    def submit(self, slot, hits):
-        torch = self.torch
-        n = min(len(hits), self.CAP)
-        buf = self.pin_in[slot].numpy()
-        buf[:8].view(np.uint64)[0] = n
-        if n:
-            buf[8:8 + n * 24] = np.ascontiguousarray(hits[:n]).view(np.uint8)
+    def prepare(self, n_first, passes):
+        """warm-up: agree on the per-pass capacity, allocate, run the collective once"""
+        torch, dist = self.torch, self.dist
         with torch.cuda.stream(self.stream):
-            self.dev_in[slot].copy_(self.pin_in[slot], non_blocking=True)
-            self.dist.all_gather_into_tensor(self.dev_out[slot], self.dev_in[slot])
-            self.pin_out[slot].copy_(self.dev_out[slot], non_blocking=True)
-            self.done[slot].record(self.stream)
-        self.armed[slot] = True
+            c = torch.tensor([int(n_first)], dtype=torch.int64, device=self.dev)
+            dist.all_reduce(c, op=dist.ReduceOp.MAX)
+            self.cap = int(c.item()) * 5 // 4 + 64
+        self.passes = passes
+        self.rec_bytes = self.cap * 24
+        nbytes = passes * (8 + self.rec_bytes)
+        self.pin_in = torch.zeros(nbytes, dtype=torch.uint8, pin_memory=True)
+        self.dev_in = torch.zeros(nbytes, dtype=torch.uint8, device=self.dev)
+        self.dev_out = torch.zeros(nbytes * self.world, dtype=torch.uint8, device=self.dev)
+        self.pin_out = torch.zeros(nbytes * self.world, dtype=torch.uint8, pin_memory=True)
+        self.nbytes = nbytes
+        self.finish()
 
-    def collect(self, slot, hit_dtype):
-        """merged list of the pass that used `slot` (every rank waits for its copy; rank 0's is the product)."""
-        if not self.armed[slot]:
-            return None
-        self.done[slot].synchronize()
-        self.armed[slot] = False
-        raw = self.pin_out[slot].numpy()
+    def add(self, i, hits):
+        n = len(hits)
+        if n > self.cap:
+            self.overflow = True
+            n = self.cap
+        buf = self.pin_in.numpy()
+        o = i * (8 + self.rec_bytes)
+        buf[o:o + 8].view(np.uint64)[0] = n
+        if n:
+            buf[o + 8:o + 8 + n * 24] = hits[:n].view(np.uint8).reshape(-1)
+
+    def finish(self):
+        """all ranks: one all_gather of every pass's list; returns the merged record count over ranks and passes"""
+        torch = self.torch
+        with torch.cuda.stream(self.stream):
+            self.dev_in.copy_(self.pin_in, non_blocking=True)
+            self.dist.all_gather_into_tensor(self.dev_out, self.dev_in)
+            self.pin_out.copy_(self.dev_out, non_blocking=True)
+        self.stream.synchronize()
+        counts = self.pin_out.numpy().reshape(self.world * self.passes, 8 + self.rec_bytes)[:, :8].copy().view(np.uint64)
+        self.gathers += 1
+        return int(counts.sum())
+
+    def merged(self, hit_dtype, i=0):
+        """the merged list of pass i (rank-major), for checks outside the timed region"""
+        raw = self.pin_out.numpy()
         parts = []
         for r in range(self.world):
-            b = raw[r * self.nbytes:(r + 1) * self.nbytes]
-            n = int(b[:8].view(np.uint64)[0])
-            parts.append(b[8:8 + n * 24].view(hit_dtype))
-        self.gathered += 1
+            o = r * self.nbytes + i * (8 + self.rec_bytes)
+            n = int(raw[o:o + 8].view(np.uint64)[0])
+            parts.append(raw[o + 8:o + 8 + n * 24].view(hit_dtype))
         return np.concatenate(parts)
 
 
 def time_search(sp, torch, ctx, stream, store, pattern, hits, steps, warmup, flush=None, gather=None):
-    """returns (total_ms for `steps` launch+finish passes, mean kernel ms, n_hits, launches/step).
+    """returns (total_ms for `steps` launch+finish passes (+ the final gather), mean kernel ms, n_hits, launches/step).
     The passes are pipelined the way the launch/finish pair of the C ABI is meant to be used: passes i+1 and
     i+2 are queued (on their own hit lists) before pass i's hits are collected, so the host's share of a pass
     (D2H of the counters + hit list, ordering) runs under the next kernels.  Every pass still delivers its
-    sorted hit list to the host; with `gather` (N > 1) every pass's list also travels to rank 0."""
+    sorted hit list to the host; with `gather` (N > 1) the lists of all passes travel to every rank in one final
+    all_gather before the closing event (HitGather)."""
     DEPTH = int(os.environ.get("SPMB_BENCH_DEPTH", "3"))   # passes in flight: two queued behind the one being collected
     hl = (hits,) + tuple(sp.Hits(ctx, 1 << 16) for _ in range(DEPTH - 1))
     for w in range(max(warmup, 2 * DEPTH)):     # every hit list twice: buffers sized, long-list ordering armed
@@ -191,9 +210,8 @@ def time_search(sp, torch, ctx, stream, store, pattern, hits, steps, warmup, flu
             flush.add_(1)
         sp.search_launch(ctx, store, pattern, hl[w % DEPTH])
         h = sp.search_finish(ctx, hl[w % DEPTH])
-        if gather is not None:
-            gather.submit(w % DEPTH, h)
-            gather.collect(w % DEPTH, sp.HIT_DTYPE)
+        if gather is not None and w == 0:
+            gather.prepare(len(h), steps)     # warm: capacity agreed, buffers, communicator
     ks = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
     ke = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -218,13 +236,9 @@ def time_search(sp, torch, ctx, stream, store, pattern, hits, steps, warmup, flu
         h = sp.search_finish(ctx, hl[i % DEPTH])
         n_hits = len(h)
         if gather is not None:
-            got = gather.collect(i % DEPTH, sp.HIT_DTYPE)      # the list of pass i - DEPTH
-            merged_hits = len(got) if got is not None else merged_hits
-            gather.submit(i % DEPTH, h)
-    if gather is not None:
-        for s in range(DEPTH):                                 # the last DEPTH gathers belong to the timed steps
-            got = gather.collect(s, sp.HIT_DTYPE)
-            merged_hits = len(got) if got is not None else merged_hits
+            gather.add(i, h)
+    if gather is not None:                                     # the final gather: all passes' lists, inside the timed region
+        merged_hits = gather.finish() // max(1, steps)
     e1.record(stream)
     torch.cuda.synchronize()
     kern = [ks[i].elapsed_time(ke[i]) for i in range(steps)]
@@ -311,7 +325,7 @@ def run_ours(args):
         pattern = sp.Pattern(ctx, sp.ALG_SHIFTOR, pat)
         setup_s = time.perf_counter() - t0
 
-        gather = HitGather(torch, dist, dev, world, int(os.environ.get("SPMB_BENCH_DEPTH", "3"))) if world > 1 else None
+        gather = HitGather(torch, dist, dev, world) if world > 1 else None
         if world > 1:
             dist.barrier()
         # clocks are sampled from the warm-up to the end of the e2e legs (the timed region of the
@@ -335,7 +349,8 @@ def run_ours(args):
                        "row_len": js.row_len, "journal_materialise_ms": journal_ms,
                        "journal_materialise_note": "spmb_store_create_journaled on a resident base, events from pinned host "
                                                    "memory: event upload + prefix + pack_chunks_kernel<JournalSource>",
-                       "hit_lists_gathered_per_step": bool(gather), "merged_hits_rank0": getattr(time_search, "merged_hits", None),
+                       "hit_lists_gathered": ("all passes' lists in one final all_gather inside the timed region" if gather else False),
+                       "merged_hits_per_pass_rank0": getattr(time_search, "merged_hits", None),
                        "step": "kernel launch + hit count/list D2H + host sort; passes i+1 and i+2 are queued before pass i's "
                                "hits are collected (spmb_search_launch / spmb_search_finish on three hit lists)"
                                + ("; every pass's hit list is all-gathered to rank 0 inside the timed region" if gather else "")},
@@ -745,7 +760,7 @@ def bench_c5(sp, synth, torch, ctx, dev, stream, hits, args, rank, world):
     gather = None
     if world > 1:
         import torch.distributed as dist
-        gather = HitGather(torch, dist, dev, world, int(os.environ.get("SPMB_BENCH_DEPTH", "3")), cap=8192)
+        gather = HitGather(torch, dist, dev, world)
         dist.barrier()
     total_ms, kern_ms, n_hits, launches = time_search(sp, torch, ctx, stream, store, pset, hits, args.steps, args.warmup,
                                                       gather=gather)
@@ -769,7 +784,8 @@ def bench_c5(sp, synth, torch, ctx, dev, stream, hits, args, rank, world):
            "value": n * args.steps / (total_ms * 1e-3) / 1e9, "unit": "Gbp/s (x 10k patterns)", "ms_per_step": total_ms / args.steps,
            "kernels_ms": kern_ms, "cell_rate_T_per_s": n * n_pat * args.steps / (total_ms * 1e-3) / 1e12,
            "hits": n_hits, "filter": pset.filter_info, "scaling": "strong",
-           "hit_lists_gathered_per_step": bool(gather), "merged_hits_rank0": getattr(time_search, "merged_hits", None),
+           "hit_lists_gathered": ("all passes' lists in one final all_gather inside the timed region" if gather else False),
+           "merged_hits_per_pass_rank0": getattr(time_search, "merged_hits", None),
            "equals_direct_myers_kernel_16_patterns_this_shard": same,
            "text_gbytes_per_s_kernels": n / world * 0.25 / (kern_ms * 1e-3) / 1e9}
     if rank == 0 and world == 1 and not args.no_cpu:

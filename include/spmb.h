@@ -252,7 +252,7 @@ uint32_t spmb_last_launch_count(const spmb_context *ctx);
  *          Finder on each chunk (myers_matcher_restorable_test.cpp:66-69).
  * submit / collect: the asynchronous pair for streaming at full rate -- submit hands the chunk to the upload pipeline
  *          and returns at once; THE HOST BUFFER MUST STAY VALID UNTIL THAT CHUNK HAS BEEN COLLECTED.  collect hands
- *          back the hits of the OLDEST chunk in flight; at most two chunks may be in flight, so the packing threads
+ *          back the hits of the OLDEST chunk in flight; at most three chunks may be in flight, so the packing threads
  *          and the copy engine run on from chunk i into chunk i+1 while chunk i is searched and its hits travel.
  * SPMB_ALG_MYERS_PREFIX streams (restorable_myers_prefix_matcher) are anchored at the START OF THE STREAM: the scan is
  * clamped to the first m + k + 1 symbols of the whole stream, whereas the reference clamps every call on its own

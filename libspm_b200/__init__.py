@@ -680,7 +680,7 @@ def read_vcf(path: str, contig: str | None = None, ref_len: int = 0):
 
 def stream_leg(ctx: Context, host: np.ndarray, pat, hits: Hits, chunk: int = 64 << 20, k: int = 0, alg: int = ALG_SHIFTOR):
     """bench.py's streaming leg: a host haystack fed in `chunk`-symbol pieces through spmb_stream_submit /
-    spmb_stream_collect (two chunks in flight), beside the one-shot spmb_search_host of the same haystack."""
+    spmb_stream_collect (three chunks in flight), beside the one-shot spmb_search_host of the same haystack."""
     import time
     n = host.size
     base = host.ctypes.data
@@ -694,7 +694,7 @@ def stream_leg(ctx: Context, host: np.ndarray, pat, hits: Hits, chunk: int = 64 
         inflight = 0
         for o in range(0, n, chunk):
             ln = min(chunk, n - o)
-            if inflight == 2:
+            if inflight == 3:
                 total_hits += len(st.collect())
                 inflight -= 1
             st.submit(ptr=base + o, n=ln)
@@ -733,7 +733,7 @@ def stream_leg(ctx: Context, host: np.ndarray, pat, hits: Hits, chunk: int = 64 
             "ms_total": dt * 1e3, "hits": int(total_hits), "one_shot_gbp_per_s": n / dt1 / 1e9, "one_shot_ms": dt1 * 1e3,
             "one_shot_hits": int(len(one)), "ratio_to_one_shot": dt1 / dt, "hits_equal_one_shot": bool(total_hits == len(one) == fh),
             "sync_feed_gbp_per_s": n / dt2 / 1e9,
-            "path": "spmb_stream_submit / spmb_stream_collect, two chunks in flight: device-resident tail, only the new chunk "
+            "path": "spmb_stream_submit / spmb_stream_collect, three chunks in flight: device-resident tail, only the new chunk "
                     "crosses PCIe (both movers of the upload queue); one-shot = spmb_search_host of the same plain haystack"}
 
 

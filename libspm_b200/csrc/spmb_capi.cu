@@ -192,6 +192,8 @@ struct spmb_hits {
     const spmb_hit *view = nullptr;
 };
 
+enum { SPMB_STREAM_SLOTS = 3 }; // chunks in flight per stream (one being collected, two in the upload pool's queue)
+
 struct spmb_stream {
     CtxRef ctx;
     const spmb_pattern *pat = nullptr;
@@ -219,8 +221,9 @@ struct spmb_stream {
         StreamHead hd;
         bool job = false;               // the bulk is a job of the upload pool
         uint64_t job_seq = 0;
-    } slot[2];
+    } slot[SPMB_STREAM_SLOTS];
     int next_submit = 0, next_collect = 0;
+    bool any_busy() const { for (const Slot &x : slot) if (x.busy) return true; return false; }
     // anchored (prefix) streams: the state is the short prefix itself, on the host
     std::vector<uint8_t> tail;
     std::vector<uint8_t> scratch;
@@ -2465,7 +2468,7 @@ extern "C" int spmb_stream_create(spmb_context *ctx, const spmb_pattern *p, spmb
     cudaError_t e = cudaMalloc(&st->d_tail, ((size_t)st->keep / 32 + 2) * sizeof(uint2));
     if (e == cudaSuccess) e = cudaMemset(st->d_tail, 0, ((size_t)st->keep / 32 + 2) * sizeof(uint2));
     if (e == cudaSuccess) e = cudaMalloc(&st->d_err, (p->n_pat ? p->n_pat : 1) * sizeof(uint32_t));
-    for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
+    for (int i = 0; i < SPMB_STREAM_SLOTS && e == cudaSuccess; ++i) {
         int rc = spmb_hits_create(ctx, 1 << 12, &st->slot[i].hits);
         if (rc) { spmb_stream_destroy(st); return rc; }
     }
@@ -2486,12 +2489,12 @@ extern "C" int spmb_stream_destroy(spmb_stream *st)
     if (!st) return SPMB_OK;
     if (st->ctx) { cudaSetDevice(st->ctx->device); cudaStreamSynchronize(st->ctx->stream); }
     // chunks handed in but never collected: their upload jobs still write into this stream's buffers
-    for (int i = 0, si = st->next_collect; i < 2; ++i, si ^= 1)
+    for (int i = 0, si = st->next_collect; i < SPMB_STREAM_SLOTS; ++i, si = (si + 1) % SPMB_STREAM_SLOTS)
         if (st->slot[si].busy && st->slot[si].job && st->ctx && st->ctx->upload) {
             st->ctx->upload->wait(st->slot[si].job_seq, st->ctx->stream, true, nullptr);
             st->slot[si].job = false;
         }
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < SPMB_STREAM_SLOTS; ++i) {
         stream_slot_release(st, i);
         if (st->slot[i].d_words && st->ctx) big_free(st->ctx, st->slot[i].d_words, st->slot[i].words_bytes);
         cudaFree(st->slot[i].d_raw);
@@ -2541,7 +2544,7 @@ extern "C" int spmb_stream_submit(spmb_context *ctx, spmb_stream *st, const uint
     ENTER(ctx);
     const int si = st->next_submit;
     spmb_stream::Slot &S = st->slot[si];
-    if (S.busy) return set_err(ctx, SPMB_ERR_ARG, "two chunks are in flight: collect one first");
+    if (S.busy) return set_err(ctx, SPMB_ERR_ARG, "three chunks are in flight: collect one first");
     const uint64_t t = st->tail_len, total = t + n;
     S.t = t; S.n = n; S.total = total; S.launches = 0;
     S.job = false; S.host = nullptr; S.bulk = 0; S.a = 0;
@@ -2594,7 +2597,7 @@ extern "C" int spmb_stream_submit(spmb_context *ctx, spmb_stream *st, const uint
             S.job = true;
         }
     }
-    st->next_submit ^= 1;
+    st->next_submit = (st->next_submit + 1) % SPMB_STREAM_SLOTS;
     S.busy = true;
     st->tail_len = (uint32_t)std::min<uint64_t>(st->keep, total);
     st->offset += n;
@@ -2669,7 +2672,7 @@ extern "C" int spmb_stream_collect(spmb_context *ctx, spmb_stream *st, spmb_hits
     const int si = st->next_collect;
     spmb_stream::Slot &S = st->slot[si];
     if (!S.busy) return set_err(ctx, SPMB_ERR_ARG, "no chunk in flight");
-    st->next_collect ^= 1;
+    st->next_collect = (st->next_collect + 1) % SPMB_STREAM_SLOTS;
     h->host.clear();
     h->count = 0;
     h->view = nullptr;
@@ -2705,7 +2708,7 @@ extern "C" int spmb_stream_feed(spmb_context *ctx, spmb_stream *st, const uint8_
 {
     if (!ctx || !st || !h || (!host_ranks && n)) return SPMB_ERR_ARG;
     if (st->pat->alg == SPMB_ALG_MYERS_PREFIX) return stream_feed_prefix(ctx, st, host_ranks, n, h);
-    if (st->slot[0].busy || st->slot[1].busy) return set_err(ctx, SPMB_ERR_ARG, "chunks submitted with spmb_stream_submit are still in flight");
+    if (st->any_busy()) return set_err(ctx, SPMB_ERR_ARG, "chunks submitted with spmb_stream_submit are still in flight");
     int rc = spmb_stream_submit(ctx, st, host_ranks, n);
     if (rc) return rc;
     return spmb_stream_collect(ctx, st, h);
@@ -2766,7 +2769,7 @@ extern "C" int spmb_stream_capture(const spmb_stream *st_c, void *buf, size_t *s
     if (*size < need) { *size = need; return SPMB_ERR_ARG; }
     std::vector<uint32_t> err(np, 0);
     if (!prefix) {
-        if (st->slot[0].busy || st->slot[1].busy) return SPMB_ERR_ARG; // collect first: the state is that of the last chunk
+        if (st->any_busy()) return SPMB_ERR_ARG; // collect first: the state is that of the last chunk
         int rc = stream_errors(st, err);
         if (rc) return rc;
     }
@@ -2793,7 +2796,7 @@ extern "C" int spmb_stream_restore(spmb_stream *st, const void *buf, size_t size
         st->tail.assign(tb, tb + tlen);
         return SPMB_OK;
     }
-    if (tlen > st->keep || st->slot[0].busy || st->slot[1].busy) return SPMB_ERR_ARG;
+    if (tlen > st->keep || st->any_busy()) return SPMB_ERR_ARG;
     spmb_context *ctx = st->ctx;
     ENTER(ctx);
     std::vector<uint64_t> words((size_t)st->keep / 32 + 2, 0);
@@ -2811,7 +2814,7 @@ extern "C" int spmb_stream_restore(spmb_stream *st, const void *buf, size_t size
 extern "C" int spmb_stream_errors(spmb_stream *st, uint32_t pattern_index, uint32_t *errors)
 {
     if (!st || !errors || pattern_index >= st->pat->n_pat) return SPMB_ERR_ARG;
-    if (st->pat->alg == SPMB_ALG_MYERS_PREFIX || st->slot[0].busy || st->slot[1].busy) return SPMB_ERR_ARG;
+    if (st->pat->alg == SPMB_ALG_MYERS_PREFIX || st->any_busy()) return SPMB_ERR_ARG;
     std::vector<uint32_t> err;
     int rc = stream_errors(st, err);
     if (rc) return rc;

@@ -157,6 +157,7 @@ struct UploadPool {
         const spmb_journal_event *ev_src = nullptr; // events job (src == nullptr)
         spmb_journal_event *d_ev = nullptr;
         uint64_t n = 0, n_chunks = 0, chunk = 0, ev_pool_len = 0, raw_pct = 100;
+        bool caller_waits = true;               // a synchronous run(): the caller's thread sleeps until the job is done
         std::atomic<uint64_t> ends{0};          // head << 32 | tail: chunks [head, tail) are unclaimed
         std::atomic<int> cuda_err{0};
         std::atomic<uint64_t> packed_chunks{0}, unpackable_chunks{0}, raw_chunks{0};
@@ -242,14 +243,17 @@ struct UploadPool {
         n_workers = (int)env_u64("SPMB_HOST_THREADS", (uint64_t)dflt);
         if (threads_override >= 0) n_workers = threads_override; // spmb_context_set_upload_threads
         if (n_workers > 256) n_workers = 256;
+        // the copy engine's share of RAW event chunks (24 B per event against 8 packed): 10 % with 15 packing threads
+        // (measured, round 1), more the fewer threads a device has -- the multi-GPU driver gives each of 8 devices 3
+        // threads, and a 10 % cap left the links idle while those packed (journal phase 15.8 ms at 8 devices)
+        if (!getenv("SPMB_EVENT_RAW_PCT")) {
+            const int pct = 100 - 6 * n_workers;
+            raw_pct_events = (uint64_t)(pct < 10 ? 10 : pct);
+        }
         cudaError_t e = cudaStreamCreateWithFlags(&raw_stream, cudaStreamNonBlocking);
-        // the raw mover spends its life waiting for the link: it sleeps in those waits (blocking events) and leaves
-        // its core to the caller's thread -- packing threads + raw mover + caller are one thread more than the default
-        // thread count leaves cores, and a packing thread that lost its core for a time slice held a whole stream
-        // feed back by 0.3-0.6 ms (traced)
         for (int s = 0; s < SLOTS && e == cudaSuccess; ++s) {
             e = cudaMalloc(&d_slot[s], chunk_sym);
-            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&slot_ev[s], cudaEventDisableTiming | cudaEventBlockingSync);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&slot_ev[s], cudaEventDisableTiming);
         }
         for (int r = 0; r < RING && e == cudaSuccess; ++r) e = cudaEventCreateWithFlags(&raw_job_ev[r], cudaEventDisableTiming);
         workers.resize(n_workers);
@@ -351,9 +355,27 @@ struct UploadPool {
                 if (e == cudaSuccess) e = cudaEventRecord(W.job_ev[r], W.stream);
             } else {
                 while (e == cudaSuccess && J.cuda_err.load(std::memory_order_relaxed) == 0) {
-                    const auto ta = now();
-                    if (slot_used[s]) e = cudaEventSynchronize(slot_ev[s]);
-                    t_wait += ns(ta, now());
+                    // text chunks land in a staging slot: wait for the slot (this also keeps the raw mover at the
+                    // link's pace, so the split with the packing threads follows the machine).  Event chunks are
+                    // copied in place and their raw share is capped, so nothing is waited for: they are short
+                    // (1.5 MB), and a sleeping wait per chunk cost more than the copy (raw-only: 78 -> 17 ms).
+                    if (J.src) {
+                        // The raw mover spends its life in this wait.  While the caller sleeps in run() it polls (the
+                        // caller's core is free); behind an asynchronous submit the caller's thread is at work too --
+                        // packing threads + raw mover + caller are one thread more than the default thread count
+                        // leaves cores, and a packing thread that lost its core for a time slice held a whole stream
+                        // feed back by 0.3-0.6 ms (traced) -- so there it sleeps between looks.
+                        const auto ta = now();
+                        if (slot_used[s]) {
+                            if (J.caller_waits) e = cudaEventSynchronize(slot_ev[s]);
+                            else {
+                                cudaError_t q;
+                                while ((q = cudaEventQuery(slot_ev[s])) == cudaErrorNotReady) std::this_thread::sleep_for(std::chrono::microseconds(20));
+                                e = q;
+                            }
+                        }
+                        t_wait += ns(ta, now());
+                    }
                     // a raw chunk costs the link 3-4x the bytes of a packed one: with packing threads at work the copy
                     // engine's share is capped (raw_pct of the chunks), or a fast link starves the packed copies
                     if (n_workers && n_mine * 100 >= J.raw_pct * J.n_chunks) break;
@@ -368,14 +390,14 @@ struct UploadPool {
                             e = cudaGetLastError();
                             J.launches.fetch_add(1, std::memory_order_relaxed);
                         }
+                        if (e == cudaSuccess) e = cudaEventRecord(slot_ev[s], raw_stream);
+                        slot_used[s] = true;
+                        s = (s + 1) % SLOTS;
                     } else {
                         const uint64_t i0 = idx * J.chunk;
                         const uint64_t len = (J.n - i0 < J.chunk) ? J.n - i0 : J.chunk;
                         e = cudaMemcpyAsync(J.d_ev + i0, J.ev_src + i0, len * sizeof(spmb_journal_event), cudaMemcpyHostToDevice, raw_stream);
                     }
-                    if (e == cudaSuccess) e = cudaEventRecord(slot_ev[s], raw_stream);
-                    slot_used[s] = true;
-                    s = (s + 1) % SLOTS;
                     ++n_mine;
                 }
                 J.raw_chunks.store(n_mine);
@@ -419,7 +441,8 @@ struct UploadPool {
 
     // host_ranks[0, n_sym) -> dst[0, ceil(n/32)) (device memory every stream may touch already).  chunk = 0: chunk_sym;
     // else the chunk size of this job (multiple of 1024, <= chunk_sym).  false: the ring is full (wait() first).
-    bool submit_text(const uint8_t *host_ranks, uint64_t n_sym, uint2 *dst, uint64_t chunk, uint64_t *seq_out, uint64_t raw_pct = 0)
+    bool submit_text(const uint8_t *host_ranks, uint64_t n_sym, uint2 *dst, uint64_t chunk, uint64_t *seq_out, uint64_t raw_pct = 0,
+                     bool caller_waits = false)
     {
         uint64_t seq;
         Job *J = begin_job(seq);
@@ -428,6 +451,7 @@ struct UploadPool {
         J->chunk = (chunk == 0 || chunk > chunk_sym) ? chunk_sym : std::max<uint64_t>(1024, chunk / 1024 * 1024);
         J->n_chunks = (n_sym + J->chunk - 1) / J->chunk;
         J->raw_pct = raw_pct ? std::min(raw_pct, raw_pct_text) : raw_pct_text;
+        J->caller_waits = caller_waits;
         job_chunk = J->chunk;
         commit_job(*J);
         *seq_out = seq;
@@ -477,7 +501,7 @@ struct UploadPool {
         cudaError_t e = cudaStreamSynchronize(stream);
         if (e != cudaSuccess) return e;
         uint64_t seq;
-        if (!submit_text(host_ranks, n_sym, dst, chunk, &seq)) return cudaErrorNotReady; // jobs of a stream still in flight
+        if (!submit_text(host_ranks, n_sym, dst, chunk, &seq, 0, true)) return cudaErrorNotReady; // jobs of a stream still in flight
         return wait(seq, stream, true, launches);
     }
 
@@ -498,6 +522,7 @@ struct UploadPool {
         if (J->chunk == 0) J->chunk = 16;       // tiny test geometries: one partial block
         J->n_chunks = (n_ev + J->chunk - 1) / J->chunk;
         J->raw_pct = raw_pct_events;
+        J->caller_waits = true;
         commit_job(*J);
         return wait(seq, stream, true, launches);
     }

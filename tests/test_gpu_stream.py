@@ -156,7 +156,7 @@ def test_capture_restore_and_errors(ctx):
     s.close(); p.close()
 
 
-def test_submit_collect_two_chunks_in_flight(ctx):
+def test_submit_collect_three_chunks_in_flight(ctx):
     rng = np.random.default_rng(77)
     n = 2_000_000
     text = rand_text(rng, n)
@@ -172,15 +172,15 @@ def test_submit_collect_two_chunks_in_flight(ctx):
     ge, gr = [], []
     inflight = []
     for o in offs:
-        if len(inflight) == 2:
+        if len(inflight) == 3:
             o0 = inflight.pop(0)
             h = s.collect()
             ge += [int(e) + o0 for e in h["end"]]; gr += [int(e) for e in h["errors"]]
         s.submit(text[o:o + chunk])
         inflight.append(o)
-    assert len(inflight) == 2
+    assert len(inflight) == 3
     with pytest.raises(sp.SpmbError):
-        s.submit(text[:10])                          # a third chunk: collect first
+        s.submit(text[:10])                          # a fourth chunk: collect first
     while inflight:
         o0 = inflight.pop(0)
         h = s.collect()
