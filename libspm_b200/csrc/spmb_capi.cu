@@ -673,13 +673,37 @@ static int store_ensure_lanes(spmb_context *ctx, const spmb_store *s);
 // ref_bias: the events' ref_pos are coordinates of a longer sequence of which `base` holds [ref_bias, ...) (the
 // shards of the multi-GPU driver pass slices of ONE caller-owned event table); probe: *probe_der = derived position
 // of event `probe_index` (where its inserted segment begins), or the derived length when probe_index == n_ev
+static int journaled_pair(spmb_context *ctx, const spmb_store *base, const spmb_journal_event *ev, uint64_t n_ev,
+                          const uint8_t *pool, uint64_t pool_len, uint32_t row_len, uint64_t ref_bias,
+                          uint64_t probe_index, uint64_t *probe_der, uint32_t pool_shift, spmb_store **out);
+
 int spmb_store_create_journaled_ex(spmb_context *ctx, const spmb_store *base, const spmb_journal_event *ev, uint64_t n_ev,
                                    const uint8_t *pool, uint64_t pool_len, uint32_t row_len, uint64_t ref_bias,
                                    uint64_t probe_index, uint64_t *probe_der, spmb_store **out)
 {
     if (!ctx || !base || !out || (n_ev && !ev) || (pool_len && !pool)) return SPMB_ERR_ARG;
     if (base->lay.mode != SPMB_MODE_PLAIN) return set_err(ctx, SPMB_ERR_ARG, "journal base must be a plain store");
-    if (base->sym_bits != 2) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "journaled stores are dna4 (2-bit) only");
+    if (base->sym_bits != 4) return journaled_pair(ctx, base, ev, n_ev, pool, pool_len, row_len, ref_bias, probe_index, probe_der, 0, out);
+    // a 4-bit alphabet (spm::dna5 / spm::dna15) is two plane pairs of the same geometry: the journal is applied to
+    // each, with bits 1..0 / 3..2 of the pool's symbols
+    if (!base->hi) return set_err(ctx, SPMB_ERR_ARG, "journal base: incomplete 4-bit store");
+    spmb_store *lo = nullptr, *hi = nullptr;
+    int rc = journaled_pair(ctx, base, ev, n_ev, pool, pool_len, row_len, ref_bias, probe_index, probe_der, 0, &lo);
+    if (rc) return rc;
+    rc = journaled_pair(ctx, base->hi, ev, n_ev, pool, pool_len, lo->lay.row_len, ref_bias, probe_index, nullptr, 2, &hi);
+    if (rc) { spmb_store_destroy(lo); return rc; }
+    lo->hi = hi;
+    lo->sym_bits = 4;
+    hi->sym_bits = 4;
+    *out = lo;
+    return SPMB_OK;
+}
+
+// one plane pair (2 bits per symbol) of a journaled store
+static int journaled_pair(spmb_context *ctx, const spmb_store *base, const spmb_journal_event *ev, uint64_t n_ev,
+                          const uint8_t *pool, uint64_t pool_len, uint32_t row_len, uint64_t ref_bias,
+                          uint64_t probe_index, uint64_t *probe_der, uint32_t pool_shift, spmb_store **out)
+{
     ENTER(ctx);
     cudaStream_t sm = ctx->stream;
     const size_t ne = n_ev ? n_ev : 1;
@@ -737,7 +761,7 @@ int spmb_store_create_journaled_ex(spmb_context *ctx, const spmb_store *base, co
     if (pool_len) {
         JCU(cudaMemcpyAsync(d_pool, pool, pool_len, cudaMemcpyHostToDevice, sm));
         if (e == cudaSuccess) { // inserted runs are fetched like base runs: 32 symbols per word pair
-            bytes_to_chunks_kernel<<<(unsigned)(((pool_len + 31) / 32 + 255) / 256), 256, 0, sm>>>(d_pool, pool_len, d_poolw);
+            bytes_to_chunks_kernel<<<(unsigned)(((pool_len + 31) / 32 + 255) / 256), 256, 0, sm>>>(d_pool, pool_len, d_poolw, pool_shift);
             ctx->launches++;
         }
     }

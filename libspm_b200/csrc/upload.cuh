@@ -43,9 +43,10 @@ __device__ __forceinline__ uint32_t spmb_fold4(uint32_t w)
     return (r | (r >> 6) | (r >> 12) | (r >> 18)) & 0xffu;
 }
 
-// raw staging slot (1 B/symbol, n_sym symbols, 16-byte aligned) -> lane-chunk words
+// raw staging slot (1 B/symbol, n_sym symbols, 16-byte aligned) -> lane-chunk words; shift = which two bits of a
+// symbol byte are packed (0: dna4 and the low pair of a 4-bit alphabet, 2: its high pair)
 __global__ void __launch_bounds__(256) bytes_to_chunks_kernel(const uint8_t *__restrict__ in, uint64_t n_sym,
-                                                              uint2 *__restrict__ out)
+                                                              uint2 *__restrict__ out, uint32_t shift = 0)
 {
     const uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const uint64_t p0 = g * 32;
@@ -67,6 +68,10 @@ __global__ void __launch_bounds__(256) bytes_to_chunks_kernel(const uint8_t *__r
             }
             w[i] = v;
         }
+    }
+    if (shift) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) w[i] = (w[i] >> shift) & 0x03030303u;
     }
     uint2 o;
     o.x = (spmb_fold4(w[0]) << 24) | (spmb_fold4(w[1]) << 16) | (spmb_fold4(w[2]) << 8) | spmb_fold4(w[3]);

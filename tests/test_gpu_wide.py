@@ -136,9 +136,9 @@ def test_width_mismatch_and_unsupported_paths_fail_loudly(ctx):
     with pytest.raises(sp.SpmbError) as ei:
         sp.Pattern(ctx, sp.ALG_MYERS_FILTERED, text[10:110], 1, bits=4)
     assert ei.value.code == 4
-    with pytest.raises(sp.SpmbError) as ei:
-        wide.journaled(np.zeros(0, sp.EVENT_DTYPE), np.zeros(0, np.uint8))
-    assert ei.value.code == 4
+    js = wide.journaled(np.zeros(0, sp.EVENT_DTYPE), np.zeros(0, np.uint8))     # journals take 4-bit stores (round 2)
+    assert js.symbol_bits == 4 and np.array_equal(js.read(), text)
+    js.close()
     with pytest.raises(sp.SpmbError):
         sp.Stream(ctx, p4)
     for x in (p2, p4, wide, narrow):
@@ -275,3 +275,43 @@ def test_long_hit_lists_ordered_by_the_launch(ctx):
             assert np.array_equal(got[f], direct[f]), (rep, f)
     for x in (p, pe, pf, pd, hits, hits_b, store, st4):
         x.close()
+
+
+@pytest.mark.parametrize("sigma,bits", [(5, 3), (15, 4)])
+@pytest.mark.parametrize("rl", [0, 96])
+def test_wide_journaled_store(ctx, sigma, bits, rl):
+    """a journal over a 4-bit store (spm::dna5 / spm::dna15): both plane pairs take the same events, the pool gives
+    bits 1..0 and 3..2; derived text = the oracle's journal apply, searches over it = the oracle's."""
+    rng = np.random.default_rng(31 * sigma + rl)
+    n = 300_000
+    ref = rand_text(rng, n, sigma)
+    # events: SNPs, insertions, deletions, sorted and non-overlapping
+    pos = np.sort(rng.choice(np.arange(10, n - 50, 40), size=3000, replace=False))
+    ev = np.zeros(len(pos), dtype=sp.EVENT_DTYPE)
+    pool = []
+    for i, p0 in enumerate(pos):
+        kind = int(rng.integers(0, 3))
+        dl = 1 if kind == 0 else (0 if kind == 1 else int(rng.integers(1, 9)))
+        il = 1 if kind == 0 else (int(rng.integers(1, 9)) if kind == 1 else 0)
+        ev[i] = (int(p0), dl, il, len(pool))
+        pool.extend(int(x) for x in rng.integers(0, sigma, size=il))
+    pool = np.array(pool, dtype=np.uint8)
+    derived = orc.journal_apply(ref, ev.astype(orc.EVENT_DTYPE), pool)
+    base = sp.Store.from_host_wide(ctx, ref, bits, rl)
+    js = base.journaled(ev, pool, rl)
+    assert js.symbol_bits == 4 and len(js) == len(derived)
+    assert np.array_equal(js.read(), derived)
+    s0 = int(pos[len(pos) // 2]) - 20
+    pat = derived[s0:s0 + 64].copy()
+    for alg in (sp.ALG_HORSPOOL, sp.ALG_SHIFTOR):
+        p = sp.Pattern(ctx, alg, pat, 0, bits=bits)
+        got = sp.search(ctx, js, p)
+        assert np.array_equal(got["end"], orc.exact_bruteforce(derived, pat))
+        p.close()
+    pm = _mutate(rng, derived[s0 + 100:s0 + 200].copy(), 2, sigma)
+    p = sp.Pattern(ctx, sp.ALG_MYERS, pm, 4, bits=bits)
+    got = sp.search(ctx, js, p)
+    we, wr = orc.sellers(derived, pm, 4)
+    assert len(we) >= 1
+    assert np.array_equal(got["end"], we) and np.array_equal(got["errors"], wr)
+    p.close(); js.close(); base.close()
