@@ -1147,6 +1147,21 @@ static int pattern_build(spmb_context *ctx, int alg, const uint8_t *ranks, const
         } else if (p->NW > 0) {
             if (e == cudaSuccess) e = pattern_upload_myers(ctx, p, k);
             if (e == cudaSuccess && p->filtered) e = pattern_upload_pigeon(ctx, p, seeds, q);
+            // A/B switch: the lane-chained scan (myers_chain_scan_kernel) over whole rows instead of the one-lane kernels
+            static const bool chain_ab = getenv("SPMB_MYERS_CHAIN") != nullptr;
+            if (e == cudaSuccess && chain_ab && alg == SPMB_ALG_MYERS && sym_bits == 2 && !ids) {
+                const uint32_t NWT = 32;
+                std::vector<uint32_t> ceq((size_t)n_pat * 4 * NWT, 0);
+                std::vector<MyersPatMeta> cm(n_pat);
+                for (uint32_t i = 0; i < n_pat; ++i) {
+                    const uint8_t *pr = p->ranks.data() + p->off[i];
+                    for (uint32_t j = 0; j < p->len[i]; ++j) ceq[(size_t)i * 4 * NWT + (pr[j] & 3u) * NWT + j / 32] |= 1u << (j % 32);
+                    cm[i].m = p->len[i]; cm[i].k = k; cm[i].pad = 0; cm[i].pattern_id = i;
+                }
+                e = upload_vec(ctx, &p->d_chain_eq, ceq);
+                if (e == cudaSuccess) e = upload_vec(ctx, &p->d_chain_meta, cm);
+                if (e == cudaSuccess) p->chain_wpl = 1;
+            }
         }
     } else if (alg == SPMB_ALG_PIGEONHOLE) {
         // SeqAn2 _patternInit(Pattern<TIndex, Pigeonhole<TSpec>>, errorRate) (UNVERIFIED-UPSTREAM; pinned by
@@ -1645,6 +1660,21 @@ static int enqueue_search(spmb_context *ctx, const spmb_store *s, const spmb_pat
     }
     if (p->alg == SPMB_ALG_PIGEONHOLE) return SPMB_OK; // no usable q-gram
     if (p->alg == SPMB_ALG_MYERS || p->alg == SPMB_ALG_MYERS_FILTERED) {
+        if (p->subs.empty() && !p->long_prefix && p->chain_wpl == 1 && p->d_chain_eq && s->lay.mode == SPMB_MODE_PLAIN && !s->hi) {
+            // SPMB_MYERS_CHAIN=1: one warp per (row, needle), words chained across the lanes (A/B measurement)
+            int rc = store_ensure_lanes(ctx, s);
+            if (rc) return rc;
+            ChainArgs ca;
+            memset(&ca, 0, sizeof(ca));
+            ca.lanes = s->lanes; ca.lay = s->lay; ca.eq = p->d_chain_eq; ca.meta = p->d_chain_meta;
+            ca.st0 = st0; ca.st1 = st1; ca.n_needles = p->n_pat; ca.warm = p->warm; ca.seq_id = seq_id; ca.sink = sink;
+            const unsigned long long tasks = (unsigned long long)(st1 - st0) * 32 * p->n_pat;
+            const unsigned grid = (unsigned)std::min<unsigned long long>((tasks + 3) / 4, (unsigned long long)ctx->sm_count * 16);
+            if (grid) myers_chain_scan_kernel<1><<<grid, 128, 0, ctx->stream>>>(ca);
+            ctx->launches++;
+            CU(cudaGetLastError());
+            return SPMB_OK;
+        }
         if (p->subs.empty() && !p->long_prefix) return enqueue_myers_direct(ctx, s, p, sink, st0, st1, seq_id, true);
         for (const spmb_pattern *c : p->subs) {
             int rc = enqueue_myers_direct(ctx, s, c, sink, st0, st1, seq_id, true);
