@@ -96,16 +96,32 @@ __device__ __forceinline__ uint2 spmb_fetch32(const uint2 *__restrict__ lanes, c
 // 1024-symbol block of the derived sequence on its own (no barrier, 256-thread CTAs, ~5 CTAs per SM):
 //   1. blk_idx[b], blk_idx[b+1]                     -> the block's events are [first, first + nb)        (one trip)
 //   2. the warp loads those records coalesced into shared memory                                         (one trip)
-//   3. every lane lists the (up to 32) source runs of its chunk from shared memory alone, ISSUES THE LOADS OF THREE
-//      RUNS AT A TIME (base lane chunks; inserted symbols come from a 2-bit packed copy of the pool, so both kinds
-//      of run are the same unaligned 32-symbol fetch) and only then shifts / masks / ORs them into place  (one trip)
+//   3. the warp loads the 48 base lane-chunk words the block can read into shared memory                   (one trip)
+//   4. every lane walks the runs of its chunk in shared memory alone: a base run is one unaligned read of the block's
+//      base words, short insertions (<= 16 symbols) sit in the event record; one loop trip per event in the chunk.
+//      Trips 1-3 of the NEXT blocks run under step 4 of this one (software pipeline).  Chunks that do not fit this
+//      shape (a run outside the window, a long insertion, more than 32 events in the block) are derived by the
+//      general walk from global memory (journal_chunk_dense).
 // Coordinates inside a block are 32-bit offsets from its first derived position D0 (rel), and an event is kept as
 // what a run needs: where its inserted segment begins / ends (rel, ins_end) and the two constants that turn a derived
 // position into a source position -- base position = d + shift behind the event, pool position = d + pshift inside
 // its insertion.
-struct JournalRec {
+struct JournalRec { // the general walk (journal_chunk_dense): built from the event table on the fly
     int32_t rel, ins_end;
     long long shift, pshift;
+};
+// what the fast walk needs of an event, block-independent (journal_rec_kernel writes one per event) ...
+struct JournalEvRec {
+    uint64_t der;       // derived position where the inserted segment begins
+    long long shift;    // base position = derived position + shift behind the event
+    uint32_t ins_len;
+    uint32_t sym;       // the first 16 inserted symbols, first one in the top two bits
+};
+// ... and in a block's coordinates (shared memory)
+struct JournalFast {
+    int32_t rel, ins_end;
+    long long shift;
+    uint32_t sym, pad;
 };
 
 struct JournalDeriveArgs {
@@ -115,12 +131,13 @@ struct JournalDeriveArgs {
     const uint64_t *__restrict__ ev_der;
     const int64_t *__restrict__ blk_idx;
     const uint2 *__restrict__ pool_words; // the insertion pool, 32 symbols per word pair, one spare pair behind the end
+    const JournalEvRec *__restrict__ ev_rec; // per event: journal_rec_kernel
     uint64_t n_ev;
     uint64_t n;                           // derived length
     uint2 *__restrict__ out;              // [ceil(n / 32)]
 };
 
-enum { JOURNAL_BATCH = 64, JOURNAL_NSEG = 3 };
+enum { JOURNAL_BATCH = 32, JOURNAL_NBASE = 48 };
 
 __device__ __forceinline__ int32_t journal_clamp(long long x)
 {
@@ -163,46 +180,57 @@ __device__ __forceinline__ unsigned long long journal_place(const uint2 w0, cons
     return W >> (2 * t);
 }
 
-// One chunk from a batch in shared memory: sm = events [0, nb) of the block (rel ascending), e = index of the last
-// one with rel <= lane * 32 (or -1), D0 / n_rel = the block's first derived position / symbols left from there.
-__device__ __forceinline__ uint2 journal_chunk(const JournalDeriveArgs &a, const JournalRec *sm, int nb, int e, uint64_t D0, int32_t n_rel,
-                                               uint32_t lane)
+// One chunk from shared memory alone: sm = events [0, nb) of the block (rel ascending), e = index of the last one
+// with rel <= lane * 32 (or -1), bw = the JOURNAL_NBASE base lane-chunk words from linear chunk qb on.  A loop trip is
+// one base run + the event behind it + that event's inserted symbols (from the record); a lane with no event in its
+// chunk makes one trip.  false = something does not fit (a run outside the base window, an insertion longer than the
+// 16 embedded symbols): the caller derives that chunk from global memory instead.
+__device__ __forceinline__ bool journal_chunk(const JournalFast *sm, int nb, int e, const uint2 *bw, long long qb, uint64_t D0, int32_t n_rel,
+                                              uint32_t lane, uint2 &res)
 {
     const int32_t c0 = (int32_t)lane * 32;
     int32_t cur = c0;
     const int32_t end = min(c0 + 32, n_rel);
-    long long shift = 0, pshift = 0;
-    int32_t ins_end = INT32_MIN, next_rel = INT32_MAX;
-    if (e >= 0) { const JournalRec r = sm[e]; shift = r.shift; pshift = r.pshift; ins_end = r.ins_end; }
+    long long shift = 0;
+    int32_t ins_end = INT32_MIN, irel = 0, next_rel = INT32_MAX;
+    uint32_t sym = 0;
+    if (e >= 0) { const JournalFast r = sm[e]; shift = r.shift; ins_end = r.ins_end; irel = r.rel; sym = r.sym; }
     if (e + 1 < nb) next_rel = sm[e + 1].rel;
     unsigned long long out = 0;
-    while (cur < end) {
-        // ---- up to JOURNAL_NSEG runs: their loads are issued together, then they are placed ----
-        uint2 w0[JOURNAL_NSEG], w1[JOURNAL_NSEG];
-        uint32_t so[JOURNAL_NSEG], st[JOURNAL_NSEG], sl[JOURNAL_NSEG];
-#pragma unroll
-        for (int q = 0; q < JOURNAL_NSEG; ++q) {
-            sl[q] = 0; st[q] = 0; so[q] = 0;
-            w0[q] = make_uint2(0, 0); w1[q] = make_uint2(0, 0);
-            if (cur < end) {
-                while (cur >= next_rel) { // enter the next event (several may begin at the same position)
-                    ++e;
-                    const JournalRec r = sm[e];
-                    shift = r.shift; pshift = r.pshift; ins_end = r.ins_end;
-                    next_rel = (e + 1 < nb) ? sm[e + 1].rel : INT32_MAX;
-                }
-                const bool pool = cur < ins_end;
-                const int32_t stop = pool ? min(end, ins_end) : min(end, next_rel);
-                journal_issue(a, pool, (uint64_t)((long long)D0 + cur + (pool ? pshift : shift)), w0[q], w1[q], so[q]);
-                st[q] = (uint32_t)(cur - c0); sl[q] = (uint32_t)(stop - cur);
-                cur = stop;
+    bool ok = true;
+    for (;;) {
+        if (cur < ins_end) { // inside the inserted segment of the event in effect
+            const int32_t stop = min(end, ins_end);
+            if (stop - irel > 16 || cur < irel) ok = false;
+            else {
+                unsigned long long W = (unsigned long long)(sym << (2 * (cur - irel))) << 32;
+                W &= ~(~0ull >> (2 * (stop - cur)));
+                out |= W >> (2 * (cur - c0));
             }
+            cur = stop;
         }
-#pragma unroll
-        for (int q = 0; q < JOURNAL_NSEG; ++q)
-            if (sl[q]) out |= journal_place(w0[q], w1[q], so[q], st[q], sl[q]);
+        const int32_t stop = min(end, next_rel);
+        if (stop > cur) { // a run copied from the base
+            const long long pb = (long long)D0 + cur + shift;
+            const long long qi = (pb >> 5) - qb;
+            if (qi < 0 || qi >= JOURNAL_NBASE - 1) ok = false;
+            else {
+                const uint2 w = spmb_chunk_shift(bw[qi], bw[qi + 1], (uint32_t)pb & 31u);
+                unsigned long long W = ((unsigned long long)w.x << 32) | w.y;
+                const int32_t len = stop - cur;
+                if (len < 32) W &= ~(~0ull >> (2 * len));
+                out |= W >> (2 * (cur - c0));
+            }
+            cur = stop;
+        }
+        if (cur >= end) break;
+        ++e; // the event that begins here
+        const JournalFast r = sm[e];
+        shift = r.shift; ins_end = r.ins_end; irel = r.rel; sym = r.sym;
+        next_rel = (e + 1 < nb) ? sm[e + 1].rel : INT32_MAX;
     }
-    return make_uint2((uint32_t)(out >> 32), (uint32_t)out);
+    res = make_uint2((uint32_t)(out >> 32), (uint32_t)out);
+    return ok;
 }
 
 // The same without a batch (a block with more events than JOURNAL_BATCH: every record comes from global memory).
@@ -243,98 +271,176 @@ __device__ __noinline__ uint2 journal_chunk_dense(const JournalDeriveArgs &a, in
     return make_uint2((uint32_t)(out >> 32), (uint32_t)out);
 }
 
-// One warp = one 1024-symbol block of the derived sequence at a time, software-pipelined over the warp's blocks:
-// while block j is derived from the records in shared memory, the event records of block j+1 are on their way into
-// registers and the block index of block j+2 is being read -- the only memory round trip left on a block's critical
-// path is the fetch of its source words.
-__global__ void __launch_bounds__(256, 4) journal_derive_kernel(JournalDeriveArgs a)
+// per event, once: what the fast walk needs, so that staging a block's events is one 24-byte load per event and a
+// subtraction (the per-block straight-line code -- index, records, base words, e0 -- was 440 of the 660 instructions
+// a block cost, most of it 64-bit address and clamp arithmetic on three arrays)
+__global__ void journal_rec_kernel(const spmb_journal_event *__restrict__ ev, const uint64_t *__restrict__ der, uint64_t n_ev,
+                                   const uint2 *__restrict__ pool_words, JournalEvRec *__restrict__ out)
 {
-    __shared__ JournalRec s_rec[8][JOURNAL_BATCH];
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_ev) return;
+    const spmb_journal_event x = ev[i];
+    JournalEvRec r;
+    r.der = der[i];
+    r.shift = (long long)(x.ref_pos + x.del_len) - (long long)r.der - (long long)x.ins_len;
+    r.ins_len = x.ins_len;
+    r.sym = 0;
+    if (x.ins_len) {
+        const uint2 w = spmb_chunk_shift(__ldg(pool_words + (x.ins_off >> 5)), __ldg(pool_words + (x.ins_off >> 5) + 1), (uint32_t)x.ins_off & 31u);
+        r.sym = w.x;
+        if (x.ins_len < 16) r.sym &= ~(0xffffffffu >> (2 * x.ins_len));
+    }
+    out[i] = r;
+}
+
+// One warp = one 1024-symbol block of the derived sequence at a time, software-pipelined over the warp's blocks:
+// while block j is derived from shared memory alone (its event records and the 48 base lane-chunk words it can read),
+// the base words of block j+1, the event records of block j+2 and the block index of block j+3 are on their way into
+// registers -- no memory round trip is left on a block's critical path.
+__global__ void __launch_bounds__(256, 3) journal_derive_kernel(JournalDeriveArgs a)
+{
+    __shared__ JournalFast s_rec[8][2][JOURNAL_BATCH];
+    __shared__ uint2 s_base[8][2][JOURNAL_NBASE];
     __shared__ int s_last[8][32];
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    JournalRec *sm = s_rec[warp];
     int *last_of = s_last[warp];
     const uint64_t n_blk = (a.n + 1023) >> 10;
     const uint64_t stride = (uint64_t)gridDim.x * 8;
-    uint64_t blk = (uint64_t)blockIdx.x * 8 + warp;
-    if (blk >= n_blk) return; // no block-wide synchronisation anywhere
+    const uint64_t blk0 = (uint64_t)blockIdx.x * 8 + warp;
+    if (blk0 >= n_blk) return; // no block-wide synchronisation anywhere
+    const uint32_t rl32 = a.base.row_len >> 5;
 
     // events [first, first + want) matter to a block: the one in effect at its start, those inside, one behind
-    auto span = [&](int64_t i_lo, int64_t i_hi, int64_t &first, uint64_t &want) {
+    auto span = [&](int64_t i_lo, int64_t i_hi, int64_t &first, uint32_t &want) {
         first = i_lo < 0 ? 0 : i_lo;
-        want = (uint64_t)(i_hi + 2 - first);
-        if (want > a.n_ev - (uint64_t)first) want = a.n_ev - (uint64_t)first;
+        uint64_t w = (uint64_t)(i_hi + 2 - first);
+        if (w > a.n_ev - (uint64_t)first) w = a.n_ev - (uint64_t)first;
+        want = (uint32_t)min(w, (uint64_t)0x7fffffff);
     };
-    // registers of the block in flight
-    spmb_journal_event xe[2];
-    uint64_t xd[2];
-    auto load_events = [&](int64_t first, uint64_t want) {
-        if (lane < want) { xe[0] = a.ev[first + lane]; xd[0] = a.ev_der[first + lane]; }
-        if (want > 32 && lane + 32 < want && lane + 32 < JOURNAL_BATCH) { xe[1] = a.ev[first + lane + 32]; xd[1] = a.ev_der[first + lane + 32]; }
+    int64_t f_tmp;
+    struct Idx { int64_t lo, hi; };
+    auto load_idx = [&](uint64_t b) -> Idx {
+        Idx x{-1, -1};
+        if (b < n_blk) { x.lo = a.blk_idx[b]; x.hi = a.blk_idx[b + 1]; }
+        return x;
     };
-    // records -> shared memory; returns this lane's e0 = last event with rel <= lane * 32
-    auto stage = [&](uint64_t want, uint64_t D0) -> int {
-        const uint32_t nb = (uint32_t)min((uint64_t)JOURNAL_BATCH, want);
-        last_of[lane] = -1;
-        const int halves = nb > 32 ? 2 : 1; // warp-uniform: most blocks hold a dozen events
-        for (int h = 0; h < halves; ++h) {
-            const uint32_t k = lane + 32 * h;
-            if (k < nb) sm[k] = journal_rec(h ? xe[1] : xe[0], h ? xd[1] : xd[0], D0);
+    // one event record per lane in flight (blocks with more than JOURNAL_BATCH events take the general walk)
+    JournalEvRec xr;
+    xr.der = 0; xr.shift = 0; xr.ins_len = 0; xr.sym = 0;
+    auto load_events = [&](int64_t first, uint32_t want) {
+        if (lane < want && want <= JOURNAL_BATCH) xr = a.ev_rec[first + lane];
+    };
+    auto stage_events = [&](JournalFast *sm, uint32_t want, uint64_t D0) {
+        if (lane < want && want <= JOURNAL_BATCH) {
+            const long long d = (long long)xr.der - (long long)D0;
+            JournalFast r;
+            r.rel = journal_clamp(d);
+            r.ins_end = journal_clamp(d + (long long)xr.ins_len);
+            r.shift = xr.shift; r.sym = xr.sym; r.pad = 0;
+            sm[lane] = r;
         }
-        __syncwarp();
-        for (int h = 0; h < halves; ++h) {
-            const uint32_t k = lane + 32 * h;
-            if (k < nb) {
-                const int32_t r = sm[k].rel;
-                const int32_t c = r <= 0 ? 0 : (r + 31) >> 5; // first chunk whose start lies at or behind the event
-                int32_t cn = 64;
-                if (k + 1 < nb) { const int32_t rn = sm[k + 1].rel; cn = rn <= 0 ? 0 : (rn + 31) >> 5; }
-                if (c < 32 && cn != c) last_of[c] = (int)k;
+    };
+    // base words in flight: linear chunks qb + lane and qb + 32 + lane (lanes 0..15)
+    uint2 xb0 = make_uint2(0, 0), xb1 = make_uint2(0, 0);
+    auto load_base = [&](long long qb) {
+        // row / chunk of qb once, then steps inside the row (rows shorter than the window: a division per chunk)
+        const uint64_t Rb = spmb_div_rl(a.base, (uint64_t)qb << 5);
+        const uint32_t cb = (uint32_t)((uint64_t)qb - Rb * rl32);
+        if (rl32 >= 2 * JOURNAL_NBASE) {
+            uint32_t c = cb + lane;
+            uint64_t R = Rb;
+            if (c >= rl32) { c -= rl32; ++R; }
+            xb0 = spmb_chunk(a.base_lanes, rl32, R, c);
+            if (lane < JOURNAL_NBASE - 32) {
+                c = cb + 32 + lane; R = Rb;
+                if (c >= rl32) { c -= rl32; ++R; }
+                xb1 = spmb_chunk(a.base_lanes, rl32, R, c);
+            }
+        } else {
+            uint64_t R = spmb_div_rl(a.base, (uint64_t)(qb + lane) << 5);
+            xb0 = spmb_chunk(a.base_lanes, rl32, R, (uint32_t)((uint64_t)(qb + lane) - R * rl32));
+            if (lane < JOURNAL_NBASE - 32) {
+                R = spmb_div_rl(a.base, (uint64_t)(qb + 32 + lane) << 5);
+                xb1 = spmb_chunk(a.base_lanes, rl32, R, (uint32_t)((uint64_t)(qb + 32 + lane) - R * rl32));
             }
         }
-        __syncwarp();
-        int v = last_of[lane];
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const int up = __shfl_up_sync(0xffffffffu, v, d);
-            if ((int)lane >= d) v = max(v, up);
-        }
-        return v;
+    };
+    // first base chunk a block may need: four chunks of slack before the position its first symbol comes from
+    auto base_start = [&](const JournalFast *sm, uint32_t want, uint64_t D0) -> long long {
+        long long s0 = 0;
+        if (want && want <= JOURNAL_BATCH) { const JournalFast r = sm[0]; if (r.rel <= 0) s0 = r.shift; }
+        long long q = (((long long)D0 + s0) >> 5) - 4;
+        return q < 0 ? 0 : q;
     };
 
-    // prologue: block index of the first two blocks, events of the first
-    int64_t lo = a.blk_idx[blk], hi = a.blk_idx[blk + 1];
-    int64_t first;
-    uint64_t want;
-    span(lo, hi, first, want);
-    load_events(first, want);
-    int64_t nlo = -1, nhi = -1;
-    if (blk + stride < n_blk) { nlo = a.blk_idx[blk + stride]; nhi = a.blk_idx[blk + stride + 1]; }
-    int e0 = stage(want, blk << 10);
+    // ---- prologue: records of block 0 staged, base words of block 0 and records of block 1 in flight ----
+    uint64_t blk = blk0;
+    Idx i0 = load_idx(blk), i1 = load_idx(blk + stride), i2 = load_idx(blk + 2 * stride);
+    uint32_t want, want1 = 0;
+    span(i0.lo, i0.hi, f_tmp, want);
+    load_events(f_tmp, want);
+    stage_events(s_rec[warp][0], want, blk << 10);
+    __syncwarp();
+    long long qb = base_start(s_rec[warp][0], want, blk << 10), qb1 = 0;
+    load_base(qb);
+    if (blk + stride < n_blk) { span(i1.lo, i1.hi, f_tmp, want1); load_events(f_tmp, want1); }
+    int par = 0;
     for (;;) {
         const uint64_t D0 = blk << 10;
         const bool has_next = blk + stride < n_blk;
-        // ---- stage 1 for the next block, stage 0 for the one after ----
-        int64_t nfirst = 0;
-        uint64_t nwant = 0;
+        JournalFast *sm = s_rec[warp][par];
+        uint2 *bw = s_base[warp][par];
+        // ---- stage what arrived: base words of this block, records of the next ----
+        bw[lane] = xb0;
+        if (lane < JOURNAL_NBASE - 32) bw[32 + lane] = xb1;
+        if (has_next) stage_events(s_rec[warp][par ^ 1], want1, (blk + stride) << 10);
+        last_of[lane] = -1;
+        __syncwarp();
+        // ---- issue the next loads: base of block j+1, records of block j+2, index of block j+3 ----
+        uint32_t want2 = 0;
         if (has_next) {
-            span(nlo, nhi, nfirst, nwant);
-            load_events(nfirst, nwant);
-            if (blk + 2 * stride < n_blk) { nlo = a.blk_idx[blk + 2 * stride]; nhi = a.blk_idx[blk + 2 * stride + 1]; }
+            qb1 = base_start(s_rec[warp][par ^ 1], want1, (blk + stride) << 10);
+            load_base(qb1);
+            if (blk + 2 * stride < n_blk) { span(i2.lo, i2.hi, f_tmp, want2); load_events(f_tmp, want2); }
+            i2 = load_idx(blk + 3 * stride);
         }
-        // ---- this block ----
+        // ---- this block: every lane's e0 = last event with rel <= lane * 32 ----
+        const bool fast = want <= JOURNAL_BATCH;
+        if (fast && lane < want) {
+            const int32_t r = sm[lane].rel;
+            const int32_t c = r <= 0 ? 0 : (r + 31) >> 5; // first chunk whose start lies at or behind the event
+            int32_t cn = 64;
+            if (lane + 1 < want) { const int32_t rn = sm[lane + 1].rel; cn = rn <= 0 ? 0 : (rn + 31) >> 5; }
+            if (c < 32 && cn != c) last_of[c] = (int)lane;
+        }
+        __syncwarp();
+        int e0 = last_of[lane];
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int up = __shfl_up_sync(0xffffffffu, e0, d);
+            if ((int)lane >= d) e0 = max(e0, up);
+        }
         const int32_t n_rel = (int32_t)min((uint64_t)1024, a.n - D0);
-        if ((int32_t)lane * 32 < n_rel) {
-            uint2 o;
-            if (want <= JOURNAL_BATCH) o = journal_chunk(a, sm, (int)want, e0, D0, n_rel, lane);
-            else o = journal_chunk_dense(a, first, first + (int64_t)want - 1, D0, n_rel, lane);
-            a.out[(D0 >> 5) + lane] = o;
+        const bool active = (int32_t)lane * 32 < n_rel;
+        uint2 o = make_uint2(0, 0);
+        bool ok = fast;
+        if (active && ok) ok = journal_chunk(sm, (int)want, e0, bw, qb, D0, n_rel, lane, o);
+        if (__any_sync(0xffffffffu, active && !ok)) { // dense blocks, long insertions, runs far from the window
+            if (active && !ok) { // the block's event range again, from the index (this path is rare)
+                const Idx ix = load_idx(blk);
+                int64_t first;
+                uint32_t w2;
+                span(ix.lo, ix.hi, first, w2);
+                o = journal_chunk_dense(a, first, first + (int64_t)w2 - 1, D0, n_rel, lane);
+            }
         }
+        if (active) a.out[(D0 >> 5) + lane] = o;
         if (!has_next) break;
         __syncwarp();
         blk += stride;
-        first = nfirst; want = nwant;
-        e0 = stage(want, blk << 10);
+        want = want1; qb = qb1;
+        want1 = want2;
+        par ^= 1;
     }
 }
 

@@ -714,6 +714,7 @@ static int journaled_pair(spmb_context *ctx, const spmb_store *base, const spmb_
     int *d_bad = nullptr;
     uint8_t *d_pool = nullptr;
     uint2 *d_poolw = nullptr, *d_chunks = nullptr; // the pool as 2-bit words; the derived sequence as linear lane-chunk words
+    JournalEvRec *d_jrec = nullptr;                // per event: what the fast walk needs (journal_rec_kernel)
     size_t chunk_bytes = 0;
     void *d_tmp = nullptr;
     size_t d_tmp_bytes = 0;
@@ -738,8 +739,8 @@ static int journaled_pair(spmb_context *ctx, const spmb_store *base, const spmb_
         auto up = [](size_t x) { return (x + 255) / 256 * 256; };
         const size_t o_ev = 0, o_delta = o_ev + up(ne * sizeof(spmb_journal_event)), o_shift = o_delta + up(ne * 8),
                      o_total = o_shift + up(ne * 8), o_bad = o_total + 256, o_pool = o_bad + 256,
-                     o_poolw = o_pool + up(pool_len + 1), o_tmp = o_poolw + up(((pool_len + 31) / 32 + 2) * sizeof(uint2)),
-                     o_end = o_tmp + up(tmp_bytes + 1);
+                     o_poolw = o_pool + up(pool_len + 1), o_sym = o_poolw + up(((pool_len + 31) / 32 + 2) * sizeof(uint2)),
+                     o_tmp = o_sym + up(ne * sizeof(JournalEvRec)), o_end = o_tmp + up(tmp_bytes + 1);
         uint8_t *sc = nullptr;
         JCU(ctx_scratch(ctx, o_end, &sc));
         if (e != cudaSuccess) { cudaGetLastError(); return set_err(ctx, SPMB_ERR_OOM, "journal scratch", e); }
@@ -751,6 +752,7 @@ static int journaled_pair(spmb_context *ctx, const spmb_store *base, const spmb_
         d_bad = (int *)(sc + o_bad);
         d_pool = sc + o_pool;
         d_poolw = (uint2 *)(sc + o_poolw);
+        d_jrec = (JournalEvRec *)(sc + o_sym);
         d_tmp = sc + o_tmp;
         d_tmp_bytes = tmp_bytes;
     }
@@ -810,7 +812,11 @@ static int journaled_pair(spmb_context *ctx, const spmb_store *base, const spmb_
         chunk_bytes = ((n_der + 31) / 32 + 2) * sizeof(uint2);
         if (rc == SPMB_OK) JCU(big_alloc(ctx, chunk_bytes, (void **)&d_chunks));
         if (rc == SPMB_OK && e == cudaSuccess) {
-            JournalDeriveArgs ja{base->lanes, base->lay, d_ev, d_der, d_blk, d_poolw, n_ev, n_der, d_chunks};
+            if (n_ev) {
+                journal_rec_kernel<<<(unsigned)((n_ev + 255) / 256), 256, 0, sm>>>(d_ev, d_der, n_ev, d_poolw, d_jrec);
+                ctx->launches++;
+            }
+            JournalDeriveArgs ja{base->lanes, base->lay, d_ev, d_der, d_blk, d_poolw, d_jrec, n_ev, n_der, d_chunks};
             const uint64_t warps = (n_der + 1023) >> 10;
             const unsigned grid = (unsigned)std::min<uint64_t>((warps + 7) / 8, (uint64_t)ctx->sm_count * 32);
             if (n_der) journal_derive_kernel<<<grid, 256, 0, sm>>>(ja);
