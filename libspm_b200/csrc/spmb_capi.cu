@@ -508,6 +508,13 @@ static int store_alloc(spmb_context *ctx, uint64_t n, uint32_t row_len, uint32_t
     return SPMB_OK;
 }
 
+// pack_chunks_kernel walks its blocks with a stride of the grid: two resident CTAs per SM, a few rounds of slack
+static unsigned pack_grid(const spmb_context *ctx, const SpmbLayout &lay)
+{
+    const uint64_t blocks = lay.n_cols_alloc / 1024;
+    return (unsigned)std::min<uint64_t>(blocks, (uint64_t)ctx->sm_count * 2);
+}
+
 template <class Source>
 static int store_pack(spmb_context *ctx, spmb_store *s, const Source &src)
 {
@@ -616,7 +623,7 @@ static int store_create_pipelined(spmb_context *ctx, const uint8_t *host_ranks, 
         uint2 *l = nullptr;
         if (big_alloc(ctx, s->bytes, (void **)&l) != cudaSuccess) { cudaGetLastError(); l = nullptr; }
         ChunkSource src{d_chunks, n};
-        pack_chunks_kernel<ChunkSource><<<(unsigned)(s->lay.n_cols_alloc / 1024), 1024, 0, ctx->stream>>>(src, s->lay, s->planes, l);
+        pack_chunks_kernel<ChunkSource><<<pack_grid(ctx, s->lay), 1024, 0, ctx->stream>>>(src, s->lay, s->planes, l);
         s->lanes = l;
         ctx->launches++;
         e = cudaGetLastError();
@@ -821,7 +828,7 @@ static int journaled_pair(spmb_context *ctx, const spmb_store *base, const spmb_
             const unsigned grid = (unsigned)std::min<uint64_t>((warps + 7) / 8, (uint64_t)ctx->sm_count * 32);
             if (n_der) journal_derive_kernel<<<grid, 256, 0, sm>>>(ja);
             ChunkSource src{d_chunks, n_der};
-            pack_chunks_kernel<ChunkSource><<<(unsigned)(s->lay.n_cols_alloc / 1024), 1024, 0, sm>>>(src, s->lay, s->planes, l);
+            pack_chunks_kernel<ChunkSource><<<pack_grid(ctx, s->lay), 1024, 0, sm>>>(src, s->lay, s->planes, l);
             ctx->launches += 2;
             JCU(cudaGetLastError());
             s->lanes = l;
@@ -2359,7 +2366,7 @@ static int jst_prepare(spmb_context *ctx, spmb_jst *j, uint32_t W)
                 uint2 *l = nullptr;
                 if (big_alloc(ctx, b.store->bytes, (void **)&l) != cudaSuccess) { cudaGetLastError(); l = nullptr; }
                 WindowChunkSource src{j->ref->lanes, j->ref->lay, j->d_var, j->d_pool, j->d_win + first, j->d_win_vars, count, b.store->lay};
-                pack_chunks_kernel<WindowChunkSource><<<(unsigned)(b.store->lay.n_cols_alloc / 1024), 1024, 0, ctx->stream>>>(
+                pack_chunks_kernel<WindowChunkSource><<<pack_grid(ctx, b.store->lay), 1024, 0, ctx->stream>>>(
                     src, b.store->lay, b.store->planes, l);
                 ctx->launches++;
                 b.store->lanes = l;
@@ -2701,7 +2708,7 @@ static int stream_enqueue(spmb_context *ctx, spmb_stream *st, spmb_stream::Slot 
         const bool want_lanes = !(st->pat->alg == SPMB_ALG_HORSPOOL || st->pat->alg == SPMB_ALG_SHIFTOR);
         if (want_lanes && big_alloc(ctx, S.store->bytes, (void **)&l) != cudaSuccess) { cudaGetLastError(); l = nullptr; }
         ChunkSource src{S.d_words, total};
-        pack_chunks_kernel<ChunkSource><<<(unsigned)(S.store->lay.n_cols_alloc / 1024), 1024, 0, sm>>>(src, S.store->lay, S.store->planes, l);
+        pack_chunks_kernel<ChunkSource><<<pack_grid(ctx, S.store->lay), 1024, 0, sm>>>(src, S.store->lay, S.store->planes, l);
         S.store->lanes = l;
         ctx->launches++;
         CU(cudaGetLastError());
