@@ -396,9 +396,12 @@ def run_ours(args):
             dist.barrier()
         phase[:] = 0
         text_h2d = 0
+        step_ms = []
         t0 = time.perf_counter()
         for _ in range(e2e_steps):
+            ts = time.perf_counter()
             nh = e2e_once()
+            step_ms.append((time.perf_counter() - ts) * 1e3)
             us = ctx.upload_last_stats()
             # bytes that crossed PCIe for the haystack: raw chunks at 1 B/symbol, host-packed ones at 0.25
             text_h2d += (min(n, us["raw_chunks"] * us["chunk_symbols"]) + us["host_packed_chunks"] * us["chunk_symbols"] // 4
@@ -417,6 +420,7 @@ def run_ours(args):
         out["e2e"] = {"value": world * n_der * e2e_steps / e2e_s / 1e9, "unit": "Gbp/s",
                       "h2d_bytes_per_step": int(text_h2d + ev_h2d + m), "d2h_bytes_per_step": int(8 + nh * 24),
                       "steps": e2e_steps, "ms_per_step": e2e_s / e2e_steps * 1e3,
+                      "ms_per_step_median_this_rank": float(np.median(step_ms)), "ms_per_step_max_this_rank": float(max(step_ms)),
                       "host_input_bytes_per_step": int(n + ev_bytes + m),
                       "upload": ctx.upload_last_stats(),
                       "phase_ms": {"store_create(upload+pack)": phase[0] / e2e_steps * 1e3,

@@ -714,10 +714,12 @@ def stream_leg(ctx: Context, host: np.ndarray, pat, hits: Hits, chunk: int = 64 
     st.close()
     one = search_host(ctx, None, p, hits, ptr=base, n=n)
     ctx.sync()
-    t0 = time.perf_counter()
-    one = search_host(ctx, None, p, hits, ptr=base, n=n)
-    ctx.sync()
-    dt1 = time.perf_counter() - t0
+    dt1 = 1e30
+    for _ in range(2):      # best of two: the boxes are shared hosts, a one-off stall of the host side shows up now and then
+        t0 = time.perf_counter()
+        one = search_host(ctx, None, p, hits, ptr=base, n=n)
+        ctx.sync()
+        dt1 = min(dt1, time.perf_counter() - t0)
     # a sync feed() of the same chunks (what a caller of the reference's restorable matchers does)
     st = Stream(ctx, p)
     t0 = time.perf_counter()

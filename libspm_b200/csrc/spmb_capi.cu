@@ -607,6 +607,12 @@ static int ensure_upload(spmb_context *ctx)
 static int store_create_pipelined(spmb_context *ctx, const uint8_t *host_ranks, uint64_t n, uint32_t row_len,
                                   spmb_store **out)
 {
+    const bool trace = UploadPool::env_u64("SPMB_UPLOAD_TRACE", 0) != 0;
+    auto tnow = [] { return std::chrono::steady_clock::now(); };
+    auto tms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+        return std::chrono::duration<double, std::milli>(b - a).count();
+    };
+    const auto t0 = tnow();
     int rcu = ensure_upload(ctx);
     if (rcu) return rcu;
     spmb_store *s = nullptr;
@@ -616,7 +622,9 @@ static int store_create_pipelined(spmb_context *ctx, const uint8_t *host_ranks, 
     const size_t chunk_bytes = (n + 31) / 32 * sizeof(uint2);
     cudaError_t e = big_alloc(ctx, chunk_bytes, (void **)&d_chunks);
     if (e != cudaSuccess) { cudaGetLastError(); spmb_store_destroy(s); return set_err(ctx, SPMB_ERR_OOM, "cudaMallocAsync(chunks)", e); }
+    const auto t1 = tnow();
     e = ctx->upload->run(host_ranks, n, d_chunks, ctx->stream, &ctx->launches);
+    const auto t2 = tnow();
     if (e == cudaSuccess) {
         // the lane-chunk copy the Myers / journal kernels read is the same words in another order: write it
         // now instead of deriving it from the planes later (skipped when memory is short)
@@ -629,7 +637,11 @@ static int store_create_pipelined(spmb_context *ctx, const uint8_t *host_ranks, 
         e = cudaGetLastError();
     }
     big_free(ctx, d_chunks, chunk_bytes);
+    const auto t3 = tnow();
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (trace)
+        fprintf(stderr, "[spmb store_create] allocs %.2f ms  upload %.2f  enqueue pack %.2f  sync %.2f\n", tms(t0, t1), tms(t1, t2), tms(t2, t3),
+                tms(t3, tnow()));
     if (e != cudaSuccess) { cudaGetLastError(); spmb_store_destroy(s); return set_err(ctx, SPMB_ERR_CUDA, "store upload", e); }
     *out = s;
     return SPMB_OK;
