@@ -98,9 +98,15 @@ __device__ __forceinline__ uint32_t exact_verify(const ExactArgs &a, uint64_t gc
         const uint32_t j = j0 + lane;
         uint32_t mm = 0xffffffffu;
         if (j < a.m) {
-            const int64_t xi = col - (int64_t)a.fo + (int64_t)j;
-            int64_t wraps = xi >= 0 ? xi / RL : -((-xi + RL - 1) / RL);
-            const uint64_t x = (uint64_t)(xi - wraps * RL);
+            // column of needle symbol j relative to the row start: inside the row almost always (no division then);
+            // |xi| < 32 rows of at most 65536 columns, so 32-bit arithmetic (a 64-bit division here cost the C2x
+            // kernel 4 % through its 49 k filter survivors per pass)
+            const int32_t rl = (int32_t)RL;
+            const int32_t xi = (int32_t)col - (int32_t)a.fo + (int32_t)j;
+            int32_t wraps = 0;
+            if (xi >= rl) wraps = xi / rl;
+            else if (xi < 0) wraps = -((-xi + rl - 1) / rl);
+            const uint64_t x = (uint64_t)(xi - wraps * rl);
             const uint32_t s = a.pat[j];
             uint32_t h, l, hh = 0, lh = 0;
             if (wraps == 0) {
