@@ -44,7 +44,10 @@
 // the exact lookup behind the bitmap compares the whole key anyway.  The bitmap holds 2^B bits (B <= 20: 128 KB):
 // x = h >> (32 - B) picks the word (x >> 5) and one bit (x & 31), h & 31 a second one for wide keys.  A bitmap of
 // any size through a multiply-high of the hash (192 KB would halve the false positives) was measured and dropped:
-// IMAD.HI made the scan 36 % slower, whatever the size.
+// IMAD.HI made the scan 36 % slower, whatever the size.  So was a second table of 64 KB behind the first (one more
+// bit per key from its own hash: 1.9 % false positives instead of 7.3 %): the five ALU instructions per position it
+// costs outweigh the survivors it removes (C5 1.183 -> 1.224 ms) -- the scan is ALU-pipe-bound, the survivors' exact
+// look-ups are latency that other warps cover.
 SPMB_HD uint32_t pg_h1(uint32_t hi) { return hi * 0x9E3779B1u; }
 SPMB_HD uint32_t pg_h3(uint32_t hi, uint32_t lo) // second-level bitmap
 {
