@@ -21,4 +21,8 @@ python tools/ncu_extract.py gpurun_out/*.ncu-rep > gpurun_out/r02_ncu_extract.lo
 timeout 900 python bench.py --steps 3 --warmup 3 --no-cpu > gpurun_out/bench_s3.json 2> gpurun_out/bench_s3.err &&
   timeout 1500 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file gpurun_out/r02_bench_launches.csv python bench.py --steps 3 --warmup 3 --no-cpu > gpurun_out/ncu_bench.log 2>&1
 echo "launch list rc=$?"
+# the later legs of the bench command (Myers C3, JST C4, C5, C1/C2) -- the first list ends inside the stream leg
+timeout 900 python bench.py --steps 3 --warmup 3 --no-cpu --no-stream --no-multi --e2e-steps 1 > gpurun_out/bench_s3b.json 2> gpurun_out/bench_s3b.err &&
+  timeout 1500 ncu --metrics gpu__time_duration.sum --clock-control none -s 2500 -c 6000 --csv --log-file gpurun_out/r02_bench_launches_late.csv python bench.py --steps 3 --warmup 3 --no-cpu --no-stream --no-multi --e2e-steps 1 > gpurun_out/ncu_bench_b.log 2>&1
+echo "late launch list rc=$?"
 
