@@ -239,6 +239,37 @@ int spmb_search_anchored(spmb_context *ctx, const spmb_store *s, const spmb_patt
 /* number of kernel launches the last search enqueued (bench.py's gpu_launches). */
 uint32_t spmb_last_launch_count(const spmb_context *ctx);
 
+/* Allocation-free variant of spmb_search for SPMB_ALG_MYERS_FILTERED sets.  It has NO counterpart in the
+ * reference: it was added for callers that cannot allocate device
+ * memory where they search (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * spmb_search keeps the seed filter's candidate list, its counters and the duplicate-suppression table in
+ * buffers of the spmb_hits object, allocated and grown on demand; here they live in ONE file-scope
+ * `static __device__` array of 3.5 MiB + 256 B that every GPU loading libspmb.so holds until the process
+ * exits.  The call makes no cudaMalloc / cudaFree / allocating library call; the caller passes the inputs
+ * (a plain 2-bit store and a filtered Myers set, both made at set-up) and the outputs:
+ *   dev_hits  DEVICE array of `capacity` records; receives the hit records UNORDERED (spmb_search sorts on
+ *             the way back, this call does not touch the host list of any spmb_hits).  A (pattern_id, end)
+ *             normally appears once, with its smallest error count; when the 2^17-slot table is crowded a few
+ *             appear again -- keep the smallest `errors` (what spmb_search's ordering does);
+ *   dev_count DEVICE counter, receives the number of records; *count_out the same number on the host.
+ * Limits, refused with a clear spmb_last_error() before anything is launched: store longer than
+ * SPMB_NOALLOC_MAX_SYMBOLS, capacity beyond SPMB_NOALLOC_MAX_HITS, a store without its lane-chunk copy (the
+ * first Myers / filtered spmb_search on a store derives it, with an allocation: run one at set-up), another
+ * algorithm, a set whose seed filter is off, windows-mode or 4-bit stores.  Data-dependent limits, reported
+ * as SPMB_ERR_OOM after the run (dev_hits is then incomplete): more than SPMB_NOALLOC_MAX_CANDIDATES filter
+ * survivors, or more records than `capacity` (*count_out then holds the number needed).
+ * The call returns when the kernels are done (it synchronises the context's stream).  The first call on a
+ * device looks the array up (cudaGetSymbolAddress, which also loads the module): make one call at set-up.
+ * ALL calls of a process on one GPU share the array -- it keeps the last call's contents, the call clears what
+ * must start at zero -- so two calls that overlap on the GPU (two contexts / streams / host threads on one
+ * device) race on it: serialise them. */
+#define SPMB_NOALLOC_MAX_CANDIDATES 131072u
+#define SPMB_NOALLOC_MAX_SYMBOLS (1ull << 32)
+#define SPMB_NOALLOC_MAX_HITS (1ull << 24)
+int spmb_search_filtered_noalloc(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p,
+                                 spmb_hit *dev_hits, uint64_t capacity, unsigned long long *dev_count,
+                                 uint64_t *count_out);
+
 /* ---------------- resumable search (capture / restore) ----------------
  * restorable_myers_matcher / restorable_shiftor_matcher
  * (myers_matcher_restorable.hpp:57-63,72-82; shiftor_matcher_restorable.hpp:44-63):

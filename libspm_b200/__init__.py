@@ -54,6 +54,7 @@ EXPORTS = [
     "spmb_multi_store_create", "spmb_multi_store_create_journaled", "spmb_multi_store_destroy", "spmb_multi_store_length",
     "spmb_multi_store_shards", "spmb_multi_pattern_create", "spmb_multi_pattern_destroy", "spmb_multi_search",
     "spmb_multi_search_host", "spmb_multi_last_stats",
+    "spmb_search_filtered_noalloc",
 ]
 
 
@@ -163,6 +164,7 @@ def lib():
             "spmb_search_finish": (i32, [vp, vp]),
             "spmb_search": (i32, [vp, vp, vp, vp]),
             "spmb_search_host": (i32, [vp, vp, u64, vp, vp]),
+            "spmb_search_filtered_noalloc": (i32, [vp, vp, vp, vp, u64, vp, C.POINTER(u64)]),
             "spmb_last_launch_count": (u32, [vp]),
             "spmb_stream_create": (i32, [vp, vp, pp]),
             "spmb_stream_destroy": (i32, [vp]),

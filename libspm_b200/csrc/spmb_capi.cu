@@ -2143,6 +2143,144 @@ extern "C" int spmb_search(spmb_context *ctx, const spmb_store *s, const spmb_pa
     return spmb_search_finish(ctx, h);
 }
 
+// ------------------------------------------------------------------------------------------
+// allocation-free filtered search (spmb.h: no counterpart in the reference).
+// The seed filter's candidate list, its counters and the duplicate-suppression table
+// live in ONE file-scope device array instead of buffers of a spmb_hits object: nothing is allocated,
+// grown or freed here.  Every GPU that loads this library holds the array until the process exits.
+// ------------------------------------------------------------------------------------------
+enum : unsigned long long {
+    SPMB_NA_COUNTER_BYTES = 256,                                              // 4 counters, padded
+    SPMB_NA_DD_BYTES = 12ull << SPMB_DD_BITS,                                 // 8-byte keys + 4-byte minima
+    SPMB_NA_CAND_BYTES = (unsigned long long)SPMB_NOALLOC_MAX_CANDIDATES * sizeof(PigeonCand),
+    SPMB_NA_BYTES = SPMB_NA_COUNTER_BYTES + SPMB_NA_DD_BYTES + SPMB_NA_CAND_BYTES // 3.5 MiB + 256 B
+};
+static_assert(SPMB_NA_DD_BYTES % 256 == 0, "the candidate records start on a 256-byte boundary");
+static_assert(SPMB_NA_BYTES == 256 + (3ull << 20) + (1ull << 19), "spmb.h states 3.5 MiB + 256 B");
+
+// In host code this name is only a handle for cudaGetSymbolAddress -- never a pointer a kernel may be given.
+static __device__ __align__(256) unsigned char spmb_noalloc_scratch[SPMB_NA_BYTES];
+
+// the array's address on the context's device (looked up once per device, with that device current)
+static int noalloc_scratch(spmb_context *ctx, unsigned char **out)
+{
+    enum { MAX_DEV = 64 };
+    static std::mutex mu;
+    static unsigned char *addr[MAX_DEV] = {nullptr};
+    if (ctx->device < 0 || ctx->device >= MAX_DEV) return set_err(ctx, SPMB_ERR_UNSUPPORTED, "no-alloc search: device ordinal beyond 63");
+    std::lock_guard<std::mutex> g(mu);
+    if (!addr[ctx->device]) {
+        void *p = nullptr;
+        CU(cudaGetSymbolAddress(&p, spmb_noalloc_scratch));
+        if (!p) return set_err(ctx, SPMB_ERR_CUDA, "cudaGetSymbolAddress(spmb_noalloc_scratch) gave no address");
+        addr[ctx->device] = static_cast<unsigned char *>(p);
+    }
+    *out = addr[ctx->device];
+    return SPMB_OK;
+}
+
+extern "C" int spmb_search_filtered_noalloc(spmb_context *ctx, const spmb_store *s, const spmb_pattern *p,
+                                            spmb_hit *dev_hits, uint64_t capacity, unsigned long long *dev_count,
+                                            uint64_t *count_out)
+{
+    if (!ctx || !s || !p || !dev_count || !count_out || (!dev_hits && capacity)) return SPMB_ERR_ARG;
+    ENTER(ctx);
+    ctx->launches = 0;
+    *count_out = 0;
+    if (p->alg != SPMB_ALG_MYERS_FILTERED || !p->filtered || p->pg.seed_pat.empty() || p->NW < 1 || p->NW > 8)
+        return set_err(ctx, SPMB_ERR_UNSUPPORTED, "no-alloc search: takes a SPMB_ALG_MYERS_FILTERED set whose seed filter is in use "
+                                                  "(spmb_pattern_filter_info: step != 0)");
+    if (s->lay.mode != SPMB_MODE_PLAIN || s->sym_bits != 2 || p->sym_bits != 2 || s->hi)
+        return set_err(ctx, SPMB_ERR_UNSUPPORTED, "no-alloc search: plain 2-bit stores only");
+    if (s->lay.n > SPMB_NOALLOC_MAX_SYMBOLS)
+        return set_err(ctx, SPMB_ERR_UNSUPPORTED, "no-alloc search: haystack longer than SPMB_NOALLOC_MAX_SYMBOLS");
+    if (capacity > SPMB_NOALLOC_MAX_HITS)
+        return set_err(ctx, SPMB_ERR_UNSUPPORTED, "no-alloc search: hit capacity beyond SPMB_NOALLOC_MAX_HITS");
+    if (!s->lanes)
+        return set_err(ctx, SPMB_ERR_ARG, "no-alloc search: the store has no lane-chunk copy yet (it is derived, with an allocation, "
+                                          "by the first Myers / filtered spmb_search on the store: run one at set-up)");
+    unsigned char *scratch = nullptr;
+    int rc = noalloc_scratch(ctx, &scratch);
+    if (rc) return rc;
+    unsigned long long *counters = reinterpret_cast<unsigned long long *>(scratch);
+    unsigned long long *dd_keys = reinterpret_cast<unsigned long long *>(scratch + SPMB_NA_COUNTER_BYTES);
+    PigeonCand *cand = reinterpret_cast<PigeonCand *>(scratch + SPMB_NA_COUNTER_BYTES + SPMB_NA_DD_BYTES);
+    // the array keeps the last call's contents: counters and table start at zero (the candidate records are
+    // only read below the counter, so they need no clearing)
+    CU(cudaMemsetAsync(scratch, 0, SPMB_NA_COUNTER_BYTES + SPMB_NA_DD_BYTES, ctx->stream));
+    CU(cudaMemsetAsync(dev_count, 0, sizeof(unsigned long long), ctx->stream));
+    if (s->lay.n == 0 || p->max_m == 0) { CU(cudaStreamSynchronize(ctx->stream)); return SPMB_OK; }
+    const uint64_t st0 = s->lay.n_st * ctx->shard / ctx->n_shards;
+    const uint64_t st1 = s->lay.n_st * (ctx->shard + 1) / ctx->n_shards;
+    if (st1 <= st0) { CU(cudaStreamSynchronize(ctx->stream)); return SPMB_OK; }
+    const uint64_t per_st = 32ull * s->lay.row_len;
+    HitSink sink{dev_hits, dev_count, capacity};
+    PigeonFilterArgs fa;
+    fa.lanes = s->lanes; fa.lay = s->lay; fa.pg = pigeon_dev(p);
+    fa.row_len = s->row_len;
+    fa.st0 = st0; fa.st1 = st1;
+    if (st0 > 0) { // a hit owned by this shard may hang on a seed that begins up to m+k symbols before it
+        const uint64_t back = ((uint64_t)p->max_m + p->k + per_st - 1) / per_st;
+        fa.st0 = st0 > back ? st0 - back : 0;
+    }
+    fa.cand = cand; fa.cand_count = counters + 1; fa.cand_cap = SPMB_NOALLOC_MAX_CANDIDATES;
+    const uint64_t chunk_cols = (fa.st1 - fa.st0) * (s->lay.row_len / 32);
+    unsigned grid = (unsigned)std::min<uint64_t>((uint64_t)ctx->sm_count, (chunk_cols + 255) / 256);
+    if (grid == 0) grid = 1;
+    const size_t smem = ((size_t)4 << (p->pg.B - 5)) + 32 * PG_QCAP * 4;
+    cudaError_t e;
+    if (p->pg.kq <= 16) e = launch_filter_kernel<SPMB_MODE_PLAIN, false, 1>(ctx, fa, grid, smem);
+    else if (p->filter_step == 4) e = launch_filter_kernel<SPMB_MODE_PLAIN, true, 4>(ctx, fa, grid, smem);
+    else if (p->filter_step == 2) e = launch_filter_kernel<SPMB_MODE_PLAIN, true, 2>(ctx, fa, grid, smem);
+    else e = launch_filter_kernel<SPMB_MODE_PLAIN, true, 1>(ctx, fa, grid, smem);
+    if (e != cudaSuccess) return set_err(ctx, SPMB_ERR_CUDA, "pigeon_filter_kernel launch (no-alloc)", e);
+    PigeonVerifyArgs va;
+    va.lanes = s->lanes; va.lay = s->lay; va.pg = fa.pg;
+    va.cand = cand; va.counters = counters; va.cand_cap = SPMB_NOALLOC_MAX_CANDIDATES;
+    va.pat_ranks = p->d_ranks; va.pat_off = p->d_off; va.eq = p->d_eq; va.meta = p->d_meta;
+    va.row_len = s->row_len; va.row_seq = s->row_seq; va.row_own = s->row_own;
+    va.seq_id = 0;
+    va.own_lo = st0 * per_st;
+    va.own_hi = std::min<uint64_t>(s->lay.n, st1 * per_st);
+    va.sink = sink;
+    va.dd_keys = nullptr; va.dd_err = nullptr; va.dd_bits = SPMB_DD_BITS; va.dd_end_bits = 0; va.dd_nseq = 1;
+    if (p->k < 255) { // the table's key: (needle, end); else every finder reports and the caller removes the duplicates
+        const int eb = bits_for(s->lay.n + 1);
+        if (bits_for((uint64_t)p->n_pat) + eb <= 62) {
+            va.dd_keys = dd_keys; va.dd_err = reinterpret_cast<uint32_t *>(dd_keys + ((size_t)1 << SPMB_DD_BITS));
+            va.dd_end_bits = (uint32_t)eb;
+        }
+    }
+    e = launch_verify<SPMB_MODE_PLAIN>(ctx, p, va);
+    if (e != cudaSuccess) return set_err(ctx, SPMB_ERR_CUDA, "pigeon verify launch (no-alloc)", e);
+    ctx->launches += 2;
+    if (va.dd_keys && capacity) {
+        const unsigned fgrid = (unsigned)std::min<unsigned long long>((capacity + 255) / 256, (unsigned long long)ctx->sm_count * 4);
+        pigeon_fixup_kernel<<<fgrid ? fgrid : 1, 256, 0, ctx->stream>>>(dev_hits, dev_count, capacity, va.dd_err);
+        ctx->launches++;
+        CU(cudaGetLastError());
+    }
+    // counters back through the context's pinned slots (allocated with the context)
+    CU(cudaMemcpyAsync(ctx->h_count, counters, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->h_count + 4, dev_count, sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    const unsigned long long n_cand = std::max(ctx->h_count[1], ctx->h_count[2]);
+    *count_out = ctx->h_count[4];
+    if (n_cand > SPMB_NOALLOC_MAX_CANDIDATES) {
+        char msg[160];
+        snprintf(msg, sizeof msg, "no-alloc search: %llu filter candidates, the scratch array holds %u (use spmb_search)", n_cand,
+                 (unsigned)SPMB_NOALLOC_MAX_CANDIDATES);
+        return set_err(ctx, SPMB_ERR_OOM, msg);
+    }
+    if (ctx->h_count[4] > capacity) {
+        char msg[160];
+        snprintf(msg, sizeof msg, "no-alloc search: %llu hit records, the caller's buffer holds %llu", ctx->h_count[4],
+                 (unsigned long long)capacity);
+        return set_err(ctx, SPMB_ERR_OOM, msg);
+    }
+    return SPMB_OK;
+}
+
 extern "C" int spmb_search_host_wide(spmb_context *ctx, const uint8_t *host_ranks, uint64_t n, uint32_t bits,
                                      const spmb_pattern *p, spmb_hits *h)
 {
