@@ -3,8 +3,7 @@
 set -u
 mkdir -p gpurun_out
 nvidia-smi -L | wc -l; nproc; free -g | head -2
-timeout 300 python -m pytest tests/test_gpu_multi.py -m gpu -q -p no:cacheprovider 2>&1 | tail -2
-timeout 600 python tools/multi_ab.py --out gpurun_out/multi_ab_n8.json 2>&1 | tail -5
-timeout 300 python tools/multi_ab.py --threads 0 --out gpurun_out/multi_ab_n8_raw.json 2>&1 | tail -5
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 8 --steps 10 --warmup 3 > gpurun_out/bench_n8.json 2> gpurun_out/bench_n8.err
+timeout 120 python -m pytest tests/test_gpu_multi.py -m gpu -q -p no:cacheprovider 2>&1 | tail -2
+timeout 200 python tools/multi_ab.py --out gpurun_out/multi_ab_n8.json 2>&1 | tail -5
+timeout 240 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 8 --steps 10 --warmup 3 > gpurun_out/bench_n8.json 2> gpurun_out/bench_n8.err
 echo "bench n8 rc=$?"; tail -c 300 gpurun_out/bench_n8.err
