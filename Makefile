@@ -7,7 +7,7 @@ CSRC := libspm_b200/csrc
 LIB := libspm_b200/lib/libspmb.so
 SYNTH := libspm_b200/lib/libspmsynth.so
 HOSTCXX := $(shell test -x /usr/bin/g++ && echo /usr/bin/g++ || echo g++)
-HDRS := $(wildcard $(CSRC)/*.cuh) include/spmb.h
+HDRS := $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/*.hpp) include/spmb.h
 
 all: $(LIB) $(SYNTH) oracle
 

@@ -196,6 +196,116 @@ class HitGather:
         return np.concatenate(parts)
 
 
+class HitGatherShm:
+    """the same final gather for ranks that share ONE host (torchrun, one node: LOCAL_WORLD_SIZE == WORLD_SIZE).
+    spmb_search_finish has already delivered every pass's sorted list to HOST memory, so the gather is a host-side
+    exchange: every rank writes its lists straight into its slot of a POSIX shared-memory segment (/dev/shm) as the
+    passes arrive, publishes a generation flag behind its last pass and waits for the flags of the others -- from then
+    on every rank holds (has mapped) the lists of all ranks and passes.  No device bounce: the NCCL form (HitGather)
+    moved host -> device -> all_gather -> host and cost 0.17 ms per timed region for 101-hit lists and 0.4-1.2 ms for the
+    C5 lists (profiles/r02_gather_n2.txt).  Two generations of slots alternate, so a rank that is one gather ahead never
+    overwrites what a slower rank still reads.  x86 only (stores stay in program order: data, then flag); other
+    hosts and multi-node jobs take the NCCL form."""
+    FLAG = 64
+
+    def __init__(self, torch, dist, dev, world, rank):
+        self.torch, self.dist, self.dev, self.world, self.rank = torch, dist, dev, world, rank
+        self.gen = 0
+        self.gathers = 0
+        self.overflow = False
+        self.mm = None
+
+    @staticmethod
+    def usable(world):
+        import platform
+        return (platform.machine() in ("x86_64", "AMD64") and os.path.isdir("/dev/shm")
+                and int(os.environ.get("LOCAL_WORLD_SIZE", "0")) == world
+                and os.environ.get("SPMB_BENCH_GATHER", "shm") == "shm")
+
+    def prepare(self, n_first, passes):
+        """warm-up (untimed): agree on the per-pass capacity, create and map the segment, run one gather"""
+        torch, dist = self.torch, self.dist
+        c = torch.tensor([int(n_first)], dtype=torch.int64, device=self.dev)
+        dist.all_reduce(c, op=dist.ReduceOp.MAX)
+        self.cap = int(c.item()) * 5 // 4 + 64
+        self.passes = passes
+        self.rec_bytes = self.cap * 24
+        self.region = (self.FLAG + 8 * passes + passes * self.rec_bytes + 63) // 64 * 64   # flag | counts | records
+        total = 2 * self.world * self.region
+        HitGatherShm.serial = getattr(HitGatherShm, "serial", 0) + 1
+        path = "/dev/shm/spmb_gather_%s_%s_%d" % (os.environ.get("MASTER_PORT", "0"),
+                                                  os.environ.get("TORCHELASTIC_RUN_ID", "0"), HitGatherShm.serial)
+        if self.rank == 0:
+            self.mm = np.memmap(path, dtype=np.uint8, mode="w+", shape=(total,))
+            self.mm[:] = 0
+        dist.barrier()
+        if self.rank != 0:
+            self.mm = np.memmap(path, dtype=np.uint8, mode="r+", shape=(total,))
+        dist.barrier()
+        if self.rank == 0:
+            os.unlink(path)                       # the segment lives as long as it is mapped
+        self.grid = self.mm.reshape(2 * self.world, self.region)
+        self.flags = self.grid[:, :8].view(np.uint64).reshape(-1)
+        self.counts = self.grid[:, self.FLAG:self.FLAG + 8 * passes].view(np.uint64)          # [2 * world, passes]
+        self.gen = 0
+        self.finish()
+
+    def _row(self, gen, rank):
+        return (gen & 1) * self.world + rank
+
+    def add(self, i, hits):
+        n = len(hits)
+        if n > self.cap:
+            self.overflow = True
+            n = self.cap
+        row = self._row(self.gen + 1, self.rank)
+        self.counts[row, i] = n
+        if n:
+            o = self.FLAG + 8 * self.passes + i * self.rec_bytes
+            self.grid[row, o:o + n * 24] = hits[:n].view(np.uint8).reshape(-1)
+
+    def finish(self):
+        """publish this rank's lists, wait for every rank's: returns the merged record count over ranks and passes"""
+        self.gen += 1
+        g = self.gen
+        base = (g & 1) * self.world
+        self.flags[base + self.rank] = g
+        fl = self.flags[base:base + self.world]
+        t_end = time.perf_counter() + 60.0
+        while not (fl == g).all():
+            if time.perf_counter() > t_end:
+                raise RuntimeError("HitGatherShm: a rank did not publish its hit lists within 60 s")
+        self.gathers += 1
+        return int(self.counts[base:base + self.world].sum())
+
+    def merged(self, hit_dtype, i=0):
+        """the merged list of pass i of the last gather (rank-major), for checks outside the timed region"""
+        base = (self.gen & 1) * self.world
+        parts = []
+        o = self.FLAG + 8 * self.passes + i * self.rec_bytes
+        for r in range(self.world):
+            n = int(self.counts[base + r, i])
+            parts.append(np.array(self.grid[base + r, o:o + n * 24]).view(hit_dtype))
+        return np.concatenate(parts)
+
+
+def gather_note(gather):
+    if gather is None:
+        return False
+    if isinstance(gather, HitGatherShm):
+        return ("all passes' lists gathered inside the timed region: ranks of one host write their (host-resident) lists into a "
+                "shared-memory segment and wait for each other's flags behind the last pass; no device bounce")
+    return "all passes' lists in one final all_gather (NCCL) inside the timed region"
+
+
+def make_gather(torch, dist, dev, world, rank):
+    if world <= 1:
+        return None
+    if HitGatherShm.usable(world):
+        return HitGatherShm(torch, dist, dev, world, rank)
+    return HitGather(torch, dist, dev, world)
+
+
 def time_search(sp, torch, ctx, stream, store, pattern, hits, steps, warmup, flush=None, gather=None):
     """returns (total_ms for `steps` launch+finish passes (+ the final gather), mean kernel ms, n_hits, launches/step).
     The passes are pipelined the way the launch/finish pair of the C ABI is meant to be used: passes i+1 and
@@ -221,11 +331,17 @@ def time_search(sp, torch, ctx, stream, store, pattern, hits, steps, warmup, flu
     n_hits = 0
     merged_hits = None
 
+    trace = [] if os.environ.get("SPMB_BENCH_TRACE") else None   # host timeline of the passes (tools/r02_trace.sh)
+    t_origin = time.perf_counter()
+
     def launch(i):
         if flush is not None:
             flush.add_(1)       # evict L2 between iterations (buffer > L2)
         ks[i].record(stream)
+        t_a = time.perf_counter()
         sp.search_launch(ctx, store, pattern, hl[i % DEPTH])
+        if trace is not None:
+            trace.append(("launch", i, (t_a - t_origin) * 1e3, (time.perf_counter() - t_origin) * 1e3))
         ke[i].record(stream)
 
     for i in range(min(DEPTH - 1, steps)):
@@ -233,16 +349,27 @@ def time_search(sp, torch, ctx, stream, store, pattern, hits, steps, warmup, flu
     for i in range(steps):
         if i + DEPTH - 1 < steps:
             launch(i + DEPTH - 1)
-        h = sp.search_finish(ctx, hl[i % DEPTH])
+        t_a = time.perf_counter()
+        h = sp.search_finish(ctx, hl[i % DEPTH], copy=False)   # the library's host list itself (spmb_hits_data)
         n_hits = len(h)
+        t_b = time.perf_counter()
         if gather is not None:
             gather.add(i, h)
+        if trace is not None:
+            trace.append(("finish", i, (t_a - t_origin) * 1e3, (t_b - t_origin) * 1e3, (time.perf_counter() - t_origin) * 1e3))
+    em = torch.cuda.Event(enable_timing=True)
+    em.record(stream)                                          # last pass collected: what follows is the gather alone
     if gather is not None:                                     # the final gather: all passes' lists, inside the timed region
         merged_hits = gather.finish() // max(1, steps)
     e1.record(stream)
     torch.cuda.synchronize()
     kern = [ks[i].elapsed_time(ke[i]) for i in range(steps)]
     total = e0.elapsed_time(e1)
+    time_search.gather_ms = em.elapsed_time(e1) if gather is not None else None
+    if trace is not None:
+        gpu = [(round(e0.elapsed_time(ks[i]), 3), round(e0.elapsed_time(ke[i]), 3)) for i in range(steps)]
+        print(json.dumps({"trace_host_ms": [[t[0], t[1]] + [round(x, 3) for x in t[2:]] for t in trace], "gpu_launch_ms": gpu,
+                          "total_ms": total}), file=sys.stderr, flush=True)
     if flush is not None:       # take the flush writes out of the step time
         f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         f0.record(stream)
@@ -325,7 +452,7 @@ def run_ours(args):
         pattern = sp.Pattern(ctx, sp.ALG_SHIFTOR, pat)
         setup_s = time.perf_counter() - t0
 
-        gather = HitGather(torch, dist, dev, world) if world > 1 else None
+        gather = make_gather(torch, dist, dev, world, rank)
         if world > 1:
             dist.barrier()
         # clocks are sampled from the warm-up to the end of the e2e legs (the timed region of the
@@ -349,11 +476,12 @@ def run_ours(args):
                        "row_len": js.row_len, "journal_materialise_ms": journal_ms,
                        "journal_materialise_note": "spmb_store_create_journaled on a resident base, events from pinned host "
                                                    "memory: event upload + prefix + pack_chunks_kernel<JournalSource>",
-                       "hit_lists_gathered": ("all passes' lists in one final all_gather inside the timed region" if gather else False),
+                       "hit_lists_gathered": gather_note(gather),
                        "merged_hits_per_pass_rank0": getattr(time_search, "merged_hits", None),
+                       "final_gather_ms_this_rank": getattr(time_search, "gather_ms", None),
                        "step": "kernel launch + hit count/list D2H + host sort; passes i+1 and i+2 are queued before pass i's "
                                "hits are collected (spmb_search_launch / spmb_search_finish on three hit lists)"
-                               + ("; every pass's hit list is all-gathered to rank 0 inside the timed region" if gather else "")},
+                               + ("; the hit lists of all passes are gathered to every rank inside the timed region" if gather else "")},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                          "frac": achieved / hbm_peak,
                          "traffic": cap.get("dram_bytes") if isinstance(cap, dict) else cap,
@@ -764,7 +892,7 @@ def bench_c5(sp, synth, torch, ctx, dev, stream, hits, args, rank, world):
     gather = None
     if world > 1:
         import torch.distributed as dist
-        gather = HitGather(torch, dist, dev, world)
+        gather = make_gather(torch, dist, dev, world, rank)
         dist.barrier()
     total_ms, kern_ms, n_hits, launches = time_search(sp, torch, ctx, stream, store, pset, hits, args.steps, args.warmup,
                                                       gather=gather)
@@ -788,8 +916,9 @@ def bench_c5(sp, synth, torch, ctx, dev, stream, hits, args, rank, world):
            "value": n * args.steps / (total_ms * 1e-3) / 1e9, "unit": "Gbp/s (x 10k patterns)", "ms_per_step": total_ms / args.steps,
            "kernels_ms": kern_ms, "cell_rate_T_per_s": n * n_pat * args.steps / (total_ms * 1e-3) / 1e12,
            "hits": n_hits, "filter": pset.filter_info, "scaling": "strong",
-           "hit_lists_gathered": ("all passes' lists in one final all_gather inside the timed region" if gather else False),
+           "hit_lists_gathered": gather_note(gather),
            "merged_hits_per_pass_rank0": getattr(time_search, "merged_hits", None),
+           "final_gather_ms_this_rank": getattr(time_search, "gather_ms", None),
            "equals_direct_myers_kernel_16_patterns_this_shard": same,
            "text_gbytes_per_s_kernels": n / world * 0.25 / (kern_ms * 1e-3) / 1e9}
     if rank == 0 and world == 1 and not args.no_cpu:

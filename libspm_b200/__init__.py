@@ -444,13 +444,16 @@ class Hits:
     def __len__(self):
         return int(lib().spmb_hits_count(self._h))
 
-    def array(self) -> np.ndarray:
+    def array(self, copy: bool = True) -> np.ndarray:
+        """the hit list; copy=False: a view of the library's host memory (spmb_hits_data), valid until the next
+        search on this hit list."""
         n = len(self)
         if n == 0:
             return np.zeros(0, dtype=HIT_DTYPE)
         ptr = lib().spmb_hits_data(self._h)
         buf = (C.c_char * (n * HIT_DTYPE.itemsize)).from_address(ptr)
-        return np.frombuffer(buf, dtype=HIT_DTYPE, count=n).copy()
+        a = np.frombuffer(buf, dtype=HIT_DTYPE, count=n)
+        return a.copy() if copy else a
 
     def close(self):
         if self._h:
@@ -492,9 +495,9 @@ def search_launch(ctx: Context, store: Store, pattern: Pattern, hits: Hits):
     ctx._check(lib().spmb_search_launch(ctx._h, store._h, pattern._h, hits._h), "spmb_search_launch")
 
 
-def search_finish(ctx: Context, hits: Hits) -> np.ndarray:
+def search_finish(ctx: Context, hits: Hits, copy: bool = True) -> np.ndarray:
     ctx._check(lib().spmb_search_finish(ctx._h, hits._h), "spmb_search_finish")
-    return hits.array()
+    return hits.array(copy)
 
 
 def search_host(ctx: Context, haystack, pattern: Pattern, hits: Hits | None = None, ptr: int | None = None,

@@ -87,3 +87,56 @@ def test_slice_math_covers_everything():
             assert owned[0][0] == 0 and owned[-1][1] == n
             for a, b in zip(owned, owned[1:]):
                 assert a[1] == b[0]
+
+
+def _shm_worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    os.environ["LOCAL_WORLD_SIZE"] = str(world)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import bench
+    from libspm_b200 import HIT_DTYPE
+    assert bench.HitGatherShm.usable(world)
+    g = bench.make_gather(torch, dist, torch.device("cpu"), world, rank)
+    assert isinstance(g, bench.HitGatherShm)
+    passes = 4
+    rng = np.random.default_rng(7)
+    lists = [[None] * passes for _ in range(world)]   # every rank draws the same lists, writes only its own
+    sizes = [[int(rng.integers(0, 90)) for _ in range(passes)] for _ in range(world)]
+    ok = True
+    for rnd in range(3):                              # three gathers in a row over the two generations of slots
+        for r in range(world):
+            for i in range(passes):
+                h = np.zeros(sizes[r][i] if rnd != 1 else sizes[r][i] // 2, dtype=HIT_DTYPE)
+                h["end"] = rng.integers(0, 1 << 40, size=len(h))
+                h["pattern_id"] = r * 100 + i + rnd
+                lists[r][i] = h
+        if rnd == 0:
+            g.prepare(max(max(s) for s in sizes), passes)
+        for i in range(passes):
+            g.add(i, lists[rank][i])
+        total = g.finish()
+        ok &= total == sum(len(lists[r][i]) for r in range(world) for i in range(passes))
+        for i in range(passes):
+            want = np.concatenate([lists[r][i] for r in range(world)])
+            ok &= bool(np.array_equal(g.merged(HIT_DTYPE, i), want))
+        dist.barrier()
+    q.put((rank, bool(ok), g.gathers))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_shared_memory_gather():
+    """bench.py's final gather of the ranks of one host (HitGatherShm): every rank ends up with every rank's lists."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31500 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=_shm_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = sorted(q.get(timeout=180) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert got == [(0, True, 4), (1, True, 4)]     # prepare's warm-up gather + three
