@@ -394,6 +394,18 @@ def allmax(torch, dev, world, *vals):
     return out if len(out) > 1 else out[0]
 
 
+def per_rank(torch, dev, world, **vals):
+    """{name: [value of rank 0, rank 1, ...]} -- the spread behind a max-over-ranks figure (N > 1 only)"""
+    if world == 1:
+        return None
+    import torch.distributed as dist
+    names = sorted(vals)
+    t = torch.tensor([float(vals[k] if vals[k] is not None else -1.0) for k in names], device=dev, dtype=torch.float64)
+    out = [torch.zeros_like(t) for _ in range(world)]
+    dist.all_gather(out, t)
+    return {k: [round(float(o[i]), 4) for o in out] for i, k in enumerate(names)}
+
+
 def host_barrier(world, group):
     """ranks that only wait use a gloo (CPU) barrier: an NCCL barrier would park a spinning kernel on their GPUs
     while rank 0 drives all of them through the single-process multi-GPU driver."""
@@ -461,6 +473,7 @@ def run_ours(args):
         clk.__enter__()
         total_ms, kern_ms, n_hits, launches = time_search(sp, torch, ctx, stream, js, pattern, hits,
                                                           args.steps, args.warmup, gather=gather)
+        spread = per_rank(torch, dev, world, total_ms=total_ms, kernel_ms=kern_ms, final_gather_ms=getattr(time_search, "gather_ms", None))
         total_ms = allmax(torch, dev, world, total_ms)
         value = world * n_der * args.steps / (total_ms * 1e-3) / 1e9
         achieved = n_der * BYTES_PER_BP / (kern_ms * 1e-3) / 1e9
@@ -479,6 +492,7 @@ def run_ours(args):
                        "hit_lists_gathered": gather_note(gather),
                        "merged_hits_per_pass_rank0": getattr(time_search, "merged_hits", None),
                        "final_gather_ms_this_rank": getattr(time_search, "gather_ms", None),
+                       "per_rank_ms": spread,
                        "step": "kernel launch + hit count/list D2H + host sort; passes i+1 and i+2 are queued before pass i's "
                                "hits are collected (spmb_search_launch / spmb_search_finish on three hit lists)"
                                + ("; the hit lists of all passes are gathered to every rank inside the timed region" if gather else "")},
@@ -896,6 +910,8 @@ def bench_c5(sp, synth, torch, ctx, dev, stream, hits, args, rank, world):
         dist.barrier()
     total_ms, kern_ms, n_hits, launches = time_search(sp, torch, ctx, stream, store, pset, hits, args.steps, args.warmup,
                                                       gather=gather)
+    spread = per_rank(torch, dev, world, total_ms=total_ms, kernels_ms=kern_ms, final_gather_ms=getattr(time_search, "gather_ms", None),
+                      hits_per_pass=float(n_hits))
     total_ms = allmax(torch, dev, world, total_ms)
     if world > 1:
         c = torch.tensor([n_hits], device=dev, dtype=torch.int64)
@@ -919,6 +935,7 @@ def bench_c5(sp, synth, torch, ctx, dev, stream, hits, args, rank, world):
            "hit_lists_gathered": gather_note(gather),
            "merged_hits_per_pass_rank0": getattr(time_search, "merged_hits", None),
            "final_gather_ms_this_rank": getattr(time_search, "gather_ms", None),
+           "per_rank_ms": spread,
            "equals_direct_myers_kernel_16_patterns_this_shard": same,
            "text_gbytes_per_s_kernels": n / world * 0.25 / (kern_ms * 1e-3) / 1e9}
     if rank == 0 and world == 1 and not args.no_cpu:

@@ -5,13 +5,14 @@
 // needles one after the other, each over ascending positions).  Lists below SPMB_ORDER_AT_LAUNCH_MIN records are
 // ordered here, on the thread that called spmb_search_finish -- which makes this loop the host's share of a pass:
 // measured on the C5 shards (13.6 k hits per pass at N = 2, 3.4 k at N = 8) the first form (LSD radix sort over
-// separate key / index arrays, fresh vectors per call) took 0.53 ms / 0.16 ms per list, as long as the kernels of
-// the pass (0.55 / 0.18 ms), and 0.12 ms of that was page faults of the fresh output vector.  This form:
-//   * (key, record index) packed into ONE 64-bit word, so a pass moves 8 bytes per record;
-//   * many needles (the seed-filter sets): ONE counting pass over the needle id, then the few records of a needle
-//     are put in order by insertion sort -- two sweeps instead of six radix passes;
-//   * few needles: LSD radix sort over the key bits only, all histograms from one sweep, constant digits skipped;
-//   * every buffer lives in a HitOrderScratch that the hit list keeps between calls.
+// separate key / index arrays, six passes, fresh vectors per call) took 0.53 ms / 0.16 ms per list, as long as the
+// kernels of the pass (0.55 / 0.18 ms), and 0.12 ms of that was page faults of the fresh output vector.  This form:
+//   * (key, record index) packed into ONE 64-bit word;
+//   * one scatter into ~n/2 buckets by the key's position inside [smallest key, largest key] (order-preserving), then
+//     an insertion sort inside each bucket (a handful of records; std::sort when a bucket is crowded, so a clustered
+//     list degrades to n log n, never worse) -- two sweeps over the words whatever the key width;
+//   * every buffer lives in a HitOrderScratch that is kept between calls.
+// Same host, same lists: 3.4 k hits 76 -> 35 us, 13.6 k hits 370 -> 210 us (tools/ lists of C5; g++ -O3, one thread).
 #pragma once
 #include <algorithm>
 #include <cstdint>
@@ -33,8 +34,8 @@ static inline int hit_order_bits(unsigned long long max_value)
 }
 
 // Orders `v` by (pattern_id, seq_id, end[, errors]); with `unique_keys` only the first record (smallest error count)
-// of every (pattern_id, seq_id, end) is kept.  false = the packed key does not fit 64 bits (the caller falls back to
-// a comparison sort).
+// of every (pattern_id, seq_id, end) is kept.  Records with equal keys keep their order of arrival.  false = the
+// packed key does not fit 64 bits (the caller falls back to a comparison sort).
 static inline bool hits_order_packed(std::vector<spmb_hit> &v, bool with_errors, bool unique_keys, HitOrderScratch &sc)
 {
     const size_t n = v.size();
@@ -48,88 +49,43 @@ static inline bool hits_order_packed(std::vector<spmb_hit> &v, bool with_errors,
     const int b_err = with_errors ? hit_order_bits(max_err) : 0, b_end = hit_order_bits(max_end);
     const int b_seq = max_seq ? hit_order_bits(max_seq) : 0, b_pat = max_pat ? hit_order_bits(max_pat) : 0;
     const int b_idx = hit_order_bits(n);
-    const int b_rest = b_seq + b_end + b_err;        // the key below the needle id
-    if (b_pat + b_rest + b_idx > 64) return false;
+    const int total = b_pat + b_seq + b_end + b_err;
+    if (total + b_idx > 64) return false;
     if (sc.a.size() < n) { sc.a.resize(n); sc.b.resize(n); }
     uint64_t *src = sc.a.data(), *dst = sc.b.data();
-    const size_t P = (size_t)max_pat + 1;
-    if (P >= 64 && n >= P / 4 && n <= 16 * P) {
-        // ---- many needles: counting sort over the needle id, insertion sort inside a needle ----
-        if (sc.hist.size() < P + 1) sc.hist.resize(P + 1);
-        uint32_t *cnt = sc.hist.data();
-        std::fill(cnt, cnt + P + 1, 0u);
-        for (size_t i = 0; i < n; ++i) ++cnt[v[i].pattern_id + 1];
-        for (size_t p = 0; p < P; ++p) cnt[p + 1] += cnt[p];
-        // cnt[p] = first slot of needle p; the scatter advances it to the first slot of needle p + 1
-        for (size_t i = 0; i < n; ++i) {
-            const spmb_hit &h = v[i];
-            uint64_t k = b_seq ? h.seq_id : 0;
-            k = (k << b_end) | h.end;
-            if (with_errors) k = (k << b_err) | h.errors;
-            dst[cnt[h.pattern_id]++] = (k << b_idx) | i;
-        }
-        size_t lo = 0;
-        for (size_t p = 0; p < P; ++p) {
-            const size_t hi = cnt[p];
-            if (hi - lo > 24) std::sort(dst + lo, dst + hi);
-            else
-                for (size_t i = lo + 1; i < hi; ++i) {
-                    const uint64_t x = dst[i];
-                    size_t j = i;
-                    while (j > lo && dst[j - 1] > x) { dst[j] = dst[j - 1]; --j; }
-                    dst[j] = x;
-                }
-            lo = hi;
-        }
-        std::swap(src, dst);
-        // src = ordered (rest key | index); the needle id comes from the record itself below
-        if (sc.out.size() < n) sc.out.resize(n);
-        spmb_hit *out = sc.out.data();
-        const uint64_t im = ((uint64_t)1 << b_idx) - 1;
-        size_t o = 0;
-        if (unique_keys) {
-            uint64_t last_k = ~0ull;
-            uint32_t last_p = 0xffffffffu;
-            for (size_t i = 0; i < n; ++i) {
-                const spmb_hit &h = v[src[i] & im];
-                const uint64_t kk = src[i] >> (b_idx + b_err);
-                if (kk != last_k || h.pattern_id != last_p) { out[o++] = h; last_k = kk; last_p = h.pattern_id; }
-            }
-        } else {
-            for (size_t i = 0; i < n; ++i) out[o++] = v[src[i] & im];
-        }
-        v.swap(sc.out);
-        v.resize(o);
-        return true;
-    }
-    // ---- few needles: LSD radix sort over (pattern | sequence | end | errors), the index rides in the low bits ----
-    const int total = b_pat + b_rest;
+    uint64_t kmin = ~0ull, kmax = 0;
     for (size_t i = 0; i < n; ++i) {
         const spmb_hit &h = v[i];
         uint64_t k = h.pattern_id;
         k = b_seq ? (k << b_seq) | h.seq_id : k;
         k = (k << b_end) | h.end;
         if (with_errors) k = (k << b_err) | h.errors;
+        kmin = std::min(kmin, k); kmax = std::max(kmax, k);
         src[i] = (k << b_idx) | i;
     }
-    const int W = 8;
-    const int passes = (total + W - 1) / W;
-    const size_t R = (size_t)1 << W;
-    if (sc.hist.size() < (size_t)passes * R) sc.hist.resize((size_t)passes * R);
-    std::fill(sc.hist.begin(), sc.hist.begin() + (size_t)passes * R, 0u);
-    for (size_t i = 0; i < n; ++i) {
-        const uint64_t k = src[i] >> b_idx;
-        for (int p = 0; p < passes; ++p) ++sc.hist[(size_t)p * R + ((k >> (p * W)) & (R - 1))];
-    }
-    for (int p = 0; p < passes; ++p) {
-        uint32_t *hp = sc.hist.data() + (size_t)p * R;
-        uint32_t sum = 0;
-        bool constant = false;
-        for (size_t d = 0; d < R; ++d) { const uint32_t c = hp[d]; constant |= (c == n); hp[d] = sum; sum += c; }
-        if (constant) continue;
-        const int sh = b_idx + p * W;
-        for (size_t i = 0; i < n; ++i) { const uint64_t x = src[i]; dst[hp[(x >> sh) & (R - 1)]++] = x; }
-        std::swap(src, dst);
+    int lb = 8;
+    while (((size_t)1 << lb) < n / 2 && lb < 16) ++lb;
+    const size_t B = (size_t)1 << lb;
+    const int span_bits = hit_order_bits(kmax - kmin);
+    const int sh = span_bits > lb ? span_bits - lb : 0;
+    if (sc.hist.size() < B + 1) sc.hist.resize(B + 1);
+    uint32_t *cnt = sc.hist.data();
+    std::fill(cnt, cnt + B + 1, 0u);
+    for (size_t i = 0; i < n; ++i) ++cnt[(((src[i] >> b_idx) - kmin) >> sh) + 1];
+    for (size_t b = 0; b < B; ++b) cnt[b + 1] += cnt[b];
+    for (size_t i = 0; i < n; ++i) { const uint64_t x = src[i]; dst[cnt[((x >> b_idx) - kmin) >> sh]++] = x; }
+    size_t lo = 0;
+    for (size_t b = 0; b < B; ++b) {
+        const size_t hi = cnt[b];
+        if (hi - lo > 24) std::sort(dst + lo, dst + hi);
+        else
+            for (size_t i = lo + 1; i < hi; ++i) {
+                const uint64_t x = dst[i];
+                size_t j = i;
+                while (j > lo && dst[j - 1] > x) { dst[j] = dst[j - 1]; --j; }
+                dst[j] = x;
+            }
+        lo = hi;
     }
     if (sc.out.size() < n) sc.out.resize(n);
     spmb_hit *out = sc.out.data();
@@ -138,11 +94,11 @@ static inline bool hits_order_packed(std::vector<spmb_hit> &v, bool with_errors,
     if (unique_keys) {
         uint64_t last = ~0ull;
         for (size_t i = 0; i < n; ++i) {
-            const uint64_t kk = src[i] >> (b_idx + b_err);
-            if (kk != last) { out[o++] = v[src[i] & im]; last = kk; }
+            const uint64_t kk = dst[i] >> (b_idx + b_err);
+            if (kk != last) { out[o++] = v[dst[i] & im]; last = kk; }
         }
     } else {
-        for (size_t i = 0; i < n; ++i) out[o++] = v[src[i] & im];
+        for (size_t i = 0; i < n; ++i) out[o++] = v[dst[i] & im];
     }
     v.swap(sc.out);
     v.resize(o);

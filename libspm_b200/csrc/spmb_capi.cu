@@ -66,7 +66,7 @@ struct spmb_context {
     size_t blocks_bytes = 0, blocks_cap = 0;
 };
 
-enum { SPEC_HITS = 1024 };
+enum { SPEC_HITS = 4096 };
 // raw hits from which the next launch on the same hit list orders them itself (enqueue_order): the ~13 small kernels
 // cost ~0.12 ms of stream time, which only pays once the list is long (measured on C5 shards: 10 k raw hits per rank
 // at N=8 0.32 ms per step ordered from finish, 0.38 ms ordered by the launch; 80 k at N=1 1.73 against 1.27 ms)
