@@ -185,6 +185,9 @@ class HitGather:
         self.gathers += 1
         return int(counts.sum())
 
+    def barrier(self):
+        self.dist.barrier()
+
     def merged(self, hit_dtype, i=0):
         """the merged list of pass i (rank-major), for checks outside the timed region"""
         raw = self.pin_out.numpy()
@@ -278,6 +281,12 @@ class HitGatherShm:
         self.gathers += 1
         return int(self.counts[base:base + self.world].sum())
 
+    def barrier(self):
+        """the ranks leave within microseconds of each other (a flag exchange, no lists)"""
+        self.counts[self._row(self.gen + 1, self.rank), :] = 0
+        self.finish()
+        self.gathers -= 1
+
     def merged(self, hit_dtype, i=0):
         """the merged list of pass i of the last gather (rank-major), for checks outside the timed region"""
         base = (self.gen & 1) * self.world
@@ -326,6 +335,8 @@ def time_search(sp, torch, ctx, stream, store, pattern, hits, steps, warmup, flu
     ke = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
+    if gather is not None:
+        gather.barrier()        # the ranks enter the timed region together (the warm-up above leaves them skewed)
     flush_ms = 0.0
     e0.record(stream)
     n_hits = 0
