@@ -31,3 +31,14 @@ def test_reference_matcher_tests_pass_on_gpu():
     print(r.stdout[-3000:])
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-1000:]
     assert "0 failures" in r.stdout
+
+
+def test_host_hit_ordering_equals_std_sort():
+    """libspm_b200/csrc/hit_order.hpp (the host's share of a search pass) against std::stable_sort + std::unique: pure C++."""
+    gxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+    exe = os.path.join(ROOT, "tests", "cpp", "hit_order_test.bin")
+    subprocess.check_call([gxx, "-std=c++17", "-O2", "-Wall", "-Wextra", "-Werror", os.path.join(ROOT, "tests", "cpp", "hit_order_test.cpp"),
+                           "-o", exe])
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-1000:]
+    assert " 0 failures" in r.stdout

@@ -1,0 +1,14 @@
+#!/bin/bash
+set -u
+mkdir -p gpurun_out
+timeout 240 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29513 bench.py --gpus 2 --steps 20 --warmup 5 --no-cpu --no-myers --no-small --no-multi --no-stream --no-pageable --e2e-steps 1 > gpurun_out/bench_n2_quick.json 2> gpurun_out/bench_n2_quick.err
+echo "rc=$?"; tail -c 400 gpurun_out/bench_n2_quick.err
+python - <<PY
+import json
+d=json.loads(open('gpurun_out/bench_n2_quick.json').read().strip().splitlines()[-1])
+print(' headline Gbp/s', round(d['value'],1), 'ms/step', round(d['ms_per_step'],4), 'kernel', round(d['roofline']['kernel_ms'],4), json.dumps(d['detail'].get('per_rank_ms')))
+c=d.get('c5') or {}
+print(' c5 ms/step', c.get('ms_per_step'), 'kernels', c.get('kernels_ms'), json.dumps(c.get('per_rank_ms')))
+c=d.get('c4') or {}
+print(' c4 ms/step', c.get('ms_per_step'), 'kernels', c.get('kernels_ms'), c.get('parity'))
+PY
