@@ -315,7 +315,8 @@ def make_gather(torch, dist, dev, world, rank):
     return HitGather(torch, dist, dev, world)
 
 
-def time_search(sp, torch, ctx, stream, store, pattern, hits, steps, warmup, flush=None, gather=None):
+def time_search(sp, torch, ctx, stream, store, pattern, hits, steps, warmup, flush=None, gather=None, launch_fn=None,
+                finish_fn=None):
     """returns (total_ms for `steps` launch+finish passes (+ the final gather), mean kernel ms, n_hits, launches/step).
     The passes are pipelined the way the launch/finish pair of the C ABI is meant to be used: passes i+1 and
     i+2 are queued (on their own hit lists) before pass i's hits are collected, so the host's share of a pass
@@ -323,12 +324,15 @@ def time_search(sp, torch, ctx, stream, store, pattern, hits, steps, warmup, flu
     sorted hit list to the host; with `gather` (N > 1) the lists of all passes travel to every rank in one final
     all_gather before the closing event (HitGather)."""
     DEPTH = int(os.environ.get("SPMB_BENCH_DEPTH", "3"))   # passes in flight: two queued behind the one being collected
+    if launch_fn is None:       # a plain store; the JST leg passes spmb_jst_search_launch / _finish
+        launch_fn = lambda h_: sp.search_launch(ctx, store, pattern, h_)
+        finish_fn = lambda h_: sp.search_finish(ctx, h_, copy=False)   # the library's host list itself (spmb_hits_data)
     hl = (hits,) + tuple(sp.Hits(ctx, 1 << 16) for _ in range(DEPTH - 1))
     for w in range(max(warmup, 2 * DEPTH)):     # every hit list twice: buffers sized, long-list ordering armed
         if flush is not None:
             flush.add_(1)
-        sp.search_launch(ctx, store, pattern, hl[w % DEPTH])
-        h = sp.search_finish(ctx, hl[w % DEPTH])
+        launch_fn(hl[w % DEPTH])
+        h = finish_fn(hl[w % DEPTH])
         if gather is not None and w == 0:
             gather.prepare(len(h), steps)     # warm: capacity agreed, buffers, communicator
     ks = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
@@ -350,7 +354,7 @@ def time_search(sp, torch, ctx, stream, store, pattern, hits, steps, warmup, flu
             flush.add_(1)       # evict L2 between iterations (buffer > L2)
         ks[i].record(stream)
         t_a = time.perf_counter()
-        sp.search_launch(ctx, store, pattern, hl[i % DEPTH])
+        launch_fn(hl[i % DEPTH])
         if trace is not None:
             trace.append(("launch", i, (t_a - t_origin) * 1e3, (time.perf_counter() - t_origin) * 1e3))
         ke[i].record(stream)
@@ -361,7 +365,7 @@ def time_search(sp, torch, ctx, stream, store, pattern, hits, steps, warmup, flu
         if i + DEPTH - 1 < steps:
             launch(i + DEPTH - 1)
         t_a = time.perf_counter()
-        h = sp.search_finish(ctx, hl[i % DEPTH], copy=False)   # the library's host list itself (spmb_hits_data)
+        h = finish_fn(hl[i % DEPTH])
         n_hits = len(h)
         t_b = time.perf_counter()
         if gather is not None:
@@ -819,16 +823,30 @@ def bench_c4(sp, synth, torch, ctx, dev, stream, hits, args, rank, world):
         import torch.distributed as dist
         dist.barrier()
     steps = args.steps
+    # one synchronous call at a time (the reference's call shape): latency of a search, its kernels and its host half
     kms, ems = [], []
     torch.cuda.synchronize()
     t0 = time.perf_counter()
-    for _ in range(steps):
+    for _ in range(min(steps, 5)):
         got = jst.search(p, hits)
         st = jst.last_stats()
         kms.append(st["kernels_ms"]); ems.append(st["expand_ms"])
     torch.cuda.synchronize()
-    warm_ms = (time.perf_counter() - t0) * 1e3 / steps
-    warm_ms, kern_ms = allmax(torch, dev, world, warm_ms, float(np.mean(kms)))
+    sync_ms = (time.perf_counter() - t0) * 1e3 / min(steps, 5)
+    sync_kern_ms = float(np.mean(kms))
+    # the timed step: searches back to back through spmb_jst_search_launch / _finish on three hit lists, so the host
+    # half of a search (D2H, expansion to haplotypes, ordering) runs under the kernels of the next one
+    gather = make_gather(torch, dist, dev, world, rank) if world > 1 else None
+    total_ms, kern_ms, n_got, _ = time_search(sp, torch, ctx, stream, None, None, hits, steps, args.warmup, gather=gather,
+                                               launch_fn=lambda h_: jst.search_launch(p, h_),
+                                               finish_fn=lambda h_: jst.search_finish(h_, copy=False))
+    c4_gather_ms = getattr(time_search, "gather_ms", None)
+    jst.search_launch(p, hits)
+    piped = jst.search_finish(hits)
+    piped_same = bool(len(piped) == len(got) and np.array_equal(piped, got))
+    warm_ms = total_ms / steps
+    spread = per_rank(torch, dev, world, total_ms=total_ms, kernels_ms=kern_ms, final_gather_ms=c4_gather_ms)
+    warm_ms, kern_ms, sync_ms = allmax(torch, dev, world, warm_ms, kern_ms, sync_ms)
     # the full recurrence on this shard (the kernel SURVEY 8(d)'s 54 instr/bp is stated on)
     ctx.set_myers_cutoff(False)
     jst.search(p, hits)
@@ -848,12 +866,18 @@ def bench_c4(sp, synth, torch, ctx, dev, stream, hits, args, rank, world):
            "value": effective / (warm_ms * 1e-3) / 1e9, "unit": "effective Gbp/s (sum of haplotype lengths per warm search)",
            "ms_per_step": warm_ms, "scaling": "strong", "steps": steps,
            "kernels_ms": kern_ms, "expand_ms": float(np.mean(ems)),
+           "step": "spmb_jst_search_launch / spmb_jst_search_finish on three hit lists in rotation: every search delivers its "
+                   "expanded, ordered hit list to the host; the host half of search i runs under the kernels of search i+1"
+                   + ("; the hit lists of all searches are gathered to every rank inside the timed region" if gather else ""),
+           "synchronous_call_ms": sync_ms, "synchronous_call_kernels_ms": sync_kern_ms,
+           "pipelined_hits_equal_synchronous": piped_same,
+           "hit_lists_gathered": gather_note(gather), "final_gather_ms_this_rank": c4_gather_ms, "per_rank_ms": spread,
            "streamed_bp": int(streamed), "effective_bp": effective,
            "streamed_gbp_per_s_kernels": streamed / (kern_ms * 1e-3) / 1e9,
            "one_off": {"jst_create_s": create_s, "flatten_ms": st_first["flatten_ms"], "materialise_ms": st_first["materialise_ms"],
                        "windows": int(st_first["windows"]), "window_symbols": int(st_first["window_symbols"]),
                        "buckets": int(st_first["buckets"])},
-           "hits": int(len(whole)), "hits_this_shard": int(len(got)), "raw_device_hits": int(st_first["raw_hits"]),
+           "hits": int(len(whole)), "hits_this_shard": int(n_got), "raw_device_hits": int(st_first["raw_hits"]),
            "full_recurrence": {"kernels_ms": full_kern_ms, "int32_instr_per_bp": ops,
                                "achieved_ginstr_per_s": streamed / world * ops / (full_kern_ms * 1e-3) / 1e9,
                                "frac_of_alu_peak": streamed / world * ops / (full_kern_ms * 1e-3) / 1e9 / peak["lop3_gops"],

@@ -324,6 +324,15 @@ int spmb_jst_create(spmb_context *ctx, const spmb_store *reference, const spmb_j
                     const uint64_t *coverage, uint32_t n_haplotypes, spmb_jst **out);
 int spmb_jst_destroy(spmb_jst *j);
 int spmb_jst_search(spmb_context *ctx, spmb_jst *j, const spmb_pattern *p, spmb_hits *h);
+/* the same search in two halves, like spmb_search_launch / spmb_search_finish (a traverser that runs one matcher
+ * call per context, concept.hpp:27-50, back to back): launch enqueues the kernels and returns, finish waits, brings
+ * the device hits back and expands them to haplotypes on the host.  With two or three spmb_hits in rotation the
+ * host half of a search runs under the kernels of the next one.  Searches in flight on one tree share the window
+ * size (a launch with another one is refused with SPMB_ERR_ARG until the pending ones are finished: it would rebuild
+ * the window stores they read); spmb_jst_destroy and the one-call spmb_jst_search want no search in flight.
+ * spmb_jst_last_stats reports no kernel time for a split search. */
+int spmb_jst_search_launch(spmb_context *ctx, spmb_jst *j, const spmb_pattern *p, spmb_hits *h);
+int spmb_jst_search_finish(spmb_context *ctx, spmb_hits *h);
 /* figures of the last search: stats[0] windows, [1] window symbols, [2] length buckets,
  * [3] raw device hits before expansion; ms[0] host flattening (0 when cached), [1] window
  * materialisation, [2] search kernels (reference + windows), [3] host expansion + sort */

@@ -54,7 +54,7 @@ EXPORTS = [
     "spmb_multi_store_create", "spmb_multi_store_create_journaled", "spmb_multi_store_destroy", "spmb_multi_store_length",
     "spmb_multi_store_shards", "spmb_multi_pattern_create", "spmb_multi_pattern_destroy", "spmb_multi_search",
     "spmb_multi_search_host", "spmb_multi_last_stats",
-    "spmb_search_filtered_noalloc",
+    "spmb_search_filtered_noalloc", "spmb_jst_search_launch", "spmb_jst_search_finish",
 ]
 
 
@@ -176,6 +176,8 @@ def lib():
             "spmb_jst_create": (i32, [vp, vp, vp, u64, vp, u64, vp, u32, pp]),
             "spmb_jst_destroy": (i32, [vp]),
             "spmb_jst_search": (i32, [vp, vp, vp, vp]),
+            "spmb_jst_search_launch": (i32, [vp, vp, vp, vp]),
+            "spmb_jst_search_finish": (i32, [vp, vp]),
             "spmb_jst_last_stats": (i32, [vp, C.POINTER(u64 * 4), C.POINTER(C.c_double * 4)]),
         }
         for name, (res, args) in sig.items():
@@ -612,6 +614,14 @@ class Jst:
         if own:
             hits.close()
         return out
+
+    def search_launch(self, pattern: Pattern, hits: Hits):
+        """spmb_jst_search_launch: enqueue the kernels of a search and return (finish it with search_finish)."""
+        self.ctx._check(lib().spmb_jst_search_launch(self.ctx._h, self._h, pattern._h, hits._h), "spmb_jst_search_launch")
+
+    def search_finish(self, hits: Hits, copy: bool = True) -> np.ndarray:
+        self.ctx._check(lib().spmb_jst_search_finish(self.ctx._h, hits._h), "spmb_jst_search_finish")
+        return hits.array(copy)
 
     def last_stats(self):
         st, ms = (C.c_uint64 * 4)(), (C.c_double * 4)()

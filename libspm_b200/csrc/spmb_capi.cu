@@ -173,6 +173,7 @@ struct spmb_hits {
     uint64_t count = 0;
     const spmb_store *pend_store = nullptr;
     const spmb_pattern *pend_pat = nullptr;
+    struct spmb_jst *pend_jst = nullptr;   // spmb_jst_search_launch
     cudaStream_t collect_stream = nullptr; // the stream hits_collect last read this list on (copy stream or the context's)
     bool spec_done = false;                // hits_collect already brought the (short) raw list to `host`
     cudaEvent_t done = nullptr;            // recorded behind the kernels of spmb_search_launch
@@ -2292,6 +2293,7 @@ struct spmb_jst {
     std::vector<JstBucket> buckets;
     uint64_t stats[4] = {0, 0, 0, 0};
     double ms[4] = {0, 0, 0, 0};
+    uint32_t in_flight = 0;            // spmb_jst_search_launch calls whose finish is still due
 };
 
 static const uint32_t JST_REF_SEQ = 0xffffffffu;
@@ -2534,41 +2536,12 @@ static int jst_enqueue(spmb_context *ctx, spmb_jst *j, const spmb_pattern *p, sp
     return rc;
 }
 
-extern "C" int spmb_jst_search(spmb_context *ctx, spmb_jst *j, const spmb_pattern *p, spmb_hits *h)
+// host half of a JST search: every device hit expanded to the haplotypes it stands for, ordered
+static void jst_expand(spmb_jst *j, const spmb_pattern *p, spmb_hits *h, std::vector<spmb_hit> &raw, uint32_t W)
 {
-    if (!ctx || !j || !p || !h) return SPMB_ERR_ARG;
-    ENTER(ctx);
-    ctx->launches = 0;
-    h->count = 0;
-    h->host.clear();
-    const uint32_t W = spmb_pattern_window_size(p);
-    j->stats[3] = 0; j->ms[2] = j->ms[3] = 0;
-    if (W == 0) return SPMB_OK;
-    int rc = jst_prepare(ctx, j, W);
-    if (rc) return rc;
-
-    cudaEvent_t e0, e1;
-    CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
-    std::vector<spmb_hit> raw;
-    auto run = [&]() -> int {
-        CU(cudaEventRecord(e0, ctx->stream));
-        int r = jst_enqueue(ctx, j, p, h);
-        if (r) return r;
-        CU(cudaEventRecord(e1, ctx->stream));
-        return SPMB_OK;
-    };
-    rc = run();
-    if (rc == SPMB_OK) rc = hits_collect(ctx, h, raw, run);
-    if (rc) { cudaEventDestroy(e0); cudaEventDestroy(e1); return rc; }
-    if (p->alg == SPMB_ALG_MYERS_FILTERED) hits_order(raw, p->alg); // one record per (window, end)
-    float t = 0;
-    cudaEventElapsedTime(&t, e0, e1);
-    cudaEventDestroy(e0); cudaEventDestroy(e1);
-    j->ms[2] = t;
-    j->stats[3] = raw.size();
-
-    // ---- host: expand every device hit to the haplotypes it stands for ----
     const auto t0 = std::chrono::steady_clock::now();
+    if (p->alg == SPMB_ALG_MYERS_FILTERED) hits_order(raw, p->alg); // one record per (window, end)
+    j->stats[3] = raw.size();
     const JstHost &H = j->H;
     std::sort(raw.begin(), raw.end(), [](const spmb_hit &a, const spmb_hit &b) {
         if (a.seq_id != b.seq_id) return a.seq_id < b.seq_id;
@@ -2578,6 +2551,7 @@ extern "C" int spmb_jst_search(spmb_context *ctx, spmb_jst *j, const spmb_patter
     std::vector<uint64_t> cov;
     std::vector<int64_t> shift;
     std::vector<spmb_hit> &out = h->host;
+    out.clear();
     size_t i = 0;
     while (i < raw.size()) {
         size_t e = i;
@@ -2616,8 +2590,94 @@ extern "C" int spmb_jst_search(spmb_context *ctx, spmb_jst *j, const spmb_patter
     }
     hits_order(out, p->alg);
     h->count = out.size();
-    h->pend_store = nullptr; h->pend_pat = nullptr;
+    h->view = nullptr;
+    h->pend_store = nullptr; h->pend_pat = nullptr; h->pend_jst = nullptr;
     j->ms[3] = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+}
+
+extern "C" int spmb_jst_search(spmb_context *ctx, spmb_jst *j, const spmb_pattern *p, spmb_hits *h)
+{
+    if (!ctx || !j || !p || !h) return SPMB_ERR_ARG;
+    ENTER(ctx);
+    ctx->launches = 0;
+    h->count = 0;
+    h->host.clear();
+    h->view = nullptr;
+    const uint32_t W = spmb_pattern_window_size(p);
+    j->stats[3] = 0; j->ms[2] = j->ms[3] = 0;
+    if (W == 0) return SPMB_OK;
+    int rc = jst_prepare(ctx, j, W);
+    if (rc) return rc;
+
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
+    std::vector<spmb_hit> raw;
+    auto run = [&]() -> int {
+        CU(cudaEventRecord(e0, ctx->stream));
+        int r = jst_enqueue(ctx, j, p, h);
+        if (r) return r;
+        CU(cudaEventRecord(e1, ctx->stream));
+        return SPMB_OK;
+    };
+    rc = run();
+    if (rc == SPMB_OK) rc = hits_collect(ctx, h, raw, run);
+    if (rc) { cudaEventDestroy(e0); cudaEventDestroy(e1); return rc; }
+    float t = 0;
+    cudaEventElapsedTime(&t, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    j->ms[2] = t;
+    jst_expand(j, p, h, raw, W);
+    return SPMB_OK;
+}
+
+// The same search in two halves, like spmb_search_launch / spmb_search_finish: launch enqueues the kernels of the
+// reference scan and of every window bucket and returns; finish waits for them, brings the device hits back and
+// expands them on the host.  With two or three hit lists in rotation the host half of a search (D2H, expansion,
+// ordering: 0.25 of the 1.09 ms of a C4 search) runs under the kernels of the next one.
+extern "C" int spmb_jst_search_launch(spmb_context *ctx, spmb_jst *j, const spmb_pattern *p, spmb_hits *h)
+{
+    if (!ctx || !j || !p || !h) return SPMB_ERR_ARG;
+    ENTER(ctx);
+    ctx->launches = 0;
+    h->view = nullptr;
+    h->ordered = false;
+    h->pend_store = nullptr;
+    h->pend_pat = p;
+    h->pend_jst = j;
+    h->done_armed = false;
+    const uint32_t W = spmb_pattern_window_size(p);
+    if (W == 0) { j->in_flight++; return SPMB_OK; }
+    // another window size rebuilds the window stores the pending searches still read
+    if (j->in_flight && !(j->have_flat && j->flat.W == W)) {
+        h->pend_jst = nullptr; h->pend_pat = nullptr;
+        return set_err(ctx, SPMB_ERR_ARG, "spmb_jst_search_launch: searches in flight on this tree use another window size "
+                                          "(finish them first)");
+    }
+    int rc = jst_prepare(ctx, j, W);
+    if (rc == SPMB_OK) rc = jst_enqueue(ctx, j, p, h);
+    if (rc) { h->pend_jst = nullptr; h->pend_pat = nullptr; return rc; }
+    j->in_flight++;
+    h->done_armed = h->done && ctx->copy_stream && cudaEventRecord(h->done, ctx->stream) == cudaSuccess;
+    return SPMB_OK;
+}
+
+extern "C" int spmb_jst_search_finish(spmb_context *ctx, spmb_hits *h)
+{
+    if (!ctx || !h || !h->pend_jst || !h->pend_pat) return SPMB_ERR_ARG;
+    ENTER(ctx);
+    spmb_jst *j = h->pend_jst;
+    const spmb_pattern *p = h->pend_pat;
+    h->count = 0;
+    h->host.clear();
+    const uint32_t W = spmb_pattern_window_size(p);
+    j->stats[3] = 0; j->ms[2] = j->ms[3] = 0; // the kernels of a split search are not timed here (the caller brackets the launch)
+    if (j->in_flight) j->in_flight--;
+    h->pend_jst = nullptr; h->pend_pat = nullptr;
+    if (W == 0) return SPMB_OK;
+    std::vector<spmb_hit> raw;
+    int rc = hits_collect(ctx, h, raw, [&]() { return jst_enqueue(ctx, j, p, h); });
+    if (rc) return rc;
+    jst_expand(j, p, h, raw, W);
     return SPMB_OK;
 }
 

@@ -195,3 +195,67 @@ def test_jst_create_rejects_overlapping_variants_of_one_haplotype(ctx):
     var2["ins_off"] = [1, 0]
     sp.Jst(ctx, store, var2, pool, both, 1).close()
     store.close()
+
+
+def test_jst_launch_finish_in_rotation_equals_the_one_call_search(ctx):
+    """spmb_jst_search_launch / _finish: three searches queued on three hit lists before the first is collected, with
+    different needles and algorithms (window sizes: the flattened tree is rebuilt between them), sharded and not;
+    every list equals the one spmb_jst_search returns and the oracle's."""
+    n_ref, n_hap, n_var, seed = 30_000, 70, 900, 31
+    ref, var, pool, cov = make_jst(n_ref, n_var, n_hap, seed, p_snp=0.6, p_ins=0.2, max_indel=8, af_max=0.7)
+    ev = var.astype(orc.EVENT_DTYPE)
+    rng = np.random.default_rng(seed)
+    store = sp.Store.from_host(ctx, ref)
+    jst = sp.Jst(ctx, store, var, pool, cov, n_hap)
+    pats = []
+    for alg, m, k, src in [(sp.ALG_MYERS, 40, 3, 0), (sp.ALG_MYERS, 40, 3, n_hap - 1), (sp.ALG_SHIFTOR, 14, 0, 5),
+                           (sp.ALG_MYERS, 70, 4, 9), (sp.ALG_MYERS, 40, 3, 20)]:
+        seq = orc.jst_haplotype(ref, ev, pool, cov, src)
+        s = int(rng.integers(0, len(seq) - m))
+        pat = seq[s:s + m].copy()
+        if alg == sp.ALG_MYERS:
+            pat[m // 2] = (pat[m // 2] + 1) % 4     # one substitution: the length (and with it the window size) stays
+        pats.append((alg, pat, k, sp.Pattern(ctx, alg, pat, k)))
+    want = [jst.search(p) for (_, _, _, p) in pats]
+    for (alg, pat, k, _), w in zip(pats, want):
+        compare(w, orc.jst_search(alg, ref, ev, pool, cov, n_hap, pat, k), "one-call search")
+        assert len(w) >= 1
+    hl = [sp.Hits(ctx, 1 << 10) for _ in range(3)]
+    # same window size back to back: three in flight
+    same_w = [0, 1, 4, 0, 1, 4, 0]
+    got = [None] * len(same_w)
+    for i in range(2):
+        jst.search_launch(pats[same_w[i]][3], hl[i % 3])
+    for i in range(len(same_w)):
+        if i + 2 < len(same_w):
+            jst.search_launch(pats[same_w[i + 2]][3], hl[(i + 2) % 3])
+        got[i] = jst.search_finish(hl[i % 3])
+    for i, pi in enumerate(same_w):
+        assert np.array_equal(got[i], want[pi]), (i, pi, len(got[i]), len(want[pi]))
+    # another window size while a search is in flight is refused (it would rebuild the window stores in use)
+    jst.search_launch(pats[0][3], hl[0])
+    assert sp.lib().spmb_jst_search_launch(ctx._h, jst._h, pats[3][3]._h, hl[1]._h) == 1
+    assert "window size" in (sp.lib().spmb_last_error(ctx._h) or b"").decode()
+    assert np.array_equal(jst.search_finish(hl[0]), want[0])
+    # window sizes change between searches: one in flight at a time (a launch may rebuild the window stores)
+    for pi in (2, 3, 0, 2):
+        jst.search_launch(pats[pi][3], hl[0])
+        g = jst.search_finish(hl[0])
+        assert np.array_equal(g, want[pi]), (pi, len(g), len(want[pi]))
+    # shards partition the list
+    parts = []
+    for sh in range(3):
+        ctx.set_shard(sh, 3)
+        jst.search_launch(pats[0][3], hl[1])
+        parts.append(jst.search_finish(hl[1]))
+    ctx.set_shard(0, 1)
+    merged = np.concatenate(parts)
+    merged = merged[np.lexsort((merged["end"], merged["seq_id"], merged["pattern_id"]))]
+    assert np.array_equal(merged, want[0])
+    # a finish without a launch is refused
+    assert sp.lib().spmb_jst_search_finish(ctx._h, hl[2]._h) == 1
+    for h in hl:
+        h.close()
+    for (_, _, _, p) in pats:
+        p.close()
+    jst.close(); store.close()

@@ -2,7 +2,12 @@
 set -u
 mkdir -p gpurun_out
 timeout 800 python -m pytest tests -m gpu -q -x -p no:cacheprovider 2>&1 | tail -3
-SPMB_BENCH_TRACE=1 timeout 300 python tools/c5_shard.py --only 2 --steps 10 --out gpurun_out/c5_t2.json > gpurun_out/c5_t2.log 2> gpurun_out/c5_t2.trace
-tail -2 gpurun_out/c5_t2.log | head -1
-SPMB_BENCH_TRACE=1 timeout 300 python tools/c5_shard.py --only 8 --steps 10 --out gpurun_out/c5_t8.json > gpurun_out/c5_t8.log 2> gpurun_out/c5_t8.trace
-tail -2 gpurun_out/c5_t8.log | head -1
+timeout 300 python bench.py --steps 20 --warmup 5 --no-cpu --no-myers --no-small --no-c5 --no-multi --no-stream --no-pageable --e2e-steps 1 > gpurun_out/bench_c4_quick.json 2> gpurun_out/bench_c4_quick.err
+echo "rc=$?"; tail -c 300 gpurun_out/bench_c4_quick.err
+python - <<PY
+import json
+d=json.loads(open('gpurun_out/bench_c4_quick.json').read().strip().splitlines()[-1])
+print(' headline Gbp/s', round(d['value'],1), 'ms/step', round(d['ms_per_step'],4), 'kernel', round(d['roofline']['kernel_ms'],4))
+c=d.get('c4') or {}
+print(' c4 ms/step', c.get('ms_per_step'), 'kernels', c.get('kernels_ms'), 'sync', c.get('synchronous_call_ms'), c.get('synchronous_call_kernels_ms'), 'expand', c.get('expand_ms'), c.get('parity'), c.get('pipelined_hits_equal_synchronous'))
+PY
