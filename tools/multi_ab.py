@@ -19,6 +19,13 @@ if a.threads >= 0:
 host = torch.empty(a.n, dtype=torch.uint8, pin_memory=True)
 cfg = synth.c2(a.n, seed=synth.SEEDS["C2"], m=64, ref=host.numpy())
 ev, pool, pat = cfg["events"], cfg["pool"], cfg["pattern"]
+# like bench.py's e2e legs: all of the step's host inputs in pinned memory (reference ranks, journal events, insertion pool)
+ev_pin = torch.empty(ev.nbytes, dtype=torch.uint8, pin_memory=True)
+ev_pin.numpy()[:] = ev.view(np.uint8)
+ev = ev_pin.numpy().view(sp.EVENT_DTYPE)
+pool_pin = torch.empty(max(pool.nbytes, 1), dtype=torch.uint8, pin_memory=True)
+pool_pin.numpy()[:pool.nbytes] = pool
+pool = pool_pin.numpy()[:pool.nbytes]
 # derived length: reference + sum(ins - del)
 n_der = int(a.n + (ev["ins_len"].astype(np.int64) - ev["del_len"].astype(np.int64)).sum())
 args = argparse.Namespace(steps=5, e2e_steps=5)
