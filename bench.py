@@ -17,6 +17,7 @@ Prints ONE JSON line on rank 0.
 from __future__ import annotations
 
 import argparse
+import gc
 import json
 import os
 import subprocess
@@ -74,6 +75,8 @@ class ClockSampler:
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
+    PERIOD_MS = "50"
+
     def __init__(self, index):
         self.index = index
         self.lines = []
@@ -82,7 +85,7 @@ class ClockSampler:
     def __enter__(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "50", "-i", str(self.index)], stdout=subprocess.PIPE,
+                                          "-lms", str(self.PERIOD_MS), "-i", str(self.index)], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._pump, daemon=True)
             self.t.start()
@@ -248,6 +251,8 @@ class HitGatherShm:
         if self.rank == 0:
             os.unlink(path)                       # the segment lives as long as it is mapped
         self.grid = self.mm.reshape(2 * self.world, self.region)
+        for g in (0, 1):                          # this rank's slots: page-table entries made now, not in the timed region
+            self.grid[self._row(g, self.rank), self.FLAG:] = 0
         self.flags = self.grid[:, :8].view(np.uint64).reshape(-1)
         self.counts = self.grid[:, self.FLAG:self.FLAG + 8 * passes].view(np.uint64)          # [2 * world, passes]
         self.gen = 0
@@ -339,6 +344,11 @@ def time_search(sp, torch, ctx, stream, store, pattern, hits, steps, warmup, flu
     ke = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
+    # no cyclic garbage collection inside the few milliseconds of the timed region (one generation-2 pass of the
+    # interpreter on one rank is a stall of the whole job: the other ranks wait for it in the final gather)
+    gc.collect()
+    gc_was_on = gc.isenabled()
+    gc.disable()
     if gather is not None:
         gather.barrier()        # the ranks enter the timed region together (the warm-up above leaves them skewed)
     flush_ms = 0.0
@@ -378,6 +388,8 @@ def time_search(sp, torch, ctx, stream, store, pattern, hits, steps, warmup, flu
         merged_hits = gather.finish() // max(1, steps)
     e1.record(stream)
     torch.cuda.synchronize()
+    if gc_was_on:
+        gc.enable()
     kern = [ks[i].elapsed_time(ke[i]) for i in range(steps)]
     total = e0.elapsed_time(e1)
     time_search.gather_ms = em.elapsed_time(e1) if gather is not None else None

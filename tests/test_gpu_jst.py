@@ -259,3 +259,38 @@ def test_jst_launch_finish_in_rotation_equals_the_one_call_search(ctx):
     for (_, _, _, p) in pats:
         p.close()
     jst.close(); store.close()
+
+
+def test_jst_window_groups_dealt_into_stripes(ctx, monkeypatch):
+    """inside a length bucket the 32-window groups are dealt into stripes so that the shards of a bucket hold short and
+    long windows alike (jst_prepare); with 2 stripes a small tree takes that path too.  Hit lists: unchanged, sharded or not."""
+    n_ref, n_hap, n_var, seed = 40_000, 90, 2500, 41
+    ref, var, pool, cov = make_jst(n_ref, n_var, n_hap, seed, p_snp=0.6, p_ins=0.2, max_indel=8, af_max=0.7)
+    ev = var.astype(orc.EVENT_DTYPE)
+    rng = np.random.default_rng(seed)
+    store = sp.Store.from_host(ctx, ref)
+    seq = orc.jst_haplotype(ref, ev, pool, cov, 7)
+    cases = []
+    for alg, m, k in [(sp.ALG_MYERS, 45, 3), (sp.ALG_SHIFTOR, 13, 0)]:
+        s0 = int(rng.integers(0, len(seq) - m))
+        pat = seq[s0:s0 + m].copy()
+        cases.append((alg, pat, k, orc.jst_search(alg, ref, ev, pool, cov, n_hap, pat, k)))
+    for stripes in ("2", "3", "64"):
+        monkeypatch.setenv("SPMB_JST_STRIPES", stripes)
+        jst = sp.Jst(ctx, store, var, pool, cov, n_hap)
+        for alg, pat, k, want in cases:
+            p = sp.Pattern(ctx, alg, pat, k)
+            got = jst.search(p)
+            assert jst.last_stats()["windows"] > 64 * 3
+            compare(got, want, f"stripes={stripes} alg={alg}")
+            parts = []
+            for sh in range(5):
+                ctx.set_shard(sh, 5)
+                parts.append(jst.search(p))
+            ctx.set_shard(0, 1)
+            merged = np.concatenate(parts)
+            merged = merged[np.lexsort((merged["end"], merged["seq_id"], merged["pattern_id"]))]
+            assert np.array_equal(merged, got), f"stripes={stripes}: shards partition the list"
+            p.close()
+        jst.close()
+    store.close()
