@@ -4,8 +4,8 @@
     python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
     python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU algorithms (oracle port)
 
-A "step" is one search pass (kernel launch -> sorted hit list on the host; at N > 1 also the gather of every
-rank's hit list to rank 0) over one resident sequence store.  Headline workload = BASELINE.json configs[1] at
+A "step" is one search pass (kernel launch -> sorted hit list on the host) over one resident sequence store; at N > 1 the
+hit lists of all passes are gathered to every rank behind the last pass, inside the timed region (HitGatherShm).  Headline workload = BASELINE.json configs[1] at
 steady-state scale ("C2x"): Shift-Or exact search, m=64, over a journaled sequence (reference + 1% SNP/indel
 journal), N = 3.2 Gbp per GPU so that the packed text (0.25 B/bp = 800 MB) exceeds the 126 MB L2.
 The same line also carries: the end-to-end legs (host buffers in, hits out: one GPU per rank, ONE host haystack
@@ -515,7 +515,7 @@ def run_ours(args):
                        "planted_across_an_edit": cfg["straddling"], "journal_events": int(len(ev)),
                        "row_len": js.row_len, "journal_materialise_ms": journal_ms,
                        "journal_materialise_note": "spmb_store_create_journaled on a resident base, events from pinned host "
-                                                   "memory: event upload + prefix + pack_chunks_kernel<JournalSource>",
+                                                   "memory: event upload + prefix sums + journal_rec_kernel + journal_derive_kernel + pack_chunks_kernel",
                        "hit_lists_gathered": gather_note(gather),
                        "merged_hits_per_pass_rank0": getattr(time_search, "merged_hits", None),
                        "final_gather_ms_this_rank": getattr(time_search, "gather_ms", None),
