@@ -220,6 +220,7 @@ class HitGatherShm:
         self.gathers = 0
         self.overflow = False
         self.mm = None
+        self._fb = None      # the NCCL form, when /dev/shm has no room for the segment
 
     @staticmethod
     def usable(world):
@@ -238,6 +239,21 @@ class HitGatherShm:
         self.rec_bytes = self.cap * 24
         self.region = (self.FLAG + 8 * passes + passes * self.rec_bytes + 63) // 64 * 64   # flag | counts | records
         total = 2 * self.world * self.region
+        # /dev/shm may be small (containers: 64 MB): writing past its free space is a SIGBUS, so every rank looks, the
+        # ranks agree (MIN), and without room the NCCL form takes over
+        try:
+            st = os.statvfs("/dev/shm")
+            room = st.f_bavail * st.f_frsize >= 2 * total + (8 << 20)
+        except OSError:
+            room = False
+        if os.environ.get("SPMB_BENCH_SHM_NO_ROOM"):    # test switch
+            room = False
+        ok = torch.tensor([1 if room else 0], dtype=torch.int64, device=self.dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok.item()) == 0:
+            self._fb = HitGather(torch, dist, self.dev, self.world)
+            self._fb.prepare(n_first, passes)
+            return
         HitGatherShm.serial = getattr(HitGatherShm, "serial", 0) + 1
         path = "/dev/shm/spmb_gather_%s_%s_%d" % (os.environ.get("MASTER_PORT", "0"),
                                                   os.environ.get("TORCHELASTIC_RUN_ID", "0"), HitGatherShm.serial)
@@ -262,6 +278,8 @@ class HitGatherShm:
         return (gen & 1) * self.world + rank
 
     def add(self, i, hits):
+        if self._fb:
+            return self._fb.add(i, hits)
         n = len(hits)
         if n > self.cap:
             self.overflow = True
@@ -274,6 +292,8 @@ class HitGatherShm:
 
     def finish(self):
         """publish this rank's lists, wait for every rank's: returns the merged record count over ranks and passes"""
+        if self._fb:
+            return self._fb.finish()
         self.gen += 1
         g = self.gen
         base = (g & 1) * self.world
@@ -288,12 +308,16 @@ class HitGatherShm:
 
     def barrier(self):
         """the ranks leave within microseconds of each other (a flag exchange, no lists)"""
+        if self._fb:
+            return self._fb.barrier()
         self.counts[self._row(self.gen + 1, self.rank), :] = 0
         self.finish()
         self.gathers -= 1
 
     def merged(self, hit_dtype, i=0):
         """the merged list of pass i of the last gather (rank-major), for checks outside the timed region"""
+        if self._fb:
+            return self._fb.merged(hit_dtype, i)
         base = (self.gen & 1) * self.world
         parts = []
         o = self.FLAG + 8 * self.passes + i * self.rec_bytes
@@ -306,7 +330,7 @@ class HitGatherShm:
 def gather_note(gather):
     if gather is None:
         return False
-    if isinstance(gather, HitGatherShm):
+    if isinstance(gather, HitGatherShm) and gather._fb is None:
         return ("all passes' lists gathered inside the timed region: ranks of one host write their (host-resident) lists into a "
                 "shared-memory segment and wait for each other's flags behind the last pass; no device bounce")
     return "all passes' lists in one final all_gather (NCCL) inside the timed region"
