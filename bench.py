@@ -367,6 +367,9 @@ def time_search(sp, torch, ctx, stream, store, pattern, hits, steps, warmup, flu
     ks = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
     ke = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    em = torch.cuda.Event(enable_timing=True)
+    for ev_ in ks + ke + [e0, e1, em]:
+        ev_.record(stream)      # torch creates the CUDA event at its first record: here, not inside the timed region
     torch.cuda.synchronize()
     # no cyclic garbage collection inside the few milliseconds of the timed region (one generation-2 pass of the
     # interpreter on one rank is a stall of the whole job: the other ranks wait for it in the final gather)
@@ -406,7 +409,6 @@ def time_search(sp, torch, ctx, stream, store, pattern, hits, steps, warmup, flu
             gather.add(i, h)
         if trace is not None:
             trace.append(("finish", i, (t_a - t_origin) * 1e3, (t_b - t_origin) * 1e3, (time.perf_counter() - t_origin) * 1e3))
-    em = torch.cuda.Event(enable_timing=True)
     em.record(stream)                                          # last pass collected: what follows is the gather alone
     if gather is not None:                                     # the final gather: all passes' lists, inside the timed region
         merged_hits = gather.finish() // max(1, steps)
